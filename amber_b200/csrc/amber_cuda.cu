@@ -1,0 +1,847 @@
+// amber_cuda.cu -- host side of libamber_cuda.so: the C ABI of include/amber_cuda.h.
+//
+// Scene preparation (flattening, light table, lens constants, acceleration build)
+// runs here on the host in float arithmetic that mirrors the reference constructors
+// it replaces; everything per-ray runs in the kernels of kernels.cuh.
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/amber_cuda.h"
+#include "bvh.cuh"
+#include "bvh_build.h"
+#include "kernels.cuh"
+
+namespace amber_cuda {
+
+
+namespace detail {
+
+thread_local std::string g_create_error;
+std::atomic<uint64_t> g_next_ctx_id{1};
+// which context's data currently sits in this device's __constant__ banks
+std::atomic<uint64_t> g_const_owner[64];
+
+template <class T>
+struct DeviceBuffer {
+  T* ptr = nullptr;
+  size_t count = 0;
+  cudaError_t resize(size_t n) {
+    if (n <= count && ptr) return cudaSuccess;
+    if (ptr) cudaFree(ptr);
+    ptr = nullptr;
+    count = 0;
+    if (n == 0) return cudaSuccess;
+    const cudaError_t err = cudaMalloc(&ptr, n * sizeof(T));
+    if (err == cudaSuccess) count = n;
+    return err;
+  }
+  cudaError_t upload(const std::vector<T>& host, cudaStream_t stream) {
+    cudaError_t err = resize(host.size());
+    if (err != cudaSuccess || host.empty()) return err;
+    return cudaMemcpyAsync(ptr, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice, stream);
+  }
+  void release() {
+    if (ptr) cudaFree(ptr);
+    ptr = nullptr;
+    count = 0;
+  }
+};
+
+}  // namespace detail
+}  // namespace amber_cuda
+
+using namespace amber_cuda;
+using namespace amber_cuda::detail;
+
+struct amber_cuda_ctx {
+  uint64_t id = 0;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+  std::string error;
+
+  // scene
+  bool has_scene = false;
+  bool use_bvh = false;
+  ConstScene const_scene;
+  CameraDev camera;
+  bool has_sensor = false;
+  SceneView view{};
+  std::vector<int32_t> internal_to_prim;
+  DeviceBuffer<TriShade> d_tri_shade;
+  DeviceBuffer<TriIsect> d_tri_isect;
+  DeviceBuffer<float4> d_spheres;
+  DeviceBuffer<int32_t> d_tri_material, d_sphere_material, d_internal_to_prim;
+  DeviceBuffer<MaterialDev> d_materials;
+  DeviceBuffer<LightDev> d_lights;
+  DeviceBuffer<float4> d_bvh_nodes;
+  uint32_t bvh_nodes = 0;
+
+  // film
+  DeviceBuffer<float4> d_film;
+  DeviceBuffer<float> d_resolved;
+  uint64_t samples_done = 0;
+
+  // path pool
+  PathPool pool{};
+  DeviceBuffer<float4> d_ray_o, d_ray_d, d_hit, d_thr, d_sh_o, d_sh_d, d_sh_c;
+  DeviceBuffer<uint4> d_meta;
+  DeviceBuffer<uint32_t> d_q_new;
+  DeviceBuffer<Control> d_ctl;
+  Control* h_ctl = nullptr;  // pinned
+
+  // scratch for the host-buffer entry points
+  DeviceBuffer<float> d_scratch_f[6];
+  DeviceBuffer<int32_t> d_scratch_i[2];
+  DeviceBuffer<float4> d_scratch_4[3];
+
+  // statistics
+  amber_cuda_stats stats{};
+  bool profiling = false;
+};
+
+namespace amber_host {
+
+int fail(amber_cuda_ctx* ctx, int code, const char* fmt, ...) {
+  char buffer[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buffer, sizeof buffer, fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->error = buffer; else g_create_error = buffer;
+  return code;
+}
+
+#define CUDA_TRY(ctx, expr)                                                                   \
+  do {                                                                                        \
+    const cudaError_t err__ = (expr);                                                         \
+    if (err__ != cudaSuccess)                                                                 \
+      return fail(ctx, AMBER_CUDA_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(err__), \
+                  __FILE__, __LINE__);                                                        \
+  } while (0)
+
+inline unsigned int blocks_for(uint64_t n, int block = kBlock) {
+  return static_cast<unsigned int>((n + block - 1) / block);
+}
+
+// --- float3 host helpers: every operation rounds to float, as the reference's
+// Vector3<float> arithmetic does (built without FMA, CMakeLists.txt:5) ------------
+struct F3 {
+  float x, y, z;
+};
+inline F3 sub(F3 a, F3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline F3 crossf(F3 u, F3 v) {
+  return {u.y * v.z - u.z * v.y, u.z * v.x - u.x * v.z, u.x * v.y - u.y * v.x};
+}
+inline float dotf(F3 a, F3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline float lengthf(F3 a) { return std::sqrt(dotf(a, a)); }
+inline F3 normalizef(F3 a) {
+  const float l = lengthf(a);
+  return {a.x / l, a.y / l, a.z / l};
+}
+
+void make_triangle(const float* v, TriIsect& isect, TriShade& shade) {
+  const F3 v0{v[0], v[1], v[2]}, v1{v[3], v[4], v[5]}, v2{v[6], v[7], v[8]};
+  const F3 e1 = sub(v1, v0), e2 = sub(v2, v0);
+  const F3 normal = normalizef(crossf(e1, e2));  // primitive_triangle.cc:59-68
+  shade.v0_nx = make_float4(v0.x, v0.y, v0.z, normal.x);
+  shade.e1_ny = make_float4(e1.x, e1.y, e1.z, normal.y);
+  shade.e2_nz = make_float4(e2.x, e2.y, e2.z, normal.z);
+  // plane form from the float edges, evaluated in double and rounded once
+  const double a[3] = {e1.x, e1.y, e1.z}, b[3] = {e2.x, e2.y, e2.z};
+  const double n[3] = {a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]};
+  const double nn = n[0] * n[0] + n[1] * n[1] + n[2] * n[2];
+  const double nu[3] = {(b[1] * n[2] - b[2] * n[1]) / nn, (b[2] * n[0] - b[0] * n[2]) / nn,
+                        (b[0] * n[1] - b[1] * n[0]) / nn};
+  const double nv[3] = {(n[1] * a[2] - n[2] * a[1]) / nn, (n[2] * a[0] - n[0] * a[2]) / nn,
+                        (n[0] * a[1] - n[1] * a[0]) / nn};
+  isect.n_v0x = make_float4((float)n[0], (float)n[1], (float)n[2], v0.x);
+  isect.nu_v0y = make_float4((float)nu[0], (float)nu[1], (float)nu[2], v0.y);
+  isect.nv_v0z = make_float4((float)nv[0], (float)nv[1], (float)nv[2], v0.z);
+}
+
+// BasicThin::BasicThin, src/amber/scene/lens_thin.cc:32-57
+int make_lens(amber_cuda_ctx* ctx, const amber_cuda_lens& in, LensDev& lens) {
+  if (in.n_blades < 1 || in.n_blades > kMaxBlades)
+    return fail(ctx, AMBER_CUDA_EINVAL, "lens.n_blades must be in [1, %d]", kMaxBlades);
+  const float* t = in.transform;
+  lens.origin[0] = t[3]; lens.origin[1] = t[7]; lens.origin[2] = t[11];
+  const float e11 = t[0], e12 = t[1], e13 = t[2], e21 = t[4], e22 = t[5], e23 = t[6], e31 = t[8],
+              e32 = t[9], e33 = t[10];
+  const float g[9] = {e11, e12, e13, e21, e22, e23, e31, e32, e33};
+  std::memcpy(lens.global, g, sizeof g);
+  // Matrix3::Inverse, include/amber/prelude/matrix3.h:110-145
+  const float det = e11 * (e22 * e33 - e23 * e32) - e21 * (e12 * e33 - e13 * e32) + e31 * (e12 * e23 - e13 * e22);
+  if (det == 0.0f) return fail(ctx, AMBER_CUDA_EINVAL, "lens transform is singular");
+  const float dinv = 1 / det;
+  const float inv[9] = {+dinv * (e22 * e33 - e23 * e32), -dinv * (e12 * e33 - e13 * e32), +dinv * (e12 * e23 - e13 * e22),
+                        -dinv * (e21 * e33 - e23 * e31), +dinv * (e11 * e33 - e13 * e31), -dinv * (e11 * e23 - e13 * e21),
+                        +dinv * (e21 * e32 - e22 * e31), -dinv * (e11 * e32 - e12 * e31), +dinv * (e11 * e22 - e12 * e21)};
+  std::memcpy(lens.local, inv, sizeof inv);
+  lens.focus_distance = in.focus_distance;
+  lens.sensor_distance = 1 / (1 / in.focal_length - 1 / in.focus_distance);
+  lens.n_blades = in.n_blades;
+  const float pi = kPiF;
+  const float nb = static_cast<float>(in.n_blades);
+  auto rim = [&](int i, float* out) {
+    const float angle = 2 * pi / nb * static_cast<float>(i);
+    const F3 p{in.radius * std::cos(angle), in.radius * std::sin(angle), in.radius * 0.0f};
+    out[0] = lens.origin[0] + (g[0] * p.x + g[1] * p.y + g[2] * p.z);
+    out[1] = lens.origin[1] + (g[3] * p.x + g[4] * p.y + g[5] * p.z);
+    out[2] = lens.origin[2] + (g[6] * p.x + g[7] * p.y + g[8] * p.z);
+  };
+  for (int i = 0; i < in.n_blades; i++) {
+    float* b = lens.blades[i];
+    rim(i, b);
+    rim(i + 1, b + 3);
+    b[6] = lens.origin[0]; b[7] = lens.origin[1]; b[8] = lens.origin[2];
+    const F3 v0{b[0], b[1], b[2]}, v1{b[3], b[4], b[5]}, v2{b[6], b[7], b[8]};
+    const F3 n = normalizef(crossf(sub(v1, v0), sub(v2, v0)));
+    b[9] = n.x; b[10] = n.y; b[11] = n.z;
+  }
+  const float* b0 = lens.blades[0];
+  const F3 v0{b0[0], b0[1], b0[2]}, v1{b0[3], b0[4], b0[5]}, v2{b0[6], b0[7], b0[8]};
+  const float area = lengthf(crossf(sub(v1, v0), sub(v2, v0))) / 2;  // Triangle::SurfaceArea
+  lens.p_area = 1.0f / (area * nb);
+  return AMBER_CUDA_OK;
+}
+
+int bind_constants(amber_cuda_ctx* ctx) {
+  if (ctx->device < 64 && g_const_owner[ctx->device].load() == ctx->id) return AMBER_CUDA_OK;
+  CUDA_TRY(ctx, cudaMemcpyToSymbolAsync(c_scene, &ctx->const_scene, sizeof(ConstScene), 0,
+                                        cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyToSymbolAsync(c_camera, &ctx->camera, sizeof(CameraDev), 0,
+                                        cudaMemcpyHostToDevice, ctx->stream));
+  if (ctx->device < 64) g_const_owner[ctx->device].store(ctx->id);
+  return AMBER_CUDA_OK;
+}
+
+void invalidate_constants(amber_cuda_ctx* ctx) {
+  if (ctx->device < 64 && g_const_owner[ctx->device].load() == ctx->id) g_const_owner[ctx->device].store(0);
+}
+
+int ensure_pool(amber_cuda_ctx* ctx, uint32_t slots) {
+  if (ctx->pool.n_slots == slots && ctx->d_ray_o.ptr) return AMBER_CUDA_OK;
+  CUDA_TRY(ctx, ctx->d_ray_o.resize(slots));
+  CUDA_TRY(ctx, ctx->d_ray_d.resize(slots));
+  CUDA_TRY(ctx, ctx->d_hit.resize(slots));
+  CUDA_TRY(ctx, ctx->d_thr.resize(slots));
+  CUDA_TRY(ctx, ctx->d_meta.resize(slots));
+  CUDA_TRY(ctx, ctx->d_q_new.resize(slots));
+  CUDA_TRY(ctx, ctx->d_sh_o.resize(slots));
+  CUDA_TRY(ctx, ctx->d_sh_d.resize(slots));
+  CUDA_TRY(ctx, ctx->d_sh_c.resize(slots));
+  ctx->pool.ray_o = ctx->d_ray_o.ptr;
+  ctx->pool.ray_d = ctx->d_ray_d.ptr;
+  ctx->pool.hit = ctx->d_hit.ptr;
+  ctx->pool.thr = ctx->d_thr.ptr;
+  ctx->pool.meta = ctx->d_meta.ptr;
+  ctx->pool.q_new = ctx->d_q_new.ptr;
+  ctx->pool.sh_o = ctx->d_sh_o.ptr;
+  ctx->pool.sh_d = ctx->d_sh_d.ptr;
+  ctx->pool.sh_c = ctx->d_sh_c.ptr;
+  ctx->pool.n_slots = slots;
+  return AMBER_CUDA_OK;
+}
+
+}  // namespace amber_host
+using namespace amber_host;
+
+// =====================================================================================
+//                                    C ABI
+// =====================================================================================
+extern "C" {
+
+int amber_cuda_abi_version(void) { return AMBER_CUDA_ABI_VERSION; }
+
+const char* amber_cuda_last_error(const amber_cuda_ctx* ctx) {
+  return ctx ? ctx->error.c_str() : g_create_error.c_str();
+}
+
+int amber_cuda_create(amber_cuda_ctx** out, int device) {
+  if (!out) return fail(nullptr, AMBER_CUDA_EINVAL, "out is NULL");
+  *out = nullptr;
+  int n_devices = 0;
+  if (cudaGetDeviceCount(&n_devices) != cudaSuccess || n_devices == 0) {
+    cudaGetLastError();
+    return fail(nullptr, AMBER_CUDA_ENODEV, "no CUDA device (libamber_cuda has no CPU fallback)");
+  }
+  if (device < 0 || device >= n_devices)
+    return fail(nullptr, AMBER_CUDA_EINVAL, "device %d out of range [0, %d)", device, n_devices);
+  amber_cuda_ctx* ctx = new amber_cuda_ctx();
+  ctx->id = g_next_ctx_id.fetch_add(1);
+  ctx->device = device;
+  cudaError_t err = cudaSetDevice(device);
+  if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+  if (err == cudaSuccess) err = cudaEventCreate(&ctx->ev_begin);
+  if (err == cudaSuccess) err = cudaEventCreate(&ctx->ev_end);
+  if (err == cudaSuccess) err = cudaMallocHost(&ctx->h_ctl, sizeof(Control));
+  if (err == cudaSuccess) err = ctx->d_ctl.resize(1);
+  if (err == cudaSuccess) err = cudaMemsetAsync(ctx->d_ctl.ptr, 0, sizeof(Control), ctx->stream);
+  if (err != cudaSuccess) {
+    fail(nullptr, AMBER_CUDA_ECUDA, "context creation failed: %s", cudaGetErrorString(err));
+    delete ctx;
+    return AMBER_CUDA_ECUDA;
+  }
+  *out = ctx;
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_destroy(amber_cuda_ctx* ctx) {
+  if (!ctx) return AMBER_CUDA_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  invalidate_constants(ctx);
+  ctx->d_tri_shade.release(); ctx->d_tri_isect.release(); ctx->d_spheres.release();
+  ctx->d_tri_material.release(); ctx->d_sphere_material.release(); ctx->d_internal_to_prim.release();
+  ctx->d_materials.release(); ctx->d_lights.release(); ctx->d_bvh_nodes.release();
+  ctx->d_film.release(); ctx->d_resolved.release();
+  ctx->d_ray_o.release(); ctx->d_ray_d.release(); ctx->d_hit.release(); ctx->d_thr.release();
+  ctx->d_sh_o.release(); ctx->d_sh_d.release(); ctx->d_sh_c.release();
+  ctx->d_meta.release(); ctx->d_q_new.release(); ctx->d_ctl.release();
+  for (auto& b : ctx->d_scratch_f) b.release();
+  for (auto& b : ctx->d_scratch_i) b.release();
+  for (auto& b : ctx->d_scratch_4) b.release();
+  if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
+  if (ctx->ev_begin) cudaEventDestroy(ctx->ev_begin);
+  if (ctx->ev_end) cudaEventDestroy(ctx->ev_end);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* scene) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!scene || (scene->n_primitives && !scene->primitives) || !scene->materials || scene->n_materials == 0)
+    return fail(ctx, AMBER_CUDA_EINVAL, "scene description is incomplete");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+
+  // ---- materials ---------------------------------------------------------------
+  std::vector<MaterialDev> materials(scene->n_materials);
+  for (uint32_t i = 0; i < scene->n_materials; i++) {
+    const amber_cuda_material& in = scene->materials[i];
+    if (in.kind < 0 || in.kind > AMBER_CUDA_MAT_EYE)
+      return fail(ctx, AMBER_CUDA_EINVAL, "material %u: unknown kind %d", i, in.kind);
+    MaterialDev m{};
+    m.kind = in.kind;
+    m.r = in.rgb[0]; m.g = in.rgb[1]; m.b = in.rgb[2];
+    m.param = in.param;
+    if (in.kind == AMBER_CUDA_MAT_REFRACTION || in.kind == AMBER_CUDA_MAT_EYE) m.r = m.g = m.b = 1.0f;
+    if (in.kind == AMBER_CUDA_MAT_REFRACTION) {
+      // BasicRefraction::Fresnel, material_refraction.cc:265-269: std::pow(float, int) is double
+      const float q = (in.param - 1) / (in.param + 1);
+      m.r0 = static_cast<float>(std::pow(static_cast<double>(q), 2));
+    }
+    m.nee = (in.kind == AMBER_CUDA_MAT_LAMBERTIAN || in.kind == AMBER_CUDA_MAT_PHONG) ? 1 : 0;
+    materials[i] = m;
+  }
+
+  // ---- primitives: triangles first, then spheres (internal order) ---------------
+  std::vector<uint32_t> tri_ids, sphere_ids;
+  for (uint32_t i = 0; i < scene->n_primitives; i++) {
+    const amber_cuda_primitive& p = scene->primitives[i];
+    if (p.material < 0 || static_cast<uint32_t>(p.material) >= scene->n_materials)
+      return fail(ctx, AMBER_CUDA_EINVAL, "primitive %u: material %d out of range", i, p.material);
+    if (p.kind == AMBER_CUDA_PRIM_TRIANGLE) tri_ids.push_back(i);
+    else if (p.kind == AMBER_CUDA_PRIM_SPHERE) sphere_ids.push_back(i);
+    else return fail(ctx, AMBER_CUDA_EINVAL, "primitive %u: unknown kind %d", i, p.kind);
+  }
+  if (sphere_ids.size() > static_cast<size_t>(kMaxConstSpheres))
+    return fail(ctx, AMBER_CUDA_EINVAL, "at most %d spheres are supported", kMaxConstSpheres);
+  if (tri_ids.size() >= (1u << 28)) return fail(ctx, AMBER_CUDA_EINVAL, "too many triangles");
+  const bool use_bvh = tri_ids.size() > static_cast<size_t>(kMaxConstTris);
+
+  bvh_build::WideBvhHost bvh;
+  if (use_bvh) {
+    std::vector<float> verts(tri_ids.size() * 9);
+    for (size_t k = 0; k < tri_ids.size(); k++)
+      std::memcpy(&verts[9 * k], scene->primitives[tri_ids[k]].data, 9 * sizeof(float));
+    bvh = bvh_build::build(verts.data(), static_cast<uint32_t>(tri_ids.size()));
+    std::vector<uint32_t> reordered(tri_ids.size());
+    for (size_t k = 0; k < tri_ids.size(); k++) reordered[k] = tri_ids[bvh.order[k]];
+    tri_ids.swap(reordered);
+  }
+
+  const size_t n_tris = tri_ids.size(), n_spheres = sphere_ids.size();
+  std::vector<TriIsect> tri_isect(n_tris);
+  std::vector<TriShade> tri_shade(n_tris);
+  std::vector<int32_t> tri_material(n_tris), sphere_material(n_spheres);
+  std::vector<float4> spheres(n_spheres);
+  ctx->internal_to_prim.assign(n_tris + n_spheres, 0);
+  for (size_t k = 0; k < n_tris; k++) {
+    const amber_cuda_primitive& p = scene->primitives[tri_ids[k]];
+    make_triangle(p.data, tri_isect[k], tri_shade[k]);
+    tri_material[k] = p.material;
+    ctx->internal_to_prim[k] = static_cast<int32_t>(tri_ids[k]);
+  }
+  for (size_t k = 0; k < n_spheres; k++) {
+    const amber_cuda_primitive& p = scene->primitives[sphere_ids[k]];
+    spheres[k] = make_float4(p.data[0], p.data[1], p.data[2], p.data[3]);
+    sphere_material[k] = p.material;
+    ctx->internal_to_prim[n_tris + k] = static_cast<int32_t>(sphere_ids[k]);
+  }
+
+  // ---- lights: emitting triangles, LightSet::LightSet (light_set.h:61-81) -------
+  struct HostLight {
+    size_t tri;
+    float power, irradiance_sum;
+  };
+  std::vector<HostLight> host_lights;
+  for (size_t k = 0; k < n_tris; k++) {
+    const MaterialDev& m = materials[tri_material[k]];
+    if (m.kind != AMBER_CUDA_MAT_DIFFUSE_LIGHT) continue;
+    const TriShade& t = tri_shade[k];
+    const F3 e1{t.e1_ny.x, t.e1_ny.y, t.e1_ny.z}, e2{t.e2_nz.x, t.e2_nz.y, t.e2_nz.z};
+    const float area = lengthf(crossf(e1, e2)) / 2;  // Triangle::SurfaceArea
+    // DiffuseLight::Irradiance = radiance * pi; Power = Sum(area * irradiance), object.h:98-103
+    const float ir = m.r * kPiF, ig = m.g * kPiF, ib = m.b * kPiF;
+    const float power = area * ir + area * ig + area * ib;
+    if (power > 0) host_lights.push_back({k, power, ir + ig + ib});
+  }
+  std::stable_sort(host_lights.begin(), host_lights.end(),
+                   [](const HostLight& a, const HostLight& b) { return a.power < b.power; });
+  std::vector<LightDev> lights(host_lights.size());
+  float total_power = 0;
+  for (size_t i = 0; i < host_lights.size(); i++) total_power += host_lights[i].power;
+  float cumulative = 0;
+  for (size_t i = 0; i < host_lights.size(); i++) {
+    const TriShade& t = tri_shade[host_lights[i].tri];
+    const MaterialDev& m = materials[tri_material[host_lights[i].tri]];
+    cumulative += host_lights[i].power;
+    const float pdf_area = host_lights[i].irradiance_sum / total_power;  // LightSet::PDFArea, light_set.h:106-111
+    LightDev& l = lights[i];
+    l.v0 = make_float4(t.v0_nx.x, t.v0_nx.y, t.v0_nx.z, cumulative);
+    const amber_cuda_primitive& p = scene->primitives[tri_ids[host_lights[i].tri]];
+    l.v1 = make_float4(p.data[3], p.data[4], p.data[5], 0.0f);
+    l.v2 = make_float4(p.data[6], p.data[7], p.data[8], 0.0f);
+    l.n = make_float4(t.v0_nx.w, t.e1_ny.w, t.e2_nz.w, 0.0f);
+    l.le_over_pdf = make_float4(m.r / pdf_area, m.g / pdf_area, m.b / pdf_area, 0.0f);
+  }
+
+  // ---- lens --------------------------------------------------------------------
+  LensDev lens{};
+  const int lens_rc = make_lens(ctx, scene->lens, lens);
+  if (lens_rc != AMBER_CUDA_OK) return lens_rc;
+
+  // ---- commit ------------------------------------------------------------------
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  invalidate_constants(ctx);
+  ctx->use_bvh = use_bvh;
+  std::memset(&ctx->const_scene, 0, sizeof(ConstScene));
+  ctx->const_scene.n_tris = use_bvh ? 0 : static_cast<int32_t>(n_tris);
+  ctx->const_scene.n_spheres = static_cast<int32_t>(n_spheres);
+  if (!use_bvh)
+    for (size_t k = 0; k < n_tris; k++) ctx->const_scene.tri_isect[k] = tri_isect[k];
+  for (size_t k = 0; k < n_spheres; k++) ctx->const_scene.sphere[k] = spheres[k];
+  ctx->camera.lens = lens;
+
+  CUDA_TRY(ctx, ctx->d_tri_shade.upload(tri_shade, ctx->stream));
+  CUDA_TRY(ctx, ctx->d_tri_isect.upload(tri_isect, ctx->stream));
+  CUDA_TRY(ctx, ctx->d_spheres.upload(spheres, ctx->stream));
+  CUDA_TRY(ctx, ctx->d_tri_material.upload(tri_material, ctx->stream));
+  CUDA_TRY(ctx, ctx->d_sphere_material.upload(sphere_material, ctx->stream));
+  CUDA_TRY(ctx, ctx->d_internal_to_prim.upload(ctx->internal_to_prim, ctx->stream));
+  CUDA_TRY(ctx, ctx->d_materials.upload(materials, ctx->stream));
+  CUDA_TRY(ctx, ctx->d_lights.upload(lights, ctx->stream));
+  if (use_bvh) {
+    std::vector<float4> nodes(bvh.nodes.size() / 4);
+    std::memcpy(nodes.data(), bvh.nodes.data(), bvh.nodes.size() * sizeof(float));
+    CUDA_TRY(ctx, ctx->d_bvh_nodes.upload(nodes, ctx->stream));
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+
+  SceneView& view = ctx->view;
+  view.tri_shade = ctx->d_tri_shade.ptr;
+  view.spheres = ctx->d_spheres.ptr;
+  view.tri_material = ctx->d_tri_material.ptr;
+  view.sphere_material = ctx->d_sphere_material.ptr;
+  view.materials = ctx->d_materials.ptr;
+  view.lights = ctx->d_lights.ptr;
+  view.n_tris = static_cast<int32_t>(n_tris);
+  view.n_spheres = static_cast<int32_t>(n_spheres);
+  view.n_lights = static_cast<int32_t>(lights.size());
+  view.total_power = total_power;
+  view.bvh_nodes = ctx->d_bvh_nodes.ptr;
+  view.tri_isect = ctx->d_tri_isect.ptr;
+  view.bvh_root = use_bvh ? bvh.root : kEmptyChild;
+  ctx->bvh_nodes = use_bvh ? bvh.n_nodes : 0;
+  ctx->has_scene = true;
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_set_sensor(amber_cuda_ctx* ctx, uint32_t width, uint32_t height, float film_width,
+                          float film_height) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (width == 0 || height == 0 || !(film_width > 0) || !(film_height > 0))
+    return fail(ctx, AMBER_CUDA_EINVAL, "bad sensor %ux%u, film %g x %g", width, height, film_width, film_height);
+  if (static_cast<uint64_t>(width) * height >= (1ull << 31))
+    return fail(ctx, AMBER_CUDA_EINVAL, "sensor too large");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  invalidate_constants(ctx);
+  SensorDev& s = ctx->camera.sensor;
+  s.width = width;
+  s.height = height;
+  s.film_width = film_width;
+  s.film_height = film_height;
+  // sensor.Size() / sensor.SceneArea(): pixel count (integer) over a float product
+  s.size_over_area = static_cast<float>(static_cast<uint64_t>(width) * height) / (film_width * film_height);
+  ctx->has_sensor = true;
+  CUDA_TRY(ctx, ctx->d_film.resize(static_cast<size_t>(width) * height));
+  return amber_cuda_film_clear(ctx);
+}
+
+int amber_cuda_film_clear(amber_cuda_ctx* ctx) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const size_t n = static_cast<size_t>(ctx->camera.sensor.width) * ctx->camera.sensor.height;
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_film.ptr, 0, n * sizeof(float4), ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_ctl.ptr, 0, sizeof(Control), ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->samples_done = 0;
+  return AMBER_CUDA_OK;
+}
+
+}  // extern "C"
+
+namespace amber_host {
+
+__global__ void control_begin_kernel(Control* ctl, unsigned long long total_paths, unsigned int slots) {
+  ctl->next_path = 0;
+  ctl->total_paths = total_paths;
+  ctl->n_new = slots;
+  ctl->n_shadow = 0;
+  ctl->n_alive = 0;
+  ctl->done = 0;
+}
+
+constexpr int kStepsPerPoll = 8;
+constexpr uint32_t kDefaultPoolPaths = 1u << 21;
+
+struct KernelTimer {
+  // profiling mode: one event pair per launch, summed per kernel class after the render
+  std::vector<cudaEvent_t> events;
+  std::vector<int> kinds;
+  size_t used = 0;
+  cudaEvent_t next() {
+    if (used == events.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      events.push_back(e);
+    }
+    return events[used++];
+  }
+  ~KernelTimer() {
+    for (cudaEvent_t e : events) cudaEventDestroy(e);
+  }
+};
+
+template <class Accel>
+int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dynamic_smem) {
+  const unsigned int grid = blocks_for(args.pool.n_slots);
+  cudaStream_t stream = ctx->stream;
+  KernelTimer timer;
+  const bool profile = ctx->profiling;
+  double ms_by_kind[4] = {0, 0, 0, 0};  // raygen, extend, shade, connect
+  uint64_t extend_launches = 0;
+  auto timed = [&](int kind, auto&& launch) {
+    if (profile) {
+      cudaEventRecord(timer.next(), stream);
+      launch();
+      cudaEventRecord(timer.next(), stream);
+      timer.kinds.push_back(kind);
+    } else {
+      launch();
+    }
+  };
+  cudaEvent_t poll_event[2];
+  Control* poll_copy = ctx->h_ctl;  // pinned, two slots are overkill: reads happen after the event
+  CUDA_TRY(ctx, cudaEventCreateWithFlags(&poll_event[0], cudaEventDisableTiming));
+  CUDA_TRY(ctx, cudaEventCreateWithFlags(&poll_event[1], cudaEventDisableTiming));
+  int rc = AMBER_CUDA_OK;
+  bool done = false;
+  for (int batch = 0; !done; batch++) {
+    for (int step = 0; step < kStepsPerPoll; step++) {
+      timed(0, [&] { raygen_kernel<<<grid, kBlock, 0, stream>>>(args); });
+      bookkeep_kernel<<<1, 1, 0, stream>>>(args.ctl);
+      timed(1, [&] { extend_kernel<Accel><<<grid, kBlock, dynamic_smem, stream>>>(args); });
+      timed(2, [&] { shade_kernel<<<grid, kBlock, 0, stream>>>(args); });
+      if (nee) timed(3, [&] { connect_kernel<Accel><<<grid, kBlock, dynamic_smem, stream>>>(args); });
+      ctx->stats.kernel_launches += nee ? 5 : 4;
+      extend_launches++;
+    }
+    // poll: the copy of batch b is read while batch b+1 is already queued
+    if (batch > 0) {
+      const cudaError_t err = cudaEventSynchronize(poll_event[(batch - 1) & 1]);
+      if (err != cudaSuccess) {
+        rc = fail(ctx, AMBER_CUDA_ECUDA, "render failed: %s", cudaGetErrorString(err));
+        break;
+      }
+      if (poll_copy[(batch - 1) & 1].done) done = true;
+    }
+    if (!done) {
+      cudaMemcpyAsync(&poll_copy[batch & 1], args.ctl, sizeof(Control), cudaMemcpyDeviceToHost, stream);
+      cudaEventRecord(poll_event[batch & 1], stream);
+    }
+  }
+  cudaEventDestroy(poll_event[0]);
+  cudaEventDestroy(poll_event[1]);
+  if (rc != AMBER_CUDA_OK) return rc;
+  CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+  if (profile) {
+    for (size_t k = 0; k < timer.kinds.size(); k++) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, timer.events[2 * k], timer.events[2 * k + 1]);
+      ms_by_kind[timer.kinds[k]] += ms;
+    }
+  }
+  ctx->stats.raygen_ms = ms_by_kind[0];
+  ctx->stats.extend_ms = ms_by_kind[1];
+  ctx->stats.shade_ms = ms_by_kind[2];
+  ctx->stats.connect_ms = ms_by_kind[3];
+  ctx->stats.extend_launches = extend_launches;
+  return AMBER_CUDA_OK;
+}
+
+size_t bvh_smem_bytes() { return static_cast<size_t>(kBvhStack) * kBlock * sizeof(int32_t); }
+
+}  // namespace amber_host
+using namespace amber_host;
+
+extern "C" {
+
+int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* params) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!params) return fail(ctx, AMBER_CUDA_EINVAL, "params is NULL");
+  if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
+  if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
+  if (params->estimator != AMBER_CUDA_ESTIMATOR_REFERENCE && params->estimator != AMBER_CUDA_ESTIMATOR_NEE)
+    return fail(ctx, AMBER_CUDA_EINVAL, "unknown estimator %d", params->estimator);
+  if (params->sample_begin + params->sample_count >= (1ull << 32))
+    return fail(ctx, AMBER_CUDA_EINVAL, "sample indices must stay below 2^32");
+  if (params->sample_count == 0) return AMBER_CUDA_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+
+  const uint32_t n_pixels = ctx->camera.sensor.width * ctx->camera.sensor.height;
+  const uint64_t total_paths = static_cast<uint64_t>(n_pixels) * params->sample_count;
+  uint64_t slots = params->pool_paths ? params->pool_paths : kDefaultPoolPaths;
+  slots = std::min<uint64_t>(slots, total_paths);
+  slots = std::max<uint64_t>(kBlock, (slots + kBlock - 1) / kBlock * kBlock);
+  int rc = ensure_pool(ctx, static_cast<uint32_t>(slots));
+  if (rc != AMBER_CUDA_OK) return rc;
+  rc = bind_constants(ctx);
+  if (rc != AMBER_CUDA_OK) return rc;
+
+  RenderArgs args{};
+  args.pool = ctx->pool;
+  args.scene = ctx->view;
+  args.ctl = ctx->d_ctl.ptr;
+  args.film = ctx->d_film.ptr;
+  args.seed = params->seed;
+  args.sample_begin = params->sample_begin;
+  args.n_pixels = n_pixels;
+  args.max_depth = params->max_depth ? std::min<uint32_t>(params->max_depth, 1u << 16) : (1u << 16);
+  args.estimator = params->estimator;
+
+  cudaStream_t stream = ctx->stream;
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_begin, stream));
+  control_begin_kernel<<<1, 1, 0, stream>>>(args.ctl, total_paths, args.pool.n_slots);
+  pool_reset_kernel<<<blocks_for(args.pool.n_slots), kBlock, 0, stream>>>(args);
+  ctx->stats.kernel_launches += 2;
+  const bool nee = params->estimator == AMBER_CUDA_ESTIMATOR_NEE && ctx->view.n_lights > 0;
+  if (ctx->use_bvh) {
+    rc = render_loop<WideBvh>(ctx, args, nee, bvh_smem_bytes());
+  } else {
+    rc = render_loop<ConstList>(ctx, args, nee, 0);
+  }
+  if (rc != AMBER_CUDA_OK) return rc;
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_end, stream));
+  CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_end));
+  CUDA_TRY(ctx, cudaGetLastError());
+  float ms = 0;
+  CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
+  ctx->stats.last_render_ms = ms;
+  ctx->samples_done += params->sample_count;
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_resolve(amber_cuda_ctx* ctx, float* host_rgb, uint64_t* samples_done) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
+  if (!host_rgb) return fail(ctx, AMBER_CUDA_EINVAL, "host_rgb is NULL");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const uint32_t n_pixels = ctx->camera.sensor.width * ctx->camera.sensor.height;
+  CUDA_TRY(ctx, ctx->d_resolved.resize(static_cast<size_t>(n_pixels) * 3));
+  const float inv = ctx->samples_done ? 1.0f / static_cast<float>(ctx->samples_done) : 0.0f;
+  resolve_kernel<<<blocks_for(n_pixels), kBlock, 0, ctx->stream>>>(ctx->d_film.ptr, n_pixels, inv,
+                                                                  ctx->d_resolved.ptr);
+  ctx->stats.kernel_launches++;
+  CUDA_TRY(ctx, cudaMemcpyAsync(host_rgb, ctx->d_resolved.ptr, static_cast<size_t>(n_pixels) * 3 * sizeof(float),
+                                cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (samples_done) *samples_done = ctx->samples_done;
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_film_device(amber_cuda_ctx* ctx, void** device_ptr, uint64_t* n_floats, uint64_t* samples_done) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
+  if (device_ptr) *device_ptr = ctx->d_film.ptr;
+  if (n_floats) *n_floats = static_cast<uint64_t>(ctx->camera.sensor.width) * ctx->camera.sensor.height * 4;
+  if (samples_done) *samples_done = ctx->samples_done;
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_film_set_samples(amber_cuda_ctx* ctx, uint64_t samples_done) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  ctx->samples_done = samples_done;
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_cast_device(amber_cuda_ctx* ctx, const void* ray_origin4, const void* ray_direction4, uint64_t n,
+                           void* hit4, float* elapsed_ms) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
+  if (n == 0) return AMBER_CUDA_OK;
+  if (!ray_origin4 || !ray_direction4 || !hit4) return fail(ctx, AMBER_CUDA_EINVAL, "NULL buffer");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  int rc = bind_constants(ctx);
+  if (rc != AMBER_CUDA_OK) return rc;
+  const float4* o = static_cast<const float4*>(ray_origin4);
+  const float4* d = static_cast<const float4*>(ray_direction4);
+  float4* h = static_cast<float4*>(hit4);
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_begin, ctx->stream));
+  if (ctx->use_bvh) {
+    cast_kernel<WideBvh><<<blocks_for(n), kBlock, bvh_smem_bytes(), ctx->stream>>>(ctx->view, o, d, n, h);
+  } else {
+    cast_kernel<ConstList><<<blocks_for(n), kBlock, 0, ctx->stream>>>(ctx->view, o, d, n, h);
+  }
+  ctx->stats.kernel_launches++;
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_end, ctx->stream));
+  CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_end));
+  CUDA_TRY(ctx, cudaGetLastError());
+  if (elapsed_ms) CUDA_TRY(ctx, cudaEventElapsedTime(elapsed_ms, ctx->ev_begin, ctx->ev_end));
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_cast(amber_cuda_ctx* ctx, const float* origins, const float* directions, uint64_t n,
+                    int32_t* prim, float* t) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
+  if (n == 0) return AMBER_CUDA_OK;
+  if (!origins || !directions || !prim || !t) return fail(ctx, AMBER_CUDA_EINVAL, "NULL buffer");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t stream = ctx->stream;
+  CUDA_TRY(ctx, ctx->d_scratch_f[0].resize(3 * n));
+  CUDA_TRY(ctx, ctx->d_scratch_f[1].resize(3 * n));
+  CUDA_TRY(ctx, ctx->d_scratch_f[2].resize(n));
+  CUDA_TRY(ctx, ctx->d_scratch_i[0].resize(n));
+  for (auto& b : ctx->d_scratch_4) CUDA_TRY(ctx, b.resize(n));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->d_scratch_f[0].ptr, origins, 3 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->d_scratch_f[1].ptr, directions, 3 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  pack_rays_kernel<<<blocks_for(n), kBlock, 0, stream>>>(ctx->d_scratch_f[0].ptr, ctx->d_scratch_f[1].ptr, n,
+                                                        ctx->d_scratch_4[0].ptr, ctx->d_scratch_4[1].ptr);
+  const int rc = amber_cuda_cast_device(ctx, ctx->d_scratch_4[0].ptr, ctx->d_scratch_4[1].ptr, n,
+                                        ctx->d_scratch_4[2].ptr, nullptr);
+  if (rc != AMBER_CUDA_OK) return rc;
+  unpack_hits_kernel<<<blocks_for(n), kBlock, 0, stream>>>(ctx->d_scratch_4[2].ptr, n, ctx->d_internal_to_prim.ptr,
+                                                          ctx->d_scratch_i[0].ptr, ctx->d_scratch_f[2].ptr);
+  ctx->stats.kernel_launches += 2;
+  CUDA_TRY(ctx, cudaMemcpyAsync(prim, ctx->d_scratch_i[0].ptr, n * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(t, ctx->d_scratch_f[2].ptr, n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+  CUDA_TRY(ctx, cudaGetLastError());
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_sample_light(amber_cuda_ctx* ctx, int32_t material, uint64_t n, const float* normal3,
+                            const float* dir_out3, const float* xi8, float* dir_in3, float* weight3,
+                            int32_t* draws) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
+  if (material < 0 || static_cast<size_t>(material) >= ctx->d_materials.count)
+    return fail(ctx, AMBER_CUDA_EINVAL, "material %d out of range", material);
+  if (n == 0) return AMBER_CUDA_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t stream = ctx->stream;
+  auto& f = ctx->d_scratch_f;
+  CUDA_TRY(ctx, f[0].resize(3 * n)); CUDA_TRY(ctx, f[1].resize(3 * n)); CUDA_TRY(ctx, f[2].resize(8 * n));
+  CUDA_TRY(ctx, f[3].resize(3 * n)); CUDA_TRY(ctx, f[4].resize(3 * n));
+  CUDA_TRY(ctx, ctx->d_scratch_i[0].resize(n));
+  CUDA_TRY(ctx, cudaMemcpyAsync(f[0].ptr, normal3, 3 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(f[1].ptr, dir_out3, 3 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(f[2].ptr, xi8, 8 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  sample_light_kernel<<<blocks_for(n), kBlock, 0, stream>>>(ctx->view, material, n, f[0].ptr, f[1].ptr, f[2].ptr,
+                                                           f[3].ptr, f[4].ptr, ctx->d_scratch_i[0].ptr);
+  ctx->stats.kernel_launches++;
+  CUDA_TRY(ctx, cudaMemcpyAsync(dir_in3, f[3].ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(weight3, f[4].ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(draws, ctx->d_scratch_i[0].ptr, n * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+  CUDA_TRY(ctx, cudaGetLastError());
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_eye_rays(amber_cuda_ctx* ctx, uint64_t n, const uint32_t* px, const uint32_t* py, const float* xi5,
+                        float* origin3, float* direction3, float* weight) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_scene || !ctx->has_sensor)
+    return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene and set_sensor must be called first");
+  if (n == 0) return AMBER_CUDA_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  int rc = bind_constants(ctx);
+  if (rc != AMBER_CUDA_OK) return rc;
+  cudaStream_t stream = ctx->stream;
+  auto& f = ctx->d_scratch_f;
+  CUDA_TRY(ctx, f[0].resize(5 * n)); CUDA_TRY(ctx, f[1].resize(3 * n)); CUDA_TRY(ctx, f[2].resize(3 * n));
+  CUDA_TRY(ctx, f[3].resize(n));
+  CUDA_TRY(ctx, ctx->d_scratch_i[0].resize(n)); CUDA_TRY(ctx, ctx->d_scratch_i[1].resize(n));
+  uint32_t* d_px = reinterpret_cast<uint32_t*>(ctx->d_scratch_i[0].ptr);
+  uint32_t* d_py = reinterpret_cast<uint32_t*>(ctx->d_scratch_i[1].ptr);
+  CUDA_TRY(ctx, cudaMemcpyAsync(d_px, px, n * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(d_py, py, n * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(f[0].ptr, xi5, 5 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  eye_rays_kernel<<<blocks_for(n), kBlock, 0, stream>>>(n, d_px, d_py, f[0].ptr, f[1].ptr, f[2].ptr, f[3].ptr);
+  ctx->stats.kernel_launches++;
+  CUDA_TRY(ctx, cudaMemcpyAsync(origin3, f[1].ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(direction3, f[2].ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(weight, f[3].ptr, n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+  CUDA_TRY(ctx, cudaGetLastError());
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_get_stats(amber_cuda_ctx* ctx, amber_cuda_stats* out) {
+  if (!ctx || !out) return AMBER_CUDA_EINVAL;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Control ctl;
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl.ptr, sizeof(Control), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  ctl = *ctx->h_ctl;
+  ctx->stats.paths = ctl.paths;
+  ctx->stats.closest_rays = ctl.closest_rays;
+  ctx->stats.shadow_rays = ctl.shadow_rays;
+  ctx->stats.truncated_paths = ctl.truncated;
+  ctx->stats.phong_capped = ctl.phong_capped;
+  ctx->stats.accel = ctx->use_bvh ? 1u : 0u;
+  ctx->stats.bvh_nodes = ctx->bvh_nodes;
+  *out = ctx->stats;
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_set_profiling(amber_cuda_ctx* ctx, int profile) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  ctx->profiling = profile != 0;
+  return AMBER_CUDA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,115 @@
+// intersect.cuh -- ray/triangle, ray/sphere and the constant-memory list traversal.
+#pragma once
+
+#include <math_constants.h>
+
+#include "scene_device.cuh"
+
+namespace amber_cuda {
+
+__constant__ ConstScene c_scene;  // single translation unit: defined here
+
+struct Ray {
+  float3 o, d;
+};
+
+// Triangle test.  Accepts iff u >= 0, v >= 0, u + v <= 1 (which implies u,v <= 1),
+// t > kEPS and t < t_best -- the inclusive edge rules and the strict `<` closest-hit
+// update of the reference (src/amber/scene/primitive_triangle.cc:108-125,
+// include/amber/raytracer/acceleration_bvh.h:346-351).  Every comparison is written
+// so that a NaN (n.d == 0, the reference's det == 0 case) rejects, as
+// include/amber/prelude/hit.h:90-94 does.
+__device__ __forceinline__ bool intersect_triangle(const float4 n_v0x, const float4 nu_v0y,
+                                                   const float4 nv_v0z, const Ray& ray,
+                                                   float t_best, float& t_out, float& u_out,
+                                                   float& v_out) {
+  const float3 T = v3(ray.o.x - n_v0x.w, ray.o.y - nu_v0y.w, ray.o.z - nv_v0z.w);
+  const float3 n = v3(n_v0x);
+  const float nd = dot(n, ray.d);
+  const float nT = dot(n, T);
+  const float t = __fdividef(-nT, nd);
+  const float3 h = v3(fmaf(t, ray.d.x, T.x), fmaf(t, ray.d.y, T.y), fmaf(t, ray.d.z, T.z));
+  const float u = dot(v3(nu_v0y), h);
+  const float v = dot(v3(nv_v0z), h);
+  const bool hit = (u >= 0.0f) & (v >= 0.0f) & (u + v <= 1.0f) & (t > kEpsF) & (t < t_best);
+  if (hit) {
+    t_out = t;
+    u_out = u;
+    v_out = v;
+  }
+  return hit;
+}
+
+// Sphere test, op for op src/amber/scene/primitive_sphere.cc:75-107 with
+// SolveQuadratic (include/amber/prelude/algebra.h:31-52): a = 1, b = -2 (c-o).d,
+// c = |c-o|^2 - r^2; cancellation-safe roots; the nearer root if > kEPS, else the
+// farther one if > kEPS.
+__device__ __forceinline__ bool intersect_sphere(const float4 sphere, const Ray& ray, float t_best,
+                                                 float& t_out) {
+  const float3 oc = v3(sphere.x - ray.o.x, sphere.y - ray.o.y, sphere.z - ray.o.z);
+  const float b = -2.0f * dot(oc, ray.d);
+  const float c = dot(oc, oc) - sphere.w * sphere.w;
+  const float disc = b * b - 4.0f * c;
+  if (!(disc >= 0.0f)) return false;
+  const float sqrt_d = sqrtf(disc);
+  float alpha = -b - sqrt_d;
+  float beta = -b + sqrt_d;
+  if (fabsf(alpha) < fabsf(beta)) {
+    alpha = __fdividef(c, beta) * 2.0f;
+    beta = beta * 0.5f;
+  } else {
+    beta = __fdividef(c, alpha) * 2.0f;
+    alpha = alpha * 0.5f;
+  }
+  const float t = alpha > kEpsF ? alpha : beta;
+  const bool hit = (t > kEpsF) & (t < t_best);
+  if (hit) t_out = t;
+  return hit;
+}
+
+// ---------------------------------------------------------------------------------
+// ConstList: every lane walks the same primitive list in __constant__ memory.
+// Closest-hit semantics of raytracer::List / a single-leaf BVH node
+// (include/amber/raytracer/acceleration_list.h:51-68, acceleration_bvh.h:343-356).
+struct ConstList {
+  static __device__ __forceinline__ HitRecord closest(const SceneView&, const Ray& ray) {
+    HitRecord hit;
+    hit.t = CUDART_MAX_NORMAL_F;  // Cast(ray) == Cast(ray, numeric_limits::max), acceleration.h:46-51
+    hit.prim = -1;
+    hit.u = 0.0f;
+    hit.v = 0.0f;
+    const int n_tris = c_scene.n_tris;
+#pragma unroll 2
+    for (int i = 0; i < n_tris; i++) {
+      const TriIsect& tri = c_scene.tri_isect[i];
+      if (intersect_triangle(tri.n_v0x, tri.nu_v0y, tri.nv_v0z, ray, hit.t, hit.t, hit.u, hit.v)) {
+        hit.prim = i;
+      }
+    }
+    const int n_spheres = c_scene.n_spheres;
+    for (int i = 0; i < n_spheres; i++) {
+      if (intersect_sphere(c_scene.sphere[i], ray, hit.t, hit.t)) hit.prim = n_tris + i;
+    }
+    if (hit.prim < 0) hit.t = CUDART_NAN_F;
+    return hit;
+  }
+
+  // true if anything lies in (kEPS, t_max)
+  static __device__ __forceinline__ bool occluded(const SceneView&, const Ray& ray, float t_max) {
+    bool blocked = false;
+    float t, u, v;
+    const int n_tris = c_scene.n_tris;
+#pragma unroll 2
+    for (int i = 0; i < n_tris; i++) {
+      const TriIsect& tri = c_scene.tri_isect[i];
+      blocked |= intersect_triangle(tri.n_v0x, tri.nu_v0y, tri.nv_v0z, ray, t_max, t, u, v);
+    }
+    const int n_spheres = c_scene.n_spheres;
+    for (int i = 0; i < n_spheres; i++) {
+      blocked |= intersect_sphere(c_scene.sphere[i], ray, t_max, t);
+    }
+    return blocked;
+  }
+};
+
+}  // namespace amber_cuda

@@ -1,0 +1,165 @@
+// materials.cuh -- BSDF sampling / evaluation and emission, one switch on the
+// material tag instead of the reference's virtual Material<RGB> interface
+// (include/amber/scene/material.h:31-88).  Each function cites what it restates.
+#pragma once
+
+#include "philox.cuh"
+#include "scene_device.cuh"
+
+namespace amber_cuda {
+
+constexpr int kPhongMaxTries = 64;
+
+struct Scatter {
+  float3 dir;     // direction_in, used as the next ray direction as-is (ray.h:52-62)
+  float3 weight;  // f cos / pdf (include/amber/rendering/scatter.h:45-48)
+  bool capped;    // Phong rejection loop hit kPhongMaxTries
+};
+
+// PerfectReflection, include/amber/prelude/geometry.h:38-47: 2 (d.n) n - d
+__device__ __forceinline__ float3 perfect_reflection(float3 incident, float3 normal, float signed_cos) {
+  const float k = 2.0f * signed_cos;
+  return v3(k * normal.x - incident.x, k * normal.y - incident.y, k * normal.z - incident.z);
+}
+
+// dir = u sin(theta) cos(phi) + v sin(theta) sin(phi) + w cos(theta)
+// (include/amber/prelude/sampling.h:248-252)
+__device__ __forceinline__ float3 local_to_world(float3 u, float3 v, float3 w, float sin_theta,
+                                                 float cos_theta, float phi) {
+  float s, c;
+  sincosf(phi, &s, &c);
+  const float a = sin_theta * c, b = sin_theta * s;
+  return v3(u.x * a + v.x * b + w.x * cos_theta, u.y * a + v.y * b + w.y * cos_theta,
+            u.z * a + v.z * b + w.z * cos_theta);
+}
+
+// HemispherePSA, sampling.h:234-265: cos = sqrt(r0), sin = sqrt(1-r0), phi = 2 pi r1.
+template <class Rng>
+__device__ __forceinline__ float3 hemisphere_psa(float3 w, Rng& rng) {
+  float3 u, v;
+  orthonormal_basis(w, u, v);
+  const float r0 = rng.next();
+  const float r1 = rng.next();
+  return local_to_world(u, v, w, sqrtf(1.0f - r0), sqrtf(r0), 2.0f * kPiF * r1);
+}
+
+// CosinePower, sampling.h:267-300: cos = r0^(1/(e+1)).
+template <class Rng>
+__device__ __forceinline__ float3 cosine_power(float3 w, float exponent, Rng& rng) {
+  float3 u, v;
+  orthonormal_basis(w, u, v);
+  const float r0 = rng.next();
+  const float r1 = rng.next();
+  const float cos_theta = powf(r0, 1.0f / (exponent + 1.0f));
+  const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+  return local_to_world(u, v, w, sin_theta, cos_theta, 2.0f * kPiF * r1);
+}
+
+// Schlick, src/amber/scene/material_refraction.cc:271-275
+__device__ __forceinline__ float schlick(float r0, float cos_theta) {
+  const float x = 1.0f - cos_theta;
+  const float x2 = x * x;
+  return r0 + (1.0f - r0) * (x2 * x2 * x);
+}
+
+// Material::SampleLight for radiance transport.  `wo` = direction_out = -ray.d.
+template <class Rng>
+__device__ __forceinline__ Scatter sample_light(const MaterialDev& m, float3 n, float3 wo, Rng& rng) {
+  Scatter s;
+  s.capped = false;
+  const float3 rho = v3(m.r, m.g, m.b);
+  const float cos_o = dot(wo, n);
+  switch (m.kind) {
+    case 0: {  // Lambertian: src/amber/scene/material_lambertian.cc:61-70, weight kd
+      const float3 w = cos_o > 0.0f ? n : -n;
+      s.dir = hemisphere_psa(w, rng);
+      s.weight = rho;
+      break;
+    }
+    case 1: {  // Phong: src/amber/scene/material_phong.cc:81-106 (rejection, bounded here)
+      const float3 refl = perfect_reflection(wo, n, cos_o);
+      s.weight = v3(0.0f, 0.0f, 0.0f);
+      s.dir = refl;
+      s.capped = true;
+      for (int attempt = 0; attempt < kPhongMaxTries; attempt++) {
+        const float3 dir = cosine_power(refl, m.param, rng);
+        const float cos_i = dot(dir, n);
+        if (cos_o * cos_i <= 0.0f) continue;
+        s.dir = dir;
+        s.weight = ((m.param + 2.0f) / (m.param + 1.0f) * fabsf(cos_i)) * rho;
+        s.capped = false;
+        break;
+      }
+      break;
+    }
+    case 2: {  // Specular: src/amber/scene/material_specular.cc:62-70
+      s.dir = perfect_reflection(wo, n, cos_o);
+      s.weight = rho;
+      break;
+    }
+    case 3: {  // Refraction: src/amber/scene/material_refraction.cc:177-220
+      const float ior = cos_o > 0.0f ? 1.0f / m.param : m.param;
+      const float cos2_beta = 1.0f - (1.0f - cos_o * cos_o) * (ior * ior);
+      const float3 dir_r = perfect_reflection(wo, n, cos_o);
+      if (cos2_beta < 0.0f) {  // total internal reflection
+        s.dir = dir_r;
+        s.weight = rho;
+        break;
+      }
+      const float cos_alpha = fabsf(cos_o);
+      const float cos_beta = sqrtf(cos2_beta);
+      const float k = (cos_o < 0.0f ? 1.0f : -1.0f) * cos_beta + ior * cos_o;
+      const float3 dir_t = v3(-ior * wo.x + k * n.x, -ior * wo.y + k * n.y, -ior * wo.z + k * n.z);
+      const float rho_r = schlick(m.r0, cos_alpha);
+      const float rho_t = (1.0f - rho_r) * (ior * ior);
+      const float total = rho_r + rho_t;
+      const float p_r = (rho_r / total + 0.5f) / 2.0f;
+      const float p_t = (rho_t / total + 0.5f) / 2.0f;
+      if (rng.next() < p_r) {
+        s.dir = dir_r;
+        s.weight = (rho_r / p_r) * rho;
+      } else {
+        s.dir = dir_t;
+        s.weight = (rho_t / p_t) * rho;
+      }
+      break;
+    }
+    case 5: {  // Eye: include/amber/scene/material_eye.h:146-155, pass-through
+      s.dir = -wo;
+      s.weight = v3(1.0f, 1.0f, 1.0f);
+      break;
+    }
+    default: {  // DiffuseLight: include/amber/scene/material_diffuse_light.h:185-194
+      s.dir = v3(0.0f, 0.0f, 0.0f);
+      s.weight = v3(0.0f, 0.0f, 0.0f);
+      break;
+    }
+  }
+  return s;
+}
+
+// Material::BSDF for the connectable (SurfaceType::Diffuse) materials, w.r.t.
+// projected solid angle.  Lambertian: material_lambertian.cc:34-49;
+// Phong: material_phong.cc:39-61.  Others return 0 (never connected,
+// include/amber/rendering/bidirectional_path_sampling.h:944-952).
+__device__ __forceinline__ float3 bsdf_eval(const MaterialDev& m, float3 n, float3 wo, float3 wi) {
+  const float cos_o = dot(wo, n);
+  const float cos_i = dot(wi, n);
+  const float3 rho = v3(m.r, m.g, m.b);
+  if (cos_o * cos_i <= 0.0f) return v3(0.0f, 0.0f, 0.0f);
+  if (m.kind == 0) return (1.0f / kPiF) * rho;
+  if (m.kind == 1) {
+    const float3 refl = perfect_reflection(wi, n, cos_i);
+    const float cos_alpha = fmaxf(0.0f, dot(refl, wo));
+    return ((m.param + 2.0f) / (2.0f * kPiF) * powf(cos_alpha, m.param)) * rho;
+  }
+  return v3(0.0f, 0.0f, 0.0f);
+}
+
+// DiffuseLight::Radiance, material_diffuse_light.h:127-139: one-sided.
+__device__ __forceinline__ float3 emitted_radiance(const MaterialDev& m, float3 n, float3 wo) {
+  if (m.kind != 4 || !(dot(wo, n) > 0.0f)) return v3(0.0f, 0.0f, 0.0f);
+  return v3(m.r, m.g, m.b);
+}
+
+}  // namespace amber_cuda

@@ -1,0 +1,124 @@
+// scene_device.cuh -- device-side scene layout.
+//
+// Two acceleration layouts sit behind the same closest-hit / any-hit interface:
+//  * ConstList (this file): scenes of up to kMaxConstTris triangles + kMaxConstSpheres
+//    spheres live entirely in __constant__ memory and are tested warp-uniformly in
+//    one loop -- every lane reads the same primitive, so operands come through the
+//    uniform datapath and no lane ever waits on a gather.  This is the layout the
+//    built-in Cornell box (25 objects) uses; the reference itself ends up testing all
+//    25 objects per ray there (its SAH tree collapses to one leaf).
+//  * WideBvh (bvh.cuh): larger scenes, 4-wide SoA nodes in global memory.
+#pragma once
+
+#include <cstdint>
+
+#include "vec.cuh"
+
+namespace amber_cuda {
+
+constexpr int kMaxConstTris = 128;
+constexpr int kMaxConstSpheres = 32;
+constexpr int kMaxBlades = 16;
+
+// float just below the reference's `kEPS = 1e-6L` (include/amber/constants.h:26):
+// (float)1e-6 = 9.99999997e-7 < 1e-6L, so for a float t, `t < kEPS` (reject,
+// src/amber/scene/primitive_triangle.cc:122-125) <=> t <= kEpsF and `t > kEPS`
+// (accept, src/amber/scene/primitive_sphere.cc:90,98) <=> t > kEpsF.
+constexpr float kEpsF = 1e-6f;
+constexpr float kRussianRoulette = 0.9375f;  // include/amber/constants.h:28
+constexpr float kPiF = 3.14159274101257324f;  // static_cast<float>(kPI)
+
+// Triangle in intersection form.  With n = E1 x E2, T = o - v0:
+//   t = -(n.T)/(n.d),  h = T + t d,  u = h.nu,  v = h.nv
+// where nu = (E2 x n)/|n|^2 and nv = (n x E1)/|n|^2.  Algebraically the test of
+// src/amber/scene/primitive_triangle.cc:97-128 (det = -n.d, Q.E2 = n.T); the edge
+// tests use the same inclusive bounds.
+struct TriIsect {
+  float4 n_v0x;   // n.xyz,  v0.x
+  float4 nu_v0y;  // nu.xyz, v0.y
+  float4 nv_v0z;  // nv.xyz, v0.z
+};
+
+// Triangle in shading form: position = v0 + u E1 + v E2 (primitive_triangle.cc:127),
+// stored geometric normal = normalize((v1-v0) x (v2-v0)) (primitive_triangle.cc:59-68).
+struct TriShade {
+  float4 v0_nx;  // v0.xyz, normal.x
+  float4 e1_ny;  // E1.xyz, normal.y
+  float4 e2_nz;  // E2.xyz, normal.z
+};
+
+struct alignas(16) MaterialDev {
+  int32_t kind;
+  float r, g, b;
+  float param;  // Phong exponent / ior
+  float r0;     // Refraction: Fresnel reflectance at normal incidence (material_refraction.cc:265-269)
+  int32_t nee;  // 1 if the surface is connectable: SurfaceType::Diffuse (Lambertian, Phong)
+  int32_t pad;
+};
+
+// Emitting triangle for next-event estimation, sorted by power as
+// include/amber/scene/light_set.h:61-81.
+struct alignas(16) LightDev {
+  float4 v0;  // xyz, cumulative power
+  float4 v1;  // xyz, unused
+  float4 v2;  // xyz, unused
+  float4 n;   // normal xyz, unused
+  float4 le_over_pdf;  // radiance / pdf_area (rgb), unused
+};
+
+struct LensDev {
+  float origin[3];
+  float global[9];  // row-major lens-local -> world (Matrix3 part of the transform)
+  float local[9];   // inverse
+  float focus_distance, sensor_distance, p_area;
+  int32_t n_blades;
+  float blades[kMaxBlades][12];  // v0 v1 v2 normal
+};
+
+struct SensorDev {
+  uint32_t width, height;
+  float film_width, film_height;
+  float size_over_area;  // sensor.Size() / sensor.SceneArea(), lens_thin.cc:145
+};
+
+struct ConstScene {
+  int32_t n_tris, n_spheres;
+  int32_t pad[2];
+  TriIsect tri_isect[kMaxConstTris];
+  float4 sphere[kMaxConstSpheres];  // centre xyz, radius
+};
+
+// Everything a lane indexes on its own (shading data, materials, lights) lives in
+// global memory and is read through the L1/read-only path; only data that a whole warp
+// reads at the same address sits in __constant__ memory.
+struct SceneView {
+  const TriShade* tri_shade;      // [n_tris], internal triangle order
+  const float4* spheres;          // [n_spheres]
+  const int32_t* tri_material;    // [n_tris]
+  const int32_t* sphere_material; // [n_spheres]
+  const MaterialDev* materials;
+  const LightDev* lights;         // sorted by power, cumulative power in v0.w
+  int32_t n_tris, n_spheres, n_lights;
+  float total_power;
+  // WideBvh only
+  const float4* bvh_nodes;
+  const TriIsect* tri_isect;
+  int32_t bvh_root;  // 0 (node 0), or a leaf reference if the whole mesh is one leaf
+};
+
+struct CameraDev {
+  LensDev lens;
+  SensorDev sensor;
+};
+
+// Hit record written by `extend`, one float4 per path slot.
+//   x = t (NaN on a miss, include/amber/prelude/hit.h:62-66)
+//   y = internal primitive index (int bits; -1 on a miss); triangles first, then spheres
+//   z, w = barycentric u, v (triangles)
+struct HitRecord {
+  float t;
+  int32_t prim;
+  float u, v;
+};
+
+}  // namespace amber_cuda

@@ -1,0 +1,219 @@
+/*
+ * amber_cuda.h -- C ABI of libamber_cuda.so, the B200 (sm_100a) implementation of
+ * amber's path-tracing hot path.
+ *
+ * This is the drop-in boundary.  Everything above it (amber's C++ scene / sensor /
+ * context / algorithm API) stays on the host; everything below it is CUDA.  Plain
+ * pointers and sizes only -- no C++ types, no torch types.
+ *
+ * Each entry point names the reference interface it stands in for (paths relative
+ * to the reference tree, file:line).  The C++ adapter that binds these calls behind
+ * `amber::rendering::Algorithm<RGB>` lives in include/amber_cuda/adapter.hpp; the
+ * ctypes binding used by the tests and bench.py is amber_b200/capi.py.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative AMBER_CUDA_E* code on failure;
+ *    amber_cuda_last_error() returns the message (the C++ adapter rethrows it as
+ *    std::runtime_error, matching the reference's exceptions-only convention,
+ *    include/amber/prelude/image.h:73-75).
+ *  - the caller owns every host buffer; the context owns all device memory.
+ *  - a context is bound to ONE device and is used by one host thread at a time
+ *    (the reference's Render() is likewise called from one thread,
+ *    src/amber/cli/application.cc:149-152).
+ *  - there is no CPU fallback: without a CUDA device amber_cuda_create() fails.
+ */
+#ifndef AMBER_CUDA_H_
+#define AMBER_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AMBER_CUDA_ABI_VERSION 1
+
+/* error codes */
+#define AMBER_CUDA_OK 0
+#define AMBER_CUDA_EINVAL (-1)  /* bad argument / bad scene description */
+#define AMBER_CUDA_ECUDA (-2)   /* a CUDA runtime call failed */
+#define AMBER_CUDA_ESTATE (-3)  /* call order violated (e.g. render before upload) */
+#define AMBER_CUDA_ENODEV (-4)  /* no usable CUDA device: there is no CPU fallback */
+
+/* Primitive kinds: include/amber/scene/primitive_triangle.h:30-35,
+ * include/amber/scene/primitive_sphere.h:30-34. */
+#define AMBER_CUDA_PRIM_TRIANGLE 0
+#define AMBER_CUDA_PRIM_SPHERE 1
+
+/* Material kinds, one per reference factory:
+ *   MakeLambertian   include/amber/scene/material_lambertian.h:65-74
+ *   MakePhong        include/amber/scene/material_phong.h
+ *   MakeSpecular     include/amber/scene/material_specular.h
+ *   MakeRefraction   include/amber/scene/material_refraction.h
+ *   MakeDiffuseLight include/amber/scene/material_diffuse_light.h:27-29
+ *   MakeEye          include/amber/scene/material_eye.h (aperture pass-through) */
+#define AMBER_CUDA_MAT_LAMBERTIAN 0
+#define AMBER_CUDA_MAT_PHONG 1
+#define AMBER_CUDA_MAT_SPECULAR 2
+#define AMBER_CUDA_MAT_REFRACTION 3
+#define AMBER_CUDA_MAT_DIFFUSE_LIGHT 4
+#define AMBER_CUDA_MAT_EYE 5
+
+/* Estimators.
+ * REFERENCE: sample-for-sample the estimator of
+ *   src/amber/rendering/algorithm_pt.cc:125-160 (emission at every hit, no light
+ *   sampling).
+ * NEE: next-event estimation; equal in expectation.  Light point sampled as
+ *   include/amber/scene/light_set.h:83-104, connection term as the s=1 branch of
+ *   include/amber/rendering/bidirectional_path_sampling.h:956-1016; emission on a
+ *   BSDF-sampled hit is counted only when the previous vertex could not be
+ *   connected (camera, Specular, Refraction, Eye). */
+#define AMBER_CUDA_ESTIMATOR_REFERENCE 0
+#define AMBER_CUDA_ESTIMATOR_NEE 1
+
+typedef struct amber_cuda_ctx amber_cuda_ctx;
+
+/* One primitive.  The index in the array is the primitive id reported by
+ * amber_cuda_cast (creation order, as objects are emplaced in
+ * src/amber/etude/cornel_box.cc:62-196). */
+typedef struct amber_cuda_primitive {
+  int32_t kind;     /* AMBER_CUDA_PRIM_* */
+  int32_t material; /* index into materials[] */
+  float data[9];    /* triangle: v0 v1 v2 (xyz each); sphere: centre xyz, radius */
+} amber_cuda_primitive;
+
+typedef struct amber_cuda_material {
+  int32_t kind; /* AMBER_CUDA_MAT_* */
+  float rgb[3]; /* kd / ks / emitted radiance; ignored for REFRACTION and EYE */
+  float param;  /* PHONG: exponent; REFRACTION: index of refraction */
+} amber_cuda_material;
+
+/* Thin lens, the arguments of MakeThinLens (include/amber/scene/lens_thin.h:30-38). */
+typedef struct amber_cuda_lens {
+  float transform[16]; /* row-major 4x4, lens-local -> world (Matrix4 ctor order) */
+  float focal_length;
+  float focus_distance;
+  float radius;
+  int32_t n_blades;
+} amber_cuda_lens;
+
+typedef struct amber_cuda_scene_desc {
+  uint32_t n_primitives;
+  const amber_cuda_primitive* primitives;
+  uint32_t n_materials;
+  const amber_cuda_material* materials;
+  amber_cuda_lens lens;
+} amber_cuda_scene_desc;
+
+typedef struct amber_cuda_render_params {
+  uint64_t sample_begin; /* first global sample index of this batch */
+  uint32_t sample_count; /* samples per pixel to add in this call */
+  uint32_t max_depth;    /* bounce cap (0 = 2^16); the reference has none, algorithm_pt.cc:137 */
+  uint64_t seed;
+  int32_t estimator;     /* AMBER_CUDA_ESTIMATOR_* */
+  uint32_t pool_paths;   /* resident path slots (0 = default) */
+} amber_cuda_render_params;
+
+typedef struct amber_cuda_stats {
+  uint64_t paths;           /* camera paths started since the last film clear */
+  uint64_t closest_rays;    /* rays through `extend` */
+  uint64_t shadow_rays;     /* rays through `connect` */
+  uint64_t truncated_paths; /* paths cut by max_depth */
+  uint64_t phong_capped;    /* Phong rejection loops that hit the retry cap */
+  uint64_t kernel_launches; /* our kernels launched since context creation */
+  double last_render_ms;    /* device time of the last amber_cuda_render */
+  double extend_ms;         /* per-kernel device time inside the last render (profiling mode) */
+  double shade_ms;
+  double connect_ms;
+  double raygen_ms;
+  uint64_t extend_launches; /* launches of `extend` inside the last render */
+  uint32_t accel;           /* 0 = constant-memory list, 1 = wide BVH */
+  uint32_t bvh_nodes;
+} amber_cuda_stats;
+
+/* ABI version of the loaded library. */
+int amber_cuda_abi_version(void);
+
+/* Message of the last failure on this context (ctx may be NULL for a failed create). */
+const char* amber_cuda_last_error(const amber_cuda_ctx* ctx);
+
+/* Create a context on CUDA device `device`.  Replaces nothing in the reference (it
+ * has no device); plays the role of constructing the algorithm object,
+ * MakeRGBPathTracing(), src/amber/rendering/algorithm_pt.cc:76-80. */
+int amber_cuda_create(amber_cuda_ctx** out, int device);
+int amber_cuda_destroy(amber_cuda_ctx* ctx);
+
+/* Upload a scene and build the acceleration structure.  Replaces
+ * scene::Scene<RGB>::Create<BVH> (include/amber/scene/scene.h:169-193) and
+ * BVH::BVH/BuildBVH (include/amber/raytracer/acceleration_bvh.h:135-180). */
+int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* scene);
+
+/* Film geometry.  Replaces rendering::Sensor::Sensor
+ * (src/amber/rendering/sensor.cc:28-38); clears the film. */
+int amber_cuda_set_sensor(amber_cuda_ctx* ctx, uint32_t width, uint32_t height,
+                          float film_width, float film_height);
+
+/* Zero the film and the sample count. */
+int amber_cuda_film_clear(amber_cuda_ctx* ctx);
+
+/* Trace sample_count samples for every pixel and add them to the device film.
+ * Replaces the body of PathTracing<RGB>::Render / Thread::operator() / Thread::Render
+ * (src/amber/rendering/algorithm_pt.cc:82-160): ray generation, extend, shade,
+ * connect.  Asynchronous work is complete when the call returns. */
+int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* params);
+
+/* Mean image to the host: host_rgb[(x + y*W)*3 + c] = film / samples.  Replaces
+ * Accumulator::Mean (include/amber/prelude/accumulator.h:88-95) and the Image
+ * returned by Render (layout include/amber/prelude/image.h:117-124).
+ * samples_done may be NULL. */
+int amber_cuda_resolve(amber_cuda_ctx* ctx, float* host_rgb, uint64_t* samples_done);
+
+/* The raw (un-normalised) device film: W*H float4 (r,g,b,unused) sums and the sample
+ * count, for the multi-GPU film reduction done by the host (NCCL all-reduce over
+ * this buffer, then amber_cuda_film_set_samples). */
+int amber_cuda_film_device(amber_cuda_ctx* ctx, void** device_ptr, uint64_t* n_floats,
+                           uint64_t* samples_done);
+int amber_cuda_film_set_samples(amber_cuda_ctx* ctx, uint64_t samples_done);
+
+/* Closest hit for n rays in HOST memory: origins/directions are n*3 floats
+ * (directions must be unit, as prelude::Ray stores them, include/amber/prelude/ray.h:52-62).
+ * prim[i] = primitive id or -1, t[i] = hit distance (NaN on a miss, as
+ * include/amber/prelude/hit.h:62-66).  Replaces scene::Scene::Cast ->
+ * Acceleration::Cast (include/amber/scene/scene.h:236-244,
+ * include/amber/raytracer/acceleration.h:46-51). */
+int amber_cuda_cast(amber_cuda_ctx* ctx, const float* origins, const float* directions,
+                    uint64_t n, int32_t* prim, float* t);
+
+/* Same, device-resident SoA float4 rays (xyz + pad) and float4 hit records
+ * (t, prim id bits, u, v): the `extend` kernel exactly as the wavefront launches it.
+ * elapsed_ms (may be NULL) receives the CUDA-event time of the launch. */
+int amber_cuda_cast_device(amber_cuda_ctx* ctx, const void* ray_origin4,
+                           const void* ray_direction4, uint64_t n, void* hit4,
+                           float* elapsed_ms);
+
+/* Per-vertex unit checks (parity entry points; each runs one tiny kernel).
+ * sample_light: n BSDF samples for material `material` at normal/dir_out with the
+ * scripted uniforms xi[n][8]; outputs direction, rgb weight and draws consumed.
+ * Replaces Material<RGB>::SampleLight (include/amber/scene/material.h:31-88). */
+int amber_cuda_sample_light(amber_cuda_ctx* ctx, int32_t material, uint64_t n,
+                            const float* normal3, const float* dir_out3, const float* xi8,
+                            float* dir_in3, float* weight3, int32_t* draws);
+
+/* eye_rays: n camera rays for pixel (px[i], py[i]) with scripted uniforms xi[n][5].
+ * Replaces scene::Scene::GenerateEyeRay (include/amber/scene/scene.h:210-223,
+ * src/amber/scene/lens_thin.cc:70-107). */
+int amber_cuda_eye_rays(amber_cuda_ctx* ctx, uint64_t n, const uint32_t* px,
+                        const uint32_t* py, const float* xi5, float* origin3,
+                        float* direction3, float* weight);
+
+/* Counters; see amber_cuda_stats.  profile != 0 makes the next renders time each
+ * kernel class with CUDA events (slower: one event pair per launch). */
+int amber_cuda_get_stats(amber_cuda_ctx* ctx, amber_cuda_stats* out);
+int amber_cuda_set_profiling(amber_cuda_ctx* ctx, int profile);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* AMBER_CUDA_H_ */

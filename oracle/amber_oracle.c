@@ -1,0 +1,739 @@
+/*
+ * amber_oracle.c -- TEST INFRASTRUCTURE.  Not part of the product.
+ *
+ * CPU restatement of the reference's path-tracing hot path, in plain C, float for
+ * float in the reference's operation order (compile with -ffp-contract=off: the
+ * reference is built without FMA, CMakeLists.txt:5).  Citations are to files under
+ * /root/reference.  See amber_oracle.h for how it is pinned.
+ */
+#include "amber_oracle.h"
+
+#include <math.h>
+#include <pthread.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "philox_stream.h"
+
+/* include/amber/constants.h:25-28 */
+static const long double kPI = 3.141592653589793238462643383279503L;
+static const long double kEPS = 1e-6L;
+static const long double kRussianRoulette = 0.9375L;
+#define PI_F ((float)kPI)
+
+typedef struct { float x, y, z; } vec3;
+
+/* ---- include/amber/prelude/vector3.h:170-342 ------------------------------------- */
+static vec3 V(float x, float y, float z) { vec3 v = {x, y, z}; return v; }
+static vec3 add(vec3 a, vec3 b) { return V(a.x + b.x, a.y + b.y, a.z + b.z); }
+static vec3 sub(vec3 a, vec3 b) { return V(a.x - b.x, a.y - b.y, a.z - b.z); }
+static vec3 mul(vec3 a, vec3 b) { return V(a.x * b.x, a.y * b.y, a.z * b.z); }
+static vec3 scale(float s, vec3 a) { return V(s * a.x, s * a.y, s * a.z); } /* Vector3(s) * a */
+static vec3 neg(vec3 a) { return V(-a.x, -a.y, -a.z); }
+static float dot(vec3 u, vec3 v) { return u.x * v.x + u.y * v.y + u.z * v.z; }
+static float length(vec3 v) { return sqrtf(dot(v, v)); }
+static vec3 normalize(vec3 v) { const float l = length(v); return V(v.x / l, v.y / l, v.z / l); }
+static vec3 cross(vec3 u, vec3 v) {
+  return V(u.y * v.z - u.z * v.y, u.z * v.x - u.x * v.z, u.x * v.y - u.y * v.x);
+}
+static float max3(vec3 v) { return fmaxf(v.x, fmaxf(v.y, v.z)); }
+static void orthonormal_basis(vec3 w, vec3* u, vec3* v) { /* vector3.h:330-342 */
+  *u = normalize(cross(w, fabsf(w.x) < fabsf(w.y) ? V(1, 0, 0) : V(0, 1, 0)));
+  *v = normalize(cross(w, *u));
+}
+
+/* ---- uniform source: the Philox stream, or a scripted list ------------------------ */
+typedef struct {
+  philox_stream* stream; /* if non-NULL */
+  const float* xi;
+  int n, used;
+} sampler;
+static float uniform(sampler* s) { /* Uniform<float>: static_cast<float>(sampler()), sampling.h:156-161 */
+  if (s->stream) return philox_stream_next(s->stream);
+  {
+    /* past the scripted list: a Weyl sequence, identical in the harness and the kernels */
+    const float v = s->used < s->n ? s->xi[s->used]
+                                   : (float)(((uint32_t)s->used * 2654435769u) >> 8) * (1.0f / 16777216.0f);
+    s->used++;
+    return v;
+  }
+}
+
+/* ---- scene ----------------------------------------------------------------------- */
+typedef struct {
+  int kind; /* AMBER_CUDA_PRIM_* */
+  int material;
+  vec3 v0, v1, v2, normal; /* triangle; normal = Normalize(Cross(v1-v0, v2-v0)), primitive_triangle.cc:59-68 */
+  vec3 center;             /* sphere */
+  float radius;
+} prim;
+
+typedef struct {
+  int prim_index;
+  float cumulative_power;
+  float pdf_area;
+} light;
+
+struct oracle_scene {
+  uint32_t n_prims, n_materials, n_lights;
+  prim* prims;
+  amber_cuda_material* materials;
+  float* r0; /* Refraction: Fresnel(ior) */
+  light* lights;
+  float total_power;
+  /* BasicThin, src/amber/scene/lens_thin.cc:32-57 */
+  vec3 lens_origin;
+  float global[9], local[9];
+  float focus_distance, sensor_distance, p_area;
+  int n_blades;
+  vec3 blades[16][4]; /* v0 v1 v2 normal */
+};
+
+static vec3 mat3_apply(const float* m, vec3 v) { /* include/amber/prelude/matrix3.h:83-90 */
+  return V(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[3] * v.x + m[4] * v.y + m[5] * v.z,
+           m[6] * v.x + m[7] * v.y + m[8] * v.z);
+}
+
+static float triangle_area(vec3 v0, vec3 v1, vec3 v2) { /* primitive_triangle.cc:130-134 */
+  return length(cross(sub(v1, v0), sub(v2, v0))) / 2;
+}
+
+oracle_scene* oracle_scene_create(const amber_cuda_scene_desc* desc) {
+  oracle_scene* s = (oracle_scene*)calloc(1, sizeof *s);
+  uint32_t i;
+  s->n_prims = desc->n_primitives;
+  s->n_materials = desc->n_materials;
+  s->prims = (prim*)calloc(desc->n_primitives ? desc->n_primitives : 1, sizeof(prim));
+  s->materials = (amber_cuda_material*)calloc(desc->n_materials, sizeof(amber_cuda_material));
+  s->r0 = (float*)calloc(desc->n_materials, sizeof(float));
+  memcpy(s->materials, desc->materials, desc->n_materials * sizeof(amber_cuda_material));
+  for (i = 0; i < desc->n_materials; i++) {
+    amber_cuda_material* m = &s->materials[i];
+    if (m->kind == AMBER_CUDA_MAT_REFRACTION || m->kind == AMBER_CUDA_MAT_EYE) {
+      m->rgb[0] = m->rgb[1] = m->rgb[2] = 1.0f; /* Radiant(1), material_refraction.h:94-101 */
+    }
+    if (m->kind == AMBER_CUDA_MAT_REFRACTION) {
+      /* BasicRefraction::Fresnel, material_refraction.cc:265-269: std::pow(float, int) -> double */
+      s->r0[i] = (float)pow((double)((m->param - 1) / (m->param + 1)), 2.0);
+    }
+  }
+  for (i = 0; i < desc->n_primitives; i++) {
+    const amber_cuda_primitive* in = &desc->primitives[i];
+    prim* p = &s->prims[i];
+    p->kind = in->kind;
+    p->material = in->material;
+    if (in->kind == AMBER_CUDA_PRIM_TRIANGLE) {
+      p->v0 = V(in->data[0], in->data[1], in->data[2]);
+      p->v1 = V(in->data[3], in->data[4], in->data[5]);
+      p->v2 = V(in->data[6], in->data[7], in->data[8]);
+      p->normal = normalize(cross(sub(p->v1, p->v0), sub(p->v2, p->v0)));
+    } else {
+      p->center = V(in->data[0], in->data[1], in->data[2]);
+      p->radius = in->data[3];
+    }
+  }
+  /* emitting triangles sorted by power, LightSet::LightSet (include/amber/scene/light_set.h:61-81);
+   * Power = Sum(SurfaceArea * Irradiance) (include/amber/scene/object.h:98-103),
+   * Irradiance = radiance * pi (material_diffuse_light.h:119-124) */
+  {
+    float (*tmp)[3] = (float (*)[3])calloc(desc->n_primitives ? desc->n_primitives : 1, sizeof *tmp);
+    uint32_t n = 0;
+    float cumulative = 0;
+    for (i = 0; i < desc->n_primitives; i++) {
+      const prim* p = &s->prims[i];
+      const amber_cuda_material* m = &s->materials[p->material];
+      if (p->kind != AMBER_CUDA_PRIM_TRIANGLE || m->kind != AMBER_CUDA_MAT_DIFFUSE_LIGHT) continue;
+      {
+        const float area = triangle_area(p->v0, p->v1, p->v2);
+        const float ir = m->rgb[0] * PI_F, ig = m->rgb[1] * PI_F, ib = m->rgb[2] * PI_F;
+        const float power = area * ir + area * ig + area * ib;
+        if (!(power > 0)) continue;
+        tmp[n][0] = power;
+        tmp[n][1] = (float)i;
+        tmp[n][2] = ir + ig + ib;
+        n++;
+      }
+    }
+    /* ascending power; equal powers keep creation order */
+    {
+      uint32_t a, b;
+      for (a = 1; a < n; a++) { /* insertion sort is stable */
+        float key[3];
+        memcpy(key, tmp[a], sizeof key);
+        b = a;
+        while (b > 0 && tmp[b - 1][0] > key[0]) {
+          memcpy(tmp[b], tmp[b - 1], sizeof key);
+          b--;
+        }
+        memcpy(tmp[b], key, sizeof key);
+      }
+    }
+    s->n_lights = n;
+    s->lights = (light*)calloc(n ? n : 1, sizeof(light));
+    s->total_power = 0;
+    for (i = 0; i < n; i++) s->total_power += tmp[i][0];
+    for (i = 0; i < n; i++) {
+      cumulative += tmp[i][0];
+      s->lights[i].prim_index = (int)tmp[i][1];
+      s->lights[i].cumulative_power = cumulative;
+      s->lights[i].pdf_area = tmp[i][2] / s->total_power; /* LightSet::PDFArea, light_set.h:106-111 */
+    }
+    free(tmp);
+  }
+  /* lens */
+  {
+    const amber_cuda_lens* in = &desc->lens;
+    const float* t = in->transform;
+    const float e11 = t[0], e12 = t[1], e13 = t[2], e21 = t[4], e22 = t[5], e23 = t[6], e31 = t[8],
+                e32 = t[9], e33 = t[10];
+    const float g[9] = {e11, e12, e13, e21, e22, e23, e31, e32, e33};
+    /* Matrix3::Determinant / Inverse, include/amber/prelude/matrix3.h:110-145 */
+    const float det = e11 * (e22 * e33 - e23 * e32) - e21 * (e12 * e33 - e13 * e32) + e31 * (e12 * e23 - e13 * e22);
+    const float dinv = 1 / det;
+    const float inv[9] = {+dinv * (e22 * e33 - e23 * e32), -dinv * (e12 * e33 - e13 * e32), +dinv * (e12 * e23 - e13 * e22),
+                          -dinv * (e21 * e33 - e23 * e31), +dinv * (e11 * e33 - e13 * e31), -dinv * (e11 * e23 - e13 * e21),
+                          +dinv * (e21 * e32 - e22 * e31), -dinv * (e11 * e32 - e12 * e31), +dinv * (e11 * e22 - e12 * e21)};
+    int b;
+    memcpy(s->global, g, sizeof g);
+    memcpy(s->local, inv, sizeof inv);
+    s->lens_origin = V(t[3], t[7], t[11]); /* transform(Vector3()), matrix4.h:100-106 */
+    s->focus_distance = in->focus_distance;
+    s->sensor_distance = 1 / (1 / in->focal_length - 1 / in->focus_distance);
+    s->n_blades = in->n_blades;
+    for (b = 0; b < in->n_blades && b < 16; b++) {
+      const float nb = (float)in->n_blades; /* size_t -> float in `2*pi / n_blades * i` */
+      const float alpha = 2 * PI_F / nb * (float)b;
+      const float beta = 2 * PI_F / nb * (float)(b + 1);
+      s->blades[b][0] = add(s->lens_origin, mat3_apply(g, scale(in->radius, V(cosf(alpha), sinf(alpha), 0))));
+      s->blades[b][1] = add(s->lens_origin, mat3_apply(g, scale(in->radius, V(cosf(beta), sinf(beta), 0))));
+      s->blades[b][2] = s->lens_origin;
+      s->blades[b][3] = normalize(cross(sub(s->blades[b][1], s->blades[b][0]), sub(s->blades[b][2], s->blades[b][0])));
+    }
+    s->p_area = 1;
+    s->p_area /= triangle_area(s->blades[0][0], s->blades[0][1], s->blades[0][2]) * (float)in->n_blades;
+  }
+  return s;
+}
+
+void oracle_scene_destroy(oracle_scene* s) {
+  if (!s) return;
+  free(s->prims);
+  free(s->materials);
+  free(s->r0);
+  free(s->lights);
+  free(s);
+}
+
+/* ---- intersection ------------------------------------------------------------------ */
+typedef struct {
+  float t; /* NaN on a miss, include/amber/prelude/hit.h:62-66 */
+  vec3 position, normal;
+} hit_t;
+
+/* Triangle::Intersect, src/amber/scene/primitive_triangle.cc:97-128 */
+static int triangle_intersect(const prim* p, vec3 o, vec3 d, hit_t* hit) {
+  const vec3 E1 = sub(p->v1, p->v0);
+  const vec3 E2 = sub(p->v2, p->v0);
+  const vec3 P = cross(d, E2);
+  const float det = dot(P, E1);
+  const vec3 T = sub(o, p->v0);
+  const float u = dot(P, T) / det;
+  vec3 Q;
+  float v, t;
+  if (u > 1 || u < 0) return 0;
+  Q = cross(T, E1);
+  v = dot(Q, d) / det;
+  if (v > 1 || v < 0) return 0;
+  if (u + v > 1) return 0;
+  t = dot(Q, E2) / det;
+  if ((long double)t < kEPS) return 0;
+  if (!isfinite(t)) return 0; /* Hit::operator bool, hit.h:90-94 */
+  hit->t = t;
+  hit->position = add(add(p->v0, scale(u, E1)), scale(v, E2));
+  hit->normal = p->normal;
+  return 1;
+}
+
+/* Sphere::Intersect, src/amber/scene/primitive_sphere.cc:75-107 +
+ * SolveQuadratic, include/amber/prelude/algebra.h:31-52 */
+static int sphere_intersect(const prim* p, vec3 o, vec3 d, hit_t* hit) {
+  const float a = 1;
+  const float b = -2 * dot(sub(p->center, o), d);
+  const vec3 oc = sub(p->center, o);
+  const float c = dot(oc, oc) - p->radius * p->radius;
+  const float disc = b * b - 4 * a * c;
+  float sqrt_d, alpha, beta, t;
+  if (disc < 0) return 0;
+  sqrt_d = sqrtf(disc);
+  alpha = -b - sqrt_d;
+  beta = -b + sqrt_d;
+  if (fabsf(alpha) < fabsf(beta)) {
+    alpha = c / beta * 2;
+    beta /= 2 * a;
+  } else {
+    beta = c / alpha * 2;
+    alpha /= 2 * a;
+  }
+  if ((long double)alpha > kEPS) t = alpha;
+  else if ((long double)beta > kEPS) t = beta;
+  else return 0;
+  if (!isfinite(t)) return 0;
+  hit->t = t;
+  hit->position = add(o, scale(t, d));
+  hit->normal = normalize(sub(hit->position, p->center)); /* Hit ctor normalises, hit.h:68-77 */
+  return 1;
+}
+
+/* raytracer::List::Cast / the leaf loop of BVH::Node::Cast
+ * (include/amber/raytracer/acceleration_list.h:51-68, acceleration_bvh.h:343-356):
+ * closest hit, strict `<`, starting from numeric_limits<float>::max (acceleration.h:46-51). */
+static int scene_cast(const oracle_scene* s, vec3 o, vec3 d, hit_t* closest) {
+  float distance = 3.402823466e+38f;
+  int object = -1;
+  uint32_t i;
+  for (i = 0; i < s->n_prims; i++) {
+    hit_t h;
+    const prim* p = &s->prims[i];
+    const int ok = p->kind == AMBER_CUDA_PRIM_TRIANGLE ? triangle_intersect(p, o, d, &h)
+                                                       : sphere_intersect(p, o, d, &h);
+    if (ok && h.t < distance) {
+      distance = h.t;
+      *closest = h;
+      object = (int)i;
+    }
+  }
+  if (object < 0) closest->t = NAN;
+  return object;
+}
+
+/* ---- sampling routines, include/amber/prelude/sampling.h ---------------------------- */
+static vec3 local_dir(vec3 u, vec3 v, vec3 w, float sin_theta, float cos_theta, float phi) {
+  /* u * sin_theta * cos(phi) + v * sin_theta * sin(phi) + w * cos_theta, sampling.h:248-252 */
+  const vec3 a = scale(cosf(phi), scale(sin_theta, u));
+  const vec3 b = scale(sinf(phi), scale(sin_theta, v));
+  const vec3 c = scale(cos_theta, w);
+  return add(add(a, b), c);
+}
+
+static vec3 hemisphere_psa(vec3 w, sampler* s) { /* sampling.h:234-265 */
+  vec3 u, v;
+  float r0, r1;
+  orthonormal_basis(w, &u, &v);
+  r0 = uniform(s);
+  r1 = uniform(s);
+  return local_dir(u, v, w, sqrtf(1 - r0), sqrtf(r0), 2 * PI_F * r1);
+}
+
+static vec3 cosine_power(vec3 w, float exponent, sampler* s) { /* sampling.h:267-300 */
+  vec3 u, v;
+  float r0, r1, cos_theta, sin_theta;
+  orthonormal_basis(w, &u, &v);
+  r0 = uniform(s);
+  r1 = uniform(s);
+  cos_theta = powf(r0, 1 / (exponent + 1));
+  sin_theta = sqrtf(1 - cos_theta * cos_theta);
+  return local_dir(u, v, w, sin_theta, cos_theta, 2 * PI_F * r1);
+}
+
+/* PerfectReflection, include/amber/prelude/geometry.h:38-47 */
+static vec3 perfect_reflection(vec3 incident, vec3 normal, float signed_cos) {
+  return sub(scale(2 * signed_cos, normal), incident);
+}
+
+/* BasicRefraction::Schlick, material_refraction.cc:271-275: std::pow(float, int) is double */
+static float schlick(float r0, float cos_theta) {
+  return (float)((double)r0 + (double)(1 - r0) * pow((double)(1 - cos_theta), 5.0));
+}
+
+typedef struct {
+  vec3 dir, weight;
+} scatter_t;
+
+/* Material<RGB>::SampleLight through the Basic*Forwarder (material_basic.h:233-245,327-338):
+ * weight = scalar weight * rho. */
+static scatter_t material_sample_light(const amber_cuda_material* m, float r0, vec3 n, vec3 wo, sampler* s) {
+  scatter_t out;
+  const vec3 rho = V(m->rgb[0], m->rgb[1], m->rgb[2]);
+  float scalar = 0;
+  out.dir = V(0, 0, 0);
+  switch (m->kind) {
+    case AMBER_CUDA_MAT_LAMBERTIAN: { /* material_lambertian.cc:61-70 */
+      const vec3 w = dot(wo, n) > 0 ? n : neg(n);
+      out.dir = hemisphere_psa(w, s);
+      scalar = 1;
+      break;
+    }
+    case AMBER_CUDA_MAT_PHONG: { /* material_phong.cc:81-106 */
+      const vec3 refl = perfect_reflection(wo, n, dot(wo, n));
+      const float cos_o = dot(wo, n);
+      for (;;) {
+        const vec3 dir = cosine_power(refl, m->param, s);
+        const float cos_i = dot(dir, n);
+        if (cos_o * cos_i <= 0) continue;
+        out.dir = dir;
+        scalar = (m->param + 2) / (m->param + 1) * fabsf(cos_i);
+        break;
+      }
+      break;
+    }
+    case AMBER_CUDA_MAT_SPECULAR: /* material_specular.cc:62-70 */
+      out.dir = perfect_reflection(wo, n, dot(wo, n));
+      scalar = 1;
+      break;
+    case AMBER_CUDA_MAT_REFRACTION: { /* material_refraction.cc:177-220 */
+      const float signed_cos_alpha = dot(wo, n);
+      const float ior = signed_cos_alpha > 0 ? 1 / m->param : m->param;
+      const float squared_cos_beta = 1 - (1 - signed_cos_alpha * signed_cos_alpha) * (ior * ior);
+      const vec3 dir_r = perfect_reflection(wo, n, signed_cos_alpha);
+      if (squared_cos_beta < 0) {
+        out.dir = dir_r;
+        scalar = 1;
+        break;
+      }
+      {
+        const float cos_alpha = fabsf(signed_cos_alpha);
+        const float cos_beta = sqrtf(squared_cos_beta);
+        const vec3 dir_t = add(scale(-ior, wo),
+                               scale((signed_cos_alpha < 0 ? 1 : -1) * cos_beta + ior * signed_cos_alpha, n));
+        const float rho_r = schlick(r0, cos_alpha);
+        const float rho_t = (1 - rho_r) * (ior * ior);
+        const float rho_sum = rho_r + rho_t;
+        const float p_r = (rho_r / rho_sum + 0.5f) / 2;
+        const float p_t = (rho_t / rho_sum + 0.5f) / 2;
+        if (uniform(s) < p_r) {
+          out.dir = dir_r;
+          scalar = rho_r / p_r;
+        } else {
+          out.dir = dir_t;
+          scalar = rho_t / p_t;
+        }
+      }
+      break;
+    }
+    case AMBER_CUDA_MAT_EYE: /* material_eye.h:146-155 */
+      out.dir = neg(wo);
+      out.weight = V(1, 1, 1);
+      return out;
+    default: /* DiffuseLight::SampleLight returns Scatter(): weight 0, material_diffuse_light.h:185-194 */
+      out.weight = V(0, 0, 0);
+      return out;
+  }
+  out.weight = scale(scalar, rho); /* scatter.weight * rho_ */
+  return out;
+}
+
+/* Material<RGB>::BSDF: Lambertian material_lambertian.cc:34-49, Phong material_phong.cc:39-61,
+ * Specular material_specular.cc:34-49 (kDiracDelta = 1), others 0 / not connectable. */
+static vec3 material_bsdf(const amber_cuda_material* m, vec3 n, vec3 wo, vec3 wi) {
+  const vec3 rho = V(m->rgb[0], m->rgb[1], m->rgb[2]);
+  const float cos_o = dot(wo, n), cos_i = dot(wi, n);
+  if (m->kind == AMBER_CUDA_MAT_LAMBERTIAN) {
+    if (cos_o * cos_i <= 0) return V(0, 0, 0);
+    return scale(1 / PI_F, rho);
+  }
+  if (m->kind == AMBER_CUDA_MAT_PHONG) {
+    vec3 refl;
+    float cos_alpha;
+    if (cos_o * cos_i <= 0) return V(0, 0, 0);
+    refl = perfect_reflection(wi, n, cos_i);
+    cos_alpha = fmaxf(0, dot(refl, wo));
+    return scale((m->param + 2) / (2 * PI_F) * powf(cos_alpha, m->param), rho);
+  }
+  return V(0, 0, 0);
+}
+
+/* DiffuseLight::Radiance, material_diffuse_light.h:127-139 (0 for every other material,
+ * include/amber/scene/material.h:101-109) */
+static vec3 material_radiance(const amber_cuda_material* m, vec3 n, vec3 wo) {
+  if (m->kind != AMBER_CUDA_MAT_DIFFUSE_LIGHT) return V(0, 0, 0);
+  if (dot(wo, n) <= 0) return V(0, 0, 0);
+  return V(m->rgb[0], m->rgb[1], m->rgb[2]);
+}
+
+/* Triangle::SampleSurfacePoint, primitive_triangle.cc:136-150 */
+static vec3 triangle_sample(vec3 v0, vec3 v1, vec3 v2, sampler* s) {
+  float u = uniform(s);
+  float v = uniform(s);
+  if (u + v >= 1) {
+    u = 1 - u;
+    v = 1 - v;
+  }
+  return add(add(scale(1 - u - v, v0), scale(u, v1)), scale(v, v2));
+}
+
+/* PixelBound::Uniform (src/amber/rendering/sensor.cc:94-101,111-120) +
+ * BasicThin::GenerateRay / PDFArea / PDFDirection (src/amber/scene/lens_thin.cc:70-107,132-148) */
+static void generate_eye_ray(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h,
+                             uint32_t px, uint32_t py, sampler* s, vec3* origin, vec3* direction,
+                             float* weight) {
+  const float nb = (float)sc->n_blades;
+  float f = floorf(uniform(s) * nb);
+  size_t pos = (size_t)f;
+  vec3 aperture_origin, aperture_point, sensor_point, dir_local, dir_world, dir_back;
+  float su, sv;
+  double factor, pdf_direction_d;
+  float pdf_direction;
+  if (pos > (size_t)sc->n_blades - 1) pos = (size_t)sc->n_blades - 1;
+  aperture_origin = triangle_sample(sc->blades[pos][0], sc->blades[pos][1], sc->blades[pos][2], s);
+  aperture_point = mat3_apply(sc->local, sub(aperture_origin, sc->lens_origin));
+  /* Vector2((x + xi) / W, (y + xi) / H), sensor.cc:114-117: the order in which the two
+   * constructor arguments are evaluated is unspecified in C++; g++ (the compiler that
+   * builds oracle/_ref) evaluates them right to left, so the Y uniform is drawn first. */
+  sv = ((float)py + uniform(s)) / (float)h;
+  su = ((float)px + uniform(s)) / (float)w;
+  sensor_point = V((su - 0.5f) * film_w, (sv - 0.5f) * film_h, sc->sensor_distance);
+  dir_local = normalize(sub(scale(-sc->focus_distance / sc->sensor_distance, sensor_point), aperture_point));
+  factor = pow((double)(normalize(sub(sensor_point, aperture_point)).z / dir_local.z), 4.0);
+  dir_world = normalize(mat3_apply(sc->global, dir_local)); /* Ray(origin, Vector3) normalises, ray.h:52-56 */
+  dir_back = mat3_apply(sc->local, dir_world);
+  /* sensor.Size() / sensor.SceneArea() * pow(sd, 2) / pow(dz, 4): float, then double */
+  pdf_direction_d = (double)((float)((unsigned long)w * (unsigned long)h) / (film_w * film_h)) *
+                    pow((double)sc->sensor_distance, 2.0) / pow((double)dir_back.z, 4.0);
+  pdf_direction = (float)pdf_direction_d;
+  *origin = aperture_origin;
+  *direction = dir_world;
+  *weight = (float)(factor / sc->p_area / pdf_direction);
+}
+
+/* ---- exported unit entry points --------------------------------------------------- */
+typedef struct {
+  const oracle_scene* scene;
+  uint64_t n;
+  const float *origins, *directions;
+  int32_t* prim;
+  float* t;
+  int worker, workers;
+} cast_job;
+
+static void* cast_worker(void* arg) {
+  cast_job* job = (cast_job*)arg;
+  uint64_t i;
+  for (i = (uint64_t)job->worker; i < job->n; i += (uint64_t)job->workers) {
+    hit_t h;
+    const vec3 o = V(job->origins[3 * i], job->origins[3 * i + 1], job->origins[3 * i + 2]);
+    const vec3 d = V(job->directions[3 * i], job->directions[3 * i + 1], job->directions[3 * i + 2]);
+    job->prim[i] = scene_cast(job->scene, o, d, &h);
+    job->t[i] = h.t;
+  }
+  return NULL;
+}
+
+void oracle_cast(const oracle_scene* scene, uint64_t n, const float* origins, const float* directions,
+                 int32_t* prim, float* t, int threads) {
+  pthread_t tid[64];
+  cast_job jobs[64];
+  int k;
+  if (threads < 1) threads = 1;
+  if (threads > 64) threads = 64;
+  for (k = 0; k < threads; k++) {
+    cast_job j = {scene, n, origins, directions, prim, t, k, threads};
+    jobs[k] = j;
+    pthread_create(&tid[k], NULL, cast_worker, &jobs[k]);
+  }
+  for (k = 0; k < threads; k++) pthread_join(tid[k], NULL);
+}
+
+void oracle_sample_light(const amber_cuda_material* material, uint64_t n, const float* normal,
+                         const float* dir_out, const float* xi8, float* dir_in, float* weight,
+                         int32_t* draws) {
+  amber_cuda_material m = *material;
+  float r0 = 0;
+  uint64_t i;
+  if (m.kind == AMBER_CUDA_MAT_REFRACTION || m.kind == AMBER_CUDA_MAT_EYE) m.rgb[0] = m.rgb[1] = m.rgb[2] = 1.0f;
+  if (m.kind == AMBER_CUDA_MAT_REFRACTION) r0 = (float)pow((double)((m.param - 1) / (m.param + 1)), 2.0);
+  for (i = 0; i < n; i++) {
+    sampler s = {NULL, xi8 + 8 * i, 8, 0};
+    const scatter_t sc = material_sample_light(&m, r0, V(normal[3 * i], normal[3 * i + 1], normal[3 * i + 2]),
+                                               V(dir_out[3 * i], dir_out[3 * i + 1], dir_out[3 * i + 2]), &s);
+    dir_in[3 * i] = sc.dir.x; dir_in[3 * i + 1] = sc.dir.y; dir_in[3 * i + 2] = sc.dir.z;
+    weight[3 * i] = sc.weight.x; weight[3 * i + 1] = sc.weight.y; weight[3 * i + 2] = sc.weight.z;
+    draws[i] = s.used;
+  }
+}
+
+void oracle_bsdf(const amber_cuda_material* material, uint64_t n, const float* normal,
+                 const float* dir_out, const float* dir_in, float* bsdf, float* radiance) {
+  uint64_t i;
+  for (i = 0; i < n; i++) {
+    const vec3 nn = V(normal[3 * i], normal[3 * i + 1], normal[3 * i + 2]);
+    const vec3 wo = V(dir_out[3 * i], dir_out[3 * i + 1], dir_out[3 * i + 2]);
+    const vec3 wi = V(dir_in[3 * i], dir_in[3 * i + 1], dir_in[3 * i + 2]);
+    const vec3 f = material_bsdf(material, nn, wo, wi);
+    const vec3 le = material_radiance(material, nn, wo);
+    bsdf[3 * i] = f.x; bsdf[3 * i + 1] = f.y; bsdf[3 * i + 2] = f.z;
+    radiance[3 * i] = le.x; radiance[3 * i + 1] = le.y; radiance[3 * i + 2] = le.z;
+  }
+}
+
+void oracle_eye_rays(const oracle_scene* scene, uint32_t w, uint32_t h, float film_w, float film_h,
+                     uint64_t n, const uint32_t* px, const uint32_t* py, const float* xi5,
+                     float* origin, float* direction, float* weight) {
+  uint64_t i;
+  for (i = 0; i < n; i++) {
+    sampler s = {NULL, xi5 + 5 * i, 5, 0};
+    vec3 o, d;
+    generate_eye_ray(scene, w, h, film_w, film_h, px[i], py[i], &s, &o, &d, &weight[i]);
+    origin[3 * i] = o.x; origin[3 * i + 1] = o.y; origin[3 * i + 2] = o.z;
+    direction[3 * i] = d.x; direction[3 * i + 1] = d.y; direction[3 * i + 2] = d.z;
+  }
+}
+
+/* ---- the path tracer ------------------------------------------------------------------
+ * REFERENCE estimator: PathTracing<RGB>::Thread::Render, src/amber/rendering/algorithm_pt.cc:125-160,
+ *   plus a bounce cap (the reference has none, :137).
+ * NEE estimator: equal in expectation.  At a connectable vertex (SurfaceType::Diffuse:
+ *   Lambertian, Phong) one light point is sampled as LightSet::GenerateRay does
+ *   (include/amber/scene/light_set.h:83-104) and connected with the s = 1 term of
+ *   include/amber/rendering/bidirectional_path_sampling.h:956-1016; the emission of an
+ *   emitting TRIANGLE found by the next BSDF-sampled ray is then not counted (it was just
+ *   sampled), while after a camera / Specular / Refraction / Eye vertex it is. */
+typedef struct {
+  uint64_t closest_rays, shadow_rays, truncated, paths;
+} counters;
+
+static void trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h,
+                       uint32_t px, uint32_t py, philox_stream* stream, uint32_t max_depth, int estimator,
+                       double rgb[3], counters* count) {
+  sampler s = {stream, NULL, 0, 0};
+  vec3 origin, direction, weight3, measurement = V(0, 0, 0);
+  float weight;
+  int count_emission = 1;
+  uint32_t depth;
+  generate_eye_ray(sc, w, h, film_w, film_h, px, py, &s, &origin, &direction, &weight);
+  weight3 = V(weight, weight, weight);
+  count->paths++;
+  for (depth = 1;; depth++) {
+    hit_t hit;
+    const int object = scene_cast(sc, origin, direction, &hit);
+    const amber_cuda_material* m;
+    const prim* p;
+    vec3 wo;
+    scatter_t scatter;
+    float p_rr;
+    int connectable;
+    count->closest_rays++;
+    if (object < 0) break;
+    p = &sc->prims[object];
+    m = &sc->materials[p->material];
+    wo = neg(direction);
+    /* measurement += weight * Radiance(...), algorithm_pt.cc:144 */
+    {
+      const int sampled_by_nee = estimator == AMBER_CUDA_ESTIMATOR_NEE && p->kind == AMBER_CUDA_PRIM_TRIANGLE;
+      if (!sampled_by_nee || count_emission) {
+        measurement = add(measurement, mul(weight3, material_radiance(m, hit.normal, wo)));
+      }
+    }
+    connectable = estimator == AMBER_CUDA_ESTIMATOR_NEE && sc->n_lights > 0 &&
+                  (m->kind == AMBER_CUDA_MAT_LAMBERTIAN || m->kind == AMBER_CUDA_MAT_PHONG);
+    if (connectable) {
+      /* light choice: lower_bound over cumulative powers of Uniform(total), light_set.h:87-91 */
+      const float target = uniform(&s) * sc->total_power;
+      uint32_t li = 0;
+      const light* l;
+      const prim* lp;
+      vec3 y, xy, wi, contribution;
+      float dist2, dist, cos_y, g;
+      while (li + 1 < sc->n_lights && sc->lights[li].cumulative_power < target) li++;
+      l = &sc->lights[li];
+      lp = &sc->prims[l->prim_index];
+      y = triangle_sample(lp->v0, lp->v1, lp->v2, &s);
+      xy = sub(y, hit.position);
+      dist2 = dot(xy, xy);
+      dist = sqrtf(dist2);
+      wi = V(xy.x / dist, xy.y / dist, xy.z / dist);
+      cos_y = -dot(wi, lp->normal);
+      if (cos_y > 0) { /* one-sided emitter, material_diffuse_light.h:133-135 */
+        const amber_cuda_material* lm = &sc->materials[lp->material];
+        const vec3 le_over_pdf = V(lm->rgb[0] / l->pdf_area, lm->rgb[1] / l->pdf_area, lm->rgb[2] / l->pdf_area);
+        /* GeometryFactor, include/amber/prelude/geometry.h:65-75 */
+        g = fabsf(cos_y * dot(wi, hit.normal)) / dist2;
+        contribution = scale(g, mul(mul(weight3, le_over_pdf), material_bsdf(m, hit.normal, wo, wi)));
+        if (max3(contribution) > 0) {
+          hit_t blocker;
+          count->shadow_rays++;
+          /* visible iff nothing lies in (kEPS, dist * (1 - 1e-4)) along x -> y */
+          if (scene_cast(sc, hit.position, wi, &blocker) < 0 || !(blocker.t < dist * (1.0f - 1e-4f))) {
+            measurement = add(measurement, contribution);
+          }
+        }
+      }
+    }
+    scatter = material_sample_light(m, sc->r0[p->material], hit.normal, wo, &s);
+    /* p = min(kRussianRoulette, Max(weight)); stop if Uniform >= p, algorithm_pt.cc:148-153 */
+    p_rr = fminf((float)kRussianRoulette, max3(scatter.weight));
+    if (uniform(&s) >= p_rr) break;
+    if (depth >= max_depth) {
+      count->truncated++;
+      break;
+    }
+    origin = hit.position; /* Ray(hit.Position(), scatter.DirectionIn()): no re-normalisation, ray.h:58-62 */
+    direction = scatter.dir;
+    weight3 = mul(weight3, V(scatter.weight.x / p_rr, scatter.weight.y / p_rr, scatter.weight.z / p_rr));
+    count_emission = !connectable;
+  }
+  rgb[0] += measurement.x;
+  rgb[1] += measurement.y;
+  rgb[2] += measurement.z;
+}
+
+typedef struct {
+  const oracle_scene* scene;
+  uint32_t w, h;
+  float film_w, film_h;
+  uint64_t sample_begin, seed;
+  uint32_t sample_count, max_depth;
+  int estimator, worker, workers;
+  float* rgb;
+  counters count;
+} render_job;
+
+static void* render_worker(void* arg) {
+  render_job* job = (render_job*)arg;
+  uint32_t x, y;
+  memset(&job->count, 0, sizeof job->count);
+  for (y = (uint32_t)job->worker; y < job->h; y += (uint32_t)job->workers) {
+    for (x = 0; x < job->w; x++) {
+      double sum[3] = {0, 0, 0};
+      uint64_t s;
+      int c;
+      for (s = job->sample_begin; s < job->sample_begin + job->sample_count; s++) {
+        philox_stream stream;
+        philox_stream_reset(&stream, job->seed, x + y * job->w, s);
+        trace_path(job->scene, job->w, job->h, job->film_w, job->film_h, x, y, &stream, job->max_depth,
+                   job->estimator, sum, &job->count);
+      }
+      for (c = 0; c < 3; c++) job->rgb[((size_t)x + (size_t)y * job->w) * 3 + c] = (float)(sum[c] / job->sample_count);
+    }
+  }
+  return NULL;
+}
+
+void oracle_render(const oracle_scene* scene, uint32_t w, uint32_t h, float film_w, float film_h,
+                   uint64_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_depth,
+                   int estimator, int threads, float* rgb, uint64_t* stats) {
+  pthread_t tid[64];
+  render_job jobs[64];
+  int k;
+  if (threads < 1) threads = 1;
+  if (threads > 64) threads = 64;
+  if (max_depth == 0) max_depth = 1u << 16;
+  for (k = 0; k < threads; k++) {
+    render_job j;
+    memset(&j, 0, sizeof j);
+    j.scene = scene; j.w = w; j.h = h; j.film_w = film_w; j.film_h = film_h;
+    j.sample_begin = sample_begin; j.seed = seed; j.sample_count = sample_count; j.max_depth = max_depth;
+    j.estimator = estimator; j.worker = k; j.workers = threads; j.rgb = rgb;
+    jobs[k] = j;
+    pthread_create(&tid[k], NULL, render_worker, &jobs[k]);
+  }
+  if (stats) memset(stats, 0, 4 * sizeof(uint64_t));
+  for (k = 0; k < threads; k++) {
+    pthread_join(tid[k], NULL);
+    if (stats) {
+      stats[0] += jobs[k].count.closest_rays;
+      stats[1] += jobs[k].count.shadow_rays;
+      stats[2] += jobs[k].count.truncated;
+      stats[3] += jobs[k].count.paths;
+    }
+  }
+}

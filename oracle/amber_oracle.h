@@ -1,0 +1,54 @@
+/*
+ * amber_oracle.h -- TEST INFRASTRUCTURE.  Not part of the product.
+ *
+ * Plain-C restatement of amber's path-tracing hot path (the algorithm of
+ * /root/reference, cited function by function in amber_oracle.c), taking the same
+ * flat scene description as the CUDA library.  It is the checker for the GPU path:
+ * only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may call it.
+ *
+ * Pinning: tests/test_oracle_pinned.py requires this restatement to reproduce the
+ * UNMODIFIED reference (oracle/_ref/libamber_ref.so) -- closest hits, BSDF samples,
+ * camera rays and whole rendered images bit for bit on the same random stream -- and
+ * checks it against the golden fixtures under tests/golden/ generated from that
+ * reference (scripts/make_golden.py), so the oracle stays pinned where /root/reference
+ * is absent.  The reference has no tests or golden vectors of its own.
+ */
+#ifndef AMBER_ORACLE_H_
+#define AMBER_ORACLE_H_
+
+#include <stdint.h>
+
+#include "../include/amber_cuda.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct oracle_scene oracle_scene;
+
+oracle_scene* oracle_scene_create(const amber_cuda_scene_desc* desc);
+void oracle_scene_destroy(oracle_scene* scene);
+
+/* closest hit, brute force in creation order (raytracer::List semantics) */
+void oracle_cast(const oracle_scene* scene, uint64_t n, const float* origins, const float* directions,
+                 int32_t* prim, float* t, int threads);
+
+void oracle_sample_light(const amber_cuda_material* material, uint64_t n, const float* normal,
+                         const float* dir_out, const float* xi8, float* dir_in, float* weight,
+                         int32_t* draws);
+void oracle_bsdf(const amber_cuda_material* material, uint64_t n, const float* normal,
+                 const float* dir_out, const float* dir_in, float* bsdf, float* radiance);
+void oracle_eye_rays(const oracle_scene* scene, uint32_t w, uint32_t h, float film_w, float film_h,
+                     uint64_t n, const uint32_t* px, const uint32_t* py, const float* xi5,
+                     float* origin, float* direction, float* weight);
+
+/* Path tracer on the device's Philox stream.  estimator: AMBER_CUDA_ESTIMATOR_*.
+ * stats[0] closest rays, [1] shadow rays, [2] truncated paths, [3] paths. */
+void oracle_render(const oracle_scene* scene, uint32_t w, uint32_t h, float film_w, float film_h,
+                   uint64_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_depth,
+                   int estimator, int threads, float* rgb, uint64_t* stats);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,67 @@
+/*
+ * philox_stream.h -- TEST INFRASTRUCTURE (oracle/).  Not part of the product.
+ *
+ * The per-path random stream the CUDA kernels use, restated in plain C so the CPU
+ * oracle and the reference harness can replay exactly the uniforms a device path
+ * consumed.  Spec (DESIGN.md "Random stream"):
+ *
+ *   Philox4x32-10 (Salmon et al., SC'11), key = (seed_lo, seed_hi),
+ *   counter = (pixel_index, sample_lo, sample_hi, block); draw j of a path is word
+ *   j%4 of block j/4, mapped to [0,1) as (word >> 8) * 2^-24.
+ *
+ * The reference draws `static_cast<float>(uniform_real_distribution<double>(0,1))`
+ * from a per-thread mt19937_64 (include/amber/prelude/sampling.h:148-161,
+ * src/amber/rendering/algorithm_pt.cc:104); which engine feeds Sampler::operator()
+ * is not part of its numerics, so a Sampler subclass fed by this stream drives the
+ * unmodified reference code along exactly the device's paths.
+ */
+#ifndef AMBER_ORACLE_PHILOX_STREAM_H_
+#define AMBER_ORACLE_PHILOX_STREAM_H_
+
+#include <stdint.h>
+
+typedef struct philox_stream {
+  uint32_t key[2];
+  uint32_t ctr[3]; /* pixel, sample_lo, sample_hi */
+  uint32_t words[4];
+  uint32_t draws; /* number of uniforms consumed so far */
+} philox_stream;
+
+static inline void philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+  uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3];
+  uint32_t k0 = key[0], k1 = key[1];
+  for (int round = 0; round < 10; round++) {
+    const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+    const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+    const uint32_t n1 = (uint32_t)p1;
+    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    const uint32_t n3 = (uint32_t)p0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+static inline void philox_stream_reset(philox_stream* s, uint64_t seed, uint32_t pixel,
+                                       uint64_t sample) {
+  s->key[0] = (uint32_t)seed;
+  s->key[1] = (uint32_t)(seed >> 32);
+  s->ctr[0] = pixel;
+  s->ctr[1] = (uint32_t)sample;
+  s->ctr[2] = (uint32_t)(sample >> 32);
+  s->draws = 0;
+}
+
+static inline float philox_stream_next(philox_stream* s) {
+  const uint32_t word = s->draws & 3u;
+  if (word == 0) {
+    const uint32_t ctr[4] = {s->ctr[0], s->ctr[1], s->ctr[2], s->draws >> 2};
+    philox4x32_10(ctr, s->key, s->words);
+  }
+  s->draws++;
+  return (float)(s->words[word] >> 8) * (1.0f / 16777216.0f);
+}
+
+#endif /* AMBER_ORACLE_PHILOX_STREAM_H_ */

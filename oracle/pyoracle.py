@@ -1,0 +1,218 @@
+"""TEST INFRASTRUCTURE: ctypes wrappers for the two checkers under oracle/.
+
+  * ``Reference`` -- oracle/_ref/libamber_ref.so, the UNMODIFIED reference compiled
+    from /root/reference (oracle/Makefile, ``make ref``) behind oracle/ref_harness.cc.
+  * ``Oracle``    -- oracle/libamber_oracle.so, the plain-C restatement
+    (oracle/amber_oracle.c).
+
+Only tests/, ``__graft_entry__.smoke()`` and bench.py's cpu_baseline / --impl
+reference legs may import this module.  The product (amber_b200/) never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REF_LIB = os.path.join(_HERE, "_ref", "libamber_ref.so")
+ORACLE_LIB = os.path.join(_HERE, "libamber_oracle.so")
+REFERENCE_ROOT = "/root/reference"
+
+
+def build(ref: bool = True) -> None:
+    """Compile the C restatement and, when /root/reference is present, the reference."""
+    subprocess.check_call(["make", "-C", _HERE, "oracle"], stdout=subprocess.DEVNULL)
+    if ref and os.path.isdir(REFERENCE_ROOT):
+        subprocess.check_call(["make", "-C", _HERE, "ref", "-j8"], stdout=subprocess.DEVNULL)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Reference:
+    """The unmodified reference behind a flat scene description."""
+
+    def __init__(self, flat_scene=None, builtin_cornel_box=False):
+        if not os.path.exists(REF_LIB):
+            raise FileNotFoundError(REF_LIB)
+        self.lib = C.CDLL(REF_LIB)
+        self.lib.ref_scene_create.restype = C.c_void_p
+        self.lib.ref_scene_create_cornel_box.restype = C.c_void_p
+        self.flat = flat_scene
+        if builtin_cornel_box:
+            self.handle = C.c_void_p(self.lib.ref_scene_create_cornel_box())
+        else:
+            self.handle = C.c_void_p(self.lib.ref_scene_create(C.byref(flat_scene.desc)))
+
+    def close(self):
+        if self.handle:
+            self.lib.ref_scene_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def cast(self, origins, directions, accel=0, threads=8):
+        o, d = _f32(origins), _f32(directions)
+        n = o.shape[0]
+        prim = np.empty(n, dtype=np.int32)
+        t = np.empty(n, dtype=np.float32)
+        rc = self.lib.ref_cast(self.handle, C.c_int(accel), C.c_uint64(n), _ptr(o), _ptr(d),
+                               _ptr(prim), _ptr(t), C.c_int(threads))
+        assert rc == 0
+        return prim, t
+
+    def sample_light(self, material, normals, dirs_out, xi8):
+        n_, wo, xi = _f32(normals), _f32(dirs_out), _f32(xi8)
+        n = n_.shape[0]
+        wi = np.empty((n, 3), dtype=np.float32)
+        w = np.empty((n, 3), dtype=np.float32)
+        draws = np.empty(n, dtype=np.int32)
+        rc = self.lib.ref_sample_light(C.byref(material), C.c_uint64(n), _ptr(n_), _ptr(wo), _ptr(xi),
+                                       _ptr(wi), _ptr(w), _ptr(draws))
+        assert rc == 0
+        return wi, w, draws
+
+    def bsdf(self, material, normals, dirs_out, dirs_in):
+        n_, wo, wi = _f32(normals), _f32(dirs_out), _f32(dirs_in)
+        n = n_.shape[0]
+        f = np.empty((n, 3), dtype=np.float32)
+        le = np.empty((n, 3), dtype=np.float32)
+        rc = self.lib.ref_bsdf(C.byref(material), C.c_uint64(n), _ptr(n_), _ptr(wo), _ptr(wi), _ptr(f), _ptr(le))
+        assert rc == 0
+        return f, le
+
+    def triangle_sample(self, v9, xi2):
+        v, xi = _f32(v9), _f32(xi2)
+        n = xi.shape[0]
+        p = np.empty((n, 3), dtype=np.float32)
+        nn = np.empty((n, 3), dtype=np.float32)
+        area = C.c_float()
+        rc = self.lib.ref_triangle_sample(_ptr(v), C.c_uint64(n), _ptr(xi), _ptr(p), _ptr(nn), C.byref(area))
+        assert rc == 0
+        return p, nn, area.value
+
+    def eye_rays(self, w, h, film_w, film_h, px, py, xi5):
+        px_ = np.ascontiguousarray(px, dtype=np.uint32)
+        py_ = np.ascontiguousarray(py, dtype=np.uint32)
+        xi = _f32(xi5)
+        n = px_.shape[0]
+        o = np.empty((n, 3), dtype=np.float32)
+        d = np.empty((n, 3), dtype=np.float32)
+        wt = np.empty(n, dtype=np.float32)
+        rc = self.lib.ref_eye_rays(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                                   C.c_float(film_h), C.c_uint64(n), _ptr(px_), _ptr(py_), _ptr(xi),
+                                   _ptr(o), _ptr(d), _ptr(wt))
+        assert rc == 0
+        return o, d, wt
+
+    def render(self, w, h, film_w, film_h, spp, threads, algo=0, want_image=True):
+        """The reference's own PT (algo 0) / BDPT (algo 1).  Returns (rgb, casts, seconds)."""
+        rgb = np.empty((h, w, 3), dtype=np.float32) if want_image else None
+        casts = C.c_uint64()
+        seconds = C.c_double()
+        rc = self.lib.ref_render(self.handle, C.c_int(algo), C.c_uint32(w), C.c_uint32(h),
+                                 C.c_float(film_w), C.c_float(film_h), C.c_uint32(spp),
+                                 C.c_uint32(threads), _ptr(rgb) if want_image else None,
+                                 C.byref(casts), C.byref(seconds))
+        assert rc == 0
+        return rgb, casts.value, seconds.value
+
+    def render_stream(self, w, h, film_w, film_h, sample_begin, sample_count, seed, max_depth=0,
+                      threads=8):
+        rgb = np.empty((h, w, 3), dtype=np.float32)
+        stats = (C.c_uint64 * 2)()
+        rc = self.lib.ref_render_stream(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                                        C.c_float(film_h), C.c_uint64(sample_begin),
+                                        C.c_uint32(sample_count), C.c_uint64(seed),
+                                        C.c_uint32(max_depth), C.c_uint32(threads), _ptr(rgb), stats)
+        assert rc == 0
+        return rgb, {"rays": stats[0], "truncated": stats[1]}
+
+
+def reference_available() -> bool:
+    return os.path.exists(REF_LIB)
+
+
+class Oracle:
+    """The plain-C restatement (oracle/amber_oracle.c) behind a flat scene description."""
+
+    def __init__(self, flat_scene):
+        if not os.path.exists(ORACLE_LIB):
+            build(ref=False)
+        self.lib = C.CDLL(ORACLE_LIB)
+        self.lib.oracle_scene_create.restype = C.c_void_p
+        self.flat = flat_scene
+        self.handle = C.c_void_p(self.lib.oracle_scene_create(C.byref(flat_scene.desc)))
+
+    def close(self):
+        if self.handle:
+            self.lib.oracle_scene_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def cast(self, origins, directions, threads=8):
+        o, d = _f32(origins), _f32(directions)
+        n = o.shape[0]
+        prim = np.empty(n, dtype=np.int32)
+        t = np.empty(n, dtype=np.float32)
+        self.lib.oracle_cast(self.handle, C.c_uint64(n), _ptr(o), _ptr(d), _ptr(prim), _ptr(t), C.c_int(threads))
+        return prim, t
+
+    def sample_light(self, material, normals, dirs_out, xi8):
+        n_, wo, xi = _f32(normals), _f32(dirs_out), _f32(xi8)
+        n = n_.shape[0]
+        wi = np.empty((n, 3), dtype=np.float32)
+        w = np.empty((n, 3), dtype=np.float32)
+        draws = np.empty(n, dtype=np.int32)
+        self.lib.oracle_sample_light(C.byref(material), C.c_uint64(n), _ptr(n_), _ptr(wo), _ptr(xi),
+                                     _ptr(wi), _ptr(w), _ptr(draws))
+        return wi, w, draws
+
+    def bsdf(self, material, normals, dirs_out, dirs_in):
+        n_, wo, wi = _f32(normals), _f32(dirs_out), _f32(dirs_in)
+        n = n_.shape[0]
+        f = np.empty((n, 3), dtype=np.float32)
+        le = np.empty((n, 3), dtype=np.float32)
+        self.lib.oracle_bsdf(C.byref(material), C.c_uint64(n), _ptr(n_), _ptr(wo), _ptr(wi), _ptr(f), _ptr(le))
+        return f, le
+
+    def eye_rays(self, w, h, film_w, film_h, px, py, xi5):
+        px_ = np.ascontiguousarray(px, dtype=np.uint32)
+        py_ = np.ascontiguousarray(py, dtype=np.uint32)
+        xi = _f32(xi5)
+        n = px_.shape[0]
+        o = np.empty((n, 3), dtype=np.float32)
+        d = np.empty((n, 3), dtype=np.float32)
+        wt = np.empty(n, dtype=np.float32)
+        self.lib.oracle_eye_rays(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                                 C.c_float(film_h), C.c_uint64(n), _ptr(px_), _ptr(py_), _ptr(xi),
+                                 _ptr(o), _ptr(d), _ptr(wt))
+        return o, d, wt
+
+    def render(self, w, h, film_w, film_h, sample_begin, sample_count, seed, max_depth=0,
+               estimator=0, threads=8):
+        rgb = np.empty((h, w, 3), dtype=np.float32)
+        stats = (C.c_uint64 * 4)()
+        self.lib.oracle_render(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                               C.c_float(film_h), C.c_uint64(sample_begin), C.c_uint32(sample_count),
+                               C.c_uint64(seed), C.c_uint32(max_depth), C.c_int(estimator),
+                               C.c_int(threads), _ptr(rgb), stats)
+        return rgb, {"closest_rays": stats[0], "shadow_rays": stats[1], "truncated": stats[2],
+                     "paths": stats[3]}
