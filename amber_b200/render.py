@@ -1,0 +1,233 @@
+"""Host-side mirror of the reference's interface for the path-tracing path.
+
+The reference drives its path tracer as
+``algorithm.Render(scene, sensor, context) -> Image<RGB>``
+(``include/amber/rendering/algorithm.h:31-45``; called from
+``src/amber/cli/application.cc:149-152``).  The same three nouns exist here with the
+same meaning, so that the tests read like a user of the reference:
+
+  * ``Sensor(width, height, film_width, film_height)`` -- ``rendering::Sensor``
+    (``src/amber/rendering/sensor.cc:28-38``).
+  * ``Context(n_threads, n_iterations)`` -- ``cli::Context``
+    (``src/amber/cli/context.cc:34-67``): one successful ``iterate()`` is one sample
+    per pixel over the whole frame; ``expire()`` ends the render early and the
+    partial mean is returned.
+  * ``CudaPathTracing(...).render(scene, sensor, context)`` -- the ``Algorithm<RGB>``
+    whose body runs on the GPU through the C ABI (``include/amber_cuda.h``).
+
+``Device`` is the thin object wrapper over one ``amber_cuda_ctx``.  There is no CPU
+path: constructing a ``Device`` without the built library or without a GPU raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+
+import numpy as np
+
+from . import capi
+from .scene import FlatScene
+
+
+class Sensor:
+    """rendering::Sensor: pixel grid + film size in scene units."""
+
+    def __init__(self, width: int, height: int, film_width: float = 0.036, film_height: float | None = None):
+        self.width = int(width)
+        self.height = int(height)
+        self.film_width = float(film_width)
+        # src/amber/cli/application.cc:89-94: 36 mm film, height scaled by aspect
+        self.film_height = float(film_height) if film_height is not None else 0.036 * height / width
+
+    def size(self) -> int:
+        return self.width * self.height
+
+
+class Context:
+    """cli::Context: thread count, iteration budget, expiry."""
+
+    def __init__(self, n_threads: int = 1, n_iterations: int = 0):
+        self._lock = threading.Lock()
+        self._n_threads = n_threads
+        self._n_iterations = n_iterations
+        self._started = 0
+        self._expired = False
+
+    def thread_count(self) -> int:
+        return self._n_threads
+
+    def iteration_count(self) -> int:
+        with self._lock:
+            return self._started
+
+    def iterate(self) -> bool:
+        with self._lock:
+            if self._n_iterations > 0 and self._started >= self._n_iterations:
+                return False
+            if self._expired:
+                return False
+            self._started += 1
+            return True
+
+    def expire(self) -> None:
+        with self._lock:
+            self._expired = True
+
+
+class Device:
+    """One ``amber_cuda_ctx`` (one GPU, one stream)."""
+
+    def __init__(self, device: int = 0, lib_path: str | None = None):
+        self.lib = capi.load(lib_path)
+        self.ctx = C.c_void_p()
+        rc = self.lib.amber_cuda_create(C.byref(self.ctx), int(device))
+        if rc != 0:
+            msg = self.lib.amber_cuda_last_error(None)
+            raise capi.AmberCudaError(f"amber_cuda_create failed ({rc}): {msg.decode() if msg else '?'}")
+        self.device = int(device)
+        self.sensor: Sensor | None = None
+        self.scene: FlatScene | None = None
+
+    def _check(self, rc: int) -> None:
+        capi.check(self.lib, self.ctx, rc)
+
+    def close(self) -> None:
+        if self.ctx:
+            self.lib.amber_cuda_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- scene / sensor -----------------------------------------------------------
+    def upload_scene(self, scene: FlatScene) -> None:
+        self._check(self.lib.amber_cuda_upload_scene(self.ctx, C.byref(scene.desc)))
+        self.scene = scene
+
+    def set_sensor(self, sensor: Sensor) -> None:
+        self._check(self.lib.amber_cuda_set_sensor(self.ctx, sensor.width, sensor.height,
+                                                   sensor.film_width, sensor.film_height))
+        self.sensor = sensor
+
+    def film_clear(self) -> None:
+        self._check(self.lib.amber_cuda_film_clear(self.ctx))
+
+    # -- rendering ----------------------------------------------------------------
+    def render(self, sample_begin: int, sample_count: int, seed: int = 1, max_depth: int = 0,
+               estimator: int = capi.ESTIMATOR_NEE, pool_paths: int = 0) -> None:
+        params = capi.RenderParams(sample_begin, sample_count, max_depth, seed, estimator, pool_paths)
+        self._check(self.lib.amber_cuda_render(self.ctx, C.byref(params)))
+
+    def resolve(self, out: np.ndarray | None = None) -> tuple[np.ndarray, int]:
+        assert self.sensor is not None
+        if out is None:
+            out = np.empty((self.sensor.height, self.sensor.width, 3), dtype=np.float32)
+        done = C.c_uint64()
+        self._check(self.lib.amber_cuda_resolve(self.ctx, out.ctypes.data_as(C.c_void_p), C.byref(done)))
+        return out, done.value
+
+    def film_device(self) -> tuple[int, int, int]:
+        ptr, n, done = C.c_void_p(), C.c_uint64(), C.c_uint64()
+        self._check(self.lib.amber_cuda_film_device(self.ctx, C.byref(ptr), C.byref(n), C.byref(done)))
+        return ptr.value, n.value, done.value
+
+    def film_set_samples(self, samples: int) -> None:
+        self._check(self.lib.amber_cuda_film_set_samples(self.ctx, samples))
+
+    # -- parity entry points ----------------------------------------------------------
+    def cast(self, origins, directions) -> tuple[np.ndarray, np.ndarray]:
+        o = np.ascontiguousarray(origins, dtype=np.float32)
+        d = np.ascontiguousarray(directions, dtype=np.float32)
+        n = o.shape[0]
+        prim = np.empty(n, dtype=np.int32)
+        t = np.empty(n, dtype=np.float32)
+        self._check(self.lib.amber_cuda_cast(self.ctx, o.ctypes.data_as(C.c_void_p), d.ctypes.data_as(C.c_void_p),
+                                             n, prim.ctypes.data_as(C.c_void_p), t.ctypes.data_as(C.c_void_p)))
+        return prim, t
+
+    def cast_device(self, origin4_ptr: int, direction4_ptr: int, n: int, hit4_ptr: int) -> float:
+        ms = C.c_float()
+        self._check(self.lib.amber_cuda_cast_device(self.ctx, origin4_ptr, direction4_ptr, n, hit4_ptr, C.byref(ms)))
+        return ms.value
+
+    def sample_light(self, material: int, normals, dirs_out, xi8):
+        nrm = np.ascontiguousarray(normals, dtype=np.float32)
+        wo = np.ascontiguousarray(dirs_out, dtype=np.float32)
+        xi = np.ascontiguousarray(xi8, dtype=np.float32)
+        n = nrm.shape[0]
+        wi = np.empty((n, 3), dtype=np.float32)
+        w = np.empty((n, 3), dtype=np.float32)
+        draws = np.empty(n, dtype=np.int32)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        self._check(self.lib.amber_cuda_sample_light(self.ctx, material, n, p(nrm), p(wo), p(xi), p(wi), p(w), p(draws)))
+        return wi, w, draws
+
+    def eye_rays(self, px, py, xi5):
+        px_ = np.ascontiguousarray(px, dtype=np.uint32)
+        py_ = np.ascontiguousarray(py, dtype=np.uint32)
+        xi = np.ascontiguousarray(xi5, dtype=np.float32)
+        n = px_.shape[0]
+        o = np.empty((n, 3), dtype=np.float32)
+        d = np.empty((n, 3), dtype=np.float32)
+        w = np.empty(n, dtype=np.float32)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        self._check(self.lib.amber_cuda_eye_rays(self.ctx, n, p(px_), p(py_), p(xi), p(o), p(d), p(w)))
+        return o, d, w
+
+    def stats(self) -> dict:
+        s = capi.Stats()
+        self._check(self.lib.amber_cuda_get_stats(self.ctx, C.byref(s)))
+        return {name: getattr(s, name) for name, _ in capi.Stats._fields_}
+
+    def set_profiling(self, on: bool) -> None:
+        self._check(self.lib.amber_cuda_set_profiling(self.ctx, int(on)))
+
+
+class CudaPathTracing:
+    """rendering::Algorithm<RGB> for ``--algorithm pt`` on the GPU.
+
+    ``render(scene, sensor, context)`` consumes ``context.iterate()`` in batches of
+    ``batch_spp`` samples (so ``--spp``, expiry and the iteration counter keep their
+    reference meaning) and returns the mean image, shape (H, W, 3), float32, row-major
+    ``x + y*W`` like ``Image<RGB>`` (``include/amber/prelude/image.h:117-124``).
+    """
+
+    def __init__(self, estimator: str = "nee", max_depth: int = 0, seed: int = 1, device: int = 0,
+                 batch_spp: int = 64, pool_paths: int = 0):
+        self.estimator = {"reference": capi.ESTIMATOR_REFERENCE, "nee": capi.ESTIMATOR_NEE}[estimator]
+        self.max_depth = max_depth
+        self.seed = seed
+        self.device_index = device
+        self.batch_spp = batch_spp
+        self.pool_paths = pool_paths
+        self.last_stats: dict | None = None
+
+    def render(self, scene: FlatScene, sensor: Sensor, context: Context) -> np.ndarray:
+        if not isinstance(scene, FlatScene):
+            # the reference adapter throws std::invalid_argument for a scene it cannot flatten
+            raise TypeError("CudaPathTracing needs a FlatScene (no CPU fallback)")
+        with Device(self.device_index) as dev:
+            dev.upload_scene(scene)
+            dev.set_sensor(sensor)
+            begin = 0
+            while True:
+                count = 0
+                while count < self.batch_spp and context.iterate():
+                    count += 1
+                if count == 0:
+                    break
+                dev.render(begin, count, seed=self.seed, max_depth=self.max_depth,
+                           estimator=self.estimator, pool_paths=self.pool_paths)
+                begin += count
+            image, _ = dev.resolve()
+            self.last_stats = dev.stats()
+        return image

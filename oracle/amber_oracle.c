@@ -737,3 +737,56 @@ void oracle_render(const oracle_scene* scene, uint32_t w, uint32_t h, float film
     }
   }
 }
+
+/* ---- test hooks -------------------------------------------------------------------- */
+void oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+  philox4x32_10(ctr, key, out);
+}
+
+void oracle_stream(uint64_t seed, uint32_t pixel, uint64_t sample, uint32_t n, float* out) {
+  philox_stream s;
+  uint32_t i;
+  philox_stream_reset(&s, seed, pixel, sample);
+  for (i = 0; i < n; i++) out[i] = philox_stream_next(&s);
+}
+
+/* The fixed ray set of the intersection-parity test: ray i of the first
+ * half is the camera ray of a uniformly random pixel (stream (seed, i, 0)); ray n + i is the
+ * secondary ray leaving its hit point in the BSDF-sampled direction -- it starts ON a surface,
+ * which exercises the t >= kEPS rule, grazing, mirror and refracted directions.  Where the
+ * camera ray misses, the secondary ray repeats it. */
+void oracle_ray_set(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h,
+                    uint64_t seed, uint64_t n, float* origins, float* directions) {
+  uint64_t i;
+  for (i = 0; i < n; i++) {
+    philox_stream stream;
+    sampler s = {&stream, NULL, 0, 0};
+    vec3 o, d, o2, d2;
+    float weight;
+    uint32_t px, py;
+    hit_t hit;
+    int object;
+    philox_stream_reset(&stream, seed, (uint32_t)i, i >> 32);
+    px = (uint32_t)(uniform(&s) * (float)w);
+    py = (uint32_t)(uniform(&s) * (float)h);
+    if (px >= w) px = w - 1;
+    if (py >= h) py = h - 1;
+    generate_eye_ray(sc, w, h, film_w, film_h, px, py, &s, &o, &d, &weight);
+    object = scene_cast(sc, o, d, &hit);
+    o2 = o;
+    d2 = d;
+    if (object >= 0) {
+      const prim* p = &sc->prims[object];
+      const scatter_t scatter =
+          material_sample_light(&sc->materials[p->material], sc->r0[p->material], hit.normal, neg(d), &s);
+      if (scatter.dir.x != 0 || scatter.dir.y != 0 || scatter.dir.z != 0) {
+        o2 = hit.position;
+        d2 = scatter.dir;
+      }
+    }
+    origins[3 * i] = o.x; origins[3 * i + 1] = o.y; origins[3 * i + 2] = o.z;
+    directions[3 * i] = d.x; directions[3 * i + 1] = d.y; directions[3 * i + 2] = d.z;
+    origins[3 * (n + i)] = o2.x; origins[3 * (n + i) + 1] = o2.y; origins[3 * (n + i) + 2] = o2.z;
+    directions[3 * (n + i)] = d2.x; directions[3 * (n + i) + 1] = d2.y; directions[3 * (n + i) + 2] = d2.z;
+  }
+}

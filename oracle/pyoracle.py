@@ -216,3 +216,23 @@ class Oracle:
                                C.c_int(threads), _ptr(rgb), stats)
         return rgb, {"closest_rays": stats[0], "shadow_rays": stats[1], "truncated": stats[2],
                      "paths": stats[3]}
+
+    def ray_set(self, w, h, film_w, film_h, seed, n):
+        """2n rays: n camera rays then n secondary rays (see oracle_ray_set)."""
+        o = np.empty((2 * n, 3), dtype=np.float32)
+        d = np.empty((2 * n, 3), dtype=np.float32)
+        self.lib.oracle_ray_set(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w), C.c_float(film_h),
+                                C.c_uint64(seed), C.c_uint64(n), _ptr(o), _ptr(d))
+        return o, d
+
+    def philox(self, ctr, key):
+        c = (C.c_uint32 * 4)(*ctr)
+        k = (C.c_uint32 * 2)(*key)
+        out = (C.c_uint32 * 4)()
+        self.lib.oracle_philox4x32_10(c, k, out)
+        return list(out)
+
+    def stream(self, seed, pixel, sample, n):
+        out = np.empty(n, dtype=np.float32)
+        self.lib.oracle_stream(C.c_uint64(seed), C.c_uint32(pixel), C.c_uint64(sample), C.c_uint32(n), _ptr(out))
+        return out

@@ -1,0 +1,123 @@
+#!/usr/bin/env python
+"""Generate tests/golden/*.npz from the UNMODIFIED reference (oracle/_ref/libamber_ref.so).
+
+Run in the build container (where /root/reference exists):
+    make -C oracle ref && python scripts/make_golden.py
+The fixtures are what keeps the CPU oracle pinned on machines without /root/reference
+(the GPU box): tests/test_oracle_golden.py replays these inputs through
+oracle/amber_oracle.c and requires bit-identical outputs.  The reference has no tests or
+golden vectors of its own -- every expected value here is produced by
+executing its code.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from amber_b200 import capi, scene  # noqa: E402
+from oracle import pyoracle  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+FILM = (0.036, 0.036)
+
+# (name, kind, rgb, param)
+MATERIALS = [
+    ("lambertian", capi.MAT_LAMBERTIAN, (.5, .4, .3), 0.0),
+    ("phong256", capi.MAT_PHONG, (.95, .95, .95), 256.0),
+    ("phong8", capi.MAT_PHONG, (.9, .8, .7), 8.0),
+    ("specular", capi.MAT_SPECULAR, (.95, .95, .95), 0.0),
+    ("water", capi.MAT_REFRACTION, (1, 1, 1), 1.333),
+    ("glass", capi.MAT_REFRACTION, (1, 1, 1), 1.125),
+    ("light", capi.MAT_DIFFUSE_LIGHT, (7.0, 5.0, 3.0), 0.0),
+    ("eye", capi.MAT_EYE, (1, 1, 1), 0.0),
+]
+
+
+def unit(rng, n):
+    v = rng.normal(size=(n, 3)).astype(np.float32)
+    return (v / np.linalg.norm(v, axis=1, keepdims=True)).astype(np.float32)
+
+
+def main():
+    os.makedirs(GOLDEN, exist_ok=True)
+    flat = scene.cornel_box()
+    ref = pyoracle.Reference(flat)
+    builtin = pyoracle.Reference(builtin_cornel_box=True)
+    oracle = pyoracle.Oracle(flat)
+    rng = np.random.default_rng(20261104)
+
+    # 1. closest hits on the fixed ray-set recipe (camera rays + secondary rays)
+    n = 8192
+    o, d = oracle.ray_set(1024, 1024, *FILM, 20261104, n)
+    prim_bvh, t_bvh = ref.cast(o, d, accel=0)
+    prim_list, t_list = ref.cast(o, d, accel=1)
+    assert (prim_bvh == prim_list).all() and np.array_equal(t_bvh, t_list, equal_nan=True)
+    np.savez_compressed(os.path.join(GOLDEN, "cornell_cast.npz"), origins=o, directions=d,
+                        prim=prim_bvh, t=t_bvh, seed=20261104, n=n)
+
+    # 2. materials: SampleLight with scripted uniforms, BSDF, Radiance
+    out = {}
+    m = 512
+    for name, kind, rgb, param in MATERIALS:
+        material = capi.Material(kind, (capi.C.c_float * 3)(*rgb), param)
+        normal, wo, wi = unit(rng, m), unit(rng, m), unit(rng, m)
+        xi = rng.random((m, 8), dtype=np.float32)
+        dir_in, weight, draws = ref.sample_light(material, normal, wo, xi)
+        bsdf, radiance = ref.bsdf(material, normal, wo, wi)
+        for key, val in dict(normal=normal, wo=wo, wi=wi, xi=xi, dir_in=dir_in, weight=weight,
+                             draws=draws, bsdf=bsdf, radiance=radiance).items():
+            out[f"{name}.{key}"] = val
+        out[f"{name}.desc"] = np.array([kind, *rgb, param], dtype=np.float64)
+    np.savez_compressed(os.path.join(GOLDEN, "materials.npz"), **out)
+
+    # 3. camera rays (thin lens, pixel-bound sensor), two resolutions
+    out = {}
+    for (w, h) in ((64, 64), (1024, 512)):
+        k = 2048
+        px, py = rng.integers(0, w, k).astype(np.uint32), rng.integers(0, h, k).astype(np.uint32)
+        xi = rng.random((k, 5), dtype=np.float32)
+        film = (0.036, 0.036 * h / w)
+        origin, direction, weight = ref.eye_rays(w, h, *film, px, py, xi)
+        origin_b, direction_b, weight_b = builtin.eye_rays(w, h, *film, px, py, xi)
+        assert np.array_equal(origin, origin_b) and np.array_equal(direction, direction_b) and np.array_equal(weight, weight_b)
+        tag = f"{w}x{h}"
+        for key, val in dict(px=px, py=py, xi=xi, origin=origin, direction=direction, weight=weight).items():
+            out[f"{tag}.{key}"] = val
+    np.savez_compressed(os.path.join(GOLDEN, "eye_rays.npz"), **out)
+
+    # 4. whole images: the reference's loop on the shared Philox stream
+    out = {}
+    for (w, spp, seed, depth) in ((32, 64, 7, 0), (48, 32, 11, 4)):
+        image, stats = ref.render_stream(w, w, *FILM, 0, spp, seed, depth)
+        image_b, stats_b = builtin.render_stream(w, w, *FILM, 0, spp, seed, depth)
+        assert np.array_equal(image, image_b) and stats == stats_b
+        tag = f"{w}x{w}x{spp}.seed{seed}.depth{depth}"
+        out[f"{tag}.image"] = image
+        out[f"{tag}.rays"] = np.array([stats["rays"], stats["truncated"]], dtype=np.uint64)
+    np.savez_compressed(os.path.join(GOLDEN, "cornell_stream.npz"), **out)
+
+    # 5. statistics of the reference's own renderer (non-reproducible engines): mean
+    #    luminance over K independent PT runs, and a BDPT image for the NEE comparison
+    k_runs, w, spp = 16, 64, 256
+    means = []
+    for _ in range(k_runs):
+        image, _, _ = builtin.render(w, w, *FILM, spp, 8, algo=0)
+        means.append(float(image.mean()))
+    bdpt, _, seconds = builtin.render(w, w, *FILM, 1024, 8, algo=1)
+    np.savez_compressed(os.path.join(GOLDEN, "cornell_bdpt_64x64.npz"), image=bdpt, spp=1024)
+    with open(os.path.join(GOLDEN, "cornell_luminance.json"), "w") as f:
+        json.dump({"width": w, "height": w, "spp": spp, "runs": k_runs, "pt_means": means,
+                   "pt_mean": float(np.mean(means)), "pt_std_of_run": float(np.std(means, ddof=1)),
+                   "bdpt_mean": float(bdpt.mean()), "bdpt_spp": 1024, "bdpt_seconds": seconds}, f, indent=1)
+    print("pt mean", np.mean(means), "+-", np.std(means, ddof=1) / np.sqrt(k_runs), "bdpt mean", bdpt.mean(),
+          f"({seconds:.1f}s)")
+
+
+if __name__ == "__main__":
+    main()

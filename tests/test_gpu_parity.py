@@ -1,0 +1,297 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU oracle on the same
+seeded inputs, against the golden fixtures of the unmodified reference, and -- at the
+benchmark's full size -- through size-independent properties.
+
+Tolerances (floating point; the north star asks for hit ids >= 99.99 % and hit distance
+within 1e-4 relative): the device uses FMA contraction, MUFU reciprocal / rsqrt and its
+own libm, so results differ from the host's by a few ulp; where a path takes a different
+branch because of that (a rejection-loop retry, a Russian-roulette threshold) a pixel can
+differ, so image checks require >= 99 % of pixels to agree to 2e-3 relative.
+"""
+import numpy as np
+import pytest
+
+from conftest import FILM, diffuse_box, golden, image_agreement, unit_vectors
+
+pytestmark = pytest.mark.gpu
+
+ID_AGREEMENT = 0.9999
+T_RTOL = 1e-4
+
+
+def check_cast(prim, t, want_prim, want_t):
+    agree = prim == want_prim
+    assert agree.mean() >= ID_AGREEMENT, f"hit ids agree on {agree.mean():.6f}"
+    both = agree & (want_prim >= 0)
+    rel = np.abs(t[both] - want_t[both]) / want_t[both]
+    # 1e-4 relative; distances at the kEPS scale (< 1e-4) are allowed 1e-8 absolute on top
+    assert np.all(rel <= T_RTOL + 1e-8 / want_t[both]), f"max rel t error {rel.max():.3e}"
+    assert np.isnan(t[agree & (want_prim < 0)]).all()
+    return float(agree.mean()), float(rel.max()) if rel.size else 0.0
+
+
+@pytest.fixture
+def cornell_device(device, cornell):
+    """The shared context with the Cornell box bound (other tests upload other scenes)."""
+    from amber_b200 import Sensor
+    if device.scene is not cornell:
+        device.upload_scene(cornell)
+    device.set_sensor(Sensor(64, 64))
+    return device
+
+
+def test_cast_matches_reference_golden(cornell_device):
+    g = golden("cornell_cast.npz")
+    prim, t = cornell_device.cast(g["origins"], g["directions"])
+    check_cast(prim, t, g["prim"], g["t"])
+
+
+def test_cast_matches_oracle_on_the_fixed_ray_set(cornell_device, oracle):
+    """The 10 M-ray set of SURVEY.md section 8d: 5 M camera rays + 5 M secondary rays, seed 20261104."""
+    o, d = oracle.ray_set(1024, 1024, *FILM, 20261104, 5_000_000)
+    want_prim, want_t = oracle.cast(o, d, threads=32)
+    prim, t = cornell_device.cast(o, d)
+    agreement, max_rel = check_cast(prim, t, want_prim, want_t)
+    print(f"10M-ray set: id agreement {agreement:.7f}, max rel t error {max_rel:.3e}")
+
+
+def test_cast_edge_cases(cornell_device, oracle):
+    rng = np.random.default_rng(11)
+    # empty input
+    prim, t = cornell_device.cast(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.float32))
+    assert prim.shape == (0,) and t.shape == (0,)
+    # rays that start on surfaces and leave along them / axis-parallel rays / rays from outside
+    o = rng.uniform(-0.99, 0.99, size=(20000, 3)).astype(np.float32)
+    d = unit_vectors(rng, 20000)
+    o[:5000, 1] = -1.0                      # on the floor
+    d[:2500, 1] = np.abs(d[:2500, 1])       # heading up
+    d[5000:7500] = np.eye(3, dtype=np.float32)[rng.integers(0, 3, 2500)] * rng.choice([-1, 1], (2500, 1)).astype(np.float32)
+    o[7500:10000] *= 5.0                    # outside the box
+    d[:10000] /= np.linalg.norm(d[:10000], axis=1, keepdims=True)
+    want_prim, want_t = oracle.cast(o, d)
+    prim, t = cornell_device.cast(o, d)
+    check_cast(prim, t, want_prim, want_t)
+    # a single ray (ragged block) straight at the back wall
+    prim, t = cornell_device.cast(np.array([[0, 0, 0.5]], np.float32), np.array([[0, 0, -1]], np.float32))
+    assert prim[0] in (12, 13) and abs(t[0] - 1.5) < 1e-5
+
+
+def test_camera_rays(cornell_device, oracle):
+    from amber_b200 import Sensor
+    g = golden("eye_rays.npz")
+    for tag, (w, h) in {"64x64": (64, 64), "1024x512": (1024, 512)}.items():
+        cornell_device.set_sensor(Sensor(w, h))
+        o, d, wt = cornell_device.eye_rays(g[f"{tag}.px"], g[f"{tag}.py"], g[f"{tag}.xi"])
+        assert np.allclose(o, g[f"{tag}.origin"], atol=1e-7)
+        assert np.allclose(d, g[f"{tag}.direction"], atol=1e-6)
+        assert np.allclose(wt, g[f"{tag}.weight"], rtol=2e-5)
+    cornell_device.set_sensor(Sensor(64, 64))
+
+
+def test_materials(device, oracle_lib):
+    """SampleLight for every material kind against the reference golden vectors."""
+    from amber_b200 import FlatSceneBuilder, Sensor, capi
+    g = golden("materials.npz")
+    names = sorted({k.split(".")[0] for k in g.files})
+    b = FlatSceneBuilder()
+    b.make_thin_lens(np.eye(4), 0.05, 4.0, 0.05, 6, add_aperture_objects=False)
+    index = {}
+    for name in names:
+        kind, r, gg, bb, param = g[f"{name}.desc"]
+        index[name] = b._material(int(kind), (r, gg, bb), param)
+    b.add_triangle((0, 0, 0), (1, 0, 0), (0, 1, 0), index[names[0]])
+    device.upload_scene(b.build())
+    device.set_sensor(Sensor(8, 8))
+    for name in names:
+        dir_in, weight, draws = device.sample_light(index[name], g[f"{name}.normal"], g[f"{name}.wo"], g[f"{name}.xi"])
+        same = draws == g[f"{name}.draws"]
+        assert same.mean() >= 0.995, (name, same.mean())
+        atol = 1e-4 if name.startswith("phong") else 5e-6
+        assert np.allclose(dir_in[same], g[f"{name}.dir_in"][same], atol=atol), name
+        assert np.allclose(weight[same], g[f"{name}.weight"][same], rtol=2e-4, atol=1e-7), name
+
+
+@pytest.mark.parametrize("estimator", [0, 1])
+def test_image_matches_oracle_on_the_same_stream(cornell_device, oracle, estimator):
+    from amber_b200 import Sensor
+    w, spp, seed, depth = 64, 32, 5, 32
+    cornell_device.set_sensor(Sensor(w, w))
+    cornell_device.render(0, spp, seed=seed, max_depth=depth, estimator=estimator)
+    image, done = cornell_device.resolve()
+    want, stats = oracle.render(w, w, *FILM, 0, spp, seed, depth, estimator=estimator)
+    assert done == spp
+    frac = image_agreement(image, want)
+    assert frac >= 0.99, f"only {frac:.4f} of pixels agree"
+    got = cornell_device.stats()
+    assert got["paths"] == w * w * spp
+    assert abs(got["closest_rays"] - stats["closest_rays"]) <= 2e-3 * stats["closest_rays"]
+    if estimator == 1:
+        assert abs(got["shadow_rays"] - stats["shadow_rays"]) <= 2e-3 * stats["shadow_rays"]
+    else:
+        assert got["shadow_rays"] == 0
+
+
+def test_image_matches_reference_golden(cornell_device):
+    """Whole images rendered by the unmodified reference on the shared Philox stream."""
+    from amber_b200 import Sensor
+    g = golden("cornell_stream.npz")
+    for tag in sorted({k.rsplit(".", 1)[0] for k in g.files}):
+        size, seed, depth = tag.split(".")
+        w, _, spp = (int(x) for x in size.split("x"))
+        cornell_device.set_sensor(Sensor(w, w))
+        cornell_device.render(0, spp, seed=int(seed[4:]), max_depth=int(depth[5:]), estimator=0)
+        image, _ = cornell_device.resolve()
+        assert image_agreement(image, g[f"{tag}.image"]) >= 0.99, tag
+        rays = int(g[f"{tag}.rays"][0])
+        assert abs(cornell_device.stats()["closest_rays"] - rays) <= 2e-3 * rays
+
+
+def test_specular_chain_stress(cornell_device, oracle):
+    """Config 3: mirror + glass + water, depth cap 32 with Russian roulette; the cap is
+    applied identically by the oracle and the truncated fraction is reported."""
+    from amber_b200 import Sensor
+    cornell_device.set_sensor(Sensor(48, 48))
+    for depth in (2, 32):
+        cornell_device.film_clear()
+        cornell_device.render(0, 16, seed=8, max_depth=depth, estimator=1)
+        image, _ = cornell_device.resolve()
+        want, stats = oracle.render(48, 48, *FILM, 0, 16, 8, depth, estimator=1)
+        assert image_agreement(image, want) >= 0.99
+        got = cornell_device.stats()
+        assert abs(got["truncated_paths"] - stats["truncated"]) <= max(8, 0.02 * stats["truncated"])
+        assert got["phong_capped"] == 0
+
+
+def test_accumulation_is_independent_of_batching_and_pool_size(cornell_device):
+    """Sample partition invariance: [0,8) in one call == [0,3)+[3,8) in two == a tiny pool."""
+    from amber_b200 import Sensor
+    cornell_device.set_sensor(Sensor(96, 64))
+    cornell_device.render(0, 8, seed=3, max_depth=16, estimator=1)
+    whole, _ = cornell_device.resolve()
+    cornell_device.film_clear()
+    cornell_device.render(0, 3, seed=3, max_depth=16, estimator=1)
+    cornell_device.render(3, 5, seed=3, max_depth=16, estimator=1)
+    split, done = cornell_device.resolve()
+    assert done == 8
+    cornell_device.film_clear()
+    cornell_device.render(0, 8, seed=3, max_depth=16, estimator=1, pool_paths=1024)
+    small_pool, _ = cornell_device.resolve()
+    for other in (split, small_pool):
+        assert np.allclose(other, whole, rtol=1e-4, atol=1e-7 * whole.mean())
+
+
+def test_algorithm_interface_mirrors_the_reference(cornell, oracle):
+    """Render(scene, sensor, context): one Iterate() = one sample per pixel; expiry ends early."""
+    from amber_b200 import Context, CudaPathTracing, Sensor
+    algo = CudaPathTracing(estimator="reference", max_depth=8, seed=2, batch_spp=4)
+    context = Context(1, 10)
+    image = algo.render(cornell, Sensor(32, 32), context)
+    assert image.shape == (32, 32, 3) and image.dtype == np.float32
+    assert context.iteration_count() == 10 and algo.last_stats["paths"] == 32 * 32 * 10
+    want, _ = oracle.render(32, 32, *FILM, 0, 10, 2, 8, estimator=0)
+    assert image_agreement(image, want) >= 0.99
+    expired = Context(1, 0)
+    expired.expire()
+    assert np.all(algo.render(cornell, Sensor(8, 8), expired) == 0)
+
+
+def test_estimators_agree_in_expectation_on_the_device(device):
+    """NEE vs the reference's estimator, low-variance scene, millions of paths: means agree."""
+    from amber_b200 import Sensor
+    device.upload_scene(diffuse_box())
+    device.set_sensor(Sensor(32, 32))
+    means = {}
+    for estimator, spp in ((0, 4096), (1, 1024)):
+        runs = []
+        for seed in range(4):
+            device.film_clear()
+            device.render(0, spp, seed=50 + seed, estimator=estimator)
+            image, _ = device.resolve()
+            runs.append(image.mean(axis=(0, 1)))
+        means[estimator] = np.array(runs)
+    diff = means[0].mean(0) - means[1].mean(0)
+    sigma = np.sqrt(means[0].var(0, ddof=1) / 4 + means[1].var(0, ddof=1) / 4)
+    assert np.all(np.abs(diff) < 4 * sigma + 2e-3 * means[0].mean(0)), (diff, sigma)
+
+
+def test_bvh_path_matches_oracle(device, oracle_lib):
+    """Scenes above the constant-memory limit go through the 4-wide BVH: closest hits and
+    images against the brute-force oracle on a displaced icosphere in the Cornell room."""
+    from amber_b200 import Sensor, cornel_mesh
+    scene = cornel_mesh(subdivisions=4)  # 5120 + 18 triangles
+    oracle = oracle_lib.Oracle(scene)
+    device.upload_scene(scene)
+    device.set_sensor(Sensor(32, 32))
+    stats = device.stats()
+    assert stats["accel"] == 1 and stats["bvh_nodes"] > 100
+    o, d = oracle.ray_set(256, 256, *FILM, 77, 60000)
+    want_prim, want_t = oracle.cast(o, d, threads=32)
+    prim, t = device.cast(o, d)
+    check_cast(prim, t, want_prim, want_t)
+    for estimator in (0, 1):
+        device.film_clear()
+        device.render(0, 8, seed=6, max_depth=16, estimator=estimator)
+        image, _ = device.resolve()
+        want, _ = oracle.render(32, 32, *FILM, 0, 8, 6, 16, estimator=estimator, threads=32)
+        assert image_agreement(image, want) >= 0.985
+
+
+def test_full_size_properties(cornell_device):
+    """Config 2 geometry (Cornell 1024x1024) at a few spp: properties that do not need an
+    oracle run of that size."""
+    from amber_b200 import Sensor
+    cornell_device.set_sensor(Sensor(1024, 1024))
+    cornell_device.render(0, 4, seed=1, max_depth=32, estimator=1)
+    a, _ = cornell_device.resolve()
+    stats = cornell_device.stats()
+    assert stats["paths"] == 4 * 1024 * 1024
+    # the reference measures 2.094 closest-hit rays per path on this scene
+    assert 1.9 < stats["closest_rays"] / stats["paths"] < 2.3
+    assert np.isfinite(a).all() and (a >= 0).all()
+    # idempotence: the same samples again give the same film (up to float summation order)
+    cornell_device.film_clear()
+    cornell_device.render(0, 4, seed=1, max_depth=32, estimator=1)
+    b, _ = cornell_device.resolve()
+    assert np.allclose(a, b, rtol=1e-4, atol=1e-7 * a.mean())
+    # linearity of the film: 2 + 2 samples == 4 samples
+    cornell_device.film_clear()
+    cornell_device.render(0, 2, seed=1, max_depth=32, estimator=1)
+    cornell_device.render(2, 2, seed=1, max_depth=32, estimator=1)
+    c, _ = cornell_device.resolve()
+    assert np.allclose(a, c, rtol=1e-4, atol=1e-7 * a.mean())
+    # pixel values scale with 1/(W*H) (lens_thin.cc:139-148): 4x dimmer than 512x512
+    cornell_device.set_sensor(Sensor(512, 512))
+    cornell_device.render(0, 16, seed=1, max_depth=32, estimator=1)
+    small, _ = cornell_device.resolve()
+    ratio = np.median(small[300:500, 100:400]) / np.median(a[600:1000, 200:800])
+    assert 3.5 < ratio < 4.5, ratio
+    cornell_device.set_sensor(Sensor(64, 64))
+
+
+def test_two_contexts_share_a_device(cornell, oracle):
+    """Constant memory is per device: contexts must re-bind their scene."""
+    from amber_b200 import Sensor
+    from amber_b200.render import Device
+    with Device(0) as a, Device(0) as b:
+        a.upload_scene(cornell)
+        a.set_sensor(Sensor(32, 32))
+        b.upload_scene(diffuse_box())
+        b.set_sensor(Sensor(16, 16))
+        b.render(0, 2, seed=1)
+        a.render(0, 4, seed=9, max_depth=8, estimator=0)
+        image, _ = a.resolve()
+        want, _ = oracle.render(32, 32, *FILM, 0, 4, 9, 8, estimator=0)
+        assert image_agreement(image, want) >= 0.99
+
+
+def test_errors_are_reported_not_swallowed(device):
+    from amber_b200 import FlatSceneBuilder, capi
+    from amber_b200.render import Device
+    with Device(0) as fresh:
+        with pytest.raises(capi.AmberCudaError, match="upload_scene"):
+            fresh.render(0, 1)
+    b = FlatSceneBuilder()
+    b.make_thin_lens(np.eye(4), 0.05, 4.0, 0.05, 6)
+    b.add_triangle((0, 0, 0), (1, 0, 0), (0, 1, 0), 7)  # material out of range
+    with pytest.raises(capi.AmberCudaError, match="material"):
+        device.upload_scene(b.build())

@@ -1,0 +1,97 @@
+"""The CPU oracle (oracle/amber_oracle.c) against the golden fixtures generated from the
+UNMODIFIED reference by scripts/make_golden.py.  Bit-exact: the oracle restates the
+reference float for float."""
+import json
+import os
+
+import numpy as np
+
+from conftest import FILM, GOLDEN, golden
+
+
+def test_philox_known_answers(oracle):
+    # Random123 kat_vectors, philox4x32 10 rounds
+    assert oracle.philox([0, 0, 0, 0], [0, 0]) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert oracle.philox([0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert oracle.philox([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+    u = oracle.stream(5, 17, 3, 4096)
+    assert u.min() >= 0.0 and u.max() < 1.0 and abs(u.mean() - 0.5) < 0.02
+
+
+def test_closest_hits_match_reference(oracle):
+    g = golden("cornell_cast.npz")
+    o, d = oracle.ray_set(1024, 1024, *FILM, int(g["seed"]), int(g["n"]))
+    assert np.array_equal(o, g["origins"]) and np.array_equal(d, g["directions"])
+    prim, t = oracle.cast(g["origins"], g["directions"])
+    assert np.array_equal(prim, g["prim"])
+    assert np.array_equal(t, g["t"], equal_nan=True)
+    # the set exercises every primitive class
+    hit = g["prim"][g["prim"] >= 0]
+    assert set(np.unique(hit)) >= set(range(8, 25))
+
+
+def test_materials_match_reference(oracle):
+    from amber_b200 import capi
+    g = golden("materials.npz")
+    names = sorted({k.split(".")[0] for k in g.files})
+    assert len(names) == 8
+    for name in names:
+        kind, r, gg, b, param = g[f"{name}.desc"]
+        m = capi.Material(int(kind), (capi.C.c_float * 3)(r, gg, b), param)
+        dir_in, weight, draws = oracle.sample_light(m, g[f"{name}.normal"], g[f"{name}.wo"], g[f"{name}.xi"])
+        assert np.array_equal(dir_in, g[f"{name}.dir_in"]), name
+        assert np.array_equal(weight, g[f"{name}.weight"]), name
+        assert np.array_equal(draws, g[f"{name}.draws"]), name
+        bsdf, radiance = oracle.bsdf(m, g[f"{name}.normal"], g[f"{name}.wo"], g[f"{name}.wi"])
+        assert np.array_equal(radiance, g[f"{name}.radiance"]), name
+        if int(kind) in (capi.MAT_LAMBERTIAN, capi.MAT_PHONG, capi.MAT_DIFFUSE_LIGHT):
+            assert np.array_equal(bsdf, g[f"{name}.bsdf"]), name
+
+
+def test_camera_rays_match_reference(oracle):
+    g = golden("eye_rays.npz")
+    for tag, (w, h) in {"64x64": (64, 64), "1024x512": (1024, 512)}.items():
+        o, d, wt = oracle.eye_rays(w, h, 0.036, 0.036 * h / w, g[f"{tag}.px"], g[f"{tag}.py"], g[f"{tag}.xi"])
+        assert np.array_equal(o, g[f"{tag}.origin"])
+        assert np.array_equal(d, g[f"{tag}.direction"])
+        assert np.array_equal(wt, g[f"{tag}.weight"])
+    # pixel values scale with 1/(W*H): lens_thin.cc:139-148
+    assert g["1024x512.weight"].mean() < g["64x64.weight"].mean() / 50
+
+
+def test_rendered_images_match_reference(oracle):
+    g = golden("cornell_stream.npz")
+    tags = sorted({k.rsplit(".", 1)[0] for k in g.files})
+    assert len(tags) == 2
+    for tag in tags:
+        size, seed, depth = tag.split(".")
+        w, _, spp = (int(x) for x in size.split("x"))
+        image, stats = oracle.render(w, w, *FILM, 0, spp, int(seed[4:]), int(depth[5:]), estimator=0)
+        assert np.array_equal(image, g[f"{tag}.image"]), tag
+        assert stats["closest_rays"] == int(g[f"{tag}.rays"][0])
+        assert stats["truncated"] == int(g[f"{tag}.rays"][1])
+
+
+def test_estimators_agree_in_expectation(oracle_lib):
+    """NEE is not in the reference's PT; it must have the same expectation.  Low-variance
+    scene (large light, diffuse + Phong): the two oracle estimators agree within 4 sigma."""
+    from conftest import diffuse_box
+    box = oracle_lib.Oracle(diffuse_box())
+    w, spp = 16, 512
+    ref_means, nee_means = [], []
+    for seed in range(6):
+        a, _ = box.render(w, w, *FILM, 0, spp, 100 + seed, 0, estimator=0)
+        b, _ = box.render(w, w, *FILM, 0, spp // 8, 200 + seed, 0, estimator=1)
+        ref_means.append(a.mean(axis=(0, 1)))
+        nee_means.append(b.mean(axis=(0, 1)))
+    ref_means, nee_means = np.array(ref_means), np.array(nee_means)
+    diff = ref_means.mean(0) - nee_means.mean(0)
+    sigma = np.sqrt(ref_means.var(0, ddof=1) / 6 + nee_means.var(0, ddof=1) / 6)
+    assert np.all(np.abs(diff) < 4 * sigma + 1e-3 * ref_means.mean(0)), (diff, sigma)
+    assert np.all(ref_means.mean(0) > 0)
+
+
+def test_reference_luminance_statistics_are_recorded():
+    stats = json.load(open(os.path.join(GOLDEN, "cornell_luminance.json")))
+    assert stats["runs"] == 16 and len(stats["pt_means"]) == 16

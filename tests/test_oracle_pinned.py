@@ -1,0 +1,74 @@
+"""The CPU oracle against the compiled UNMODIFIED reference (oracle/_ref/libamber_ref.so),
+on fresh random inputs.  Skipped where the reference was not built; the committed golden
+fixtures (test_oracle_golden.py) cover that case."""
+import numpy as np
+
+from conftest import FILM, unit_vectors
+
+
+def test_flat_cornell_is_the_builtin_cornel_box(reference, oracle_lib):
+    builtin = oracle_lib.Reference(builtin_cornel_box=True)
+    a, sa = reference.render_stream(32, 32, *FILM, 0, 32, 5)
+    b, sb = builtin.render_stream(32, 32, *FILM, 0, 32, 5)
+    assert np.array_equal(a, b) and sa == sb
+
+
+def test_cast_bit_exact(reference, oracle):
+    o, d = oracle.ray_set(512, 512, *FILM, 99, 50000)
+    for accel in (0, 1):  # reference BVH and reference List
+        prim, t = reference.cast(o, d, accel=accel)
+        oprim, ot = oracle.cast(o, d)
+        assert np.array_equal(prim, oprim)
+        assert np.array_equal(t, ot, equal_nan=True)
+
+
+def test_random_rays_inside_the_box(reference, oracle):
+    rng = np.random.default_rng(3)
+    o = rng.uniform(-0.99, 0.99, size=(50000, 3)).astype(np.float32)
+    d = unit_vectors(rng, 50000)
+    prim, t = reference.cast(o, d)
+    oprim, ot = oracle.cast(o, d)
+    assert np.array_equal(prim, oprim) and np.array_equal(t, ot, equal_nan=True)
+
+
+def test_camera_rays_bit_exact(reference, oracle):
+    rng = np.random.default_rng(4)
+    for (w, h) in ((37, 91), (1024, 1024)):
+        n = 4000
+        px, py = rng.integers(0, w, n), rng.integers(0, h, n)
+        xi = rng.random((n, 5), dtype=np.float32)
+        film = (0.036, 0.036 * h / w)
+        a = reference.eye_rays(w, h, *film, px, py, xi)
+        b = oracle.eye_rays(w, h, *film, px, py, xi)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+
+
+def test_materials_bit_exact(reference, oracle):
+    from amber_b200 import capi
+    rng = np.random.default_rng(5)
+    n = 5000
+    for kind, rgb, param in [(0, (.5, .4, .3), 0), (1, (.95, .9, .8), 256), (1, (.9, .9, .9), 2), (2, (.9, .9, .9), 0),
+                             (3, (1, 1, 1), 1.333), (3, (1, 1, 1), 2.4), (4, (5, 5, 5), 0), (5, (1, 1, 1), 0)]:
+        m = capi.Material(kind, (capi.C.c_float * 3)(*rgb), param)
+        nrm, wo, wi = unit_vectors(rng, n), unit_vectors(rng, n), unit_vectors(rng, n)
+        xi = rng.random((n, 8), dtype=np.float32)
+        a = reference.sample_light(m, nrm, wo, xi)
+        b = oracle.sample_light(m, nrm, wo, xi)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y), (kind, param)
+        fa, la = reference.bsdf(m, nrm, wo, wi)
+        fb, lb = oracle.bsdf(m, nrm, wo, wi)
+        assert np.array_equal(la, lb)
+        if kind in (0, 1, 4):
+            assert np.array_equal(fa, fb)
+
+
+def test_images_bit_exact_including_depth_cap(reference, oracle):
+    for (w, spp, seed, depth) in ((40, 48, 21, 0), (24, 64, 22, 3)):
+        a, sa = reference.render_stream(w, w, *FILM, 8, spp, seed, depth)
+        b, sb = oracle.render(w, w, *FILM, 8, spp, seed, depth, estimator=0)
+        assert np.array_equal(a, b)
+        assert sa["rays"] == sb["closest_rays"] and sa["truncated"] == sb["truncated"]
+        if depth:
+            assert sb["truncated"] > 0
