@@ -188,6 +188,7 @@ int make_lens(amber_cuda_ctx* ctx, const amber_cuda_lens& in, LensDev& lens) {
   std::memcpy(lens.local, inv, sizeof inv);
   lens.focus_distance = in.focus_distance;
   lens.sensor_distance = 1 / (1 / in.focal_length - 1 / in.focus_distance);
+  lens.focus_over_sensor = -lens.focus_distance / lens.sensor_distance;
   lens.n_blades = in.n_blades;
   const float pi = kPiF;
   const float nb = static_cast<float>(in.n_blades);
@@ -406,8 +407,10 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
     const float power = area * ir + area * ig + area * ib;
     if (power > 0) host_lights.push_back({k, power, ir + ig + ib});
   }
-  std::stable_sort(host_lights.begin(), host_lights.end(),
-                   [](const HostLight& a, const HostLight& b) { return a.power < b.power; });
+  // ascending power; equal powers in creation order (the BVH permutes `tri_ids`)
+  std::stable_sort(host_lights.begin(), host_lights.end(), [&](const HostLight& a, const HostLight& b) {
+    return a.power < b.power || (a.power == b.power && tri_ids[a.tri] < tri_ids[b.tri]);
+  });
   std::vector<LightDev> lights(host_lights.size());
   float total_power = 0;
   for (size_t i = 0; i < host_lights.size(); i++) total_power += host_lights[i].power;

@@ -43,22 +43,25 @@ __device__ __forceinline__ bool intersect_triangle(const float4 n_v0x, const flo
 // Sphere test, op for op src/amber/scene/primitive_sphere.cc:75-107 with
 // SolveQuadratic (include/amber/prelude/algebra.h:31-52): a = 1, b = -2 (c-o).d,
 // c = |c-o|^2 - r^2; cancellation-safe roots; the nearer root if > kEPS, else the
-// farther one if > kEPS.
+// farther one if > kEPS.  A ray leaving a sphere re-tests that sphere with c equal to
+// pure rounding noise, and whether the root clears kEPS depends on that noise: the
+// arithmetic here is therefore the reference's, operation by operation, with no FMA
+// contraction and IEEE sqrt / division, so t is bit-identical to the host's.
 __device__ __forceinline__ bool intersect_sphere(const float4 sphere, const Ray& ray, float t_best,
                                                  float& t_out) {
   const float3 oc = v3(sphere.x - ray.o.x, sphere.y - ray.o.y, sphere.z - ray.o.z);
-  const float b = -2.0f * dot(oc, ray.d);
-  const float c = dot(oc, oc) - sphere.w * sphere.w;
-  const float disc = b * b - 4.0f * c;
+  const float b = -2.0f * dot_exact(oc, ray.d);
+  const float c = __fsub_rn(dot_exact(oc, oc), __fmul_rn(sphere.w, sphere.w));
+  const float disc = __fsub_rn(__fmul_rn(b, b), 4.0f * c);
   if (!(disc >= 0.0f)) return false;
-  const float sqrt_d = sqrtf(disc);
+  const float sqrt_d = __fsqrt_rn(disc);
   float alpha = -b - sqrt_d;
   float beta = -b + sqrt_d;
   if (fabsf(alpha) < fabsf(beta)) {
-    alpha = __fdividef(c, beta) * 2.0f;
+    alpha = __fdiv_rn(c, beta) * 2.0f;
     beta = beta * 0.5f;
   } else {
-    beta = __fdividef(c, alpha) * 2.0f;
+    beta = __fdiv_rn(c, alpha) * 2.0f;
     alpha = alpha * 0.5f;
   }
   const float t = alpha > kEpsF ? alpha : beta;

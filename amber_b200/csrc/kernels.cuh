@@ -107,45 +107,47 @@ __device__ __forceinline__ uint32_t queue_alloc(bool want, unsigned int* counter
 template <class Rng>
 __device__ __forceinline__ void generate_eye_ray(uint32_t px, uint32_t py, Rng& rng, float3& origin,
                                                  float3& direction, float& weight) {
+  // Origin and direction are computed with the host's operations one by one (no FMA
+  // contraction, IEEE sqrt / division): the camera sits 3-5 units from the scene, where
+  // one ulp of the direction moves the first hit by more than kEPS, so only bit-identical
+  // camera rays give the reference's first-hit behaviour on curved surfaces.
   const LensDev& lens = c_camera.lens;
   const SensorDev& sensor = c_camera.sensor;
   const float nb = static_cast<float>(lens.n_blades);
-  int blade = static_cast<int>(floorf(rng.next() * nb));
+  int blade = static_cast<int>(floorf(__fmul_rn(rng.next(), nb)));
   blade = min(lens.n_blades - 1, blade);
   const float* b = lens.blades[blade];
   // Triangle::SampleSurfacePoint, src/amber/scene/primitive_triangle.cc:136-150
   float u = rng.next();
   float v = rng.next();
-  if (u + v >= 1.0f) {
+  if (__fadd_rn(u, v) >= 1.0f) {
     u = 1.0f - u;
     v = 1.0f - v;
   }
-  const float w0 = 1.0f - u - v;
-  origin = v3(w0 * b[0] + u * b[3] + v * b[6], w0 * b[1] + u * b[4] + v * b[7],
-              w0 * b[2] + u * b[5] + v * b[8]);
+  const float w0 = __fsub_rn(__fsub_rn(1.0f, u), v);
+  origin = v3(__fadd_rn(__fadd_rn(__fmul_rn(w0, b[0]), __fmul_rn(u, b[3])), __fmul_rn(v, b[6])),
+              __fadd_rn(__fadd_rn(__fmul_rn(w0, b[1]), __fmul_rn(u, b[4])), __fmul_rn(v, b[7])),
+              __fadd_rn(__fadd_rn(__fmul_rn(w0, b[2]), __fmul_rn(u, b[5])), __fmul_rn(v, b[8])));
   const float3 rel = v3(origin.x - lens.origin[0], origin.y - lens.origin[1], origin.z - lens.origin[2]);
-  const float* L = lens.local;
-  const float3 aperture = v3(L[0] * rel.x + L[1] * rel.y + L[2] * rel.z,
-                             L[3] * rel.x + L[4] * rel.y + L[5] * rel.z,
-                             L[6] * rel.x + L[7] * rel.y + L[8] * rel.z);
+  const float3 aperture = mat3_apply_exact(lens.local, rel);
   // The reference builds Vector2((x + xi)/W, (y + xi)/H) (sensor.cc:114-117); argument
   // evaluation order is unspecified and the g++ build used as the oracle draws Y first.
-  const float sv = (static_cast<float>(py) + rng.next()) / static_cast<float>(sensor.height);
-  const float su = (static_cast<float>(px) + rng.next()) / static_cast<float>(sensor.width);
-  const float3 sensor_point =
-      v3((su - 0.5f) * sensor.film_width, (sv - 0.5f) * sensor.film_height, lens.sensor_distance);
-  const float k = -lens.focus_distance / lens.sensor_distance;
-  const float3 dir_local = normalize(v3(k * sensor_point.x - aperture.x, k * sensor_point.y - aperture.y,
-                                        k * sensor_point.z - aperture.z));
+  const float sv = __fdiv_rn(__fadd_rn(static_cast<float>(py), rng.next()), static_cast<float>(sensor.height));
+  const float su = __fdiv_rn(__fadd_rn(static_cast<float>(px), rng.next()), static_cast<float>(sensor.width));
+  const float3 sensor_point = v3(__fmul_rn(su - 0.5f, sensor.film_width), __fmul_rn(sv - 0.5f, sensor.film_height),
+                                 lens.sensor_distance);
+  const float k = lens.focus_over_sensor;  // -focus_distance / sensor_distance
+  const float3 dir_local = normalize_exact(v3(__fsub_rn(__fmul_rn(k, sensor_point.x), aperture.x),
+                                              __fsub_rn(__fmul_rn(k, sensor_point.y), aperture.y),
+                                              __fsub_rn(__fmul_rn(k, sensor_point.z), aperture.z)));
+  direction = normalize_exact(mat3_apply_exact(lens.global, dir_local));
+  // weight = factor / PDFArea / PDFDirection (lens_thin.cc:96-105,132-148); the host
+  // evaluates the pow() calls in double, float is within 1e-6 relative of it
   const float3 to_sensor = normalize(sensor_point - aperture);
   const float ratio = to_sensor.z / dir_local.z;
   const float r2 = ratio * ratio;
   const float factor = r2 * r2;
-  const float* G = lens.global;
-  direction = normalize(v3(G[0] * dir_local.x + G[1] * dir_local.y + G[2] * dir_local.z,
-                           G[3] * dir_local.x + G[4] * dir_local.y + G[5] * dir_local.z,
-                           G[6] * dir_local.x + G[7] * dir_local.y + G[8] * dir_local.z));
-  // PDFDirection, lens_thin.cc:138-148: direction re-expressed in lens space
+  const float* L = lens.local;
   const float dz = L[6] * direction.x + L[7] * direction.y + L[8] * direction.z;
   const float dz2 = dz * dz;
   const float pdf_direction =
@@ -238,14 +240,25 @@ __device__ __forceinline__ void surface_point(const SceneView& scene, const Ray&
   if (hit.prim < scene.n_tris) {
     const float4* tri = reinterpret_cast<const float4*>(scene.tri_shade + hit.prim);
     const float4 a = __ldg(tri), b = __ldg(tri + 1), c = __ldg(tri + 2);
-    position = madd_exact(madd_exact(v3(a), hit.u, v3(b)), hit.v, v3(c));
+    // The traversal found WHICH triangle; the barycentrics that place the hit point are
+    // recomputed here once per hit with the reference's own Moeller-Trumbore sequence
+    // (primitive_triangle.cc:100-127), separately rounded and with IEEE division, so the
+    // vertex position -- the origin of the next ray -- is the host's bit for bit.
+    const float3 v0 = v3(a), E1 = v3(b), E2 = v3(c);
+    const float3 P = cross_exact(ray.d, E2);
+    const float det = dot_exact(P, E1);
+    const float3 T = v3(ray.o.x - v0.x, ray.o.y - v0.y, ray.o.z - v0.z);
+    const float u = __fdiv_rn(dot_exact(P, T), det);
+    const float3 Q = cross_exact(T, E1);
+    const float v = __fdiv_rn(dot_exact(Q, ray.d), det);
+    position = add_exact(add_exact(v0, scale_exact(u, E1)), scale_exact(v, E2));
     normal = v3(a.w, b.w, c.w);
     material = __ldg(scene.tri_material + hit.prim);
   } else {
     const int s = hit.prim - scene.n_tris;
     const float4 sphere = __ldg(scene.spheres + s);
     position = madd_exact(ray.o, hit.t, ray.d);
-    normal = normalize(position - v3(sphere));
+    normal = normalize_exact(v3(position.x - sphere.x, position.y - sphere.y, position.z - sphere.z));
     material = __ldg(scene.sphere_material + s);
   }
 }

@@ -19,18 +19,21 @@ struct Scatter {
 // PerfectReflection, include/amber/prelude/geometry.h:38-47: 2 (d.n) n - d
 __device__ __forceinline__ float3 perfect_reflection(float3 incident, float3 normal, float signed_cos) {
   const float k = 2.0f * signed_cos;
-  return v3(k * normal.x - incident.x, k * normal.y - incident.y, k * normal.z - incident.z);
+  return v3(__fsub_rn(__fmul_rn(k, normal.x), incident.x), __fsub_rn(__fmul_rn(k, normal.y), incident.y),
+            __fsub_rn(__fmul_rn(k, normal.z), incident.z));
 }
 
-// dir = u sin(theta) cos(phi) + v sin(theta) sin(phi) + w cos(theta)
-// (include/amber/prelude/sampling.h:248-252)
+// dir = u sin(theta) cos(phi) + v sin(theta) sin(phi) + w cos(theta), evaluated in the
+// host's order ((u*sin)*cos + (v*sin)*sin) + w*cos without contraction
+// (include/amber/prelude/sampling.h:248-252); only sincosf itself can differ from the
+// host's libm, by an ulp.
 __device__ __forceinline__ float3 local_to_world(float3 u, float3 v, float3 w, float sin_theta,
                                                  float cos_theta, float phi) {
   float s, c;
   sincosf(phi, &s, &c);
-  const float a = sin_theta * c, b = sin_theta * s;
-  return v3(u.x * a + v.x * b + w.x * cos_theta, u.y * a + v.y * b + w.y * cos_theta,
-            u.z * a + v.z * b + w.z * cos_theta);
+  const float3 a = scale_exact(c, scale_exact(sin_theta, u));
+  const float3 b = scale_exact(s, scale_exact(sin_theta, v));
+  return add_exact(add_exact(a, b), scale_exact(cos_theta, w));
 }
 
 // HemispherePSA, sampling.h:234-265: cos = sqrt(r0), sin = sqrt(1-r0), phi = 2 pi r1.
@@ -40,7 +43,7 @@ __device__ __forceinline__ float3 hemisphere_psa(float3 w, Rng& rng) {
   orthonormal_basis(w, u, v);
   const float r0 = rng.next();
   const float r1 = rng.next();
-  return local_to_world(u, v, w, sqrtf(1.0f - r0), sqrtf(r0), 2.0f * kPiF * r1);
+  return local_to_world(u, v, w, __fsqrt_rn(1.0f - r0), __fsqrt_rn(r0), __fmul_rn(2.0f * kPiF, r1));
 }
 
 // CosinePower, sampling.h:267-300: cos = r0^(1/(e+1)).
@@ -50,16 +53,17 @@ __device__ __forceinline__ float3 cosine_power(float3 w, float exponent, Rng& rn
   orthonormal_basis(w, u, v);
   const float r0 = rng.next();
   const float r1 = rng.next();
-  const float cos_theta = powf(r0, 1.0f / (exponent + 1.0f));
-  const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
-  return local_to_world(u, v, w, sin_theta, cos_theta, 2.0f * kPiF * r1);
+  const float cos_theta = powf(r0, __fdiv_rn(1.0f, exponent + 1.0f));
+  const float sin_theta = __fsqrt_rn(__fsub_rn(1.0f, __fmul_rn(cos_theta, cos_theta)));
+  return local_to_world(u, v, w, sin_theta, cos_theta, __fmul_rn(2.0f * kPiF, r1));
 }
 
-// Schlick, src/amber/scene/material_refraction.cc:271-275
+// Schlick, src/amber/scene/material_refraction.cc:271-275.  The host evaluates
+// r0 + (1 - r0) * pow(1 - cos, 5) in double (std::pow(float, int)) and rounds once.
 __device__ __forceinline__ float schlick(float r0, float cos_theta) {
-  const float x = 1.0f - cos_theta;
-  const float x2 = x * x;
-  return r0 + (1.0f - r0) * (x2 * x2 * x);
+  const double x = static_cast<double>(1.0f - cos_theta);
+  const double x2 = x * x;
+  return static_cast<float>(static_cast<double>(r0) + static_cast<double>(1.0f - r0) * (x2 * x2 * x));
 }
 
 // Material::SampleLight for radiance transport.  `wo` = direction_out = -ray.d.
@@ -68,7 +72,7 @@ __device__ __forceinline__ Scatter sample_light(const MaterialDev& m, float3 n, 
   Scatter s;
   s.capped = false;
   const float3 rho = v3(m.r, m.g, m.b);
-  const float cos_o = dot(wo, n);
+  const float cos_o = dot_exact(wo, n);
   switch (m.kind) {
     case 0: {  // Lambertian: src/amber/scene/material_lambertian.cc:61-70, weight kd
       const float3 w = cos_o > 0.0f ? n : -n;
@@ -98,8 +102,9 @@ __device__ __forceinline__ Scatter sample_light(const MaterialDev& m, float3 n, 
       break;
     }
     case 3: {  // Refraction: src/amber/scene/material_refraction.cc:177-220
-      const float ior = cos_o > 0.0f ? 1.0f / m.param : m.param;
-      const float cos2_beta = 1.0f - (1.0f - cos_o * cos_o) * (ior * ior);
+      const float ior = cos_o > 0.0f ? __fdiv_rn(1.0f, m.param) : m.param;
+      const float ior2 = __fmul_rn(ior, ior);
+      const float cos2_beta = __fsub_rn(1.0f, __fmul_rn(__fsub_rn(1.0f, __fmul_rn(cos_o, cos_o)), ior2));
       const float3 dir_r = perfect_reflection(wo, n, cos_o);
       if (cos2_beta < 0.0f) {  // total internal reflection
         s.dir = dir_r;
@@ -107,20 +112,20 @@ __device__ __forceinline__ Scatter sample_light(const MaterialDev& m, float3 n, 
         break;
       }
       const float cos_alpha = fabsf(cos_o);
-      const float cos_beta = sqrtf(cos2_beta);
-      const float k = (cos_o < 0.0f ? 1.0f : -1.0f) * cos_beta + ior * cos_o;
-      const float3 dir_t = v3(-ior * wo.x + k * n.x, -ior * wo.y + k * n.y, -ior * wo.z + k * n.z);
+      const float cos_beta = __fsqrt_rn(cos2_beta);
+      const float k = __fadd_rn(cos_o < 0.0f ? cos_beta : -cos_beta, __fmul_rn(ior, cos_o));
+      const float3 dir_t = add_exact(scale_exact(-ior, wo), scale_exact(k, n));
       const float rho_r = schlick(m.r0, cos_alpha);
-      const float rho_t = (1.0f - rho_r) * (ior * ior);
+      const float rho_t = __fmul_rn(1.0f - rho_r, ior2);
       const float total = rho_r + rho_t;
-      const float p_r = (rho_r / total + 0.5f) / 2.0f;
-      const float p_t = (rho_t / total + 0.5f) / 2.0f;
+      const float p_r = __fdiv_rn(__fdiv_rn(rho_r, total) + 0.5f, 2.0f);
+      const float p_t = __fdiv_rn(__fdiv_rn(rho_t, total) + 0.5f, 2.0f);
       if (rng.next() < p_r) {
         s.dir = dir_r;
-        s.weight = (rho_r / p_r) * rho;
+        s.weight = __fdiv_rn(rho_r, p_r) * rho;
       } else {
         s.dir = dir_t;
-        s.weight = (rho_t / p_t) * rho;
+        s.weight = __fdiv_rn(rho_t, p_t) * rho;
       }
       break;
     }

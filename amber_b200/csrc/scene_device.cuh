@@ -71,6 +71,7 @@ struct LensDev {
   float global[9];  // row-major lens-local -> world (Matrix3 part of the transform)
   float local[9];   // inverse
   float focus_distance, sensor_distance, p_area;
+  float focus_over_sensor;  // -focus_distance / sensor_distance, lens_thin.cc:92
   int32_t n_blades;
   float blades[kMaxBlades][12];  // v0 v1 v2 normal
 };

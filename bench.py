@@ -118,8 +118,8 @@ def cpu_baseline(budget_s: float = 12.0) -> dict:
     threads = host_threads()
     if pyoracle.reference_available():
         ref = pyoracle.Reference(cornel_box())
-        casts, seconds = reference_step(ref, 1, threads)          # calibrate on one frame
-        spp = int(max(1, min(64, budget_s / max(seconds, 1e-3))))
+        casts, seconds = reference_step(ref, 4, threads)          # calibrate on four frames
+        spp = int(max(4, min(256, 4 * budget_s / max(seconds, 1e-3))))
         casts, seconds = reference_step(ref, spp, threads)
         kind = "reference"
     else:  # the C port of the same algorithm
@@ -151,9 +151,9 @@ def run_reference(args) -> None:
     else:
         kind, ref = "reference", pyoracle.Reference(cornel_box())
     if ref is not None:
-        _, calib = reference_step(ref, 1, threads)
+        _, calib = reference_step(ref, 4, threads)
         budget = 150.0 / max(1, args.steps + args.warmup)          # whole run within a few minutes
-        spp = int(max(1, min(64, budget / max(calib, 1e-3))))
+        spp = int(max(4, min(256, 4 * budget / max(calib, 1e-3))))
         for _ in range(args.warmup):
             reference_step(ref, spp, threads)
         rays = seconds = 0.0

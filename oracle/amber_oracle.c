@@ -790,3 +790,48 @@ void oracle_ray_set(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w
     directions[3 * (n + i)] = d2.x; directions[3 * (n + i) + 1] = d2.y; directions[3 * (n + i) + 2] = d2.z;
   }
 }
+
+/* Debug: the vertices of one path, REFERENCE estimator.  out[k] = {prim, t, x, y, z, draws
+ * consumed after the vertex, throughput.r, p_rr}; returns the number of vertices. */
+int oracle_trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h,
+                      uint32_t px, uint32_t py, uint64_t sample, uint64_t seed, uint32_t max_depth,
+                      int estimator, float* out, int max_vertices) {
+  philox_stream stream;
+  sampler s = {&stream, NULL, 0, 0};
+  vec3 origin, direction, weight3;
+  float weight;
+  int n = 0;
+  uint32_t depth;
+  philox_stream_reset(&stream, seed, px + py * w, sample);
+  generate_eye_ray(sc, w, h, film_w, film_h, px, py, &s, &origin, &direction, &weight);
+  weight3 = V(weight, weight, weight);
+  for (depth = 1; n < max_vertices; depth++) {
+    hit_t hit;
+    const int object = scene_cast(sc, origin, direction, &hit);
+    const amber_cuda_material* m;
+    const prim* p;
+    scatter_t scatter;
+    float p_rr;
+    float* v = out + 8 * n;
+    v[0] = (float)object; v[1] = hit.t; v[2] = v[3] = v[4] = 0; v[5] = (float)stream.draws; v[6] = weight3.x; v[7] = 0;
+    n++;
+    if (object < 0) break;
+    v[2] = hit.position.x; v[3] = hit.position.y; v[4] = hit.position.z;
+    p = &sc->prims[object];
+    m = &sc->materials[p->material];
+    if (estimator == AMBER_CUDA_ESTIMATOR_NEE && sc->n_lights > 0 &&
+        (m->kind == AMBER_CUDA_MAT_LAMBERTIAN || m->kind == AMBER_CUDA_MAT_PHONG)) {
+      uniform(&s); uniform(&s); uniform(&s);
+    }
+    scatter = material_sample_light(m, sc->r0[p->material], hit.normal, neg(direction), &s);
+    p_rr = fminf((float)kRussianRoulette, max3(scatter.weight));
+    v[7] = p_rr;
+    if (uniform(&s) >= p_rr) break;
+    v[5] = (float)stream.draws;
+    if (depth >= max_depth) break;
+    origin = hit.position;
+    direction = scatter.dir;
+    weight3 = mul(weight3, V(scatter.weight.x / p_rr, scatter.weight.y / p_rr, scatter.weight.z / p_rr));
+  }
+  return n;
+}

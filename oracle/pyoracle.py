@@ -236,3 +236,12 @@ class Oracle:
         out = np.empty(n, dtype=np.float32)
         self.lib.oracle_stream(C.c_uint64(seed), C.c_uint32(pixel), C.c_uint64(sample), C.c_uint32(n), _ptr(out))
         return out
+
+    def trace_path(self, w, h, film_w, film_h, px, py, sample, seed, max_depth=0, estimator=0, max_vertices=64):
+        """Debug: per-vertex (prim, t, x, y, z, draws, throughput.r, p_rr) of one path."""
+        out = np.zeros((max_vertices, 8), dtype=np.float32)
+        n = self.lib.oracle_trace_path(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                                       C.c_float(film_h), C.c_uint32(px), C.c_uint32(py), C.c_uint64(sample),
+                                       C.c_uint64(seed), C.c_uint32(max_depth or (1 << 16)), C.c_int(estimator),
+                                       _ptr(out), C.c_int(max_vertices))
+        return out[:n]

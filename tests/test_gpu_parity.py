@@ -24,8 +24,12 @@ def check_cast(prim, t, want_prim, want_t):
     assert agree.mean() >= ID_AGREEMENT, f"hit ids agree on {agree.mean():.6f}"
     both = agree & (want_prim >= 0)
     rel = np.abs(t[both] - want_t[both]) / want_t[both]
-    # 1e-4 relative; distances at the kEPS scale (< 1e-4) are allowed 1e-8 absolute on top
-    assert np.all(rel <= T_RTOL + 1e-8 / want_t[both]), f"max rel t error {rel.max():.3e}"
+    # 1e-4 relative, plus an absolute floor of 0.1 kEPS = 1e-7: hits at t ~ 1e-5 are a
+    # surface re-hitting itself, where the reference's own t is cancellation noise
+    # (c = |c-o|^2 - r^2 in primitive_sphere.cc:79) and no two float evaluations agree
+    # to 1e-4.  The pure 1e-4 bound must still hold for >= 99.99 % of the hits.
+    assert np.all(rel <= T_RTOL + 1e-7 / want_t[both]), f"max rel t error {rel.max():.3e}"
+    assert (rel <= T_RTOL).mean() >= 0.9999, f"pure relative bound holds on {(rel <= T_RTOL).mean():.6f}"
     assert np.isnan(t[agree & (want_prim < 0)]).all()
     return float(agree.mean()), float(rel.max()) if rel.size else 0.0
 
@@ -82,8 +86,9 @@ def test_camera_rays(cornell_device, oracle):
     for tag, (w, h) in {"64x64": (64, 64), "1024x512": (1024, 512)}.items():
         cornell_device.set_sensor(Sensor(w, h))
         o, d, wt = cornell_device.eye_rays(g[f"{tag}.px"], g[f"{tag}.py"], g[f"{tag}.xi"])
-        assert np.allclose(o, g[f"{tag}.origin"], atol=1e-7)
-        assert np.allclose(d, g[f"{tag}.direction"], atol=1e-6)
+        # origin and direction are computed with the host's operations: bit-identical
+        assert np.array_equal(o, g[f"{tag}.origin"])
+        assert np.array_equal(d, g[f"{tag}.direction"])
         assert np.allclose(wt, g[f"{tag}.weight"], rtol=2e-5)
     cornell_device.set_sensor(Sensor(64, 64))
 
@@ -121,6 +126,7 @@ def test_image_matches_oracle_on_the_same_stream(cornell_device, oracle, estimat
     want, stats = oracle.render(w, w, *FILM, 0, spp, seed, depth, estimator=estimator)
     assert done == spp
     frac = image_agreement(image, want)
+    print(f"estimator {estimator}: {frac:.4f} of pixels agree with the oracle at {spp} spp")
     assert frac >= 0.99, f"only {frac:.4f} of pixels agree"
     got = cornell_device.stats()
     assert got["paths"] == w * w * spp
@@ -263,8 +269,11 @@ def test_full_size_properties(cornell_device):
     cornell_device.set_sensor(Sensor(512, 512))
     cornell_device.render(0, 16, seed=1, max_depth=32, estimator=1)
     small, _ = cornell_device.resolve()
-    ratio = np.median(small[300:500, 100:400]) / np.median(a[600:1000, 200:800])
-    assert 3.5 < ratio < 4.5, ratio
+    def robust_mean(image):  # firefly-free: mean of the luminance clipped at its 90th percentile
+        lum = image.sum(-1)
+        return float(np.minimum(lum, np.percentile(lum, 90)).mean())
+    ratio = robust_mean(small) / robust_mean(a)
+    assert 3.6 < ratio < 4.4, ratio
     cornell_device.set_sensor(Sensor(64, 64))
 
 
