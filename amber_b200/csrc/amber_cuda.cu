@@ -92,8 +92,8 @@ struct amber_cuda_ctx {
 
   // path pool
   PathPool pool{};
-  DeviceBuffer<float4> d_ray_o, d_ray_d, d_hit, d_thr, d_sh_o, d_sh_d, d_sh_c;
-  DeviceBuffer<uint4> d_meta;
+  DeviceBuffer<float4> d_ray, d_state, d_shadow;
+  DeviceBuffer<float2> d_hit;
   DeviceBuffer<uint32_t> d_q_new;
   DeviceBuffer<Control> d_ctl;
   Control* h_ctl = nullptr;  // pinned
@@ -230,25 +230,17 @@ void invalidate_constants(amber_cuda_ctx* ctx) {
 }
 
 int ensure_pool(amber_cuda_ctx* ctx, uint32_t slots) {
-  if (ctx->pool.n_slots == slots && ctx->d_ray_o.ptr) return AMBER_CUDA_OK;
-  CUDA_TRY(ctx, ctx->d_ray_o.resize(slots));
-  CUDA_TRY(ctx, ctx->d_ray_d.resize(slots));
+  if (ctx->pool.n_slots == slots && ctx->d_ray.ptr) return AMBER_CUDA_OK;
+  CUDA_TRY(ctx, ctx->d_ray.resize(2 * static_cast<size_t>(slots)));
+  CUDA_TRY(ctx, ctx->d_state.resize(2 * static_cast<size_t>(slots)));
   CUDA_TRY(ctx, ctx->d_hit.resize(slots));
-  CUDA_TRY(ctx, ctx->d_thr.resize(slots));
-  CUDA_TRY(ctx, ctx->d_meta.resize(slots));
   CUDA_TRY(ctx, ctx->d_q_new.resize(slots));
-  CUDA_TRY(ctx, ctx->d_sh_o.resize(slots));
-  CUDA_TRY(ctx, ctx->d_sh_d.resize(slots));
-  CUDA_TRY(ctx, ctx->d_sh_c.resize(slots));
-  ctx->pool.ray_o = ctx->d_ray_o.ptr;
-  ctx->pool.ray_d = ctx->d_ray_d.ptr;
+  CUDA_TRY(ctx, ctx->d_shadow.resize(3 * static_cast<size_t>(slots)));
+  ctx->pool.ray = ctx->d_ray.ptr;
+  ctx->pool.state = ctx->d_state.ptr;
   ctx->pool.hit = ctx->d_hit.ptr;
-  ctx->pool.thr = ctx->d_thr.ptr;
-  ctx->pool.meta = ctx->d_meta.ptr;
   ctx->pool.q_new = ctx->d_q_new.ptr;
-  ctx->pool.sh_o = ctx->d_sh_o.ptr;
-  ctx->pool.sh_d = ctx->d_sh_d.ptr;
-  ctx->pool.sh_c = ctx->d_sh_c.ptr;
+  ctx->pool.shadow = ctx->d_shadow.ptr;
   ctx->pool.n_slots = slots;
   return AMBER_CUDA_OK;
 }
@@ -305,9 +297,8 @@ int amber_cuda_destroy(amber_cuda_ctx* ctx) {
   ctx->d_tri_material.release(); ctx->d_sphere_material.release(); ctx->d_internal_to_prim.release();
   ctx->d_materials.release(); ctx->d_lights.release(); ctx->d_bvh_nodes.release();
   ctx->d_film.release(); ctx->d_resolved.release();
-  ctx->d_ray_o.release(); ctx->d_ray_d.release(); ctx->d_hit.release(); ctx->d_thr.release();
-  ctx->d_sh_o.release(); ctx->d_sh_d.release(); ctx->d_sh_c.release();
-  ctx->d_meta.release(); ctx->d_q_new.release(); ctx->d_ctl.release();
+  ctx->d_ray.release(); ctx->d_state.release(); ctx->d_hit.release(); ctx->d_shadow.release();
+  ctx->d_q_new.release(); ctx->d_ctl.release();
   for (auto& b : ctx->d_scratch_f) b.release();
   for (auto& b : ctx->d_scratch_i) b.release();
   for (auto& b : ctx->d_scratch_4) b.release();

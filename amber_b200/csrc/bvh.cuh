@@ -85,7 +85,7 @@ struct WideBvh {
         const int first = bvh_leaf_first(current), count = bvh_leaf_count(current);
         for (int k = 0; k < count; k++) {
           const float4* tri = reinterpret_cast<const float4*>(scene.tri_isect + first + k);
-          if (intersect_triangle(__ldg(tri), __ldg(tri + 1), __ldg(tri + 2), ray, hit.t, hit.t, hit.u, hit.v)) {
+          if (intersect_triangle(__ldg(tri), __ldg(tri + 1), __ldg(tri + 2), ray, hit.t, hit.t)) {
             hit.prim = first + k;
             if (kAnyHit) return true;
           }
@@ -115,7 +115,6 @@ struct WideBvh {
     HitRecord hit;
     hit.t = t_max;
     hit.prim = -1;
-    hit.u = hit.v = 0.0f;
     return traverse<true>(scene, ray, hit);
   }
 };

@@ -21,8 +21,7 @@ struct Ray {
 // include/amber/prelude/hit.h:90-94 does.
 __device__ __forceinline__ bool intersect_triangle(const float4 n_v0x, const float4 nu_v0y,
                                                    const float4 nv_v0z, const Ray& ray,
-                                                   float t_best, float& t_out, float& u_out,
-                                                   float& v_out) {
+                                                   float t_best, float& t_out) {
   const float3 T = v3(ray.o.x - n_v0x.w, ray.o.y - nu_v0y.w, ray.o.z - nv_v0z.w);
   const float3 n = v3(n_v0x);
   const float nd = dot(n, ray.d);
@@ -32,11 +31,7 @@ __device__ __forceinline__ bool intersect_triangle(const float4 n_v0x, const flo
   const float u = dot(v3(nu_v0y), h);
   const float v = dot(v3(nv_v0z), h);
   const bool hit = (u >= 0.0f) & (v >= 0.0f) & (u + v <= 1.0f) & (t > kEpsF) & (t < t_best);
-  if (hit) {
-    t_out = t;
-    u_out = u;
-    v_out = v;
-  }
+  if (hit) t_out = t;
   return hit;
 }
 
@@ -79,15 +74,11 @@ struct ConstList {
     HitRecord hit;
     hit.t = CUDART_MAX_NORMAL_F;  // Cast(ray) == Cast(ray, numeric_limits::max), acceleration.h:46-51
     hit.prim = -1;
-    hit.u = 0.0f;
-    hit.v = 0.0f;
     const int n_tris = c_scene.n_tris;
 #pragma unroll 2
     for (int i = 0; i < n_tris; i++) {
       const TriIsect& tri = c_scene.tri_isect[i];
-      if (intersect_triangle(tri.n_v0x, tri.nu_v0y, tri.nv_v0z, ray, hit.t, hit.t, hit.u, hit.v)) {
-        hit.prim = i;
-      }
+      if (intersect_triangle(tri.n_v0x, tri.nu_v0y, tri.nv_v0z, ray, hit.t, hit.t)) hit.prim = i;
     }
     const int n_spheres = c_scene.n_spheres;
     for (int i = 0; i < n_spheres; i++) {
@@ -100,12 +91,12 @@ struct ConstList {
   // true if anything lies in (kEPS, t_max)
   static __device__ __forceinline__ bool occluded(const SceneView&, const Ray& ray, float t_max) {
     bool blocked = false;
-    float t, u, v;
+    float t;
     const int n_tris = c_scene.n_tris;
 #pragma unroll 2
     for (int i = 0; i < n_tris; i++) {
       const TriIsect& tri = c_scene.tri_isect[i];
-      blocked |= intersect_triangle(tri.n_v0x, tri.nu_v0y, tri.nv_v0z, ray, t_max, t, u, v);
+      blocked |= intersect_triangle(tri.n_v0x, tri.nu_v0y, tri.nv_v0z, ray, t_max, t);
     }
     const int n_spheres = c_scene.n_spheres;
     for (int i = 0; i < n_spheres; i++) {

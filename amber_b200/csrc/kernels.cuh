@@ -1,6 +1,6 @@
 // kernels.cuh -- the wavefront path tracer: raygen, extend, shade, connect, resolve.
 //
-// One pool of P resident path slots in SoA float4 arrays.  Per wavefront step:
+// One pool of P resident path slots.  Per wavefront step:
 //   raygen   : slots freed by the previous shade take the next (pixel, sample) and a
 //              thin-lens camera ray             (algorithm_pt.cc:112-135, lens_thin.cc:70-107)
 //   bookkeep : one thread advances the path counter and clears the queue counters
@@ -10,6 +10,14 @@
 //   connect  : any-hit for the shadow queue + film add
 // Terminated slots are compacted into `q_new`, shadow rays into the shadow queue:
 // __ballot_sync/__popc inside the warp, one smem scan and ONE global atomic per block.
+//
+// Layout in HBM (all float4 / 16-byte accesses):
+//   ray[2i], ray[2i+1]     origin xyz + live flag, direction xyz             32 B per slot
+//   state[2i], state[2i+1] throughput rgb ; (pixel, sample, depth|flags, -)  32 B per slot
+//   hit[i]                 (t, primitive)                                     8 B per slot
+//   shadow[3j..3j+2]       origin + t_max, direction + pixel, contribution   48 B per entry
+// A slot's ray and state each fill exactly one 32-byte sector, so the scattered writes of
+// raygen (slots arrive in queue order) never touch a partial sector.
 #pragma once
 
 #include "intersect.cuh"
@@ -18,7 +26,8 @@
 namespace amber_cuda {
 
 constexpr int kBlock = 256;
-constexpr uint32_t kFlagCountEmission = 1u << 31;  // meta.w: emission at the next hit counts
+constexpr uint32_t kFlagCountEmission = 1u << 31;  // emission at the next hit counts
+constexpr uint32_t kDepthMask = 0xffffffu;
 
 struct Control {
   unsigned long long next_path;    // next path index of this render call
@@ -31,15 +40,11 @@ struct Control {
 };
 
 struct PathPool {
-  float4* ray_o;  // origin xyz, w = 1 live / 0 free
-  float4* ray_d;  // direction xyz (not re-normalised, ray.h:52-62)
-  float4* hit;    // HitRecord
-  float4* thr;    // throughput rgb
-  uint4* meta;    // pixel, sample, draws consumed, depth | flags
-  uint32_t* q_new;
-  float4* sh_o;  // shadow ray origin xyz, w = t_max
-  float4* sh_d;  // direction xyz, w = pixel (int bits)
-  float4* sh_c;  // contribution rgb
+  float4* ray;      // [2 * n_slots]
+  float4* state;    // [2 * n_slots]
+  float2* hit;      // [n_slots]
+  uint32_t* q_new;  // [n_slots]
+  float4* shadow;   // [3 * n_slots]
   uint32_t n_slots;
 };
 
@@ -75,7 +80,7 @@ struct ScriptedRng {
 // Block-aggregated queue slot allocation: returns this thread's index in the queue
 // (valid only if `want`).  Warp ballot + popc, smem scan over the warps, one atomicAdd
 // per block.
-__device__ __forceinline__ uint32_t queue_alloc(bool want, unsigned int* counter, uint32_t* smem /*[kBlock/32+1]*/) {
+__device__ __forceinline__ uint32_t queue_alloc(bool want, unsigned int* counter, uint32_t* smem /*[kBlock/32]*/) {
   const unsigned int ballot = __ballot_sync(0xffffffffu, want);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane == 0) smem[warp] = __popc(ballot);
@@ -161,22 +166,24 @@ __global__ void __launch_bounds__(kBlock) raygen_kernel(const RenderArgs args) {
   if (j >= ctl->n_new) return;
   const uint32_t slot = args.pool.q_new[j];
   const unsigned long long path = ctl->next_path + j;
+  float4* ray = args.pool.ray + 2 * static_cast<size_t>(slot);
   if (path >= ctl->total_paths) {
-    args.pool.ray_o[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    ray[0] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     return;
   }
   const uint32_t pixel = static_cast<uint32_t>(path % args.n_pixels);
   const uint32_t sample = static_cast<uint32_t>(args.sample_begin + path / args.n_pixels);
-  Philox rng;
-  rng.init(args.seed, pixel, sample, 0);
+  CameraRng rng;
+  rng.init(args.seed, pixel, sample);
   const uint32_t width = c_camera.sensor.width;
   float3 o, d;
   float w;
   generate_eye_ray(pixel % width, pixel / width, rng, o, d, w);
-  args.pool.ray_o[slot] = make_float4(o.x, o.y, o.z, 1.0f);
-  args.pool.ray_d[slot] = make_float4(d.x, d.y, d.z, 0.0f);
-  args.pool.thr[slot] = make_float4(w, w, w, 0.0f);
-  args.pool.meta[slot] = make_uint4(pixel, sample, rng.draws, kFlagCountEmission);
+  ray[0] = make_float4(o.x, o.y, o.z, 1.0f);
+  ray[1] = make_float4(d.x, d.y, d.z, 0.0f);
+  float4* state = args.pool.state + 2 * static_cast<size_t>(slot);
+  state[0] = make_float4(w, w, w, 0.0f);
+  state[1] = make_float4(__uint_as_float(pixel), __uint_as_float(sample), __uint_as_float(kFlagCountEmission), 0.0f);
 }
 
 // Fills q_new with every slot (start of a render call: all slots are free).
@@ -184,7 +191,7 @@ __global__ void __launch_bounds__(kBlock) pool_reset_kernel(const RenderArgs arg
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= args.pool.n_slots) return;
   args.pool.q_new[i] = i;
-  args.pool.ray_o[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  args.pool.ray[2 * static_cast<size_t>(i)] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 }
 
 __global__ void bookkeep_kernel(Control* ctl) {
@@ -207,14 +214,15 @@ template <class Accel>
 __global__ void __launch_bounds__(kBlock) extend_kernel(const RenderArgs args) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= args.pool.n_slots) return;
-  const float4 o = args.pool.ray_o[i];
+  const float4* r = args.pool.ray + 2 * static_cast<size_t>(i);
+  const float4 o = r[0];
   if (o.w == 0.0f) return;
-  const float4 d = __ldg(&args.pool.ray_d[i]);
+  const float4 d = r[1];
   Ray ray;
   ray.o = v3(o);
   ray.d = v3(d);
   const HitRecord hit = Accel::closest(args.scene, ray);
-  args.pool.hit[i] = make_float4(hit.t, __int_as_float(hit.prim), hit.u, hit.v);
+  args.pool.hit[i] = make_float2(hit.t, __int_as_float(hit.prim));
 }
 
 // `extend` on caller-supplied rays (amber_cuda_cast / amber_cuda_cast_device).
@@ -228,7 +236,7 @@ __global__ void __launch_bounds__(kBlock) cast_kernel(const SceneView scene, con
   ray.o = v3(ray_o[i]);
   ray.d = v3(ray_d[i]);
   const HitRecord hit = Accel::closest(scene, ray);
-  hits[i] = make_float4(hit.t, __int_as_float(hit.prim), hit.u, hit.v);
+  hits[i] = make_float4(hit.t, __int_as_float(hit.prim), 0.0f, 0.0f);
 }
 
 // ---------------------------------------------------------------------------------
@@ -286,14 +294,11 @@ struct ShadowRay {
 // lower_bound, Triangle::SampleSurfacePoint); contribution as the s = 1 connection
 // of include/amber/rendering/bidirectional_path_sampling.h:956-1016:
 //   Le(y -> x) / pdf_area * throughput * BSDF(x) * |cos_x cos_y| / r^2.
-// Three uniforms: light, u, v.
-template <class Rng>
+// Three uniforms: light choice, u, v (fixed slots 3, 4, 5 of the vertex).
 __device__ __forceinline__ bool sample_direct(const SceneView& scene, const MaterialDev& m, float3 x,
-                                              float3 n, float3 wo, float3 throughput, Rng& rng,
-                                              ShadowRay& shadow) {
-  const float target = rng.next() * scene.total_power;
-  float u = rng.next();
-  float v = rng.next();
+                                              float3 n, float3 wo, float3 throughput, float xi_light,
+                                              float u, float v, ShadowRay& shadow) {
+  const float target = xi_light * scene.total_power;
   int lo = 0, hi = scene.n_lights - 1;
   while (lo < hi) {  // first light whose cumulative power >= target
     const int mid = (lo + hi) >> 1;
@@ -329,55 +334,69 @@ __device__ __forceinline__ void film_add(float4* film, uint32_t pixel, float3 va
 }
 
 __global__ void __launch_bounds__(kBlock) shade_kernel(const RenderArgs args) {
-  __shared__ uint32_t smem[kBlock / 32 + 1];
+  __shared__ uint32_t smem[kBlock / 32];
+  __shared__ unsigned int block_live, block_alive;
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   const PathPool& pool = args.pool;
+  if (threadIdx.x == 0) {
+    block_live = 0;
+    block_alive = 0;
+  }
   bool live = false, terminated = false, has_shadow = false;
   ShadowRay shadow;
   uint32_t pixel = 0;
   if (i < pool.n_slots) {
-    const float4 o4 = pool.ray_o[i];
+    float4* ray_slot = pool.ray + 2 * static_cast<size_t>(i);
+    const float4 o4 = ray_slot[0];
     live = o4.w != 0.0f;
     if (live) {
-      const float4 d4 = pool.ray_d[i];
-      const float4 h4 = pool.hit[i];
+      const float2 h2 = pool.hit[i];
       HitRecord hit;
-      hit.t = h4.x; hit.prim = __float_as_int(h4.y); hit.u = h4.z; hit.v = h4.w;
+      hit.t = h2.x;
+      hit.prim = __float_as_int(h2.y);
       if (hit.prim < 0) {
         terminated = true;  // algorithm_pt.cc:140-142
       } else {
+        const float4 d4 = ray_slot[1];
+        float4* state_slot = pool.state + 2 * static_cast<size_t>(i);
+        const float4 t4 = state_slot[0];
+        const float4 m4 = state_slot[1];
         Ray ray;
         ray.o = v3(o4);
         ray.d = v3(d4);
-        const float4 t4 = pool.thr[i];
-        uint4 meta = pool.meta[i];
-        pixel = meta.x;
+        pixel = __float_as_uint(m4.x);
+        const uint32_t sample = __float_as_uint(m4.y);
+        const uint32_t flags = __float_as_uint(m4.z);
+        const uint32_t depth = (flags & kDepthMask) + 1u;  // this is the depth-th surface vertex
         float3 throughput = v3(t4);
         float3 x, n;
         int material_index;
         surface_point(args.scene, ray, hit, x, n, material_index);
         const MaterialDev m = load_material(args.scene, material_index);
         const float3 wo = -ray.d;
-        Philox rng;
-        rng.init(args.seed, meta.x, meta.y, meta.z);
+        VertexRng rng;
+        rng.init(args.seed, pixel, sample, depth);  // one Philox block, same place for every lane
 
         // emission, algorithm_pt.cc:144
         if (m.kind == 4) {
           const bool sampled_by_nee = args.estimator == 1 && hit.prim < args.scene.n_tris;
-          if (!sampled_by_nee || (meta.w & kFlagCountEmission)) {
+          if (!sampled_by_nee || (flags & kFlagCountEmission)) {
             const float3 le = emitted_radiance(m, n, wo);
             if (le.x > 0.0f || le.y > 0.0f || le.z > 0.0f) film_add(args.film, pixel, throughput * le);
           }
         }
         const bool connect = args.estimator == 1 && m.nee && args.scene.n_lights > 0;
-        if (connect) has_shadow = sample_direct(args.scene, m, x, n, wo, throughput, rng, shadow);
+        if (connect) {
+          float lu, lv;
+          rng.light_point(lu, lv);
+          has_shadow = sample_direct(args.scene, m, x, n, wo, throughput, rng.light_choice(), lu, lv, shadow);
+        }
 
         // BSDF sample + Russian roulette, algorithm_pt.cc:145-156
         const Scatter scatter = sample_light(m, n, wo, rng);
         const float p = fminf(kRussianRoulette, max3(scatter.weight));
-        const uint32_t depth = (meta.w & 0xffffu) + 1u;
         if (scatter.capped) atomicAdd(&args.ctl->phong_capped, 1ull);
-        if (!(rng.next() < p)) {
+        if (!(rng.rr() < p)) {
           terminated = true;
         } else if (depth >= args.max_depth) {
           terminated = true;
@@ -385,12 +404,10 @@ __global__ void __launch_bounds__(kBlock) shade_kernel(const RenderArgs args) {
         } else {
           const float inv_p = 1.0f / p;
           throughput = throughput * (inv_p * scatter.weight);
-          pool.ray_o[i] = make_float4(x.x, x.y, x.z, 1.0f);
-          pool.ray_d[i] = make_float4(scatter.dir.x, scatter.dir.y, scatter.dir.z, 0.0f);
-          pool.thr[i] = make_float4(throughput.x, throughput.y, throughput.z, 0.0f);
-          meta.z = rng.draws;
-          meta.w = depth | (connect ? 0u : kFlagCountEmission);
-          pool.meta[i] = meta;
+          ray_slot[0] = make_float4(x.x, x.y, x.z, 1.0f);
+          ray_slot[1] = make_float4(scatter.dir.x, scatter.dir.y, scatter.dir.z, 0.0f);
+          state_slot[0] = make_float4(throughput.x, throughput.y, throughput.z, 0.0f);
+          state_slot[1] = make_float4(m4.x, m4.y, __uint_as_float(depth | (connect ? 0u : kFlagCountEmission)), 0.0f);
         }
       }
     }
@@ -400,20 +417,14 @@ __global__ void __launch_bounds__(kBlock) shade_kernel(const RenderArgs args) {
   if (terminated) pool.q_new[new_index] = i;
   const uint32_t shadow_index = queue_alloc(has_shadow, &args.ctl->n_shadow, smem);
   if (has_shadow) {
-    pool.sh_o[shadow_index] = make_float4(shadow.o.x, shadow.o.y, shadow.o.z, shadow.t_max);
-    pool.sh_d[shadow_index] = make_float4(shadow.d.x, shadow.d.y, shadow.d.z, __uint_as_float(pixel));
-    pool.sh_c[shadow_index] =
-        make_float4(shadow.contribution.x, shadow.contribution.y, shadow.contribution.z, 0.0f);
+    float4* out = pool.shadow + 3 * static_cast<size_t>(shadow_index);
+    out[0] = make_float4(shadow.o.x, shadow.o.y, shadow.o.z, shadow.t_max);
+    out[1] = make_float4(shadow.d.x, shadow.d.y, shadow.d.z, __uint_as_float(pixel));
+    out[2] = make_float4(shadow.contribution.x, shadow.contribution.y, shadow.contribution.z, 0.0f);
   }
-  // statistics: rays extended this step, survivors
+  // statistics: rays extended this step, survivors (queue_alloc's barriers order the init above)
   const unsigned int live_ballot = __ballot_sync(0xffffffffu, live);
   const unsigned int alive_ballot = __ballot_sync(0xffffffffu, live && !terminated);
-  __shared__ unsigned int block_live, block_alive;
-  if (threadIdx.x == 0) {
-    block_live = 0;
-    block_alive = 0;
-  }
-  __syncthreads();
   if ((threadIdx.x & 31) == 0) {
     atomicAdd(&block_live, __popc(live_ballot));
     atomicAdd(&block_alive, __popc(alive_ballot));
@@ -430,13 +441,14 @@ template <class Accel>
 __global__ void __launch_bounds__(kBlock) connect_kernel(const RenderArgs args) {
   const uint32_t j = blockIdx.x * kBlock + threadIdx.x;
   if (j >= args.ctl->n_shadow) return;
-  const float4 o = args.pool.sh_o[j];
-  const float4 d = args.pool.sh_d[j];
+  const float4* in = args.pool.shadow + 3 * static_cast<size_t>(j);
+  const float4 o = in[0];
+  const float4 d = in[1];
   Ray ray;
   ray.o = v3(o);
   ray.d = v3(d);
   if (Accel::occluded(args.scene, ray, o.w)) return;
-  const float4 c = args.pool.sh_c[j];
+  const float4 c = in[2];
   film_add(args.film, __float_as_uint(d.w), v3(c));
 }
 

@@ -36,28 +36,6 @@ __device__ __forceinline__ float3 local_to_world(float3 u, float3 v, float3 w, f
   return add_exact(add_exact(a, b), scale_exact(cos_theta, w));
 }
 
-// HemispherePSA, sampling.h:234-265: cos = sqrt(r0), sin = sqrt(1-r0), phi = 2 pi r1.
-template <class Rng>
-__device__ __forceinline__ float3 hemisphere_psa(float3 w, Rng& rng) {
-  float3 u, v;
-  orthonormal_basis(w, u, v);
-  const float r0 = rng.next();
-  const float r1 = rng.next();
-  return local_to_world(u, v, w, __fsqrt_rn(1.0f - r0), __fsqrt_rn(r0), __fmul_rn(2.0f * kPiF, r1));
-}
-
-// CosinePower, sampling.h:267-300: cos = r0^(1/(e+1)).
-template <class Rng>
-__device__ __forceinline__ float3 cosine_power(float3 w, float exponent, Rng& rng) {
-  float3 u, v;
-  orthonormal_basis(w, u, v);
-  const float r0 = rng.next();
-  const float r1 = rng.next();
-  const float cos_theta = powf(r0, __fdiv_rn(1.0f, exponent + 1.0f));
-  const float sin_theta = __fsqrt_rn(__fsub_rn(1.0f, __fmul_rn(cos_theta, cos_theta)));
-  return local_to_world(u, v, w, sin_theta, cos_theta, __fmul_rn(2.0f * kPiF, r1));
-}
-
 // Schlick, src/amber/scene/material_refraction.cc:271-275.  The host evaluates
 // r0 + (1 - r0) * pow(1 - cos, 5) in double (std::pow(float, int)) and rounds once.
 __device__ __forceinline__ float schlick(float r0, float cos_theta) {
@@ -67,40 +45,39 @@ __device__ __forceinline__ float schlick(float r0, float cos_theta) {
 }
 
 // Material::SampleLight for radiance transport.  `wo` = direction_out = -ray.d.
+// `rng.next()` yields the BSDF-sampling uniforms in the reference's call order.
+//
+// Lambertian (material_lambertian.cc:61-70: HemispherePSA, sampling.h:234-265, cos = sqrt(r0),
+// sin = sqrt(1-r0), phi = 2 pi r1, weight kd) and Phong (material_phong.cc:81-106: CosinePower,
+// sampling.h:267-300, cos = r0^(1/(e+1)), rejected until on the side of wo, weight
+// ks (e+2)/(e+1)|cos_i|) share one lobe-sampling block -- basis, compose, test -- so that a
+// warp holding both kinds runs it once.  The reference rebuilds the basis on every Phong
+// retry; it only depends on the mirror direction, so it is hoisted.  The retry loop is
+// unbounded there; here it is capped (the cap is counted and never hit in practice).
 template <class Rng>
 __device__ __forceinline__ Scatter sample_light(const MaterialDev& m, float3 n, float3 wo, Rng& rng) {
   Scatter s;
   s.capped = false;
+  s.dir = v3(0.0f, 0.0f, 0.0f);
+  s.weight = v3(0.0f, 0.0f, 0.0f);
   const float3 rho = v3(m.r, m.g, m.b);
   const float cos_o = dot_exact(wo, n);
+  float3 axis = n;
+  bool lobe = false;
+  const bool phong = m.kind == 1;
   switch (m.kind) {
-    case 0: {  // Lambertian: src/amber/scene/material_lambertian.cc:61-70, weight kd
-      const float3 w = cos_o > 0.0f ? n : -n;
-      s.dir = hemisphere_psa(w, rng);
-      s.weight = rho;
+    case 0:
+      axis = cos_o > 0.0f ? n : -n;
+      lobe = true;
       break;
-    }
-    case 1: {  // Phong: src/amber/scene/material_phong.cc:81-106 (rejection, bounded here)
-      const float3 refl = perfect_reflection(wo, n, cos_o);
-      s.weight = v3(0.0f, 0.0f, 0.0f);
-      s.dir = refl;
-      s.capped = true;
-      for (int attempt = 0; attempt < kPhongMaxTries; attempt++) {
-        const float3 dir = cosine_power(refl, m.param, rng);
-        const float cos_i = dot(dir, n);
-        if (cos_o * cos_i <= 0.0f) continue;
-        s.dir = dir;
-        s.weight = ((m.param + 2.0f) / (m.param + 1.0f) * fabsf(cos_i)) * rho;
-        s.capped = false;
-        break;
-      }
+    case 1:
+      axis = perfect_reflection(wo, n, cos_o);
+      lobe = true;
       break;
-    }
-    case 2: {  // Specular: src/amber/scene/material_specular.cc:62-70
+    case 2:  // Specular: src/amber/scene/material_specular.cc:62-70
       s.dir = perfect_reflection(wo, n, cos_o);
       s.weight = rho;
       break;
-    }
     case 3: {  // Refraction: src/amber/scene/material_refraction.cc:177-220
       const float ior = cos_o > 0.0f ? __fdiv_rn(1.0f, m.param) : m.param;
       const float ior2 = __fmul_rn(ior, ior);
@@ -129,15 +106,44 @@ __device__ __forceinline__ Scatter sample_light(const MaterialDev& m, float3 n, 
       }
       break;
     }
-    case 5: {  // Eye: include/amber/scene/material_eye.h:146-155, pass-through
+    case 5:  // Eye: include/amber/scene/material_eye.h:146-155, pass-through
       s.dir = -wo;
       s.weight = v3(1.0f, 1.0f, 1.0f);
       break;
-    }
-    default: {  // DiffuseLight: include/amber/scene/material_diffuse_light.h:185-194
-      s.dir = v3(0.0f, 0.0f, 0.0f);
-      s.weight = v3(0.0f, 0.0f, 0.0f);
+    default:  // DiffuseLight: include/amber/scene/material_diffuse_light.h:185-194, weight 0
       break;
+  }
+  if (lobe) {
+    float3 u, v;
+    orthonormal_basis(axis, u, v);
+    const float inv_e1 = __fdiv_rn(1.0f, m.param + 1.0f);
+    float r0 = rng.next();
+    float r1 = rng.next();
+    for (int attempt = 1;; attempt++) {
+      float cos_theta, sin_theta;
+      if (phong) {
+        cos_theta = powf(r0, inv_e1);
+        sin_theta = __fsqrt_rn(__fsub_rn(1.0f, __fmul_rn(cos_theta, cos_theta)));
+      } else {
+        cos_theta = __fsqrt_rn(r0);
+        sin_theta = __fsqrt_rn(1.0f - r0);
+      }
+      s.dir = local_to_world(u, v, axis, sin_theta, cos_theta, __fmul_rn(2.0f * kPiF, r1));
+      if (!phong) {
+        s.weight = rho;
+        break;
+      }
+      const float cos_i = dot_exact(s.dir, n);
+      if (cos_o * cos_i > 0.0f) {
+        s.weight = ((m.param + 2.0f) / (m.param + 1.0f) * fabsf(cos_i)) * rho;
+        break;
+      }
+      if (attempt >= kPhongMaxTries) {
+        s.capped = true;
+        break;
+      }
+      r0 = rng.next();
+      r1 = rng.next();
     }
   }
   return s;

@@ -112,14 +112,14 @@ struct CameraDev {
   SensorDev sensor;
 };
 
-// Hit record written by `extend`, one float4 per path slot.
-//   x = t (NaN on a miss, include/amber/prelude/hit.h:62-66)
-//   y = internal primitive index (int bits; -1 on a miss); triangles first, then spheres
-//   z, w = barycentric u, v (triangles)
+// Hit record written by `extend`, one float2 per path slot:
+//   t    (NaN on a miss, include/amber/prelude/hit.h:62-66)
+//   prim internal primitive index (int bits; -1 on a miss); triangles first, then spheres.
+// Barycentrics are not carried: `shade` recomputes them once per hit with the reference's
+// exact operation sequence (kernels.cuh, surface_point).
 struct HitRecord {
   float t;
   int32_t prim;
-  float u, v;
 };
 
 }  // namespace amber_cuda

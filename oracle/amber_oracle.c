@@ -47,16 +47,24 @@ typedef struct {
   philox_stream* stream; /* if non-NULL */
   const float* xi;
   int n, used;
+  int camera; /* stream only: 1 while the camera vertex is being sampled */
 } sampler;
-static float uniform(sampler* s) { /* Uniform<float>: static_cast<float>(sampler()), sampling.h:156-161 */
-  if (s->stream) return philox_stream_next(s->stream);
-  {
-    /* past the scripted list: a Weyl sequence, identical in the harness and the kernels */
-    const float v = s->used < s->n ? s->xi[s->used]
-                                   : (float)(((uint32_t)s->used * 2654435769u) >> 8) * (1.0f / 16777216.0f);
-    s->used++;
-    return v;
-  }
+static float scripted(sampler* s) {
+  /* past the scripted list: a Weyl sequence, identical in the harness and the kernels */
+  const float v = s->used < s->n ? s->xi[s->used]
+                                 : (float)(((uint32_t)s->used * 2654435769u) >> 8) * (1.0f / 16777216.0f);
+  s->used++;
+  return v;
+}
+/* Uniform<float>: static_cast<float>(sampler()), sampling.h:156-161.  On the stream the call
+ * is a camera uniform or the next BSDF-sampling uniform of the current vertex. */
+static float uniform(sampler* s) {
+  if (!s->stream) return scripted(s);
+  return s->camera ? philox_stream_next_camera(s->stream) : philox_stream_next_bsdf(s->stream);
+}
+static float uniform_rr(sampler* s) { return s->stream ? philox_stream_rr(s->stream) : scripted(s); }
+static float uniform_light(sampler* s, uint32_t i) {
+  return s->stream ? philox_stream_light(s->stream, i) : scripted(s);
 }
 
 /* ---- scene ----------------------------------------------------------------------- */
@@ -451,14 +459,17 @@ static vec3 material_radiance(const amber_cuda_material* m, vec3 n, vec3 wo) {
 }
 
 /* Triangle::SampleSurfacePoint, primitive_triangle.cc:136-150 */
-static vec3 triangle_sample(vec3 v0, vec3 v1, vec3 v2, sampler* s) {
-  float u = uniform(s);
-  float v = uniform(s);
+static vec3 triangle_point(vec3 v0, vec3 v1, vec3 v2, float u, float v) {
   if (u + v >= 1) {
     u = 1 - u;
     v = 1 - v;
   }
   return add(add(scale(1 - u - v, v0), scale(u, v1)), scale(v, v2));
+}
+static vec3 triangle_sample(vec3 v0, vec3 v1, vec3 v2, sampler* s) {
+  const float u = uniform(s);
+  const float v = uniform(s);
+  return triangle_point(v0, v1, v2, u, v);
 }
 
 /* PixelBound::Uniform (src/amber/rendering/sensor.cc:94-101,111-120) +
@@ -542,7 +553,7 @@ void oracle_sample_light(const amber_cuda_material* material, uint64_t n, const 
   if (m.kind == AMBER_CUDA_MAT_REFRACTION || m.kind == AMBER_CUDA_MAT_EYE) m.rgb[0] = m.rgb[1] = m.rgb[2] = 1.0f;
   if (m.kind == AMBER_CUDA_MAT_REFRACTION) r0 = (float)pow((double)((m.param - 1) / (m.param + 1)), 2.0);
   for (i = 0; i < n; i++) {
-    sampler s = {NULL, xi8 + 8 * i, 8, 0};
+    sampler s = {NULL, xi8 + 8 * i, 8, 0, 0};
     const scatter_t sc = material_sample_light(&m, r0, V(normal[3 * i], normal[3 * i + 1], normal[3 * i + 2]),
                                                V(dir_out[3 * i], dir_out[3 * i + 1], dir_out[3 * i + 2]), &s);
     dir_in[3 * i] = sc.dir.x; dir_in[3 * i + 1] = sc.dir.y; dir_in[3 * i + 2] = sc.dir.z;
@@ -570,7 +581,7 @@ void oracle_eye_rays(const oracle_scene* scene, uint32_t w, uint32_t h, float fi
                      float* origin, float* direction, float* weight) {
   uint64_t i;
   for (i = 0; i < n; i++) {
-    sampler s = {NULL, xi5 + 5 * i, 5, 0};
+    sampler s = {NULL, xi5 + 5 * i, 5, 0, 0};
     vec3 o, d;
     generate_eye_ray(scene, w, h, film_w, film_h, px[i], py[i], &s, &o, &d, &weight[i]);
     origin[3 * i] = o.x; origin[3 * i + 1] = o.y; origin[3 * i + 2] = o.z;
@@ -594,7 +605,7 @@ typedef struct {
 static void trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h,
                        uint32_t px, uint32_t py, philox_stream* stream, uint32_t max_depth, int estimator,
                        double rgb[3], counters* count) {
-  sampler s = {stream, NULL, 0, 0};
+  sampler s = {stream, NULL, 0, 0, 1};
   vec3 origin, direction, weight3, measurement = V(0, 0, 0);
   float weight;
   int count_emission = 1;
@@ -611,6 +622,8 @@ static void trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float fil
     scatter_t scatter;
     float p_rr;
     int connectable;
+    philox_stream_begin_vertex(stream, depth);
+    s.camera = 0;
     count->closest_rays++;
     if (object < 0) break;
     p = &sc->prims[object];
@@ -627,7 +640,7 @@ static void trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float fil
                   (m->kind == AMBER_CUDA_MAT_LAMBERTIAN || m->kind == AMBER_CUDA_MAT_PHONG);
     if (connectable) {
       /* light choice: lower_bound over cumulative powers of Uniform(total), light_set.h:87-91 */
-      const float target = uniform(&s) * sc->total_power;
+      const float target = uniform_light(&s, 0) * sc->total_power;
       uint32_t li = 0;
       const light* l;
       const prim* lp;
@@ -636,7 +649,11 @@ static void trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float fil
       while (li + 1 < sc->n_lights && sc->lights[li].cumulative_power < target) li++;
       l = &sc->lights[li];
       lp = &sc->prims[l->prim_index];
-      y = triangle_sample(lp->v0, lp->v1, lp->v2, &s);
+      {
+        const float lu = uniform_light(&s, 1);
+        const float lv = uniform_light(&s, 2);
+        y = triangle_point(lp->v0, lp->v1, lp->v2, lu, lv);
+      }
       xy = sub(y, hit.position);
       dist2 = dot(xy, xy);
       dist = sqrtf(dist2);
@@ -661,7 +678,7 @@ static void trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float fil
     scatter = material_sample_light(m, sc->r0[p->material], hit.normal, wo, &s);
     /* p = min(kRussianRoulette, Max(weight)); stop if Uniform >= p, algorithm_pt.cc:148-153 */
     p_rr = fminf((float)kRussianRoulette, max3(scatter.weight));
-    if (uniform(&s) >= p_rr) break;
+    if (uniform_rr(&s) >= p_rr) break;
     if (depth >= max_depth) {
       count->truncated++;
       break;
@@ -747,7 +764,7 @@ void oracle_stream(uint64_t seed, uint32_t pixel, uint64_t sample, uint32_t n, f
   philox_stream s;
   uint32_t i;
   philox_stream_reset(&s, seed, pixel, sample);
-  for (i = 0; i < n; i++) out[i] = philox_stream_next(&s);
+  for (i = 0; i < n; i++) out[i] = philox_stream_next_camera(&s); /* vertex 0, slots 0.. */
 }
 
 /* The fixed ray set of the intersection-parity test: ray i of the first
@@ -760,13 +777,13 @@ void oracle_ray_set(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w
   uint64_t i;
   for (i = 0; i < n; i++) {
     philox_stream stream;
-    sampler s = {&stream, NULL, 0, 0};
+    sampler s = {&stream, NULL, 0, 0, 1};
     vec3 o, d, o2, d2;
     float weight;
     uint32_t px, py;
     hit_t hit;
     int object;
-    philox_stream_reset(&stream, seed, (uint32_t)i, i >> 32);
+    philox_stream_reset(&stream, seed, (uint32_t)i, 0);
     px = (uint32_t)(uniform(&s) * (float)w);
     py = (uint32_t)(uniform(&s) * (float)h);
     if (px >= w) px = w - 1;
@@ -777,7 +794,10 @@ void oracle_ray_set(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w
     d2 = d;
     if (object >= 0) {
       const prim* p = &sc->prims[object];
-      const scatter_t scatter =
+      scatter_t scatter;
+      philox_stream_begin_vertex(&stream, 1);
+      s.camera = 0;
+      scatter =
           material_sample_light(&sc->materials[p->material], sc->r0[p->material], hit.normal, neg(d), &s);
       if (scatter.dir.x != 0 || scatter.dir.y != 0 || scatter.dir.z != 0) {
         o2 = hit.position;
@@ -797,7 +817,7 @@ int oracle_trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float film
                       uint32_t px, uint32_t py, uint64_t sample, uint64_t seed, uint32_t max_depth,
                       int estimator, float* out, int max_vertices) {
   philox_stream stream;
-  sampler s = {&stream, NULL, 0, 0};
+  sampler s = {&stream, NULL, 0, 0, 1};
   vec3 origin, direction, weight3;
   float weight;
   int n = 0;
@@ -813,6 +833,8 @@ int oracle_trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float film
     scatter_t scatter;
     float p_rr;
     float* v = out + 8 * n;
+    philox_stream_begin_vertex(&stream, depth);
+    s.camera = 0;
     v[0] = (float)object; v[1] = hit.t; v[2] = v[3] = v[4] = 0; v[5] = (float)stream.draws; v[6] = weight3.x; v[7] = 0;
     n++;
     if (object < 0) break;
@@ -821,12 +843,12 @@ int oracle_trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float film
     m = &sc->materials[p->material];
     if (estimator == AMBER_CUDA_ESTIMATOR_NEE && sc->n_lights > 0 &&
         (m->kind == AMBER_CUDA_MAT_LAMBERTIAN || m->kind == AMBER_CUDA_MAT_PHONG)) {
-      uniform(&s); uniform(&s); uniform(&s);
+      /* the light-sampling slots are fixed: nothing to skip */
     }
     scatter = material_sample_light(m, sc->r0[p->material], hit.normal, neg(direction), &s);
     p_rr = fminf((float)kRussianRoulette, max3(scatter.weight));
     v[7] = p_rr;
-    if (uniform(&s) >= p_rr) break;
+    if (uniform_rr(&s) >= p_rr) break;
     v[5] = (float)stream.draws;
     if (depth >= max_depth) break;
     origin = hit.position;

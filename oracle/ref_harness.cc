@@ -85,7 +85,13 @@ struct HarnessContext : rendering::Context {
 // reference code from the device's Philox stream, or from a scripted list.
 struct StreamSampler : prelude::Sampler {
   philox_stream stream;
-  result_type operator()() { return static_cast<result_type>(philox_stream_next(&stream)); }
+  bool camera = true;  // camera vertex: sequential slots; surface vertex: BSDF-sampling slots
+  result_type operator()() {
+    return static_cast<result_type>(camera ? philox_stream_next_camera(&stream)
+                                           : philox_stream_next_bsdf(&stream));
+  }
+  // The Russian-roulette uniform has a fixed slot of its own (philox_stream.h).
+  rendering::real_type RussianRoulette() { return philox_stream_rr(&stream); }
 };
 
 struct ScriptedSampler : prelude::Sampler {
@@ -389,6 +395,7 @@ int ref_render_stream(void* handle, uint32_t w, uint32_t h, float film_w, float 
           double sum[3] = {0, 0, 0};
           for (uint64_t s = sample_begin; s < sample_begin + sample_count; s++) {
             philox_stream_reset(&sampler.stream, seed, x + y * w, s);
+            sampler.camera = true;
             auto generated = scene.GenerateEyeRay(sensor.Bind(prelude::Pixel(x, y)), sampler);
             auto& object = std::get<rendering::ObjectPointer>(generated);
             auto& leading = std::get<rendering::Leading<RGB>>(generated);
@@ -397,6 +404,8 @@ int ref_render_stream(void* handle, uint32_t w, uint32_t h, float film_w, float 
             auto weight = leading.Weight();
             for (uint32_t depth = 1;; depth++) {
               rendering::Hit hit;
+              philox_stream_begin_vertex(&sampler.stream, depth);
+              sampler.camera = false;
               std::tie(object, hit) = scene.Cast(ray);
               rays++;
               if (!hit) break;
@@ -404,7 +413,7 @@ int ref_render_stream(void* handle, uint32_t w, uint32_t h, float film_w, float 
               const auto scatter =
                   scene.SampleLight(object, hit.Normal(), -ray.Direction(), sampler);
               const auto p = std::min<rendering::real_type>(kRussianRoulette, Max(scatter.Weight()));
-              if (prelude::Uniform<rendering::real_type>(sampler) >= p) break;
+              if (sampler.RussianRoulette() >= p) break;
               if (depth >= max_depth) {
                 truncated++;
                 break;
