@@ -276,7 +276,7 @@ int amber_cuda_create(amber_cuda_ctx** out, int device) {
   if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (err == cudaSuccess) err = cudaEventCreate(&ctx->ev_begin);
   if (err == cudaSuccess) err = cudaEventCreate(&ctx->ev_end);
-  if (err == cudaSuccess) err = cudaMallocHost(&ctx->h_ctl, sizeof(Control));
+  if (err == cudaSuccess) err = cudaMallocHost(&ctx->h_ctl, 2 * sizeof(Control));  // two poll slots
   if (err == cudaSuccess) err = ctx->d_ctl.resize(1);
   if (err == cudaSuccess) err = cudaMemsetAsync(ctx->d_ctl.ptr, 0, sizeof(Control), ctx->stream);
   if (err != cudaSuccess) {

@@ -1,0 +1,30 @@
+#!/usr/bin/env python
+"""Short Cornell render through the C ABI, for `ncu --set full` captures (keeps the
+bench's scene, frame size, estimator and pool; only the sample count is small)."""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from amber_b200 import capi, cornel_box, cornel_mesh  # noqa: E402
+from amber_b200.render import Device, Sensor  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--spp", type=int, default=16)
+ap.add_argument("--size", type=int, default=1024)
+ap.add_argument("--estimator", default="nee", choices=["nee", "reference"])
+ap.add_argument("--mesh", type=int, default=-1, help="icosphere subdivisions (config 4); -1 = built-in Cornell box")
+ap.add_argument("--pool", type=int, default=0)
+args = ap.parse_args()
+
+scene = cornel_box() if args.mesh < 0 else cornel_mesh(args.mesh)
+with Device(0) as dev:
+    dev.upload_scene(scene)
+    dev.set_sensor(Sensor(args.size, args.size))
+    est = capi.ESTIMATOR_NEE if args.estimator == "nee" else capi.ESTIMATOR_REFERENCE
+    dev.render(0, args.spp, seed=1, max_depth=32, estimator=est, pool_paths=args.pool)
+    s = dev.stats()
+    rays = s["closest_rays"] + s["shadow_rays"]
+    print(f"{rays / s['last_render_ms'] / 1e3:.1f} Mrays/s, {s['paths'] / s['last_render_ms'] / 1e3:.1f} Mpaths/s, "
+          f"{s['last_render_ms']:.2f} ms, launches {s['kernel_launches']}, accel {s['accel']}")
