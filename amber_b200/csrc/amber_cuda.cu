@@ -81,6 +81,7 @@ struct amber_cuda_ctx {
   DeviceBuffer<float4> d_spheres;
   DeviceBuffer<int32_t> d_tri_material, d_sphere_material, d_internal_to_prim;
   DeviceBuffer<MaterialDev> d_materials;
+  DeviceBuffer<uint8_t> d_prim_class;
   DeviceBuffer<LightDev> d_lights;
   DeviceBuffer<float4> d_bvh_nodes;
   uint32_t bvh_nodes = 0;
@@ -94,7 +95,7 @@ struct amber_cuda_ctx {
   PathPool pool{};
   DeviceBuffer<float4> d_ray, d_state, d_shadow;
   DeviceBuffer<float2> d_hit;
-  DeviceBuffer<uint32_t> d_q_new;
+  DeviceBuffer<uint32_t> d_q_new, d_q_shadow;
   DeviceBuffer<Control> d_ctl;
   Control* h_ctl = nullptr;  // pinned
 
@@ -235,12 +236,14 @@ int ensure_pool(amber_cuda_ctx* ctx, uint32_t slots) {
   CUDA_TRY(ctx, ctx->d_state.resize(2 * static_cast<size_t>(slots)));
   CUDA_TRY(ctx, ctx->d_hit.resize(slots));
   CUDA_TRY(ctx, ctx->d_q_new.resize(slots));
-  CUDA_TRY(ctx, ctx->d_shadow.resize(3 * static_cast<size_t>(slots)));
+  CUDA_TRY(ctx, ctx->d_q_shadow.resize(slots));
+  CUDA_TRY(ctx, ctx->d_shadow.resize(2 * static_cast<size_t>(slots)));
   ctx->pool.ray = ctx->d_ray.ptr;
   ctx->pool.state = ctx->d_state.ptr;
   ctx->pool.hit = ctx->d_hit.ptr;
   ctx->pool.q_new = ctx->d_q_new.ptr;
   ctx->pool.shadow = ctx->d_shadow.ptr;
+  ctx->pool.q_shadow = ctx->d_q_shadow.ptr;
   ctx->pool.n_slots = slots;
   return AMBER_CUDA_OK;
 }
@@ -298,7 +301,7 @@ int amber_cuda_destroy(amber_cuda_ctx* ctx) {
   ctx->d_materials.release(); ctx->d_lights.release(); ctx->d_bvh_nodes.release();
   ctx->d_film.release(); ctx->d_resolved.release();
   ctx->d_ray.release(); ctx->d_state.release(); ctx->d_hit.release(); ctx->d_shadow.release();
-  ctx->d_q_new.release(); ctx->d_ctl.release();
+  ctx->d_q_new.release(); ctx->d_q_shadow.release(); ctx->d_ctl.release(); ctx->d_prim_class.release();
   for (auto& b : ctx->d_scratch_f) b.release();
   for (auto& b : ctx->d_scratch_i) b.release();
   for (auto& b : ctx->d_scratch_4) b.release();
@@ -381,6 +384,12 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
     ctx->internal_to_prim[n_tris + k] = static_cast<int32_t>(sphere_ids[k]);
   }
 
+  // hit class of every primitive (internal order): what `shade` sorts a tile by
+  std::vector<uint8_t> prim_class(n_tris + n_spheres);
+  for (size_t k = 0; k < n_tris; k++) prim_class[k] = static_cast<uint8_t>(materials[tri_material[k]].kind * 2);
+  for (size_t k = 0; k < n_spheres; k++)
+    prim_class[n_tris + k] = static_cast<uint8_t>(materials[sphere_material[k]].kind * 2 + 1);
+
   // ---- lights: emitting triangles, LightSet::LightSet (light_set.h:61-81) -------
   struct HostLight {
     size_t tri;
@@ -445,6 +454,7 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   CUDA_TRY(ctx, ctx->d_internal_to_prim.upload(ctx->internal_to_prim, ctx->stream));
   CUDA_TRY(ctx, ctx->d_materials.upload(materials, ctx->stream));
   CUDA_TRY(ctx, ctx->d_lights.upload(lights, ctx->stream));
+  CUDA_TRY(ctx, ctx->d_prim_class.upload(prim_class, ctx->stream));
   if (use_bvh) {
     std::vector<float4> nodes(bvh.nodes.size() / 4);
     std::memcpy(nodes.data(), bvh.nodes.data(), bvh.nodes.size() * sizeof(float));
@@ -459,6 +469,7 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   view.sphere_material = ctx->d_sphere_material.ptr;
   view.materials = ctx->d_materials.ptr;
   view.lights = ctx->d_lights.ptr;
+  view.prim_class = ctx->d_prim_class.ptr;
   view.n_tris = static_cast<int32_t>(n_tris);
   view.n_spheres = static_cast<int32_t>(n_spheres);
   view.n_lights = static_cast<int32_t>(lights.size());
@@ -542,6 +553,7 @@ struct KernelTimer {
 template <class Accel>
 int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dynamic_smem) {
   const unsigned int grid = blocks_for(args.pool.n_slots);
+  const unsigned int shade_grid = blocks_for(args.pool.n_slots, kShadeTile);
   cudaStream_t stream = ctx->stream;
   KernelTimer timer;
   const bool profile = ctx->profiling;
@@ -568,7 +580,7 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
       timed(0, [&] { raygen_kernel<<<grid, kBlock, 0, stream>>>(args); });
       bookkeep_kernel<<<1, 1, 0, stream>>>(args.ctl);
       timed(1, [&] { extend_kernel<Accel><<<grid, kBlock, dynamic_smem, stream>>>(args); });
-      timed(2, [&] { shade_kernel<<<grid, kBlock, 0, stream>>>(args); });
+      timed(2, [&] { shade_kernel<<<shade_grid, kBlock, 0, stream>>>(args); });
       if (nee) timed(3, [&] { connect_kernel<Accel><<<grid, kBlock, dynamic_smem, stream>>>(args); });
       ctx->stats.kernel_launches += nee ? 5 : 4;
       extend_launches++;

@@ -5,4 +5,4 @@ cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 $NVCC -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
   -Xcompiler -fPIC,-Wall,-Wno-unused-function,-pthread -shared -cudart static \
-  ${AMBER_NVCC_FLAGS} -o libamber_cuda.so amber_cuda.cu -lpthread
+  ${AMBER_NVCC_FLAGS} -o ${AMBER_OUT:-libamber_cuda.so} amber_cuda.cu -lpthread

@@ -8,16 +8,19 @@
 //   shade    : emission, [light sampling -> shadow queue], BSDF sample, Russian
 //              roulette, next ray in place      (algorithm_pt.cc:137-157)
 //   connect  : any-hit for the shadow queue + film add
-// Terminated slots are compacted into `q_new`, shadow rays into the shadow queue:
-// __ballot_sync/__popc inside the warp, one smem scan and ONE global atomic per block.
+// `shade` sorts each 2048-slot tile by hit class in shared memory so that a warp shades one
+// material; freed slots are compacted into `q_new` and slots with a pending shadow ray into
+// `q_shadow`: per-thread bit masks, warp shuffles, one smem scan and ONE global atomic per
+// queue per tile.
 //
 // Layout in HBM (all float4 / 16-byte accesses):
-//   ray[2i], ray[2i+1]     origin xyz + live flag, direction xyz             32 B per slot
-//   state[2i], state[2i+1] throughput rgb ; (pixel, sample, depth|flags, -)  32 B per slot
-//   hit[i]                 (t, primitive)                                     8 B per slot
-//   shadow[3j..3j+2]       origin + t_max, direction + pixel, contribution   48 B per entry
-// A slot's ray and state each fill exactly one 32-byte sector, so the scattered writes of
-// raygen (slots arrive in queue order) never touch a partial sector.
+//   ray[2i], ray[2i+1]       origin xyz + live flag, direction xyz             32 B per slot
+//   state[2i], state[2i+1]   throughput rgb ; (pixel, sample, depth|flags, -)  32 B per slot
+//   hit[i]                   (t, primitive | -1 miss | -2 empty slot)           8 B per slot
+//   shadow[2i], shadow[2i+1] direction + t_max ; contribution rgb + pixel      32 B per slot
+//   q_new[j], q_shadow[j]    slot ids                                           4 B per entry
+// A slot's ray, state and shadow record each fill exactly one 32-byte sector, so the
+// permuted accesses of raygen / shade / connect never touch a partial sector.
 #pragma once
 
 #include "intersect.cuh"
@@ -43,8 +46,9 @@ struct PathPool {
   float4* ray;      // [2 * n_slots]
   float4* state;    // [2 * n_slots]
   float2* hit;      // [n_slots]
-  uint32_t* q_new;  // [n_slots]
-  float4* shadow;   // [3 * n_slots]
+  uint32_t* q_new;  // [n_slots] slots freed by the last shade
+  float4* shadow;   // [2 * n_slots] per-slot shadow ray: direction + t_max ; contribution + pixel
+  uint32_t* q_shadow;  // [n_slots] slots whose shadow ray is pending
   uint32_t n_slots;
 };
 
@@ -75,35 +79,6 @@ struct ScriptedRng {
     return v;
   }
 };
-
-// ---------------------------------------------------------------------------------
-// Block-aggregated queue slot allocation: returns this thread's index in the queue
-// (valid only if `want`).  Warp ballot + popc, smem scan over the warps, one atomicAdd
-// per block.
-__device__ __forceinline__ uint32_t queue_alloc(bool want, unsigned int* counter, uint32_t* smem /*[kBlock/32]*/) {
-  const unsigned int ballot = __ballot_sync(0xffffffffu, want);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (lane == 0) smem[warp] = __popc(ballot);
-  __syncthreads();
-  if (warp == 0) {
-    const uint32_t count = lane < kBlock / 32 ? smem[lane] : 0u;
-    uint32_t scan = count;
-#pragma unroll
-    for (int delta = 1; delta < kBlock / 32; delta <<= 1) {
-      const uint32_t up = __shfl_up_sync(0xffffffffu, scan, delta);
-      if (lane >= delta) scan += up;
-    }
-    const uint32_t total = __shfl_sync(0xffffffffu, scan, kBlock / 32 - 1);
-    uint32_t base = 0;
-    if (lane == 0 && total) base = atomicAdd(counter, total);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (lane < kBlock / 32) smem[lane] = base + scan - count;
-  }
-  __syncthreads();
-  const uint32_t index = smem[warp] + __popc(ballot & ((1u << lane) - 1u));
-  __syncthreads();  // smem is reused by the next call
-  return index;
-}
 
 // ---------------------------------------------------------------------------------
 // Camera ray: PixelBound::Uniform (src/amber/rendering/sensor.cc:111-120) +
@@ -216,7 +191,10 @@ __global__ void __launch_bounds__(kBlock) extend_kernel(const RenderArgs args) {
   if (i >= args.pool.n_slots) return;
   const float4* r = args.pool.ray + 2 * static_cast<size_t>(i);
   const float4 o = r[0];
-  if (o.w == 0.0f) return;
+  if (o.w == 0.0f) {  // no path in this slot: tell `shade` so (it sorts the tile by hit class)
+    args.pool.hit[i] = make_float2(CUDART_NAN_F, __int_as_float(-2));
+    return;
+  }
   const float4 d = r[1];
   Ray ray;
   ray.o = v3(o);
@@ -284,7 +262,7 @@ __device__ __forceinline__ MaterialDev load_material(const SceneView& scene, int
 }
 
 struct ShadowRay {
-  float3 o, d;
+  float3 d;
   float t_max;
   float3 contribution;
 };
@@ -323,7 +301,6 @@ __device__ __forceinline__ bool sample_direct(const SceneView& scene, const Mate
   const float g = fabsf(cos_y * dot(wi, n)) / dist2;
   shadow.contribution = throughput * v3(le) * f * g;
   if (!(max3(shadow.contribution) > 0.0f)) return false;
-  shadow.o = x;
   shadow.d = wi;
   shadow.t_max = dist2 * inv_dist * (1.0f - 1e-4f);
   return true;
@@ -333,123 +310,229 @@ __device__ __forceinline__ void film_add(float4* film, uint32_t pixel, float3 va
   atomicAdd(&film[pixel], make_float4(value.x, value.y, value.z, 0.0f));
 }
 
-__global__ void __launch_bounds__(kBlock) shade_kernel(const RenderArgs args) {
-  __shared__ uint32_t smem[kBlock / 32];
-  __shared__ unsigned int block_live, block_alive;
-  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+// ---------------------------------------------------------------------------------
+// shade.  One block owns a TILE of kShadeTile consecutive path slots and works in three
+// phases:
+//   1. classify: every slot's hit record -> class = (material kind, triangle|sphere),
+//      or MISS / DEAD; a counting sort of the tile's slot indices by class in shared
+//      memory (warp match + one smem atomic per distinct class per warp).
+//   2. shade in sorted order: thread t of round r takes sorted[r * kBlock + t], so a
+//      warp runs ONE material's code on 32 lanes instead of six materials' code on a
+//      few lanes each.  Ray / state records are 32-byte sectors, so the permuted
+//      accesses inside the tile's 64 KB window still move whole sectors.
+//   3. queues: each thread has one bit per round for "slot freed" and "shadow ray
+//      emitted"; one block scan and ONE global atomic per queue per tile hand out the
+//      q_new / q_shadow ranges.
+// The shadow ray itself stays in the slot (pool.shadow[2 slot..]); its origin is the
+// vertex position, which phase 2 has just written to ray[2 slot].
+#ifndef AMBER_SHADE_MIN_BLOCKS
+#define AMBER_SHADE_MIN_BLOCKS 4
+#endif
+#ifndef AMBER_SHADE_ROUNDS
+#define AMBER_SHADE_ROUNDS 8
+#endif
+constexpr int kShadeRounds = AMBER_SHADE_ROUNDS;
+constexpr int kShadeTile = kShadeRounds * kBlock;
+constexpr int kClassMiss = 14;  // hit.prim == -1: the path left the scene, algorithm_pt.cc:140-142
+constexpr int kClassDead = 15;  // hit.prim == -2: slot holds no path
+constexpr int32_t kPrimMiss = -1, kPrimDead = -2;
+
+__global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(const RenderArgs args) {
+  __shared__ uint16_t sorted[kShadeTile];
+  __shared__ uint32_t class_count[16], class_offset[16];
+  __shared__ uint32_t warp_scan[kBlock / 32];
+  __shared__ uint32_t queue_base[2];
   const PathPool& pool = args.pool;
-  if (threadIdx.x == 0) {
-    block_live = 0;
-    block_alive = 0;
-  }
-  bool live = false, terminated = false, has_shadow = false;
-  ShadowRay shadow;
-  uint32_t pixel = 0;
-  if (i < pool.n_slots) {
-    float4* ray_slot = pool.ray + 2 * static_cast<size_t>(i);
-    const float4 o4 = ray_slot[0];
-    live = o4.w != 0.0f;
-    if (live) {
-      const float2 h2 = pool.hit[i];
-      HitRecord hit;
-      hit.t = h2.x;
-      hit.prim = __float_as_int(h2.y);
-      if (hit.prim < 0) {
-        terminated = true;  // algorithm_pt.cc:140-142
-      } else {
-        const float4 d4 = ray_slot[1];
-        float4* state_slot = pool.state + 2 * static_cast<size_t>(i);
-        const float4 t4 = state_slot[0];
-        const float4 m4 = state_slot[1];
-        Ray ray;
-        ray.o = v3(o4);
-        ray.d = v3(d4);
-        pixel = __float_as_uint(m4.x);
-        const uint32_t sample = __float_as_uint(m4.y);
-        const uint32_t flags = __float_as_uint(m4.z);
-        const uint32_t depth = (flags & kDepthMask) + 1u;  // this is the depth-th surface vertex
-        float3 throughput = v3(t4);
-        float3 x, n;
-        int material_index;
-        surface_point(args.scene, ray, hit, x, n, material_index);
-        const MaterialDev m = load_material(args.scene, material_index);
-        const float3 wo = -ray.d;
-        VertexRng rng;
-        rng.init(args.seed, pixel, sample, depth);  // one Philox block, same place for every lane
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t tile_base = blockIdx.x * kShadeTile;
+  const uint32_t lane_lt = (1u << lane) - 1u;
+  if (tid < 16) class_count[tid] = 0;
+  __syncthreads();
 
-        // emission, algorithm_pt.cc:144
-        if (m.kind == 4) {
-          const bool sampled_by_nee = args.estimator == 1 && hit.prim < args.scene.n_tris;
-          if (!sampled_by_nee || (flags & kFlagCountEmission)) {
-            const float3 le = emitted_radiance(m, n, wo);
-            if (le.x > 0.0f || le.y > 0.0f || le.z > 0.0f) film_add(args.film, pixel, throughput * le);
-          }
-        }
-        const bool connect = args.estimator == 1 && m.nee && args.scene.n_lights > 0;
-        if (connect) {
-          float lu, lv;
-          rng.light_point(lu, lv);
-          has_shadow = sample_direct(args.scene, m, x, n, wo, throughput, rng.light_choice(), lu, lv, shadow);
-        }
-
-        // BSDF sample + Russian roulette, algorithm_pt.cc:145-156
-        const Scatter scatter = sample_light(m, n, wo, rng);
-        const float p = fminf(kRussianRoulette, max3(scatter.weight));
-        if (scatter.capped) atomicAdd(&args.ctl->phong_capped, 1ull);
-        if (!(rng.rr() < p)) {
-          terminated = true;
-        } else if (depth >= args.max_depth) {
-          terminated = true;
-          atomicAdd(&args.ctl->truncated, 1ull);
-        } else {
-          const float inv_p = 1.0f / p;
-          throughput = throughput * (inv_p * scatter.weight);
-          ray_slot[0] = make_float4(x.x, x.y, x.z, 1.0f);
-          ray_slot[1] = make_float4(scatter.dir.x, scatter.dir.y, scatter.dir.z, 0.0f);
-          state_slot[0] = make_float4(throughput.x, throughput.y, throughput.z, 0.0f);
-          state_slot[1] = make_float4(m4.x, m4.y, __uint_as_float(depth | (connect ? 0u : kFlagCountEmission)), 0.0f);
-        }
-      }
+  // ---- phase 1: classify + counting sort ------------------------------------------
+  uint32_t keys[kShadeRounds / 2];  // two (class:4 | rank:12) halves per register
+#pragma unroll
+  for (int r = 0; r < kShadeRounds; r++) {
+    const uint32_t i = tile_base + r * kBlock + tid;
+    int cls = kClassDead;
+    if (i < pool.n_slots) {
+      const int prim = __float_as_int(pool.hit[i].y);
+      cls = prim >= 0 ? __ldg(args.scene.prim_class + prim) : (prim == kPrimMiss ? kClassMiss : kClassDead);
     }
-  }
-  // queues: freed slots -> q_new, shadow rays -> shadow queue; counters per block
-  const uint32_t new_index = queue_alloc(terminated, &args.ctl->n_new, smem);
-  if (terminated) pool.q_new[new_index] = i;
-  const uint32_t shadow_index = queue_alloc(has_shadow, &args.ctl->n_shadow, smem);
-  if (has_shadow) {
-    float4* out = pool.shadow + 3 * static_cast<size_t>(shadow_index);
-    out[0] = make_float4(shadow.o.x, shadow.o.y, shadow.o.z, shadow.t_max);
-    out[1] = make_float4(shadow.d.x, shadow.d.y, shadow.d.z, __uint_as_float(pixel));
-    out[2] = make_float4(shadow.contribution.x, shadow.contribution.y, shadow.contribution.z, 0.0f);
-  }
-  // statistics: rays extended this step, survivors (queue_alloc's barriers order the init above)
-  const unsigned int live_ballot = __ballot_sync(0xffffffffu, live);
-  const unsigned int alive_ballot = __ballot_sync(0xffffffffu, live && !terminated);
-  if ((threadIdx.x & 31) == 0) {
-    atomicAdd(&block_live, __popc(live_ballot));
-    atomicAdd(&block_alive, __popc(alive_ballot));
+    const uint32_t peers = __match_any_sync(0xffffffffu, cls);
+    const int leader = __ffs(peers) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(&class_count[cls], __popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    const uint32_t key = (static_cast<uint32_t>(cls) << 12) | (base + __popc(peers & lane_lt));
+    if (r & 1) keys[r >> 1] |= key << 16; else keys[r >> 1] = key;
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    if (block_live) atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(block_live));
-    if (block_alive) atomicAdd(&args.ctl->n_alive, block_alive);
+  if (warp == 0) {
+    const uint32_t count = lane < 16 ? class_count[lane] : 0u;
+    uint32_t scan = count;
+#pragma unroll
+    for (int delta = 1; delta < 16; delta <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xffffffffu, scan, delta);
+      if (lane >= delta) scan += up;
+    }
+    if (lane < 16) class_offset[lane] = scan - count;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < kShadeRounds; r++) {
+    const uint32_t key = (keys[r >> 1] >> ((r & 1) * 16)) & 0xffffu;
+    sorted[class_offset[key >> 12] + (key & 0xfffu)] = static_cast<uint16_t>(r * kBlock + tid);
+  }
+  __syncthreads();
+  const uint32_t n_hit = class_offset[kClassMiss];   // entries [0, n_hit): surface vertices
+  const uint32_t n_live = class_offset[kClassDead];  // entries [n_hit, n_live): misses
+
+  // ---- phase 2: shade in class order ------------------------------------------------
+  uint32_t freed_mask = 0, shadow_mask = 0;
+#pragma unroll 1
+  for (int r = 0; r < kShadeRounds; r++) {
+    const uint32_t j = r * kBlock + tid;
+    if (j >= n_live) break;
+    if (j >= n_hit) {  // miss: the slot is free again
+      freed_mask |= 1u << r;
+      continue;
+    }
+    const uint32_t slot = tile_base + sorted[j];
+    float4* ray_slot = pool.ray + 2 * static_cast<size_t>(slot);
+    float4* state_slot = pool.state + 2 * static_cast<size_t>(slot);
+    const float4 o4 = ray_slot[0];
+    const float4 d4 = ray_slot[1];
+    const float4 t4 = state_slot[0];
+    const float4 m4 = state_slot[1];
+    const float2 h2 = pool.hit[slot];
+    HitRecord hit;
+    hit.t = h2.x;
+    hit.prim = __float_as_int(h2.y);
+    Ray ray;
+    ray.o = v3(o4);
+    ray.d = v3(d4);
+    const uint32_t pixel = __float_as_uint(m4.x);
+    const uint32_t sample = __float_as_uint(m4.y);
+    const uint32_t flags = __float_as_uint(m4.z);
+    const uint32_t depth = (flags & kDepthMask) + 1u;  // this is the depth-th surface vertex
+    float3 throughput = v3(t4);
+    float3 x, n;
+    int material_index;
+    surface_point(args.scene, ray, hit, x, n, material_index);
+    const MaterialDev m = load_material(args.scene, material_index);
+    const float3 wo = -ray.d;
+    VertexRng rng;
+    rng.init(args.seed, pixel, sample, depth);  // one Philox block, same place for every lane
+
+    // emission, algorithm_pt.cc:144
+    if (m.kind == 4) {
+      const bool sampled_by_nee = args.estimator == 1 && hit.prim < args.scene.n_tris;
+      if (!sampled_by_nee || (flags & kFlagCountEmission)) {
+        const float3 le = emitted_radiance(m, n, wo);
+        if (le.x > 0.0f || le.y > 0.0f || le.z > 0.0f) film_add(args.film, pixel, throughput * le);
+      }
+    }
+    const bool connect = args.estimator == 1 && m.nee && args.scene.n_lights > 0;
+    if (connect) {
+      float lu, lv;
+      rng.light_point(lu, lv);
+      ShadowRay shadow;
+      if (sample_direct(args.scene, m, x, n, wo, throughput, rng.light_choice(), lu, lv, shadow)) {
+        shadow_mask |= 1u << r;
+        float4* out = pool.shadow + 2 * static_cast<size_t>(slot);
+        out[0] = make_float4(shadow.d.x, shadow.d.y, shadow.d.z, shadow.t_max);
+        out[1] = make_float4(shadow.contribution.x, shadow.contribution.y, shadow.contribution.z,
+                             __uint_as_float(pixel));
+      }
+    }
+
+    // BSDF sample + Russian roulette, algorithm_pt.cc:145-156
+    const Scatter scatter = sample_light(m, n, wo, rng);
+    const float p = fminf(kRussianRoulette, max3(scatter.weight));
+    if (scatter.capped) atomicAdd(&args.ctl->phong_capped, 1ull);
+    bool terminated = false;
+    if (!(rng.rr() < p)) {
+      terminated = true;
+    } else if (depth >= args.max_depth) {
+      terminated = true;
+      atomicAdd(&args.ctl->truncated, 1ull);
+    }
+    if (terminated) {
+      freed_mask |= 1u << r;
+      // the vertex stays readable for `connect` (shadow origin); w = 0 marks the slot free
+      ray_slot[0] = make_float4(x.x, x.y, x.z, 0.0f);
+    } else {
+      const float inv_p = 1.0f / p;
+      throughput = throughput * (inv_p * scatter.weight);
+      ray_slot[0] = make_float4(x.x, x.y, x.z, 1.0f);
+      ray_slot[1] = make_float4(scatter.dir.x, scatter.dir.y, scatter.dir.z, 0.0f);
+      state_slot[0] = make_float4(throughput.x, throughput.y, throughput.z, 0.0f);
+      state_slot[1] = make_float4(m4.x, m4.y, __uint_as_float(depth | (connect ? 0u : kFlagCountEmission)), 0.0f);
+    }
+  }
+
+  // ---- phase 3: queue ranges, one atomic per queue per tile --------------------------
+  const uint32_t mine = static_cast<uint32_t>(__popc(freed_mask)) | (static_cast<uint32_t>(__popc(shadow_mask)) << 16);
+  uint32_t scan = mine;  // two 16-bit inclusive scans side by side (tile size < 65536)
+#pragma unroll
+  for (int delta = 1; delta < 32; delta <<= 1) {
+    const uint32_t up = __shfl_up_sync(0xffffffffu, scan, delta);
+    if (lane >= delta) scan += up;
+  }
+  if (lane == 31) warp_scan[warp] = scan;
+  __syncthreads();
+  if (warp == 0) {
+    const uint32_t total = lane < kBlock / 32 ? warp_scan[lane] : 0u;
+    uint32_t wscan = total;
+#pragma unroll
+    for (int delta = 1; delta < kBlock / 32; delta <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xffffffffu, wscan, delta);
+      if (lane >= delta) wscan += up;
+    }
+    if (lane < kBlock / 32) warp_scan[lane] = wscan - total;
+    if (lane == kBlock / 32 - 1) {
+      const uint32_t n_freed = wscan & 0xffffu, n_shadow = wscan >> 16;
+      queue_base[0] = n_freed ? atomicAdd(&args.ctl->n_new, n_freed) : 0u;
+      queue_base[1] = n_shadow ? atomicAdd(&args.ctl->n_shadow, n_shadow) : 0u;
+      const uint32_t live = n_live;
+      if (live) atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(live));
+      if (live > n_freed) atomicAdd(&args.ctl->n_alive, live - n_freed);
+    }
+  }
+  __syncthreads();
+  const uint32_t before = warp_scan[warp] + scan - mine;
+  uint32_t freed_at = queue_base[0] + (before & 0xffffu);
+  uint32_t shadow_at = queue_base[1] + (before >> 16);
+  while (freed_mask) {
+    const int r = __ffs(freed_mask) - 1;
+    freed_mask &= freed_mask - 1u;
+    pool.q_new[freed_at++] = tile_base + sorted[r * kBlock + tid];
+  }
+  while (shadow_mask) {
+    const int r = __ffs(shadow_mask) - 1;
+    shadow_mask &= shadow_mask - 1u;
+    pool.q_shadow[shadow_at++] = tile_base + sorted[r * kBlock + tid];
   }
 }
 
 // ---------------------------------------------------------------------------------
+// connect: any-hit along the shadow rays queued by `shade`; unoccluded ones add their
+// contribution to the film.  Queue entry = slot id; the slot holds the ray.
 template <class Accel>
 __global__ void __launch_bounds__(kBlock) connect_kernel(const RenderArgs args) {
   const uint32_t j = blockIdx.x * kBlock + threadIdx.x;
   if (j >= args.ctl->n_shadow) return;
-  const float4* in = args.pool.shadow + 3 * static_cast<size_t>(j);
-  const float4 o = in[0];
-  const float4 d = in[1];
+  const uint32_t slot = args.pool.q_shadow[j];
+  const float4 o = args.pool.ray[2 * static_cast<size_t>(slot)];
+  const float4* in = args.pool.shadow + 2 * static_cast<size_t>(slot);
+  const float4 d = in[0];
   Ray ray;
   ray.o = v3(o);
   ray.d = v3(d);
-  if (Accel::occluded(args.scene, ray, o.w)) return;
-  const float4 c = in[2];
-  film_add(args.film, __float_as_uint(d.w), v3(c));
+  if (Accel::occluded(args.scene, ray, d.w)) return;
+  const float4 c = in[1];
+  film_add(args.film, __float_as_uint(c.w), v3(c));
 }
 
 // Accumulator::Mean (include/amber/prelude/accumulator.h:88-95): film / samples,

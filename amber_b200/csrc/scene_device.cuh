@@ -99,6 +99,7 @@ struct SceneView {
   const int32_t* sphere_material; // [n_spheres]
   const MaterialDev* materials;
   const LightDev* lights;         // sorted by power, cumulative power in v0.w
+  const uint8_t* prim_class;      // [n_tris + n_spheres] material kind * 2 + (sphere ? 1 : 0)
   int32_t n_tris, n_spheres, n_lights;
   float total_power;
   // WideBvh only

@@ -16,15 +16,25 @@ ap.add_argument("--size", type=int, default=1024)
 ap.add_argument("--estimator", default="nee", choices=["nee", "reference"])
 ap.add_argument("--mesh", type=int, default=-1, help="icosphere subdivisions (config 4); -1 = built-in Cornell box")
 ap.add_argument("--pool", type=int, default=0)
+ap.add_argument("--lib", default=None, help="alternative libamber_cuda.so (build variants)")
+ap.add_argument("--repeat", type=int, default=1)
+ap.add_argument("--profile", action="store_true", help="per-kernel CUDA-event times")
 args = ap.parse_args()
 
 scene = cornel_box() if args.mesh < 0 else cornel_mesh(args.mesh)
-with Device(0) as dev:
+with Device(0, lib_path=args.lib) as dev:
     dev.upload_scene(scene)
     dev.set_sensor(Sensor(args.size, args.size))
     est = capi.ESTIMATOR_NEE if args.estimator == "nee" else capi.ESTIMATOR_REFERENCE
-    dev.render(0, args.spp, seed=1, max_depth=32, estimator=est, pool_paths=args.pool)
+    dev.set_profiling(args.profile)
+    for _ in range(args.repeat):
+        dev.film_clear()
+        dev.render(0, args.spp, seed=1, max_depth=32, estimator=est, pool_paths=args.pool)
     s = dev.stats()
     rays = s["closest_rays"] + s["shadow_rays"]
     print(f"{rays / s['last_render_ms'] / 1e3:.1f} Mrays/s, {s['paths'] / s['last_render_ms'] / 1e3:.1f} Mpaths/s, "
           f"{s['last_render_ms']:.2f} ms, launches {s['kernel_launches']}, accel {s['accel']}")
+    if args.profile:
+        n = max(1, s["extend_launches"])
+        print("per launch (us): " + ", ".join(f"{k} {s[k + '_ms'] / n * 1e3:.1f}" for k in ("raygen", "extend", "shade", "connect"))
+              + f"; wavefront iterations {n}, closest rays/iteration {s['closest_rays'] / n:.0f}, shadow rays/iteration {s['shadow_rays'] / n:.0f}")
