@@ -169,6 +169,114 @@ void make_triangle(const float* v, TriIsect& isect, TriShade& shade) {
   isect.nv_v0z = make_float4((float)nv[0], (float)nv[1], (float)nv[2], v0.z);
 }
 
+
+// Batches the triangles of a small scene by supporting plane for the constant-memory list.
+// `tri_ids` (creation-order ids) is permuted so that each group is contiguous: groups in order
+// of their first member; inside a group the parallelogram pairs (earlier triangle first, so a
+// hit on the shared diagonal goes to it, as in a creation-order scan), then the lone
+// triangles.  All geometry is evaluated in double from the float vertices.
+void group_by_plane(const amber_cuda_primitive* prims, std::vector<uint32_t>& tri_ids,
+                    std::vector<PlaneGroup>& groups, std::vector<PlaneEntry>& entries) {
+  struct D3 { double x, y, z; };
+  auto sub = [](D3 a, D3 b) { return D3{a.x - b.x, a.y - b.y, a.z - b.z}; };
+  auto cross = [](D3 a, D3 b) { return D3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; };
+  auto dot = [](D3 a, D3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; };
+  auto vertex = [&](uint32_t id, int k) {
+    const float* d = prims[id].data + 3 * k;
+    return D3{d[0], d[1], d[2]};
+  };
+  struct Group { D3 anchor, unit_n, n; double scale; std::vector<uint32_t> members; };
+  std::vector<Group> found;
+  for (uint32_t id : tri_ids) {
+    const D3 v0 = vertex(id, 0), v1 = vertex(id, 1), v2 = vertex(id, 2);
+    const D3 n = cross(sub(v1, v0), sub(v2, v0));
+    const double len = std::sqrt(dot(n, n));
+    int home = -1;
+    if (len > 0) {
+      const D3 unit{n.x / len, n.y / len, n.z / len};
+      for (size_t g = 0; g < found.size() && home < 0; g++) {
+        const Group& G = found[g];
+        const D3 c = cross(unit, G.unit_n);
+        if (dot(c, c) > 1e-14) continue;  // not parallel
+        const double tol = 1e-7 * G.scale;
+        if (std::fabs(dot(G.unit_n, sub(v0, G.anchor))) <= tol && std::fabs(dot(G.unit_n, sub(v1, G.anchor))) <= tol &&
+            std::fabs(dot(G.unit_n, sub(v2, G.anchor))) <= tol)
+          home = static_cast<int>(g);
+      }
+      if (home < 0) {
+        const double scale = std::max({1.0, std::fabs(v0.x), std::fabs(v0.y), std::fabs(v0.z)});
+        found.push_back({v0, unit, n, scale, {}});
+        home = static_cast<int>(found.size()) - 1;
+      }
+    } else {  // degenerate triangle: a group of its own; its NaN plane rejects every ray, as the
+      found.push_back({v0, D3{0, 0, 0}, n, 1.0, {}});  // reference's det == 0 does (hit.h:90-94)
+      home = static_cast<int>(found.size()) - 1;
+    }
+    found[home].members.push_back(id);
+  }
+  auto same = [](D3 a, D3 b) { return a.x == b.x && a.y == b.y && a.z == b.z; };
+  auto entry_for = [&](D3 corner, D3 e1, D3 e2, D3 anchor) {
+    const D3 n = cross(e1, e2);
+    const double nn = dot(n, n);
+    D3 nu = cross(e2, n), nv = cross(n, e1);
+    nu = D3{nu.x / nn, nu.y / nn, nu.z / nn};
+    nv = D3{nv.x / nn, nv.y / nn, nv.z / nn};
+    const D3 rel = sub(corner, anchor);
+    PlaneEntry t;
+    t.nu_cu = make_float4((float)nu.x, (float)nu.y, (float)nu.z, (float)-dot(nu, rel));
+    t.nv_cv = make_float4((float)nv.x, (float)nv.y, (float)nv.z, (float)-dot(nv, rel));
+    return t;
+  };
+  tri_ids.clear();
+  for (const Group& G : found) {
+    // pair up triangles that form a parallelogram: A = (r, p, q), B = {p, q, p + q - r}
+    const size_t m = G.members.size();
+    std::vector<int> partner(m, -1);
+    std::vector<PlaneEntry> quad_entries, tri_entries;
+    std::vector<uint32_t> quad_ids, lone_ids;
+    for (size_t a = 0; a < m; a++) {
+      if (partner[a] >= 0) continue;
+      const D3 A[3] = {vertex(G.members[a], 0), vertex(G.members[a], 1), vertex(G.members[a], 2)};
+      for (size_t b = a + 1; b < m && partner[a] < 0; b++) {
+        if (partner[b] >= 0) continue;
+        const D3 B[3] = {vertex(G.members[b], 0), vertex(G.members[b], 1), vertex(G.members[b], 2)};
+        for (int lone = 0; lone < 3 && partner[a] < 0; lone++) {  // A's corner off the shared edge
+          const D3 r = A[lone], p = A[(lone + 1) % 3], q = A[(lone + 2) % 3];
+          const D3 fourth{p.x + q.x - r.x, p.y + q.y - r.y, p.z + q.z - r.z};
+          int shared = 0, other = -1;
+          for (int k = 0; k < 3; k++) {
+            if (same(B[k], p) || same(B[k], q)) shared++; else other = k;
+          }
+          if (shared != 2 || other < 0) continue;
+          const D3 diff = sub(B[other], fourth);
+          if (std::sqrt(dot(diff, diff)) > 1e-6 * G.scale) continue;
+          partner[a] = static_cast<int>(b);
+          partner[b] = static_cast<int>(a);
+          quad_entries.push_back(entry_for(r, sub(p, r), sub(q, r), G.anchor));
+          quad_ids.push_back(G.members[a]);
+          quad_ids.push_back(G.members[b]);
+        }
+      }
+      if (partner[a] < 0) {
+        const D3 v0 = A[0];
+        tri_entries.push_back(entry_for(v0, sub(A[1], v0), sub(A[2], v0), G.anchor));
+        lone_ids.push_back(G.members[a]);
+      }
+    }
+    PlaneGroup out;
+    const int32_t firsts = static_cast<int32_t>(entries.size()) | (static_cast<int32_t>(tri_ids.size()) << 16);
+    const int32_t counts = static_cast<int32_t>(quad_entries.size()) | (static_cast<int32_t>(tri_entries.size()) << 16);
+    out.n_gx = make_float4((float)G.n.x, (float)G.n.y, (float)G.n.z, (float)G.anchor.x);
+    out.g_range = make_float4((float)G.anchor.y, (float)G.anchor.z, __builtin_bit_cast(float, firsts),
+                              __builtin_bit_cast(float, counts));
+    groups.push_back(out);
+    entries.insert(entries.end(), quad_entries.begin(), quad_entries.end());
+    entries.insert(entries.end(), tri_entries.begin(), tri_entries.end());
+    tri_ids.insert(tri_ids.end(), quad_ids.begin(), quad_ids.end());
+    tri_ids.insert(tri_ids.end(), lone_ids.begin(), lone_ids.end());
+  }
+}
+
 // BasicThin::BasicThin, src/amber/scene/lens_thin.cc:32-57
 int make_lens(amber_cuda_ctx* ctx, const amber_cuda_lens& in, LensDev& lens) {
   if (in.n_blades < 1 || in.n_blades > kMaxBlades)
@@ -365,6 +473,11 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
     tri_ids.swap(reordered);
   }
 
+  // constant-memory list: batch the triangles by supporting plane (scene_device.cuh, PlaneGroup)
+  std::vector<PlaneGroup> groups;
+  std::vector<PlaneEntry> plane_entries;
+  if (!use_bvh) group_by_plane(scene->primitives, tri_ids, groups, plane_entries);
+
   const size_t n_tris = tri_ids.size(), n_spheres = sphere_ids.size();
   std::vector<TriIsect> tri_isect(n_tris);
   std::vector<TriShade> tri_shade(n_tris);
@@ -441,8 +554,9 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   std::memset(&ctx->const_scene, 0, sizeof(ConstScene));
   ctx->const_scene.n_tris = use_bvh ? 0 : static_cast<int32_t>(n_tris);
   ctx->const_scene.n_spheres = static_cast<int32_t>(n_spheres);
-  if (!use_bvh)
-    for (size_t k = 0; k < n_tris; k++) ctx->const_scene.tri_isect[k] = tri_isect[k];
+  ctx->const_scene.n_groups = static_cast<int32_t>(groups.size());
+  for (size_t g = 0; g < groups.size(); g++) ctx->const_scene.group[g] = groups[g];
+  for (size_t k = 0; k < plane_entries.size(); k++) ctx->const_scene.entry[k] = plane_entries[k];
   for (size_t k = 0; k < n_spheres; k++) ctx->const_scene.sphere[k] = spheres[k];
   ctx->camera.lens = lens;
 

@@ -70,16 +70,58 @@ __device__ __forceinline__ bool intersect_sphere(const float4 sphere, const Ray&
 // Closest-hit semantics of raytracer::List / a single-leaf BVH node
 // (include/amber/raytracer/acceleration_list.h:51-68, acceleration_bvh.h:343-356).
 struct ConstList {
+  // One plane group: the ray/plane intersection once, then two dot products per entry
+  // (scene_device.cuh, PlaneGroup).  Acceptance is the reference's: inclusive edges, t > kEPS,
+  // t < t_best (see intersect_triangle); a NaN or infinite t (n.d == 0) rejects the whole
+  // group.  Returns the first accepting triangle of the group or -1 -- triangles of one group
+  // share t, so after the first acceptance the strict `<` of the reference's closest-hit
+  // update rejects the rest.
+  static __device__ __forceinline__ int intersect_group(int g, const Ray& ray, float t_best, float& t_out) {
+    const float4 n_gx = c_scene.group[g].n_gx;
+    const float4 g_range = c_scene.group[g].g_range;
+    const float3 T = v3(ray.o.x - n_gx.w, ray.o.y - g_range.x, ray.o.z - g_range.y);
+    const float3 n = v3(n_gx);
+    float inv_nd;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_nd) : "f"(dot(n, ray.d)));
+    const float t = -dot(n, T) * inv_nd;
+    bool open = (t > kEpsF) & (t < t_best);
+    const float3 h = v3(fmaf(t, ray.d.x, T.x), fmaf(t, ray.d.y, T.y), fmaf(t, ray.d.z, T.z));
+    const int firsts = __float_as_int(g_range.z), counts = __float_as_int(g_range.w);
+    int e = firsts & 0xffff, tri = firsts >> 16;
+    const int quads_end = e + (counts & 0xffff), tris_end = quads_end + (counts >> 16);
+    int found = -1;
+    for (; e < quads_end; e++, tri += 2) {
+      const float4 a = c_scene.entry[e].nu_cu, b = c_scene.entry[e].nv_cv;
+      const float s = fmaf(a.x, h.x, fmaf(a.y, h.y, fmaf(a.z, h.z, a.w)));
+      const float r = fmaf(b.x, h.x, fmaf(b.y, h.y, fmaf(b.z, h.z, b.w)));
+      if (open & (s >= 0.0f) & (s <= 1.0f) & (r >= 0.0f) & (r <= 1.0f)) {
+        found = tri + (s + r > 1.0f ? 1 : 0);
+        open = false;
+      }
+    }
+    for (; e < tris_end; e++, tri++) {
+      const float4 a = c_scene.entry[e].nu_cu, b = c_scene.entry[e].nv_cv;
+      const float u = fmaf(a.x, h.x, fmaf(a.y, h.y, fmaf(a.z, h.z, a.w)));
+      const float v = fmaf(b.x, h.x, fmaf(b.y, h.y, fmaf(b.z, h.z, b.w)));
+      if (open & (u >= 0.0f) & (v >= 0.0f) & (u + v <= 1.0f)) {
+        found = tri;
+        open = false;
+      }
+    }
+    if (found >= 0) t_out = t;
+    return found;
+  }
+
   static __device__ __forceinline__ HitRecord closest(const SceneView&, const Ray& ray) {
     HitRecord hit;
     hit.t = CUDART_MAX_NORMAL_F;  // Cast(ray) == Cast(ray, numeric_limits::max), acceleration.h:46-51
     hit.prim = -1;
-    const int n_tris = c_scene.n_tris;
-#pragma unroll 2
-    for (int i = 0; i < n_tris; i++) {
-      const TriIsect& tri = c_scene.tri_isect[i];
-      if (intersect_triangle(tri.n_v0x, tri.nu_v0y, tri.nv_v0z, ray, hit.t, hit.t)) hit.prim = i;
+    const int n_groups = c_scene.n_groups;
+    for (int g = 0; g < n_groups; g++) {
+      const int k = intersect_group(g, ray, hit.t, hit.t);
+      if (k >= 0) hit.prim = k;
     }
+    const int n_tris = c_scene.n_tris;
     const int n_spheres = c_scene.n_spheres;
     for (int i = 0; i < n_spheres; i++) {
       if (intersect_sphere(c_scene.sphere[i], ray, hit.t, hit.t)) hit.prim = n_tris + i;
@@ -92,12 +134,8 @@ struct ConstList {
   static __device__ __forceinline__ bool occluded(const SceneView&, const Ray& ray, float t_max) {
     bool blocked = false;
     float t;
-    const int n_tris = c_scene.n_tris;
-#pragma unroll 2
-    for (int i = 0; i < n_tris; i++) {
-      const TriIsect& tri = c_scene.tri_isect[i];
-      blocked |= intersect_triangle(tri.n_v0x, tri.nu_v0y, tri.nv_v0z, ray, t_max, t);
-    }
+    const int n_groups = c_scene.n_groups;
+    for (int g = 0; g < n_groups; g++) blocked |= intersect_group(g, ray, t_max, t) >= 0;
     const int n_spheres = c_scene.n_spheres;
     for (int i = 0; i < n_spheres; i++) {
       blocked |= intersect_sphere(c_scene.sphere[i], ray, t_max, t);

@@ -331,7 +331,14 @@ __device__ __forceinline__ void film_add(float4* film, uint32_t pixel, float3 va
 #ifndef AMBER_SHADE_ROUNDS
 #define AMBER_SHADE_ROUNDS 8
 #endif
+#ifndef AMBER_SHADE_PREFETCH
+#define AMBER_SHADE_PREFETCH 1
+#endif
 constexpr int kShadeRounds = AMBER_SHADE_ROUNDS;
+
+__device__ __forceinline__ void prefetch_l1(const void* p) {
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+}
 constexpr int kShadeTile = kShadeRounds * kBlock;
 constexpr int kClassMiss = 14;  // hit.prim == -1: the path left the scene, algorithm_pt.cc:140-142
 constexpr int kClassDead = 15;  // hit.prim == -2: slot holds no path
@@ -351,14 +358,16 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
 
   // ---- phase 1: classify + counting sort ------------------------------------------
   uint32_t keys[kShadeRounds / 2];  // two (class:4 | rank:12) halves per register
+  int prims[kShadeRounds];
+#pragma unroll
+  for (int r = 0; r < kShadeRounds; r++) {  // all of the tile's hit records in flight at once
+    const uint32_t i = tile_base + r * kBlock + tid;
+    prims[r] = i < pool.n_slots ? __float_as_int(pool.hit[i].y) : kPrimDead;
+  }
 #pragma unroll
   for (int r = 0; r < kShadeRounds; r++) {
-    const uint32_t i = tile_base + r * kBlock + tid;
-    int cls = kClassDead;
-    if (i < pool.n_slots) {
-      const int prim = __float_as_int(pool.hit[i].y);
-      cls = prim >= 0 ? __ldg(args.scene.prim_class + prim) : (prim == kPrimMiss ? kClassMiss : kClassDead);
-    }
+    const int prim = prims[r];
+    const int cls = prim >= 0 ? __ldg(args.scene.prim_class + prim) : (prim == kPrimMiss ? kClassMiss : kClassDead);
     const uint32_t peers = __match_any_sync(0xffffffffu, cls);
     const int leader = __ffs(peers) - 1;
     uint32_t base = 0;
@@ -401,6 +410,14 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
     const uint32_t slot = tile_base + sorted[j];
     float4* ray_slot = pool.ray + 2 * static_cast<size_t>(slot);
     float4* state_slot = pool.state + 2 * static_cast<size_t>(slot);
+#if AMBER_SHADE_PREFETCH
+    if (j + kBlock < n_hit) {  // next round's records travel while this round computes
+      const size_t next = tile_base + sorted[j + kBlock];
+      prefetch_l1(pool.ray + 2 * next);
+      prefetch_l1(pool.state + 2 * next);
+      prefetch_l1(pool.hit + next);
+    }
+#endif
     const float4 o4 = ray_slot[0];
     const float4 d4 = ray_slot[1];
     const float4 t4 = state_slot[0];

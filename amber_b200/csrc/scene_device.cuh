@@ -82,10 +82,29 @@ struct SensorDev {
   float size_over_area;  // sensor.Size() / sensor.SceneArea(), lens_thin.cc:145
 };
 
+// Constant-memory list, triangles batched by supporting plane.  Triangles that lie in one
+// plane (the two halves of a wall, the blades of the aperture) share ONE ray/plane
+// intersection.  With g = the group's anchor vertex, n = its (unnormalised) normal,
+// T = o - g:   t = -(n.T)/(n.d),  h = T + t d.
+// Inside a group, two triangles that form a parallelogram (r, p, q | q, p + q - r, p) are ONE
+// entry: s = ns.h + cs, r = nr.h + cr are its edge coordinates from corner r, the hit is
+// inside iff s, r in [0, 1] and belongs to the first triangle iff s + r <= 1.  A lone
+// triangle is an entry with the usual u, v >= 0, u + v <= 1.  Either way an entry is two
+// float4: (nu, cu), (nv, cv) with cu = -nu.(v0 - g), i.e. u = nu.h + cu.
+struct PlaneGroup {
+  float4 n_gx;     // n.xyz, g.x
+  float4 g_range;  // g.y, g.z, (first entry | first triangle << 16), (quads | lone triangles << 16)
+};
+struct PlaneEntry {
+  float4 nu_cu;  // nu.xyz, cu
+  float4 nv_cv;  // nv.xyz, cv
+};
+
 struct ConstScene {
-  int32_t n_tris, n_spheres;
-  int32_t pad[2];
-  TriIsect tri_isect[kMaxConstTris];
+  int32_t n_tris, n_spheres, n_groups;
+  int32_t pad;
+  PlaneGroup group[kMaxConstTris];
+  PlaneEntry entry[kMaxConstTris];  // group by group: quads, then lone triangles
   float4 sphere[kMaxConstSpheres];  // centre xyz, radius
 };
 
