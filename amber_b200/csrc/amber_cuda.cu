@@ -644,7 +644,8 @@ __global__ void control_begin_kernel(Control* ctl, unsigned long long total_path
 }
 
 constexpr int kStepsPerPoll = 8;
-constexpr uint32_t kDefaultPoolPaths = 1u << 21;
+// 8 waves of shade tiles at 4 resident blocks per SM on 148 SMs (148 * 4 * kShadeTile * 8)
+constexpr uint32_t kDefaultPoolPaths = 148u * 4u * static_cast<uint32_t>(kShadeTile) * 8u;
 
 struct KernelTimer {
   // profiling mode: one event pair per launch, summed per kernel class after the render

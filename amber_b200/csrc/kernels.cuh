@@ -329,16 +329,18 @@ __device__ __forceinline__ void film_add(float4* film, uint32_t pixel, float3 va
 #define AMBER_SHADE_MIN_BLOCKS 4
 #endif
 #ifndef AMBER_SHADE_ROUNDS
-#define AMBER_SHADE_ROUNDS 8
-#endif
-#ifndef AMBER_SHADE_PREFETCH
-#define AMBER_SHADE_PREFETCH 1
+#define AMBER_SHADE_ROUNDS 4
 #endif
 constexpr int kShadeRounds = AMBER_SHADE_ROUNDS;
 
-__device__ __forceinline__ void prefetch_l1(const void* p) {
-  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+__device__ __forceinline__ void cp_async_16(void* smem, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem))), "l"(gmem));
 }
+__device__ __forceinline__ void cp_async_8(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem))), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+__device__ __forceinline__ void cp_async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 constexpr int kShadeTile = kShadeRounds * kBlock;
 constexpr int kClassMiss = 14;  // hit.prim == -1: the path left the scene, algorithm_pt.cc:140-142
 constexpr int kClassDead = 15;  // hit.prim == -2: slot holds no path
@@ -346,6 +348,8 @@ constexpr int32_t kPrimMiss = -1, kPrimDead = -2;
 
 __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(const RenderArgs args) {
   __shared__ uint16_t sorted[kShadeTile];
+  __shared__ float4 stage[2][4][kBlock];  // double-buffered ray.o, ray.d, throughput, path ids
+  __shared__ float2 stage_hit[2][kBlock];
   __shared__ uint32_t class_count[16], class_offset[16];
   __shared__ uint32_t warp_scan[kBlock / 32];
   __shared__ uint32_t queue_base[2];
@@ -398,6 +402,23 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
   const uint32_t n_live = class_offset[kClassDead];  // entries [n_hit, n_live): misses
 
   // ---- phase 2: shade in class order ------------------------------------------------
+  // Each thread streams ITS records (ray, state, hit: 72 B) of round r + 1 into shared memory
+  // with cp.async while it shades round r, so the DRAM latency of the permuted gathers is
+  // paid once per tile, not once per round.  Thread-private staging: no barrier involved.
+  auto stage_records = [&](int round) {
+    const uint32_t jn = round * kBlock + tid;
+    if (round < kShadeRounds && jn < n_hit) {
+      const size_t next = tile_base + sorted[jn];
+      const int b = round & 1;
+      cp_async_16(&stage[b][0][tid], pool.ray + 2 * next);
+      cp_async_16(&stage[b][1][tid], pool.ray + 2 * next + 1);
+      cp_async_16(&stage[b][2][tid], pool.state + 2 * next);
+      cp_async_16(&stage[b][3][tid], pool.state + 2 * next + 1);
+      cp_async_8(&stage_hit[b][tid], pool.hit + next);
+    }
+    cp_async_commit();
+  };
+  stage_records(0);
   uint32_t freed_mask = 0, shadow_mask = 0;
 #pragma unroll 1
   for (int r = 0; r < kShadeRounds; r++) {
@@ -410,19 +431,16 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
     const uint32_t slot = tile_base + sorted[j];
     float4* ray_slot = pool.ray + 2 * static_cast<size_t>(slot);
     float4* state_slot = pool.state + 2 * static_cast<size_t>(slot);
-#if AMBER_SHADE_PREFETCH
-    if (j + kBlock < n_hit) {  // next round's records travel while this round computes
-      const size_t next = tile_base + sorted[j + kBlock];
-      prefetch_l1(pool.ray + 2 * next);
-      prefetch_l1(pool.state + 2 * next);
-      prefetch_l1(pool.hit + next);
-    }
-#endif
-    const float4 o4 = ray_slot[0];
-    const float4 d4 = ray_slot[1];
-    const float4 t4 = state_slot[0];
-    const float4 m4 = state_slot[1];
-    const float2 h2 = pool.hit[slot];
+    // this round's records were copied to shared memory asynchronously during the previous
+    // round (the copies of round 0 overlap nothing); start the next round's copies now
+    stage_records(r + 1);
+    cp_async_wait_all_but_one();
+    const int buf = r & 1;
+    const float4 o4 = stage[buf][0][tid];
+    const float4 d4 = stage[buf][1][tid];
+    const float4 t4 = stage[buf][2][tid];
+    const float4 m4 = stage[buf][3][tid];
+    const float2 h2 = stage_hit[buf][tid];
     HitRecord hit;
     hit.t = h2.x;
     hit.prim = __float_as_int(h2.y);

@@ -36,11 +36,24 @@ MAX_DEPTH = 32
 SEED = 1
 METRIC = "Mrays/s (closest-hit + shadow rays), Cornell box 1024x1024 unidirectional path tracing"
 FILM = (0.036, 0.036)
-# algorithmic bytes per ray over the whole wavefront, and the share of the
-# dominant kernel (`extend`: read ray 2 x float4, write hit float4)
+# algorithmic bytes per ray over the whole wavefront ...
 BYTES_PER_CLOSEST_RAY = 160
 BYTES_PER_SHADOW_RAY = 108
-EXTEND_BYTES_PER_RAY = 48
+# ... and per kernel, from the record layout in HBM ("Data layout"): bytes one unit of
+# that kernel's work must move, (per closest ray, per shadow ray, per camera path).
+KERNEL_BYTES = {
+    # read q_new 4, write ray 32 + state 32
+    "raygen": (0, 0, 68),
+    # read ray 32, write hit 8
+    "extend": (40, 0, 0),
+    # read hit 8 (classify) + hit 8, ray 32, state 32; write ray 32, state 32 | shadow record 32 +
+    # q_shadow 4 per shadow ray | q_new 4 per finished path
+    "shade": (144, 36, 4),
+    # read q_shadow 4, ray origin 16, shadow record 32; film atomic 16
+    "connect": (0, 68, 0),
+}
+KERNEL_NAMES = {"raygen": "raygen_kernel", "extend": "extend_kernel<ConstList>", "shade": "shade_kernel",
+                "connect": "connect_kernel<ConstList>"}
 
 
 def host_threads() -> int:
@@ -275,30 +288,38 @@ def run_gpu(args) -> None:
     if rank == 0:
         dev.set_profiling(True)
         dev.film_clear()
-        dev.render(begin, min(count, 128), seed=SEED, max_depth=MAX_DEPTH, estimator=estimator, pool_paths=args.pool)
+        dev.render(begin, count, seed=SEED, max_depth=MAX_DEPTH, estimator=estimator, pool_paths=args.pool)
         s = dev.stats()
         dev.set_profiling(False)
         peak, peak_kind = measured_peaks()
         kernel_ms = {k: s[f"{k}_ms"] for k in ("raygen", "extend", "shade", "connect")}
         dominant = max(kernel_ms, key=kernel_ms.get)
-        rays_per_launch = s["closest_rays"] / max(1, s["extend_launches"])
-        avg_ms = s["extend_ms"] / max(1, s["extend_launches"])
-        achieved = EXTEND_BYTES_PER_RAY * rays_per_launch / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+        launches_each = max(1, s["extend_launches"])          # every kernel runs once per wavefront iteration
+        per_closest, per_shadow, per_path = KERNEL_BYTES[dominant]
+        bytes_per_launch = (per_closest * s["closest_rays"] + per_shadow * s["shadow_rays"]
+                            + per_path * s["paths"]) / launches_each
+        avg_ms = kernel_ms[dominant] / launches_each
+        achieved = bytes_per_launch / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
         whole = (BYTES_PER_CLOSEST_RAY * s["closest_rays"] + BYTES_PER_SHADOW_RAY * s["shadow_rays"]) / \
                 (s["last_render_ms"] * 1e-3) / 1e9
         roofline = {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": None, "kernel": "extend_kernel<ConstList>", "peak_source": peak_kind,
-            "algorithmic_bytes_per_ray": EXTEND_BYTES_PER_RAY, "rays_per_launch": rays_per_launch,
-            "avg_launch_ms": avg_ms, "dominant_by_time": dominant,
+            "traffic": None, "kernel": KERNEL_NAMES[dominant], "peak_source": peak_kind,
+            "algorithmic_bytes_per_launch": bytes_per_launch,
+            "bytes_model": {"per_closest_ray": per_closest, "per_shadow_ray": per_shadow, "per_camera_path": per_path},
+            "closest_rays_per_launch": s["closest_rays"] / launches_each,
+            "shadow_rays_per_launch": s["shadow_rays"] / launches_each,
+            "avg_launch_ms": avg_ms, "launches_timed": launches_each,
+            "timing": "CUDA events on the context's stream around every launch of one extra full step",
             "kernel_share_of_step": {k: v / max(1e-9, sum(kernel_ms.values())) for k, v in kernel_ms.items()},
             "whole_wavefront": {"achieved": whole, "frac": whole / peak,
                                 "bytes_model": "160 B/closest ray + 108 B/shadow ray (SURVEY 8d)"},
-            "note": "issue-bound kernel: the 25-primitive scene sits in constant memory, see DESIGN.md / profiles/",
+            "note": "the kernels are instruction-issue bound (scene in constant memory, exact-arithmetic "
+                    "shading); issue-slot utilisation per kernel is in profiles/",
         }
-        traffic_file = os.path.join(ROOT, "profiles", "extend_traffic.json")
+        traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(traffic_file):
-            roofline["traffic"] = json.load(open(traffic_file)).get("dram_bytes_per_launch")
+            roofline["traffic"] = json.load(open(traffic_file)).get(dominant, {}).get("dram_bytes_per_launch")
 
     if rank != 0:
         if distributed:
