@@ -1,0 +1,207 @@
+// adapter_demo.cc -- the drop-in, exercised the way a maintainer of the reference would use it.
+//
+// Builds the Cornell box of src/amber/etude/cornel_box.cc:38-204 through
+// amber::cuda::FlatSceneBuilder (the reference's factory verbs), then renders the SAME scene
+// object twice through the SAME interface, rendering::Algorithm<RGB>::Render(scene, sensor, context):
+//   1. the reference's own CPU path tracer, MakeRGBPathTracing()   (unmodified reference code)
+//   2. the GPU path tracer,                 MakeRGBCudaPathTracing()
+// and compares the two images statistically (mean luminance, 16x16 block means).
+//
+// Built by `make -C oracle adapter_demo` into oracle/_ref/ (it links the compiled reference).
+// usage: adapter_demo [size=128] [spp=64] [threads=8] [devices=1]
+//        adapter_demo --dump <file>     (flat scene description only; needs no GPU)
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+#include <string>
+
+#include "amber/etude/cornel_box.h"
+#include "amber/rendering/algorithm_pt.h"
+
+#include "amber_cuda/adapter.hpp"
+
+using namespace amber;
+using rendering::RGB;
+using scene::Vector3;
+
+namespace {
+
+// cli::Context semantics, src/amber/cli/context.cc:34-67
+class DemoContext : public rendering::Context
+{
+public:
+  DemoContext(std::size_t threads, std::size_t iterations) : threads_(threads), iterations_(iterations) {}
+  std::size_t ThreadCount() const noexcept { return threads_; }
+  std::size_t IterationCount() const noexcept
+  {
+    std::lock_guard<std::mutex> lock(mutex_);
+    return started_;
+  }
+  bool Iterate() noexcept
+  {
+    std::lock_guard<std::mutex> lock(mutex_);
+    if (started_ >= iterations_) return false;
+    started_++;
+    return true;
+  }
+
+private:
+  std::size_t threads_, iterations_, started_ = 0;
+  mutable std::mutex mutex_;
+};
+
+std::unique_ptr<cuda::Scene> CornelBox()
+{
+  cuda::FlatSceneBuilder b;
+  const scene::real_type transform[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 4, 0, 0, 0, 1};
+  b.MakeThinLens(transform, 0.050, 4.0, 0.050, 6);
+  auto quad = [&](cuda::FlatSceneBuilder::MaterialId m, Vector3 a0, Vector3 a1, Vector3 a2, Vector3 b0, Vector3 b1, Vector3 b2) {
+    b.MakeTriangle(a0, a1, a2, m);
+    b.MakeTriangle(b0, b1, b2, m);
+  };
+  quad(b.MakeDiffuseLight(RGB(1e11, 1e11, 1e11)),
+       Vector3(0.01, 0.99, 0.01), Vector3(-0.01, 0.99, 0.01), Vector3(-0.01, 0.99, -0.01),
+       Vector3(-0.01, 0.99, -0.01), Vector3(0.01, 0.99, -0.01), Vector3(0.01, 0.99, 0.01));
+  quad(b.MakeLambertian(RGB(.5, 0, 0)),
+       Vector3(-1, 1, 1), Vector3(-1, -1, 1), Vector3(-1, -1, -1), Vector3(-1, -1, -1), Vector3(-1, 1, -1), Vector3(-1, 1, 1));
+  quad(b.MakeLambertian(RGB(0, .5, 0)),
+       Vector3(1, 1, 1), Vector3(1, 1, -1), Vector3(1, -1, -1), Vector3(1, -1, -1), Vector3(1, -1, 1), Vector3(1, 1, 1));
+  quad(b.MakePhong(RGB(.95, .95, .95), 256),
+       Vector3(1, 1, -1), Vector3(-1, 1, -1), Vector3(-1, -1, -1), Vector3(-1, -1, -1), Vector3(1, -1, -1), Vector3(1, 1, -1));
+  quad(b.MakeLambertian(RGB(.5, .5, .5)),
+       Vector3(1, -1, 1), Vector3(1, -1, -1), Vector3(-1, -1, -1), Vector3(-1, -1, -1), Vector3(-1, -1, 1), Vector3(1, -1, 1));
+  quad(b.MakeLambertian(RGB(.5, .5, .5)),
+       Vector3(1, 1, 1), Vector3(-1, 1, 1), Vector3(-1, 1, -1), Vector3(-1, 1, -1), Vector3(1, 1, -1), Vector3(1, 1, 1));
+  const auto water = b.MakeRefraction(1.333);
+  quad(water, Vector3(1, -0.5, 1), Vector3(1, -0.5, -1), Vector3(-1, -0.5, -1),
+       Vector3(-1, -0.5, -1), Vector3(-1, -0.5, 1), Vector3(1, -0.5, 1));
+  quad(water, Vector3(1, -0.5, 1), Vector3(-1, -0.5, 1), Vector3(-1, -1, 1),
+       Vector3(-1, -1, 1), Vector3(1, -1, 1), Vector3(1, -0.5, 1));
+  b.MakeSphere(Vector3(0.4, -0.6, -0.5), 0.4, b.MakeLambertian(RGB(.5, .5, .5)));
+  b.MakeSphere(Vector3(-0.4, -0.7, 0.1), 0.3, b.MakeSpecular(RGB(.95, .95, .95)));
+  b.MakeSphere(Vector3(0.1, -0.8, 0.6), 0.2, b.MakeRefraction(1.125));
+  return b.Build();
+}
+
+struct Summary { double mean; std::vector<double> blocks; };
+
+Summary Summarise(const rendering::Image<RGB>& image, unsigned size)
+{
+  const unsigned nb = 16, bs = size / nb;
+  Summary s{0, std::vector<double>(nb * nb, 0.0)};
+  for (unsigned y = 0; y < size; y++) {
+    for (unsigned x = 0; x < size; x++) {
+      const auto& v = image[rendering::Pixel(x, y)];
+      const double lum = 0.2126 * v.X() + 0.7152 * v.Y() + 0.0722 * v.Z();
+      s.mean += lum;
+      s.blocks[(y / bs) * nb + (x / bs)] += lum;
+    }
+  }
+  s.mean /= double(size) * size;
+  for (auto& b : s.blocks) b /= double(bs) * bs;
+  return s;
+}
+
+}  // namespace
+
+int main(int argc, char** argv)
+{
+  const unsigned size = argc > 1 ? std::atoi(argv[1]) : 128;
+  const unsigned spp = argc > 2 ? std::atoi(argv[2]) : 64;
+  const unsigned threads = argc > 3 ? std::atoi(argv[3]) : 8;
+  const unsigned n_devices = argc > 4 ? std::atoi(argv[4]) : 1;
+
+  const auto scene = CornelBox();
+  if (argc > 2 && std::string(argv[1]) == "--dump") {
+    // flat description as the GPU receives it: per primitive kind, 9 floats, then its material
+    // (kind, rgb, param) -- compared with the Python builder's Cornell box by tests/test_adapter.py
+    const auto& d = scene->FlatDescription();
+    std::FILE* f = std::fopen(argv[2], "wb");
+    if (!f) return 4;
+    for (uint32_t i = 0; i < d.n_primitives; i++) {
+      const auto& p = d.primitives[i];
+      const auto& m = d.materials[p.material];
+      std::fwrite(&p.kind, 4, 1, f);
+      std::fwrite(p.data, 4, 9, f);
+      std::fwrite(&m.kind, 4, 1, f);
+      std::fwrite(m.rgb, 4, 3, f);
+      std::fwrite(&m.param, 4, 1, f);
+    }
+    std::fwrite(&d.lens, sizeof d.lens, 1, f);
+    std::fclose(f);
+    return 0;
+  }
+  const cuda::Sensor sensor(size, size, 0.036f, 0.036f * size / size);
+  std::printf("scene: %u flat primitives, %u materials\n", scene->FlatDescription().n_primitives,
+              scene->FlatDescription().n_materials);
+
+  auto timed = [&](rendering::Algorithm<RGB>& algorithm, unsigned n_threads, unsigned iterations, const char* name) {
+    DemoContext context(n_threads, iterations);
+    const auto t0 = std::chrono::steady_clock::now();
+    auto image = algorithm.Render(*scene, sensor, context);
+    const double seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::printf("%-28s %4u spp in %8.3f s  (%.2f Mpaths/s)\n", name, iterations, seconds,
+                double(size) * size * iterations / seconds / 1e6);
+    return image;
+  };
+
+  // 1. the reference's CPU path tracer on the builder's scene
+  const auto cpu_algorithm = rendering::MakeRGBPathTracing();
+  const auto cpu_image = timed(*cpu_algorithm, threads, spp, "reference pt (CPU)");
+  const auto cpu = Summarise(cpu_image, size);
+
+  // 2. the GPU path tracer behind the same interface
+  cuda::CudaPathTracingOptions options;
+  options.devices.clear();
+  for (unsigned d = 0; d < n_devices; d++) options.devices.push_back(int(d));
+  std::unique_ptr<rendering::Algorithm<RGB>> gpu_algorithm;
+  rendering::Image<RGB> gpu_image(size, size);
+  try {
+    options.estimator = AMBER_CUDA_ESTIMATOR_REFERENCE;
+    gpu_algorithm = cuda::MakeRGBCudaPathTracing(options);
+    gpu_image = timed(*gpu_algorithm, 1, spp * 16, "pt-cuda, reference estimator");
+  } catch (const std::runtime_error& error) {
+    std::printf("pt-cuda failed loudly (no CPU fallback): %s\n", error.what());
+    return 3;
+  }
+  const auto gpu = Summarise(gpu_image, size);
+  options.estimator = AMBER_CUDA_ESTIMATOR_NEE;
+  gpu_algorithm = cuda::MakeRGBCudaPathTracing(options);
+  const auto nee = Summarise(timed(*gpu_algorithm, 1, spp * 16, "pt-cuda, NEE estimator"), size);
+
+  // a reference scene that was NOT built by the builder must be refused, not rendered on the CPU
+  bool refused = false;
+  try {
+    const auto builtin = etude::CornelBox(0.050, 0.050, 6);  // src/amber/cli/application.cc:69-73
+    DemoContext context(1, 1);
+    gpu_algorithm->Render(builtin, sensor, context);
+  } catch (const std::invalid_argument& error) {
+    refused = true;
+    std::printf("built-in etude::CornelBox refused as expected: %s\n", error.what());
+  }
+  if (!refused) {
+    std::printf("adapter_demo: a non-flat scene was not refused\n");
+    return 2;
+  }
+
+  // block means: the reference estimator has fireflies (no light sampling), so compare robustly:
+  // median relative deviation of the 256 block means, and the overall mean
+  auto median_rel = [](const Summary& a, const Summary& b) {
+    std::vector<double> rel;
+    for (std::size_t i = 0; i < a.blocks.size(); i++) {
+      const double denom = 0.5 * (a.blocks[i] + b.blocks[i]);
+      if (denom > 0) rel.push_back(std::fabs(a.blocks[i] - b.blocks[i]) / denom);
+    }
+    std::sort(rel.begin(), rel.end());
+    return rel.empty() ? 0.0 : rel[rel.size() / 2];
+  };
+  std::printf("mean luminance: reference CPU %.6g | pt-cuda reference-estimator %.6g | pt-cuda NEE %.6g\n",
+              cpu.mean, gpu.mean, nee.mean);
+  std::printf("median relative deviation of 16x16 block means: CPU vs cuda(ref) %.4f, cuda(ref) vs cuda(NEE) %.4f\n",
+              median_rel(cpu, gpu), median_rel(gpu, nee));
+  const bool ok = median_rel(gpu, nee) < 0.25 && median_rel(cpu, gpu) < 0.5;
+  std::printf("%s\n", ok ? "adapter_demo: OK" : "adapter_demo: MISMATCH");
+  return ok ? 0 : 1;
+}
