@@ -66,7 +66,7 @@ def test_cpp_adapter_fails_loudly_without_a_gpu():
 def test_cpp_adapter_renders_through_the_reference_interface():
     """rendering::Algorithm<RGB>::Render with the reference's CPU path tracer and with the GPU one
     on the same amber::cuda::Scene: block means agree, a non-flat scene is refused."""
-    rc = subprocess.run([DEMO, "128", "256", "16"], capture_output=True, text=True, timeout=600)
+    rc = subprocess.run([DEMO, "128", "1024", "16"], capture_output=True, text=True, timeout=600)
     print(rc.stdout)
     assert rc.returncode == 0, rc.stdout + rc.stderr
     assert "adapter_demo: OK" in rc.stdout and "refused as expected" in rc.stdout
