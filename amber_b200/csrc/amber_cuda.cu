@@ -85,6 +85,9 @@ struct amber_cuda_ctx {
   DeviceBuffer<LightDev> d_lights;
   DeviceBuffer<float4> d_bvh_nodes;
   uint32_t bvh_nodes = 0;
+  uint32_t bvh_stack_entries = 0;  // per-lane traversal stack: 3 * depth + 1
+  unsigned int bvh_grid = 0;       // persistent grid: SMs * resident blocks
+  size_t bvh_smem = 0;
 
   // film
   DeviceBuffer<float4> d_film;
@@ -356,6 +359,50 @@ int ensure_pool(amber_cuda_ctx* ctx, uint32_t slots) {
   return AMBER_CUDA_OK;
 }
 
+// Depth of the flattened 4-wide tree (root = depth 1); a node step pushes at most 3 children,
+// so 3 * depth + 1 stack entries per lane can never overflow.
+int wide_bvh_depth(const bvh_build::WideBvhHost& bvh) {
+  if (bvh.root < 0 || bvh.root == bvh_build::kEmpty || bvh.n_nodes == 0) return 0;
+  std::vector<std::pair<int32_t, int>> todo{{bvh.root, 1}};
+  int depth = 0;
+  while (!todo.empty()) {
+    const auto [node, d] = todo.back();
+    todo.pop_back();
+    depth = std::max(depth, d);
+    for (int c = 0; c < 4; c++) {
+      int32_t ref;
+      std::memcpy(&ref, &bvh.nodes[static_cast<size_t>(node) * 32 + 24 + c], sizeof ref);
+      if (ref >= 0 && ref != bvh_build::kEmpty) todo.push_back({ref, d + 1});
+    }
+  }
+  return depth;
+}
+
+// Persistent BVH kernels: stack size from the tree depth, grid = SMs x resident blocks.
+int configure_bvh_launch(amber_cuda_ctx* ctx, const bvh_build::WideBvhHost& bvh) {
+  const int depth = wide_bvh_depth(bvh);
+  ctx->bvh_stack_entries = static_cast<uint32_t>(3 * depth + 1);
+  if (ctx->bvh_stack_entries > static_cast<uint32_t>(kBvhStackMax))
+    return fail(ctx, AMBER_CUDA_EINVAL, "BVH depth %d needs %u stack entries per lane (limit %d)", depth,
+                ctx->bvh_stack_entries, kBvhStackMax);
+  ctx->bvh_smem = static_cast<size_t>(ctx->bvh_stack_entries) * kBlock * sizeof(int32_t);
+  cudaDeviceProp prop;
+  CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, ctx->device));
+  const void* kernels[] = {reinterpret_cast<const void*>(&extend_kernel<WideBvh>),
+                           reinterpret_cast<const void*>(&connect_kernel<WideBvh>),
+                           reinterpret_cast<const void*>(&cast_bvh_kernel)};
+  int resident = 1 << 30;
+  for (const void* k : kernels) {
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ctx->bvh_smem)));
+    int blocks = 0;
+    CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, k, kBlock, ctx->bvh_smem));
+    resident = std::min(resident, blocks);
+  }
+  if (resident < 1) return fail(ctx, AMBER_CUDA_ECUDA, "BVH kernels do not fit on an SM (%zu B of shared memory)", ctx->bvh_smem);
+  ctx->bvh_grid = static_cast<unsigned int>(prop.multiProcessorCount * resident);
+  return AMBER_CUDA_OK;
+}
+
 }  // namespace amber_host
 using namespace amber_host;
 
@@ -592,6 +639,10 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   view.tri_isect = ctx->d_tri_isect.ptr;
   view.bvh_root = use_bvh ? bvh.root : kEmptyChild;
   ctx->bvh_nodes = use_bvh ? bvh.n_nodes : 0;
+  if (use_bvh) {
+    const int rc = configure_bvh_launch(ctx, bvh);
+    if (rc != AMBER_CUDA_OK) return rc;
+  }
   ctx->has_scene = true;
   return AMBER_CUDA_OK;
 }
@@ -669,6 +720,7 @@ template <class Accel>
 int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dynamic_smem) {
   const unsigned int grid = blocks_for(args.pool.n_slots);
   const unsigned int shade_grid = blocks_for(args.pool.n_slots, kShadeTile);
+  const unsigned int trace_grid = Accel::kPersistent ? ctx->bvh_grid : grid;
   cudaStream_t stream = ctx->stream;
   KernelTimer timer;
   const bool profile = ctx->profiling;
@@ -694,9 +746,9 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
     for (int step = 0; step < kStepsPerPoll; step++) {
       timed(0, [&] { raygen_kernel<<<grid, kBlock, 0, stream>>>(args); });
       bookkeep_kernel<<<1, 1, 0, stream>>>(args.ctl);
-      timed(1, [&] { extend_kernel<Accel><<<grid, kBlock, dynamic_smem, stream>>>(args); });
+      timed(1, [&] { extend_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args); });
       timed(2, [&] { shade_kernel<<<shade_grid, kBlock, 0, stream>>>(args); });
-      if (nee) timed(3, [&] { connect_kernel<Accel><<<grid, kBlock, dynamic_smem, stream>>>(args); });
+      if (nee) timed(3, [&] { connect_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args); });
       ctx->stats.kernel_launches += nee ? 5 : 4;
       extend_launches++;
     }
@@ -733,7 +785,6 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
   return AMBER_CUDA_OK;
 }
 
-size_t bvh_smem_bytes() { return static_cast<size_t>(kBvhStack) * kBlock * sizeof(int32_t); }
 
 }  // namespace amber_host
 using namespace amber_host;
@@ -780,7 +831,7 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
   ctx->stats.kernel_launches += 2;
   const bool nee = params->estimator == AMBER_CUDA_ESTIMATOR_NEE && ctx->view.n_lights > 0;
   if (ctx->use_bvh) {
-    rc = render_loop<WideBvh>(ctx, args, nee, bvh_smem_bytes());
+    rc = render_loop<WideBvh>(ctx, args, nee, ctx->bvh_smem);
   } else {
     rc = render_loop<ConstList>(ctx, args, nee, 0);
   }
@@ -842,7 +893,10 @@ int amber_cuda_cast_device(amber_cuda_ctx* ctx, const void* ray_origin4, const v
   float4* h = static_cast<float4*>(hit4);
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev_begin, ctx->stream));
   if (ctx->use_bvh) {
-    cast_kernel<WideBvh><<<blocks_for(n), kBlock, bvh_smem_bytes(), ctx->stream>>>(ctx->view, o, d, n, h);
+    if (n >= (1ull << 32)) return fail(ctx, AMBER_CUDA_EINVAL, "at most 2^32 - 1 rays per call");
+    CUDA_TRY(ctx, cudaMemsetAsync(&ctx->d_ctl.ptr->cursor_cast, 0, sizeof(unsigned int), ctx->stream));
+    cast_bvh_kernel<<<ctx->bvh_grid, kBlock, ctx->bvh_smem, ctx->stream>>>(ctx->view, o, d, static_cast<uint32_t>(n), h,
+                                                                         &ctx->d_ctl.ptr->cursor_cast);
   } else {
     cast_kernel<ConstList><<<blocks_for(n), kBlock, 0, ctx->stream>>>(ctx->view, o, d, n, h);
   }

@@ -70,6 +70,7 @@ __device__ __forceinline__ bool intersect_sphere(const float4 sphere, const Ray&
 // Closest-hit semantics of raytracer::List / a single-leaf BVH node
 // (include/amber/raytracer/acceleration_list.h:51-68, acceleration_bvh.h:343-356).
 struct ConstList {
+  static constexpr bool kPersistent = false;
   // One plane group: the ray/plane intersection once, then two dot products per entry
   // (scene_device.cuh, PlaneGroup).  Acceptance is the reference's: inclusive edges, t > kEPS,
   // t < t_best (see intersect_triangle); a NaN or infinite t (n.d == 0) rejects the whole
@@ -112,8 +113,13 @@ struct ConstList {
     return found;
   }
 
-  static __device__ __forceinline__ HitRecord closest(const SceneView&, const Ray& ray) {
+  static __device__ __forceinline__ HitRecord closest(const SceneView&, const Ray& ray, bool active) {
     HitRecord hit;
+    if (!active) {
+      hit.t = CUDART_NAN_F;
+      hit.prim = -1;
+      return hit;
+    }
     hit.t = CUDART_MAX_NORMAL_F;  // Cast(ray) == Cast(ray, numeric_limits::max), acceleration.h:46-51
     hit.prim = -1;
     const int n_groups = c_scene.n_groups;
@@ -131,7 +137,8 @@ struct ConstList {
   }
 
   // true if anything lies in (kEPS, t_max)
-  static __device__ __forceinline__ bool occluded(const SceneView&, const Ray& ray, float t_max) {
+  static __device__ __forceinline__ bool occluded(const SceneView&, const Ray& ray, float t_max, bool active) {
+    if (!active) return false;
     bool blocked = false;
     float t;
     const int n_groups = c_scene.n_groups;

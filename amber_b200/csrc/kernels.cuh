@@ -23,6 +23,7 @@
 // permuted accesses of raygen / shade / connect never touch a partial sector.
 #pragma once
 
+#include "bvh.cuh"
 #include "intersect.cuh"
 #include "materials.cuh"
 
@@ -39,6 +40,8 @@ struct Control {
   unsigned int n_shadow;           // entries in the shadow queue
   unsigned int n_alive;            // survivors of the last shade
   unsigned int done;
+  unsigned int cursor_extend, cursor_connect, cursor_cast;  // persistent BVH kernels: next item to fetch
+  unsigned int pad;
   unsigned long long paths, closest_rays, shadow_rays, truncated, phong_capped;
 };
 
@@ -182,25 +185,33 @@ __global__ void bookkeep_kernel(Control* ctl) {
   ctl->n_new = 0;
   ctl->n_shadow = 0;
   ctl->n_alive = 0;
+  ctl->cursor_extend = 0;
+  ctl->cursor_connect = 0;
 }
 
 // ---------------------------------------------------------------------------------
+// Every thread reaches Accel::closest (the BVH walk votes across the warp); threads without a
+// ray pass active = false.
 template <class Accel>
 __global__ void __launch_bounds__(kBlock) extend_kernel(const RenderArgs args) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  if (i >= args.pool.n_slots) return;
-  const float4* r = args.pool.ray + 2 * static_cast<size_t>(i);
-  const float4 o = r[0];
-  if (o.w == 0.0f) {  // no path in this slot: tell `shade` so (it sorts the tile by hit class)
-    args.pool.hit[i] = make_float2(CUDART_NAN_F, __int_as_float(-2));
-    return;
+  const bool in_range = i < args.pool.n_slots;
+  float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
+  if (in_range) {
+    const float4* r = args.pool.ray + 2 * static_cast<size_t>(i);
+    o = r[0];
+    if (o.w != 0.0f) d = r[1];
   }
-  const float4 d = r[1];
+  const bool active = in_range && o.w != 0.0f;
   Ray ray;
   ray.o = v3(o);
   ray.d = v3(d);
-  const HitRecord hit = Accel::closest(args.scene, ray);
-  args.pool.hit[i] = make_float2(hit.t, __int_as_float(hit.prim));
+  const HitRecord hit = Accel::closest(args.scene, ray, active);
+  if (active) {
+    args.pool.hit[i] = make_float2(hit.t, __int_as_float(hit.prim));
+  } else if (in_range) {  // no path in this slot: tell `shade` so (it sorts the tile by hit class)
+    args.pool.hit[i] = make_float2(CUDART_NAN_F, __int_as_float(-2));
+  }
 }
 
 // `extend` on caller-supplied rays (amber_cuda_cast / amber_cuda_cast_device).
@@ -209,12 +220,86 @@ __global__ void __launch_bounds__(kBlock) cast_kernel(const SceneView scene, con
                                                       const float4* __restrict__ ray_d, uint64_t n,
                                                       float4* __restrict__ hits) {
   const uint64_t i = static_cast<uint64_t>(blockIdx.x) * kBlock + threadIdx.x;
-  if (i >= n) return;
+  const bool active = i < n;
   Ray ray;
-  ray.o = v3(ray_o[i]);
-  ray.d = v3(ray_d[i]);
-  const HitRecord hit = Accel::closest(scene, ray);
-  hits[i] = make_float4(hit.t, __int_as_float(hit.prim), 0.0f, 0.0f);
+  ray.o = active ? v3(ray_o[i]) : v3(0.0f, 0.0f, 0.0f);
+  ray.d = active ? v3(ray_d[i]) : v3(0.0f, 0.0f, 1.0f);
+  const HitRecord hit = Accel::closest(scene, ray, active);
+  if (active) hits[i] = make_float4(hit.t, __int_as_float(hit.prim), 0.0f, 0.0f);
+}
+
+// ---------------------------------------------------------------------------------
+// Large scenes: `extend` / cast as persistent kernels over the 4-wide BVH (bvh.cuh,
+// trace_persistent).  A source hands rays to idle lanes and takes finished hits back.
+// Spheres (constant memory) are tested when a ray is loaded and bound the walk.
+struct SphereBound {
+  int sphere;  // index of the closest sphere or -1
+  __device__ __forceinline__ float bound(const SceneView& scene, const Ray& ray) {
+    const HitRecord h = ConstList::closest(scene, ray, true);
+    sphere = h.prim;  // c_scene.n_tris == 0 on this path: prim = sphere index
+    return sphere >= 0 ? h.t : CUDART_MAX_NORMAL_F;
+  }
+  __device__ __forceinline__ HitRecord resolve(const SceneView& scene, const HitRecord& hit, bool found) const {
+    HitRecord out;
+    out.prim = found ? hit.prim : (sphere >= 0 ? scene.n_tris + sphere : -1);
+    out.t = out.prim < 0 ? CUDART_NAN_F : hit.t;
+    return out;
+  }
+};
+
+struct ExtendSource {
+  const RenderArgs& args;
+  SphereBound spheres;
+  __device__ __forceinline__ uint32_t count() const { return args.pool.n_slots; }
+  __device__ __forceinline__ bool load(uint32_t i, Ray& ray, float& t_best) {
+    const float4* r = args.pool.ray + 2 * static_cast<size_t>(i);
+    const float4 o = r[0];
+    if (o.w == 0.0f) {  // no path in this slot
+      args.pool.hit[i] = make_float2(CUDART_NAN_F, __int_as_float(-2));
+      return false;
+    }
+    ray.o = v3(o);
+    ray.d = v3(r[1]);
+    t_best = spheres.bound(args.scene, ray);
+    return true;
+  }
+  __device__ __forceinline__ void store(uint32_t i, const HitRecord& hit, bool found) const {
+    const HitRecord out = spheres.resolve(args.scene, hit, found);
+    args.pool.hit[i] = make_float2(out.t, __int_as_float(out.prim));
+  }
+};
+
+template <>
+__global__ void __launch_bounds__(kBlock) extend_kernel<WideBvh>(const RenderArgs args) {
+  ExtendSource source{args, {-1}};
+  WideBvh::trace_persistent<false>(args.scene, source, &args.ctl->cursor_extend);
+}
+
+struct CastSource {
+  const SceneView& scene;
+  const float4* ray_o;
+  const float4* ray_d;
+  float4* hits;
+  uint32_t n;
+  SphereBound spheres;
+  __device__ __forceinline__ uint32_t count() const { return n; }
+  __device__ __forceinline__ bool load(uint32_t i, Ray& ray, float& t_best) {
+    ray.o = v3(ray_o[i]);
+    ray.d = v3(ray_d[i]);
+    t_best = spheres.bound(scene, ray);
+    return true;
+  }
+  __device__ __forceinline__ void store(uint32_t i, const HitRecord& hit, bool found) const {
+    const HitRecord out = spheres.resolve(scene, hit, found);
+    hits[i] = make_float4(out.t, __int_as_float(out.prim), 0.0f, 0.0f);
+  }
+};
+
+__global__ void __launch_bounds__(kBlock) cast_bvh_kernel(const SceneView scene, const float4* __restrict__ ray_o,
+                                                          const float4* __restrict__ ray_d, uint32_t n,
+                                                          float4* __restrict__ hits, unsigned int* cursor) {
+  CastSource source{scene, ray_o, ray_d, hits, n, {-1}};
+  WideBvh::trace_persistent<false>(scene, source, cursor);
 }
 
 // ---------------------------------------------------------------------------------
@@ -557,17 +642,49 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
 template <class Accel>
 __global__ void __launch_bounds__(kBlock) connect_kernel(const RenderArgs args) {
   const uint32_t j = blockIdx.x * kBlock + threadIdx.x;
-  if (j >= args.ctl->n_shadow) return;
-  const uint32_t slot = args.pool.q_shadow[j];
-  const float4 o = args.pool.ray[2 * static_cast<size_t>(slot)];
-  const float4* in = args.pool.shadow + 2 * static_cast<size_t>(slot);
-  const float4 d = in[0];
+  const uint32_t n_shadow = args.ctl->n_shadow;
+  if (blockIdx.x * kBlock >= n_shadow) return;  // whole block idle (block-uniform exit)
+  const bool active = j < n_shadow;
+  float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
+  const float4* in = args.pool.shadow;
+  if (active) {
+    const uint32_t slot = args.pool.q_shadow[j];
+    o = args.pool.ray[2 * static_cast<size_t>(slot)];
+    in += 2 * static_cast<size_t>(slot);
+    d = in[0];
+  }
   Ray ray;
   ray.o = v3(o);
   ray.d = v3(d);
-  if (Accel::occluded(args.scene, ray, d.w)) return;
+  if (Accel::occluded(args.scene, ray, d.w, active) || !active) return;
   const float4 c = in[1];
   film_add(args.film, __float_as_uint(c.w), v3(c));
+}
+
+struct ConnectSource {
+  const RenderArgs& args;
+  uint32_t slot;
+  __device__ __forceinline__ uint32_t count() const { return args.ctl->n_shadow; }
+  __device__ __forceinline__ bool load(uint32_t j, Ray& ray, float& t_best) {
+    slot = args.pool.q_shadow[j];
+    const float4 o = args.pool.ray[2 * static_cast<size_t>(slot)];
+    const float4 d = args.pool.shadow[2 * static_cast<size_t>(slot)];
+    ray.o = v3(o);
+    ray.d = v3(d);
+    t_best = d.w;
+    return !ConstList::occluded(args.scene, ray, d.w, true);  // a sphere in the way: nothing to add
+  }
+  __device__ __forceinline__ void store(uint32_t, const HitRecord&, bool found) const {
+    if (found) return;
+    const float4 c = args.pool.shadow[2 * static_cast<size_t>(slot) + 1];
+    film_add(args.film, __float_as_uint(c.w), v3(c));
+  }
+};
+
+template <>
+__global__ void __launch_bounds__(kBlock) connect_kernel<WideBvh>(const RenderArgs args) {
+  ConnectSource source{args, 0u};
+  WideBvh::trace_persistent<true>(args.scene, source, &args.ctl->cursor_connect);
 }
 
 // Accumulator::Mean (include/amber/prelude/accumulator.h:88-95): film / samples,
