@@ -21,7 +21,7 @@ namespace amber_cuda {
 
 constexpr int kBvhStackMax = 160;  // entries per lane the 227 KB of shared memory allow at 256 threads + margin
 #ifndef AMBER_BVH_REFILL_LANES
-#define AMBER_BVH_REFILL_LANES 12
+#define AMBER_BVH_REFILL_LANES 20
 #endif
 #ifndef AMBER_BVH_MIN_DESCEND_LANES
 #define AMBER_BVH_MIN_DESCEND_LANES 12
