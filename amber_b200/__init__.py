@@ -4,8 +4,8 @@ Only what that path needs: ``csrc/`` (CUDA kernels + the C ABI of
 ``include/amber_cuda.h``), ``scene`` (flat scene description with the reference's
 factory verbs), ``render`` (Sensor / Context / CudaPathTracing: the host-side mirror
 of ``rendering::Algorithm<RGB>::Render``), ``dist`` (sample partition + film
-all-reduce).  The product never imports ``oracle/``.
+all-reduce), ``image_io`` (PNG / PFM output of the resolved film).  The product never imports ``oracle/``.
 """
-from . import capi, scene  # noqa: F401
+from . import capi, image_io, scene  # noqa: F401
 from .render import Context, CudaPathTracing, Device, Sensor  # noqa: F401
 from .scene import FlatScene, FlatSceneBuilder, cornel_box, cornel_mesh  # noqa: F401

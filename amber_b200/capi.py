@@ -30,6 +30,7 @@ SYMBOLS = (
     "amber_cuda_film_clear",
     "amber_cuda_render",
     "amber_cuda_resolve",
+    "amber_cuda_resolve_ldr",
     "amber_cuda_film_device",
     "amber_cuda_film_set_samples",
     "amber_cuda_cast",
@@ -131,6 +132,7 @@ def load(path: str | None = None) -> C.CDLL:
         "amber_cuda_film_clear": [vp],
         "amber_cuda_render": [vp, C.POINTER(RenderParams)],
         "amber_cuda_resolve": [vp, vp, C.POINTER(u64)],
+        "amber_cuda_resolve_ldr": [vp, vp, C.c_int, C.POINTER(u64)],
         "amber_cuda_film_device": [vp, C.POINTER(vp), C.POINTER(u64), C.POINTER(u64)],
         "amber_cuda_film_set_samples": [vp, u64],
         "amber_cuda_cast": [vp, vp, vp, u64, vp, vp],

@@ -92,6 +92,7 @@ struct amber_cuda_ctx {
   // film
   DeviceBuffer<float4> d_film;
   DeviceBuffer<float> d_resolved;
+  DeviceBuffer<uint8_t> d_resolved8;
   uint64_t samples_done = 0;
 
   // path pool
@@ -454,7 +455,7 @@ int amber_cuda_destroy(amber_cuda_ctx* ctx) {
   ctx->d_tri_shade.release(); ctx->d_tri_isect.release(); ctx->d_spheres.release();
   ctx->d_tri_material.release(); ctx->d_sphere_material.release(); ctx->d_internal_to_prim.release();
   ctx->d_materials.release(); ctx->d_lights.release(); ctx->d_bvh_nodes.release();
-  ctx->d_film.release(); ctx->d_resolved.release();
+  ctx->d_film.release(); ctx->d_resolved.release(); ctx->d_resolved8.release();
   ctx->d_ray.release(); ctx->d_state.release(); ctx->d_hit.release(); ctx->d_shadow.release();
   ctx->d_q_new.release(); ctx->d_q_shadow.release(); ctx->d_ctl.release(); ctx->d_prim_class.release();
   for (auto& b : ctx->d_scratch_f) b.release();
@@ -860,6 +861,25 @@ int amber_cuda_resolve(amber_cuda_ctx* ctx, float* host_rgb, uint64_t* samples_d
   CUDA_TRY(ctx, cudaMemcpyAsync(host_rgb, ctx->d_resolved.ptr, static_cast<size_t>(n_pixels) * 3 * sizeof(float),
                                 cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (samples_done) *samples_done = ctx->samples_done;
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_resolve_ldr(amber_cuda_ctx* ctx, uint8_t* host_rgb8, int flip_x, uint64_t* samples_done) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
+  if (!host_rgb8) return fail(ctx, AMBER_CUDA_EINVAL, "host_rgb8 is NULL");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const uint32_t width = ctx->camera.sensor.width, height = ctx->camera.sensor.height;
+  const size_t n_pixels = static_cast<size_t>(width) * height;
+  CUDA_TRY(ctx, ctx->d_resolved8.resize(n_pixels * 3));
+  const float inv = ctx->samples_done ? 1.0f / static_cast<float>(ctx->samples_done) : 0.0f;
+  resolve_tonemap_kernel<<<blocks_for(n_pixels), kBlock, 0, ctx->stream>>>(ctx->d_film.ptr, width, height, inv,
+                                                                          flip_x ? 1 : 0, ctx->d_resolved8.ptr);
+  ctx->stats.kernel_launches++;
+  CUDA_TRY(ctx, cudaMemcpyAsync(host_rgb8, ctx->d_resolved8.ptr, n_pixels * 3, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CUDA_TRY(ctx, cudaGetLastError());
   if (samples_done) *samples_done = ctx->samples_done;
   return AMBER_CUDA_OK;
 }

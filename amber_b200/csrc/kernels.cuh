@@ -699,6 +699,40 @@ __global__ void __launch_bounds__(kBlock) resolve_kernel(const float4* __restric
   rgb[3 * i + 2] = v.z * inv_samples;
 }
 
+// Resolve fused with the reference's post-process (src/amber/cli/application.cc:98-106):
+// film / samples -> Filmic (src/amber/postprocess/filmic.cc:28-67: Hable's curve, exposure 16,
+// white point 0.70) -> Gamma 2.2 (src/amber/postprocess/gamma.cc:36-52) -> 8 bit.  The curve is
+// evaluated with the host's float operations one by one; only powf can differ from glibc's by
+// an ulp, i.e. by one 8-bit level on the rare value that sits on a level boundary.  flip_x
+// mirrors columns as ExportPNG does (src/amber/cli/image.cc:59-71, `Width - i - 1`).
+__device__ __forceinline__ float filmic_map(float h) {
+  const float kA = 0.22f, kB = 0.30f, kC = 0.10f, kD = 0.20f, kE = 0.01f, kF = 0.30f;
+  const float num = __fadd_rn(__fmul_rn(h, __fadd_rn(__fmul_rn(h, kA), __fmul_rn(kB, kC))), __fmul_rn(kD, kE));
+  const float den = __fadd_rn(__fmul_rn(h, __fadd_rn(__fmul_rn(h, kA), kB)), __fmul_rn(kD, kF));
+  return __fsub_rn(__fdiv_rn(num, den), __fdiv_rn(kE, kF));
+}
+
+__device__ __forceinline__ uint8_t tonemap_channel(float value, float white) {
+  const float mapped = __fdiv_rn(filmic_map(__fmul_rn(value, 16.0f)), white);
+  const float p = powf(mapped, __fdiv_rn(1.0f, 2.2f));
+  const float clamped = p < 1.0f ? p : 1.0f;  // std::min<float>(1, p): a NaN becomes 1
+  return static_cast<uint8_t>(__fmul_rn(255.0f, clamped));
+}
+
+__global__ void __launch_bounds__(kBlock) resolve_tonemap_kernel(const float4* __restrict__ film, uint32_t width,
+                                                                 uint32_t height, float inv_samples, int flip_x,
+                                                                 uint8_t* __restrict__ rgb8) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= width * height) return;
+  const uint32_t x = i % width, y = i / width;
+  const float4 v = film[i];
+  const float white = filmic_map(0.70f);
+  const uint32_t out = (flip_x ? width - 1 - x : x) + y * width;
+  rgb8[3 * out + 0] = tonemap_channel(v.x * inv_samples, white);
+  rgb8[3 * out + 1] = tonemap_channel(v.y * inv_samples, white);
+  rgb8[3 * out + 2] = tonemap_channel(v.z * inv_samples, white);
+}
+
 // ---------------------------------------------------------------------------------
 // helpers for the host-buffer entry points
 __global__ void pack_rays_kernel(const float* __restrict__ o3, const float* __restrict__ d3, uint64_t n,

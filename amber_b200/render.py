@@ -135,6 +135,16 @@ class Device:
         self._check(self.lib.amber_cuda_resolve(self.ctx, out.ctypes.data_as(C.c_void_p), C.byref(done)))
         return out, done.value
 
+    def resolve_ldr(self, flip_x: bool = False) -> tuple[np.ndarray, int]:
+        """Mean image through Filmic + Gamma, 8-bit RGB (H, W, 3): what the reference writes as
+        ``<output>.png`` (``src/amber/cli/application.cc:98-106``); ``flip_x`` mirrors the
+        columns as its ``ExportPNG`` does."""
+        assert self.sensor is not None
+        out = np.empty((self.sensor.height, self.sensor.width, 3), dtype=np.uint8)
+        done = C.c_uint64()
+        self._check(self.lib.amber_cuda_resolve_ldr(self.ctx, out.ctypes.data_as(C.c_void_p), int(flip_x), C.byref(done)))
+        return out, done.value
+
     def film_device(self) -> tuple[int, int, int]:
         ptr, n, done = C.c_void_p(), C.c_uint64(), C.c_uint64()
         self._check(self.lib.amber_cuda_film_device(self.ctx, C.byref(ptr), C.byref(n), C.byref(done)))

@@ -169,6 +169,14 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
  * samples_done may be NULL. */
 int amber_cuda_resolve(amber_cuda_ctx* ctx, float* host_rgb, uint64_t* samples_done);
 
+/* Mean image through the reference's post-process, to the host as 8-bit RGB:
+ * host_rgb8[(x + y*W)*3 + c] = Gamma(2.2)(Filmic(film / samples)), the image the reference
+ * writes as <output>.png.  Replaces postprocess::Filmic::operator()
+ * (src/amber/postprocess/filmic.cc:28-67) and postprocess::Gamma::operator()
+ * (src/amber/postprocess/gamma.cc:36-52) as applied at src/amber/cli/application.cc:98-106.
+ * flip_x != 0 mirrors the columns as ExportPNG does (src/amber/cli/image.cc:59-71). */
+int amber_cuda_resolve_ldr(amber_cuda_ctx* ctx, uint8_t* host_rgb8, int flip_x, uint64_t* samples_done);
+
 /* The raw (un-normalised) device film: W*H float4 (r,g,b,unused) sums and the sample
  * count, for the multi-GPU film reduction done by the host (NCCL all-reduce over
  * this buffer, then amber_cuda_film_set_samples). */

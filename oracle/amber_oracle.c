@@ -857,3 +857,26 @@ int oracle_trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float film
   }
   return n;
 }
+
+/* ---- post-process: Filmic + Gamma -> 8 bit (row N4) ------------------------------------
+ * Filmic::operator() / Filmic::Map, src/amber/postprocess/filmic.cc:28-67: Hable's curve with
+ * exposure 16 and white point 0.70, every operation in float (hdr_value_type = std::float_t);
+ * Gamma::operator(), src/amber/postprocess/gamma.cc:36-52: 255 * min(1, pow(x, 1 / 2.2)),
+ * truncated to uint_fast8_t.  A NaN (pow of a tiny negative Map value) becomes 255 through
+ * std::min's operand order, as in the reference. */
+static float filmic_map(float h) {
+  const float kA = 0.22f, kB = 0.30f, kC = 0.10f, kD = 0.20f, kE = 0.01f, kF = 0.30f;
+  return (h * (h * kA + kB * kC) + kD * kE) / (h * (h * kA + kB) + kD * kF) - kE / kF;
+}
+
+void oracle_tonemap(uint64_t n_values, const float* hdr, uint8_t* ldr) {
+  const float kW = 0.70f, kExposure = 16.0f, gamma = 2.2f;
+  const float white = filmic_map(kW);
+  uint64_t i;
+  for (i = 0; i < n_values; i++) {
+    const float mapped = filmic_map(hdr[i] * kExposure) / white;
+    const float p = powf(mapped, 1 / gamma);
+    const float clamped = p < 1.0f ? p : 1.0f; /* std::min<float>(1, p) */
+    ldr[i] = (uint8_t)(255 * clamped);
+  }
+}

@@ -48,6 +48,9 @@ void oracle_render(const oracle_scene* scene, uint32_t w, uint32_t h, float film
                    uint64_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_depth,
                    int estimator, int threads, float* rgb, uint64_t* stats);
 
+/* Filmic (exposure 16) + Gamma (2.2) + 8-bit truncation of n_values floats (any layout). */
+void oracle_tonemap(uint64_t n_values, const float* hdr, uint8_t* ldr);
+
 /* test hooks: the Philox stream itself, and the fixed ray set of the intersection-parity
  * test (n camera rays followed by n secondary rays). */
 void oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);

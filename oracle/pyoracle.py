@@ -141,6 +141,27 @@ class Reference:
         return rgb, {"rays": stats[0], "truncated": stats[1]}
 
 
+def reference_tonemap(rgb):
+    """Gamma()(Filmic()(image)) of the unmodified reference; rgb (h, w, 3) float32 -> uint8."""
+    lib = C.CDLL(REF_LIB)
+    rgb = _f32(rgb)
+    h, w = rgb.shape[:2]
+    out = np.empty((h, w, 3), dtype=np.uint8)
+    assert lib.ref_tonemap(C.c_uint32(w), C.c_uint32(h), _ptr(rgb), _ptr(out)) == 0
+    return out
+
+
+def oracle_tonemap(rgb):
+    """The C restatement of the same post-process (oracle_tonemap)."""
+    if not os.path.exists(ORACLE_LIB):
+        build(ref=False)
+    lib = C.CDLL(ORACLE_LIB)
+    rgb = _f32(rgb)
+    out = np.empty(rgb.shape, dtype=np.uint8)
+    lib.oracle_tonemap(C.c_uint64(rgb.size), _ptr(rgb), _ptr(out))
+    return out
+
+
 def reference_available() -> bool:
     return os.path.exists(REF_LIB)
 

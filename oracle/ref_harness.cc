@@ -22,6 +22,8 @@
 #include <vector>
 
 #include "amber/etude/cornel_box.h"
+#include "amber/postprocess/filmic.h"
+#include "amber/postprocess/gamma.h"
 #include "amber/prelude/hit.h"
 #include "amber/prelude/image.h"
 #include "amber/prelude/matrix4.h"
@@ -437,6 +439,30 @@ int ref_render_stream(void* handle, uint32_t w, uint32_t h, float film_w, float 
   if (stats) {
     stats[0] = total_rays;
     stats[1] = total_truncated;
+  }
+  return 0;
+}
+
+
+// The reference's post-process as src/amber/cli/application.cc:98-106 applies it:
+// Gamma()(Filmic()(image)).  rgb: w*h*3 floats (x + y*w), ldr: the same layout, 8 bit.
+int ref_tonemap(uint32_t w, uint32_t h, const float* rgb, uint8_t* ldr) {
+  postprocess::HDRImage image(w, h);
+  for (uint32_t y = 0; y < h; y++) {
+    for (uint32_t x = 0; x < w; x++) {
+      const float* in = rgb + (static_cast<size_t>(x) + static_cast<size_t>(y) * w) * 3;
+      image[prelude::Pixel(x, y)] = postprocess::HDR(in[0], in[1], in[2]);
+    }
+  }
+  const auto out = postprocess::Gamma()(postprocess::Filmic()(image));
+  for (uint32_t y = 0; y < h; y++) {
+    for (uint32_t x = 0; x < w; x++) {
+      const auto& value = out[prelude::Pixel(x, y)];
+      uint8_t* o = ldr + (static_cast<size_t>(x) + static_cast<size_t>(y) * w) * 3;
+      o[0] = value.X();
+      o[1] = value.Y();
+      o[2] = value.Z();
+    }
   }
   return 0;
 }

@@ -44,8 +44,23 @@ def unit(rng, n):
     return (v / np.linalg.norm(v, axis=1, keepdims=True)).astype(np.float32)
 
 
+def tonemap_fixture():
+    """6. post-process (row N4): Gamma()(Filmic()(image)) of the reference on a value ramp that
+    covers black, the toe, the shoulder, level boundaries and overflow."""
+    rng = np.random.default_rng(20261104)
+    values = np.concatenate([np.zeros(6), 10.0 ** rng.uniform(-9, 2, 6000), np.linspace(0, 0.25, 2988),
+                             [1e30, 3.0e38, 1e-30, 1e-38, 0.5, 1.0]]).astype(np.float32)
+    hdr = values.reshape(50, 60, 3)
+    ldr = pyoracle.reference_tonemap(hdr)
+    np.savez_compressed(os.path.join(GOLDEN, "tonemap.npz"), hdr=hdr, ldr=ldr)
+    print("tonemap: levels used", np.unique(ldr).size)
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "tonemap":
+        tonemap_fixture()  # (the statistics of section 5 are not reproducible: do not regenerate them casually)
+        return
     flat = scene.cornel_box()
     ref = pyoracle.Reference(flat)
     builtin = pyoracle.Reference(builtin_cornel_box=True)
@@ -115,6 +130,7 @@ def main():
         json.dump({"width": w, "height": w, "spp": spp, "runs": k_runs, "pt_means": means,
                    "pt_mean": float(np.mean(means)), "pt_std_of_run": float(np.std(means, ddof=1)),
                    "bdpt_mean": float(bdpt.mean()), "bdpt_spp": 1024, "bdpt_seconds": seconds}, f, indent=1)
+    tonemap_fixture()
     print("pt mean", np.mean(means), "+-", np.std(means, ddof=1) / np.sqrt(k_runs), "bdpt mean", bdpt.mean(),
           f"({seconds:.1f}s)")
 

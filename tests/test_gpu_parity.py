@@ -242,6 +242,52 @@ def test_bvh_path_matches_oracle(device, oracle_lib):
         assert image_agreement(image, want) >= 0.985
 
 
+def test_bvh_full_size_mesh_against_brute_force(device, oracle_lib):
+    """Config 4's geometry at full size (1 310 720-triangle displaced icosphere + room): the
+    persistent BVH traversal against the oracle's brute-force scan on a ray set small enough
+    for the CPU (4000 rays x 1.3 M triangles), plus whole-render invariants."""
+    from amber_b200 import Sensor, cornel_mesh
+    scene = cornel_mesh(subdivisions=8)
+    oracle = oracle_lib.Oracle(scene)
+    device.upload_scene(scene)
+    device.set_sensor(Sensor(256, 256))
+    stats = device.stats()
+    assert stats["accel"] == 1 and stats["bvh_nodes"] > 100000
+    # 2000 camera rays + 2000 secondary rays leaving the surfaces those hit (the recipe of the
+    # fixed ray set, with the brute-force casts spread over the host threads)
+    rng = np.random.default_rng(99)
+    n = 2000
+    co, cd, _ = oracle.eye_rays(256, 256, *FILM, rng.integers(0, 256, n), rng.integers(0, 256, n),
+                                rng.random((n, 5), dtype=np.float32))
+    cprim, ct = oracle.cast(co, cd, threads=32)
+    hit = cprim >= 0
+    so = (co + ct[:, None] * cd)[hit].astype(np.float32)
+    sd = unit_vectors(rng, int(hit.sum()))
+    o, d = np.concatenate([co, so]), np.concatenate([cd, sd])
+    want_prim, want_t = oracle.cast(o, d, threads=32)
+    prim, t = device.cast(o, d)
+    # 4000 rays cannot resolve 99.99 %: at most one disagreement, and t within tolerance
+    agree = prim == want_prim
+    assert (~agree).sum() <= 1, f"{(~agree).sum()} hit ids differ"
+    both = agree & (want_prim >= 0)
+    # 1e-4 relative + an absolute floor of 2e-6 (a few ulp of the unit-scale coordinates): the
+    # secondary rays start a rounding error away from a 3 mm triangle of a bumpy surface and
+    # re-hit its neighbours at t ~ 1e-6..1e-3, where both sides' t is cancellation noise
+    err = np.abs(t[both] - want_t[both])
+    assert np.all(err <= T_RTOL * want_t[both] + 2e-6), f"max abs t error {err.max():.3e}"
+    assert (err <= T_RTOL * want_t[both]).mean() >= 0.99
+    assert (want_prim[:n] >= 18).mean() > 0.05  # the mesh itself is being hit, not only the room
+    # a render through the wavefront: path count exact, batching invariance
+    device.render(0, 4, seed=2, max_depth=16, estimator=1)
+    a, _ = device.resolve()
+    assert device.stats()["paths"] == 4 * 256 * 256
+    device.film_clear()
+    device.render(0, 1, seed=2, max_depth=16, estimator=1)
+    device.render(1, 3, seed=2, max_depth=16, estimator=1, pool_paths=4096)
+    b, _ = device.resolve()
+    assert np.isfinite(a).all() and np.allclose(a, b, rtol=1e-4, atol=1e-7 * a.mean())
+
+
 def test_full_size_properties(cornell_device):
     """Config 2 geometry (Cornell 1024x1024) at a few spp: properties that do not need an
     oracle run of that size."""
@@ -274,6 +320,28 @@ def test_full_size_properties(cornell_device):
         return float(np.minimum(lum, np.percentile(lum, 90)).mean())
     ratio = robust_mean(small) / robust_mean(a)
     assert 3.6 < ratio < 4.4, ratio
+    cornell_device.set_sensor(Sensor(64, 64))
+
+
+def test_tonemapped_resolve_matches_the_reference_postprocess(cornell_device, oracle_lib, tmp_path):
+    """Row N4: resolve fused with Filmic + Gamma against the oracle's restatement (pinned bit for
+    bit to the reference) applied to the float image of the same film; and the exported files."""
+    from amber_b200 import Sensor, image_io
+    cornell_device.set_sensor(Sensor(96, 64))
+    cornell_device.render(0, 64, seed=4, max_depth=32, estimator=1)
+    hdr, _ = cornell_device.resolve()
+    ldr, done = cornell_device.resolve_ldr()
+    want = oracle_lib.oracle_tonemap(hdr)
+    assert done == 64 and ldr.shape == (64, 96, 3)
+    diff = np.abs(ldr.astype(np.int16) - want.astype(np.int16))
+    # device powf vs glibc powf: at most one 8-bit level, on values that sit on a level boundary
+    assert diff.max() <= 1 and (diff > 0).mean() < 2e-3, (diff.max(), (diff > 0).mean())
+    assert np.unique(want).size > 100  # the frame spans the curve, not just black and white
+    flipped, _ = cornell_device.resolve_ldr(flip_x=True)
+    assert np.array_equal(flipped, ldr[:, ::-1])
+    png, pfm = image_io.export(cornell_device, str(tmp_path / "render"))
+    assert np.array_equal(image_io.read_png(png), flipped)
+    assert np.array_equal(image_io.read_pfm(pfm), hdr[:, ::-1])
     cornell_device.set_sensor(Sensor(64, 64))
 
 

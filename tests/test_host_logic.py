@@ -134,3 +134,15 @@ def test_sample_partition_and_film_reduce_over_gloo(tmp_path, oracle_lib):
     outs = [p.communicate(timeout=300)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), "\n".join(outs)
     assert "PARTITION_OK" in outs[0]
+
+
+def test_image_files_round_trip(tmp_path):
+    """PNG / PFM writers of amber_b200.image_io (the reference's exporters need OpenCV)."""
+    from amber_b200 import image_io
+    rng = np.random.default_rng(2)
+    ldr = rng.integers(0, 256, size=(37, 53, 3), dtype=np.uint8)
+    hdr = rng.random((37, 53, 3), dtype=np.float32) * 1e3
+    image_io.write_png(str(tmp_path / "a.png"), ldr)
+    image_io.write_pfm(str(tmp_path / "a.pfm"), hdr)
+    assert np.array_equal(image_io.read_png(str(tmp_path / "a.png")), ldr)
+    assert np.array_equal(image_io.read_pfm(str(tmp_path / "a.pfm")), hdr)

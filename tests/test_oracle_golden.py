@@ -95,3 +95,11 @@ def test_estimators_agree_in_expectation(oracle_lib):
 def test_reference_luminance_statistics_are_recorded():
     stats = json.load(open(os.path.join(GOLDEN, "cornell_luminance.json")))
     assert stats["runs"] == 16 and len(stats["pt_means"]) == 16
+
+
+def test_tonemap_matches_reference(oracle_lib):
+    """Row N4: Filmic + Gamma + 8-bit truncation, bit for bit on the reference's golden ramp."""
+    g = golden("tonemap.npz")
+    ldr = oracle_lib.oracle_tonemap(g["hdr"])
+    assert np.array_equal(ldr, g["ldr"])
+    assert g["ldr"].min() == 0 and g["ldr"].max() == 255 and np.unique(g["ldr"]).size == 256

@@ -72,3 +72,11 @@ def test_images_bit_exact_including_depth_cap(reference, oracle):
         assert sa["rays"] == sb["closest_rays"] and sa["truncated"] == sb["truncated"]
         if depth:
             assert sb["truncated"] > 0
+
+
+def test_tonemap_bit_exact(reference, oracle_lib):
+    """Gamma()(Filmic()(image)) of the compiled reference against the C restatement."""
+    rng = np.random.default_rng(8)
+    hdr = (10.0 ** rng.uniform(-10, 3, size=(64, 96, 3))).astype(np.float32)
+    hdr[0, :8] = 0.0
+    assert np.array_equal(oracle_lib.reference_tonemap(hdr), oracle_lib.oracle_tonemap(hdr))
