@@ -6,6 +6,6 @@ factory verbs), ``render`` (Sensor / Context / CudaPathTracing: the host-side mi
 of ``rendering::Algorithm<RGB>::Render``), ``dist`` (sample partition + film
 all-reduce), ``image_io`` (PNG / PFM output of the resolved film).  The product never imports ``oracle/``.
 """
-from . import capi, image_io, scene  # noqa: F401
+from . import capi, image_io, importer, scene  # noqa: F401
 from .render import Context, CudaPathTracing, Device, Sensor  # noqa: F401
 from .scene import FlatScene, FlatSceneBuilder, cornel_box, cornel_mesh  # noqa: F401
