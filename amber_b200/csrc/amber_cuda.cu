@@ -175,12 +175,20 @@ void make_triangle(const float* v, TriIsect& isect, TriShade& shade) {
 
 
 // Batches the triangles of a small scene by supporting plane for the constant-memory list.
-// `tri_ids` (creation-order ids) is permuted so that each group is contiguous: groups in order
-// of their first member; inside a group the parallelogram pairs (earlier triangle first, so a
+// `tri_ids` (creation-order ids) is permuted so that each group is contiguous: the planes
+// perpendicular to x, then y, then z (AxisPlane: no dot products), then the other groups, each in
+// order of their first member; inside a group the parallelogram pairs (earlier triangle first, so a
 // hit on the shared diagonal goes to it, as in a creation-order scan), then the lone
 // triangles.  All geometry is evaluated in double from the float vertices.
-void group_by_plane(const amber_cuda_primitive* prims, std::vector<uint32_t>& tri_ids,
-                    std::vector<PlaneGroup>& groups, std::vector<PlaneEntry>& entries) {
+struct ConstListHost {
+  std::vector<AxisPlane> axis_planes;
+  std::vector<AxisEntry> axis_entries;
+  int32_t n_axis_planes[3] = {0, 0, 0};
+  std::vector<PlaneGroup> groups;
+  std::vector<PlaneEntry> entries;
+};
+
+void group_by_plane(const amber_cuda_primitive* prims, std::vector<uint32_t>& tri_ids, ConstListHost& out) {
   struct D3 { double x, y, z; };
   auto sub = [](D3 a, D3 b) { return D3{a.x - b.x, a.y - b.y, a.z - b.z}; };
   auto cross = [](D3 a, D3 b) { return D3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; };
@@ -219,25 +227,30 @@ void group_by_plane(const amber_cuda_primitive* prims, std::vector<uint32_t>& tr
     found[home].members.push_back(id);
   }
   auto same = [](D3 a, D3 b) { return a.x == b.x && a.y == b.y && a.z == b.z; };
-  auto entry_for = [&](D3 corner, D3 e1, D3 e2, D3 anchor) {
-    const D3 n = cross(e1, e2);
+  auto comp = [](D3 a, int k) { return k == 0 ? a.x : k == 1 ? a.y : a.z; };
+  struct Corner { D3 r, e1, e2; };  // u = nu.(x - r), v = nv.(x - r) with nu, nv from e1, e2
+  auto edge_vectors = [&](const Corner& c, D3& nu, D3& nv) {
+    const D3 n = cross(c.e1, c.e2);
     const double nn = dot(n, n);
-    D3 nu = cross(e2, n), nv = cross(n, e1);
+    nu = cross(c.e2, n);
+    nv = cross(n, c.e1);
     nu = D3{nu.x / nn, nu.y / nn, nu.z / nn};
     nv = D3{nv.x / nn, nv.y / nn, nv.z / nn};
-    const D3 rel = sub(corner, anchor);
-    PlaneEntry t;
-    t.nu_cu = make_float4((float)nu.x, (float)nu.y, (float)nu.z, (float)-dot(nu, rel));
-    t.nv_cv = make_float4((float)nv.x, (float)nv.y, (float)nv.z, (float)-dot(nv, rel));
-    return t;
   };
-  tri_ids.clear();
+  struct Batch { int axis; std::vector<Corner> quads, tris; std::vector<uint32_t> quad_ids, lone_ids; };
+  std::vector<Batch> batches;
   for (const Group& G : found) {
     // pair up triangles that form a parallelogram: A = (r, p, q), B = {p, q, p + q - r}
     const size_t m = G.members.size();
     std::vector<int> partner(m, -1);
-    std::vector<PlaneEntry> quad_entries, tri_entries;
-    std::vector<uint32_t> quad_ids, lone_ids;
+    Batch batch;
+    batch.axis = -1;
+    for (int k = 0; k < 3 && batch.axis < 0; k++) {  // every vertex has the anchor's k-coordinate exactly
+      bool flat = G.scale > 0 && comp(G.unit_n, k) != 0;
+      for (size_t i = 0; i < m && flat; i++)
+        for (int c = 0; c < 3; c++) flat = flat && comp(vertex(G.members[i], c), k) == comp(G.anchor, k);
+      if (flat) batch.axis = k;
+    }
     for (size_t a = 0; a < m; a++) {
       if (partner[a] >= 0) continue;
       const D3 A[3] = {vertex(G.members[a], 0), vertex(G.members[a], 1), vertex(G.members[a], 2)};
@@ -256,28 +269,75 @@ void group_by_plane(const amber_cuda_primitive* prims, std::vector<uint32_t>& tr
           if (std::sqrt(dot(diff, diff)) > 1e-6 * G.scale) continue;
           partner[a] = static_cast<int>(b);
           partner[b] = static_cast<int>(a);
-          quad_entries.push_back(entry_for(r, sub(p, r), sub(q, r), G.anchor));
-          quad_ids.push_back(G.members[a]);
-          quad_ids.push_back(G.members[b]);
+          batch.quads.push_back({r, sub(p, r), sub(q, r)});
+          batch.quad_ids.push_back(G.members[a]);
+          batch.quad_ids.push_back(G.members[b]);
         }
       }
       if (partner[a] < 0) {
-        const D3 v0 = A[0];
-        tri_entries.push_back(entry_for(v0, sub(A[1], v0), sub(A[2], v0), G.anchor));
-        lone_ids.push_back(G.members[a]);
+        batch.tris.push_back({A[0], sub(A[1], A[0]), sub(A[2], A[0])});
+        batch.lone_ids.push_back(G.members[a]);
       }
     }
-    PlaneGroup out;
-    const int32_t firsts = static_cast<int32_t>(entries.size()) | (static_cast<int32_t>(tri_ids.size()) << 16);
-    const int32_t counts = static_cast<int32_t>(quad_entries.size()) | (static_cast<int32_t>(tri_entries.size()) << 16);
-    out.n_gx = make_float4((float)G.n.x, (float)G.n.y, (float)G.n.z, (float)G.anchor.x);
-    out.g_range = make_float4((float)G.anchor.y, (float)G.anchor.z, __builtin_bit_cast(float, firsts),
-                              __builtin_bit_cast(float, counts));
-    groups.push_back(out);
-    entries.insert(entries.end(), quad_entries.begin(), quad_entries.end());
-    entries.insert(entries.end(), tri_entries.begin(), tri_entries.end());
-    tri_ids.insert(tri_ids.end(), quad_ids.begin(), quad_ids.end());
-    tri_ids.insert(tri_ids.end(), lone_ids.begin(), lone_ids.end());
+    batches.push_back(std::move(batch));
+  }
+
+  // emit: planes perpendicular to x, y, z (AxisPlane), then everything else (PlaneGroup)
+  tri_ids.clear();
+  for (int axis = 0; axis < 3; axis++) {
+    const int ka = (axis + 1) % 3, kb = (axis + 2) % 3;
+    for (size_t g = 0; g < found.size(); g++) {
+      const Batch& B = batches[g];
+      if (B.axis != axis) continue;
+      const Group& G = found[g];
+      AxisPlane plane;
+      plane.g_k = (float)comp(G.anchor, axis);
+      plane.g_a = (float)comp(G.anchor, ka);
+      plane.g_b = (float)comp(G.anchor, kb);
+      plane.ranges = static_cast<int32_t>(out.axis_entries.size()) | (static_cast<int32_t>(tri_ids.size()) << 8) |
+                     (static_cast<int32_t>(B.quads.size()) << 16) | (static_cast<int32_t>(B.tris.size()) << 24);
+      out.axis_planes.push_back(plane);
+      out.n_axis_planes[axis]++;
+      for (const std::vector<Corner>* list : {&B.quads, &B.tris}) {
+        for (const Corner& c : *list) {
+          D3 nu, nv;
+          edge_vectors(c, nu, nv);
+          const D3 rel = sub(c.r, G.anchor);
+          AxisEntry e;
+          e.nu = make_float2((float)comp(nu, ka), (float)comp(nu, kb));
+          e.cu_nv = make_float2((float)-(comp(nu, ka) * comp(rel, ka) + comp(nu, kb) * comp(rel, kb)), (float)comp(nv, ka));
+          e.nv_cv = make_float2((float)comp(nv, kb), (float)-(comp(nv, ka) * comp(rel, ka) + comp(nv, kb) * comp(rel, kb)));
+          out.axis_entries.push_back(e);
+        }
+      }
+      tri_ids.insert(tri_ids.end(), B.quad_ids.begin(), B.quad_ids.end());
+      tri_ids.insert(tri_ids.end(), B.lone_ids.begin(), B.lone_ids.end());
+    }
+  }
+  for (size_t g = 0; g < found.size(); g++) {
+    const Batch& B = batches[g];
+    if (B.axis >= 0) continue;
+    const Group& G = found[g];
+    PlaneGroup group;
+    const int32_t firsts = static_cast<int32_t>(out.entries.size()) | (static_cast<int32_t>(tri_ids.size()) << 16);
+    const int32_t counts = static_cast<int32_t>(B.quads.size()) | (static_cast<int32_t>(B.tris.size()) << 16);
+    group.n_gx = make_float4((float)G.n.x, (float)G.n.y, (float)G.n.z, (float)G.anchor.x);
+    group.g_range = make_float4((float)G.anchor.y, (float)G.anchor.z, __builtin_bit_cast(float, firsts),
+                                __builtin_bit_cast(float, counts));
+    out.groups.push_back(group);
+    for (const std::vector<Corner>* list : {&B.quads, &B.tris}) {
+      for (const Corner& c : *list) {
+        D3 nu, nv;
+        edge_vectors(c, nu, nv);
+        const D3 rel = sub(c.r, G.anchor);
+        PlaneEntry e;
+        e.nu_cu = make_float4((float)nu.x, (float)nu.y, (float)nu.z, (float)-dot(nu, rel));
+        e.nv_cv = make_float4((float)nv.x, (float)nv.y, (float)nv.z, (float)-dot(nv, rel));
+        out.entries.push_back(e);
+      }
+    }
+    tri_ids.insert(tri_ids.end(), B.quad_ids.begin(), B.quad_ids.end());
+    tri_ids.insert(tri_ids.end(), B.lone_ids.begin(), B.lone_ids.end());
   }
 }
 
@@ -522,9 +582,8 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   }
 
   // constant-memory list: batch the triangles by supporting plane (scene_device.cuh, PlaneGroup)
-  std::vector<PlaneGroup> groups;
-  std::vector<PlaneEntry> plane_entries;
-  if (!use_bvh) group_by_plane(scene->primitives, tri_ids, groups, plane_entries);
+  ConstListHost const_list;
+  if (!use_bvh) group_by_plane(scene->primitives, tri_ids, const_list);
 
   const size_t n_tris = tri_ids.size(), n_spheres = sphere_ids.size();
   std::vector<TriIsect> tri_isect(n_tris);
@@ -602,9 +661,12 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   std::memset(&ctx->const_scene, 0, sizeof(ConstScene));
   ctx->const_scene.n_tris = use_bvh ? 0 : static_cast<int32_t>(n_tris);
   ctx->const_scene.n_spheres = static_cast<int32_t>(n_spheres);
-  ctx->const_scene.n_groups = static_cast<int32_t>(groups.size());
-  for (size_t g = 0; g < groups.size(); g++) ctx->const_scene.group[g] = groups[g];
-  for (size_t k = 0; k < plane_entries.size(); k++) ctx->const_scene.entry[k] = plane_entries[k];
+  ctx->const_scene.n_groups = static_cast<int32_t>(const_list.groups.size());
+  for (int axis = 0; axis < 3; axis++) ctx->const_scene.n_axis_planes[axis] = const_list.n_axis_planes[axis];
+  for (size_t g = 0; g < const_list.axis_planes.size(); g++) ctx->const_scene.axis_plane[g] = const_list.axis_planes[g];
+  for (size_t k = 0; k < const_list.axis_entries.size(); k++) ctx->const_scene.axis_entry[k] = const_list.axis_entries[k];
+  for (size_t g = 0; g < const_list.groups.size(); g++) ctx->const_scene.group[g] = const_list.groups[g];
+  for (size_t k = 0; k < const_list.entries.size(); k++) ctx->const_scene.entry[k] = const_list.entries[k];
   for (size_t k = 0; k < n_spheres; k++) ctx->const_scene.sphere[k] = spheres[k];
   ctx->camera.lens = lens;
 
@@ -748,7 +810,7 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
       timed(0, [&] { raygen_kernel<<<grid, kBlock, 0, stream>>>(args); });
       bookkeep_kernel<<<1, 1, 0, stream>>>(args.ctl);
       timed(1, [&] { extend_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args); });
-      timed(2, [&] { shade_kernel<<<shade_grid, kBlock, 0, stream>>>(args); });
+      timed(2, [&] { shade_kernel<<<shade_grid, kShadeBlock, 0, stream>>>(args); });
       if (nee) timed(3, [&] { connect_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args); });
       ctx->stats.kernel_launches += nee ? 5 : 4;
       extend_launches++;

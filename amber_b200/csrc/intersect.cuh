@@ -113,6 +113,79 @@ struct ConstList {
     return found;
   }
 
+  // The planes perpendicular to axis K (scene_device.cuh, AxisPlane).  ok / oa / ob (dk / da / db)
+  // are the ray origin (direction) along K and the two other axes, inv_dk = 1 / dk.  Same
+  // acceptance rules as intersect_group; updates the closest hit in place (kAnyHit: returns as
+  // soon as anything is hit).
+  template <bool kAnyHit>
+  static __device__ __forceinline__ bool scan_axis(int first_plane, int n_planes, float ok, float oa, float ob,
+                                                   float inv_dk, float da, float db, float& t_best, int& prim) {
+    bool any = false;
+    for (int p = first_plane; p < first_plane + n_planes; p++) {
+      const AxisPlane plane = c_scene.axis_plane[p];
+      const float t = (plane.g_k - ok) * inv_dk;
+      bool open = (t > kEpsF) & (t < t_best);
+      const float ha = fmaf(t, da, oa - plane.g_a), hb = fmaf(t, db, ob - plane.g_b);
+      int e = plane.ranges & 0xff, tri = (plane.ranges >> 8) & 0xff;
+      const int quads_end = e + ((plane.ranges >> 16) & 0xff), tris_end = quads_end + ((plane.ranges >> 24) & 0xff);
+      int found = -1;
+      for (; e < quads_end; e++, tri += 2) {
+        const float2 nu = c_scene.axis_entry[e].nu, cu_nv = c_scene.axis_entry[e].cu_nv, nv_cv = c_scene.axis_entry[e].nv_cv;
+        const float s = fmaf(nu.x, ha, fmaf(nu.y, hb, cu_nv.x));
+        const float r = fmaf(cu_nv.y, ha, fmaf(nv_cv.x, hb, nv_cv.y));
+        if (open & (s >= 0.0f) & (s <= 1.0f) & (r >= 0.0f) & (r <= 1.0f)) {
+          found = tri + (s + r > 1.0f ? 1 : 0);
+          open = false;
+        }
+      }
+      for (; e < tris_end; e++, tri++) {
+        const float2 nu = c_scene.axis_entry[e].nu, cu_nv = c_scene.axis_entry[e].cu_nv, nv_cv = c_scene.axis_entry[e].nv_cv;
+        const float u = fmaf(nu.x, ha, fmaf(nu.y, hb, cu_nv.x));
+        const float v = fmaf(cu_nv.y, ha, fmaf(nv_cv.x, hb, nv_cv.y));
+        if (open & (u >= 0.0f) & (v >= 0.0f) & (u + v <= 1.0f)) {
+          found = tri;
+          open = false;
+        }
+      }
+      if (found >= 0) {
+        t_best = t;
+        prim = found;
+        any = true;
+        if (kAnyHit) return true;
+      }
+    }
+    return any;
+  }
+
+  // All constant-memory triangles: axis-perpendicular planes, then the general plane groups.
+  template <bool kAnyHit>
+  static __device__ __forceinline__ bool scan_triangles(const Ray& ray, float& t_best, int& prim) {
+    bool any = false;
+    const int nx = c_scene.n_axis_planes[0], ny = c_scene.n_axis_planes[1], nz = c_scene.n_axis_planes[2];
+    if (nx + ny + nz > 0) {
+      float ix, iy, iz;  // 1 / 0 = inf: t = +-inf or NaN rejects the plane, as n.d == 0 does elsewhere
+      asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ix) : "f"(ray.d.x));
+      asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iy) : "f"(ray.d.y));
+      asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iz) : "f"(ray.d.z));
+      any |= scan_axis<kAnyHit>(0, nx, ray.o.x, ray.o.y, ray.o.z, ix, ray.d.y, ray.d.z, t_best, prim);
+      if (kAnyHit && any) return true;
+      any |= scan_axis<kAnyHit>(nx, ny, ray.o.y, ray.o.z, ray.o.x, iy, ray.d.z, ray.d.x, t_best, prim);
+      if (kAnyHit && any) return true;
+      any |= scan_axis<kAnyHit>(nx + ny, nz, ray.o.z, ray.o.x, ray.o.y, iz, ray.d.x, ray.d.y, t_best, prim);
+      if (kAnyHit && any) return true;
+    }
+    const int n_groups = c_scene.n_groups;
+    for (int g = 0; g < n_groups; g++) {
+      const int k = intersect_group(g, ray, t_best, t_best);
+      if (k >= 0) {
+        prim = k;
+        any = true;
+        if (kAnyHit) return true;
+      }
+    }
+    return any;
+  }
+
   static __device__ __forceinline__ HitRecord closest(const SceneView&, const Ray& ray, bool active) {
     HitRecord hit;
     if (!active) {
@@ -122,11 +195,7 @@ struct ConstList {
     }
     hit.t = CUDART_MAX_NORMAL_F;  // Cast(ray) == Cast(ray, numeric_limits::max), acceleration.h:46-51
     hit.prim = -1;
-    const int n_groups = c_scene.n_groups;
-    for (int g = 0; g < n_groups; g++) {
-      const int k = intersect_group(g, ray, hit.t, hit.t);
-      if (k >= 0) hit.prim = k;
-    }
+    scan_triangles<false>(ray, hit.t, hit.prim);
     const int n_tris = c_scene.n_tris;
     const int n_spheres = c_scene.n_spheres;
     for (int i = 0; i < n_spheres; i++) {
@@ -139,15 +208,14 @@ struct ConstList {
   // true if anything lies in (kEPS, t_max)
   static __device__ __forceinline__ bool occluded(const SceneView&, const Ray& ray, float t_max, bool active) {
     if (!active) return false;
-    bool blocked = false;
-    float t;
-    const int n_groups = c_scene.n_groups;
-    for (int g = 0; g < n_groups; g++) blocked |= intersect_group(g, ray, t_max, t) >= 0;
+    float t = t_max;
+    int prim = -1;
+    if (scan_triangles<true>(ray, t, prim)) return true;
     const int n_spheres = c_scene.n_spheres;
     for (int i = 0; i < n_spheres; i++) {
-      blocked |= intersect_sphere(c_scene.sphere[i], ray, t_max, t);
+      if (intersect_sphere(c_scene.sphere[i], ray, t_max, t)) return true;
     }
-    return blocked;
+    return false;
   }
 };
 

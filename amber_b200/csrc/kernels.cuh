@@ -426,17 +426,21 @@ __device__ __forceinline__ void cp_async_8(void* smem, const void* gmem) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
 __device__ __forceinline__ void cp_async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
-constexpr int kShadeTile = kShadeRounds * kBlock;
+#ifndef AMBER_SHADE_BLOCK
+#define AMBER_SHADE_BLOCK 256
+#endif
+constexpr int kShadeBlock = AMBER_SHADE_BLOCK;  // threads per block of `shade`
+constexpr int kShadeTile = kShadeRounds * kShadeBlock;
 constexpr int kClassMiss = 14;  // hit.prim == -1: the path left the scene, algorithm_pt.cc:140-142
 constexpr int kClassDead = 15;  // hit.prim == -2: slot holds no path
 constexpr int32_t kPrimMiss = -1, kPrimDead = -2;
 
-__global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(const RenderArgs args) {
+__global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(const RenderArgs args) {
   __shared__ uint16_t sorted[kShadeTile];
-  __shared__ float4 stage[2][4][kBlock];  // double-buffered ray.o, ray.d, throughput, path ids
-  __shared__ float2 stage_hit[2][kBlock];
+  __shared__ float4 stage[2][4][kShadeBlock];  // double-buffered ray.o, ray.d, throughput, path ids
+  __shared__ float2 stage_hit[2][kShadeBlock];
   __shared__ uint32_t class_count[16], class_offset[16];
-  __shared__ uint32_t warp_scan[kBlock / 32];
+  __shared__ uint32_t warp_scan[kShadeBlock / 32];
   __shared__ uint32_t queue_base[2];
   const PathPool& pool = args.pool;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -450,7 +454,7 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
   int prims[kShadeRounds];
 #pragma unroll
   for (int r = 0; r < kShadeRounds; r++) {  // all of the tile's hit records in flight at once
-    const uint32_t i = tile_base + r * kBlock + tid;
+    const uint32_t i = tile_base + r * kShadeBlock + tid;
     prims[r] = i < pool.n_slots ? __float_as_int(pool.hit[i].y) : kPrimDead;
   }
 #pragma unroll
@@ -480,7 +484,7 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
 #pragma unroll
   for (int r = 0; r < kShadeRounds; r++) {
     const uint32_t key = (keys[r >> 1] >> ((r & 1) * 16)) & 0xffffu;
-    sorted[class_offset[key >> 12] + (key & 0xfffu)] = static_cast<uint16_t>(r * kBlock + tid);
+    sorted[class_offset[key >> 12] + (key & 0xfffu)] = static_cast<uint16_t>(r * kShadeBlock + tid);
   }
   __syncthreads();
   const uint32_t n_hit = class_offset[kClassMiss];   // entries [0, n_hit): surface vertices
@@ -491,7 +495,7 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
   // with cp.async while it shades round r, so the DRAM latency of the permuted gathers is
   // paid once per tile, not once per round.  Thread-private staging: no barrier involved.
   auto stage_records = [&](int round) {
-    const uint32_t jn = round * kBlock + tid;
+    const uint32_t jn = round * kShadeBlock + tid;
     if (round < kShadeRounds && jn < n_hit) {
       const size_t next = tile_base + sorted[jn];
       const int b = round & 1;
@@ -507,7 +511,7 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
   uint32_t freed_mask = 0, shadow_mask = 0;
 #pragma unroll 1
   for (int r = 0; r < kShadeRounds; r++) {
-    const uint32_t j = r * kBlock + tid;
+    const uint32_t j = r * kShadeBlock + tid;
     if (j >= n_live) break;
     if (j >= n_hit) {  // miss: the slot is free again
       freed_mask |= 1u << r;
@@ -603,15 +607,15 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
   if (lane == 31) warp_scan[warp] = scan;
   __syncthreads();
   if (warp == 0) {
-    const uint32_t total = lane < kBlock / 32 ? warp_scan[lane] : 0u;
+    const uint32_t total = lane < kShadeBlock / 32 ? warp_scan[lane] : 0u;
     uint32_t wscan = total;
 #pragma unroll
-    for (int delta = 1; delta < kBlock / 32; delta <<= 1) {
+    for (int delta = 1; delta < kShadeBlock / 32; delta <<= 1) {
       const uint32_t up = __shfl_up_sync(0xffffffffu, wscan, delta);
       if (lane >= delta) wscan += up;
     }
-    if (lane < kBlock / 32) warp_scan[lane] = wscan - total;
-    if (lane == kBlock / 32 - 1) {
+    if (lane < kShadeBlock / 32) warp_scan[lane] = wscan - total;
+    if (lane == kShadeBlock / 32 - 1) {
       const uint32_t n_freed = wscan & 0xffffu, n_shadow = wscan >> 16;
       queue_base[0] = n_freed ? atomicAdd(&args.ctl->n_new, n_freed) : 0u;
       queue_base[1] = n_shadow ? atomicAdd(&args.ctl->n_shadow, n_shadow) : 0u;
@@ -627,12 +631,12 @@ __global__ void __launch_bounds__(kBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(c
   while (freed_mask) {
     const int r = __ffs(freed_mask) - 1;
     freed_mask &= freed_mask - 1u;
-    pool.q_new[freed_at++] = tile_base + sorted[r * kBlock + tid];
+    pool.q_new[freed_at++] = tile_base + sorted[r * kShadeBlock + tid];
   }
   while (shadow_mask) {
     const int r = __ffs(shadow_mask) - 1;
     shadow_mask &= shadow_mask - 1u;
-    pool.q_shadow[shadow_at++] = tile_base + sorted[r * kBlock + tid];
+    pool.q_shadow[shadow_at++] = tile_base + sorted[r * kShadeBlock + tid];
   }
 }
 

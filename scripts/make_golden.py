@@ -56,8 +56,35 @@ def tonemap_fixture():
     print("tonemap: levels used", np.unique(ldr).size)
 
 
+def mesh_fixture():
+    """7. config 4's geometry at FULL size (1 310 720-triangle displaced icosphere in the room)
+    through the reference's OWN BVH (acceleration_bvh.h; its build takes minutes at this size):
+    20 000 camera rays + the secondary rays leaving the surfaces they hit."""
+    flat = scene.cornel_mesh(8)
+    ref = pyoracle.Reference(flat)
+    rng = np.random.default_rng(20261104)
+    n = 20000
+    px, py = rng.integers(0, 2048, n).astype(np.uint32), rng.integers(0, 2048, n).astype(np.uint32)
+    co, cd, _ = ref.eye_rays(2048, 2048, *FILM, px, py, rng.random((n, 5), dtype=np.float32))
+    cprim, ct = ref.cast(co, cd, accel=0)
+    hit = cprim >= 0
+    so = (co + ct[:, None] * cd)[hit].astype(np.float32)
+    sd = unit(rng, int(hit.sum()))
+    o, d = np.concatenate([co, so]), np.concatenate([cd, sd])
+    prim, t = ref.cast(o, d, accel=0)
+    # the reference's brute-force List agrees with its BVH (checked on a subset: 1.3 M tests per ray)
+    sub = rng.choice(len(o), 300, replace=False)
+    lprim, lt = ref.cast(o[sub], d[sub], accel=1)
+    assert np.array_equal(lprim, prim[sub]) and np.array_equal(lt, t[sub], equal_nan=True)
+    np.savez_compressed(os.path.join(GOLDEN, "mesh8_cast.npz"), origins=o, directions=d, prim=prim, t=t)
+    print("mesh8: rays", len(o), "hit fraction", float((prim >= 0).mean()), "on the mesh", float((prim >= 18).mean()))
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "mesh":
+        mesh_fixture()
+        return
     if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "tonemap":
         tonemap_fixture()  # (the statistics of section 5 are not reproducible: do not regenerate them casually)
         return
@@ -131,6 +158,7 @@ def main():
                    "pt_mean": float(np.mean(means)), "pt_std_of_run": float(np.std(means, ddof=1)),
                    "bdpt_mean": float(bdpt.mean()), "bdpt_spp": 1024, "bdpt_seconds": seconds}, f, indent=1)
     tonemap_fixture()
+    mesh_fixture()
     print("pt mean", np.mean(means), "+-", np.std(means, ddof=1) / np.sqrt(k_runs), "bdpt mean", bdpt.mean(),
           f"({seconds:.1f}s)")
 

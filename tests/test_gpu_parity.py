@@ -288,6 +288,25 @@ def test_bvh_full_size_mesh_against_brute_force(device, oracle_lib):
     assert np.isfinite(a).all() and np.allclose(a, b, rtol=1e-4, atol=1e-7 * a.mean())
 
 
+def test_bvh_full_size_mesh_against_the_reference_bvh(device):
+    """Config 4's geometry at full size against golden hits produced by the reference's OWN BVH
+    (include/amber/raytracer/acceleration_bvh.h, built over the 1.3 M triangles by
+    scripts/make_golden.py --only mesh): 20 000 camera rays + their secondary rays."""
+    from amber_b200 import cornel_mesh
+    g = golden("mesh8_cast.npz")
+    if device.scene is None or device.scene.n_primitives != 1310738:
+        device.upload_scene(cornel_mesh(subdivisions=8))
+    prim, t = device.cast(g["origins"], g["directions"])
+    agree = prim == g["prim"]
+    assert agree.mean() >= ID_AGREEMENT, f"hit ids agree on {agree.mean():.6f}"
+    both = agree & (g["prim"] >= 0)
+    err = np.abs(t[both] - g["t"][both])
+    assert np.all(err <= T_RTOL * g["t"][both] + 2e-6), f"max abs t error {err.max():.3e}"
+    assert (err <= T_RTOL * g["t"][both]).mean() >= 0.99
+    assert np.isnan(t[agree & (g["prim"] < 0)]).all()
+    print(f"mesh8 golden: id agreement {agree.mean():.6f} on {len(prim)} rays")
+
+
 def test_full_size_properties(cornell_device):
     """Config 2 geometry (Cornell 1024x1024) at a few spp: properties that do not need an
     oracle run of that size."""
