@@ -176,14 +176,14 @@ void make_triangle(const float* v, TriIsect& isect, TriShade& shade) {
 
 // Batches the triangles of a small scene by supporting plane for the constant-memory list.
 // `tri_ids` (creation-order ids) is permuted so that each group is contiguous: the planes
-// perpendicular to x, then y, then z (AxisPlane: no dot products), then the other groups, each in
+// perpendicular to x, then y, then z (AxisEntry: no dot products), then the other groups, each in
 // order of their first member; inside a group the parallelogram pairs (earlier triangle first, so a
 // hit on the shared diagonal goes to it, as in a creation-order scan), then the lone
 // triangles.  All geometry is evaluated in double from the float vertices.
 struct ConstListHost {
-  std::vector<AxisPlane> axis_planes;
   std::vector<AxisEntry> axis_entries;
-  int32_t n_axis_planes[3] = {0, 0, 0};
+  std::vector<uint8_t> axis_tri;
+  int32_t n_axis_entries[3] = {0, 0, 0};
   std::vector<PlaneGroup> groups;
   std::vector<PlaneEntry> entries;
 };
@@ -282,7 +282,7 @@ void group_by_plane(const amber_cuda_primitive* prims, std::vector<uint32_t>& tr
     batches.push_back(std::move(batch));
   }
 
-  // emit: planes perpendicular to x, y, z (AxisPlane), then everything else (PlaneGroup)
+  // emit: entries perpendicular to x, y, z (AxisEntry), then everything else (PlaneGroup)
   tri_ids.clear();
   for (int axis = 0; axis < 3; axis++) {
     const int ka = (axis + 1) % 3, kb = (axis + 2) % 3;
@@ -290,24 +290,24 @@ void group_by_plane(const amber_cuda_primitive* prims, std::vector<uint32_t>& tr
       const Batch& B = batches[g];
       if (B.axis != axis) continue;
       const Group& G = found[g];
-      AxisPlane plane;
-      plane.g_k = (float)comp(G.anchor, axis);
-      plane.g_a = (float)comp(G.anchor, ka);
-      plane.g_b = (float)comp(G.anchor, kb);
-      plane.ranges = static_cast<int32_t>(out.axis_entries.size()) | (static_cast<int32_t>(tri_ids.size()) << 8) |
-                     (static_cast<int32_t>(B.quads.size()) << 16) | (static_cast<int32_t>(B.tris.size()) << 24);
-      out.axis_planes.push_back(plane);
-      out.n_axis_planes[axis]++;
-      for (const std::vector<Corner>* list : {&B.quads, &B.tris}) {
-        for (const Corner& c : *list) {
+      uint32_t tri = static_cast<uint32_t>(tri_ids.size());
+      for (int is_tri = 0; is_tri < 2; is_tri++) {
+        for (const Corner& c : is_tri ? B.tris : B.quads) {
           D3 nu, nv;
           edge_vectors(c, nu, nv);
-          const D3 rel = sub(c.r, G.anchor);
           AxisEntry e;
-          e.nu = make_float2((float)comp(nu, ka), (float)comp(nu, kb));
-          e.cu_nv = make_float2((float)-(comp(nu, ka) * comp(rel, ka) + comp(nu, kb) * comp(rel, kb)), (float)comp(nv, ka));
-          e.nv_cv = make_float2((float)comp(nv, kb), (float)-(comp(nv, ka) * comp(rel, ka) + comp(nv, kb) * comp(rel, kb)));
+          e.r_k = (float)comp(c.r, axis);
+          e.r_a = (float)comp(c.r, ka);
+          e.r_b = (float)comp(c.r, kb);
+          e.nu_a = (float)comp(nu, ka);
+          e.nu_b = (float)comp(nu, kb);
+          e.nv_a = (float)comp(nv, ka);
+          e.nv_b = (float)comp(nv, kb);
+          e.limit = is_tri ? 1.0f : 2.0f;
           out.axis_entries.push_back(e);
+          out.axis_tri.push_back(static_cast<uint8_t>(tri));
+          out.n_axis_entries[axis]++;
+          tri += is_tri ? 1 : 2;
         }
       }
       tri_ids.insert(tri_ids.end(), B.quad_ids.begin(), B.quad_ids.end());
@@ -662,9 +662,11 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   ctx->const_scene.n_tris = use_bvh ? 0 : static_cast<int32_t>(n_tris);
   ctx->const_scene.n_spheres = static_cast<int32_t>(n_spheres);
   ctx->const_scene.n_groups = static_cast<int32_t>(const_list.groups.size());
-  for (int axis = 0; axis < 3; axis++) ctx->const_scene.n_axis_planes[axis] = const_list.n_axis_planes[axis];
-  for (size_t g = 0; g < const_list.axis_planes.size(); g++) ctx->const_scene.axis_plane[g] = const_list.axis_planes[g];
-  for (size_t k = 0; k < const_list.axis_entries.size(); k++) ctx->const_scene.axis_entry[k] = const_list.axis_entries[k];
+  for (int axis = 0; axis < 3; axis++) ctx->const_scene.n_axis_entries[axis] = const_list.n_axis_entries[axis];
+  for (size_t k = 0; k < const_list.axis_entries.size(); k++) {
+    ctx->const_scene.axis_entry[k] = const_list.axis_entries[k];
+    ctx->const_scene.axis_tri[k] = const_list.axis_tri[k];
+  }
   for (size_t g = 0; g < const_list.groups.size(); g++) ctx->const_scene.group[g] = const_list.groups[g];
   for (size_t k = 0; k < const_list.entries.size(); k++) ctx->const_scene.entry[k] = const_list.entries[k];
   for (size_t k = 0; k < n_spheres; k++) ctx->const_scene.sphere[k] = spheres[k];

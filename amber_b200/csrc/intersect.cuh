@@ -113,43 +113,25 @@ struct ConstList {
     return found;
   }
 
-  // The planes perpendicular to axis K (scene_device.cuh, AxisPlane).  ok / oa / ob (dk / da / db)
-  // are the ray origin (direction) along K and the two other axes, inv_dk = 1 / dk.  Same
+  // The entries perpendicular to one axis (scene_device.cuh, AxisEntry).  ok / oa / ob (dk / da / db)
+  // are the ray origin (direction) along that axis and the two others, inv_dk = 1 / dk.  Same
   // acceptance rules as intersect_group; updates the closest hit in place (kAnyHit: returns as
   // soon as anything is hit).
   template <bool kAnyHit>
-  static __device__ __forceinline__ bool scan_axis(int first_plane, int n_planes, float ok, float oa, float ob,
-                                                   float inv_dk, float da, float db, float& t_best, int& prim) {
+  static __device__ __forceinline__ bool scan_axis(int first, int count, float ok, float oa, float ob, float inv_dk,
+                                                   float da, float db, float& t_best, int& prim) {
     bool any = false;
-    for (int p = first_plane; p < first_plane + n_planes; p++) {
-      const AxisPlane plane = c_scene.axis_plane[p];
-      const float t = (plane.g_k - ok) * inv_dk;
-      bool open = (t > kEpsF) & (t < t_best);
-      const float ha = fmaf(t, da, oa - plane.g_a), hb = fmaf(t, db, ob - plane.g_b);
-      int e = plane.ranges & 0xff, tri = (plane.ranges >> 8) & 0xff;
-      const int quads_end = e + ((plane.ranges >> 16) & 0xff), tris_end = quads_end + ((plane.ranges >> 24) & 0xff);
-      int found = -1;
-      for (; e < quads_end; e++, tri += 2) {
-        const float2 nu = c_scene.axis_entry[e].nu, cu_nv = c_scene.axis_entry[e].cu_nv, nv_cv = c_scene.axis_entry[e].nv_cv;
-        const float s = fmaf(nu.x, ha, fmaf(nu.y, hb, cu_nv.x));
-        const float r = fmaf(cu_nv.y, ha, fmaf(nv_cv.x, hb, nv_cv.y));
-        if (open & (s >= 0.0f) & (s <= 1.0f) & (r >= 0.0f) & (r <= 1.0f)) {
-          found = tri + (s + r > 1.0f ? 1 : 0);
-          open = false;
-        }
-      }
-      for (; e < tris_end; e++, tri++) {
-        const float2 nu = c_scene.axis_entry[e].nu, cu_nv = c_scene.axis_entry[e].cu_nv, nv_cv = c_scene.axis_entry[e].nv_cv;
-        const float u = fmaf(nu.x, ha, fmaf(nu.y, hb, cu_nv.x));
-        const float v = fmaf(cu_nv.y, ha, fmaf(nv_cv.x, hb, nv_cv.y));
-        if (open & (u >= 0.0f) & (v >= 0.0f) & (u + v <= 1.0f)) {
-          found = tri;
-          open = false;
-        }
-      }
-      if (found >= 0) {
+#pragma unroll 1
+    for (int e = first; e < first + count; e++) {
+      const AxisEntry& E = c_scene.axis_entry[e];
+      const float t = (E.r_k - ok) * inv_dk;
+      const float ha = fmaf(t, da, oa - E.r_a), hb = fmaf(t, db, ob - E.r_b);
+      const float s = fmaf(E.nu_a, ha, E.nu_b * hb);
+      const float q = fmaf(E.nv_a, ha, E.nv_b * hb);
+      const float sum = s + q;
+      if ((t > kEpsF) & (t < t_best) & (s >= 0.0f) & (q >= 0.0f) & (s <= 1.0f) & (q <= 1.0f) & (sum <= E.limit)) {
         t_best = t;
-        prim = found;
+        prim = c_scene.axis_tri[e] + (sum > 1.0f ? 1 : 0);
         any = true;
         if (kAnyHit) return true;
       }
@@ -157,11 +139,11 @@ struct ConstList {
     return any;
   }
 
-  // All constant-memory triangles: axis-perpendicular planes, then the general plane groups.
+  // All constant-memory triangles: axis-perpendicular entries, then the general plane groups.
   template <bool kAnyHit>
   static __device__ __forceinline__ bool scan_triangles(const Ray& ray, float& t_best, int& prim) {
     bool any = false;
-    const int nx = c_scene.n_axis_planes[0], ny = c_scene.n_axis_planes[1], nz = c_scene.n_axis_planes[2];
+    const int nx = c_scene.n_axis_entries[0], ny = c_scene.n_axis_entries[1], nz = c_scene.n_axis_entries[2];
     if (nx + ny + nz > 0) {
       float ix, iy, iz;  // 1 / 0 = inf: t = +-inf or NaN rejects the plane, as n.d == 0 does elsewhere
       asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ix) : "f"(ray.d.x));

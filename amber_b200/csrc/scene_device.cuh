@@ -100,26 +100,26 @@ struct PlaneEntry {
   float4 nv_cv;  // nv.xyz, cv
 };
 
-// Plane groups whose plane is perpendicular to a coordinate axis k (walls, floors, table tops:
-// most of an architectural scene) need no dot products: with a, b the other two axes and g the
-// anchor,   t = (g_k - o_k) / d_k,   h = (o_a - g_a + t d_a, o_b - g_b + t d_b)   and an entry's
-// edge coordinates are 2-D:   u = nu_a h_a + nu_b h_b + cu.   1/d is computed once per ray.
-struct AxisPlane {
-  float g_k, g_a, g_b;  // anchor: plane offset along the axis, in-plane coordinates
-  int32_t ranges;       // first entry | first triangle << 8 | quads << 16 | lone triangles << 24
-};
+// Triangles whose plane is perpendicular to a coordinate axis k (walls, floors, table tops: most
+// of an architectural scene) need no dot products.  With a, b the other two axes and r the entry's
+// corner:   t = (r_k - o_k) / d_k,   h = (o_a - r_a + t d_a, o_b - r_b + t d_b),
+//           s = nu_a h_a + nu_b h_b,   q = nv_a h_a + nv_b h_b      (1/d once per ray).
+// One entry is a parallelogram (two triangles, limit = 2) or a lone triangle (limit = 1); the hit
+// is inside iff s, q in [0, 1] and s + q <= limit, and belongs to triangle `tri` + (s + q > 1).
+// Entries are self-contained (no per-plane state), so the scan is one flat loop per axis.
 struct AxisEntry {
-  float2 nu;     // nu_a, nu_b
-  float2 cu_nv;  // cu, nv_a
-  float2 nv_cv;  // nv_b, cv
+  float r_k, r_a;
+  float r_b, nu_a;
+  float nu_b, nv_a;
+  float nv_b, limit;
 };
 
 struct ConstScene {
   int32_t n_tris, n_spheres, n_groups;
-  int32_t n_axis_planes[3];  // planes perpendicular to x, y, z: axis_plane[] holds them in that order
+  int32_t n_axis_entries[3];  // entries perpendicular to x, y, z: axis_entry[] holds them in that order
   int32_t pad[2];
-  AxisPlane axis_plane[kMaxConstTris];
-  AxisEntry axis_entry[kMaxConstTris];  // plane by plane: quads, then lone triangles
+  AxisEntry axis_entry[kMaxConstTris];
+  uint8_t axis_tri[kMaxConstTris];  // first triangle (internal index) of each entry
   PlaneGroup group[kMaxConstTris];
   PlaneEntry entry[kMaxConstTris];  // group by group: quads, then lone triangles
   float4 sphere[kMaxConstSpheres];  // centre xyz, radius
