@@ -401,11 +401,12 @@ __device__ __forceinline__ void film_add(float4* film, uint32_t pixel, float3 va
 //   1. classify: every slot's hit record -> class = (material kind, triangle|sphere),
 //      or MISS / DEAD; a counting sort of the tile's slot indices by class in shared
 //      memory (warp match + one smem atomic per distinct class per warp).
-//   2. shade in sorted order: thread t of round r takes sorted[r * kBlock + t], so a
-//      warp runs ONE material's code on 32 lanes instead of six materials' code on a
-//      few lanes each.  Ray / state records are 32-byte sectors, so the permuted
-//      accesses inside the tile's 64 KB window still move whole sectors.
-//   3. queues: each thread has one bit per round for "slot freed" and "shadow ray
+//   2. shade in sorted order: warps take 32-entry chunks of the sorted tile from a shared
+//      counter, so a warp runs ONE material's code on 32 lanes instead of six materials'
+//      code on a few lanes each, and no warp idles while another works through an
+//      expensive class.  Ray / state records are 32-byte sectors, so the permuted accesses
+//      inside the tile's window still move whole sectors.
+//   3. queues: each thread has one bit per chunk for "slot freed" and "shadow ray
 //      emitted"; one block scan and ONE global atomic per queue per tile hand out the
 //      q_new / q_shadow ranges.
 // The shadow ray itself stays in the slot (pool.shadow[2 slot..]); its origin is the
@@ -442,11 +443,13 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
   __shared__ uint32_t class_count[16], class_offset[16];
   __shared__ uint32_t warp_scan[kShadeBlock / 32];
   __shared__ uint32_t queue_base[2];
+  __shared__ uint32_t next_chunk;
   const PathPool& pool = args.pool;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t tile_base = blockIdx.x * kShadeTile;
   const uint32_t lane_lt = (1u << lane) - 1u;
   if (tid < 16) class_count[tid] = 0;
+  if (tid == 0) next_chunk = 0;
   __syncthreads();
 
   // ---- phase 1: classify + counting sort ------------------------------------------
@@ -491,14 +494,23 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
   const uint32_t n_live = class_offset[kClassDead];  // entries [n_hit, n_live): misses
 
   // ---- phase 2: shade in class order ------------------------------------------------
-  // Each thread streams ITS records (ray, state, hit: 72 B) of round r + 1 into shared memory
-  // with cp.async while it shades round r, so the DRAM latency of the permuted gathers is
-  // paid once per tile, not once per round.  Thread-private staging: no barrier involved.
-  auto stage_records = [&](int round) {
-    const uint32_t jn = round * kShadeBlock + tid;
-    if (round < kShadeRounds && jn < n_hit) {
+  // The sorted tile is cut into chunks of 32 entries; a warp takes the next chunk from a shared
+  // counter until none is left, so warps that drew cheap classes (misses, emitters, mirrors) keep
+  // taking work instead of waiting at the barrier for the warps that drew refraction and Phong.
+  // Each thread streams the records of ITS entry of the warp's NEXT chunk (ray, state, hit: 72 B)
+  // into shared memory with cp.async while it shades the current one: the DRAM latency of the
+  // permuted gathers is paid once per tile.  Staging is thread-private: no barrier involved.
+  static_assert(kShadeTile <= 1024, "one bit per chunk in the 32-bit freed / shadow masks");
+  const uint32_t n_chunks = (n_live + 31u) >> 5;
+  auto take_chunk = [&]() {
+    uint32_t c = 0;
+    if (lane == 0) c = atomicAdd(&next_chunk, 1u);
+    return __shfl_sync(0xffffffffu, c, 0);
+  };
+  auto stage_records = [&](uint32_t chunk, int b) {
+    const uint32_t jn = chunk * 32u + lane;
+    if (chunk < n_chunks && jn < n_hit) {
       const size_t next = tile_base + sorted[jn];
-      const int b = round & 1;
       cp_async_16(&stage[b][0][tid], pool.ray + 2 * next);
       cp_async_16(&stage[b][1][tid], pool.ray + 2 * next + 1);
       cp_async_16(&stage[b][2][tid], pool.state + 2 * next);
@@ -507,12 +519,19 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     }
     cp_async_commit();
   };
-  stage_records(0);
-  uint32_t freed_mask = 0, shadow_mask = 0;
+  uint32_t freed_mask = 0, shadow_mask = 0;  // bit c: my entry of chunk c (sorted[32 c + lane])
+  uint32_t chunk = take_chunk();
+  int buf = 0;
+  stage_records(chunk, buf);
 #pragma unroll 1
-  for (int r = 0; r < kShadeRounds; r++) {
-    const uint32_t j = r * kShadeBlock + tid;
-    if (j >= n_live) break;
+  for (; chunk < n_chunks; buf ^= 1) {
+    const uint32_t r = chunk;  // bit index of this chunk in the masks
+    const uint32_t j = chunk * 32u + lane;
+    // this chunk's records were copied during the previous one; start the next chunk's copies now
+    chunk = take_chunk();
+    stage_records(chunk, buf ^ 1);
+    cp_async_wait_all_but_one();
+    if (j >= n_live) continue;
     if (j >= n_hit) {  // miss: the slot is free again
       freed_mask |= 1u << r;
       continue;
@@ -520,11 +539,6 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     const uint32_t slot = tile_base + sorted[j];
     float4* ray_slot = pool.ray + 2 * static_cast<size_t>(slot);
     float4* state_slot = pool.state + 2 * static_cast<size_t>(slot);
-    // this round's records were copied to shared memory asynchronously during the previous
-    // round (the copies of round 0 overlap nothing); start the next round's copies now
-    stage_records(r + 1);
-    cp_async_wait_all_but_one();
-    const int buf = r & 1;
     const float4 o4 = stage[buf][0][tid];
     const float4 d4 = stage[buf][1][tid];
     const float4 t4 = stage[buf][2][tid];
@@ -631,12 +645,12 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
   while (freed_mask) {
     const int r = __ffs(freed_mask) - 1;
     freed_mask &= freed_mask - 1u;
-    pool.q_new[freed_at++] = tile_base + sorted[r * kShadeBlock + tid];
+    pool.q_new[freed_at++] = tile_base + sorted[r * 32 + lane];
   }
   while (shadow_mask) {
     const int r = __ffs(shadow_mask) - 1;
     shadow_mask &= shadow_mask - 1u;
-    pool.q_shadow[shadow_at++] = tile_base + sorted[r * kShadeBlock + tid];
+    pool.q_shadow[shadow_at++] = tile_base + sorted[r * 32 + lane];
   }
 }
 
