@@ -17,7 +17,7 @@ ABI_VERSION = 1
 
 PRIM_TRIANGLE, PRIM_SPHERE = 0, 1
 MAT_LAMBERTIAN, MAT_PHONG, MAT_SPECULAR, MAT_REFRACTION, MAT_DIFFUSE_LIGHT, MAT_EYE = range(6)
-ESTIMATOR_REFERENCE, ESTIMATOR_NEE = 0, 1
+ESTIMATOR_REFERENCE, ESTIMATOR_NEE, ESTIMATOR_LIGHT_TRACING = 0, 1, 2
 
 # every symbol include/amber_cuda.h declares (checked by tests/test_abi.py)
 SYMBOLS = (
@@ -37,6 +37,9 @@ SYMBOLS = (
     "amber_cuda_cast_device",
     "amber_cuda_sample_light",
     "amber_cuda_eye_rays",
+    "amber_cuda_sample_importance",
+    "amber_cuda_light_rays",
+    "amber_cuda_lens_response",
     "amber_cuda_get_stats",
     "amber_cuda_set_profiling",
 )
@@ -97,6 +100,7 @@ class Stats(C.Structure):
         ("extend_launches", C.c_uint64),
         ("accel", C.c_uint32),
         ("bvh_nodes", C.c_uint32),
+        ("light_splats", C.c_uint64),
     ]
 
 
@@ -139,6 +143,9 @@ def load(path: str | None = None) -> C.CDLL:
         "amber_cuda_cast_device": [vp, vp, vp, u64, vp, f32p],
         "amber_cuda_sample_light": [vp, i32, u64, vp, vp, vp, vp, vp, vp],
         "amber_cuda_eye_rays": [vp, u64, vp, vp, vp, vp, vp, vp],
+        "amber_cuda_sample_importance": [vp, i32, u64, vp, vp, vp, vp, vp, vp],
+        "amber_cuda_light_rays": [vp, u64, vp, vp, vp, vp],
+        "amber_cuda_lens_response": [vp, u64, vp, vp, vp, vp],
         "amber_cuda_get_stats": [vp, C.POINTER(Stats)],
         "amber_cuda_set_profiling": [vp, C.c_int],
     }

@@ -74,6 +74,7 @@ struct amber_cuda_ctx {
   ConstScene const_scene;
   CameraDev camera;
   bool has_sensor = false;
+  bool has_sphere_light = false;  // an emitting sphere: fine for the path tracer, not sampled by light tracing
   SceneView view{};
   std::vector<int32_t> internal_to_prim;
   DeviceBuffer<TriShade> d_tri_shade;
@@ -631,6 +632,11 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   std::stable_sort(host_lights.begin(), host_lights.end(), [&](const HostLight& a, const HostLight& b) {
     return a.power < b.power || (a.power == b.power && tri_ids[a.tri] < tri_ids[b.tri]);
   });
+  bool has_sphere_light = false;
+  for (size_t k = 0; k < n_spheres; k++) {
+    const MaterialDev& m = materials[sphere_material[k]];
+    if (m.kind == AMBER_CUDA_MAT_DIFFUSE_LIGHT && (m.r > 0 || m.g > 0 || m.b > 0)) has_sphere_light = true;
+  }
   std::vector<LightDev> lights(host_lights.size());
   float total_power = 0;
   for (size_t i = 0; i < host_lights.size(); i++) total_power += host_lights[i].power;
@@ -646,6 +652,10 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
     l.v1 = make_float4(p.data[3], p.data[4], p.data[5], 0.0f);
     l.v2 = make_float4(p.data[6], p.data[7], p.data[8], 0.0f);
     l.n = make_float4(t.v0_nx.w, t.e1_ny.w, t.e2_nz.w, 0.0f);
+    // weight of a light ray, LightSet::GenerateRay: Irradiance / PDFArea (light_set.h:101)
+    l.v1.w = m.r * kPiF / pdf_area;
+    l.v2.w = m.g * kPiF / pdf_area;
+    l.n.w = m.b * kPiF / pdf_area;
     l.le_over_pdf = make_float4(m.r / pdf_area, m.g / pdf_area, m.b / pdf_area, 0.0f);
   }
 
@@ -658,6 +668,7 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   invalidate_constants(ctx);
   ctx->use_bvh = use_bvh;
+  ctx->has_sphere_light = has_sphere_light;
   std::memset(&ctx->const_scene, 0, sizeof(ConstScene));
   ctx->const_scene.n_tris = use_bvh ? 0 : static_cast<int32_t>(n_tris);
   ctx->const_scene.n_spheres = static_cast<int32_t>(n_spheres);
@@ -786,6 +797,7 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
   const unsigned int grid = blocks_for(args.pool.n_slots);
   const unsigned int shade_grid = blocks_for(args.pool.n_slots, kShadeTile);
   const unsigned int trace_grid = Accel::kPersistent ? ctx->bvh_grid : grid;
+  const bool light_tracing = args.estimator == AMBER_CUDA_ESTIMATOR_LIGHT_TRACING;
   cudaStream_t stream = ctx->stream;
   KernelTimer timer;
   const bool profile = ctx->profiling;
@@ -809,10 +821,16 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
   bool done = false;
   for (int batch = 0; !done; batch++) {
     for (int step = 0; step < kStepsPerPoll; step++) {
-      timed(0, [&] { raygen_kernel<<<grid, kBlock, 0, stream>>>(args); });
+      timed(0, [&] {
+        if (light_tracing) raygen_kernel<true><<<grid, kBlock, 0, stream>>>(args);
+        else raygen_kernel<false><<<grid, kBlock, 0, stream>>>(args);
+      });
       bookkeep_kernel<<<1, 1, 0, stream>>>(args.ctl);
       timed(1, [&] { extend_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args); });
-      timed(2, [&] { shade_kernel<<<shade_grid, kShadeBlock, 0, stream>>>(args); });
+      timed(2, [&] {
+        if (light_tracing) shade_kernel<true><<<shade_grid, kShadeBlock, 0, stream>>>(args);
+        else shade_kernel<false><<<shade_grid, kShadeBlock, 0, stream>>>(args);
+      });
       if (nee) timed(3, [&] { connect_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args); });
       ctx->stats.kernel_launches += nee ? 5 : 4;
       extend_launches++;
@@ -861,8 +879,15 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
   if (!params) return fail(ctx, AMBER_CUDA_EINVAL, "params is NULL");
   if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
   if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
-  if (params->estimator != AMBER_CUDA_ESTIMATOR_REFERENCE && params->estimator != AMBER_CUDA_ESTIMATOR_NEE)
+  if (params->estimator != AMBER_CUDA_ESTIMATOR_REFERENCE && params->estimator != AMBER_CUDA_ESTIMATOR_NEE &&
+      params->estimator != AMBER_CUDA_ESTIMATOR_LIGHT_TRACING)
     return fail(ctx, AMBER_CUDA_EINVAL, "unknown estimator %d", params->estimator);
+  if (params->estimator == AMBER_CUDA_ESTIMATOR_LIGHT_TRACING) {
+    // LightSet::GenerateRay on an empty set is undefined in the reference (light_set.h:87-92)
+    if (ctx->view.n_lights == 0) return fail(ctx, AMBER_CUDA_EINVAL, "light tracing needs at least one emitting triangle");
+    if (ctx->has_sphere_light)
+      return fail(ctx, AMBER_CUDA_EINVAL, "light tracing: emitting spheres are not supported (triangle emitters only)");
+  }
   if (params->sample_begin + params->sample_count >= (1ull << 32))
     return fail(ctx, AMBER_CUDA_EINVAL, "sample indices must stay below 2^32");
   if (params->sample_count == 0) return AMBER_CUDA_OK;
@@ -888,6 +913,7 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
   args.n_pixels = n_pixels;
   args.max_depth = params->max_depth ? std::min<uint32_t>(params->max_depth, 1u << 16) : (1u << 16);
   args.estimator = params->estimator;
+  args.inv_n_pixels = 1.0f / static_cast<float>(n_pixels);
 
   cudaStream_t stream = ctx->stream;
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev_begin, stream));
@@ -1022,9 +1048,9 @@ int amber_cuda_cast(amber_cuda_ctx* ctx, const float* origins, const float* dire
   return AMBER_CUDA_OK;
 }
 
-int amber_cuda_sample_light(amber_cuda_ctx* ctx, int32_t material, uint64_t n, const float* normal3,
-                            const float* dir_out3, const float* xi8, float* dir_in3, float* weight3,
-                            int32_t* draws) {
+static int sample_scatter(amber_cuda_ctx* ctx, bool importance, int32_t material, uint64_t n, const float* normal3,
+                          const float* dir_out3, const float* xi8, float* dir_in3, float* weight3,
+                          int32_t* draws) {
   if (!ctx) return AMBER_CUDA_EINVAL;
   if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
   if (material < 0 || static_cast<size_t>(material) >= ctx->d_materials.count)
@@ -1039,12 +1065,70 @@ int amber_cuda_sample_light(amber_cuda_ctx* ctx, int32_t material, uint64_t n, c
   CUDA_TRY(ctx, cudaMemcpyAsync(f[0].ptr, normal3, 3 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(f[1].ptr, dir_out3, 3 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(f[2].ptr, xi8, 8 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
-  sample_light_kernel<<<blocks_for(n), kBlock, 0, stream>>>(ctx->view, material, n, f[0].ptr, f[1].ptr, f[2].ptr,
-                                                           f[3].ptr, f[4].ptr, ctx->d_scratch_i[0].ptr);
+  sample_light_kernel<<<blocks_for(n), kBlock, 0, stream>>>(ctx->view, material, importance, n, f[0].ptr, f[1].ptr,
+                                                           f[2].ptr, f[3].ptr, f[4].ptr, ctx->d_scratch_i[0].ptr);
   ctx->stats.kernel_launches++;
   CUDA_TRY(ctx, cudaMemcpyAsync(dir_in3, f[3].ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(weight3, f[4].ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(draws, ctx->d_scratch_i[0].ptr, n * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+  CUDA_TRY(ctx, cudaGetLastError());
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_sample_light(amber_cuda_ctx* ctx, int32_t material, uint64_t n, const float* normal3,
+                            const float* dir_out3, const float* xi8, float* dir_in3, float* weight3,
+                            int32_t* draws) {
+  return sample_scatter(ctx, false, material, n, normal3, dir_out3, xi8, dir_in3, weight3, draws);
+}
+
+int amber_cuda_sample_importance(amber_cuda_ctx* ctx, int32_t material, uint64_t n, const float* normal3,
+                                 const float* dir_out3, const float* xi8, float* dir_in3, float* weight3,
+                                 int32_t* draws) {
+  return sample_scatter(ctx, true, material, n, normal3, dir_out3, xi8, dir_in3, weight3, draws);
+}
+
+int amber_cuda_light_rays(amber_cuda_ctx* ctx, uint64_t n, const float* xi5, float* origin3, float* direction3,
+                          float* weight3) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
+  if (ctx->view.n_lights == 0) return fail(ctx, AMBER_CUDA_EINVAL, "the scene has no emitting triangle");
+  if (n == 0) return AMBER_CUDA_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t stream = ctx->stream;
+  auto& f = ctx->d_scratch_f;
+  CUDA_TRY(ctx, f[0].resize(5 * n));
+  for (int k = 1; k <= 3; k++) CUDA_TRY(ctx, f[k].resize(3 * n));
+  CUDA_TRY(ctx, cudaMemcpyAsync(f[0].ptr, xi5, 5 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  light_rays_kernel<<<blocks_for(n), kBlock, 0, stream>>>(ctx->view, n, f[0].ptr, f[1].ptr, f[2].ptr, f[3].ptr);
+  ctx->stats.kernel_launches++;
+  CUDA_TRY(ctx, cudaMemcpyAsync(origin3, f[1].ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(direction3, f[2].ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(weight3, f[3].ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+  CUDA_TRY(ctx, cudaGetLastError());
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_lens_response(amber_cuda_ctx* ctx, uint64_t n, const float* position3, const float* dir_out3,
+                             int32_t* pixel, float* value) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_scene || !ctx->has_sensor)
+    return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene and set_sensor must be called first");
+  if (n == 0) return AMBER_CUDA_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  int rc = bind_constants(ctx);
+  if (rc != AMBER_CUDA_OK) return rc;
+  cudaStream_t stream = ctx->stream;
+  auto& f = ctx->d_scratch_f;
+  CUDA_TRY(ctx, f[0].resize(3 * n)); CUDA_TRY(ctx, f[1].resize(3 * n)); CUDA_TRY(ctx, f[2].resize(n));
+  CUDA_TRY(ctx, ctx->d_scratch_i[0].resize(n));
+  CUDA_TRY(ctx, cudaMemcpyAsync(f[0].ptr, position3, 3 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(f[1].ptr, dir_out3, 3 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  lens_response_kernel<<<blocks_for(n), kBlock, 0, stream>>>(n, f[0].ptr, f[1].ptr, ctx->d_scratch_i[0].ptr, f[2].ptr);
+  ctx->stats.kernel_launches++;
+  CUDA_TRY(ctx, cudaMemcpyAsync(pixel, ctx->d_scratch_i[0].ptr, n * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(value, f[2].ptr, n * sizeof(float), cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(stream));
   CUDA_TRY(ctx, cudaGetLastError());
   return AMBER_CUDA_OK;
@@ -1091,6 +1175,7 @@ int amber_cuda_get_stats(amber_cuda_ctx* ctx, amber_cuda_stats* out) {
   ctx->stats.shadow_rays = ctl.shadow_rays;
   ctx->stats.truncated_paths = ctl.truncated;
   ctx->stats.phong_capped = ctl.phong_capped;
+  ctx->stats.light_splats = ctl.splats;
   ctx->stats.accel = ctx->use_bvh ? 1u : 0u;
   ctx->stats.bvh_nodes = ctx->bvh_nodes;
   *out = ctx->stats;

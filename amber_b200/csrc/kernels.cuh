@@ -32,6 +32,7 @@ namespace amber_cuda {
 constexpr int kBlock = 256;
 constexpr uint32_t kFlagCountEmission = 1u << 31;  // emission at the next hit counts
 constexpr uint32_t kDepthMask = 0xffffffu;
+constexpr int32_t kEstimatorNee = 1, kEstimatorLightTracing = 2;  // AMBER_CUDA_ESTIMATOR_*
 
 struct Control {
   unsigned long long next_path;    // next path index of this render call
@@ -43,6 +44,7 @@ struct Control {
   unsigned int cursor_extend, cursor_connect, cursor_cast;  // persistent BVH kernels: next item to fetch
   unsigned int pad;
   unsigned long long paths, closest_rays, shadow_rays, truncated, phong_capped;
+  unsigned long long splats;  // light tracing: film contributions through the lens
 };
 
 struct PathPool {
@@ -65,6 +67,7 @@ struct RenderArgs {
   uint32_t n_pixels;
   uint32_t max_depth;
   int32_t estimator;
+  float inv_n_pixels;  // light tracing: each splat is divided by image.Size(), algorithm_lt.cc:146
 };
 
 __constant__ CameraDev c_camera;  // single translation unit: defined here
@@ -138,6 +141,69 @@ __device__ __forceinline__ void generate_eye_ray(uint32_t px, uint32_t py, Rng& 
   weight = factor / lens.p_area / pdf_direction;
 }
 
+// ---------------------------------------------------------------------------------
+// Light ray (light tracing, row N2): LightSet::GenerateRay, include/amber/scene/light_set.h:83-104.
+// Light by lower_bound over the cumulative powers of Uniform(total power); point by
+// Triangle::SampleSurfacePoint (primitive_triangle.cc:136-150); direction by HemispherePSA about
+// the triangle's stored normal (sampling.h:234-265); weight = Irradiance / PDFArea (host-side,
+// in LightDev).  Five uniforms, like the camera vertex.
+template <class Rng>
+__device__ __forceinline__ void generate_light_ray(const SceneView& scene, Rng& rng, float3& origin,
+                                                   float3& direction, float3& weight) {
+  const float target = __fmul_rn(rng.next(), scene.total_power);
+  int lo = 0, hi = scene.n_lights - 1;
+  while (lo < hi) {  // first light whose cumulative power >= target
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(&scene.lights[mid].v0.w) < target) lo = mid + 1; else hi = mid;
+  }
+  const float4* L = reinterpret_cast<const float4*>(scene.lights + lo);
+  const float4 v0 = __ldg(L), v1 = __ldg(L + 1), v2 = __ldg(L + 2), nl = __ldg(L + 3);
+  float u = rng.next();
+  float v = rng.next();
+  if (__fadd_rn(u, v) >= 1.0f) {
+    u = 1.0f - u;
+    v = 1.0f - v;
+  }
+  const float w0 = __fsub_rn(__fsub_rn(1.0f, u), v);
+  origin = v3(__fadd_rn(__fadd_rn(__fmul_rn(w0, v0.x), __fmul_rn(u, v1.x)), __fmul_rn(v, v2.x)),
+              __fadd_rn(__fadd_rn(__fmul_rn(w0, v0.y), __fmul_rn(u, v1.y)), __fmul_rn(v, v2.y)),
+              __fadd_rn(__fadd_rn(__fmul_rn(w0, v0.z), __fmul_rn(u, v1.z)), __fmul_rn(v, v2.z)));
+  const float3 axis = v3(nl);
+  float3 bu, bv;
+  orthonormal_basis(axis, bu, bv);
+  const float r0 = rng.next();
+  const float r1 = rng.next();
+  direction = local_to_world(bu, bv, axis, __fsqrt_rn(1.0f - r0), __fsqrt_rn(r0), __fmul_rn(2.0f * kPiF, r1));
+  weight = v3(v1.w, v2.w, nl.w);
+}
+
+// Lens response (light tracing): BasicThin::Response, src/amber/scene/lens_thin.cc:109-130, with
+// Sensor::ResponsePixel / UVToPixel, src/amber/rendering/sensor.cc:52-65,122-129.  `position` is a
+// point on the aperture, `dir_out` points from it back along the arriving ray.  The pixel is a
+// discrete decision, so the projection onto the film uses the host's operations one by one.
+__device__ __forceinline__ bool lens_response(float3 position, float3 dir_out, uint32_t& pixel, float& value) {
+  const LensDev& lens = c_camera.lens;
+  const SensorDev& sensor = c_camera.sensor;
+  const float3 direction = mat3_apply_exact(lens.local, dir_out);
+  if (direction.z >= 0.0f) return false;
+  const float3 aperture = mat3_apply_exact(
+      lens.local, v3(position.x - lens.origin[0], position.y - lens.origin[1], position.z - lens.origin[2]));
+  const float k_aperture = __fdiv_rn(-lens.sensor_distance, lens.focus_distance);
+  const float k_direction = __fdiv_rn(lens.sensor_distance, direction.z);
+  const float3 sensor_point = add_exact(scale_exact(k_aperture, aperture), scale_exact(k_direction, direction));
+  const float u = __fadd_rn(__fdiv_rn(sensor_point.x, sensor.film_width), 0.5f);
+  const float v = __fadd_rn(__fdiv_rn(sensor_point.y, sensor.film_height), 0.5f);
+  if (fminf(u, v) < 0.0f || fmaxf(u, v) >= 1.0f) return false;
+  const uint32_t ix = min(sensor.width - 1u, static_cast<uint32_t>(__fmul_rn(u, static_cast<float>(sensor.width))));
+  const uint32_t iy = min(sensor.height - 1u, static_cast<uint32_t>(__fmul_rn(v, static_cast<float>(sensor.height))));
+  pixel = ix + iy * sensor.width;
+  const float ratio = normalize(sensor_point - aperture).z / direction.z;
+  const float r2 = ratio * ratio;
+  value = r2 * r2;
+  return true;
+}
+
+template <bool kLightTracing>
 __global__ void __launch_bounds__(kBlock) raygen_kernel(const RenderArgs args) {
   const uint32_t j = blockIdx.x * kBlock + threadIdx.x;
   const Control* ctl = args.ctl;
@@ -154,13 +220,19 @@ __global__ void __launch_bounds__(kBlock) raygen_kernel(const RenderArgs args) {
   CameraRng rng;
   rng.init(args.seed, pixel, sample);
   const uint32_t width = c_camera.sensor.width;
-  float3 o, d;
-  float w;
-  generate_eye_ray(pixel % width, pixel / width, rng, o, d, w);
+  float3 o, d, w3;
+  if constexpr (kLightTracing) {
+    // one sample = W*H light paths (algorithm_lt.cc:112-122); `pixel` is only the path's stream key
+    generate_light_ray(args.scene, rng, o, d, w3);
+  } else {
+    float w;
+    generate_eye_ray(pixel % width, pixel / width, rng, o, d, w);
+    w3 = v3(w, w, w);
+  }
   ray[0] = make_float4(o.x, o.y, o.z, 1.0f);
   ray[1] = make_float4(d.x, d.y, d.z, 0.0f);
   float4* state = args.pool.state + 2 * static_cast<size_t>(slot);
-  state[0] = make_float4(w, w, w, 0.0f);
+  state[0] = make_float4(w3.x, w3.y, w3.z, 0.0f);
   state[1] = make_float4(__uint_as_float(pixel), __uint_as_float(sample), __uint_as_float(kFlagCountEmission), 0.0f);
 }
 
@@ -436,6 +508,9 @@ constexpr int kClassMiss = 14;  // hit.prim == -1: the path left the scene, algo
 constexpr int kClassDead = 15;  // hit.prim == -2: slot holds no path
 constexpr int32_t kPrimMiss = -1, kPrimDead = -2;
 
+// kLightTracing selects the light-tracing variant (row N2) at compile time, so the path tracer's
+// instantiation keeps its register allocation.
+template <bool kLightTracing>
 __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_kernel(const RenderArgs args) {
   __shared__ uint16_t sorted[kShadeTile];
   __shared__ float4 stage[2][4][kShadeBlock];  // double-buffered ray.o, ray.d, throughput, path ids
@@ -563,15 +638,26 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     VertexRng rng;
     rng.init(args.seed, pixel, sample, depth);  // one Philox block, same place for every lane
 
-    // emission, algorithm_pt.cc:144
-    if (m.kind == 4) {
-      const bool sampled_by_nee = args.estimator == 1 && hit.prim < args.scene.n_tris;
+    constexpr bool light_tracing = kLightTracing;
+    if constexpr (kLightTracing) {
+      // a light path that lands on the aperture is measured there (algorithm_lt.cc:141-148) and
+      // then goes on through it like any other surface; nothing else contributes
+      if (m.kind == 5) {
+        uint32_t film_pixel;
+        float response;
+        if (lens_response(x, wo, film_pixel, response)) {
+          film_add(args.film, film_pixel, (response * args.inv_n_pixels) * throughput);
+          atomicAdd(&args.ctl->splats, 1ull);
+        }
+      }
+    } else if (m.kind == 4) {  // emission, algorithm_pt.cc:144
+      const bool sampled_by_nee = args.estimator == kEstimatorNee && hit.prim < args.scene.n_tris;
       if (!sampled_by_nee || (flags & kFlagCountEmission)) {
         const float3 le = emitted_radiance(m, n, wo);
         if (le.x > 0.0f || le.y > 0.0f || le.z > 0.0f) film_add(args.film, pixel, throughput * le);
       }
     }
-    const bool connect = args.estimator == 1 && m.nee && args.scene.n_lights > 0;
+    const bool connect = !kLightTracing && args.estimator == kEstimatorNee && m.nee && args.scene.n_lights > 0;
     if (connect) {
       float lu, lv;
       rng.light_point(lu, lv);
@@ -586,7 +672,7 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     }
 
     // BSDF sample + Russian roulette, algorithm_pt.cc:145-156
-    const Scatter scatter = sample_light(m, n, wo, rng);
+    const Scatter scatter = sample_light(m, n, wo, rng, light_tracing);
     const float p = fminf(kRussianRoulette, max3(scatter.weight));
     if (scatter.capped) atomicAdd(&args.ctl->phong_capped, 1ull);
     bool terminated = false;
@@ -772,7 +858,7 @@ __global__ void unpack_hits_kernel(const float4* __restrict__ hits, uint64_t n,
   t[i] = h.x;
 }
 
-__global__ void sample_light_kernel(const SceneView scene, int material, uint64_t n,
+__global__ void sample_light_kernel(const SceneView scene, int material, bool importance, uint64_t n,
                                     const float* __restrict__ normal, const float* __restrict__ dir_out,
                                     const float* __restrict__ xi8, float* __restrict__ dir_in,
                                     float* __restrict__ weight, int32_t* __restrict__ draws) {
@@ -781,7 +867,7 @@ __global__ void sample_light_kernel(const SceneView scene, int material, uint64_
   const MaterialDev m = load_material(scene, material);
   ScriptedRng rng{xi8 + 8 * i, 8, 0};
   const Scatter s = sample_light(m, v3(normal[3 * i], normal[3 * i + 1], normal[3 * i + 2]),
-                                 v3(dir_out[3 * i], dir_out[3 * i + 1], dir_out[3 * i + 2]), rng);
+                                 v3(dir_out[3 * i], dir_out[3 * i + 1], dir_out[3 * i + 2]), rng, importance);
   dir_in[3 * i] = s.dir.x; dir_in[3 * i + 1] = s.dir.y; dir_in[3 * i + 2] = s.dir.z;
   weight[3 * i] = s.weight.x; weight[3 * i + 1] = s.weight.y; weight[3 * i + 2] = s.weight.z;
   draws[i] = rng.draws;
@@ -799,6 +885,32 @@ __global__ void eye_rays_kernel(uint64_t n, const uint32_t* __restrict__ px, con
   origin[3 * i] = o.x; origin[3 * i + 1] = o.y; origin[3 * i + 2] = o.z;
   direction[3 * i] = d.x; direction[3 * i + 1] = d.y; direction[3 * i + 2] = d.z;
   weight[i] = w;
+}
+
+__global__ void light_rays_kernel(const SceneView scene, uint64_t n, const float* __restrict__ xi5,
+                                  float* __restrict__ origin, float* __restrict__ direction,
+                                  float* __restrict__ weight) {
+  const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  ScriptedRng rng{xi5 + 5 * i, 5, 0};
+  float3 o, d, w;
+  generate_light_ray(scene, rng, o, d, w);
+  origin[3 * i] = o.x; origin[3 * i + 1] = o.y; origin[3 * i + 2] = o.z;
+  direction[3 * i] = d.x; direction[3 * i + 1] = d.y; direction[3 * i + 2] = d.z;
+  weight[3 * i] = w.x; weight[3 * i + 1] = w.y; weight[3 * i + 2] = w.z;
+}
+
+__global__ void lens_response_kernel(uint64_t n, const float* __restrict__ position,
+                                     const float* __restrict__ dir_out, int32_t* __restrict__ pixel,
+                                     float* __restrict__ value) {
+  const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t p = 0;
+  float f = 0.0f;
+  const bool ok = lens_response(v3(position[3 * i], position[3 * i + 1], position[3 * i + 2]),
+                                v3(dir_out[3 * i], dir_out[3 * i + 1], dir_out[3 * i + 2]), p, f);
+  pixel[i] = ok ? static_cast<int32_t>(p) : -1;
+  value[i] = ok ? f : 0.0f;
 }
 
 }  // namespace amber_cuda

@@ -54,8 +54,16 @@ __device__ __forceinline__ float schlick(float r0, float cos_theta) {
 // warp holding both kinds runs it once.  The reference rebuilds the basis on every Phong
 // retry; it only depends on the mirror direction, so it is hoisted.  The retry loop is
 // unbounded there; here it is capped (the cap is counted and never hit in practice).
+//
+// importance = true gives Material::SampleImportance, the light-tracing direction (row N2):
+// Lambertian, Phong and Specular sit behind SymmetricBasicMaterialForwarder, whose
+// SampleImportance IS Sample (include/amber/scene/material_basic.h:340-351), Eye passes through
+// and DiffuseLight returns weight 0 either way; only Refraction changes
+// (material_refraction.cc:222-263: no ior^2 scaling of the transmitted weight, probabilities
+// (rho + 1/2) / 2 without the normalisation).
 template <class Rng>
-__device__ __forceinline__ Scatter sample_light(const MaterialDev& m, float3 n, float3 wo, Rng& rng) {
+__device__ __forceinline__ Scatter sample_light(const MaterialDev& m, float3 n, float3 wo, Rng& rng,
+                                                bool importance = false) {
   Scatter s;
   s.capped = false;
   s.dir = v3(0.0f, 0.0f, 0.0f);
@@ -93,10 +101,10 @@ __device__ __forceinline__ Scatter sample_light(const MaterialDev& m, float3 n, 
       const float k = __fadd_rn(cos_o < 0.0f ? cos_beta : -cos_beta, __fmul_rn(ior, cos_o));
       const float3 dir_t = add_exact(scale_exact(-ior, wo), scale_exact(k, n));
       const float rho_r = schlick(m.r0, cos_alpha);
-      const float rho_t = __fmul_rn(1.0f - rho_r, ior2);
+      const float rho_t = importance ? 1.0f - rho_r : __fmul_rn(1.0f - rho_r, ior2);
       const float total = rho_r + rho_t;
-      const float p_r = __fdiv_rn(__fdiv_rn(rho_r, total) + 0.5f, 2.0f);
-      const float p_t = __fdiv_rn(__fdiv_rn(rho_t, total) + 0.5f, 2.0f);
+      const float p_r = __fdiv_rn((importance ? rho_r : __fdiv_rn(rho_r, total)) + 0.5f, 2.0f);
+      const float p_t = __fdiv_rn((importance ? rho_t : __fdiv_rn(rho_t, total)) + 0.5f, 2.0f);
       if (rng.next() < p_r) {
         s.dir = dir_r;
         s.weight = __fdiv_rn(rho_r, p_r) * rho;

@@ -181,6 +181,41 @@ class Device:
         self._check(self.lib.amber_cuda_sample_light(self.ctx, material, n, p(nrm), p(wo), p(xi), p(wi), p(w), p(draws)))
         return wi, w, draws
 
+    def sample_importance(self, material: int, normals, dirs_out, xi8):
+        """Material::SampleImportance (light tracing) with scripted uniforms."""
+        nrm = np.ascontiguousarray(normals, dtype=np.float32)
+        wo = np.ascontiguousarray(dirs_out, dtype=np.float32)
+        xi = np.ascontiguousarray(xi8, dtype=np.float32)
+        n = nrm.shape[0]
+        wi = np.empty((n, 3), dtype=np.float32)
+        w = np.empty((n, 3), dtype=np.float32)
+        draws = np.empty(n, dtype=np.int32)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        self._check(self.lib.amber_cuda_sample_importance(self.ctx, material, n, p(nrm), p(wo), p(xi), p(wi), p(w), p(draws)))
+        return wi, w, draws
+
+    def light_rays(self, xi5):
+        """Scene::GenerateLightRay with scripted uniforms: origins, directions, rgb weights."""
+        xi = np.ascontiguousarray(xi5, dtype=np.float32)
+        n = xi.shape[0]
+        o = np.empty((n, 3), dtype=np.float32)
+        d = np.empty((n, 3), dtype=np.float32)
+        w = np.empty((n, 3), dtype=np.float32)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        self._check(self.lib.amber_cuda_light_rays(self.ctx, n, p(xi), p(o), p(d), p(w)))
+        return o, d, w
+
+    def lens_response(self, positions, dirs_out):
+        """Scene::Response: pixel index (x + y*W, -1 = none) and response value per arriving ray."""
+        pos = np.ascontiguousarray(positions, dtype=np.float32)
+        wo = np.ascontiguousarray(dirs_out, dtype=np.float32)
+        n = pos.shape[0]
+        pixel = np.empty(n, dtype=np.int32)
+        value = np.empty(n, dtype=np.float32)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        self._check(self.lib.amber_cuda_lens_response(self.ctx, n, p(pos), p(wo), p(pixel), p(value)))
+        return pixel, value
+
     def eye_rays(self, px, py, xi5):
         px_ = np.ascontiguousarray(px, dtype=np.uint32)
         py_ = np.ascontiguousarray(py, dtype=np.uint32)
@@ -213,7 +248,8 @@ class CudaPathTracing:
 
     def __init__(self, estimator: str = "nee", max_depth: int = 0, seed: int = 1, device: int = 0,
                  batch_spp: int = 64, pool_paths: int = 0):
-        self.estimator = {"reference": capi.ESTIMATOR_REFERENCE, "nee": capi.ESTIMATOR_NEE}[estimator]
+        self.estimator = {"reference": capi.ESTIMATOR_REFERENCE, "nee": capi.ESTIMATOR_NEE,
+                          "lt": capi.ESTIMATOR_LIGHT_TRACING}[estimator]
         self.max_depth = max_depth
         self.seed = seed
         self.device_index = device
@@ -241,3 +277,13 @@ class CudaPathTracing:
             image, _ = dev.resolve()
             self.last_stats = dev.stats()
         return image
+
+
+class CudaLightTracing(CudaPathTracing):
+    """rendering::Algorithm<RGB> for ``--algorithm lt`` (row N2): the light tracer of
+    ``src/amber/rendering/algorithm_lt.cc:82-163`` on the same wavefront kernels.  One
+    ``context.iterate()`` is W*H light paths, as ``Thread::operator()`` traces them."""
+
+    def __init__(self, max_depth: int = 0, seed: int = 1, device: int = 0, batch_spp: int = 64,
+                 pool_paths: int = 0):
+        super().__init__("lt", max_depth, seed, device, batch_spp, pool_paths)

@@ -71,6 +71,13 @@ extern "C" {
  *   connected (camera, Specular, Refraction, Eye). */
 #define AMBER_CUDA_ESTIMATOR_REFERENCE 0
 #define AMBER_CUDA_ESTIMATOR_NEE 1
+/* LIGHT_TRACING (row N2): sample-for-sample the algorithm of
+ *   src/amber/rendering/algorithm_lt.cc:112-163 on the same wavefront kernels: one sample = W*H
+ *   paths started on the lights (LightSet::GenerateRay, include/amber/scene/light_set.h:83-104),
+ *   scattered with Material::SampleImportance; a path that lands on the aperture is mapped to a
+ *   pixel by the lens (BasicThin::Response, src/amber/scene/lens_thin.cc:109-130) and its weight
+ *   / (W*H) is added there.  Emitters must be triangles. */
+#define AMBER_CUDA_ESTIMATOR_LIGHT_TRACING 2
 
 typedef struct amber_cuda_ctx amber_cuda_ctx;
 
@@ -130,6 +137,7 @@ typedef struct amber_cuda_stats {
   uint64_t extend_launches; /* launches of `extend` inside the last render */
   uint32_t accel;           /* 0 = constant-memory list, 1 = wide BVH */
   uint32_t bvh_nodes;
+  uint64_t light_splats;    /* light tracing: film contributions through the lens */
 } amber_cuda_stats;
 
 /* ABI version of the loaded library. */
@@ -207,6 +215,28 @@ int amber_cuda_cast_device(amber_cuda_ctx* ctx, const void* ray_origin4,
 int amber_cuda_sample_light(amber_cuda_ctx* ctx, int32_t material, uint64_t n,
                             const float* normal3, const float* dir_out3, const float* xi8,
                             float* dir_in3, float* weight3, int32_t* draws);
+
+/* sample_importance: the same for Material<RGB>::SampleImportance, the light-tracing
+ * direction (include/amber/scene/material.h:31-88; src/amber/scene/material_refraction.cc:222-263
+ * is the one material that differs from SampleLight). */
+int amber_cuda_sample_importance(amber_cuda_ctx* ctx, int32_t material, uint64_t n,
+                                 const float* normal3, const float* dir_out3, const float* xi8,
+                                 float* dir_in3, float* weight3, int32_t* draws);
+
+/* light_rays: n rays leaving the lights with scripted uniforms xi[n][5] (light choice, point u,
+ * v, direction r0, r1); weight3 = Irradiance / PDFArea.  Replaces scene::Scene::GenerateLightRay
+ * (include/amber/scene/scene.h:225-234) -> LightSet::GenerateRay
+ * (include/amber/scene/light_set.h:83-104). */
+int amber_cuda_light_rays(amber_cuda_ctx* ctx, uint64_t n, const float* xi5, float* origin3,
+                          float* direction3, float* weight3);
+
+/* lens_response: for n rays arriving at aperture point position3[i] from direction dir_out3[i]
+ * (unit, pointing away from the lens), the pixel x + y*W they land on (-1: none) and the
+ * response value.  Replaces scene::Scene::Response (include/amber/scene/scene.h:298-307) ->
+ * BasicThin::Response (src/amber/scene/lens_thin.cc:109-130) + Sensor::ResponsePixel
+ * (src/amber/rendering/sensor.cc:52-65). */
+int amber_cuda_lens_response(amber_cuda_ctx* ctx, uint64_t n, const float* position3,
+                             const float* dir_out3, int32_t* pixel, float* value);
 
 /* eye_rays: n camera rays for pixel (px[i], py[i]) with scripted uniforms xi[n][5].
  * Replaces scene::Scene::GenerateEyeRay (include/amber/scene/scene.h:210-223,

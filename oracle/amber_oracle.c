@@ -430,6 +430,47 @@ static scatter_t material_sample_light(const amber_cuda_material* m, float r0, v
   return out;
 }
 
+/* Material<RGB>::SampleImportance (light tracing, row N2).  Lambertian / Phong / Specular sit
+ * behind SymmetricBasicMaterialForwarder, whose SampleImportance IS Sample
+ * (material_basic.h:340-351); Eye passes through (material_eye.h:157-166); DiffuseLight returns
+ * Scatter() (material_diffuse_light.h:196-205).  Only Refraction differs
+ * (material_refraction.cc:222-263): no ior^2 radiance scaling of the transmitted weight and
+ * sampling probabilities (rho + 1/2) / 2 without the normalisation by rho_r + rho_t. */
+static scatter_t material_sample_importance(const amber_cuda_material* m, float r0, vec3 n, vec3 wo, sampler* s) {
+  scatter_t out;
+  if (m->kind != AMBER_CUDA_MAT_REFRACTION) return material_sample_light(m, r0, n, wo, s);
+  {
+    const vec3 rho = V(m->rgb[0], m->rgb[1], m->rgb[2]);
+    const float signed_cos_alpha = dot(wo, n);
+    const float ior = signed_cos_alpha > 0 ? 1 / m->param : m->param;
+    const float squared_cos_beta = 1 - (1 - signed_cos_alpha * signed_cos_alpha) * (ior * ior);
+    const vec3 dir_r = perfect_reflection(wo, n, signed_cos_alpha);
+    float scalar;
+    if (squared_cos_beta < 0) {
+      out.dir = dir_r;
+      scalar = 1;
+    } else {
+      const float cos_alpha = fabsf(signed_cos_alpha);
+      const float cos_beta = sqrtf(squared_cos_beta);
+      const vec3 dir_t = add(scale(-ior, wo),
+                             scale((signed_cos_alpha < 0 ? 1 : -1) * cos_beta + ior * signed_cos_alpha, n));
+      const float rho_r = schlick(r0, cos_alpha);
+      const float rho_t = 1 - rho_r;
+      const float p_r = (rho_r + 0.5f) / 2;
+      const float p_t = (rho_t + 0.5f) / 2;
+      if (uniform(s) < p_r) {
+        out.dir = dir_r;
+        scalar = rho_r / p_r;
+      } else {
+        out.dir = dir_t;
+        scalar = rho_t / p_t;
+      }
+    }
+    out.weight = scale(scalar, rho);
+  }
+  return out;
+}
+
 /* Material<RGB>::BSDF: Lambertian material_lambertian.cc:34-49, Phong material_phong.cc:39-61,
  * Specular material_specular.cc:34-49 (kDiracDelta = 1), others 0 / not connectable. */
 static vec3 material_bsdf(const amber_cuda_material* m, vec3 n, vec3 wo, vec3 wi) {
@@ -504,6 +545,52 @@ static void generate_eye_ray(const oracle_scene* sc, uint32_t w, uint32_t h, flo
   *origin = aperture_origin;
   *direction = dir_world;
   *weight = (float)(factor / sc->p_area / pdf_direction);
+}
+
+/* BasicThin::Response (src/amber/scene/lens_thin.cc:109-130) + Sensor::ResponsePixel / UVToPixel
+ * (src/amber/rendering/sensor.cc:52-65,122-129): the pixel a ray ARRIVING at the aperture point
+ * `position` from direction `dir_out` (pointing away from the lens) lands on, and the factor
+ * (cos at the sensor / cos at the lens)^4.  Returns 0 when the ray comes from behind the lens or
+ * misses the film. */
+static int lens_response(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h,
+                         vec3 position, vec3 dir_out, uint32_t* px, uint32_t* py, float* value) {
+  const vec3 direction = mat3_apply(sc->local, dir_out);
+  vec3 aperture_point, sensor_point;
+  float u, v;
+  unsigned long ix, iy;
+  if (direction.z >= 0) return 0;
+  aperture_point = mat3_apply(sc->local, sub(position, sc->lens_origin));
+  sensor_point = add(scale(-sc->sensor_distance / sc->focus_distance, aperture_point),
+                     scale(sc->sensor_distance / direction.z, direction));
+  u = sensor_point.x / film_w + 0.5f;
+  v = sensor_point.y / film_h + 0.5f;
+  if (fminf(u, v) < 0 || fmaxf(u, v) >= 1) return 0;
+  /* std::min<pixel_size_type>(W - 1, uv.X() * W): float product, truncated to unsigned */
+  ix = (unsigned long)(u * (float)(unsigned long)w);
+  iy = (unsigned long)(v * (float)(unsigned long)h);
+  *px = ix < (unsigned long)w - 1 ? (uint32_t)ix : w - 1;
+  *py = iy < (unsigned long)h - 1 ? (uint32_t)iy : h - 1;
+  /* std::pow(float, int) is double; PixelValue<real_type> stores float */
+  *value = (float)pow((double)(normalize(sub(sensor_point, aperture_point)).z / direction.z), 4.0);
+  return 1;
+}
+
+/* LightSet::GenerateRay (include/amber/scene/light_set.h:83-104): light by lower_bound over the
+ * cumulative powers of Uniform(total), point by Triangle::SampleSurfacePoint, direction by
+ * HemispherePSA about the triangle's stored normal, weight = Irradiance / PDFArea. */
+static void generate_light_ray(const oracle_scene* sc, sampler* s, vec3* origin, vec3* direction, vec3* weight) {
+  const float target = uniform(s) * sc->total_power;
+  uint32_t li = 0;
+  const light* l;
+  const prim* lp;
+  const amber_cuda_material* lm;
+  while (li + 1 < sc->n_lights && sc->lights[li].cumulative_power < target) li++;
+  l = &sc->lights[li];
+  lp = &sc->prims[l->prim_index];
+  lm = &sc->materials[lp->material];
+  *origin = triangle_sample(lp->v0, lp->v1, lp->v2, s);
+  *direction = hemisphere_psa(lp->normal, s);
+  *weight = V(lm->rgb[0] * PI_F / l->pdf_area, lm->rgb[1] * PI_F / l->pdf_area, lm->rgb[2] * PI_F / l->pdf_area);
 }
 
 /* ---- exported unit entry points --------------------------------------------------- */
@@ -752,6 +839,181 @@ void oracle_render(const oracle_scene* scene, uint32_t w, uint32_t h, float film
       stats[2] += jobs[k].count.truncated;
       stats[3] += jobs[k].count.paths;
     }
+  }
+}
+
+/* ---- light tracing (row N2) ---------------------------------------------------------
+ * LightTracing<RGB>::Thread::Render, src/amber/rendering/algorithm_lt.cc:124-163: a path starts
+ * on a light, and whenever it lands on the aperture (an Eye surface) the lens maps it to a pixel
+ * and the path weight is splatted there; it then goes on through the aperture like any other
+ * surface.  One iteration = w*h such paths, each splat divided by w*h (:112-122,146).
+ * film: w*h*3 doubles.  Same stream convention as the path tracer: vertex 0 = the light's five
+ * sequential uniforms, vertex k >= 1 = the k-th surface interaction. */
+static void trace_light_path(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h,
+                             philox_stream* stream, uint32_t max_depth, double* film, counters* count) {
+  sampler s = {stream, NULL, 0, 0, 1};
+  vec3 origin, direction, weight3;
+  const float n_pixels = (float)((unsigned long)w * (unsigned long)h);
+  uint32_t depth;
+  generate_light_ray(sc, &s, &origin, &direction, &weight3);
+  count->paths++;
+  for (depth = 1;; depth++) {
+    hit_t hit;
+    const int object = scene_cast(sc, origin, direction, &hit);
+    const amber_cuda_material* m;
+    const prim* p;
+    vec3 wo;
+    scatter_t scatter;
+    float p_rr;
+    philox_stream_begin_vertex(stream, depth);
+    s.camera = 0;
+    count->closest_rays++;
+    if (object < 0) break;
+    p = &sc->prims[object];
+    m = &sc->materials[p->material];
+    wo = neg(direction);
+    if (m->kind == AMBER_CUDA_MAT_EYE) {
+      uint32_t px, py;
+      float value;
+      if (lens_response(sc, w, h, film_w, film_h, hit.position, wo, &px, &py, &value)) {
+        /* image[pixel] += weight * response.Value() / image.Size() */
+        double* out = film + ((size_t)px + (size_t)py * w) * 3;
+        out[0] += (double)(weight3.x * value / n_pixels);
+        out[1] += (double)(weight3.y * value / n_pixels);
+        out[2] += (double)(weight3.z * value / n_pixels);
+        count->shadow_rays++; /* counts splats here */
+      }
+    }
+    scatter = material_sample_importance(m, sc->r0[p->material], hit.normal, wo, &s);
+    p_rr = fminf((float)kRussianRoulette, max3(scatter.weight));
+    if (uniform_rr(&s) >= p_rr) break;
+    if (depth >= max_depth) {
+      count->truncated++;
+      break;
+    }
+    origin = hit.position;
+    direction = scatter.dir;
+    weight3 = mul(weight3, V(scatter.weight.x / p_rr, scatter.weight.y / p_rr, scatter.weight.z / p_rr));
+  }
+}
+
+typedef struct {
+  const oracle_scene* scene;
+  uint32_t w, h;
+  float film_w, film_h;
+  uint64_t sample_begin, seed;
+  uint32_t sample_count, max_depth;
+  int worker, workers;
+  double* film;
+  counters count;
+} lt_job;
+
+static void* lt_worker(void* arg) {
+  lt_job* job = (lt_job*)arg;
+  const uint64_t n_pixels = (uint64_t)job->w * job->h;
+  uint64_t s, i;
+  memset(&job->count, 0, sizeof job->count);
+  for (s = job->sample_begin; s < job->sample_begin + job->sample_count; s++) {
+    for (i = (uint64_t)job->worker; i < n_pixels; i += (uint64_t)job->workers) {
+      philox_stream stream;
+      philox_stream_reset(&stream, job->seed, (uint32_t)i, s);
+      trace_light_path(job->scene, job->w, job->h, job->film_w, job->film_h, &stream, job->max_depth,
+                       job->film, &job->count);
+    }
+  }
+  return NULL;
+}
+
+/* stats[0] closest rays, [1] splats, [2] truncated paths, [3] paths */
+void oracle_render_lt(const oracle_scene* scene, uint32_t w, uint32_t h, float film_w, float film_h,
+                      uint64_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_depth,
+                      int threads, float* rgb, uint64_t* stats) {
+  pthread_t tid[64];
+  lt_job jobs[64];
+  const size_t n_values = (size_t)w * h * 3;
+  size_t v;
+  int k;
+  if (threads < 1) threads = 1;
+  if (threads > 64) threads = 64;
+  if (max_depth == 0) max_depth = 1u << 16;
+  if (stats) memset(stats, 0, 4 * sizeof(uint64_t));
+  if (scene->n_lights == 0) { /* LightSet::GenerateRay on an empty set is undefined in the reference */
+    memset(rgb, 0, n_values * sizeof(float));
+    return;
+  }
+  for (k = 0; k < threads; k++) {
+    lt_job j;
+    memset(&j, 0, sizeof j);
+    j.scene = scene; j.w = w; j.h = h; j.film_w = film_w; j.film_h = film_h;
+    j.sample_begin = sample_begin; j.seed = seed; j.sample_count = sample_count; j.max_depth = max_depth;
+    j.worker = k; j.workers = threads;
+    j.film = (double*)calloc(n_values, sizeof(double));
+    jobs[k] = j;
+    pthread_create(&tid[k], NULL, lt_worker, &jobs[k]);
+  }
+  for (k = 0; k < threads; k++) {
+    pthread_join(tid[k], NULL);
+    if (stats) {
+      stats[0] += jobs[k].count.closest_rays;
+      stats[1] += jobs[k].count.shadow_rays;
+      stats[2] += jobs[k].count.truncated;
+      stats[3] += jobs[k].count.paths;
+    }
+  }
+  for (v = 0; v < n_values; v++) {
+    double sum = 0;
+    for (k = 0; k < threads; k++) sum += jobs[k].film[v];
+    rgb[v] = (float)(sum / sample_count);
+  }
+  for (k = 0; k < threads; k++) free(jobs[k].film);
+}
+
+/* Unit checks for the two functions light tracing adds to the path. */
+void oracle_sample_importance(const amber_cuda_material* material, uint64_t n, const float* normal,
+                              const float* dir_out, const float* xi8, float* dir_in, float* weight,
+                              int32_t* draws) {
+  uint64_t i;
+  amber_cuda_material m = *material;
+  float r0 = 0;
+  if (m.kind == AMBER_CUDA_MAT_REFRACTION || m.kind == AMBER_CUDA_MAT_EYE) m.rgb[0] = m.rgb[1] = m.rgb[2] = 1.0f;
+  if (m.kind == AMBER_CUDA_MAT_REFRACTION) r0 = (float)pow((double)((m.param - 1) / (m.param + 1)), 2.0);
+  for (i = 0; i < n; i++) {
+    sampler s = {NULL, xi8 + 8 * i, 8, 0, 0};
+    const scatter_t sc = material_sample_importance(&m, r0, V(normal[3 * i], normal[3 * i + 1], normal[3 * i + 2]),
+                                                    V(dir_out[3 * i], dir_out[3 * i + 1], dir_out[3 * i + 2]), &s);
+    dir_in[3 * i] = sc.dir.x; dir_in[3 * i + 1] = sc.dir.y; dir_in[3 * i + 2] = sc.dir.z;
+    weight[3 * i] = sc.weight.x; weight[3 * i + 1] = sc.weight.y; weight[3 * i + 2] = sc.weight.z;
+    if (draws) draws[i] = s.used;
+  }
+}
+
+/* pixel[i] = x + y*w, or -1 when the lens does not respond */
+void oracle_lens_response(const oracle_scene* scene, uint32_t w, uint32_t h, float film_w, float film_h,
+                          uint64_t n, const float* position, const float* dir_out, int32_t* pixel,
+                          float* value) {
+  uint64_t i;
+  for (i = 0; i < n; i++) {
+    uint32_t px = 0, py = 0;
+    float f = 0;
+    const int ok = lens_response(scene, w, h, film_w, film_h,
+                                 V(position[3 * i], position[3 * i + 1], position[3 * i + 2]),
+                                 V(dir_out[3 * i], dir_out[3 * i + 1], dir_out[3 * i + 2]), &px, &py, &f);
+    pixel[i] = ok ? (int32_t)(px + py * w) : -1;
+    value[i] = ok ? f : 0.0f;
+  }
+}
+
+/* n light rays with scripted uniforms xi5[n][5] (choice, u, v, direction 2) */
+void oracle_light_rays(const oracle_scene* scene, uint64_t n, const float* xi5, float* origin,
+                       float* direction, float* weight) {
+  uint64_t i;
+  for (i = 0; i < n; i++) {
+    sampler s = {NULL, xi5 + 5 * i, 5, 0, 0};
+    vec3 o, d, wgt;
+    generate_light_ray(scene, &s, &o, &d, &wgt);
+    origin[3 * i] = o.x; origin[3 * i + 1] = o.y; origin[3 * i + 2] = o.z;
+    direction[3 * i] = d.x; direction[3 * i + 1] = d.y; direction[3 * i + 2] = d.z;
+    weight[3 * i] = wgt.x; weight[3 * i + 1] = wgt.y; weight[3 * i + 2] = wgt.z;
   }
 }
 

@@ -48,6 +48,21 @@ void oracle_render(const oracle_scene* scene, uint32_t w, uint32_t h, float film
                    uint64_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_depth,
                    int estimator, int threads, float* rgb, uint64_t* stats);
 
+/* Light tracing (src/amber/rendering/algorithm_lt.cc:124-163) on the same stream: one sample =
+ * w*h light paths keyed (path index, sample).  stats[0] closest rays, [1] splats,
+ * [2] truncated paths, [3] paths. */
+void oracle_render_lt(const oracle_scene* scene, uint32_t w, uint32_t h, float film_w, float film_h,
+                      uint64_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_depth,
+                      int threads, float* rgb, uint64_t* stats);
+void oracle_sample_importance(const amber_cuda_material* material, uint64_t n, const float* normal,
+                              const float* dir_out, const float* xi8, float* dir_in, float* weight,
+                              int32_t* draws);
+void oracle_lens_response(const oracle_scene* scene, uint32_t w, uint32_t h, float film_w, float film_h,
+                          uint64_t n, const float* position, const float* dir_out, int32_t* pixel,
+                          float* value);
+void oracle_light_rays(const oracle_scene* scene, uint64_t n, const float* xi5, float* origin,
+                       float* direction, float* weight);
+
 /* Filmic (exposure 16) + Gamma (2.2) + 8-bit truncation of n_values floats (any layout). */
 void oracle_tonemap(uint64_t n_values, const float* hdr, uint8_t* ldr);
 

@@ -140,6 +140,50 @@ class Reference:
         assert rc == 0
         return rgb, {"rays": stats[0], "truncated": stats[1]}
 
+    # ---- light tracing (row N2) ----
+    def sample_importance(self, material, normals, dirs_out, xi8):
+        n_, wo, xi = _f32(normals), _f32(dirs_out), _f32(xi8)
+        n = n_.shape[0]
+        wi = np.empty((n, 3), dtype=np.float32)
+        w = np.empty((n, 3), dtype=np.float32)
+        draws = np.empty(n, dtype=np.int32)
+        rc = self.lib.ref_sample_importance(C.byref(material), C.c_uint64(n), _ptr(n_), _ptr(wo), _ptr(xi),
+                                            _ptr(wi), _ptr(w), _ptr(draws))
+        assert rc == 0
+        return wi, w, draws
+
+    def lens_response(self, w, h, film_w, film_h, positions, dirs_out):
+        p, d = _f32(positions), _f32(dirs_out)
+        n = p.shape[0]
+        pixel = np.empty(n, dtype=np.int32)
+        value = np.empty(n, dtype=np.float32)
+        rc = self.lib.ref_lens_response(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                                        C.c_float(film_h), C.c_uint64(n), _ptr(p), _ptr(d), _ptr(pixel), _ptr(value))
+        assert rc == 0
+        return pixel, value
+
+    def light_rays(self, xi5):
+        xi = _f32(xi5)
+        n = xi.shape[0]
+        o = np.empty((n, 3), dtype=np.float32)
+        d = np.empty((n, 3), dtype=np.float32)
+        wt = np.empty((n, 3), dtype=np.float32)
+        rc = self.lib.ref_light_rays(self.handle, C.c_uint64(n), _ptr(xi), _ptr(o), _ptr(d), _ptr(wt))
+        assert rc == 0
+        return o, d, wt
+
+    def render_lt_stream(self, w, h, film_w, film_h, sample_begin, sample_count, seed, max_depth=0,
+                         threads=8):
+        """algorithm_lt.cc's loop over the reference Scene API on the device's Philox stream."""
+        rgb = np.empty((h, w, 3), dtype=np.float32)
+        stats = (C.c_uint64 * 3)()
+        rc = self.lib.ref_render_lt_stream(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                                           C.c_float(film_h), C.c_uint64(sample_begin),
+                                           C.c_uint32(sample_count), C.c_uint64(seed),
+                                           C.c_uint32(max_depth), C.c_uint32(threads), _ptr(rgb), stats)
+        assert rc == 0
+        return rgb, {"rays": stats[0], "truncated": stats[1], "splats": stats[2]}
+
 
 def reference_tonemap(rgb):
     """Gamma()(Filmic()(image)) of the unmodified reference; rgb (h, w, 3) float32 -> uint8."""
@@ -237,6 +281,43 @@ class Oracle:
                                C.c_int(threads), _ptr(rgb), stats)
         return rgb, {"closest_rays": stats[0], "shadow_rays": stats[1], "truncated": stats[2],
                      "paths": stats[3]}
+
+    # ---- light tracing (row N2) ----
+    def sample_importance(self, material, normals, dirs_out, xi8):
+        n_, wo, xi = _f32(normals), _f32(dirs_out), _f32(xi8)
+        n = n_.shape[0]
+        wi = np.empty((n, 3), dtype=np.float32)
+        w = np.empty((n, 3), dtype=np.float32)
+        draws = np.empty(n, dtype=np.int32)
+        self.lib.oracle_sample_importance(C.byref(material), C.c_uint64(n), _ptr(n_), _ptr(wo), _ptr(xi),
+                                          _ptr(wi), _ptr(w), _ptr(draws))
+        return wi, w, draws
+
+    def lens_response(self, w, h, film_w, film_h, positions, dirs_out):
+        p, d = _f32(positions), _f32(dirs_out)
+        n = p.shape[0]
+        pixel = np.empty(n, dtype=np.int32)
+        value = np.empty(n, dtype=np.float32)
+        self.lib.oracle_lens_response(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                                      C.c_float(film_h), C.c_uint64(n), _ptr(p), _ptr(d), _ptr(pixel), _ptr(value))
+        return pixel, value
+
+    def light_rays(self, xi5):
+        xi = _f32(xi5)
+        n = xi.shape[0]
+        o = np.empty((n, 3), dtype=np.float32)
+        d = np.empty((n, 3), dtype=np.float32)
+        wt = np.empty((n, 3), dtype=np.float32)
+        self.lib.oracle_light_rays(self.handle, C.c_uint64(n), _ptr(xi), _ptr(o), _ptr(d), _ptr(wt))
+        return o, d, wt
+
+    def render_lt(self, w, h, film_w, film_h, sample_begin, sample_count, seed, max_depth=0, threads=8):
+        rgb = np.empty((h, w, 3), dtype=np.float32)
+        stats = (C.c_uint64 * 4)()
+        self.lib.oracle_render_lt(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                                  C.c_float(film_h), C.c_uint64(sample_begin), C.c_uint32(sample_count),
+                                  C.c_uint64(seed), C.c_uint32(max_depth), C.c_int(threads), _ptr(rgb), stats)
+        return rgb, {"closest_rays": stats[0], "splats": stats[1], "truncated": stats[2], "paths": stats[3]}
 
     def ray_set(self, w, h, film_w, film_h, seed, n):
         """2n rays: n camera rays then n secondary rays (see oracle_ray_set)."""

@@ -34,6 +34,7 @@
 #include "amber/raytracer/acceleration_bvh.h"
 #include "amber/raytracer/acceleration_list.h"
 #include "amber/rendering/algorithm_bdpt.h"
+#include "amber/rendering/algorithm_lt.h"
 #include "amber/rendering/algorithm_pt.h"
 #include "amber/rendering/context.h"
 #include "amber/rendering/leading.h"
@@ -354,16 +355,80 @@ int ref_eye_rays(void* handle, uint32_t w, uint32_t h, float film_w, float film_
   return 0;
 }
 
-// The reference's own path tracer (algo = 0, MakeRGBPathTracing) or bidirectional path
-// tracer (algo = 1), unmodified, `threads` std::threads, `spp` iterations.  Engines
-// are seeded from std::random_device inside the reference => not reproducible.
+// Unit checks for light tracing (row N2): Material::SampleImportance, Scene::Response
+// (lens + sensor), Scene::GenerateLightRay -- each with scripted uniforms.
+int ref_sample_importance(const amber_cuda_material* material, uint64_t n, const float* normal,
+                          const float* dir_out, const float* xi8, float* dir_in, float* weight,
+                          int32_t* draws) {
+  const auto m = MakeMaterial(*material);
+  if (!m) return -1;
+  for (uint64_t i = 0; i < n; i++) {
+    ScriptedSampler sampler;
+    sampler.xi = xi8 + 8 * i;
+    sampler.n = 8;
+    const UnitVector3 nn(normal[3 * i], normal[3 * i + 1], normal[3 * i + 2]);
+    const UnitVector3 wo(dir_out[3 * i], dir_out[3 * i + 1], dir_out[3 * i + 2]);
+    const auto scatter = m->SampleImportance(nn, wo, sampler);
+    dir_in[3 * i] = scatter.DirectionIn().X();
+    dir_in[3 * i + 1] = scatter.DirectionIn().Y();
+    dir_in[3 * i + 2] = scatter.DirectionIn().Z();
+    weight[3 * i] = scatter.Weight().X();
+    weight[3 * i + 1] = scatter.Weight().Y();
+    weight[3 * i + 2] = scatter.Weight().Z();
+    if (draws) draws[i] = sampler.used;
+  }
+  return 0;
+}
+
+int ref_lens_response(void* handle, uint32_t w, uint32_t h, float film_w, float film_h, uint64_t n,
+                      const float* position, const float* dir_out, int32_t* pixel, float* value) {
+  auto* ref = static_cast<RefScene*>(handle);
+  const auto sensor = MakeSensor(w, h, film_w, film_h);
+  const rendering::Scene<RGB>& scene = *ref->scene;
+  for (uint64_t i = 0; i < n; i++) {
+    const Vector3 p(position[3 * i], position[3 * i + 1], position[3 * i + 2]);
+    const UnitVector3 d(dir_out[3 * i], dir_out[3 * i + 1], dir_out[3 * i + 2]);
+    const auto response = scene.Response(sensor, p, d);
+    if (response.Pixel()) {
+      pixel[i] = static_cast<int32_t>(response.Pixel().X() + response.Pixel().Y() * w);
+      value[i] = response.Value().X();
+    } else {
+      pixel[i] = -1;
+      value[i] = 0;
+    }
+  }
+  return 0;
+}
+
+int ref_light_rays(void* handle, uint64_t n, const float* xi5, float* origin, float* direction,
+                   float* weight) {
+  auto* ref = static_cast<RefScene*>(handle);
+  const rendering::Scene<RGB>& scene = *ref->scene;
+  for (uint64_t i = 0; i < n; i++) {
+    ScriptedSampler sampler;
+    sampler.xi = xi5 + 5 * i;
+    sampler.n = 5;
+    const auto generated = scene.GenerateLightRay(sampler);
+    const auto& leading = std::get<rendering::Leading<RGB>>(generated);
+    const auto ray = leading.Ray();
+    origin[3 * i] = ray.Origin().X(); origin[3 * i + 1] = ray.Origin().Y(); origin[3 * i + 2] = ray.Origin().Z();
+    direction[3 * i] = ray.Direction().X(); direction[3 * i + 1] = ray.Direction().Y(); direction[3 * i + 2] = ray.Direction().Z();
+    weight[3 * i] = leading.Weight().X(); weight[3 * i + 1] = leading.Weight().Y(); weight[3 * i + 2] = leading.Weight().Z();
+  }
+  return 0;
+}
+
+// The reference's own path tracer (algo = 0, MakeRGBPathTracing), bidirectional path
+// tracer (algo = 1) or light tracer (algo = 2, MakeRGBLightTracing), unmodified, `threads`
+// std::threads, `spp` iterations.  Engines are seeded from std::random_device inside the reference => not reproducible.
 int ref_render(void* handle, int algo, uint32_t w, uint32_t h, float film_w, float film_h,
                uint32_t spp, uint32_t threads, float* rgb, uint64_t* casts, double* seconds) {
   auto* ref = static_cast<RefScene*>(handle);
   const auto sensor = MakeSensor(w, h, film_w, film_h);
   HarnessContext context(threads, spp);
-  auto algorithm =
-      algo == 0 ? rendering::MakeRGBPathTracing() : rendering::MakeRGBBidirectionalPathTracing();
+  auto algorithm = algo == 0   ? rendering::MakeRGBPathTracing()
+                   : algo == 1 ? rendering::MakeRGBBidirectionalPathTracing()
+                               : rendering::MakeRGBLightTracing();
   g_casts = 0;
   const auto begin = std::chrono::steady_clock::now();
   const auto image = algorithm->Render(*ref->scene, sensor, context);
@@ -439,6 +504,89 @@ int ref_render_stream(void* handle, uint32_t w, uint32_t h, float film_w, float 
   if (stats) {
     stats[0] = total_rays;
     stats[1] = total_truncated;
+  }
+  return 0;
+}
+
+// Reproducible reference LIGHT TRACING: the loop of src/amber/rendering/algorithm_lt.cc:124-163
+// restated over the reference's own Scene API.  One iteration = w*h light paths
+// (algorithm_lt.cc:112-122); path i of sample s draws every uniform from the device's Philox
+// stream keyed (i, s): vertex 0 is the light (choice, point u, v, direction: five sequential
+// slots, as the camera's), vertex k >= 1 the k-th surface interaction.  rgb = mean over the
+// samples, as ParallelMean returns it.  stats: [0] rays cast, [1] truncated paths, [2] splats.
+int ref_render_lt_stream(void* handle, uint32_t w, uint32_t h, float film_w, float film_h,
+                         uint64_t sample_begin, uint32_t sample_count, uint64_t seed,
+                         uint32_t max_depth, uint32_t threads, float* rgb, uint64_t* stats) {
+  auto* ref = static_cast<RefScene*>(handle);
+  const auto sensor = MakeSensor(w, h, film_w, film_h);
+  const rendering::Scene<RGB>& scene = *ref->scene;
+  if (max_depth == 0) max_depth = 1u << 16;
+  if (threads < 1) threads = 1;
+  const uint64_t n_pixels = static_cast<uint64_t>(w) * h;
+  std::atomic<uint64_t> total_rays{0}, total_truncated{0}, total_splats{0};
+  std::vector<std::vector<double>> films(threads, std::vector<double>(n_pixels * 3, 0.0));
+  std::vector<std::thread> pool;
+  for (uint32_t worker = 0; worker < threads; worker++) {
+    pool.emplace_back([&, worker]() {
+      StreamSampler sampler;
+      std::vector<double>& film = films[worker];
+      uint64_t rays = 0, truncated = 0, splats = 0;
+      for (uint64_t s = sample_begin; s < sample_begin + sample_count; s++) {
+        for (uint64_t i = worker; i < n_pixels; i += threads) {
+          philox_stream_reset(&sampler.stream, seed, static_cast<uint32_t>(i), s);
+          sampler.camera = true;
+          auto generated = scene.GenerateLightRay(sampler);
+          auto& object = std::get<rendering::ObjectPointer>(generated);
+          auto& leading = std::get<rendering::Leading<RGB>>(generated);
+          auto ray = leading.Ray();
+          auto weight = leading.Weight();
+          for (uint32_t depth = 1;; depth++) {
+            rendering::Hit hit;
+            philox_stream_begin_vertex(&sampler.stream, depth);
+            sampler.camera = false;
+            std::tie(object, hit) = scene.Cast(ray);
+            rays++;
+            if (!hit) break;
+            if (scene.Surface(object) == rendering::SurfaceType::Eye) {
+              const auto response = scene.Response(sensor, hit.Position(), -ray.Direction());
+              if (response.Pixel()) {
+                const RGB value = weight * response.Value() / n_pixels;  // image.Size()
+                const auto pixel = response.Pixel();
+                double* out = film.data() + (static_cast<size_t>(pixel.X()) + static_cast<size_t>(pixel.Y()) * w) * 3;
+                out[0] += value.X();
+                out[1] += value.Y();
+                out[2] += value.Z();
+                splats++;
+              }
+            }
+            const auto scatter =
+                scene.SampleImportance(object, hit.Normal(), -ray.Direction(), sampler);
+            const auto p = std::min<rendering::real_type>(kRussianRoulette, Max(scatter.Weight()));
+            if (sampler.RussianRoulette() >= p) break;
+            if (depth >= max_depth) {
+              truncated++;
+              break;
+            }
+            ray = rendering::Ray(hit.Position(), scatter.DirectionIn());
+            weight *= scatter.Weight() / p;
+          }
+        }
+      }
+      total_rays += rays;
+      total_truncated += truncated;
+      total_splats += splats;
+    });
+  }
+  for (auto& thread : pool) thread.join();
+  for (uint64_t k = 0; k < n_pixels * 3; k++) {
+    double sum = 0;
+    for (uint32_t worker = 0; worker < threads; worker++) sum += films[worker][k];
+    rgb[k] = static_cast<float>(sum / sample_count);
+  }
+  if (stats) {
+    stats[0] = total_rays;
+    stats[1] = total_truncated;
+    stats[2] = total_splats;
   }
   return 0;
 }

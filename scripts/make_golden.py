@@ -80,8 +80,49 @@ def mesh_fixture():
     print("mesh8: rays", len(o), "hit fraction", float((prim >= 0).mean()), "on the mesh", float((prim >= 18).mean()))
 
 
+def light_tracing_fixture():
+    """Row N2: light rays, SampleImportance, lens response and whole light-tracing images from the
+    compiled reference (ref_light_rays / ref_sample_importance / ref_lens_response /
+    ref_render_lt_stream in oracle/ref_harness.cc)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from conftest import light_tracing_box
+    from test_oracle_pinned import lens_response_inputs
+    rng = np.random.default_rng(20261105)
+    flat = scene.cornel_box()
+    ref = pyoracle.Reference(flat)
+    out = {}
+    xi = rng.random((2048, 5), dtype=np.float32)
+    o, d, w = ref.light_rays(xi)
+    out.update({"light_rays.xi": xi, "light_rays.origin": o, "light_rays.direction": d, "light_rays.weight": w})
+    for name, kind, rgb, param in MATERIALS:
+        material = capi.Material(kind, (capi.C.c_float * 3)(*rgb), param)
+        normal, wo = unit(rng, 512), unit(rng, 512)
+        xi8 = rng.random((512, 8), dtype=np.float32)
+        dir_in, weight, draws = ref.sample_importance(material, normal, wo, xi8)
+        for key, val in dict(normal=normal, wo=wo, xi=xi8, dir_in=dir_in, weight=weight, draws=draws).items():
+            out[f"importance.{name}.{key}"] = val
+        out[f"importance.{name}.desc"] = np.array([kind, *rgb, param], dtype=np.float64)
+    pos, dirs = lens_response_inputs(rng, 4096, 4.0, 0.05)
+    out["response.position"], out["response.dir_out"] = pos, dirs
+    for (w_, h_) in ((64, 64), (1024, 512)):
+        pixel, value = ref.lens_response(w_, h_, 0.036, 0.036 * h_ / w_, pos, dirs)
+        out[f"response.{w_}x{h_}.pixel"], out[f"response.{w_}x{h_}.value"] = pixel, value
+    image, stats = ref.render_lt_stream(64, 64, *FILM, 3, 64, 23)
+    out["cornell.64x64.begin3.spp64.seed23.image"] = image
+    out["cornell.64x64.begin3.spp64.seed23.stats"] = np.array([stats["rays"], stats["truncated"], stats["splats"]], dtype=np.uint64)
+    box = pyoracle.Reference(light_tracing_box())
+    for depth in (0, 3):
+        image, stats = box.render_lt_stream(96, 64, 0.036, 0.024, 0, 64, 24, depth)
+        out[f"box.96x64.spp64.seed24.depth{depth}.image"] = image
+        out[f"box.96x64.spp64.seed24.depth{depth}.stats"] = np.array([stats["rays"], stats["truncated"], stats["splats"]], dtype=np.uint64)
+    np.savez_compressed(os.path.join(GOLDEN, "light_tracing.npz"), **out)
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "lt":
+        light_tracing_fixture()
+        return
     if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "mesh":
         mesh_fixture()
         return

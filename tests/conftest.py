@@ -71,12 +71,13 @@ def image_agreement(got, want, rtol=2e-3):
     return float(ok.all(axis=-1).mean())
 
 
-def diffuse_box():
+def diffuse_box(aperture_radius=0.01, extra=False):
     """A small low-variance scene for estimator-equivalence checks: closed grey box,
-    one Phong wall, a large ceiling light, a diffuse sphere; thin lens inside the box."""
+    one Phong wall, a large ceiling light, a diffuse sphere; thin lens inside the box.
+    ``extra`` adds a glass sphere and a mirror sphere (every material kind on the path)."""
     from amber_b200 import FlatSceneBuilder
     b = FlatSceneBuilder()
-    b.make_thin_lens([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0.9, 0, 0, 0, 1], 0.05, 1.5, 0.01, 5,
+    b.make_thin_lens([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0.9, 0, 0, 0, 1], 0.05, 1.5, aperture_radius, 5,
                      add_aperture_objects=True)
 
     def quad(m, p0, p1, p2, p3):
@@ -95,4 +96,14 @@ def diffuse_box():
     quad(grey, (-1, -1, 1), (-1, 1, 1), (1, 1, 1), (1, -1, 1))          # front (behind camera)
     quad(light, (-0.5, 0.98, 0.5), (-0.5, 0.98, -0.5), (0.5, 0.98, -0.5), (0.5, 0.98, 0.5))  # faces down
     b.add_sphere((0.3, -0.6, -0.3), 0.4, b.make_lambertian((.3, .5, .7)))
+    if extra:
+        b.add_sphere((-0.45, -0.7, 0.1), 0.3, b.make_refraction(1.5))
+        b.add_sphere((-0.3, 0.3, -0.6), 0.25, b.make_specular((.9, .9, .9)))
     return b.build()
+
+
+def light_tracing_box():
+    """The box with a wide aperture (radius 0.25): about one light path in a thousand lands on
+    the lens inside the field of view (in the Cornell box: three in a hundred thousand), so
+    light-tracing images hold hundreds of splats at test sizes."""
+    return diffuse_box(aperture_radius=0.25, extra=True)

@@ -11,7 +11,7 @@ differ, so image checks require >= 99 % of pixels to agree to 2e-3 relative.
 import numpy as np
 import pytest
 
-from conftest import FILM, diffuse_box, golden, image_agreement, unit_vectors
+from conftest import FILM, diffuse_box, golden, image_agreement, light_tracing_box, unit_vectors
 
 pytestmark = pytest.mark.gpu
 
@@ -391,3 +391,139 @@ def test_errors_are_reported_not_swallowed(device):
     b.add_triangle((0, 0, 0), (1, 0, 0), (0, 1, 0), 7)  # material out of range
     with pytest.raises(capi.AmberCudaError, match="material"):
         device.upload_scene(b.build())
+
+
+# ---- light tracing (row N2): src/amber/rendering/algorithm_lt.cc on the same kernels ------
+def test_light_tracing_unit_functions(cornell_device):
+    """GenerateLightRay, SampleImportance and the lens response against the compiled reference's
+    golden vectors."""
+    from amber_b200 import FlatSceneBuilder, Sensor
+    g = golden("light_tracing.npz")
+    o, d, w = cornell_device.light_rays(g["light_rays.xi"])
+    assert np.array_equal(o, g["light_rays.origin"])  # host operations one by one: bit-identical
+    assert np.allclose(d, g["light_rays.direction"], atol=5e-6)
+    assert np.array_equal(w, g["light_rays.weight"])
+    for (w_, h_) in ((64, 64), (1024, 512)):
+        cornell_device.set_sensor(Sensor(w_, h_))
+        pixel, value = cornell_device.lens_response(g["response.position"], g["response.dir_out"])
+        want_pixel, want_value = g[f"response.{w_}x{h_}.pixel"], g[f"response.{w_}x{h_}.value"]
+        same = pixel == want_pixel
+        assert same.mean() >= 0.9995, same.mean()
+        assert np.allclose(value[same], want_value[same], rtol=1e-5)
+    cornell_device.set_sensor(Sensor(64, 64))
+    names = sorted({k.split(".")[1] for k in g.files if k.startswith("importance.")})
+    b = FlatSceneBuilder()
+    b.make_thin_lens(np.eye(4), 0.05, 4.0, 0.05, 6, add_aperture_objects=False)
+    index = {}
+    for name in names:
+        kind, r, gg, bb, param = g[f"importance.{name}.desc"]
+        index[name] = b._material(int(kind), (r, gg, bb), param)
+    b.add_triangle((0, 0, 0), (1, 0, 0), (0, 1, 0), index[names[0]])
+    cornell_device.upload_scene(b.build())
+    for name in names:
+        key = f"importance.{name}"
+        dir_in, weight, draws = cornell_device.sample_importance(index[name], g[f"{key}.normal"], g[f"{key}.wo"], g[f"{key}.xi"])
+        same = draws == g[f"{key}.draws"]
+        assert same.mean() >= 0.995, (name, same.mean())
+        atol = 1e-4 if name.startswith("phong") else 5e-6
+        assert np.allclose(dir_in[same], g[f"{key}.dir_in"][same], atol=atol), name
+        assert np.allclose(weight[same], g[f"{key}.weight"][same], rtol=2e-4, atol=1e-7), name
+
+
+def light_tracing_agreement(image, want):
+    """Light-tracing images are sums of a few large splats per pixel: compare the pixels either
+    image lights up."""
+    lit = (want.sum(-1) > 0) | (image.sum(-1) > 0)
+    ok = np.abs(image - want) <= 2e-3 * np.abs(want) + 1e-6 * want[lit].mean()
+    return float(ok.all(-1)[lit].mean()), int(lit.sum())
+
+
+def test_light_tracing_matches_reference_golden_and_oracle(device, oracle_lib):
+    from amber_b200 import Sensor, capi
+    g = golden("light_tracing.npz")
+    box = light_tracing_box()
+    device.upload_scene(box)
+    device.set_sensor(Sensor(96, 64, 0.036, 0.024))
+    for depth in (0, 3):  # images of the unmodified reference on the shared stream
+        device.film_clear()
+        device.render(0, 64, seed=24, max_depth=depth, estimator=capi.ESTIMATOR_LIGHT_TRACING)
+        image, done = device.resolve()
+        rays, truncated, splats = (int(v) for v in g[f"box.96x64.spp64.seed24.depth{depth}.stats"])
+        frac, lit = light_tracing_agreement(image, g[f"box.96x64.spp64.seed24.depth{depth}.image"])
+        got = device.stats()
+        print(f"depth {depth}: {frac:.4f} of {lit} lit pixels agree; splats {got['light_splats']} vs {splats}")
+        assert done == 64 and frac >= 0.98
+        assert got["paths"] == 96 * 64 * 64 and got["shadow_rays"] == 0
+        assert abs(got["light_splats"] - splats) <= max(3, 0.01 * splats)
+        assert abs(got["closest_rays"] - rays) <= 2e-3 * rays
+        assert abs(got["truncated_paths"] - truncated) <= max(8, 0.02 * truncated)
+    # a larger run against the oracle: 4.2 M light paths
+    oracle = oracle_lib.Oracle(box)
+    device.set_sensor(Sensor(256, 256))
+    device.render(5, 64, seed=77, estimator=capi.ESTIMATOR_LIGHT_TRACING)
+    image, _ = device.resolve()
+    want, stats = oracle.render_lt(256, 256, *FILM, 5, 64, 77, threads=32)
+    frac, lit = light_tracing_agreement(image, want)
+    got = device.stats()
+    print(f"256x256x64: {frac:.4f} of {lit} lit pixels agree; splats {got['light_splats']} vs {stats['splats']}")
+    assert frac >= 0.98 and lit > 2000
+    assert abs(got["light_splats"] - stats["splats"]) <= 0.01 * stats["splats"]
+
+
+def test_light_tracing_on_the_cornell_box(cornell_device, oracle):
+    """The built-in scene: the aperture is 3 to 5 units from everything, so splats are rare
+    (3 in 1e5 paths) -- every one of them must land where the oracle puts it."""
+    from amber_b200 import Sensor, capi
+    cornell_device.set_sensor(Sensor(128, 128))
+    cornell_device.render(0, 256, seed=9, estimator=capi.ESTIMATOR_LIGHT_TRACING)
+    image, _ = cornell_device.resolve()
+    want, stats = oracle.render_lt(128, 128, *FILM, 0, 256, 9, threads=32)
+    frac, lit = light_tracing_agreement(image, want)
+    got = cornell_device.stats()
+    print(f"cornell: {frac:.4f} of {lit} lit pixels agree; splats {got['light_splats']} vs {stats['splats']}")
+    assert lit > 50 and frac >= 0.97
+    assert abs(got["light_splats"] - stats["splats"]) <= max(2, 0.02 * stats["splats"])
+    # sample partition invariance, as for the path tracer
+    cornell_device.film_clear()
+    cornell_device.render(0, 100, seed=9, estimator=capi.ESTIMATOR_LIGHT_TRACING)
+    cornell_device.render(100, 156, seed=9, estimator=capi.ESTIMATOR_LIGHT_TRACING, pool_paths=4096)
+    split, done = cornell_device.resolve()
+    assert done == 256 and np.allclose(split, image, rtol=1e-4, atol=1e-7 * image.mean())
+
+
+def test_light_tracing_agrees_with_path_tracing_in_expectation(device):
+    """Both algorithms measure the same image: mean radiance per channel over the film, wide
+    aperture, tens of millions of paths each."""
+    from amber_b200 import Sensor, capi
+    device.upload_scene(light_tracing_box())
+    device.set_sensor(Sensor(32, 32))
+    means = {}
+    for estimator, spp in ((capi.ESTIMATOR_LIGHT_TRACING, 32768), (capi.ESTIMATOR_NEE, 2048)):
+        runs = []
+        for seed in range(4):
+            device.film_clear()
+            device.render(0, spp, seed=90 + seed, estimator=estimator)
+            image, _ = device.resolve()
+            runs.append(image.mean(axis=(0, 1)))
+        means[estimator] = np.array(runs)
+    lt, pt = means[capi.ESTIMATOR_LIGHT_TRACING], means[capi.ESTIMATOR_NEE]
+    diff = lt.mean(0) - pt.mean(0)
+    sigma = np.sqrt(lt.var(0, ddof=1) / 4 + pt.var(0, ddof=1) / 4)
+    print("light tracing", lt.mean(0), "path tracing", pt.mean(0), "sigma", sigma)
+    assert np.all(np.abs(diff) < 4 * sigma + 5e-3 * pt.mean(0)), (diff, sigma)
+
+
+def test_light_tracing_refuses_what_it_cannot_sample(device):
+    from amber_b200 import FlatSceneBuilder, Sensor, capi
+    from amber_b200.capi import AmberCudaError
+    for emitter in ("none", "sphere"):
+        b = FlatSceneBuilder()
+        b.make_thin_lens(np.eye(4), 0.05, 4.0, 0.05, 6, add_aperture_objects=True)
+        b.add_triangle((0, 0, -2), (1, 0, -2), (0, 1, -2), b.make_lambertian((.5, .5, .5)))
+        if emitter == "sphere":
+            b.add_sphere((0, 2, -2), 0.5, b.make_diffuse_light((1, 1, 1)))
+        device.upload_scene(b.build())
+        device.set_sensor(Sensor(8, 8))
+        with pytest.raises(AmberCudaError):
+            device.render(0, 1, estimator=capi.ESTIMATOR_LIGHT_TRACING)
+        device.render(0, 1, estimator=capi.ESTIMATOR_REFERENCE)  # the path tracer takes both

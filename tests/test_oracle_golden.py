@@ -103,3 +103,41 @@ def test_tonemap_matches_reference(oracle_lib):
     ldr = oracle_lib.oracle_tonemap(g["hdr"])
     assert np.array_equal(ldr, g["ldr"])
     assert g["ldr"].min() == 0 and g["ldr"].max() == 255 and np.unique(g["ldr"]).size == 256
+
+
+def test_light_tracing_matches_reference(oracle, oracle_lib):
+    """Row N2: light rays, SampleImportance, lens response and light-tracing images of the
+    compiled reference (tests/golden/light_tracing.npz), bit for bit."""
+    from amber_b200 import capi
+    from conftest import light_tracing_box
+    g = golden("light_tracing.npz")
+    o, d, w = oracle.light_rays(g["light_rays.xi"])
+    assert np.array_equal(o, g["light_rays.origin"]) and np.array_equal(d, g["light_rays.direction"])
+    assert np.array_equal(w, g["light_rays.weight"])
+    # Irradiance / PDFArea of the Cornell light: pi * 1e11 * (total area 4e-4)
+    assert np.allclose(w, np.pi * 1e11 * 4e-4, rtol=1e-5)
+    names = sorted({k.split(".")[1] for k in g.files if k.startswith("importance.")})
+    assert len(names) == 8
+    for name in names:
+        kind, r, gg, b, param = g[f"importance.{name}.desc"]
+        m = capi.Material(int(kind), (capi.C.c_float * 3)(r, gg, b), param)
+        dir_in, weight, draws = oracle.sample_importance(m, g[f"importance.{name}.normal"], g[f"importance.{name}.wo"],
+                                                         g[f"importance.{name}.xi"])
+        assert np.array_equal(dir_in, g[f"importance.{name}.dir_in"]), name
+        assert np.array_equal(weight, g[f"importance.{name}.weight"]), name
+        assert np.array_equal(draws, g[f"importance.{name}.draws"]), name
+    for (w_, h_) in ((64, 64), (1024, 512)):
+        pixel, value = oracle.lens_response(w_, h_, 0.036, 0.036 * h_ / w_, g["response.position"], g["response.dir_out"])
+        assert np.array_equal(pixel, g[f"response.{w_}x{h_}.pixel"])
+        assert np.array_equal(value, g[f"response.{w_}x{h_}.value"])
+        assert 0.05 < (pixel >= 0).mean() < 0.95
+    image, stats = oracle.render_lt(64, 64, *FILM, 3, 64, 23)
+    assert np.array_equal(image, g["cornell.64x64.begin3.spp64.seed23.image"])
+    assert stats["splats"] == int(g["cornell.64x64.begin3.spp64.seed23.stats"][2]) > 0
+    box = oracle_lib.Oracle(light_tracing_box())
+    for depth in (0, 3):
+        image, stats = box.render_lt(96, 64, 0.036, 0.024, 0, 64, 24, depth)
+        want = g[f"box.96x64.spp64.seed24.depth{depth}.stats"]
+        assert np.array_equal(image, g[f"box.96x64.spp64.seed24.depth{depth}.image"]), depth
+        assert (stats["closest_rays"], stats["truncated"], stats["splats"]) == tuple(int(v) for v in want)
+    assert int(g["box.96x64.spp64.seed24.depth3.stats"][1]) > 0

@@ -3,7 +3,7 @@ on fresh random inputs.  Skipped where the reference was not built; the committe
 fixtures (test_oracle_golden.py) cover that case."""
 import numpy as np
 
-from conftest import FILM, unit_vectors
+from conftest import FILM, light_tracing_box, unit_vectors
 
 
 def test_flat_cornell_is_the_builtin_cornel_box(reference, oracle_lib):
@@ -80,3 +80,66 @@ def test_tonemap_bit_exact(reference, oracle_lib):
     hdr = (10.0 ** rng.uniform(-10, 3, size=(64, 96, 3))).astype(np.float32)
     hdr[0, :8] = 0.0
     assert np.array_equal(oracle_lib.reference_tonemap(hdr), oracle_lib.oracle_tonemap(hdr))
+
+
+# ---- light tracing (row N2) -------------------------------------------------------------
+def test_light_rays_bit_exact(reference, oracle):
+    rng = np.random.default_rng(31)
+    xi = rng.random((20000, 5), dtype=np.float32)
+    for x, y in zip(reference.light_rays(xi), oracle.light_rays(xi)):
+        assert np.array_equal(x, y)
+
+
+def test_sample_importance_bit_exact(reference, oracle):
+    from amber_b200 import capi
+    rng = np.random.default_rng(32)
+    n = 5000
+    for kind, rgb, param in [(0, (.5, .4, .3), 0), (1, (.95, .9, .8), 64), (2, (.9, .9, .9), 0),
+                             (3, (1, 1, 1), 1.333), (3, (1, 1, 1), 1.125), (3, (1, 1, 1), 2.4),
+                             (4, (5, 5, 5), 0), (5, (1, 1, 1), 0)]:
+        m = capi.Material(kind, (capi.C.c_float * 3)(*rgb), param)
+        nrm, wo = unit_vectors(rng, n), unit_vectors(rng, n)
+        xi = rng.random((n, 8), dtype=np.float32)
+        for x, y in zip(reference.sample_importance(m, nrm, wo, xi), oracle.sample_importance(m, nrm, wo, xi)):
+            assert np.array_equal(x, y), (kind, param)
+        if kind == 3:  # the one material whose importance sampling is not its radiance sampling
+            wl = oracle.sample_light(m, nrm, wo, xi)[1]
+            wi = oracle.sample_importance(m, nrm, wo, xi)[1]
+            assert not np.array_equal(wl, wi)
+
+
+def lens_response_inputs(rng, n, lens_z, radius):
+    """Points on (and around) the aperture disc at z = lens_z, directions mostly towards -z."""
+    r = radius * np.sqrt(rng.random(n)) * 1.05
+    phi = rng.uniform(0, 2 * np.pi, n)
+    pos = np.stack([r * np.cos(phi), r * np.sin(phi), np.full(n, lens_z)], axis=1).astype(np.float32)
+    d = np.stack([rng.normal(0, 0.3, n), rng.normal(0, 0.3, n), -np.abs(rng.normal(1, 0.3, n))], axis=1)
+    d[: n // 20, 2] *= -1  # a few arrive from behind the lens
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    return pos, d
+
+
+def test_lens_response_bit_exact(reference, oracle):
+    rng = np.random.default_rng(33)
+    pos, d = lens_response_inputs(rng, 20000, 4.0, 0.05)
+    for (w, h) in ((64, 64), (1024, 512), (37, 91)):
+        film = (0.036, 0.036 * h / w)
+        pa, va = reference.lens_response(w, h, *film, pos, d)
+        pb, vb = oracle.lens_response(w, h, *film, pos, d)
+        assert np.array_equal(pa, pb) and np.array_equal(va, vb)
+        assert (pa >= 0).mean() > 0.05
+
+
+def test_light_tracing_images_bit_exact(reference, oracle, oracle_lib):
+    a, sa = reference.render_lt_stream(64, 64, *FILM, 3, 32, 23)
+    b, sb = oracle.render_lt(64, 64, *FILM, 3, 32, 23)
+    assert np.array_equal(a, b) and sa["splats"] == sb["splats"]
+    # a scene where the lens is hit often, with every material kind, and a depth cap
+    box = light_tracing_box()
+    ref_box, orc_box = oracle_lib.Reference(box), oracle_lib.Oracle(box)
+    for depth in (0, 3):
+        a, sa = ref_box.render_lt_stream(96, 64, 0.036, 0.024, 0, 64, 24, depth)
+        b, sb = orc_box.render_lt(96, 64, 0.036, 0.024, 0, 64, 24, depth)
+        assert sa["splats"] == sb["splats"] and sa["splats"] > 100
+        assert sa["rays"] == sb["closest_rays"] and sa["truncated"] == sb["truncated"]
+        assert np.array_equal(a, b)
