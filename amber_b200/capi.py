@@ -18,6 +18,7 @@ ABI_VERSION = 1
 PRIM_TRIANGLE, PRIM_SPHERE = 0, 1
 MAT_LAMBERTIAN, MAT_PHONG, MAT_SPECULAR, MAT_REFRACTION, MAT_DIFFUSE_LIGHT, MAT_EYE = range(6)
 ESTIMATOR_REFERENCE, ESTIMATOR_NEE, ESTIMATOR_LIGHT_TRACING = 0, 1, 2
+LENS_THIN, LENS_PINHOLE = 0, 1
 
 # every symbol include/amber_cuda.h declares (checked by tests/test_abi.py)
 SYMBOLS = (
@@ -60,6 +61,8 @@ class Lens(C.Structure):
         ("focus_distance", C.c_float),
         ("radius", C.c_float),
         ("n_blades", C.c_int32),
+        ("kind", C.c_int32),
+        ("sensor_distance", C.c_float),
     ]
 
 

@@ -344,8 +344,13 @@ void group_by_plane(const amber_cuda_primitive* prims, std::vector<uint32_t>& tr
 
 // BasicThin::BasicThin, src/amber/scene/lens_thin.cc:32-57
 int make_lens(amber_cuda_ctx* ctx, const amber_cuda_lens& in, LensDev& lens) {
-  if (in.n_blades < 1 || in.n_blades > kMaxBlades)
+  if (in.kind != AMBER_CUDA_LENS_THIN && in.kind != AMBER_CUDA_LENS_PINHOLE)
+    return fail(ctx, AMBER_CUDA_EINVAL, "unknown lens kind %d", in.kind);
+  if (in.kind == AMBER_CUDA_LENS_PINHOLE && !(in.sensor_distance > 0))
+    return fail(ctx, AMBER_CUDA_EINVAL, "pinhole lens: sensor_distance must be positive");
+  if (in.kind == AMBER_CUDA_LENS_THIN && (in.n_blades < 1 || in.n_blades > kMaxBlades))
     return fail(ctx, AMBER_CUDA_EINVAL, "lens.n_blades must be in [1, %d]", kMaxBlades);
+  lens.kind = in.kind;
   const float* t = in.transform;
   lens.origin[0] = t[3]; lens.origin[1] = t[7]; lens.origin[2] = t[11];
   const float e11 = t[0], e12 = t[1], e13 = t[2], e21 = t[4], e22 = t[5], e23 = t[6], e31 = t[8],
@@ -360,6 +365,12 @@ int make_lens(amber_cuda_ctx* ctx, const amber_cuda_lens& in, LensDev& lens) {
                         -dinv * (e21 * e33 - e23 * e31), +dinv * (e11 * e33 - e13 * e31), -dinv * (e11 * e23 - e13 * e21),
                         +dinv * (e21 * e32 - e22 * e31), -dinv * (e11 * e32 - e12 * e31), +dinv * (e11 * e22 - e12 * e21)};
   std::memcpy(lens.local, inv, sizeof inv);
+  if (in.kind == AMBER_CUDA_LENS_PINHOLE) {  // BasicPinhole::BasicPinhole, lens_pinhole.cc:31-42
+    lens.sensor_distance = in.sensor_distance;
+    lens.n_blades = 0;
+    lens.p_area = 1.0f;  // kDiracDelta
+    return AMBER_CUDA_OK;
+  }
   lens.focus_distance = in.focus_distance;
   lens.sensor_distance = 1 / (1 / in.focal_length - 1 / in.focus_distance);
   lens.focus_over_sensor = -lens.focus_distance / lens.sensor_distance;
@@ -740,6 +751,7 @@ int amber_cuda_set_sensor(amber_cuda_ctx* ctx, uint32_t width, uint32_t height, 
   s.film_height = film_height;
   // sensor.Size() / sensor.SceneArea(): pixel count (integer) over a float product
   s.size_over_area = static_cast<float>(static_cast<uint64_t>(width) * height) / (film_width * film_height);
+  s.inv_area = 1 / (film_width * film_height);
   ctx->has_sensor = true;
   CUDA_TRY(ctx, ctx->d_film.resize(static_cast<size_t>(width) * height));
   return amber_cuda_film_clear(ctx);

@@ -99,6 +99,22 @@ __device__ __forceinline__ void generate_eye_ray(uint32_t px, uint32_t py, Rng& 
   // camera rays give the reference's first-hit behaviour on curved surfaces.
   const LensDev& lens = c_camera.lens;
   const SensorDev& sensor = c_camera.sensor;
+  if (lens.kind == 1) {
+    // BasicPinhole::GenerateRay / PDFArea / PDFDirection, src/amber/scene/lens_pinhole.cc:48-69,
+    // 87-108: the ray from the lens origin through the film point mirrored about it; weight =
+    // 1 / kDiracDelta / (p_area / geometry factor).  Two uniforms (film y, film x).
+    const float sv = __fdiv_rn(__fadd_rn(static_cast<float>(py), rng.next()), static_cast<float>(sensor.height));
+    const float su = __fdiv_rn(__fadd_rn(static_cast<float>(px), rng.next()), static_cast<float>(sensor.width));
+    const float3 film_point = v3(-__fmul_rn(su - 0.5f, sensor.film_width), -__fmul_rn(sv - 0.5f, sensor.film_height),
+                                 -lens.sensor_distance);
+    origin = v3(lens.origin[0], lens.origin[1], lens.origin[2]);
+    direction = normalize_exact(mat3_apply_exact(lens.global, film_point));
+    const float3 back = mat3_apply_exact(lens.local, direction);
+    const float3 point = (lens.sensor_distance / back.z) * back;
+    const float geometry_factor = back.z * back.z / dot(point, point);
+    weight = 1.0f / (sensor.inv_area / geometry_factor);
+    return;
+  }
   const float nb = static_cast<float>(lens.n_blades);
   int blade = static_cast<int>(floorf(__fmul_rn(rng.next(), nb)));
   blade = min(lens.n_blades - 1, blade);
@@ -185,18 +201,28 @@ __device__ __forceinline__ bool lens_response(float3 position, float3 dir_out, u
   const LensDev& lens = c_camera.lens;
   const SensorDev& sensor = c_camera.sensor;
   const float3 direction = mat3_apply_exact(lens.local, dir_out);
-  if (direction.z >= 0.0f) return false;
-  const float3 aperture = mat3_apply_exact(
-      lens.local, v3(position.x - lens.origin[0], position.y - lens.origin[1], position.z - lens.origin[2]));
-  const float k_aperture = __fdiv_rn(-lens.sensor_distance, lens.focus_distance);
   const float k_direction = __fdiv_rn(lens.sensor_distance, direction.z);
-  const float3 sensor_point = add_exact(scale_exact(k_aperture, aperture), scale_exact(k_direction, direction));
+  float3 aperture = v3(0.0f, 0.0f, 0.0f);
+  float3 sensor_point;
+  if (lens.kind == 1) {  // BasicPinhole::Response, lens_pinhole.cc:71-85: no facing test, value 1
+    sensor_point = scale_exact(k_direction, direction);
+  } else {
+    if (direction.z >= 0.0f) return false;
+    aperture = mat3_apply_exact(
+        lens.local, v3(position.x - lens.origin[0], position.y - lens.origin[1], position.z - lens.origin[2]));
+    const float k_aperture = __fdiv_rn(-lens.sensor_distance, lens.focus_distance);
+    sensor_point = add_exact(scale_exact(k_aperture, aperture), scale_exact(k_direction, direction));
+  }
   const float u = __fadd_rn(__fdiv_rn(sensor_point.x, sensor.film_width), 0.5f);
   const float v = __fadd_rn(__fdiv_rn(sensor_point.y, sensor.film_height), 0.5f);
   if (fminf(u, v) < 0.0f || fmaxf(u, v) >= 1.0f) return false;
   const uint32_t ix = min(sensor.width - 1u, static_cast<uint32_t>(__fmul_rn(u, static_cast<float>(sensor.width))));
   const uint32_t iy = min(sensor.height - 1u, static_cast<uint32_t>(__fmul_rn(v, static_cast<float>(sensor.height))));
   pixel = ix + iy * sensor.width;
+  if (lens.kind == 1) {
+    value = 1.0f;
+    return true;
+  }
   const float ratio = normalize(sensor_point - aperture).z / direction.z;
   const float r2 = ratio * ratio;
   value = r2 * r2;

@@ -72,6 +72,7 @@ struct LensDev {
   float local[9];   // inverse
   float focus_distance, sensor_distance, p_area;
   float focus_over_sensor;  // -focus_distance / sensor_distance, lens_thin.cc:92
+  int32_t kind;             // AMBER_CUDA_LENS_*: 1 = BasicPinhole (src/amber/scene/lens_pinhole.cc)
   int32_t n_blades;
   float blades[kMaxBlades][12];  // v0 v1 v2 normal
 };
@@ -80,6 +81,7 @@ struct SensorDev {
   uint32_t width, height;
   float film_width, film_height;
   float size_over_area;  // sensor.Size() / sensor.SceneArea(), lens_thin.cc:145
+  float inv_area;        // 1 / sensor.SceneArea(), lens_pinhole.cc:103
 };
 
 // Constant-memory list, triangles batched by supporting plane.  Triangles that lie in one

@@ -119,6 +119,13 @@ class FlatSceneBuilder:
             for tri in thin_lens_blades(t, radius, n_blades):
                 self.add_triangle(tri[0:3], tri[3:6], tri[6:9], eye)
 
+    def make_pinhole_lens(self, transform, sensor_distance) -> None:
+        """MakePinholeLens (include/amber/scene/lens_pinhole.h:32-37).  Its aperture object is a
+        degenerate triangle at the lens origin (src/amber/scene/lens_pinhole.cc:38) that no ray
+        can hit, so nothing is added to the primitives."""
+        t = [float(f32(v)) for v in np.asarray(transform, dtype=np.float64).reshape(16)]
+        self._lens = capi.Lens((C.c_float * 16)(*t), 0.0, 0.0, 0.0, 0, capi.LENS_PINHOLE, float(sensor_distance))
+
     def build(self) -> FlatScene:
         if self._lens is None:
             raise ValueError("scene has no lens")

@@ -96,13 +96,21 @@ typedef struct amber_cuda_material {
   float param;  /* PHONG: exponent; REFRACTION: index of refraction */
 } amber_cuda_material;
 
-/* Thin lens, the arguments of MakeThinLens (include/amber/scene/lens_thin.h:30-38). */
+/* Lens kinds: MakeThinLens (include/amber/scene/lens_thin.h:30-38; the lens of the built-in
+ * scene and of the importer) and MakePinholeLens (include/amber/scene/lens_pinhole.h:32-37). */
+#define AMBER_CUDA_LENS_THIN 0
+#define AMBER_CUDA_LENS_PINHOLE 1
+
+/* The arguments of MakeThinLens, or (kind = PINHOLE) of MakePinholeLens: transform and
+ * sensor_distance; the thin-lens fields are then ignored.  A zero-initialised tail is a thin lens. */
 typedef struct amber_cuda_lens {
   float transform[16]; /* row-major 4x4, lens-local -> world (Matrix4 ctor order) */
   float focal_length;
   float focus_distance;
   float radius;
   int32_t n_blades;
+  int32_t kind;          /* AMBER_CUDA_LENS_* */
+  float sensor_distance; /* PINHOLE only */
 } amber_cuda_lens;
 
 typedef struct amber_cuda_scene_desc {

@@ -6,7 +6,7 @@
 //
 //   amber::cuda::FlatSceneBuilder        the reference's factory verbs (MakeTriangle, MakeSphere,
 //                                        MakeLambertian, MakePhong, MakeSpecular, MakeRefraction,
-//                                        MakeDiffuseLight, MakeThinLens); builds the real reference
+//                                        MakeDiffuseLight, MakeThinLens, MakePinholeLens); builds the real reference
 //                                        scene (scene::Scene<RGB>::Create<BVH>,
 //                                        include/amber/scene/scene.h:169-193) AND records the flat
 //                                        description the GPU needs, in creation order
@@ -14,6 +14,7 @@
 //                                        CPU algorithm of the reference unchanged
 //   amber::cuda::MakeRGBCudaPathTracing  std::unique_ptr<rendering::Algorithm<RGB>>, the factory
 //                                        convention of include/amber/rendering/algorithm_pt.h:30-31
+//   amber::cuda::MakeRGBCudaLightTracing the same for the light tracer (algorithm_lt.h:29-30)
 //
 // Why a builder: scene::Object<R> keeps its primitive and material private
 // (include/amber/scene/object.h:93-96) and the concrete classes are .cc-local, so geometry
@@ -40,6 +41,7 @@
 #include "amber/rendering/algorithm.h"
 #include "amber/rendering/context.h"
 #include "amber/rendering/sensor.h"
+#include "amber/scene/lens_pinhole.h"
 #include "amber/scene/lens_thin.h"
 #include "amber/scene/material_diffuse_light.h"
 #include "amber/scene/material_lambertian.h"
@@ -188,11 +190,30 @@ public:
       Matrix4(t[0], t[1], t[2], t[3], t[4], t[5], t[6], t[7],
               t[8], t[9], t[10], t[11], t[12], t[13], t[14], t[15]),
       focal_length, focus_distance, radius, n_blades);
+    flat_lens_ = amber_cuda_lens();
     std::memcpy(flat_lens_.transform, transform, sizeof flat_lens_.transform);
+    flat_lens_.kind = AMBER_CUDA_LENS_THIN;
     flat_lens_.focal_length = focal_length;
     flat_lens_.focus_distance = focus_distance;
     flat_lens_.radius = radius;
     flat_lens_.n_blades = static_cast<int32_t>(n_blades);
+  }
+
+  /** MakePinholeLens (include/amber/scene/lens_pinhole.h:32-37).  Its aperture object -- a
+   *  degenerate triangle at the lens origin (src/amber/scene/lens_pinhole.cc:38) that no ray can
+   *  hit -- goes into the reference scene like any lens's, and is left out of the flat
+   *  description. */
+  void MakePinholeLens(const real_type (&transform)[16], real_type sensor_distance)
+  {
+    const real_type* t = transform;
+    lens_ = scene::MakePinholeLens<RGB>(
+      Matrix4(t[0], t[1], t[2], t[3], t[4], t[5], t[6], t[7],
+              t[8], t[9], t[10], t[11], t[12], t[13], t[14], t[15]),
+      sensor_distance);
+    flat_lens_ = amber_cuda_lens();
+    std::memcpy(flat_lens_.transform, transform, sizeof flat_lens_.transform);
+    flat_lens_.kind = AMBER_CUDA_LENS_PINHOLE;
+    flat_lens_.sensor_distance = sensor_distance;
   }
 
   /** scene::Scene<RGB>::Create<Acceleration> + the flat description. */
@@ -269,7 +290,7 @@ std::unique_ptr<Scene>
 FlatSceneBuilder::Build()
 {
   if (!lens_) {
-    throw std::logic_error("FlatSceneBuilder: MakeThinLens has not been called");
+    throw std::logic_error("FlatSceneBuilder: MakeThinLens / MakePinholeLens has not been called");
   }
 
   // Aperture blades first, as src/amber/etude/cornel_box.cc:62-64 emplaces them; in the flat
@@ -286,6 +307,7 @@ FlatSceneBuilder::Build()
   const int32_t eye_id = static_cast<int32_t>(flat_materials.size() - 1);
   for (const auto& object : lens_->ApertureObjects()) {
     objects.emplace_back(*object);
+    if (flat_lens_.kind == AMBER_CUDA_LENS_PINHOLE) continue;
     amber_cuda_primitive p;
     p.kind = AMBER_CUDA_PRIM_TRIANGLE;
     p.material = eye_id;
@@ -471,6 +493,18 @@ private:
 inline std::unique_ptr<rendering::Algorithm<RGB>>
 MakeRGBCudaPathTracing(const CudaPathTracingOptions& options = CudaPathTracingOptions())
 {
+  return std::make_unique<CudaPathTracing>(options);
+}
+
+/** Row N2: the light tracer (src/amber/rendering/algorithm_lt.cc:82-163) behind the same
+ *  interface, in the convention of include/amber/rendering/algorithm_lt.h:29-30 -- what
+ *  algorithm_factory.cc would register under "lt-cuda".  One Context::Iterate() is W*H light
+ *  paths, as LightTracing::Thread::operator() traces them; the estimator field of the options
+ *  is overridden. */
+inline std::unique_ptr<rendering::Algorithm<RGB>>
+MakeRGBCudaLightTracing(CudaPathTracingOptions options = CudaPathTracingOptions())
+{
+  options.estimator = AMBER_CUDA_ESTIMATOR_LIGHT_TRACING;
   return std::make_unique<CudaPathTracing>(options);
 }
 

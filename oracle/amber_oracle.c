@@ -93,6 +93,7 @@ struct oracle_scene {
   vec3 lens_origin;
   float global[9], local[9];
   float focus_distance, sensor_distance, p_area;
+  int lens_kind; /* AMBER_CUDA_LENS_*; PINHOLE: BasicPinhole, src/amber/scene/lens_pinhole.cc:31-42 */
   int n_blades;
   vec3 blades[16][4]; /* v0 v1 v2 normal */
 };
@@ -205,6 +206,13 @@ oracle_scene* oracle_scene_create(const amber_cuda_scene_desc* desc) {
     memcpy(s->global, g, sizeof g);
     memcpy(s->local, inv, sizeof inv);
     s->lens_origin = V(t[3], t[7], t[11]); /* transform(Vector3()), matrix4.h:100-106 */
+    s->lens_kind = in->kind;
+    if (in->kind == AMBER_CUDA_LENS_PINHOLE) {
+      s->sensor_distance = in->sensor_distance;
+      s->n_blades = 0;
+      s->p_area = 1; /* kDiracDelta */
+      return s;
+    }
     s->focus_distance = in->focus_distance;
     s->sensor_distance = 1 / (1 / in->focal_length - 1 / in->focus_distance);
     s->n_blades = in->n_blades;
@@ -519,12 +527,31 @@ static void generate_eye_ray(const oracle_scene* sc, uint32_t w, uint32_t h, flo
                              uint32_t px, uint32_t py, sampler* s, vec3* origin, vec3* direction,
                              float* weight) {
   const float nb = (float)sc->n_blades;
-  float f = floorf(uniform(s) * nb);
-  size_t pos = (size_t)f;
+  float f;
+  size_t pos;
   vec3 aperture_origin, aperture_point, sensor_point, dir_local, dir_world, dir_back;
   float su, sv;
   double factor, pdf_direction_d;
   float pdf_direction;
+  if (sc->lens_kind == AMBER_CUDA_LENS_PINHOLE) {
+    /* BasicPinhole::GenerateRay / PDFArea / PDFDirection, src/amber/scene/lens_pinhole.cc:48-69,
+     * 87-108: ray through the lens origin, weight = 1 / kDiracDelta / (p_area / geometry factor) */
+    vec3 point;
+    float geometry_factor;
+    sv = ((float)py + uniform(s)) / (float)h; /* Y first, as below */
+    su = ((float)px + uniform(s)) / (float)w;
+    sensor_point = V((su - 0.5f) * film_w, (sv - 0.5f) * film_h, sc->sensor_distance);
+    dir_world = normalize(mat3_apply(sc->global, neg(sensor_point)));
+    dir_back = mat3_apply(sc->local, dir_world);
+    point = scale(sc->sensor_distance / dir_back.z, dir_back);
+    geometry_factor = dir_back.z * dir_back.z / dot(point, point);
+    *origin = sc->lens_origin;
+    *direction = dir_world;
+    *weight = 1 / 1.0f / ((1 / (film_w * film_h)) / geometry_factor);
+    return;
+  }
+  f = floorf(uniform(s) * nb);
+  pos = (size_t)f;
   if (pos > (size_t)sc->n_blades - 1) pos = (size_t)sc->n_blades - 1;
   aperture_origin = triangle_sample(sc->blades[pos][0], sc->blades[pos][1], sc->blades[pos][2], s);
   aperture_point = mat3_apply(sc->local, sub(aperture_origin, sc->lens_origin));
@@ -558,10 +585,16 @@ static int lens_response(const oracle_scene* sc, uint32_t w, uint32_t h, float f
   vec3 aperture_point, sensor_point;
   float u, v;
   unsigned long ix, iy;
-  if (direction.z >= 0) return 0;
-  aperture_point = mat3_apply(sc->local, sub(position, sc->lens_origin));
-  sensor_point = add(scale(-sc->sensor_distance / sc->focus_distance, aperture_point),
-                     scale(sc->sensor_distance / direction.z, direction));
+  if (sc->lens_kind == AMBER_CUDA_LENS_PINHOLE) {
+    /* BasicPinhole::Response, lens_pinhole.cc:71-85: no facing test, value 1 */
+    aperture_point = V(0, 0, 0);
+    sensor_point = scale(sc->sensor_distance / direction.z, direction);
+  } else {
+    if (direction.z >= 0) return 0;
+    aperture_point = mat3_apply(sc->local, sub(position, sc->lens_origin));
+    sensor_point = add(scale(-sc->sensor_distance / sc->focus_distance, aperture_point),
+                       scale(sc->sensor_distance / direction.z, direction));
+  }
   u = sensor_point.x / film_w + 0.5f;
   v = sensor_point.y / film_h + 0.5f;
   if (fminf(u, v) < 0 || fmaxf(u, v) >= 1) return 0;
@@ -570,6 +603,10 @@ static int lens_response(const oracle_scene* sc, uint32_t w, uint32_t h, float f
   iy = (unsigned long)(v * (float)(unsigned long)h);
   *px = ix < (unsigned long)w - 1 ? (uint32_t)ix : w - 1;
   *py = iy < (unsigned long)h - 1 ? (uint32_t)iy : h - 1;
+  if (sc->lens_kind == AMBER_CUDA_LENS_PINHOLE) {
+    *value = 1;
+    return 1;
+  }
   /* std::pow(float, int) is double; PixelValue<real_type> stores float */
   *value = (float)pow((double)(normalize(sub(sensor_point, aperture_point)).z / direction.z), 4.0);
   return 1;

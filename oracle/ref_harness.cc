@@ -40,6 +40,7 @@
 #include "amber/rendering/leading.h"
 #include "amber/rendering/scatter.h"
 #include "amber/rendering/sensor.h"
+#include "amber/scene/lens_pinhole.h"
 #include "amber/scene/lens_thin.h"
 #include "amber/scene/material_diffuse_light.h"
 #include "amber/scene/material_eye.h"
@@ -212,15 +213,21 @@ void* ref_scene_create(const amber_cuda_scene_desc* desc) {
   std::vector<std::unique_ptr<scene::Primitive>> primitives;
   std::vector<std::unique_ptr<scene::Material<RGB>>> materials;
   std::vector<scene::Object<RGB>> objects;
-  auto lens = scene::MakeThinLens<RGB>(LensTransform(desc->lens), desc->lens.focal_length,
-                                       desc->lens.focus_distance, desc->lens.radius,
-                                       static_cast<std::size_t>(desc->lens.n_blades));
+  auto lens = desc->lens.kind == AMBER_CUDA_LENS_PINHOLE
+                  ? scene::MakePinholeLens<RGB>(LensTransform(desc->lens), desc->lens.sensor_distance)
+                  : scene::MakeThinLens<RGB>(LensTransform(desc->lens), desc->lens.focal_length,
+                                             desc->lens.focus_distance, desc->lens.radius,
+                                             static_cast<std::size_t>(desc->lens.n_blades));
   bool has_aperture = false;
   for (uint32_t i = 0; i < desc->n_primitives; i++) {
     if (desc->materials[desc->primitives[i].material].kind == AMBER_CUDA_MAT_EYE) {
       has_aperture = true;
     }
   }
+  // The pinhole's aperture object is a degenerate triangle (lens_pinhole.cc:38) that no ray can
+  // hit (its Intersect returns t = NaN); it is in the reference scene as a user of the reference
+  // would put it there, and absent from the flat description.
+  if (desc->lens.kind == AMBER_CUDA_LENS_PINHOLE) has_aperture = true;
   if (has_aperture) {
     for (const auto& object : lens->ApertureObjects()) objects.emplace_back(*object);
   }

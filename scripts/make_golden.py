@@ -118,8 +118,36 @@ def light_tracing_fixture():
     np.savez_compressed(os.path.join(GOLDEN, "light_tracing.npz"), **out)
 
 
+def pinhole_fixture():
+    """Row N1's pinhole lens (MakePinholeLens): camera rays, an image on the shared stream and
+    the lens response, from the compiled reference."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from conftest import pinhole_box
+    rng = np.random.default_rng(20261106)
+    ref = pyoracle.Reference(pinhole_box())
+    out = {}
+    for (w, h) in ((64, 48), (1024, 512)):
+        k = 2048
+        px, py = rng.integers(0, w, k).astype(np.uint32), rng.integers(0, h, k).astype(np.uint32)
+        xi = rng.random((k, 5), dtype=np.float32)
+        origin, direction, weight = ref.eye_rays(w, h, 0.036, 0.036 * h / w, px, py, xi)
+        for key, val in dict(px=px, py=py, xi=xi, origin=origin, direction=direction, weight=weight).items():
+            out[f"{w}x{h}.{key}"] = val
+    image, stats = ref.render_stream(48, 32, 0.036, 0.024, 2, 32, 5, 0)
+    out["48x32.begin2.spp32.seed5.image"] = image
+    out["48x32.begin2.spp32.seed5.rays"] = np.array([stats["rays"], stats["truncated"]], dtype=np.uint64)
+    d = unit(rng, 4096)
+    pos = np.tile(np.array([[0.2, 0.1, 0.9]], np.float32), (4096, 1))
+    pixel, value = ref.lens_response(64, 48, 0.036, 0.027, pos, d)
+    out.update({"response.position": pos, "response.dir_out": d, "response.64x48.pixel": pixel, "response.64x48.value": value})
+    np.savez_compressed(os.path.join(GOLDEN, "pinhole.npz"), **out)
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "pinhole":
+        pinhole_fixture()
+        return
     if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "lt":
         light_tracing_fixture()
         return

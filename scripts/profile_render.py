@@ -13,7 +13,7 @@ from amber_b200.render import Device, Sensor  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--spp", type=int, default=16)
 ap.add_argument("--size", type=int, default=1024)
-ap.add_argument("--estimator", default="nee", choices=["nee", "reference"])
+ap.add_argument("--estimator", default="nee", choices=["nee", "reference", "lt"])
 ap.add_argument("--mesh", type=int, default=-1, help="icosphere subdivisions (config 4); -1 = built-in Cornell box")
 ap.add_argument("--pool", type=int, default=0)
 ap.add_argument("--lib", default=None, help="alternative libamber_cuda.so (build variants)")
@@ -25,7 +25,7 @@ scene = cornel_box() if args.mesh < 0 else cornel_mesh(args.mesh)
 with Device(0, lib_path=args.lib) as dev:
     dev.upload_scene(scene)
     dev.set_sensor(Sensor(args.size, args.size))
-    est = capi.ESTIMATOR_NEE if args.estimator == "nee" else capi.ESTIMATOR_REFERENCE
+    est = {"nee": capi.ESTIMATOR_NEE, "reference": capi.ESTIMATOR_REFERENCE, "lt": capi.ESTIMATOR_LIGHT_TRACING}[args.estimator]
     dev.set_profiling(args.profile)
     for _ in range(args.repeat):
         dev.film_clear()

@@ -107,3 +107,27 @@ def light_tracing_box():
     the lens inside the field of view (in the Cornell box: three in a hundred thousand), so
     light-tracing images hold hundreds of splats at test sizes."""
     return diffuse_box(aperture_radius=0.25, extra=True)
+
+
+def pinhole_box():
+    """A closed box seen through MakePinholeLens (tilted, off-centre transform): row N1's second
+    lens (src/amber/scene/lens_pinhole.cc)."""
+    from amber_b200 import FlatSceneBuilder
+    b = FlatSceneBuilder()
+    b.make_pinhole_lens([0.8, 0, 0.6, 0.2, 0, 1, 0, 0.1, -0.6, 0, 0.8, 0.9, 0, 0, 0, 1], 0.04)
+
+    def quad(m, p0, p1, p2, p3):
+        b.add_triangle(p0, p1, p2, m)
+        b.add_triangle(p2, p3, p0, m)
+
+    grey = b.make_lambertian((.6, .6, .6))
+    light = b.make_diffuse_light((4.0, 4.0, 3.0))
+    quad(grey, (-1, -1, 1), (1, -1, 1), (1, -1, -1), (-1, -1, -1))
+    quad(grey, (-1, 1, 1), (-1, 1, -1), (1, 1, -1), (1, 1, 1))
+    quad(b.make_lambertian((.6, .2, .2)), (-1, -1, 1), (-1, -1, -1), (-1, 1, -1), (-1, 1, 1))
+    quad(grey, (1, -1, 1), (1, 1, 1), (1, 1, -1), (1, -1, -1))
+    quad(b.make_phong((.7, .7, .7), 16), (-1, -1, -1), (1, -1, -1), (1, 1, -1), (-1, 1, -1))
+    quad(grey, (-1, -1, 1), (-1, 1, 1), (1, 1, 1), (1, -1, 1))
+    quad(light, (-0.5, 0.98, 0.5), (-0.5, 0.98, -0.5), (0.5, 0.98, -0.5), (0.5, 0.98, 0.5))
+    b.add_sphere((0.3, -0.6, -0.3), 0.4, b.make_refraction(1.5))
+    return b.build()

@@ -11,7 +11,7 @@ differ, so image checks require >= 99 % of pixels to agree to 2e-3 relative.
 import numpy as np
 import pytest
 
-from conftest import FILM, diffuse_box, golden, image_agreement, light_tracing_box, unit_vectors
+from conftest import FILM, diffuse_box, golden, image_agreement, light_tracing_box, pinhole_box, unit_vectors
 
 pytestmark = pytest.mark.gpu
 
@@ -527,3 +527,34 @@ def test_light_tracing_refuses_what_it_cannot_sample(device):
         with pytest.raises(AmberCudaError):
             device.render(0, 1, estimator=capi.ESTIMATOR_LIGHT_TRACING)
         device.render(0, 1, estimator=capi.ESTIMATOR_REFERENCE)  # the path tracer takes both
+
+
+# ---- pinhole lens (row N1): src/amber/scene/lens_pinhole.cc --------------------------------
+def test_pinhole_lens(device, oracle_lib):
+    from amber_b200 import Sensor
+    g = golden("pinhole.npz")
+    scene = pinhole_box()
+    device.upload_scene(scene)
+    for (w, h) in ((64, 48), (1024, 512)):
+        tag = f"{w}x{h}"
+        device.set_sensor(Sensor(w, h))
+        o, d, wt = device.eye_rays(g[f"{tag}.px"], g[f"{tag}.py"], g[f"{tag}.xi"])
+        assert np.array_equal(o, g[f"{tag}.origin"]) and np.array_equal(d, g[f"{tag}.direction"])
+        assert np.allclose(wt, g[f"{tag}.weight"], rtol=2e-5)
+    device.set_sensor(Sensor(64, 48))
+    pixel, value = device.lens_response(g["response.position"], g["response.dir_out"])
+    same = pixel == g["response.64x48.pixel"]
+    assert same.mean() >= 0.9995 and np.array_equal(value[same], g["response.64x48.value"][same])
+    # the reference's image on the shared stream, then the NEE estimator against the oracle
+    device.set_sensor(Sensor(48, 32, 0.036, 0.024))
+    device.render(2, 32, seed=5, estimator=0)
+    image, _ = device.resolve()
+    assert image_agreement(image, g["48x32.begin2.spp32.seed5.image"]) >= 0.99
+    rays = int(g["48x32.begin2.spp32.seed5.rays"][0])
+    assert abs(device.stats()["closest_rays"] - rays) <= 2e-3 * rays
+    oracle = oracle_lib.Oracle(scene)
+    device.film_clear()
+    device.render(0, 16, seed=6, max_depth=12, estimator=1)
+    image, _ = device.resolve()
+    want, _ = oracle.render(48, 32, 0.036, 0.024, 0, 16, 6, 12, estimator=1)
+    assert image_agreement(image, want) >= 0.99

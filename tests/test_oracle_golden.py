@@ -141,3 +141,21 @@ def test_light_tracing_matches_reference(oracle, oracle_lib):
         assert np.array_equal(image, g[f"box.96x64.spp64.seed24.depth{depth}.image"]), depth
         assert (stats["closest_rays"], stats["truncated"], stats["splats"]) == tuple(int(v) for v in want)
     assert int(g["box.96x64.spp64.seed24.depth3.stats"][1]) > 0
+
+
+def test_pinhole_lens_matches_reference(oracle_lib):
+    """Row N1's second lens, MakePinholeLens (tests/golden/pinhole.npz)."""
+    from conftest import pinhole_box
+    g = golden("pinhole.npz")
+    orc = oracle_lib.Oracle(pinhole_box())
+    for (w, h) in ((64, 48), (1024, 512)):
+        tag = f"{w}x{h}"
+        o, d, wt = orc.eye_rays(w, h, 0.036, 0.036 * h / w, g[f"{tag}.px"], g[f"{tag}.py"], g[f"{tag}.xi"])
+        assert np.array_equal(o, g[f"{tag}.origin"]) and np.array_equal(d, g[f"{tag}.direction"])
+        assert np.array_equal(wt, g[f"{tag}.weight"])
+        assert np.all(o == np.array([0.2, 0.1, 0.9], np.float32))  # every ray leaves the lens origin
+    image, stats = orc.render(48, 32, 0.036, 0.024, 2, 32, 5, 0, estimator=0)
+    assert np.array_equal(image, g["48x32.begin2.spp32.seed5.image"])
+    assert stats["closest_rays"] == int(g["48x32.begin2.spp32.seed5.rays"][0])
+    pixel, value = orc.lens_response(64, 48, 0.036, 0.027, g["response.position"], g["response.dir_out"])
+    assert np.array_equal(pixel, g["response.64x48.pixel"]) and np.array_equal(value, g["response.64x48.value"])

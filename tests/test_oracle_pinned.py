@@ -3,7 +3,7 @@ on fresh random inputs.  Skipped where the reference was not built; the committe
 fixtures (test_oracle_golden.py) cover that case."""
 import numpy as np
 
-from conftest import FILM, light_tracing_box, unit_vectors
+from conftest import FILM, light_tracing_box, pinhole_box, unit_vectors
 
 
 def test_flat_cornell_is_the_builtin_cornel_box(reference, oracle_lib):
@@ -143,3 +143,29 @@ def test_light_tracing_images_bit_exact(reference, oracle, oracle_lib):
         assert sa["splats"] == sb["splats"] and sa["splats"] > 100
         assert sa["rays"] == sb["closest_rays"] and sa["truncated"] == sb["truncated"]
         assert np.array_equal(a, b)
+
+
+# ---- pinhole lens (row N1): src/amber/scene/lens_pinhole.cc ---------------------------------
+def test_pinhole_lens_bit_exact(oracle_lib):
+    if not oracle_lib.reference_available():
+        import pytest
+        pytest.skip("oracle/_ref/libamber_ref.so not built (needs /root/reference)")
+    flat = pinhole_box()
+    ref, orc = oracle_lib.Reference(flat), oracle_lib.Oracle(flat)
+    rng = np.random.default_rng(41)
+    for (w, h) in ((64, 48), (1024, 512)):
+        n = 5000
+        px, py = rng.integers(0, w, n), rng.integers(0, h, n)
+        xi = rng.random((n, 5), dtype=np.float32)
+        film = (0.036, 0.036 * h / w)
+        for x, y in zip(ref.eye_rays(w, h, *film, px, py, xi), orc.eye_rays(w, h, *film, px, py, xi)):
+            assert np.array_equal(x, y)
+    for estimator_depth in (0, 4):
+        a, sa = ref.render_stream(48, 32, 0.036, 0.024, 2, 32, 5, estimator_depth)
+        b, sb = orc.render(48, 32, 0.036, 0.024, 2, 32, 5, estimator_depth, estimator=0)
+        assert np.array_equal(a, b) and sa["rays"] == sb["closest_rays"] and a.mean() > 0
+    d = unit_vectors(rng, 5000)
+    pos = np.tile(np.array([[0.2, 0.1, 0.9]], np.float32), (5000, 1))
+    pa, va = ref.lens_response(64, 48, 0.036, 0.027, pos, d)
+    pb, vb = orc.lens_response(64, 48, 0.036, 0.027, pos, d)
+    assert np.array_equal(pa, pb) and np.array_equal(va, vb) and (pa >= 0).any()
