@@ -185,6 +185,7 @@ struct ConstListHost {
   std::vector<AxisEntry> axis_entries;
   std::vector<uint8_t> axis_tri;
   int32_t n_axis_entries[3] = {0, 0, 0};
+  std::vector<AxisCluster> clusters;
   std::vector<PlaneGroup> groups;
   std::vector<PlaneEntry> entries;
 };
@@ -283,19 +284,37 @@ void group_by_plane(const amber_cuda_primitive* prims, std::vector<uint32_t>& tr
     batches.push_back(std::move(batch));
   }
 
-  // emit: entries perpendicular to x, y, z (AxisEntry), then everything else (PlaneGroup)
+  // emit: entries perpendicular to x, y, z (AxisEntry), the clustered planes (three or more entries
+  // in one plane: AxisCluster), then everything else (PlaneGroup)
   tri_ids.clear();
-  for (int axis = 0; axis < 3; axis++) {
-    const int ka = (axis + 1) % 3, kb = (axis + 2) % 3;
+  auto clustered = [&](const Batch& B) { return B.quads.size() + B.tris.size() >= 3; };
+  size_t n_clustered = 0;
+  for (const Batch& B : batches) n_clustered += B.axis >= 0 && clustered(B);
+  const bool use_clusters = n_clustered <= static_cast<size_t>(kMaxAxisClusters);
+  for (int pass = 0; pass < 4; pass++) {  // pass 0-2: unclustered entries of axis x, y, z; pass 3: clusters
     for (size_t g = 0; g < found.size(); g++) {
       const Batch& B = batches[g];
-      if (B.axis != axis) continue;
-      const Group& G = found[g];
+      if (B.axis < 0) continue;
+      const bool in_cluster = use_clusters && clustered(B);
+      if (pass < 3 ? (in_cluster || B.axis != pass) : !in_cluster) continue;
+      const int axis = B.axis;
+      const int ka = (axis + 1) % 3, kb = (axis + 2) % 3;
+      AxisCluster cluster{};
+      cluster.first = static_cast<int32_t>(out.axis_entries.size());
+      cluster.axis = axis;
+      cluster.r_k = (float)comp(found[g].anchor, axis);
+      double lo_a = 1e300, hi_a = -1e300, lo_b = 1e300, hi_b = -1e300;
       uint32_t tri = static_cast<uint32_t>(tri_ids.size());
       for (int is_tri = 0; is_tri < 2; is_tri++) {
         for (const Corner& c : is_tri ? B.tris : B.quads) {
           D3 nu, nv;
           edge_vectors(c, nu, nv);
+          for (int corner = 0; corner < 4; corner++) {  // r, r + e1, r + e2, r + e1 + e2 (a superset for a triangle)
+            const double wa = comp(c.r, ka) + (corner & 1 ? comp(c.e1, ka) : 0) + (corner & 2 ? comp(c.e2, ka) : 0);
+            const double wb = comp(c.r, kb) + (corner & 1 ? comp(c.e1, kb) : 0) + (corner & 2 ? comp(c.e2, kb) : 0);
+            lo_a = std::min(lo_a, wa); hi_a = std::max(hi_a, wa);
+            lo_b = std::min(lo_b, wb); hi_b = std::max(hi_b, wb);
+          }
           AxisEntry e;
           e.r_k = (float)comp(c.r, axis);
           e.r_a = (float)comp(c.r, ka);
@@ -307,9 +326,17 @@ void group_by_plane(const amber_cuda_primitive* prims, std::vector<uint32_t>& tr
           e.limit = is_tri ? 1.0f : 2.0f;
           out.axis_entries.push_back(e);
           out.axis_tri.push_back(static_cast<uint8_t>(tri));
-          out.n_axis_entries[axis]++;
+          if (pass < 3) out.n_axis_entries[axis]++;
           tri += is_tri ? 1 : 2;
         }
+      }
+      if (pass == 3) {
+        // the rectangle is widened by far more than the rounding of the fast plane point
+        const double slack = 1e-4 * std::max({hi_a - lo_a, hi_b - lo_b, 1e-3});
+        cluster.count = static_cast<int32_t>(out.axis_entries.size()) - cluster.first;
+        cluster.a_min = (float)(lo_a - slack); cluster.a_max = (float)(hi_a + slack);
+        cluster.b_min = (float)(lo_b - slack); cluster.b_max = (float)(hi_b + slack);
+        out.clusters.push_back(cluster);
       }
       tri_ids.insert(tri_ids.end(), B.quad_ids.begin(), B.quad_ids.end());
       tri_ids.insert(tri_ids.end(), B.lone_ids.begin(), B.lone_ids.end());
@@ -685,6 +712,8 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   ctx->const_scene.n_spheres = static_cast<int32_t>(n_spheres);
   ctx->const_scene.n_groups = static_cast<int32_t>(const_list.groups.size());
   for (int axis = 0; axis < 3; axis++) ctx->const_scene.n_axis_entries[axis] = const_list.n_axis_entries[axis];
+  ctx->const_scene.n_clusters = static_cast<int32_t>(const_list.clusters.size());
+  for (size_t c = 0; c < const_list.clusters.size(); c++) ctx->const_scene.cluster[c] = const_list.clusters[c];
   for (size_t k = 0; k < const_list.axis_entries.size(); k++) {
     ctx->const_scene.axis_entry[k] = const_list.axis_entries[k];
     ctx->const_scene.axis_tri[k] = const_list.axis_tri[k];

@@ -144,7 +144,7 @@ struct ConstList {
   static __device__ __forceinline__ bool scan_triangles(const Ray& ray, float& t_best, int& prim) {
     bool any = false;
     const int nx = c_scene.n_axis_entries[0], ny = c_scene.n_axis_entries[1], nz = c_scene.n_axis_entries[2];
-    if (nx + ny + nz > 0) {
+    if (nx + ny + nz + c_scene.n_clusters > 0) {
       float ix, iy, iz;  // 1 / 0 = inf: t = +-inf or NaN rejects the plane, as n.d == 0 does elsewhere
       asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ix) : "f"(ray.d.x));
       asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iy) : "f"(ray.d.y));
@@ -155,6 +155,28 @@ struct ConstList {
       if (kAnyHit && any) return true;
       any |= scan_axis<kAnyHit>(nx + ny, nz, ray.o.z, ray.o.x, ray.o.y, iz, ray.d.x, ray.d.y, t_best, prim);
       if (kAnyHit && any) return true;
+      // clusters: one bounding-rectangle test per plane, entries only if some lane lands inside.
+      // The vote only ever ADDS work (a lane that lands inside always scans), so which lanes take
+      // part in it does not matter.
+      const int n_clusters = c_scene.n_clusters;
+#pragma unroll 1
+      for (int c = 0; c < n_clusters; c++) {
+        const AxisCluster& C = c_scene.cluster[c];
+        const int axis = C.axis;
+        const float ok = axis == 0 ? ray.o.x : axis == 1 ? ray.o.y : ray.o.z;
+        const float oa = axis == 0 ? ray.o.y : axis == 1 ? ray.o.z : ray.o.x;
+        const float ob = axis == 0 ? ray.o.z : axis == 1 ? ray.o.x : ray.o.y;
+        const float ik = axis == 0 ? ix : axis == 1 ? iy : iz;
+        const float da = axis == 0 ? ray.d.y : axis == 1 ? ray.d.z : ray.d.x;
+        const float db = axis == 0 ? ray.d.z : axis == 1 ? ray.d.x : ray.d.y;
+        const float t = (C.r_k - ok) * ik;
+        const float pa = fmaf(t, da, oa), pb = fmaf(t, db, ob);
+        const bool inside = (t > kEpsF) & (t < t_best) & (pa >= C.a_min) & (pa <= C.a_max) & (pb >= C.b_min) & (pb <= C.b_max);
+        if (__any_sync(__activemask(), inside)) {
+          any |= scan_axis<kAnyHit>(C.first, C.count, ok, oa, ob, ik, da, db, t_best, prim);
+          if (kAnyHit && any) return true;
+        }
+      }
     }
     const int n_groups = c_scene.n_groups;
     for (int g = 0; g < n_groups; g++) {

@@ -116,10 +116,22 @@ struct AxisEntry {
   float nv_b, limit;
 };
 
+// Three or more axis entries in ONE plane (the blades of the aperture, a tessellated wall) form a
+// cluster: the ray/plane point is tested against the cluster's bounding rectangle first and the
+// entries are scanned only if some lane of the warp lands inside it.  The Cornell box's aperture fan
+// (6 entries, reached by 3 rays in 1e5) is skipped this way.
+constexpr int kMaxAxisClusters = 16;
+struct AxisCluster {
+  float r_k, a_min, a_max, b_min;
+  float b_max;
+  int32_t first, count, axis;  // entries axis_entry[first, first + count)
+};
 struct ConstScene {
   int32_t n_tris, n_spheres, n_groups;
-  int32_t n_axis_entries[3];  // entries perpendicular to x, y, z: axis_entry[] holds them in that order
-  int32_t pad[2];
+  int32_t n_axis_entries[3];  // unclustered entries perpendicular to x, y, z: axis_entry[] holds them in that order
+  int32_t n_clusters;         // clustered entries follow in axis_entry[]
+  int32_t pad;
+  AxisCluster cluster[kMaxAxisClusters];
   AxisEntry axis_entry[kMaxConstTris];
   uint8_t axis_tri[kMaxConstTris];  // first triangle (internal index) of each entry
   PlaneGroup group[kMaxConstTris];
