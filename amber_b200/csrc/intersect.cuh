@@ -120,7 +120,10 @@ struct ConstList {
   template <bool kAnyHit>
   static __device__ __forceinline__ bool scan_axis(int first, int count, float ok, float oa, float ob, float inv_dk,
                                                    float da, float db, float& t_best, int& prim) {
-    bool any = false;
+    // the winning entry and its s + q are kept in registers; the triangle id is looked up once
+    // after the loop instead of once per entry
+    int best = -1;
+    float best_sum = 0.0f;
 #pragma unroll 1
     for (int e = first; e < first + count; e++) {
       const AxisEntry& E = c_scene.axis_entry[e];
@@ -131,12 +134,14 @@ struct ConstList {
       const float sum = s + q;
       if ((t > kEpsF) & (t < t_best) & (s >= 0.0f) & (q >= 0.0f) & (s <= 1.0f) & (q <= 1.0f) & (sum <= E.limit)) {
         t_best = t;
-        prim = c_scene.axis_tri[e] + (sum > 1.0f ? 1 : 0);
-        any = true;
+        best = e;
+        best_sum = sum;
         if (kAnyHit) return true;
       }
     }
-    return any;
+    if (best < 0) return false;
+    prim = c_scene.axis_tri[best] + (best_sum > 1.0f ? 1 : 0);
+    return true;
   }
 
   // All constant-memory triangles: axis-perpendicular entries, then the general plane groups.
