@@ -1054,6 +1054,469 @@ void oracle_light_rays(const oracle_scene* scene, uint64_t n, const float* xi5, 
   }
 }
 
+/* ---- bidirectional path tracing (row N3) ----------------------------------------------
+ * include/amber/rendering/bidirectional_path_sampling.h restated: SubpathEvent (:46-90,281-315),
+ * GenerateLightSubpath (:726-801), GenerateEyeSubpath (:821-899), Connect (:901-1017),
+ * BidirectionalPathSamplingBuffer (:448-697: geometry factors, light / importance
+ * probabilities, technique probabilities, specular connections disabled), Combine (:1019-1068)
+ * with BalanceHeuristic (multiple_importance_sampling.h:58-69), driven per pixel as
+ * src/amber/rendering/algorithm_bdpt.cc:116-148.  Each subpath draws from its own sequential
+ * stream (philox_stream.h).  Everything in float, in the reference's operation order. */
+#define BDPT_MAX_EVENTS 64
+#define OBJECT_LENS (-2) /* the lens's own aperture object: never equal to an object found by Cast */
+
+typedef struct {
+  int object;   /* primitive index, or OBJECT_LENS on the eye's leading event */
+  int material; /* material index; -1 = Eye (leading eye event) */
+  vec3 position, normal, direction_out, weight;
+  float geometry_factor, p_backward, p_forward; /* NaN on a leading event */
+} event_t;
+
+enum { SURFACE_DIFFUSE, SURFACE_SPECULAR, SURFACE_LIGHT, SURFACE_EYE };
+static int surface_of(const oracle_scene* sc, int material) {
+  int kind;
+  if (material < 0) return SURFACE_EYE;
+  kind = sc->materials[material].kind;
+  if (kind == AMBER_CUDA_MAT_LAMBERTIAN || kind == AMBER_CUDA_MAT_PHONG) return SURFACE_DIFFUSE;
+  if (kind == AMBER_CUDA_MAT_DIFFUSE_LIGHT) return SURFACE_LIGHT;
+  if (kind == AMBER_CUDA_MAT_EYE) return SURFACE_EYE;
+  return SURFACE_SPECULAR;
+}
+static int event_is_leading(const event_t* e) { return isnan(e->geometry_factor); }
+
+/* Refraction, material_refraction.cc:41-109: Fresnel term of the branch (reflection if wo and wi
+ * are on the same side), with (radiance) or without (importance) the ior^2 scaling. */
+static float refraction_term(const amber_cuda_material* m, float r0, vec3 n, vec3 wo, vec3 wi, int adjoint) {
+  const float signed_cos_alpha = dot(wo, n);
+  const float ior = signed_cos_alpha > 0 ? 1 / m->param : m->param;
+  const float squared_cos_beta = 1 - (1 - signed_cos_alpha * signed_cos_alpha) * (ior * ior);
+  float rho_r, rho_t, signed_cos_i;
+  if (squared_cos_beta < 0) return 1; /* kDiracDelta */
+  rho_r = schlick(r0, fabsf(signed_cos_alpha));
+  rho_t = adjoint ? 1 - rho_r : (1 - rho_r) * (ior * ior);
+  signed_cos_i = dot(wi, n);
+  return signed_cos_alpha * signed_cos_i > 0 ? rho_r * 1 : rho_t * 1;
+}
+/* PDFLight (:111-143) / PDFImportance (:145-175) */
+static float refraction_pdf(const amber_cuda_material* m, float r0, vec3 n, vec3 wo, vec3 wi, int importance) {
+  const float signed_cos_alpha = dot(wo, n);
+  const float ior = signed_cos_alpha > 0 ? 1 / m->param : m->param;
+  const float squared_cos_beta = 1 - (1 - signed_cos_alpha * signed_cos_alpha) * (ior * ior);
+  float rho_r, rho_t, rho, signed_cos_i;
+  if (squared_cos_beta < 0) return 1;
+  rho_r = schlick(r0, fabsf(signed_cos_alpha));
+  signed_cos_i = dot(wi, n);
+  if (importance) {
+    rho_t = 1 - rho_r;
+    return signed_cos_alpha * signed_cos_i > 0 ? (rho_r + 0.5f) / 2 * 1.0f : (rho_t + 0.5f) / 2 * 1.0f;
+  }
+  rho_t = (1 - rho_r) * (ior * ior);
+  rho = rho_r + rho_t;
+  return signed_cos_alpha * signed_cos_i > 0 ? (rho_r / rho + 0.5f) / 2 * 1.0f : (rho_t / rho + 0.5f) / 2 * 1.0f;
+}
+
+/* Material::BSDF (adjoint = 0) / Material::AdjointBSDF (adjoint = 1) of every material kind */
+static vec3 event_bsdf(const oracle_scene* sc, int material, vec3 n, vec3 wo, vec3 wi, int adjoint) {
+  const amber_cuda_material* m;
+  vec3 rho;
+  if (material < 0) return V(1, 1, 1); /* Eye: Radiant(kDiracDelta), material_eye.h:97-117 */
+  m = &sc->materials[material];
+  rho = V(m->rgb[0], m->rgb[1], m->rgb[2]);
+  switch (m->kind) {
+    case AMBER_CUDA_MAT_LAMBERTIAN:
+    case AMBER_CUDA_MAT_PHONG: return material_bsdf(m, n, wo, wi);
+    case AMBER_CUDA_MAT_SPECULAR: /* material_specular.cc:36-50 */
+      if (dot(wo, n) * dot(wi, n) <= 0) return V(0, 0, 0);
+      return scale(1.0f, rho);
+    case AMBER_CUDA_MAT_REFRACTION: return scale(refraction_term(m, sc->r0[material], n, wo, wi, adjoint), rho);
+    case AMBER_CUDA_MAT_EYE: return V(1, 1, 1);
+    default: return V(0, 0, 0); /* DiffuseLight, material_diffuse_light.h:141-161 */
+  }
+}
+/* Material::PDFLight (importance = 0) / PDFImportance (importance = 1) */
+static float event_pdf(const oracle_scene* sc, int material, vec3 n, vec3 wo, vec3 wi, int importance) {
+  const amber_cuda_material* m;
+  if (material < 0) return 1;
+  m = &sc->materials[material];
+  switch (m->kind) {
+    case AMBER_CUDA_MAT_LAMBERTIAN: return 1 / PI_F; /* material_lambertian.cc:51-59 */
+    case AMBER_CUDA_MAT_PHONG: {                     /* material_phong.cc:64-79 */
+      const vec3 refl = perfect_reflection(wo, n, dot(wo, n));
+      const float cos_alpha = fmaxf(0, dot(wi, refl));
+      const float cos_i = fabsf(dot(wi, n));
+      return (m->param + 1) / (2 * PI_F) * powf(cos_alpha, m->param) / cos_i;
+    }
+    case AMBER_CUDA_MAT_REFRACTION: return refraction_pdf(m, sc->r0[material], n, wo, wi, importance);
+    default: return 1; /* Specular, DiffuseLight, Eye: kDiracDelta */
+  }
+}
+static float min_rr(float x) { return x < (float)kRussianRoulette ? x : (float)kRussianRoulette; } /* std::min(kRR, x) */
+static vec3 div3(vec3 a, float b) { return V(a.x / b, a.y / b, a.z / b); }
+
+static float light_pdf_area(const oracle_scene* sc, int material) { /* LightSet::PDFArea, light_set.h:106-111 */
+  const amber_cuda_material* m = &sc->materials[material];
+  return (m->rgb[0] * PI_F + m->rgb[1] * PI_F + m->rgb[2] * PI_F) / sc->total_power;
+}
+/* Lens::PDFDirection: BasicThin lens_thin.cc:138-148, BasicPinhole lens_pinhole.cc:93-108 */
+static float eye_pdf_direction(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h, vec3 dir) {
+  const vec3 d = mat3_apply(sc->local, dir);
+  if (sc->lens_kind == AMBER_CUDA_LENS_PINHOLE) {
+    const vec3 point = scale(sc->sensor_distance / d.z, d);
+    const float geometry_factor = d.z * d.z / dot(point, point);
+    return (1 / (film_w * film_h)) / geometry_factor;
+  }
+  return (float)((double)((float)((unsigned long)w * (unsigned long)h) / (film_w * film_h)) *
+                 pow((double)sc->sensor_distance, 2.0) / pow((double)d.z, 4.0));
+}
+/* prelude::GeometryFactor, geometry.h:49-75 */
+static float geometry_factor_dir(vec3 direction, float squared_distance, vec3 nx, vec3 ny) {
+  return fabsf(dot(direction, nx) * dot(direction, ny) / squared_distance);
+}
+static float geometry_factor_points(vec3 px, vec3 py, vec3 nx, vec3 ny) {
+  const vec3 xy = sub(py, px);
+  const float squared_distance = dot(xy, xy);
+  const float distance = sqrtf(squared_distance);
+  return geometry_factor_dir(V(xy.x / distance, xy.y / distance, xy.z / distance), squared_distance, nx, ny);
+}
+
+/* GenerateLightSubpath (importance = 1) / GenerateEyeSubpath (importance = 0); returns the events */
+static int generate_subpath(const oracle_scene* sc, int importance, uint32_t w, uint32_t h, float film_w,
+                            float film_h, uint32_t px, uint32_t py, sampler* s, int cap, event_t* out) {
+  vec3 origin, direction, weight, normal;
+  int n = 0, i;
+  if (cap == 0) return 0;
+  if (importance) {
+    /* the light's leading event: generate_light_ray + which light it was */
+    const float target = uniform(s) * sc->total_power;
+    uint32_t li = 0;
+    const light* l;
+    const prim* lp;
+    const amber_cuda_material* lm;
+    while (li + 1 < sc->n_lights && sc->lights[li].cumulative_power < target) li++;
+    l = &sc->lights[li];
+    lp = &sc->prims[l->prim_index];
+    lm = &sc->materials[lp->material];
+    origin = triangle_sample(lp->v0, lp->v1, lp->v2, s);
+    direction = hemisphere_psa(lp->normal, s);
+    weight = V(lm->rgb[0] * PI_F / l->pdf_area, lm->rgb[1] * PI_F / l->pdf_area, lm->rgb[2] * PI_F / l->pdf_area);
+    normal = lp->normal;
+    out[n].object = l->prim_index;
+    out[n].material = lp->material;
+  } else {
+    float wgt;
+    size_t blade;
+    /* the blade is the first camera uniform: its normal is the leading event's normal */
+    {
+      sampler probe = *s;
+      philox_stream probe_stream;
+      if (s->stream) {
+        probe_stream = *s->stream;
+        probe.stream = &probe_stream;
+      }
+      blade = sc->lens_kind == AMBER_CUDA_LENS_PINHOLE ? 0 : (size_t)floorf(uniform(&probe) * (float)sc->n_blades);
+      if (sc->lens_kind != AMBER_CUDA_LENS_PINHOLE && blade > (size_t)sc->n_blades - 1) blade = (size_t)sc->n_blades - 1;
+    }
+    generate_eye_ray(sc, w, h, film_w, film_h, px, py, s, &origin, &direction, &wgt);
+    weight = V(wgt, wgt, wgt);
+    /* BasicThin: the blade's normal (lens_thin.cc:99); BasicPinhole: Normalize(global(0, 0, -1)) (lens_pinhole.cc:62) */
+    normal = sc->lens_kind == AMBER_CUDA_LENS_PINHOLE ? normalize(mat3_apply(sc->global, V(0, 0, -1))) : sc->blades[blade][3];
+    out[n].object = OBJECT_LENS;
+    out[n].material = -1;
+  }
+  out[n].position = origin;
+  out[n].normal = normal;
+  out[n].direction_out = normal; /* SubpathEvent(object, leading), :281-294 */
+  out[n].weight = weight;
+  out[n].geometry_factor = out[n].p_backward = out[n].p_forward = NAN;
+  n++;
+  for (i = 1; i < cap && n < BDPT_MAX_EVENTS; i++) {
+    hit_t hit;
+    const int object = scene_cast(sc, origin, direction, &hit);
+    const prim* p;
+    const amber_cuda_material* m;
+    vec3 wo, wi, bsdf_backward;
+    scatter_t scatter;
+    float p_forward, p_rr_forward, p_backward, p_rr_backward;
+    event_t* e;
+    if (object < 0) break;
+    p = &sc->prims[object];
+    m = &sc->materials[p->material];
+    wo = neg(direction);
+    scatter = importance ? material_sample_importance(m, sc->r0[p->material], hit.normal, wo, s)
+                         : material_sample_light(m, sc->r0[p->material], hit.normal, wo, s);
+    wi = scatter.dir;
+    /* forward = the transport being traced, backward = the other one */
+    p_forward = event_pdf(sc, p->material, hit.normal, wo, wi, importance);
+    p_rr_forward = min_rr(max3(scatter.weight));
+    p_backward = event_pdf(sc, p->material, hit.normal, wi, wo, !importance);
+    bsdf_backward = event_bsdf(sc, p->material, hit.normal, wi, wo, !importance);
+    p_rr_backward = min_rr(max3(div3(bsdf_backward, p_backward)));
+    e = &out[n++];
+    e->object = object;
+    e->material = p->material;
+    e->position = hit.position;
+    e->normal = hit.normal;
+    e->direction_out = wo;
+    e->weight = weight;
+    e->geometry_factor = geometry_factor_dir(wo, hit.t * hit.t, normal, hit.normal);
+    e->p_backward = p_backward * p_rr_backward;
+    e->p_forward = p_forward * p_rr_forward;
+    if (uniform(s) >= p_rr_forward) break;
+    origin = hit.position;
+    direction = wi;
+    normal = hit.normal;
+    weight = mul(weight, div3(scatter.weight, p_rr_forward));
+  }
+  return n;
+}
+
+typedef struct {
+  vec3 value;
+  int has_pixel;
+  uint32_t px, py;
+} contribution_t;
+
+/* Connect, :901-1017 */
+static contribution_t bdpt_connect(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h,
+                                   const event_t* le, const event_t* ee) {
+  contribution_t c;
+  vec3 shadow_dir, to_light;
+  c.value = V(0, 0, 0);
+  c.has_pixel = 0;
+  c.px = c.py = 0;
+  if (!le && !ee) return c;
+  if (!le) { /* s = 0: the eye subpath found a light */
+    if (surface_of(sc, ee->material) != SURFACE_LIGHT) return c;
+    c.value = mul(ee->weight, material_radiance(&sc->materials[ee->material], ee->normal, ee->direction_out));
+    return c;
+  }
+  if (!ee) { /* t = 0: the light subpath found the aperture */
+    float response;
+    if (surface_of(sc, le->material) != SURFACE_EYE) return c;
+    if (!lens_response(sc, w, h, film_w, film_h, le->position, le->direction_out, &c.px, &c.py, &response)) return c;
+    c.has_pixel = 1;
+    c.value = mul(le->weight, V(response, response, response));
+    return c;
+  }
+  if (!event_is_leading(le) && surface_of(sc, le->material) != SURFACE_DIFFUSE) return c;
+  if (!event_is_leading(ee) && surface_of(sc, ee->material) != SURFACE_DIFFUSE) return c;
+  c.value = V(1, 1, 1);
+  shadow_dir = normalize(sub(ee->position, le->position)); /* Ray(origin, Vector3) normalises */
+  to_light = neg(shadow_dir);
+  if (event_is_leading(le)) { /* s = 1 */
+    c.value = mul(c.value, div3(material_radiance(&sc->materials[le->material], le->normal, shadow_dir),
+                                light_pdf_area(sc, le->material)));
+  } else {
+    c.value = mul(c.value, mul(le->weight, event_bsdf(sc, le->material, le->normal, le->direction_out, shadow_dir, 1)));
+  }
+  if (event_is_leading(ee)) { /* t = 1 */
+    float response;
+    if (!lens_response(sc, w, h, film_w, film_h, ee->position, to_light, &c.px, &c.py, &response)) {
+      c.value = V(0, 0, 0);
+      return c;
+    }
+    c.has_pixel = 1;
+    c.value = div3(mul(c.value, V(response, response, response)), sc->p_area);
+  } else {
+    c.value = mul(c.value, mul(ee->weight, event_bsdf(sc, ee->material, ee->normal, ee->direction_out, to_light, 0)));
+  }
+  if (!(max3(c.value) > 0)) {
+    c.value = V(0, 0, 0);
+    return c;
+  }
+  { /* "XXX rough check": the first object along the shadow ray must be the eye endpoint's object */
+    hit_t hit;
+    const int object = scene_cast(sc, le->position, shadow_dir, &hit);
+    if (object != ee->object) {
+      c.value = V(0, 0, 0);
+      return c;
+    }
+  }
+  c.value = scale(geometry_factor_points(le->position, ee->position, le->normal, ee->normal), c.value);
+  return c;
+}
+
+/* BidirectionalPathSamplingBuffer::Buffer + MISWeight(BalanceHeuristic), :423-697 */
+static float bdpt_mis_weight(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h,
+                             const event_t* L, int s, const event_t* E, int t) {
+  float gf[2 * BDPT_MAX_EVENTS + 2], p_light[2 * BDPT_MAX_EVENTS + 2], p_importance[2 * BDPT_MAX_EVENTS + 2];
+  float p_technique[2 * BDPT_MAX_EVENTS + 2];
+  int n_gf = 0, n_pl = 0, n_pi = 0, i;
+  const int n = s + t + 1;
+  float sum;
+  /* geometry factors */
+  for (i = 1; i < s; i++) gf[n_gf++] = L[i].geometry_factor;
+  if (s > 0 && t > 0) gf[n_gf++] = geometry_factor_points(L[s - 1].position, E[t - 1].position, L[s - 1].normal, E[t - 1].normal);
+  for (i = t - 1; i >= 1; i--) gf[n_gf++] = E[i].geometry_factor;
+  /* light probabilities */
+  for (i = 1; i < s; i++) p_light[n_pl++] = L[i].p_backward;
+  if (s > 0 && t > 0) {
+    const event_t* le = &L[s - 1];
+    const event_t* ee = &E[t - 1];
+    const vec3 din = normalize(sub(le->position, ee->position));
+    const vec3 bsdf = event_bsdf(sc, ee->material, ee->normal, ee->direction_out, din, 0);
+    const float pdf = event_pdf(sc, ee->material, ee->normal, ee->direction_out, din, 0);
+    p_light[n_pl++] = pdf * min_rr(max3(div3(bsdf, pdf)));
+  }
+  for (i = t - 2; i >= 0; i--) p_light[n_pl++] = E[i].p_forward;
+  {
+    const event_t* z0;
+    const event_t* z1;
+    if (t == 0) { z0 = &L[s - 1]; z1 = &L[s - 2]; }
+    else if (t == 1) { z0 = &E[0]; z1 = &L[s - 1]; }
+    else { z0 = &E[0]; z1 = &E[1]; }
+    p_light[n_pl - 1] = eye_pdf_direction(sc, w, h, film_w, film_h, normalize(sub(z1->position, z0->position)));
+  }
+  /* importance probabilities */
+  for (i = 0; i + 1 < s; i++) p_importance[n_pi++] = L[i].p_forward;
+  if (s > 0 && t > 0) {
+    const event_t* le = &L[s - 1];
+    const event_t* ee = &E[t - 1];
+    const vec3 din = normalize(sub(ee->position, le->position));
+    const vec3 bsdf = event_bsdf(sc, le->material, le->normal, le->direction_out, din, 1);
+    const float pdf = event_pdf(sc, le->material, le->normal, le->direction_out, din, 1);
+    p_importance[n_pi++] = pdf * min_rr(max3(div3(bsdf, pdf)));
+  }
+  for (i = t - 1; i >= 1; i--) p_importance[n_pi++] = E[i].p_backward;
+  p_importance[0] = (float)(1 / kPI); /* LightSet::PDFDirection, light_set.h:113-122 */
+  /* technique probabilities relative to the one that was used (index s) */
+  for (i = 0; i < n; i++) p_technique[i] = 1;
+  for (i = s - 1; i >= 0; i--) {
+    float p = p_technique[i + 1];
+    if (t == 0 && i == n - 2) p *= sc->p_area; else p *= p_light[i] * gf[i];
+    if (s > 0 && i == 0) p /= light_pdf_area(sc, L[0].material); else p /= p_importance[i - 1] * gf[i - 1];
+    p_technique[i] = p;
+  }
+  for (i = s + 1; i < n; i++) {
+    float p = p_technique[i - 1];
+    if (s == 0 && i == 1) p *= light_pdf_area(sc, E[t - 1].material); else p *= p_importance[i - 2] * gf[i - 2];
+    if (t > 0 && i == n - 1) p /= sc->p_area; else p /= p_light[i - 1] * gf[i - 1];
+    p_technique[i] = p;
+  }
+  /* DisableSpecularConnection */
+  for (i = 1; i + 1 < s; i++) {
+    if (surface_of(sc, L[i].material) != SURFACE_DIFFUSE) p_technique[i] = p_technique[i + 1] = 0;
+  }
+  for (i = 1; i + 1 < t; i++) {
+    if (surface_of(sc, E[i].material) != SURFACE_DIFFUSE) p_technique[n - i - 1] = p_technique[n - i - 2] = 0;
+  }
+  sum = 0;
+  for (i = 0; i < n; i++) sum = sum + p_technique[i];
+  (void)n_gf;
+  return 1 / sum;
+}
+
+typedef struct {
+  uint64_t light_events, eye_events, splats;
+} bdpt_counters;
+
+/* Thread::Render + Combine for one pixel sample; film: w*h*3 doubles */
+static void bdpt_sample(const oracle_scene* sc, uint32_t w, uint32_t h, float film_w, float film_h, uint32_t px,
+                        uint32_t py, uint64_t seed, uint64_t sample, int cap, double* film, bdpt_counters* count) {
+  event_t L[BDPT_MAX_EVENTS], E[BDPT_MAX_EVENTS];
+  philox_stream stream;
+  sampler smp = {&stream, NULL, 0, 0, 1};
+  const float n_pixels = (float)((unsigned long)w * (unsigned long)h);
+  int s_max, t_max, s, t;
+  vec3 measurement = V(0, 0, 0);
+  philox_stream_reset(&stream, seed, px + py * w, sample);
+  philox_stream_begin_sequence(&stream, PHILOX_SUBPATH_LIGHT);
+  s_max = generate_subpath(sc, 1, w, h, film_w, film_h, px, py, &smp, cap, L);
+  philox_stream_begin_sequence(&stream, PHILOX_SUBPATH_EYE);
+  t_max = generate_subpath(sc, 0, w, h, film_w, film_h, px, py, &smp, cap, E);
+  count->light_events += (uint64_t)s_max;
+  count->eye_events += (uint64_t)t_max;
+  for (s = 0; s <= s_max; s++) {
+    for (t = 0; t <= t_max; t++) {
+      contribution_t c = bdpt_connect(sc, w, h, film_w, film_h, s ? &L[s - 1] : NULL, t ? &E[t - 1] : NULL);
+      float weight;
+      if (!(max3(c.value) > 0)) continue;
+      weight = bdpt_mis_weight(sc, w, h, film_w, film_h, L, s, E, t);
+      c.value = scale(weight, c.value);
+      if (c.has_pixel) { /* light image: / sensor.Size() */
+        double* to = film + ((size_t)c.px + (size_t)c.py * w) * 3;
+        to[0] += (double)(c.value.x / n_pixels);
+        to[1] += (double)(c.value.y / n_pixels);
+        to[2] += (double)(c.value.z / n_pixels);
+        count->splats++;
+      } else {
+        measurement = add(measurement, c.value);
+      }
+    }
+  }
+  {
+    double* to = film + ((size_t)px + (size_t)py * w) * 3;
+    to[0] += (double)measurement.x;
+    to[1] += (double)measurement.y;
+    to[2] += (double)measurement.z;
+  }
+}
+
+typedef struct {
+  const oracle_scene* scene;
+  uint32_t w, h;
+  float film_w, film_h;
+  uint64_t sample_begin, seed;
+  uint32_t sample_count;
+  int cap, worker, workers;
+  double* film;
+  bdpt_counters count;
+} bdpt_job;
+
+static void* bdpt_worker(void* arg) {
+  bdpt_job* job = (bdpt_job*)arg;
+  const uint64_t n_pixels = (uint64_t)job->w * job->h;
+  uint64_t s, i;
+  memset(&job->count, 0, sizeof job->count);
+  for (s = job->sample_begin; s < job->sample_begin + job->sample_count; s++) {
+    for (i = (uint64_t)job->worker; i < n_pixels; i += (uint64_t)job->workers) {
+      bdpt_sample(job->scene, job->w, job->h, job->film_w, job->film_h, (uint32_t)(i % job->w), (uint32_t)(i / job->w),
+                  job->seed, s, job->cap, job->film, &job->count);
+    }
+  }
+  return NULL;
+}
+
+/* stats[0] light-subpath events, [1] eye-subpath events, [2] light-image splats.
+ * max_vertices: events per subpath, 1..64 (0 = 64; the reference has no cap). */
+void oracle_render_bdpt(const oracle_scene* scene, uint32_t w, uint32_t h, float film_w, float film_h,
+                        uint64_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_vertices,
+                        int threads, float* rgb, uint64_t* stats) {
+  pthread_t tid[64];
+  bdpt_job jobs[64];
+  const size_t n_values = (size_t)w * h * 3;
+  size_t v;
+  int k;
+  if (threads < 1) threads = 1;
+  if (threads > 64) threads = 64;
+  if (max_vertices == 0 || max_vertices > BDPT_MAX_EVENTS) max_vertices = BDPT_MAX_EVENTS;
+  if (stats) memset(stats, 0, 3 * sizeof(uint64_t));
+  for (k = 0; k < threads; k++) {
+    bdpt_job j;
+    memset(&j, 0, sizeof j);
+    j.scene = scene; j.w = w; j.h = h; j.film_w = film_w; j.film_h = film_h;
+    j.sample_begin = sample_begin; j.seed = seed; j.sample_count = sample_count; j.cap = (int)max_vertices;
+    j.worker = k; j.workers = threads;
+    j.film = (double*)calloc(n_values, sizeof(double));
+    jobs[k] = j;
+    pthread_create(&tid[k], NULL, bdpt_worker, &jobs[k]);
+  }
+  for (k = 0; k < threads; k++) {
+    pthread_join(tid[k], NULL);
+    if (stats) {
+      stats[0] += jobs[k].count.light_events;
+      stats[1] += jobs[k].count.eye_events;
+      stats[2] += jobs[k].count.splats;
+    }
+  }
+  for (v = 0; v < n_values; v++) {
+    double sum = 0;
+    for (k = 0; k < threads; k++) sum += jobs[k].film[v];
+    rgb[v] = (float)(sum / sample_count);
+  }
+  for (k = 0; k < threads; k++) free(jobs[k].film);
+}
+
 /* ---- test hooks -------------------------------------------------------------------- */
 void oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
   philox4x32_10(ctr, key, out);

@@ -63,6 +63,14 @@ void oracle_lens_response(const oracle_scene* scene, uint32_t w, uint32_t h, flo
 void oracle_light_rays(const oracle_scene* scene, uint64_t n, const float* xi5, float* origin,
                        float* direction, float* weight);
 
+/* Bidirectional path tracing (include/amber/rendering/bidirectional_path_sampling.h,
+ * src/amber/rendering/algorithm_bdpt.cc:116-148), each subpath on its sequential stream.
+ * max_vertices: events per subpath, 1..64 (0 = 64).  stats[0] light events, [1] eye events,
+ * [2] light-image splats. */
+void oracle_render_bdpt(const oracle_scene* scene, uint32_t w, uint32_t h, float film_w, float film_h,
+                        uint64_t sample_begin, uint32_t sample_count, uint64_t seed, uint32_t max_vertices,
+                        int threads, float* rgb, uint64_t* stats);
+
 /* Filmic (exposure 16) + Gamma (2.2) + 8-bit truncation of n_values floats (any layout). */
 void oracle_tonemap(uint64_t n_values, const float* hdr, uint8_t* ldr);
 

@@ -84,6 +84,17 @@ static inline float philox_stream_slot(philox_stream* s, uint32_t slot) {
   return (float)(s->words[slot & 3u] >> 8) * (1.0f / 16777216.0f);
 }
 
+/* Bidirectional path tracing (row N3) draws each SUBPATH from one purely sequential stream: the
+ * counter's vertex word is kPhiloxSubpath | subpath (0 = light, 1 = eye) and uniform i is word
+ * i % 4 of block i / 4 -- the reference's subpath generators interleave BSDF and Russian-roulette
+ * draws in one call order, and the device's per-thread kernel replays exactly that order. */
+#define PHILOX_SUBPATH_LIGHT 0x40000000u
+#define PHILOX_SUBPATH_EYE 0x40000001u
+static inline void philox_stream_begin_sequence(philox_stream* s, uint32_t id) {
+  philox_stream_begin_vertex(s, id);
+  s->camera_i = 0;
+}
+
 /* camera vertex: sequential slots */
 static inline float philox_stream_next_camera(philox_stream* s) { return philox_stream_slot(s, s->camera_i++); }
 /* surface vertex */

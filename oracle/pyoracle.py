@@ -184,6 +184,19 @@ class Reference:
         assert rc == 0
         return rgb, {"rays": stats[0], "truncated": stats[1], "splats": stats[2]}
 
+    def render_bdpt_stream(self, w, h, film_w, film_h, sample_begin, sample_count, seed, max_vertices=0,
+                           threads=8):
+        """The reference's own GenerateLightSubpath / GenerateEyeSubpath / Combine driven per pixel
+        as algorithm_bdpt.cc:116-148 does, each subpath on its sequential Philox stream."""
+        rgb = np.empty((h, w, 3), dtype=np.float32)
+        stats = (C.c_uint64 * 3)()
+        rc = self.lib.ref_render_bdpt_stream(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                                             C.c_float(film_h), C.c_uint64(sample_begin),
+                                             C.c_uint32(sample_count), C.c_uint64(seed),
+                                             C.c_uint32(max_vertices), C.c_uint32(threads), _ptr(rgb), stats)
+        assert rc == 0
+        return rgb, {"light_events": stats[0], "eye_events": stats[1], "splats": stats[2]}
+
 
 def reference_tonemap(rgb):
     """Gamma()(Filmic()(image)) of the unmodified reference; rgb (h, w, 3) float32 -> uint8."""
@@ -318,6 +331,14 @@ class Oracle:
                                   C.c_float(film_h), C.c_uint64(sample_begin), C.c_uint32(sample_count),
                                   C.c_uint64(seed), C.c_uint32(max_depth), C.c_int(threads), _ptr(rgb), stats)
         return rgb, {"closest_rays": stats[0], "splats": stats[1], "truncated": stats[2], "paths": stats[3]}
+
+    def render_bdpt(self, w, h, film_w, film_h, sample_begin, sample_count, seed, max_vertices=0, threads=8):
+        rgb = np.empty((h, w, 3), dtype=np.float32)
+        stats = (C.c_uint64 * 3)()
+        self.lib.oracle_render_bdpt(self.handle, C.c_uint32(w), C.c_uint32(h), C.c_float(film_w),
+                                    C.c_float(film_h), C.c_uint64(sample_begin), C.c_uint32(sample_count),
+                                    C.c_uint64(seed), C.c_uint32(max_vertices), C.c_int(threads), _ptr(rgb), stats)
+        return rgb, {"light_events": stats[0], "eye_events": stats[1], "splats": stats[2]}
 
     def ray_set(self, w, h, film_w, film_h, seed, n):
         """2n rays: n camera rays then n secondary rays (see oracle_ray_set)."""

@@ -36,6 +36,8 @@
 #include "amber/rendering/algorithm_bdpt.h"
 #include "amber/rendering/algorithm_lt.h"
 #include "amber/rendering/algorithm_pt.h"
+#include "amber/rendering/bidirectional_path_sampling.h"
+#include "amber/rendering/multiple_importance_sampling.h"
 #include "amber/rendering/context.h"
 #include "amber/rendering/leading.h"
 #include "amber/rendering/scatter.h"
@@ -593,6 +595,82 @@ int ref_render_lt_stream(void* handle, uint32_t w, uint32_t h, float film_w, flo
   if (stats) {
     stats[0] = total_rays;
     stats[1] = total_truncated;
+    stats[2] = total_splats;
+  }
+  return 0;
+}
+
+// Reproducible reference BIDIRECTIONAL PATH TRACING: BidirectionalPathTracing::Thread::operator()
+// and ::Render (src/amber/rendering/algorithm_bdpt.cc:116-148) restated -- a dozen lines -- over the
+// reference's OWN GenerateLightSubpath / GenerateEyeSubpath / Combine
+// (include/amber/rendering/bidirectional_path_sampling.h:726-1068, called unmodified).  Each
+// subpath draws from its own sequential Philox stream (philox_stream.h).  max_vertices caps
+// the events per subpath (the generators' own s / t arguments; 0 = no cap, as the reference).
+// stats: [0] light-subpath events, [1] eye-subpath events, [2] light-image splats.
+int ref_render_bdpt_stream(void* handle, uint32_t w, uint32_t h, float film_w, float film_h,
+                           uint64_t sample_begin, uint32_t sample_count, uint64_t seed,
+                           uint32_t max_vertices, uint32_t threads, float* rgb, uint64_t* stats) {
+  using rendering::path_size_type;
+  auto* ref = static_cast<RefScene*>(handle);
+  const auto sensor = MakeSensor(w, h, film_w, film_h);
+  const rendering::Scene<RGB>& scene = *ref->scene;
+  const path_size_type cap = max_vertices ? max_vertices : std::numeric_limits<path_size_type>::max();
+  if (threads < 1) threads = 1;
+  const uint64_t n_pixels = static_cast<uint64_t>(w) * h;
+  std::atomic<uint64_t> total_light{0}, total_eye{0}, total_splats{0};
+  std::vector<std::vector<double>> films(threads, std::vector<double>(n_pixels * 3, 0.0));
+  std::vector<std::thread> pool;
+  for (uint32_t worker = 0; worker < threads; worker++) {
+    pool.emplace_back([&, worker]() {
+      StreamSampler sampler;
+      sampler.camera = true;  // sequential slots
+      rendering::Subpath<RGB> light_path, eye_path;
+      rendering::BidirectionalPathSamplingBuffer<RGB> buffer;
+      prelude::SparseImage<RGB> light_image;
+      std::vector<double>& film = films[worker];
+      uint64_t n_light = 0, n_eye = 0, n_splats = 0;
+      for (uint64_t s = sample_begin; s < sample_begin + sample_count; s++) {
+        for (uint64_t i = worker; i < n_pixels; i += threads) {
+          const prelude::Pixel pixel(i % w, i / w);
+          const auto bound = sensor.Bind(pixel);
+          light_image.Clear();
+          philox_stream_reset(&sampler.stream, seed, static_cast<uint32_t>(i), s);
+          philox_stream_begin_sequence(&sampler.stream, PHILOX_SUBPATH_LIGHT);
+          rendering::GenerateLightSubpath(scene, sampler, light_path, cap);
+          philox_stream_begin_sequence(&sampler.stream, PHILOX_SUBPATH_EYE);
+          rendering::GenerateEyeSubpath(scene, bound, sampler, eye_path, cap);
+          const RGB measurement = rendering::Combine(scene, bound, light_path, eye_path,
+                                                     rendering::BalanceHeuristic(), buffer, light_image);
+          n_light += light_path.Size();
+          n_eye += eye_path.Size();
+          double* out = film.data() + i * 3;
+          out[0] += measurement.X();
+          out[1] += measurement.Y();
+          out[2] += measurement.Z();
+          for (const auto& splat : light_image) {
+            const auto p = splat.Pixel();
+            double* to = film.data() + (static_cast<size_t>(p.X()) + static_cast<size_t>(p.Y()) * w) * 3;
+            to[0] += splat.Value().X();
+            to[1] += splat.Value().Y();
+            to[2] += splat.Value().Z();
+            n_splats++;
+          }
+        }
+      }
+      total_light += n_light;
+      total_eye += n_eye;
+      total_splats += n_splats;
+    });
+  }
+  for (auto& thread : pool) thread.join();
+  for (uint64_t k = 0; k < n_pixels * 3; k++) {
+    double sum = 0;
+    for (uint32_t worker = 0; worker < threads; worker++) sum += films[worker][k];
+    rgb[k] = static_cast<float>(sum / sample_count);
+  }
+  if (stats) {
+    stats[0] = total_light;
+    stats[1] = total_eye;
     stats[2] = total_splats;
   }
   return 0;
