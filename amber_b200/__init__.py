@@ -7,5 +7,6 @@ of ``rendering::Algorithm<RGB>::Render``), ``dist`` (sample partition + film
 all-reduce), ``image_io`` (PNG / PFM output of the resolved film).  The product never imports ``oracle/``.
 """
 from . import capi, image_io, importer, scene  # noqa: F401
-from .render import Context, CudaLightTracing, CudaPathTracing, Device, Sensor  # noqa: F401
+from .render import (Context, CudaBidirectionalPathTracing, CudaLightTracing, CudaPathTracing, Device,  # noqa: F401
+                     Sensor)
 from .scene import FlatScene, FlatSceneBuilder, cornel_box, cornel_mesh  # noqa: F401

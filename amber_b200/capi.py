@@ -17,7 +17,7 @@ ABI_VERSION = 1
 
 PRIM_TRIANGLE, PRIM_SPHERE = 0, 1
 MAT_LAMBERTIAN, MAT_PHONG, MAT_SPECULAR, MAT_REFRACTION, MAT_DIFFUSE_LIGHT, MAT_EYE = range(6)
-ESTIMATOR_REFERENCE, ESTIMATOR_NEE, ESTIMATOR_LIGHT_TRACING = 0, 1, 2
+ESTIMATOR_REFERENCE, ESTIMATOR_NEE, ESTIMATOR_LIGHT_TRACING, ESTIMATOR_BDPT = 0, 1, 2, 3
 LENS_THIN, LENS_PINHOLE = 0, 1
 
 # every symbol include/amber_cuda.h declares (checked by tests/test_abi.py)

@@ -694,7 +694,8 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
     l.v1.w = m.r * kPiF / pdf_area;
     l.v2.w = m.g * kPiF / pdf_area;
     l.n.w = m.b * kPiF / pdf_area;
-    l.le_over_pdf = make_float4(m.r / pdf_area, m.g / pdf_area, m.b / pdf_area, 0.0f);
+    l.le_over_pdf = make_float4(m.r / pdf_area, m.g / pdf_area, m.b / pdf_area,
+                                __builtin_bit_cast(float, static_cast<int32_t>(tri_material[host_lights[i].tri])));
   }
 
   // ---- lens --------------------------------------------------------------------
@@ -911,6 +912,44 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
 
 
 }  // namespace amber_host
+namespace amber_host {
+
+// Bidirectional path tracing (bdpt.cuh): one kernel, one thread per (pixel, sample).
+int render_bdpt(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, uint32_t n_pixels, uint64_t total_pairs) {
+  int rc = bind_constants(ctx);
+  if (rc != AMBER_CUDA_OK) return rc;
+  RenderArgs args{};
+  args.scene = ctx->view;
+  args.ctl = ctx->d_ctl.ptr;
+  args.film = ctx->d_film.ptr;
+  args.seed = params->seed;
+  args.sample_begin = params->sample_begin;
+  args.n_pixels = n_pixels;
+  args.estimator = params->estimator;
+  args.inv_n_pixels = 1.0f / static_cast<float>(n_pixels);
+  const int cap = params->max_depth ? static_cast<int>(params->max_depth) : kBdptMaxEvents;
+  const uint64_t blocks_needed = (total_pairs + 127) / 128;
+  const unsigned int grid = static_cast<unsigned int>(std::min<uint64_t>(blocks_needed, 148ull * 16ull));
+  cudaStream_t stream = ctx->stream;
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_begin, stream));
+  if (ctx->use_bvh) {
+    bdpt_kernel<WideBvh><<<grid, 128, 0, stream>>>(args, total_pairs, cap);
+  } else {
+    bdpt_kernel<ConstList><<<grid, 128, 0, stream>>>(args, total_pairs, cap);
+  }
+  ctx->stats.kernel_launches++;
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_end, stream));
+  CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_end));
+  CUDA_TRY(ctx, cudaGetLastError());
+  float ms = 0;
+  CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
+  ctx->stats.last_render_ms = ms;
+  ctx->samples_done += params->sample_count;
+  return AMBER_CUDA_OK;
+}
+
+}  // namespace amber_host
+
 using namespace amber_host;
 
 extern "C" {
@@ -921,13 +960,18 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
   if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
   if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
   if (params->estimator != AMBER_CUDA_ESTIMATOR_REFERENCE && params->estimator != AMBER_CUDA_ESTIMATOR_NEE &&
-      params->estimator != AMBER_CUDA_ESTIMATOR_LIGHT_TRACING)
+      params->estimator != AMBER_CUDA_ESTIMATOR_LIGHT_TRACING && params->estimator != AMBER_CUDA_ESTIMATOR_BDPT)
     return fail(ctx, AMBER_CUDA_EINVAL, "unknown estimator %d", params->estimator);
-  if (params->estimator == AMBER_CUDA_ESTIMATOR_LIGHT_TRACING) {
+  if (params->estimator == AMBER_CUDA_ESTIMATOR_BDPT && params->max_depth > static_cast<uint32_t>(kBdptMaxEvents))
+    return fail(ctx, AMBER_CUDA_EINVAL, "bidirectional path tracing: max_depth (events per subpath) must be <= %d",
+                kBdptMaxEvents);
+  if (params->estimator == AMBER_CUDA_ESTIMATOR_LIGHT_TRACING || params->estimator == AMBER_CUDA_ESTIMATOR_BDPT) {
     // LightSet::GenerateRay on an empty set is undefined in the reference (light_set.h:87-92)
-    if (ctx->view.n_lights == 0) return fail(ctx, AMBER_CUDA_EINVAL, "light tracing needs at least one emitting triangle");
+    if (ctx->view.n_lights == 0)
+      return fail(ctx, AMBER_CUDA_EINVAL, "light / bidirectional path tracing needs at least one emitting triangle");
     if (ctx->has_sphere_light)
-      return fail(ctx, AMBER_CUDA_EINVAL, "light tracing: emitting spheres are not supported (triangle emitters only)");
+      return fail(ctx, AMBER_CUDA_EINVAL,
+                  "light / bidirectional path tracing: emitting spheres are not supported (triangle emitters only)");
   }
   if (params->sample_begin + params->sample_count >= (1ull << 32))
     return fail(ctx, AMBER_CUDA_EINVAL, "sample indices must stay below 2^32");
@@ -936,6 +980,7 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
 
   const uint32_t n_pixels = ctx->camera.sensor.width * ctx->camera.sensor.height;
   const uint64_t total_paths = static_cast<uint64_t>(n_pixels) * params->sample_count;
+  if (params->estimator == AMBER_CUDA_ESTIMATOR_BDPT) return render_bdpt(ctx, params, n_pixels, total_paths);
   uint64_t slots = params->pool_paths ? params->pool_paths : kDefaultPoolPaths;
   slots = std::min<uint64_t>(slots, total_paths);
   slots = std::max<uint64_t>(kBlock, (slots + kBlock - 1) / kBlock * kBlock);

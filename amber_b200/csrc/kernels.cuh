@@ -92,7 +92,7 @@ struct ScriptedRng {
 // (:132-148).  Five uniforms in the compiled reference's order: blade, u, v, film y, film x.
 template <class Rng>
 __device__ __forceinline__ void generate_eye_ray(uint32_t px, uint32_t py, Rng& rng, float3& origin,
-                                                 float3& direction, float& weight) {
+                                                 float3& direction, float& weight, float3* lens_normal = nullptr) {
   // Origin and direction are computed with the host's operations one by one (no FMA
   // contraction, IEEE sqrt / division): the camera sits 3-5 units from the scene, where
   // one ulp of the direction moves the first hit by more than kEPS, so only bit-identical
@@ -113,12 +113,15 @@ __device__ __forceinline__ void generate_eye_ray(uint32_t px, uint32_t py, Rng& 
     const float3 point = (lens.sensor_distance / back.z) * back;
     const float geometry_factor = back.z * back.z / dot(point, point);
     weight = 1.0f / (sensor.inv_area / geometry_factor);
+    // the leading event's normal (BDPT): Normalize(global(0, 0, -1)), lens_pinhole.cc:62
+    if (lens_normal) *lens_normal = normalize_exact(mat3_apply_exact(lens.global, v3(0.0f, 0.0f, -1.0f)));
     return;
   }
   const float nb = static_cast<float>(lens.n_blades);
   int blade = static_cast<int>(floorf(__fmul_rn(rng.next(), nb)));
   blade = min(lens.n_blades - 1, blade);
   const float* b = lens.blades[blade];
+  if (lens_normal) *lens_normal = v3(b[9], b[10], b[11]);  // the leading event's normal (BDPT), lens_thin.cc:99
   // Triangle::SampleSurfacePoint, src/amber/scene/primitive_triangle.cc:136-150
   float u = rng.next();
   float v = rng.next();
@@ -165,13 +168,14 @@ __device__ __forceinline__ void generate_eye_ray(uint32_t px, uint32_t py, Rng& 
 // in LightDev).  Five uniforms, like the camera vertex.
 template <class Rng>
 __device__ __forceinline__ void generate_light_ray(const SceneView& scene, Rng& rng, float3& origin,
-                                                   float3& direction, float3& weight) {
+                                                   float3& direction, float3& weight, int* light_index = nullptr) {
   const float target = __fmul_rn(rng.next(), scene.total_power);
   int lo = 0, hi = scene.n_lights - 1;
   while (lo < hi) {  // first light whose cumulative power >= target
     const int mid = (lo + hi) >> 1;
     if (__ldg(&scene.lights[mid].v0.w) < target) lo = mid + 1; else hi = mid;
   }
+  if (light_index) *light_index = lo;
   const float4* L = reinterpret_cast<const float4*>(scene.lights + lo);
   const float4 v0 = __ldg(L), v1 = __ldg(L + 1), v2 = __ldg(L + 2), nl = __ldg(L + 3);
   float u = rng.next();
@@ -940,3 +944,5 @@ __global__ void lens_response_kernel(uint64_t n, const float* __restrict__ posit
 }
 
 }  // namespace amber_cuda
+
+#include "bdpt.cuh"

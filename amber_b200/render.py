@@ -249,7 +249,7 @@ class CudaPathTracing:
     def __init__(self, estimator: str = "nee", max_depth: int = 0, seed: int = 1, device: int = 0,
                  batch_spp: int = 64, pool_paths: int = 0):
         self.estimator = {"reference": capi.ESTIMATOR_REFERENCE, "nee": capi.ESTIMATOR_NEE,
-                          "lt": capi.ESTIMATOR_LIGHT_TRACING}[estimator]
+                          "lt": capi.ESTIMATOR_LIGHT_TRACING, "bdpt": capi.ESTIMATOR_BDPT}[estimator]
         self.max_depth = max_depth
         self.seed = seed
         self.device_index = device
@@ -287,3 +287,13 @@ class CudaLightTracing(CudaPathTracing):
     def __init__(self, max_depth: int = 0, seed: int = 1, device: int = 0, batch_spp: int = 64,
                  pool_paths: int = 0):
         super().__init__("lt", max_depth, seed, device, batch_spp, pool_paths)
+
+
+class CudaBidirectionalPathTracing(CudaPathTracing):
+    """rendering::Algorithm<RGB> for ``--algorithm bdpt`` (row N3):
+    ``src/amber/rendering/algorithm_bdpt.cc:82-148`` over
+    ``include/amber/rendering/bidirectional_path_sampling.h``.  ``max_vertices`` caps the events
+    per subpath (<= 16; the reference has no cap)."""
+
+    def __init__(self, max_vertices: int = 0, seed: int = 1, device: int = 0, batch_spp: int = 64):
+        super().__init__("bdpt", max_vertices, seed, device, batch_spp, 0)

@@ -78,6 +78,13 @@ extern "C" {
  *   pixel by the lens (BasicThin::Response, src/amber/scene/lens_thin.cc:109-130) and its weight
  *   / (W*H) is added there.  Emitters must be triangles. */
 #define AMBER_CUDA_ESTIMATOR_LIGHT_TRACING 2
+/* BDPT (row N3): sample for sample src/amber/rendering/algorithm_bdpt.cc:116-148 over
+ *   include/amber/rendering/bidirectional_path_sampling.h (GenerateLightSubpath,
+ *   GenerateEyeSubpath, Connect for every (s, t), balance-heuristic MIS weights, light image) --
+ *   one sample = one light subpath + one eye subpath per pixel.  max_depth is the number of
+ *   events per subpath (0 = 16, the maximum; the reference has no cap).  Emitters must be
+ *   triangles. */
+#define AMBER_CUDA_ESTIMATOR_BDPT 3
 
 typedef struct amber_cuda_ctx amber_cuda_ctx;
 

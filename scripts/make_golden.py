@@ -143,8 +143,32 @@ def pinhole_fixture():
     np.savez_compressed(os.path.join(GOLDEN, "pinhole.npz"), **out)
 
 
+def bdpt_fixture():
+    """Row N3: images of the reference's own GenerateLightSubpath / GenerateEyeSubpath / Combine on the
+    sequential subpath streams (ref_render_bdpt_stream)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from conftest import light_tracing_box, pinhole_box
+    out = {}
+    ref = pyoracle.Reference(scene.cornel_box())
+    for (w, spp, seed, cap) in ((48, 16, 31, 12), (32, 16, 33, 3)):
+        image, stats = ref.render_bdpt_stream(w, w, *FILM, 2, spp, seed, cap)
+        tag = f"cornell.{w}x{w}.begin2.spp{spp}.seed{seed}.cap{cap}"
+        out[f"{tag}.image"] = image
+        out[f"{tag}.stats"] = np.array([stats["light_events"], stats["eye_events"], stats["splats"]], dtype=np.uint64)
+    for name, flat in (("ltbox", light_tracing_box()), ("pinhole", pinhole_box())):
+        box = pyoracle.Reference(flat)
+        image, stats = box.render_bdpt_stream(48, 32, 0.036, 0.024, 0, 16, 32, 10)
+        tag = f"{name}.48x32.begin0.spp16.seed32.cap10"
+        out[f"{tag}.image"] = image
+        out[f"{tag}.stats"] = np.array([stats["light_events"], stats["eye_events"], stats["splats"]], dtype=np.uint64)
+    np.savez_compressed(os.path.join(GOLDEN, "bdpt.npz"), **out)
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "bdpt":
+        bdpt_fixture()
+        return
     if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "pinhole":
         pinhole_fixture()
         return

@@ -13,7 +13,7 @@ from amber_b200.render import Device, Sensor  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--spp", type=int, default=16)
 ap.add_argument("--size", type=int, default=1024)
-ap.add_argument("--estimator", default="nee", choices=["nee", "reference", "lt"])
+ap.add_argument("--estimator", default="nee", choices=["nee", "reference", "lt", "bdpt"])
 ap.add_argument("--mesh", type=int, default=-1, help="icosphere subdivisions (config 4); -1 = built-in Cornell box")
 ap.add_argument("--pool", type=int, default=0)
 ap.add_argument("--lib", default=None, help="alternative libamber_cuda.so (build variants)")
@@ -25,11 +25,11 @@ scene = cornel_box() if args.mesh < 0 else cornel_mesh(args.mesh)
 with Device(0, lib_path=args.lib) as dev:
     dev.upload_scene(scene)
     dev.set_sensor(Sensor(args.size, args.size))
-    est = {"nee": capi.ESTIMATOR_NEE, "reference": capi.ESTIMATOR_REFERENCE, "lt": capi.ESTIMATOR_LIGHT_TRACING}[args.estimator]
+    est = {"nee": capi.ESTIMATOR_NEE, "reference": capi.ESTIMATOR_REFERENCE, "lt": capi.ESTIMATOR_LIGHT_TRACING, "bdpt": capi.ESTIMATOR_BDPT}[args.estimator]
     dev.set_profiling(args.profile)
     for _ in range(args.repeat):
         dev.film_clear()
-        dev.render(0, args.spp, seed=1, max_depth=32, estimator=est, pool_paths=args.pool)
+        dev.render(0, args.spp, seed=1, max_depth=0 if args.estimator == 'bdpt' else 32, estimator=est, pool_paths=args.pool)
     s = dev.stats()
     rays = s["closest_rays"] + s["shadow_rays"]
     print(f"{rays / s['last_render_ms'] / 1e3:.1f} Mrays/s, {s['paths'] / s['last_render_ms'] / 1e3:.1f} Mpaths/s, "

@@ -30,7 +30,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--config", type=int, required=True, choices=sorted(CONFIGS))
 ap.add_argument("--spp", type=int, default=0)
 ap.add_argument("--size", type=int, default=0)
-ap.add_argument("--estimator", default="nee", choices=["nee", "reference", "lt"])
+ap.add_argument("--estimator", default="nee", choices=["nee", "reference", "lt", "bdpt"])
 ap.add_argument("--depth", type=int, default=32)
 ap.add_argument("--subdivisions", type=int, default=8)
 ap.add_argument("--repeat", type=int, default=1)
@@ -54,7 +54,7 @@ dev.upload_scene(scene)
 upload_s = time.perf_counter() - t0
 dev.set_sensor(Sensor(size, size))
 begin, count = partition_samples(spp, rank, world)
-est = {"nee": capi.ESTIMATOR_NEE, "reference": capi.ESTIMATOR_REFERENCE, "lt": capi.ESTIMATOR_LIGHT_TRACING}[args.estimator]
+est = {"nee": capi.ESTIMATOR_NEE, "reference": capi.ESTIMATOR_REFERENCE, "lt": capi.ESTIMATOR_LIGHT_TRACING, "bdpt": capi.ESTIMATOR_BDPT}[args.estimator]
 
 best = None
 for _ in range(args.repeat):

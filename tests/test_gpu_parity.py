@@ -558,3 +558,55 @@ def test_pinhole_lens(device, oracle_lib):
     image, _ = device.resolve()
     want, _ = oracle.render(48, 32, 0.036, 0.024, 0, 16, 6, 12, estimator=1)
     assert image_agreement(image, want) >= 0.99
+
+
+# ---- bidirectional path tracing (row N3) ------------------------------------------------------
+def test_bidirectional_path_tracing_matches_reference_golden(device):
+    """bdpt_kernel against images of the reference's own subpath generators + Combine on the shared
+    sequential streams: Cornell box (two subpath caps), the wide-aperture box with every material
+    kind, and the pinhole box."""
+    from amber_b200 import Sensor, capi
+    from test_oracle_golden import bdpt_cases
+    for tag, make, w, h, fw, fh, begin, spp, seed, cap, want, stats in bdpt_cases():
+        device.upload_scene(make())
+        device.set_sensor(Sensor(w, h, fw, fh))
+        device.render(begin, spp, seed=seed, max_depth=cap, estimator=capi.ESTIMATOR_BDPT)
+        image, done = device.resolve()
+        frac = image_agreement(image, want, rtol=5e-3)
+        got = device.stats()
+        print(f"{tag}: {frac:.4f} of pixels agree; mean {image.mean():.6g} vs {want.mean():.6g}; splats {got['light_splats']} vs {stats[2]}")
+        assert done == spp and got["paths"] == w * h * spp
+        assert frac >= 0.98, tag
+        assert abs(got["light_splats"] - stats[2]) <= max(2, 0.05 * stats[2])
+
+
+def test_bidirectional_path_tracing_matches_oracle_and_path_tracing(device, oracle_lib):
+    from amber_b200 import Sensor, capi
+    from amber_b200.capi import AmberCudaError
+    scene = diffuse_box()
+    oracle = oracle_lib.Oracle(scene)
+    device.upload_scene(scene)
+    device.set_sensor(Sensor(64, 64))
+    device.render(0, 32, seed=12, estimator=capi.ESTIMATOR_BDPT)
+    image, _ = device.resolve()
+    want, stats = oracle.render_bdpt(64, 64, *FILM, 0, 32, 12, 16, threads=32)
+    frac = image_agreement(image, want, rtol=5e-3)
+    print(f"diffuse box 64x64x32: {frac:.4f} of pixels agree with the oracle")
+    assert frac >= 0.98
+    # same measurement as the path tracer: mean radiance per channel, many samples
+    device.set_sensor(Sensor(32, 32))
+    means = {}
+    for estimator, spp in ((capi.ESTIMATOR_BDPT, 512), (capi.ESTIMATOR_NEE, 1024)):
+        runs = []
+        for seed in range(4):
+            device.film_clear()
+            device.render(0, spp, seed=70 + seed, estimator=estimator)
+            runs.append(device.resolve()[0].mean(axis=(0, 1)))
+        means[estimator] = np.array(runs)
+    bd, pt = means[capi.ESTIMATOR_BDPT], means[capi.ESTIMATOR_NEE]
+    diff = bd.mean(0) - pt.mean(0)
+    sigma = np.sqrt(bd.var(0, ddof=1) / 4 + pt.var(0, ddof=1) / 4)
+    print("bdpt", bd.mean(0), "pt", pt.mean(0), "sigma", sigma)
+    assert np.all(np.abs(diff) < 4 * sigma + 2e-2 * pt.mean(0)), (diff, sigma)
+    with pytest.raises(AmberCudaError):  # more events per subpath than the kernel stores
+        device.render(0, 1, max_depth=17, estimator=capi.ESTIMATOR_BDPT)

@@ -159,3 +159,26 @@ def test_pinhole_lens_matches_reference(oracle_lib):
     assert stats["closest_rays"] == int(g["48x32.begin2.spp32.seed5.rays"][0])
     pixel, value = orc.lens_response(64, 48, 0.036, 0.027, g["response.position"], g["response.dir_out"])
     assert np.array_equal(pixel, g["response.64x48.pixel"]) and np.array_equal(value, g["response.64x48.value"])
+
+
+def bdpt_cases():
+    from amber_b200 import cornel_box
+    from conftest import light_tracing_box, pinhole_box
+    g = golden("bdpt.npz")
+    scenes = {"cornell": cornel_box, "ltbox": light_tracing_box, "pinhole": pinhole_box}
+    for tag in sorted({k.rsplit(".", 1)[0] for k in g.files}):
+        name, size, begin, spp, seed, cap = tag.split(".")
+        w, h = (int(v) for v in size.split("x"))
+        yield (tag, scenes[name], w, h, 0.036, 0.036 * h / w, int(begin[5:]), int(spp[3:]), int(seed[4:]), int(cap[3:]),
+               g[f"{tag}.image"], tuple(int(v) for v in g[f"{tag}.stats"]))
+
+
+def test_bidirectional_path_tracing_matches_reference(oracle_lib):
+    """Row N3: images of the reference's own subpath generators and Combine (tests/golden/bdpt.npz)."""
+    n = 0
+    for tag, make, w, h, fw, fh, begin, spp, seed, cap, want, stats in bdpt_cases():
+        image, got = oracle_lib.Oracle(make()).render_bdpt(w, h, fw, fh, begin, spp, seed, cap)
+        assert np.array_equal(image, want), tag
+        assert (got["light_events"], got["eye_events"], got["splats"]) == stats, tag
+        n += 1
+    assert n == 4

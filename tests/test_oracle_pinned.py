@@ -169,3 +169,19 @@ def test_pinhole_lens_bit_exact(oracle_lib):
     pa, va = ref.lens_response(64, 48, 0.036, 0.027, pos, d)
     pb, vb = orc.lens_response(64, 48, 0.036, 0.027, pos, d)
     assert np.array_equal(pa, pb) and np.array_equal(va, vb) and (pa >= 0).any()
+
+
+# ---- bidirectional path tracing (row N3) ----------------------------------------------------
+def test_bidirectional_path_tracing_bit_exact(reference, oracle, oracle_lib):
+    """The C restatement of bidirectional_path_sampling.h against the reference's own
+    GenerateLightSubpath / GenerateEyeSubpath / Combine (called unmodified by the harness): images,
+    subpath lengths and light-image splats, with and without a tight cap on the subpath length."""
+    for cap in (12, 3):
+        a, sa = reference.render_bdpt_stream(40, 40, *FILM, 2, 16, 31, cap)
+        b, sb = oracle.render_bdpt(40, 40, *FILM, 2, 16, 31, cap)
+        assert sa == sb and np.array_equal(a, b) and a.mean() > 0
+    for flat, film in ((light_tracing_box(), (0.036, 0.024)), (pinhole_box(), (0.036, 0.024))):
+        ref_box, orc_box = oracle_lib.Reference(flat), oracle_lib.Oracle(flat)
+        a, sa = ref_box.render_bdpt_stream(48, 32, *film, 0, 16, 32, 10)
+        b, sb = orc_box.render_bdpt(48, 32, *film, 0, 16, 32, 10)
+        assert sa == sb and np.array_equal(a, b) and a.mean() > 0
