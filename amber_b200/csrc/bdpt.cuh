@@ -43,14 +43,32 @@ struct SequentialRng {
   }
 };
 
-// SubpathEvent, bidirectional_path_sampling.h:46-90,281-315
+// SubpathEvent, bidirectional_path_sampling.h:46-90,281-315, as five float4 so that local-memory
+// accesses are 128-bit and the MIS weight (which walks every event of both subpaths for every
+// connection) reads ONE of them per event: `mis` = geometry factor, backward pdf, forward pdf
+// (NaN on a leading event) and material | surface type << 28.
 struct BdptEvent {
-  int32_t object;    // internal primitive index; kObjectLens on the eye's leading event
-  int32_t material;  // material index; -1 = Eye (the eye's leading event)
-  float3 position, normal, direction_out, weight;
-  float geometry_factor, p_backward, p_forward;  // NaN on a leading event
-  __device__ __forceinline__ bool leading() const { return isnan(geometry_factor); }
+  float4 mis;      // geometry_factor, p_backward, p_forward, bits
+  float4 pos_obj;  // position, object (internal primitive index; kObjectLens / -3 - light on a leading event)
+  float4 normal4;
+  float4 dout4;    // direction_out
+  float4 weight4;
+  __device__ __forceinline__ bool leading() const { return isnan(mis.x); }
+  __device__ __forceinline__ int32_t object() const { return __float_as_int(pos_obj.w); }
+  __device__ __forceinline__ int32_t material() const {  // -1 = Eye (the eye's leading event)
+    const int32_t bits = __float_as_int(mis.w);
+    return bits < 0 ? -1 : (bits & 0x0fffffff);
+  }
+  __device__ __forceinline__ int surface() const { return (__float_as_int(mis.w) >> 28) & 3; }
+  __device__ __forceinline__ float3 position() const { return v3(pos_obj); }
+  __device__ __forceinline__ float3 normal() const { return v3(normal4); }
+  __device__ __forceinline__ float3 direction_out() const { return v3(dout4); }
+  __device__ __forceinline__ float3 weight() const { return v3(weight4); }
 };
+// bits of a leading eye event: sign bit set (material -1), surface Eye
+__device__ __forceinline__ float event_bits(int material, int surface) {
+  return __int_as_float(material < 0 ? static_cast<int32_t>(0x80000000u | (3u << 28)) : (material | (surface << 28)));
+}
 
 enum : int { kSurfaceDiffuse = 0, kSurfaceSpecular = 1, kSurfaceLight = 2, kSurfaceEye = 3 };
 __device__ __forceinline__ int surface_of_kind(int kind) {
@@ -122,10 +140,7 @@ __device__ __forceinline__ void refraction_terms(const MaterialDev& m, float3 n,
 // Material::BSDF (adjoint = false) / AdjointBSDF (true) for every material kind:
 // material_{lambertian,phong,specular}.cc (symmetric), material_refraction.cc,
 // material_diffuse_light.h:141-161 (0), material_eye.h:97-117 (kDiracDelta).
-__device__ __forceinline__ float3 event_bsdf(const SceneView& scene, int material, float3 n, float3 wo, float3 wi,
-                                             bool adjoint) {
-  if (material < 0) return v3(1.0f, 1.0f, 1.0f);
-  const MaterialDev m = load_material(scene, material);
+__device__ __forceinline__ float3 event_bsdf(const MaterialDev& m, float3 n, float3 wo, float3 wi, bool adjoint) {
   const float3 rho = v3(m.r, m.g, m.b);
   switch (m.kind) {
     case 0:
@@ -142,10 +157,7 @@ __device__ __forceinline__ float3 event_bsdf(const SceneView& scene, int materia
 }
 
 // Material::PDFLight (importance = false) / PDFImportance (true)
-__device__ __forceinline__ float event_pdf(const SceneView& scene, int material, float3 n, float3 wo, float3 wi,
-                                           bool importance) {
-  if (material < 0) return 1.0f;
-  const MaterialDev m = load_material(scene, material);
+__device__ __forceinline__ float event_pdf(const MaterialDev& m, float3 n, float3 wo, float3 wi, bool importance) {
   switch (m.kind) {
     case 0: return 1.0f / kPiF;  // material_lambertian.cc:51-59
     case 1: {                    // material_phong.cc:64-79
@@ -195,33 +207,38 @@ struct BdptCounters {
   uint32_t casts, splats;
 };
 
-// GenerateLightSubpath (kImportance = true, :726-801) / GenerateEyeSubpath (false, :821-899)
+// GenerateLightSubpath (kImportance = true, :726-801) / GenerateEyeSubpath (false, :821-899).
+// Returns the number of events; `specular` gets one bit per event whose surface is not Diffuse.
 template <class Accel, bool kImportance>
 __device__ __forceinline__ int generate_subpath(const RenderArgs& args, uint32_t pixel, SequentialRng& rng, int cap,
-                                                BdptEvent* out, BdptCounters& count) {
+                                                BdptEvent* out, uint32_t& specular, BdptCounters& count) {
   const SceneView& scene = args.scene;
   Ray ray;
   float3 weight, normal;
+  int32_t object;
+  float bits;
   if (kImportance) {
     int light_index;
     generate_light_ray(scene, rng, ray.o, ray.d, weight, &light_index);
     const float4* L = reinterpret_cast<const float4*>(scene.lights + light_index);
     normal = v3(__ldg(L + 3));
-    out[0].object = -3 - light_index;
-    out[0].material = __float_as_int(__ldg(L + 4).w);
+    object = -3 - light_index;
+    bits = event_bits(__float_as_int(__ldg(L + 4).w), kSurfaceLight);
   } else {
     const uint32_t width = c_camera.sensor.width;
     float w;
     generate_eye_ray(pixel % width, pixel / width, rng, ray.o, ray.d, w, &normal);
     weight = v3(w, w, w);
-    out[0].object = kObjectLens;
-    out[0].material = -1;
+    object = kObjectLens;
+    bits = event_bits(-1, kSurfaceEye);
   }
-  out[0].position = ray.o;
-  out[0].normal = normal;
-  out[0].direction_out = normal;  // SubpathEvent(object, leading), :281-294
-  out[0].weight = weight;
-  out[0].geometry_factor = out[0].p_backward = out[0].p_forward = CUDART_NAN_F;
+  // SubpathEvent(object, leading), :281-294: direction_out = normal, NaN geometry factor and pdfs
+  out[0].mis = make_float4(CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F, bits);
+  out[0].pos_obj = make_float4(ray.o.x, ray.o.y, ray.o.z, __int_as_float(object));
+  out[0].normal4 = make_float4(normal.x, normal.y, normal.z, 0.0f);
+  out[0].dout4 = out[0].normal4;
+  out[0].weight4 = make_float4(weight.x, weight.y, weight.z, 0.0f);
+  specular = 1u;  // a leading event is never "Diffuse"; bit 0 is not looked at
   int n = 1;
   for (int i = 1; i < cap; i++) {
     const HitRecord hit = closest_lane<Accel>(scene, ray);
@@ -235,21 +252,20 @@ __device__ __forceinline__ int generate_subpath(const RenderArgs& args, uint32_t
     const Scatter scatter = sample_light(m, hn, wo, rng, kImportance);
     const float3 wi = scatter.dir;
     // forward = the transport being traced, backward = the other one
-    const float p_forward = event_pdf(scene, material_index, hn, wo, wi, kImportance);
+    const float p_forward = event_pdf(m, hn, wo, wi, kImportance);
     const float p_rr_forward = min_rr(max3(scatter.weight));
-    const float p_backward = event_pdf(scene, material_index, hn, wi, wo, !kImportance);
-    const float3 bsdf_backward = event_bsdf(scene, material_index, hn, wi, wo, !kImportance);
+    const float p_backward = event_pdf(m, hn, wi, wo, !kImportance);
+    const float3 bsdf_backward = event_bsdf(m, hn, wi, wo, !kImportance);
     const float p_rr_backward = min_rr(max3((1.0f / p_backward) * bsdf_backward));
+    const int surface = surface_of_kind(m.kind);
+    if (surface != kSurfaceDiffuse) specular |= 1u << n;
     BdptEvent& e = out[n++];
-    e.object = hit.prim;
-    e.material = material_index;
-    e.position = x;
-    e.normal = hn;
-    e.direction_out = wo;
-    e.weight = weight;
-    e.geometry_factor = fabsf(dot(wo, normal) * dot(wo, hn) / (hit.t * hit.t));
-    e.p_backward = p_backward * p_rr_backward;
-    e.p_forward = p_forward * p_rr_forward;
+    e.mis = make_float4(fabsf(dot(wo, normal) * dot(wo, hn) / (hit.t * hit.t)), p_backward * p_rr_backward,
+                        p_forward * p_rr_forward, event_bits(material_index, surface));
+    e.pos_obj = make_float4(x.x, x.y, x.z, __int_as_float(hit.prim));
+    e.normal4 = make_float4(hn.x, hn.y, hn.z, 0.0f);
+    e.dout4 = make_float4(wo.x, wo.y, wo.z, 0.0f);
+    e.weight4 = make_float4(weight.x, weight.y, weight.z, 0.0f);
     if (!(rng.next() < p_rr_forward)) break;
     ray.o = x;
     ray.d = wi;
@@ -263,9 +279,12 @@ struct BdptContribution {
   float3 value;
   bool has_pixel;
   uint32_t pixel;
+  // the connection edge, for the MIS weight: geometry factor, pdf (x rr) of sampling the light
+  // endpoint from the eye endpoint (radiance transport) and the eye endpoint from the light endpoint
+  float edge_gf, edge_p_light, edge_p_importance;
 };
 
-// Connect, :901-1017
+// Connect, :901-1017.  le / ee are register copies of the two endpoints (null = that subpath is empty).
 template <class Accel>
 __device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene, const BdptEvent* le, const BdptEvent* ee,
                                                          BdptCounters& count) {
@@ -273,117 +292,154 @@ __device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene,
   c.value = v3(0.0f, 0.0f, 0.0f);
   c.has_pixel = false;
   c.pixel = 0;
+  c.edge_gf = c.edge_p_light = c.edge_p_importance = 0.0f;
   if (!le && !ee) return c;
   if (!le) {  // s = 0: the eye subpath found a light
-    if (surface_of(scene, ee->material) != kSurfaceLight) return c;
-    c.value = ee->weight * emitted_radiance(load_material(scene, ee->material), ee->normal, ee->direction_out);
+    if (ee->surface() != kSurfaceLight) return c;
+    c.value = ee->weight() * emitted_radiance(load_material(scene, ee->material()), ee->normal(), ee->direction_out());
     return c;
   }
   if (!ee) {  // t = 0: the light subpath found the aperture
     float response;
-    if (surface_of(scene, le->material) != kSurfaceEye) return c;
-    if (!lens_response(le->position, le->direction_out, c.pixel, response)) return c;
+    if (le->surface() != kSurfaceEye || le->leading()) return c;
+    if (!lens_response(le->position(), le->direction_out(), c.pixel, response)) return c;
     c.has_pixel = true;
-    c.value = response * le->weight;
+    c.value = response * le->weight();
     return c;
   }
-  if (!le->leading() && surface_of(scene, le->material) != kSurfaceDiffuse) return c;
-  if (!ee->leading() && surface_of(scene, ee->material) != kSurfaceDiffuse) return c;
+  if (!le->leading() && le->surface() != kSurfaceDiffuse) return c;
+  if (!ee->leading() && ee->surface() != kSurfaceDiffuse) return c;
+  const float3 lp = le->position(), ep = ee->position();
   Ray shadow;
-  shadow.o = le->position;
-  shadow.d = normalize_exact(v3(ee->position.x - le->position.x, ee->position.y - le->position.y,
-                                ee->position.z - le->position.z));
+  shadow.o = lp;
+  shadow.d = normalize_exact(v3(ep.x - lp.x, ep.y - lp.y, ep.z - lp.z));
   const float3 to_light = -shadow.d;
   float3 value;
+  float3 adjoint_bsdf = v3(0.0f, 0.0f, 0.0f);
+  MaterialDev lm;
   if (le->leading()) {  // s = 1: Radiance / LightPDFArea
-    const float4 le_over_pdf = __ldg(reinterpret_cast<const float4*>(scene.lights + (-3 - le->object)) + 4);
-    value = dot(shadow.d, le->normal) > 0.0f ? v3(le_over_pdf) : v3(0.0f, 0.0f, 0.0f);
+    const float4 le_over_pdf = __ldg(reinterpret_cast<const float4*>(scene.lights + (-3 - le->object())) + 4);
+    value = dot(shadow.d, le->normal()) > 0.0f ? v3(le_over_pdf) : v3(0.0f, 0.0f, 0.0f);
   } else {
-    value = le->weight * event_bsdf(scene, le->material, le->normal, le->direction_out, shadow.d, true);
+    lm = load_material(scene, le->material());
+    adjoint_bsdf = event_bsdf(lm, le->normal(), le->direction_out(), shadow.d, true);
+    value = le->weight() * adjoint_bsdf;
   }
   if (ee->leading()) {  // t = 1
     float response;
-    if (!lens_response(ee->position, to_light, c.pixel, response)) return c;
+    if (!lens_response(ep, to_light, c.pixel, response)) return c;
     c.has_pixel = true;
     value = (response / c_camera.lens.p_area) * value;
   } else {
-    value = value * (ee->weight * event_bsdf(scene, ee->material, ee->normal, ee->direction_out, to_light, false));
+    // (the eye endpoint's BSDF is evaluated again below for the MIS edge; kept separate for clarity)
+    value = value * (ee->weight() * event_bsdf(load_material(scene, ee->material()), ee->normal(), ee->direction_out(),
+                                               to_light, false));
   }
   if (!(max3(value) > 0.0f)) return c;
   // "XXX rough check" (:1006-1010): the first object along the shadow ray must be the eye
   // endpoint's object.  The eye's leading event carries the lens's own aperture object, which
   // no cast ever returns, so t = 1 connections contribute nothing in the reference -- nor here.
+  if (ee->leading()) return c;
   const HitRecord hit = closest_lane<Accel>(scene, shadow);
   count.casts++;
-  if (hit.prim != ee->object) return c;
-  c.value = geometry_factor(le->position, ee->position, le->normal, ee->normal) * value;
+  if (hit.prim != ee->object()) return c;
+  c.edge_gf = geometry_factor(lp, ep, le->normal(), ee->normal());
+  c.value = c.edge_gf * value;
+  {  // BufferLightProbability / BufferImportanceProbability at the connection, :519-535, :574-590
+    const MaterialDev em = load_material(scene, ee->material());
+    const float3 bsdf = event_bsdf(em, ee->normal(), ee->direction_out(), to_light, false);
+    const float pdf = event_pdf(em, ee->normal(), ee->direction_out(), to_light, false);
+    c.edge_p_light = pdf * min_rr(max3((1.0f / pdf) * bsdf));
+    if (le->leading()) {  // DiffuseLight: AdjointBSDF 0, PDFImportance kDiracDelta
+      c.edge_p_importance = 0.0f;
+    } else {
+      const float pdf_i = event_pdf(lm, le->normal(), le->direction_out(), shadow.d, true);
+      c.edge_p_importance = pdf_i * min_rr(max3((1.0f / pdf_i) * adjoint_bsdf));
+    }
+  }
   return c;
 }
 
 // BidirectionalPathSamplingBuffer::Buffer + MISWeight(BalanceHeuristic), :423-697 and
-// include/amber/rendering/multiple_importance_sampling.h:58-69
-__device__ __forceinline__ float bdpt_mis_weight(const SceneView& scene, const BdptEvent* L, int s, const BdptEvent* E,
-                                                 int t) {
-  float gf[2 * kBdptMaxEvents], p_light[2 * kBdptMaxEvents], p_importance[2 * kBdptMaxEvents];
-  float p_technique[2 * kBdptMaxEvents + 1];
-  int n_gf = 0, n_pl = 0, n_pi = 0;
-  const int n = s + t + 1;
-  const bool joined = s > 0 && t > 0;
-  for (int i = 1; i < s; i++) gf[n_gf++] = L[i].geometry_factor;
-  if (joined) gf[n_gf++] = geometry_factor(L[s - 1].position, E[t - 1].position, L[s - 1].normal, E[t - 1].normal);
-  for (int i = t - 1; i >= 1; i--) gf[n_gf++] = E[i].geometry_factor;
-
-  for (int i = 1; i < s; i++) p_light[n_pl++] = L[i].p_backward;
-  if (joined) {
-    const BdptEvent& le = L[s - 1];
-    const BdptEvent& ee = E[t - 1];
-    const float3 din = normalize(le.position - ee.position);
-    const float3 bsdf = event_bsdf(scene, ee.material, ee.normal, ee.direction_out, din, false);
-    const float pdf = event_pdf(scene, ee.material, ee.normal, ee.direction_out, din, false);
-    p_light[n_pl++] = pdf * min_rr(max3((1.0f / pdf) * bsdf));
-  }
-  for (int i = t - 2; i >= 0; i--) p_light[n_pl++] = E[i].p_forward;
-  {
-    const BdptEvent* z0 = t == 0 ? &L[s - 1] : &E[0];
-    const BdptEvent* z1 = t == 0 ? &L[s - 2] : t == 1 ? &L[s - 1] : &E[1];
-    p_light[n_pl - 1] = eye_pdf_direction(normalize(z1->position - z0->position));
-  }
-
-  for (int i = 0; i + 1 < s; i++) p_importance[n_pi++] = L[i].p_forward;
-  if (joined) {
-    const BdptEvent& le = L[s - 1];
-    const BdptEvent& ee = E[t - 1];
-    const float3 din = normalize(ee.position - le.position);
-    const float3 bsdf = event_bsdf(scene, le.material, le.normal, le.direction_out, din, true);
-    const float pdf = event_pdf(scene, le.material, le.normal, le.direction_out, din, true);
-    p_importance[n_pi++] = pdf * min_rr(max3((1.0f / pdf) * bsdf));
-  }
-  for (int i = t - 1; i >= 1; i--) p_importance[n_pi++] = E[i].p_backward;
-  p_importance[0] = 1.0f / kPiF;  // LightSet::PDFDirection, light_set.h:113-122
-
+// include/amber/rendering/multiple_importance_sampling.h:58-69, without the buffers: with the full
+// path x_0 .. x_{s+t-1} (x_k = L[k] for k < s, E[s+t-1-k] otherwise) the reference's arrays are views
+// of the events' own three numbers,
+//   gf[j]           edge (x_j, x_j+1):  L[j+1].gf | the connection | E[s+t-1-j].gf
+//   p_light[j]      x_j sampled from x_j+1 by radiance transport:   L[j+1].p_backward | connection | E[s+t-2-j].p_forward
+//   p_importance[j] x_j+1 sampled from x_j by importance transport: L[j].p_forward | connection | E[s+t-1-j].p_backward
+// with p_light[last] = the lens's directional pdf and p_importance[0] = the light's (1/pi).  The
+// technique ratios are accumulated outward from technique s as running products; a technique is
+// disabled when it would connect at a specular interior event (:661-697).
+__device__ __forceinline__ float bdpt_mis_weight(const SceneView& scene, const BdptEvent* L, int s, uint32_t spec_l,
+                                                 const BdptEvent* E, int t, uint32_t spec_e, const BdptContribution& c) {
+  const int n = s + t + 1, last = s + t - 2;  // last edge index
   const float eye_pdf_area = c_camera.lens.p_area;
-  for (int i = 0; i < n; i++) p_technique[i] = 1.0f;
-  for (int i = s - 1; i >= 0; i--) {
-    float p = p_technique[i + 1];
-    if (t == 0 && i == n - 2) p *= eye_pdf_area; else p *= p_light[i] * gf[i];
-    if (s > 0 && i == 0) p /= light_pdf_area(scene, L[0].material); else p /= p_importance[i - 1] * gf[i - 1];
-    p_technique[i] = p;
+  // technique i is disabled if a light interior event a in [1, s-2] is specular and i in {a, a+1},
+  // or an eye interior event b in [1, t-2] is specular and i in {n-b-1, n-b-2}
+  uint64_t disabled = 0;
+  {
+    const uint32_t li = s >= 3 ? spec_l & ((1u << (s - 1)) - 2u) : 0u;  // bits 1 .. s-2
+    disabled |= static_cast<uint64_t>(li) | (static_cast<uint64_t>(li) << 1);
+    uint32_t ei = t >= 3 ? spec_e & ((1u << (t - 1)) - 2u) : 0u;
+    while (ei) {
+      const int b = __ffs(ei) - 1;
+      ei &= ei - 1u;
+      disabled |= (1ull << (n - b - 1)) | (1ull << (n - b - 2));
+    }
   }
-  for (int i = s + 1; i < n; i++) {
-    float p = p_technique[i - 1];
-    if (s == 0 && i == 1) p *= light_pdf_area(scene, E[t - 1].material); else p *= p_importance[i - 2] * gf[i - 2];
-    if (t > 0 && i == n - 1) p /= eye_pdf_area; else p /= p_light[i - 1] * gf[i - 1];
-    p_technique[i] = p;
+  // the lens's directional pdf replaces p_light[last] (:541-547)
+  float eye_dir_pdf;
+  {
+    const float3 z0 = t == 0 ? L[s - 1].position() : E[0].position();
+    const float3 z1 = t == 0 ? L[s - 2].position() : t == 1 ? L[s - 1].position() : E[1].position();
+    eye_dir_pdf = eye_pdf_direction(normalize(z1 - z0));
   }
-  // DisableSpecularConnection, :661-697
-  for (int i = 1; i + 1 < s; i++) {
-    if (surface_of(scene, L[i].material) != kSurfaceDiffuse) p_technique[i] = p_technique[i + 1] = 0.0f;
+  auto edge = [&](int j, float& gf, float& p_light, float& p_importance) {
+    if (j < s - 1) {
+      const float4 a = L[j + 1].mis;
+      gf = a.x;
+      p_light = a.y;
+      p_importance = L[j].mis.z;
+    } else if (j == s - 1 && s > 0 && t > 0) {
+      gf = c.edge_gf;
+      p_light = c.edge_p_light;
+      p_importance = c.edge_p_importance;
+    } else {
+      const float4 a = E[s + t - 1 - j].mis;
+      gf = a.x;
+      p_importance = a.y;
+      p_light = E[s + t - 2 - j].mis.z;
+    }
+    if (j == last) p_light = eye_dir_pdf;
+    if (j == 0) p_importance = 1.0f / kPiF;  // LightSet::PDFDirection, light_set.h:113-122
+  };
+  float sum = 1.0f;  // technique s itself
+  {
+    float p = 1.0f;
+    float gf_i = 0.0f, pl_i = 0.0f, pi_i = 0.0f;
+    if (s - 1 <= last && s >= 1) edge(s - 1, gf_i, pl_i, pi_i);
+    for (int i = s - 1; i >= 0; i--) {  // techniques with a shorter light subpath
+      float gf_m = 0.0f, pl_m = 0.0f, pi_m = 0.0f;
+      if (i >= 1) edge(i - 1, gf_m, pl_m, pi_m);
+      p *= (t == 0 && i == n - 2) ? eye_pdf_area : pl_i * gf_i;
+      p /= (i == 0) ? light_pdf_area(scene, L[0].material()) : pi_m * gf_m;
+      if (!((disabled >> i) & 1ull)) sum += p;
+      gf_i = gf_m; pl_i = pl_m; pi_i = pi_m;
+    }
   }
-  for (int i = 1; i + 1 < t; i++) {
-    if (surface_of(scene, E[i].material) != kSurfaceDiffuse) p_technique[n - i - 1] = p_technique[n - i - 2] = 0.0f;
+  {
+    float p = 1.0f;
+    for (int i = s + 1; i < n; i++) {  // techniques with a longer light subpath
+      float gf_a = 0.0f, pl_a = 0.0f, pi_a = 0.0f, gf_b = 0.0f, pl_b = 0.0f, pi_b = 0.0f;
+      if (i >= 2) edge(i - 2, gf_a, pl_a, pi_a);
+      if (i - 1 <= last) edge(i - 1, gf_b, pl_b, pi_b);
+      p *= (s == 0 && i == 1) ? light_pdf_area(scene, E[t - 1].material()) : pi_a * gf_a;
+      p /= (t > 0 && i == n - 1) ? eye_pdf_area : pl_b * gf_b;
+      if (!((disabled >> i) & 1ull)) sum += p;
+    }
   }
-  float sum = 0.0f;
-  for (int i = 0; i < n; i++) sum += p_technique[i];
+  // technique s is disabled too when it connects at a specular interior event
+  if ((disabled >> s) & 1ull) sum -= 1.0f;
   return 1.0f / sum;
 }
 
@@ -401,16 +457,22 @@ __global__ void __launch_bounds__(128) bdpt_kernel(const RenderArgs args, unsign
     const uint32_t pixel = static_cast<uint32_t>(pair % args.n_pixels);
     const uint32_t sample = static_cast<uint32_t>(args.sample_begin + pair / args.n_pixels);
     SequentialRng rng;
+    uint32_t spec_l, spec_e;
     rng.init(args.seed, pixel, sample, 0x40000000u);
-    const int s_max = generate_subpath<Accel, true>(args, pixel, rng, cap, L, count);
+    const int s_max = generate_subpath<Accel, true>(args, pixel, rng, cap, L, spec_l, count);
     rng.init(args.seed, pixel, sample, 0x40000001u);
-    const int t_max = generate_subpath<Accel, false>(args, pixel, rng, cap, E, count);
+    const int t_max = generate_subpath<Accel, false>(args, pixel, rng, cap, E, spec_e, count);
     float3 measurement = v3(0.0f, 0.0f, 0.0f);
-    for (int s = 0; s <= s_max; s++) {
-      for (int t = 0; t <= t_max; t++) {
-        BdptContribution c = bdpt_connect<Accel>(args.scene, s ? &L[s - 1] : nullptr, t ? &E[t - 1] : nullptr, count);
+    for (int t = 0; t <= t_max; t++) {
+      BdptEvent ee;
+      if (t) ee = E[t - 1];
+      for (int s = 0; s <= s_max; s++) {
+        if (s == 0 && t == 0) continue;
+        BdptEvent le;
+        if (s) le = L[s - 1];
+        const BdptContribution c = bdpt_connect<Accel>(args.scene, s ? &le : nullptr, t ? &ee : nullptr, count);
         if (!(max3(c.value) > 0.0f)) continue;
-        const float weight = bdpt_mis_weight(args.scene, L, s, E, t);
+        const float weight = bdpt_mis_weight(args.scene, L, s, spec_l, E, t, spec_e, c);
         if (c.has_pixel) {  // light image: / sensor.Size(), :1054-1056
           film_add(args.film, c.pixel, (weight * args.inv_n_pixels) * c.value);
           count.splats++;
