@@ -15,6 +15,7 @@
 //   amber::cuda::MakeRGBCudaPathTracing  std::unique_ptr<rendering::Algorithm<RGB>>, the factory
 //                                        convention of include/amber/rendering/algorithm_pt.h:30-31
 //   amber::cuda::MakeRGBCudaLightTracing the same for the light tracer (algorithm_lt.h:29-30)
+//   amber::cuda::MakeRGBCudaBidirectionalPathTracing   and for BDPT (algorithm_bdpt.h)
 //
 // Why a builder: scene::Object<R> keeps its primitive and material private
 // (include/amber/scene/object.h:93-96) and the concrete classes are .cc-local, so geometry
@@ -493,6 +494,17 @@ private:
 inline std::unique_ptr<rendering::Algorithm<RGB>>
 MakeRGBCudaPathTracing(const CudaPathTracingOptions& options = CudaPathTracingOptions())
 {
+  return std::make_unique<CudaPathTracing>(options);
+}
+
+/** Row N3: the bidirectional path tracer (src/amber/rendering/algorithm_bdpt.cc:82-148 over
+ *  include/amber/rendering/bidirectional_path_sampling.h), in the convention of
+ *  include/amber/rendering/algorithm_bdpt.h -- what algorithm_factory.cc would register under
+ *  "bdpt-cuda".  options.max_depth is the number of events per subpath (0 = 16, the maximum). */
+inline std::unique_ptr<rendering::Algorithm<RGB>>
+MakeRGBCudaBidirectionalPathTracing(CudaPathTracingOptions options = CudaPathTracingOptions())
+{
+  options.estimator = AMBER_CUDA_ESTIMATOR_BDPT;
   return std::make_unique<CudaPathTracing>(options);
 }
 

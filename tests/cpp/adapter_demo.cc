@@ -18,6 +18,7 @@
 #include <string>
 
 #include "amber/etude/cornel_box.h"
+#include "amber/rendering/algorithm_bdpt.h"
 #include "amber/rendering/algorithm_lt.h"
 #include "amber/rendering/algorithm_pt.h"
 
@@ -180,7 +181,14 @@ int main(int argc, char** argv)
   gpu_algorithm = cuda::MakeRGBCudaLightTracing(options);
   const auto lt = Summarise(timed(*gpu_algorithm, 1, spp * 64, "lt-cuda"), size);
 
+  // row N3: bidirectional path tracing behind the same interface, CPU reference beside it
+  const auto cpu_bdpt = rendering::MakeRGBBidirectionalPathTracing();
+  const auto bdpt_cpu = Summarise(timed(*cpu_bdpt, threads, std::max(1u, spp / 4), "reference bdpt (CPU)"), size);
+  gpu_algorithm = cuda::MakeRGBCudaBidirectionalPathTracing(options);
+  const auto bdpt_gpu = Summarise(timed(*gpu_algorithm, 1, spp, "bdpt-cuda"), size);
+  std::printf("mean luminance: reference bdpt %.6g | bdpt-cuda %.6g\n", bdpt_cpu.mean, bdpt_gpu.mean);
 
+  // a reference scene that was NOT built by the builder must be refused, not rendered on the CPU
   bool refused = false;
   try {
     const auto builtin = etude::CornelBox(0.050, 0.050, 6);  // src/amber/cli/application.cc:69-73
