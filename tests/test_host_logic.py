@@ -114,6 +114,17 @@ assert total == S
 if rank == 0:
     whole, _ = oracle.render(W, W, 0.036, 0.036, 0, S, SEED, 8, 1, threads=2)
     np.testing.assert_allclose(film.numpy() / total, whole, rtol=1e-5, atol=1e-9)
+# the same partition for the film-splatting algorithms (rows N2, N3): a rank's light paths land
+# on any pixel, the reduce still only sums films
+for render in (lambda b, c: oracle.render_lt(64, 64, 0.036, 0.036, b, c, SEED, threads=2)[0],
+               lambda b, c: oracle.render_bdpt(W, W, 0.036, 0.036, b, c, SEED, 8, threads=2)[0]):
+    S2 = 24
+    begin, count = partition_samples(S2, rank, world)
+    film = torch.from_numpy(render(begin, count).astype(np.float64) * count)
+    assert all_reduce_film(film, count) == S2
+    if rank == 0:
+        np.testing.assert_allclose(film.numpy() / S2, render(0, S2), rtol=1e-5, atol=1e-9)
+if rank == 0:
     print("PARTITION_OK")
 dist.destroy_process_group()
 """
