@@ -208,10 +208,12 @@ struct BdptCounters {
 };
 
 // GenerateLightSubpath (kImportance = true, :726-801) / GenerateEyeSubpath (false, :821-899).
-// Returns the number of events; `specular` gets one bit per event whose surface is not Diffuse.
+// Returns the number of events; `specular` gets one bit per event whose surface is not Diffuse,
+// `eye_surface` one bit per (non-leading) event on an aperture triangle.
 template <class Accel, bool kImportance>
 __device__ __forceinline__ int generate_subpath(const RenderArgs& args, uint32_t pixel, SequentialRng& rng, int cap,
-                                                BdptEvent* out, uint32_t& specular, BdptCounters& count) {
+                                                BdptEvent* out, uint32_t& specular, uint32_t& eye_surface,
+                                                BdptCounters& count) {
   const SceneView& scene = args.scene;
   Ray ray;
   float3 weight, normal;
@@ -239,6 +241,7 @@ __device__ __forceinline__ int generate_subpath(const RenderArgs& args, uint32_t
   out[0].dout4 = out[0].normal4;
   out[0].weight4 = make_float4(weight.x, weight.y, weight.z, 0.0f);
   specular = 1u;  // a leading event is never "Diffuse"; bit 0 is not looked at
+  eye_surface = 0u;
   int n = 1;
   for (int i = 1; i < cap; i++) {
     const HitRecord hit = closest_lane<Accel>(scene, ray);
@@ -259,6 +262,7 @@ __device__ __forceinline__ int generate_subpath(const RenderArgs& args, uint32_t
     const float p_rr_backward = min_rr(max3((1.0f / p_backward) * bsdf_backward));
     const int surface = surface_of_kind(m.kind);
     if (surface != kSurfaceDiffuse) specular |= 1u << n;
+    if (surface == kSurfaceEye) eye_surface |= 1u << n;
     BdptEvent& e = out[n++];
     e.mis = make_float4(fabsf(dot(wo, normal) * dot(wo, hn) / (hit.t * hit.t)), p_backward * p_rr_backward,
                         p_forward * p_rr_forward, event_bits(material_index, surface));
@@ -452,37 +456,68 @@ __global__ void __launch_bounds__(128) bdpt_kernel(const RenderArgs args, unsign
   count.splats = 0;
   uint32_t pairs = 0;
   const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * blockDim.x;
-  for (unsigned long long pair = static_cast<unsigned long long>(blockIdx.x) * blockDim.x + threadIdx.x; pair < total_pairs;
-       pair += stride) {
+  const uint32_t lane = threadIdx.x & 31u;
+  // the loop is warp-uniform (the connection rounds below vote across the warp): a warp's lanes
+  // hold 32 consecutive pairs, lanes past the end carry empty subpaths
+  for (unsigned long long first = static_cast<unsigned long long>(blockIdx.x) * blockDim.x + threadIdx.x - lane;
+       first < total_pairs; first += stride) {
+    const unsigned long long pair = first + lane;
+    const bool valid = pair < total_pairs;
     const uint32_t pixel = static_cast<uint32_t>(pair % args.n_pixels);
     const uint32_t sample = static_cast<uint32_t>(args.sample_begin + pair / args.n_pixels);
     SequentialRng rng;
-    uint32_t spec_l, spec_e;
-    rng.init(args.seed, pixel, sample, 0x40000000u);
-    const int s_max = generate_subpath<Accel, true>(args, pixel, rng, cap, L, spec_l, count);
-    rng.init(args.seed, pixel, sample, 0x40000001u);
-    const int t_max = generate_subpath<Accel, false>(args, pixel, rng, cap, E, spec_e, count);
+    uint32_t spec_l = 0, spec_e = 0, eye_l = 0, eye_e = 0;
+    int s_max = 0, t_max = 0;
+    if (valid) {
+      rng.init(args.seed, pixel, sample, 0x40000000u);
+      s_max = generate_subpath<Accel, true>(args, pixel, rng, cap, L, spec_l, eye_l, count);
+      rng.init(args.seed, pixel, sample, 0x40000001u);
+      t_max = generate_subpath<Accel, false>(args, pixel, rng, cap, E, spec_e, eye_e, count);
+      pairs++;
+    }
     float3 measurement = v3(0.0f, 0.0f, 0.0f);
-    for (int t = 0; t <= t_max; t++) {
-      BdptEvent ee;
-      if (t) ee = E[t - 1];
-      for (int s = 0; s <= s_max; s++) {
-        if (s == 0 && t == 0) continue;
-        BdptEvent le;
-        if (s) le = L[s - 1];
-        const BdptContribution c = bdpt_connect<Accel>(args.scene, s ? &le : nullptr, t ? &ee : nullptr, count);
-        if (!(max3(c.value) > 0.0f)) continue;
-        const float weight = bdpt_mis_weight(args.scene, L, s, spec_l, E, t, spec_e, c);
-        if (c.has_pixel) {  // light image: / sensor.Size(), :1054-1056
-          film_add(args.film, c.pixel, (weight * args.inv_n_pixels) * c.value);
-          count.splats++;
-        } else {
-          measurement = measurement + weight * c.value;
-        }
+    auto accumulate = [&](const BdptContribution& c, int s, int t) {
+      if (!(max3(c.value) > 0.0f)) return;
+      const float weight = bdpt_mis_weight(args.scene, L, s, spec_l, E, t, spec_e, c);
+      if (c.has_pixel) {  // light image: / sensor.Size(), :1054-1056
+        film_add(args.film, c.pixel, (weight * args.inv_n_pixels) * c.value);
+        count.splats++;
+      } else {
+        measurement = measurement + weight * c.value;
+      }
+    };
+    // Combine, :1019-1068.  Which (s, t) can contribute at all follows from the surface types alone
+    // (Connect, :910-950): s = 0 needs the eye subpath to END on a light (a light absorbs: only the
+    // last event can be one); t = 0 needs a light-subpath event on the aperture; t = 1 never passes
+    // the visibility test (see bdpt_connect); every other pair needs a Diffuse (or leading light)
+    // endpoint on each side -- the PRODUCT of two event sets.  A lane therefore walks its
+    // candidate list by index, and the warp runs max-over-lanes rounds in lockstep, so the expensive
+    // part (BSDFs, the shadow cast, the MIS weight) runs with the lanes packed instead of once per
+    // cell of the widest lane's (s, t) grid.
+    if (t_max >= 2 && E[t_max - 1].surface() == kSurfaceLight) {
+      const BdptEvent ee = E[t_max - 1];
+      accumulate(bdpt_connect<Accel>(args.scene, nullptr, &ee, count), 0, t_max);
+    }
+    for (uint32_t m = eye_l; m; m &= m - 1u) {
+      const int s = __ffs(m);  // event index + 1
+      const BdptEvent le = L[s - 1];
+      accumulate(bdpt_connect<Accel>(args.scene, &le, nullptr, count), s, 0);
+    }
+    const uint32_t s_set = (~spec_l | 1u) & ((s_max >= 32 ? 0u : (1u << s_max)) - 1u);       // bit k: s = k + 1
+    const uint32_t t_set = (~spec_e & ~1u) & ((t_max >= 32 ? 0u : (1u << t_max)) - 1u);      // bit k: t = k + 1 >= 2
+    const int n_s = __popc(s_set), n_t = __popc(t_set);
+    const int mine = n_s * n_t;
+    const int rounds = __reduce_max_sync(0xffffffffu, mine);
+    for (int j = 0; j < rounds; j++) {
+      if (j < mine) {
+        const int s = __fns(s_set, 0, j % n_s + 1) + 1;
+        const int t = __fns(t_set, 0, j / n_s + 1) + 1;
+        const BdptEvent le = L[s - 1];
+        const BdptEvent ee = E[t - 1];
+        accumulate(bdpt_connect<Accel>(args.scene, &le, &ee, count), s, t);
       }
     }
     if (max3(measurement) > 0.0f) film_add(args.film, pixel, measurement);
-    pairs++;
   }
   // counters: one atomic per warp
   const uint32_t casts = __reduce_add_sync(0xffffffffu, count.casts);
