@@ -610,3 +610,46 @@ def test_bidirectional_path_tracing_matches_oracle_and_path_tracing(device, orac
     assert np.all(np.abs(diff) < 4 * sigma + 2e-2 * pt.mean(0)), (diff, sigma)
     with pytest.raises(AmberCudaError):  # more events per subpath than the kernel stores
         device.render(0, 1, max_depth=17, estimator=capi.ESTIMATOR_BDPT)
+
+
+def test_light_and_bidirectional_tracing_through_the_bvh(device, oracle_lib):
+    """Rows N2 / N3 on a scene above the constant-memory limit: the light tracer's wavefront and the
+    BDPT kernel's per-thread walk of the 4-wide BVH against the brute-force oracle."""
+    from amber_b200 import FlatSceneBuilder, Sensor, capi
+    from amber_b200.scene import icosphere
+    b = FlatSceneBuilder()
+    b.make_thin_lens([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0.9, 0, 0, 0, 1], 0.05, 1.5, 0.25, 5, add_aperture_objects=True)
+
+    def quad(m, p0, p1, p2, p3):
+        b.add_triangle(p0, p1, p2, m)
+        b.add_triangle(p2, p3, p0, m)
+
+    grey = b.make_lambertian((.6, .6, .6))
+    quad(grey, (-1, -1, 1), (1, -1, 1), (1, -1, -1), (-1, -1, -1))
+    quad(grey, (-1, 1, 1), (-1, 1, -1), (1, 1, -1), (1, 1, 1))
+    quad(b.make_lambertian((.6, .2, .2)), (-1, -1, 1), (-1, -1, -1), (-1, 1, -1), (-1, 1, 1))
+    quad(grey, (1, -1, 1), (1, 1, 1), (1, 1, -1), (1, -1, -1))
+    quad(b.make_phong((.7, .7, .7), 16), (-1, -1, -1), (1, -1, -1), (1, 1, -1), (-1, 1, -1))
+    quad(grey, (-1, -1, 1), (-1, 1, 1), (1, 1, 1), (1, -1, 1))
+    quad(b.make_diffuse_light((4.0, 4.0, 3.0)), (-0.5, 0.98, 0.5), (-0.5, 0.98, -0.5), (0.5, 0.98, -0.5), (0.5, 0.98, 0.5))
+    b.add_triangles(icosphere(3, center=(0.1, -0.4, -0.2), radius=0.45), b.make_lambertian((.3, .5, .7)))  # 1280 triangles
+    b.add_sphere((-0.5, -0.7, 0.3), 0.25, b.make_refraction(1.5))
+    scene = b.build()
+    oracle = oracle_lib.Oracle(scene)
+    device.upload_scene(scene)
+    assert device.stats()["accel"] == 1
+    device.set_sensor(Sensor(64, 64))
+    device.render(0, 64, seed=41, estimator=capi.ESTIMATOR_LIGHT_TRACING)
+    image, _ = device.resolve()
+    want, stats = oracle.render_lt(64, 64, *FILM, 0, 64, 41, threads=32)
+    frac, lit = light_tracing_agreement(image, want)
+    got = device.stats()
+    print(f"lt through the BVH: {frac:.4f} of {lit} lit pixels agree; splats {got['light_splats']} vs {stats['splats']}")
+    assert frac >= 0.98 and lit > 100 and abs(got["light_splats"] - stats["splats"]) <= max(3, 0.02 * stats["splats"])
+    device.set_sensor(Sensor(48, 48))
+    device.render(0, 8, seed=42, max_depth=10, estimator=capi.ESTIMATOR_BDPT)
+    image, _ = device.resolve()
+    want, _ = oracle.render_bdpt(48, 48, *FILM, 0, 8, 42, 10, threads=32)
+    frac = image_agreement(image, want, rtol=5e-3)
+    print(f"bdpt through the BVH: {frac:.4f} of pixels agree")
+    assert frac >= 0.98
