@@ -4,7 +4,7 @@
 // Why not the wavefront: a BDPT sample is two short subpaths (2.8 events each on the Cornell box)
 // followed by (s + 1)(t + 1) connections whose MIS weights need every event of both subpaths; the
 // state is two event arrays, not one ray.  A thread therefore keeps both subpaths in local memory
-// (L1-resident, <= 2 x 16 events x 64 B), traces with the same intersection code as `extend`
+// (<= 2 x 16 events x 80 B), traces with the same intersection code as `extend`
 // (constant-memory list, or a per-thread walk of the 4-wide BVH), and adds its contributions to the
 // film with float4 atomics: the eye image at its own pixel, the light image where the lens maps it.
 //
@@ -22,7 +22,6 @@ namespace amber_cuda {
 
 constexpr int kBdptMaxEvents = 16;  // events per subpath (the reference has no cap: truncations are rare)
 constexpr int32_t kObjectLens = -2;  // the lens's own aperture object: never equal to an object found by a cast
-constexpr int32_t kEstimatorBdpt = 3;
 
 struct SequentialRng {
   uint32_t key0, key1, pixel, sample, id, i;

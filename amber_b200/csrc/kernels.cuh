@@ -8,10 +8,13 @@
 //   shade    : emission, [light sampling -> shadow queue], BSDF sample, Russian
 //              roulette, next ray in place      (algorithm_pt.cc:137-157)
 //   connect  : any-hit for the shadow queue + film add
-// `shade` sorts each 2048-slot tile by hit class in shared memory so that a warp shades one
+// `shade` sorts each 1024-slot tile by hit class in shared memory so that a warp shades one
 // material; freed slots are compacted into `q_new` and slots with a pending shadow ray into
 // `q_shadow`: per-thread bit masks, warp shuffles, one smem scan and ONE global atomic per
 // queue per tile.
+// The same wavefront runs amber's light tracer (algorithm_lt.cc:112-163): raygen<true> starts paths
+// on the lights, shade<true> scatters importance and splats paths that land on the aperture.
+// Bidirectional path tracing is one kernel of its own (bdpt.cuh, included at the end).
 //
 // Layout in HBM (all float4 / 16-byte accesses):
 //   ray[2i], ray[2i+1]       origin xyz + live flag, direction xyz             32 B per slot
