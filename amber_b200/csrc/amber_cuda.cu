@@ -471,7 +471,7 @@ int wide_bvh_depth(const bvh_build::WideBvhHost& bvh) {
     depth = std::max(depth, d);
     for (int c = 0; c < 4; c++) {
       int32_t ref;
-      std::memcpy(&ref, &bvh.nodes[static_cast<size_t>(node) * 32 + 24 + c], sizeof ref);
+      std::memcpy(&ref, &bvh.nodes[static_cast<size_t>(node) * bvh_build::kNodeFloats + 12 + c], sizeof ref);
       if (ref >= 0 && ref != bvh_build::kEmpty) todo.push_back({ref, d + 1});
     }
   }

@@ -1,17 +1,20 @@
 // bvh.cuh -- 4-wide BVH: layout, device traversal.  The host builder is bvh_build.h.
 //
 // Replaces raytracer::BVH (include/amber/raytracer/acceleration_bvh.h): there a
-// pointer-linked binary tree walked recursively; here a flat array of 128-byte
-// 4-wide nodes in SoA form walked with a per-lane stack in shared memory, the lanes of a
+// pointer-linked binary tree walked recursively; here a flat array of 64-byte
+// 4-wide nodes with quantised child boxes walked with a per-lane stack in shared memory, the lanes of a
 // warp kept together by votes (see traverse).  Tree shape
 // is ours (binned SAH, collapsed 2 -> 4); only closest-hit semantics are shared:
 // nearest t in (kEPS, t_best), strict `<` update (acceleration_bvh.h:346-351).
 //
-// Node = 8 float4 (one 128 B line):
-//   [0] lo.x of children 0..3   [1] hi.x   [2] lo.y   [3] hi.y   [4] lo.z   [5] hi.z
-//   [6] child reference (int bits): >= 0 inner node index; < 0 leaf, ~ref =
-//       (first_triangle << 3) | triangle_count; kEmptyChild for an unused lane
-//   [7] unused
+// Node = 4 float4 = 64 B = two sectors, read with two 256-bit loads.  Incoherent traversal is
+// bound by the L1 gather path (every lane reads its own line; measured: lane-gathers cost in
+// proportion to the SECTORS they touch, scripts/micro/gather.cu), so the node is as small as four
+// children allow: child boxes are 8-bit grid indices on the node's own box,
+//   plane = origin + q * scale   (lo rounded down, hi rounded up: conservative; bvh_build.h)
+//   [0] origin.xyz, scale.x      [1] scale.yz, x-lo word, x-hi word (byte k = child k)
+//   [2] y-lo, y-hi, z-lo, z-hi   [3] child references (int bits): >= 0 inner node index; < 0
+//       leaf, ~ref = (first_triangle << 3) | triangle_count; kEmptyChild for an unused lane
 // Triangles are stored in leaf order as TriIsect (3 float4).
 #pragma once
 
@@ -20,31 +23,63 @@
 namespace amber_cuda {
 
 constexpr int kBvhStackMax = 160;  // entries per lane the 227 KB of shared memory allow at 256 threads + margin
+// Vote thresholds of trace_persistent, measured on the 1.3 M-triangle scene (closest hit: 8/16
+// 544 us, 20/12 592 us per launch; any hit: 20/12 286 us, 8/16 339 us -- shadow rays end early, so
+// refilling often costs more than the idle lanes do).
 #ifndef AMBER_BVH_REFILL_LANES
-#define AMBER_BVH_REFILL_LANES 20
+#define AMBER_BVH_REFILL_LANES 8
 #endif
 #ifndef AMBER_BVH_MIN_DESCEND_LANES
-#define AMBER_BVH_MIN_DESCEND_LANES 12
+#define AMBER_BVH_MIN_DESCEND_LANES 16
+#endif
+#ifndef AMBER_BVH_REFILL_LANES_ANYHIT
+#define AMBER_BVH_REFILL_LANES_ANYHIT 20
+#endif
+#ifndef AMBER_BVH_MIN_DESCEND_LANES_ANYHIT
+#define AMBER_BVH_MIN_DESCEND_LANES_ANYHIT 12
 #endif
 constexpr int kBvhLeafMax = 4;
 constexpr int32_t kEmptyChild = 0x7fffffff;
+
+// 256-bit read-only load (LDG.E.256, sm_100+): one L1 wavefront brings 32 B of a lane's node where a
+// 128-bit load brings 16 -- the traversal is bound by L1 wavefronts (every lane reads its own line).
+struct Wide8 {
+  float4 a, b;
+};
+__device__ __forceinline__ Wide8 ldg256(const void* p) {
+  Wide8 r;
+  asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=f"(r.a.x), "=f"(r.a.y), "=f"(r.a.z), "=f"(r.a.w), "=f"(r.b.x), "=f"(r.b.y), "=f"(r.b.z), "=f"(r.b.w)
+      : "l"(p));
+  return r;
+}
 
 __device__ __forceinline__ int32_t bvh_leaf_first(int32_t ref) { return (~ref) >> 3; }
 __device__ __forceinline__ int32_t bvh_leaf_count(int32_t ref) { return (~ref) & 7; }
 
 struct WideBvh {
-  // Slab test of one child against [0, t_best]; returns entry distance or +inf.
-  // fminf/fmaxf drop NaNs (0 * inf), which only ever makes the test more permissive;
-  // boxes are padded at build time so rounding never culls a true hit.
-  static __device__ __forceinline__ float child_entry(float lox, float hix, float loy, float hiy, float loz,
-                                                      float hiz, const float3& idir, const float3& oidir,
-                                                      float t_best) {
-    const float tx0 = fmaf(lox, idir.x, -oidir.x), tx1 = fmaf(hix, idir.x, -oidir.x);
-    const float ty0 = fmaf(loy, idir.y, -oidir.y), ty1 = fmaf(hiy, idir.y, -oidir.y);
-    const float tz0 = fmaf(loz, idir.z, -oidir.z), tz1 = fmaf(hiz, idir.z, -oidir.z);
-    const float t_near = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fmaxf(fminf(tz0, tz1), 0.0f));
-    const float t_far = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fminf(fmaxf(tz0, tz1), t_best));
-    return t_near <= t_far ? t_near : CUDART_INF_F;
+  // Byte k of a packed plane word as a float: PRMT builds 2^23 + q, the subtraction is exact.
+  template <int k>
+  static __device__ __forceinline__ float plane_byte(uint32_t word) {
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440 | k)) - 8388608.0f;
+  }
+
+  // Slab test of child k against [0, t_best] in the node's quantised frame: the plane at grid
+  // index q lies at ray parameter q * s + o with s = scale * idir, o = (origin - O) * idir per
+  // axis; `near`/`far` are the plane words already chosen by the sign of the direction, so no
+  // min/max per axis is left.  Returns the entry distance or +inf.  fminf/fmaxf drop NaNs
+  // (0 * inf on an axis-parallel ray), which only ever makes the test more permissive; boxes
+  // are padded at build time so rounding never culls a true hit.
+  template <int k>
+  static __device__ __forceinline__ float child_entry(uint32_t near_x, uint32_t far_x, uint32_t near_y, uint32_t far_y,
+                                                      uint32_t near_z, uint32_t far_z, const float3& s,
+                                                      const float3& o, float t_best, int32_t ref) {
+    const float nx = fmaf(plane_byte<k>(near_x), s.x, o.x), fx = fmaf(plane_byte<k>(far_x), s.x, o.x);
+    const float ny = fmaf(plane_byte<k>(near_y), s.y, o.y), fy = fmaf(plane_byte<k>(far_y), s.y, o.y);
+    const float nz = fmaf(plane_byte<k>(near_z), s.z, o.z), fz = fmaf(plane_byte<k>(far_z), s.z, o.z);
+    const float t_near = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
+    const float t_far = fminf(fminf(fx, fy), fminf(fz, t_best));
+    return (t_near <= t_far) & (ref != kEmptyChild) ? t_near : CUDART_INF_F;
   }
 
   // One node step of one lane: four slab tests, children sorted by entry distance, the far
@@ -52,15 +87,25 @@ struct WideBvh {
   static __device__ __forceinline__ int32_t node_step(const SceneView& scene, int32_t current, const float3& idir,
                                                       const float3& oidir, float t_best, int32_t* stack, int stride,
                                                       int& sp) {
-    const float4* node = scene.bvh_nodes + static_cast<size_t>(current) * 8;
-    const float4 lox = __ldg(node + 0), hix = __ldg(node + 1), loy = __ldg(node + 2), hiy = __ldg(node + 3);
-    const float4 loz = __ldg(node + 4), hiz = __ldg(node + 5), ref4 = __ldg(node + 6);
-    float d0 = child_entry(lox.x, hix.x, loy.x, hiy.x, loz.x, hiz.x, idir, oidir, t_best);
-    float d1 = child_entry(lox.y, hix.y, loy.y, hiy.y, loz.y, hiz.y, idir, oidir, t_best);
-    float d2 = child_entry(lox.z, hix.z, loy.z, hiy.z, loz.z, hiz.z, idir, oidir, t_best);
-    float d3 = child_entry(lox.w, hix.w, loy.w, hiy.w, loz.w, hiz.w, idir, oidir, t_best);
+    const float4* node = scene.bvh_nodes + static_cast<size_t>(current) * 4;
+    const Wide8 head = ldg256(node), tail = ldg256(node + 2);
+    const float3 s = v3(head.a.w * idir.x, head.b.x * idir.y, head.b.y * idir.z);
+    const float3 o = v3(fmaf(head.a.x, idir.x, -oidir.x), fmaf(head.a.y, idir.y, -oidir.y),
+                        fmaf(head.a.z, idir.z, -oidir.z));
+    const uint32_t x_lo = __float_as_uint(head.b.z), x_hi = __float_as_uint(head.b.w);
+    const uint32_t y_lo = __float_as_uint(tail.a.x), y_hi = __float_as_uint(tail.a.y);
+    const uint32_t z_lo = __float_as_uint(tail.a.z), z_hi = __float_as_uint(tail.a.w);
+    const bool rx = idir.x < 0.0f, ry = idir.y < 0.0f, rz = idir.z < 0.0f;
+    const uint32_t near_x = rx ? x_hi : x_lo, far_x = rx ? x_lo : x_hi;
+    const uint32_t near_y = ry ? y_hi : y_lo, far_y = ry ? y_lo : y_hi;
+    const uint32_t near_z = rz ? z_hi : z_lo, far_z = rz ? z_lo : z_hi;
+    const float4 ref4 = tail.b;
     int32_t c0 = __float_as_int(ref4.x), c1 = __float_as_int(ref4.y), c2 = __float_as_int(ref4.z),
             c3 = __float_as_int(ref4.w);
+    float d0 = child_entry<0>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c0);
+    float d1 = child_entry<1>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c1);
+    float d2 = child_entry<2>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c2);
+    float d3 = child_entry<3>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c3);
     // sort the four (distance, child) pairs ascending: 5-comparator network, branch-free
 #define AMBER_CSWAP(da, ca, db, cb)            \
   {                                            \
@@ -105,8 +150,8 @@ struct WideBvh {
     int32_t* stack = bvh_stack_smem + threadIdx.x;
     const int stride = blockDim.x;
     constexpr uint32_t kFull = 0xffffffffu;
-    constexpr int kRefillLanes = AMBER_BVH_REFILL_LANES;
-    constexpr int kMinDescendLanes = AMBER_BVH_MIN_DESCEND_LANES;
+    constexpr int kRefillLanes = kAnyHit ? AMBER_BVH_REFILL_LANES_ANYHIT : AMBER_BVH_REFILL_LANES;
+    constexpr int kMinDescendLanes = kAnyHit ? AMBER_BVH_MIN_DESCEND_LANES_ANYHIT : AMBER_BVH_MIN_DESCEND_LANES;
     const int lane = threadIdx.x & 31;
     const uint32_t lane_lt = (1u << lane) - 1u;
     const uint32_t n = source.count();
@@ -163,6 +208,8 @@ struct WideBvh {
         if (inner) current = node_step(scene, current, idir, oidir, hit.t, stack, stride, sp);
       }
       // ---- leaves ---------------------------------------------------------------------
+      // (Dealing the (lane, triangle) pairs of a leaf phase out over the whole warp by shuffle --
+      // one pass of ~20 busy lanes for four passes of ~5 -- was measured slower: 570 vs 544 us.)
       if (current < 0) {
         const int first = bvh_leaf_first(current), count = bvh_leaf_count(current);
 #pragma unroll

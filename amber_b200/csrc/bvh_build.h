@@ -1,5 +1,5 @@
 // bvh_build.h -- host-side BVH construction: binned SAH binary tree, collapsed to
-// 4-wide nodes in the SoA layout of bvh.cuh.
+// 4-wide 64-byte nodes with 8-bit quantised child boxes (layout: bvh.cuh).
 //
 // Replaces BVH::BuildBVH / CreateNode / FindSplit / FindSplitAxis /
 // SurfaceAreaHeuristic (include/amber/raytracer/acceleration_bvh.h:135-312).  The
@@ -165,7 +165,7 @@ struct Builder {
 };
 
 struct WideBvhHost {
-  std::vector<float> nodes;     // n_nodes * 32 floats (8 float4)
+  std::vector<float> nodes;     // n_nodes * kNodeFloats (4 float4 per node, bvh.cuh)
   std::vector<uint32_t> order;  // leaf order -> input triangle index
   int32_t root = 0;             // 0, or a leaf reference when the whole scene is one leaf
   uint32_t n_nodes = 0;
@@ -173,14 +173,64 @@ struct WideBvhHost {
 
 inline int32_t leaf_ref(int32_t first, int32_t count) { return ~((first << 3) | count); }
 
-// pad so that float rounding in the slab test can never cull a true hit
+// pad so that float rounding in the slab test can never cull a true hit: the device evaluates
+// t = q * (s * idir) + (o * idir - O * idir) (bvh.cuh node_step), four roundings of relative size
+// 2^-24 on terms no larger than the scene, where the exact slab test has none
 inline void padded(const Box& b, float* lo, float* hi) {
   for (int a = 0; a < 3; a++) {
     const float m = std::max(std::max(std::fabs(b.lo[a]), std::fabs(b.hi[a])), 1.0f);
-    lo[a] = b.lo[a] - 4e-7f * m;
-    hi[a] = b.hi[a] + 4e-7f * m;
+    lo[a] = b.lo[a] - 2e-6f * m;
+    hi[a] = b.hi[a] + 2e-6f * m;
   }
 }
+
+// One 64-byte node (bvh.cuh): the children's boxes quantised to 8 bits per plane on the grid
+// origin + q * scale of the node's own box; lo rounds down, hi rounds up, checked with the very
+// expression the device decodes with (fmaf(q, scale, origin)), so a decoded box always contains
+// the true one.  lo/hi: [n_kids][3]; unused lanes get ref = kEmpty (and lo > hi).
+inline void encode_node(const float (*lo)[3], const float (*hi)[3], const int32_t* refs, int n_kids, float* out16) {
+  uint32_t words[6] = {0, 0, 0, 0, 0, 0};  // x lo, x hi, y lo, y hi, z lo, z hi; byte k = child k
+  float origin[3], scale[3];
+  for (int a = 0; a < 3; a++) {
+    float o = FLT_MAX, top = -FLT_MAX;
+    for (int k = 0; k < n_kids; k++) {
+      o = std::min(o, lo[k][a]);
+      top = std::max(top, hi[k][a]);
+    }
+    float s = std::max((top - o) / 255.0f, 1e-30f);
+    uint32_t w_lo = 0, w_hi = 0;
+    for (bool ok = false; !ok;) {
+      ok = true;
+      w_lo = w_hi = 0;
+      for (int k = 0; k < 4 && ok; k++) {
+        int q_lo = 255, q_hi = 0;  // unused lane: empty interval
+        if (k < n_kids) {
+          q_lo = std::min(255, std::max(0, static_cast<int>(std::floor((lo[k][a] - o) / s))));
+          while (q_lo > 0 && std::fmaf(static_cast<float>(q_lo), s, o) > lo[k][a]) q_lo--;
+          q_hi = std::min(255, std::max(0, static_cast<int>(std::ceil((hi[k][a] - o) / s))));
+          while (q_hi < 255 && std::fmaf(static_cast<float>(q_hi), s, o) < hi[k][a]) q_hi++;
+          if (std::fmaf(static_cast<float>(q_hi), s, o) < hi[k][a]) ok = false;  // grid too short: widen it
+        }
+        w_lo |= static_cast<uint32_t>(q_lo) << (8 * k);
+        w_hi |= static_cast<uint32_t>(q_hi) << (8 * k);
+      }
+      if (!ok) s = std::max(std::nextafter(s, FLT_MAX), s * 1.0001f);
+    }
+    origin[a] = o;
+    scale[a] = s;
+    words[2 * a] = w_lo;
+    words[2 * a + 1] = w_hi;
+  }
+  out16[0] = origin[0]; out16[1] = origin[1]; out16[2] = origin[2];
+  out16[3] = scale[0]; out16[4] = scale[1]; out16[5] = scale[2];
+  std::memcpy(&out16[6], words, sizeof words);
+  for (int k = 0; k < 4; k++) {
+    const int32_t ref = k < n_kids ? refs[k] : kEmpty;
+    std::memcpy(&out16[12 + k], &ref, 4);
+  }
+}
+
+constexpr int kNodeFloats = 16;  // 64 B
 
 inline WideBvhHost build(const float* verts9, uint32_t n) {
   WideBvhHost out;
@@ -210,7 +260,7 @@ inline WideBvhHost build(const float* verts9, uint32_t n) {
   if (n2[root].count > 0 || n == 0) {
     out.root = n == 0 ? kEmpty : leaf_ref(n2[root].first, n2[root].count);
     // a dummy node keeps the device pointer valid
-    out.nodes.assign(32, 0.0f);
+    out.nodes.assign(kNodeFloats, 0.0f);
     out.n_nodes = 1;
     return out;
   }
@@ -223,7 +273,7 @@ inline WideBvhHost build(const float* verts9, uint32_t n) {
   std::vector<Pending> queue;
   queue.push_back({root, 0});
   out.n_nodes = 1;
-  out.nodes.resize(32);
+  out.nodes.resize(kNodeFloats);
   for (size_t head = 0; head < queue.size(); head++) {
     const Pending item = queue[head];
     int32_t kids[4];
@@ -246,31 +296,23 @@ inline WideBvhHost build(const float* verts9, uint32_t n) {
       kids[best] = n2[open].left;
       kids[n_kids++] = n2[open].right;
     }
-    float node[32];
-    for (int k = 0; k < 4; k++) {
-      int32_t ref = kEmpty;
-      // unused lane: lo = hi = +inf can never pass the slab test (bvh.cuh child_entry)
-      float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {INFINITY, INFINITY, INFINITY};
-      if (k < n_kids) {
-        const Node2& child = n2[kids[k]];
-        padded(child.box, lo, hi);
-        if (child.count > 0) {
-          ref = leaf_ref(child.first, child.count);
-        } else {
-          ref = static_cast<int32_t>(out.n_nodes++);
-          queue.push_back({kids[k], ref});
-        }
+    float lo[4][3], hi[4][3];
+    int32_t refs[4];
+    for (int k = 0; k < n_kids; k++) {
+      const Node2& child = n2[kids[k]];
+      padded(child.box, lo[k], hi[k]);
+      if (child.count > 0) {
+        refs[k] = leaf_ref(child.first, child.count);
+      } else {
+        refs[k] = static_cast<int32_t>(out.n_nodes++);
+        queue.push_back({kids[k], refs[k]});
       }
-      node[0 + k] = lo[0]; node[4 + k] = hi[0];
-      node[8 + k] = lo[1]; node[12 + k] = hi[1];
-      node[16 + k] = lo[2]; node[20 + k] = hi[2];
-      std::memcpy(&node[24 + k], &ref, 4);
-      node[28 + k] = 0.0f;
     }
-    if (out.nodes.size() < static_cast<size_t>(out.n_nodes) * 32) out.nodes.resize(static_cast<size_t>(out.n_nodes) * 32);
-    std::memcpy(&out.nodes[static_cast<size_t>(item.wide) * 32], node, sizeof node);
+    if (out.nodes.size() < static_cast<size_t>(out.n_nodes) * kNodeFloats)
+      out.nodes.resize(std::max(out.nodes.size() * 2, static_cast<size_t>(out.n_nodes) * kNodeFloats));
+    encode_node(lo, hi, refs, n_kids, &out.nodes[static_cast<size_t>(item.wide) * kNodeFloats]);
   }
-  out.nodes.resize(static_cast<size_t>(out.n_nodes) * 32);
+  out.nodes.resize(static_cast<size_t>(out.n_nodes) * kNodeFloats);
   return out;
 }
 

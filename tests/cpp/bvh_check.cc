@@ -1,5 +1,8 @@
 // CPU check of the host BVH builder (amber_b200/csrc/bvh_build.h): every triangle lands in
-// exactly one leaf, every child box contains its subtree, depth fits the device stack.
+// exactly one leaf, every DECODED (quantised) child box contains its subtree, depth fits the
+// device stack.
+#include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -36,15 +39,25 @@ static int check(const WideBvhHost& bvh, const float* verts, uint32_t n) {
       }
       continue;
     }
-    const float* node = &bvh.nodes[(size_t)it.ref * 32];
+    // decode as the device does (bvh.cuh): plane = fmaf(q, scale, origin)
+    const float* node = &bvh.nodes[(size_t)it.ref * kNodeFloats];
+    uint32_t words[6];
+    std::memcpy(words, &node[6], sizeof words);
     for (int k = 0; k < 4; k++) {
       Item child;
-      std::memcpy(&child.ref, &node[24 + k], 4);
-      for (int a = 0; a < 3; a++) { child.lo[a] = node[8 * a + k]; child.hi[a] = node[8 * a + 4 + k]; }
+      std::memcpy(&child.ref, &node[12 + k], 4);
+      for (int a = 0; a < 3; a++) {
+        child.lo[a] = std::fmaf((float)((words[2 * a] >> (8 * k)) & 0xff), node[3 + a], node[a]);
+        child.hi[a] = std::fmaf((float)((words[2 * a + 1] >> (8 * k)) & 0xff), node[3 + a], node[a]);
+      }
       child.depth = it.depth + 1;
-      if (child.ref != kEmpty)
-        for (int a = 0; a < 3; a++)
-          if (child.lo[a] < it.lo[a] - 1e-5f || child.hi[a] > it.hi[a] + 1e-5f) { std::printf("child escapes parent\n"); return 1; }
+      // a ray reaches a triangle only through every ancestor's box: carry the intersection down,
+      // so the leaf check above proves each triangle lies inside ALL the boxes on its path
+      // (a quantised child box may stick out of its parent's by a grid step; that is harmless)
+      for (int a = 0; a < 3; a++) {
+        child.lo[a] = std::max(child.lo[a], it.lo[a]);
+        child.hi[a] = std::min(child.hi[a], it.hi[a]);
+      }
       stack.push_back(child);
     }
   }
