@@ -38,6 +38,9 @@ constexpr int kBvhStackMax = 160;  // entries per lane the 227 KB of shared memo
 #ifndef AMBER_BVH_MIN_DESCEND_LANES_ANYHIT
 #define AMBER_BVH_MIN_DESCEND_LANES_ANYHIT 12
 #endif
+#ifndef AMBER_BVH_MIN_BLOCKS
+#define AMBER_BVH_MIN_BLOCKS 5  // resident 256-thread blocks per SM the traversal kernels are compiled for (<= 51 registers)
+#endif
 constexpr int kBvhLeafMax = 4;
 constexpr int32_t kEmptyChild = 0x7fffffff;
 
@@ -60,6 +63,10 @@ __device__ __forceinline__ int32_t bvh_leaf_count(int32_t ref) { return (~ref) &
 struct WideBvh {
   // Byte k of a packed plane word as a float: PRMT builds 2^23 + q, the subtraction is exact.
   template <int k>
+  static __device__ __forceinline__ float plane_magic(uint32_t word) {  // 2^23 + byte k
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440 | k));
+  }
+  template <int k>
   static __device__ __forceinline__ float plane_byte(uint32_t word) {
     return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440 | k)) - 8388608.0f;
   }
@@ -74,9 +81,21 @@ struct WideBvh {
   static __device__ __forceinline__ float child_entry(uint32_t near_x, uint32_t far_x, uint32_t near_y, uint32_t far_y,
                                                       uint32_t near_z, uint32_t far_z, const float3& s,
                                                       const float3& o, float t_best, int32_t ref) {
+#ifdef AMBER_BVH_SCALAR_DECODE
     const float nx = fmaf(plane_byte<k>(near_x), s.x, o.x), fx = fmaf(plane_byte<k>(far_x), s.x, o.x);
     const float ny = fmaf(plane_byte<k>(near_y), s.y, o.y), fy = fmaf(plane_byte<k>(far_y), s.y, o.y);
     const float nz = fmaf(plane_byte<k>(near_z), s.z, o.z), fz = fmaf(plane_byte<k>(far_z), s.z, o.z);
+#else
+    // the near and far plane of an axis go through one packed FADD2 + FFMA2 (sm_100)
+    const float2 magic = make_float2(-8388608.0f, -8388608.0f);
+    const float2 x = __ffma2_rn(__fadd2_rn(make_float2(plane_magic<k>(near_x), plane_magic<k>(far_x)), magic),
+                                make_float2(s.x, s.x), make_float2(o.x, o.x));
+    const float2 y = __ffma2_rn(__fadd2_rn(make_float2(plane_magic<k>(near_y), plane_magic<k>(far_y)), magic),
+                                make_float2(s.y, s.y), make_float2(o.y, o.y));
+    const float2 z = __ffma2_rn(__fadd2_rn(make_float2(plane_magic<k>(near_z), plane_magic<k>(far_z)), magic),
+                                make_float2(s.z, s.z), make_float2(o.z, o.z));
+    const float nx = x.x, fx = x.y, ny = y.x, fy = y.y, nz = z.x, fz = z.y;
+#endif
     const float t_near = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
     const float t_far = fminf(fminf(fx, fy), fminf(fz, t_best));
     return (t_near <= t_far) & (ref != kEmptyChild) ? t_near : CUDART_INF_F;

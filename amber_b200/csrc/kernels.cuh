@@ -375,7 +375,7 @@ struct ExtendSource {
 };
 
 template <>
-__global__ void __launch_bounds__(kBlock) extend_kernel<WideBvh>(const RenderArgs args) {
+__global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) extend_kernel<WideBvh>(const RenderArgs args) {
   ExtendSource source{args, {-1}};
   WideBvh::trace_persistent<false>(args.scene, source, &args.ctl->cursor_extend);
 }
@@ -400,7 +400,7 @@ struct CastSource {
   }
 };
 
-__global__ void __launch_bounds__(kBlock) cast_bvh_kernel(const SceneView scene, const float4* __restrict__ ray_o,
+__global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) cast_bvh_kernel(const SceneView scene, const float4* __restrict__ ray_o,
                                                           const float4* __restrict__ ray_d, uint32_t n,
                                                           float4* __restrict__ hits, unsigned int* cursor) {
   CastSource source{scene, ray_o, ray_d, hits, n, {-1}};
@@ -819,7 +819,7 @@ struct ConnectSource {
 };
 
 template <>
-__global__ void __launch_bounds__(kBlock) connect_kernel<WideBvh>(const RenderArgs args) {
+__global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) connect_kernel<WideBvh>(const RenderArgs args) {
   ConnectSource source{args, 0u};
   WideBvh::trace_persistent<true>(args.scene, source, &args.ctl->cursor_connect);
 }
