@@ -7,7 +7,7 @@
 //    uniform datapath and no lane ever waits on a gather.  This is the layout the
 //    built-in Cornell box (25 objects) uses; the reference itself ends up testing all
 //    25 objects per ray there (its SAH tree collapses to one leaf).
-//  * WideBvh (bvh.cuh): larger scenes, 4-wide SoA nodes in global memory.
+//  * WideBvh (bvh.cuh): larger scenes, 4-wide 64-byte quantised nodes in global memory.
 #pragma once
 
 #include <cstdint>
