@@ -41,6 +41,7 @@ SYMBOLS = (
     "amber_cuda_sample_importance",
     "amber_cuda_light_rays",
     "amber_cuda_lens_response",
+    "amber_cuda_normalize",
     "amber_cuda_get_stats",
     "amber_cuda_set_profiling",
 )
@@ -149,6 +150,7 @@ def load(path: str | None = None) -> C.CDLL:
         "amber_cuda_sample_importance": [vp, i32, u64, vp, vp, vp, vp, vp, vp],
         "amber_cuda_light_rays": [vp, u64, vp, vp, vp, vp],
         "amber_cuda_lens_response": [vp, u64, vp, vp, vp, vp],
+        "amber_cuda_normalize": [vp, u64, vp, vp, vp],
         "amber_cuda_get_stats": [vp, C.POINTER(Stats)],
         "amber_cuda_set_profiling": [vp, C.c_int],
     }

@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -531,6 +532,7 @@ int amber_cuda_create(amber_cuda_ctx** out, int device) {
   ctx->id = g_next_ctx_id.fetch_add(1);
   ctx->device = device;
   cudaError_t err = cudaSetDevice(device);
+  if (const char* g = std::getenv("AMBER_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, std::atoi(g));
   if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (err == cudaSuccess) err = cudaEventCreate(&ctx->ev_begin);
   if (err == cudaSuccess) err = cudaEventCreate(&ctx->ev_end);
@@ -803,8 +805,12 @@ int amber_cuda_film_clear(amber_cuda_ctx* ctx) {
 
 namespace amber_host {
 
-__global__ void control_begin_kernel(Control* ctl, unsigned long long total_paths, unsigned int slots) {
+__global__ void control_begin_kernel(Control* ctl, unsigned long long total_paths, unsigned int slots,
+                                     unsigned int n_pixels) {
   ctl->next_path = 0;
+  ctl->base_pixel = 0;
+  ctl->base_sample = 0;
+  ctl->n_pixels = n_pixels;
   ctl->total_paths = total_paths;
   ctl->n_new = slots;
   ctl->n_shadow = 0;
@@ -813,8 +819,8 @@ __global__ void control_begin_kernel(Control* ctl, unsigned long long total_path
 }
 
 constexpr int kStepsPerPoll = 8;
-// 8 waves of shade tiles at 4 resident blocks per SM on 148 SMs (148 * 4 * kShadeTile * 8)
-constexpr uint32_t kDefaultPoolPaths = 148u * 4u * static_cast<uint32_t>(kShadeTile) * 8u;
+// 8 waves of 1024-slot windows at 4 per SM on 148 SMs
+constexpr uint32_t kDefaultPoolPaths = 148u * 4u * 1024u * 8u;
 
 struct KernelTimer {
   // profiling mode: one event pair per launch, summed per kernel class after the render
@@ -839,6 +845,12 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
   const unsigned int grid = blocks_for(args.pool.n_slots);
   const unsigned int shade_grid = blocks_for(args.pool.n_slots, kShadeTile);
   const unsigned int trace_grid = Accel::kPersistent ? ctx->bvh_grid : grid;
+  // raygen and the list connect are grid-stride loops over queues whose length only the device knows:
+  // one wave of resident blocks (kQueueBlocks per SM), never more than the pool
+  int sm_count = 148;
+  cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
+  const unsigned int queue_grid = std::min<unsigned int>(grid, static_cast<unsigned int>(sm_count) * static_cast<unsigned int>(kQueueBlocks));
+  const unsigned int connect_grid = Accel::kPersistent ? ctx->bvh_grid : queue_grid;
   const bool light_tracing = args.estimator == AMBER_CUDA_ESTIMATOR_LIGHT_TRACING;
   cudaStream_t stream = ctx->stream;
   KernelTimer timer;
@@ -864,8 +876,9 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
   for (int batch = 0; !done; batch++) {
     for (int step = 0; step < kStepsPerPoll; step++) {
       timed(0, [&] {
-        if (light_tracing) raygen_kernel<true><<<grid, kBlock, 0, stream>>>(args);
-        else raygen_kernel<false><<<grid, kBlock, 0, stream>>>(args);
+        const unsigned int raygen_grid = AMBER_RAYGEN_LOOP ? std::min<unsigned int>(grid, static_cast<unsigned int>(sm_count) * AMBER_RAYGEN_BLOCKS) : grid;
+        if (light_tracing) raygen_kernel<true><<<raygen_grid, kBlock, 0, stream>>>(args);
+        else raygen_kernel<false><<<raygen_grid, kBlock, 0, stream>>>(args);
       });
       bookkeep_kernel<<<1, 1, 0, stream>>>(args.ctl);
       timed(1, [&] { extend_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args); });
@@ -873,7 +886,7 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
         if (light_tracing) shade_kernel<true><<<shade_grid, kShadeBlock, 0, stream>>>(args);
         else shade_kernel<false><<<shade_grid, kShadeBlock, 0, stream>>>(args);
       });
-      if (nee) timed(3, [&] { connect_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args); });
+      if (nee) timed(3, [&] { connect_kernel<Accel><<<connect_grid, kBlock, dynamic_smem, stream>>>(args); });
       ctx->stats.kernel_launches += nee ? 5 : 4;
       extend_launches++;
     }
@@ -1003,7 +1016,7 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
 
   cudaStream_t stream = ctx->stream;
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev_begin, stream));
-  control_begin_kernel<<<1, 1, 0, stream>>>(args.ctl, total_paths, args.pool.n_slots);
+  control_begin_kernel<<<1, 1, 0, stream>>>(args.ctl, total_paths, args.pool.n_slots, n_pixels);
   pool_reset_kernel<<<blocks_for(args.pool.n_slots), kBlock, 0, stream>>>(args);
   ctx->stats.kernel_launches += 2;
   const bool nee = params->estimator == AMBER_CUDA_ESTIMATOR_NEE && ctx->view.n_lights > 0;
@@ -1215,6 +1228,28 @@ int amber_cuda_lens_response(amber_cuda_ctx* ctx, uint64_t n, const float* posit
   ctx->stats.kernel_launches++;
   CUDA_TRY(ctx, cudaMemcpyAsync(pixel, ctx->d_scratch_i[0].ptr, n * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(value, f[2].ptr, n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+  CUDA_TRY(ctx, cudaGetLastError());
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_normalize(amber_cuda_ctx* ctx, uint64_t n, const float* vector3, const float* denominator,
+                         float* unit3) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!vector3 || !unit3) return fail(ctx, AMBER_CUDA_EINVAL, "vector3 / unit3 is NULL");
+  if (n == 0) return AMBER_CUDA_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t stream = ctx->stream;
+  auto& f = ctx->d_scratch_f;
+  CUDA_TRY(ctx, f[0].resize(3 * n)); CUDA_TRY(ctx, f[1].resize(3 * n));
+  CUDA_TRY(ctx, cudaMemcpyAsync(f[0].ptr, vector3, 3 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  if (denominator) {
+    CUDA_TRY(ctx, f[2].resize(n));
+    CUDA_TRY(ctx, cudaMemcpyAsync(f[2].ptr, denominator, n * sizeof(float), cudaMemcpyHostToDevice, stream));
+  }
+  normalize_kernel<<<blocks_for(n), kBlock, 0, stream>>>(n, f[0].ptr, denominator ? f[2].ptr : nullptr, f[1].ptr);
+  ctx->stats.kernel_launches++;
+  CUDA_TRY(ctx, cudaMemcpyAsync(unit3, f[1].ptr, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(stream));
   CUDA_TRY(ctx, cudaGetLastError());
   return AMBER_CUDA_OK;

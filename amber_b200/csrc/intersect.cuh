@@ -49,16 +49,21 @@ __device__ __forceinline__ bool intersect_sphere(const float4 sphere, const Ray&
   const float c = __fsub_rn(dot_exact(oc, oc), __fmul_rn(sphere.w, sphere.w));
   const float disc = __fsub_rn(__fmul_rn(b, b), 4.0f * c);
   if (!(disc >= 0.0f)) return false;
+  // Origin outside (c > 0) and the centre behind the ray (b > 0): both roots are negative in the
+  // reference's arithmetic too (alpha = -b - sqrt_d < 0 keeps the larger magnitude, so its branch
+  // gives beta = 2 c / alpha < 0), so the sqrt and the division are skipped -- same result.
+  if (c > 0.0f && b > 0.0f) return false;
   const float sqrt_d = __fsqrt_rn(disc);
   float alpha = -b - sqrt_d;
   float beta = -b + sqrt_d;
-  if (fabsf(alpha) < fabsf(beta)) {
-    alpha = __fdiv_rn(c, beta) * 2.0f;
-    beta = beta * 0.5f;
-  } else {
-    beta = __fdiv_rn(c, alpha) * 2.0f;
-    alpha = alpha * 0.5f;
-  }
+  // SolveQuadratic's two branches (algebra.h:43-49) as ONE division: a warp whose lanes take both
+  // sides would otherwise run the IEEE division sequence twice
+  const bool by_beta = fabsf(alpha) < fabsf(beta);
+  const float den = by_beta ? beta : alpha;
+  const float quotient = __fdiv_rn(c, den) * 2.0f;
+  const float half = den * 0.5f;
+  alpha = by_beta ? quotient : half;
+  beta = by_beta ? half : quotient;
   const float t = alpha > kEpsF ? alpha : beta;
   const bool hit = (t > kEpsF) & (t < t_best);
   if (hit) t_out = t;

@@ -45,9 +45,12 @@ struct Control {
   unsigned int n_alive;            // survivors of the last shade
   unsigned int done;
   unsigned int cursor_extend, cursor_connect, cursor_cast;  // persistent BVH kernels: next item to fetch
-  unsigned int pad;
+  unsigned int base_pixel;         // next_path % n_pixels, kept by bookkeep so raygen divides 32-bit numbers
   unsigned long long paths, closest_rays, shadow_rays, truncated, phong_capped;
   unsigned long long splats;  // light tracing: film contributions through the lens
+  unsigned long long base_sample;  // next_path / n_pixels
+  unsigned int n_pixels;
+  unsigned int pad;
 };
 
 struct PathPool {
@@ -236,37 +239,62 @@ __device__ __forceinline__ bool lens_response(float3 position, float3 dir_out, u
   return true;
 }
 
+// Grid-stride over the q_new entries: the host does not know n_new, so the grid is sized for the
+// device (resident blocks), not for the pool -- a launch over every slot spent 40 % of its stall samples
+// in blocks that only read n_new and left.
+#ifndef AMBER_QUEUE_BLOCKS
+#define AMBER_QUEUE_BLOCKS 6
+#endif
+constexpr int kQueueBlocks = AMBER_QUEUE_BLOCKS;  // resident blocks per SM of the grid-stride queue kernels
+#ifndef AMBER_RAYGEN_BLOCKS
+#define AMBER_RAYGEN_BLOCKS 4
+#endif
+#ifndef AMBER_RAYGEN_LOOP
+#define AMBER_RAYGEN_LOOP 1
+#endif
 template <bool kLightTracing>
-__global__ void __launch_bounds__(kBlock) raygen_kernel(const RenderArgs args) {
-  const uint32_t j = blockIdx.x * kBlock + threadIdx.x;
+__global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(const RenderArgs args) {
   const Control* ctl = args.ctl;
-  if (j >= ctl->n_new) return;
-  const uint32_t slot = args.pool.q_new[j];
-  const unsigned long long path = ctl->next_path + j;
-  float4* ray = args.pool.ray + 2 * static_cast<size_t>(slot);
-  if (path >= ctl->total_paths) {
-    ray[0] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    return;
-  }
-  const uint32_t pixel = static_cast<uint32_t>(path % args.n_pixels);
-  const uint32_t sample = static_cast<uint32_t>(args.sample_begin + path / args.n_pixels);
-  CameraRng rng;
-  rng.init(args.seed, pixel, sample);
+  const uint32_t n_new = AMBER_RAYGEN_LOOP ? ctl->n_new : min(ctl->n_new, (blockIdx.x + 1) * kBlock);
+  const unsigned long long next_path = ctl->next_path, total_paths = ctl->total_paths;
+  const unsigned long long base_pixel = ctl->base_pixel, base_sample = args.sample_begin + ctl->base_sample;
   const uint32_t width = c_camera.sensor.width;
-  float3 o, d, w3;
-  if constexpr (kLightTracing) {
-    // one sample = W*H light paths (algorithm_lt.cc:112-122); `pixel` is only the path's stream key
-    generate_light_ray(args.scene, rng, o, d, w3);
-  } else {
-    float w;
-    generate_eye_ray(pixel % width, pixel / width, rng, o, d, w);
-    w3 = v3(w, w, w);
+  for (uint32_t j = blockIdx.x * kBlock + threadIdx.x; j < n_new; j += gridDim.x * kBlock) {
+    const uint32_t slot = args.pool.q_new[j];
+    float4* ray = args.pool.ray + 2 * static_cast<size_t>(slot);
+    if (next_path + j >= total_paths) {
+      ray[0] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      continue;
+    }
+    // path = next_path + j = (base_sample * n_pixels + base_pixel) + j: the 64-bit division is done once
+    // per launch by `bookkeep`, a thread divides the 32-bit (base_pixel + j)
+    const unsigned long long offset = base_pixel + j;
+    uint32_t pixel, wrapped;
+    if (offset >> 32) {
+      pixel = static_cast<uint32_t>(offset % args.n_pixels);
+      wrapped = static_cast<uint32_t>(offset / args.n_pixels);
+    } else {
+      wrapped = static_cast<uint32_t>(offset) / args.n_pixels;
+      pixel = static_cast<uint32_t>(offset) - wrapped * args.n_pixels;
+    }
+    const uint32_t sample = static_cast<uint32_t>(base_sample + wrapped);
+    CameraRng rng;
+    rng.init(args.seed, pixel, sample);
+    float3 o, d, w3;
+    if constexpr (kLightTracing) {
+      // one sample = W*H light paths (algorithm_lt.cc:112-122); `pixel` is only the path's stream key
+      generate_light_ray(args.scene, rng, o, d, w3);
+    } else {
+      float w;
+      generate_eye_ray(pixel % width, pixel / width, rng, o, d, w);
+      w3 = v3(w, w, w);
+    }
+    ray[0] = make_float4(o.x, o.y, o.z, 1.0f);
+    ray[1] = make_float4(d.x, d.y, d.z, 0.0f);
+    float4* state = args.pool.state + 2 * static_cast<size_t>(slot);
+    state[0] = make_float4(w3.x, w3.y, w3.z, 0.0f);
+    state[1] = make_float4(__uint_as_float(pixel), __uint_as_float(sample), __uint_as_float(kFlagCountEmission), 0.0f);
   }
-  ray[0] = make_float4(o.x, o.y, o.z, 1.0f);
-  ray[1] = make_float4(d.x, d.y, d.z, 0.0f);
-  float4* state = args.pool.state + 2 * static_cast<size_t>(slot);
-  state[0] = make_float4(w3.x, w3.y, w3.z, 0.0f);
-  state[1] = make_float4(__uint_as_float(pixel), __uint_as_float(sample), __uint_as_float(kFlagCountEmission), 0.0f);
 }
 
 // Fills q_new with every slot (start of a render call: all slots are free).
@@ -284,6 +312,8 @@ __global__ void bookkeep_kernel(Control* ctl) {
     generated = ctl->n_new < left ? ctl->n_new : left;
   }
   ctl->next_path += generated;
+  ctl->base_pixel = static_cast<unsigned int>(ctl->next_path % ctl->n_pixels);
+  ctl->base_sample = ctl->next_path / ctl->n_pixels;
   ctl->paths += generated;
   ctl->shadow_rays += ctl->n_shadow;
   ctl->done = (generated == 0 && ctl->n_alive == 0) ? 1u : 0u;
@@ -424,9 +454,11 @@ __device__ __forceinline__ void surface_point(const SceneView& scene, const Ray&
     const float3 P = cross_exact(ray.d, E2);
     const float det = dot_exact(P, E1);
     const float3 T = v3(ray.o.x - v0.x, ray.o.y - v0.y, ray.o.z - v0.z);
-    const float u = __fdiv_rn(dot_exact(P, T), det);
     const float3 Q = cross_exact(T, E1);
-    const float v = __fdiv_rn(dot_exact(Q, ray.d), det);
+    // u = (P.T) / det, v = (Q.d) / det: two IEEE divisions over one denominator (vec.cuh, div3_exact;
+    // the third lane of it is a constant and folds away)
+    const float3 uv = div3_exact(v3(dot_exact(P, T), dot_exact(Q, ray.d), 1.0f), det);
+    const float u = uv.x, v = uv.y;
     position = add_exact(add_exact(v0, scale_exact(u, E1)), scale_exact(v, E2));
     normal = v3(a.w, b.w, c.w);
     material = __ldg(scene.tri_material + hit.prim);
@@ -517,7 +549,7 @@ __device__ __forceinline__ void film_add(float4* film, uint32_t pixel, float3 va
 // The shadow ray itself stays in the slot (pool.shadow[2 slot..]); its origin is the
 // vertex position, which phase 2 has just written to ray[2 slot].
 #ifndef AMBER_SHADE_MIN_BLOCKS
-#define AMBER_SHADE_MIN_BLOCKS 4
+#define AMBER_SHADE_MIN_BLOCKS 8
 #endif
 #ifndef AMBER_SHADE_ROUNDS
 #define AMBER_SHADE_ROUNDS 4
@@ -530,10 +562,21 @@ __device__ __forceinline__ void cp_async_16(void* smem, const void* gmem) {
 __device__ __forceinline__ void cp_async_8(void* smem, const void* gmem) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem))), "l"(gmem));
 }
+// atomicAdd on a __shared__ counter as ONE ATOMS.ADD: the C++ atomicAdd is expanded by the compiler into a
+// warp-aggregated sequence (vote, leader, popc, shuffle: ~15 instructions), which the callers here
+// have already done by hand (one elected lane per warp).
+__device__ __forceinline__ uint32_t atom_shared_add(uint32_t* counter, uint32_t value) {
+  uint32_t old;
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;"
+               : "=r"(old)
+               : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(counter))), "r"(value)
+               : "memory");
+  return old;
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
 __device__ __forceinline__ void cp_async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 #ifndef AMBER_SHADE_BLOCK
-#define AMBER_SHADE_BLOCK 256
+#define AMBER_SHADE_BLOCK 128
 #endif
 constexpr int kShadeBlock = AMBER_SHADE_BLOCK;  // threads per block of `shade`
 constexpr int kShadeTile = kShadeRounds * kShadeBlock;
@@ -575,7 +618,7 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     const uint32_t peers = __match_any_sync(0xffffffffu, cls);
     const int leader = __ffs(peers) - 1;
     uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(&class_count[cls], __popc(peers));
+    if (lane == leader) base = atom_shared_add(&class_count[cls], __popc(peers));
     base = __shfl_sync(0xffffffffu, base, leader);
     const uint32_t key = (static_cast<uint32_t>(cls) << 12) | (base + __popc(peers & lane_lt));
     if (r & 1) keys[r >> 1] |= key << 16; else keys[r >> 1] = key;
@@ -612,7 +655,7 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
   const uint32_t n_chunks = (n_live + 31u) >> 5;
   auto take_chunk = [&]() {
     uint32_t c = 0;
-    if (lane == 0) c = atomicAdd(&next_chunk, 1u);
+    if (lane == 0) c = atom_shared_add(&next_chunk, 1u);
     return __shfl_sync(0xffffffffu, c, 0);
   };
   auto stage_records = [&](uint32_t chunk, int b) {
@@ -720,7 +763,7 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
       // the vertex stays readable for `connect` (shadow origin); w = 0 marks the slot free
       ray_slot[0] = make_float4(x.x, x.y, x.z, 0.0f);
     } else {
-      const float inv_p = 1.0f / p;
+      const float inv_p = __fdividef(1.0f, p);  // scales the throughput only
       throughput = throughput * (inv_p * scatter.weight);
       ray_slot[0] = make_float4(x.x, x.y, x.z, 1.0f);
       ray_slot[1] = make_float4(scatter.dir.x, scatter.dir.y, scatter.dir.z, 0.0f);
@@ -777,25 +820,28 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
 // connect: any-hit along the shadow rays queued by `shade`; unoccluded ones add their
 // contribution to the film.  Queue entry = slot id; the slot holds the ray.
 template <class Accel>
-__global__ void __launch_bounds__(kBlock) connect_kernel(const RenderArgs args) {
-  const uint32_t j = blockIdx.x * kBlock + threadIdx.x;
+__global__ void __launch_bounds__(kBlock, kQueueBlocks) connect_kernel(const RenderArgs args) {
+  // grid-stride over the shadow queue (the grid is sized for the device, see raygen_kernel); the loop
+  // bound is warp-uniform so that Accel::occluded may vote
   const uint32_t n_shadow = args.ctl->n_shadow;
-  if (blockIdx.x * kBlock >= n_shadow) return;  // whole block idle (block-uniform exit)
-  const bool active = j < n_shadow;
-  float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
-  const float4* in = args.pool.shadow;
-  if (active) {
-    const uint32_t slot = args.pool.q_shadow[j];
-    o = args.pool.ray[2 * static_cast<size_t>(slot)];
-    in += 2 * static_cast<size_t>(slot);
-    d = in[0];
+  for (uint32_t base = blockIdx.x * kBlock; base < n_shadow; base += gridDim.x * kBlock) {
+    const uint32_t j = base + threadIdx.x;
+    const bool active = j < n_shadow;
+    float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
+    float4 c = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (active) {
+      const uint32_t slot = args.pool.q_shadow[j];
+      o = args.pool.ray[2 * static_cast<size_t>(slot)];
+      const float4* in = args.pool.shadow + 2 * static_cast<size_t>(slot);
+      d = in[0];
+      c = in[1];  // same 32-byte sector as in[0]: requested now, not after the visibility test
+    }
+    Ray ray;
+    ray.o = v3(o);
+    ray.d = v3(d);
+    if (Accel::occluded(args.scene, ray, d.w, active) || !active) continue;
+    film_add(args.film, __float_as_uint(c.w), v3(c));
   }
-  Ray ray;
-  ray.o = v3(o);
-  ray.d = v3(d);
-  if (Accel::occluded(args.scene, ray, d.w, active) || !active) return;
-  const float4 c = in[1];
-  film_add(args.film, __float_as_uint(c.w), v3(c));
 }
 
 struct ConnectSource {
@@ -931,6 +977,18 @@ __global__ void light_rays_kernel(const SceneView scene, uint64_t n, const float
   origin[3 * i] = o.x; origin[3 * i + 1] = o.y; origin[3 * i + 2] = o.z;
   direction[3 * i] = d.x; direction[3 * i + 1] = d.y; direction[3 * i + 2] = d.z;
   weight[3 * i] = w.x; weight[3 * i + 1] = w.y; weight[3 * i + 2] = w.z;
+}
+
+// Normalize (include/amber/prelude/vector3.h:309-316) on caller-supplied vectors: the exact
+// normalisation every sampled direction and basis vector goes through (vec.cuh, normalize_exact).
+// With a denominator array: the three IEEE quotients in3[i] / denominator[i] (div3_exact) instead.
+__global__ void normalize_kernel(uint64_t n, const float* __restrict__ in3, const float* __restrict__ denominator,
+                                 float* __restrict__ out3) {
+  const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float3 a = v3(in3[3 * i], in3[3 * i + 1], in3[3 * i + 2]);
+  const float3 u = denominator ? div3_exact(a, denominator[i]) : normalize_exact(a);
+  out3[3 * i] = u.x; out3[3 * i + 1] = u.y; out3[3 * i + 2] = u.z;
 }
 
 __global__ void lens_response_kernel(uint64_t n, const float* __restrict__ position,

@@ -216,6 +216,16 @@ class Device:
         self._check(self.lib.amber_cuda_lens_response(self.ctx, n, p(pos), p(wo), p(pixel), p(value)))
         return pixel, value
 
+    def normalize(self, vectors, denominators=None):
+        """prelude::Normalize on the device (the exact normalisation of vec.cuh); with `denominators`
+        the IEEE quotients vectors[i] / denominators[i] instead.  For the parity tests."""
+        v = np.ascontiguousarray(vectors, dtype=np.float32)
+        out = np.empty_like(v)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        den = None if denominators is None else np.ascontiguousarray(denominators, dtype=np.float32)
+        self._check(self.lib.amber_cuda_normalize(self.ctx, v.shape[0], p(v), None if den is None else p(den), p(out)))
+        return out
+
     def eye_rays(self, px, py, xi5):
         px_ = np.ascontiguousarray(px, dtype=np.uint32)
         py_ = np.ascontiguousarray(py, dtype=np.uint32)

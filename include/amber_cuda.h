@@ -253,6 +253,14 @@ int amber_cuda_light_rays(amber_cuda_ctx* ctx, uint64_t n, const float* xi5, flo
 int amber_cuda_lens_response(amber_cuda_ctx* ctx, uint64_t n, const float* position3,
                              const float* dir_out3, int32_t* pixel, float* value);
 
+/* normalize: unit3[i] = vector3[i] / |vector3[i]| with the device's exact normalisation (IEEE sqrt and
+ * three IEEE divisions, bit for bit the host's).  Replaces prelude::Normalize
+ * (include/amber/prelude/vector3.h:309-316); a unit check for the parity tests.  With denominator != NULL
+ * the result is vector3[i] / denominator[i] instead (the same division sequence, e.g. the barycentrics of
+ * src/amber/scene/primitive_triangle.cc:108-118 over det). */
+int amber_cuda_normalize(amber_cuda_ctx* ctx, uint64_t n, const float* vector3, const float* denominator,
+                         float* unit3);
+
 /* eye_rays: n camera rays for pixel (px[i], py[i]) with scripted uniforms xi[n][5].
  * Replaces scene::Scene::GenerateEyeRay (include/amber/scene/scene.h:210-223,
  * src/amber/scene/lens_thin.cc:70-107). */

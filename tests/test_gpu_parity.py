@@ -93,6 +93,39 @@ def test_camera_rays(cornell_device, oracle):
     cornell_device.set_sensor(Sensor(64, 64))
 
 
+def test_exact_normalisation_is_ieee(device):
+    """vec.cuh normalize_exact (one shared reciprocal, zero numerators by select) must be bit for bit
+    Normalize of include/amber/prelude/vector3.h:309-316 in IEEE binary32: sqrt((x*x + y*y) + z*z), then
+    three divisions -- numpy float32 arithmetic is exactly that.  Covers the magnitudes the short
+    sequence takes, the ones it hands to div.rn (tiny, huge, denormal), signed zeros, inf and NaN."""
+    rng = np.random.default_rng(7)
+    n = 1 << 22
+    parts = [rng.standard_normal((n, 3))]                                       # directions
+    v = rng.standard_normal((n, 3)); v[rng.random((n, 3)) < 0.4] = 0.0; parts.append(v)   # axis-aligned: zeros
+    v = rng.standard_normal((n, 3)); v[rng.random((n, 3)) < 0.3] *= -0.0; parts.append(v)  # signed zeros
+    parts.append(rng.standard_normal((n, 3)) * np.exp2(rng.integers(-30, 30, (n, 1))))    # any scale, one vector
+    parts.append(rng.standard_normal((n, 3)) * np.exp2(rng.integers(-60, 20, (n, 3))))    # mixed scales in one vector
+    parts.append(rng.standard_normal((n // 4, 3)) * np.exp2(rng.integers(-149, 127, (n // 4, 3))))  # ends of the range
+    parts.append(np.array([[0, 0, 0], [np.inf, 1, 0], [np.nan, 1, 2], [1e-45, 0, 0], [3e38, 3e38, 0], [1, -0.0, 0.0],
+                           [1e-30, 1, 0], [1e-39, 1e-39, 1e-39], [-0.0, -0.0, -1e-20]]))
+    for part in parts:
+        with np.errstate(all="ignore"):
+            v = np.ascontiguousarray(part, dtype=np.float32)
+            length = np.sqrt((v[:, 0] * v[:, 0] + v[:, 1] * v[:, 1]) + v[:, 2] * v[:, 2], dtype=np.float32)
+            want = (v / length[:, None]).astype(np.float32)
+        got = device.normalize(v)
+        same = (got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))
+        assert same.all(), f"{(~same).sum()} of {same.size} components differ, e.g. {v[~same.all(axis=1)][:3]}"
+        # the same sequence as a plain division (barycentrics over det): either sign of the denominator
+        with np.errstate(all="ignore"):
+            den = (rng.standard_normal(v.shape[0]) * np.exp2(rng.integers(-45, 45, v.shape[0]))).astype(np.float32)
+            den[:: 97] = np.float32(0.0)
+            want = (v / den[:, None]).astype(np.float32)
+        got = device.normalize(v, den)
+        same = (got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))
+        assert same.all(), f"division: {(~same).sum()} of {same.size} quotients differ"
+
+
 def test_materials(device, oracle_lib):
     """SampleLight for every material kind against the reference golden vectors."""
     from amber_b200 import FlatSceneBuilder, Sensor, capi
