@@ -34,9 +34,11 @@ struct SequentialRng {
     id = stream_id;
     i = 0;
   }
-  __device__ __forceinline__ float next() {
+  // out of line: next() has some 16 call sites in the subpath generator, a Philox block is ~90 instructions
+  __device__ __noinline__ void refill(uint32_t index) { block = philox4x32_10(key0, key1, pixel, sample, id, index); }
+  __device__ __noinline__ float next() {
     const uint32_t k = i++;
-    if ((k & 3u) == 0) block = philox4x32_10(key0, key1, pixel, sample, id, k >> 2);
+    if ((k & 3u) == 0) refill(k >> 2);
     const uint32_t w = k & 3u;
     return philox_uniform(w == 0 ? block.x : w == 1 ? block.y : w == 2 ? block.z : block.w);
   }
@@ -79,14 +81,20 @@ __device__ __forceinline__ int surface_of(const SceneView& scene, int material) 
 }
 
 // Closest hit of one lane's ray, callable from divergent code.
+//
+// Code size: the first version of this kernel inlined everything and came to 176 KB of SASS -- far beyond
+// the instruction caches, and ncu showed 86 % of its stall samples as "no instruction" with 9.5 % of the
+// issue slots used.  Every large piece that has more than one call site (the cast, subpath generation, the
+// BSDF / pdf evaluators with their powf, the connection, the MIS weight) is therefore ONE out-of-line
+// function (__noinline__): a call costs a few moves, an instruction-cache miss costs hundreds of cycles.
 template <class Accel>
-__device__ __forceinline__ HitRecord closest_lane(const SceneView& scene, const Ray& ray);
+__device__ __forceinline__ HitRecord closest_lane_inline(const SceneView& scene, const Ray& ray);
 template <>
-__device__ __forceinline__ HitRecord closest_lane<ConstList>(const SceneView& scene, const Ray& ray) {
+__device__ __forceinline__ HitRecord closest_lane_inline<ConstList>(const SceneView& scene, const Ray& ray) {
   return ConstList::closest(scene, ray, true);
 }
 template <>
-__device__ __forceinline__ HitRecord closest_lane<WideBvh>(const SceneView& scene, const Ray& ray) {
+__device__ __forceinline__ HitRecord closest_lane_inline<WideBvh>(const SceneView& scene, const Ray& ray) {
   SphereBound spheres;
   HitRecord hit;
   hit.t = spheres.bound(scene, ray);
@@ -115,6 +123,11 @@ __device__ __forceinline__ HitRecord closest_lane<WideBvh>(const SceneView& scen
   return spheres.resolve(scene, hit, found);
 }
 
+template <class Accel>
+__device__ __noinline__ HitRecord closest_lane(const SceneView& scene, const Ray& ray) {
+  return closest_lane_inline<Accel>(scene, ray);
+}
+
 // Refraction, src/amber/scene/material_refraction.cc:41-175: the Fresnel term of the branch
 // (reflection iff wo and wi lie on one side) and its sampling probability, for radiance
 // (BSDF / PDFLight: ior^2 scaling) or importance (AdjointBSDF / PDFImportance).
@@ -139,7 +152,7 @@ __device__ __forceinline__ void refraction_terms(const MaterialDev& m, float3 n,
 // Material::BSDF (adjoint = false) / AdjointBSDF (true) for every material kind:
 // material_{lambertian,phong,specular}.cc (symmetric), material_refraction.cc,
 // material_diffuse_light.h:141-161 (0), material_eye.h:97-117 (kDiracDelta).
-__device__ __forceinline__ float3 event_bsdf(const MaterialDev& m, float3 n, float3 wo, float3 wi, bool adjoint) {
+__device__ __noinline__ float3 event_bsdf(const MaterialDev& m, float3 n, float3 wo, float3 wi, bool adjoint) {
   const float3 rho = v3(m.r, m.g, m.b);
   switch (m.kind) {
     case 0:
@@ -156,7 +169,7 @@ __device__ __forceinline__ float3 event_bsdf(const MaterialDev& m, float3 n, flo
 }
 
 // Material::PDFLight (importance = false) / PDFImportance (true)
-__device__ __forceinline__ float event_pdf(const MaterialDev& m, float3 n, float3 wo, float3 wi, bool importance) {
+__device__ __noinline__ float event_pdf(const MaterialDev& m, float3 n, float3 wo, float3 wi, bool importance) {
   switch (m.kind) {
     case 0: return 1.0f / kPiF;  // material_lambertian.cc:51-59
     case 1: {                    // material_phong.cc:64-79
@@ -206,32 +219,43 @@ struct BdptCounters {
   uint32_t casts, splats;
 };
 
+// The leading event of a light subpath (LightSet::GenerateRay) / an eye subpath (Lens::GenerateRay): run
+// once per subpath, kept out of the generator's loop body (code size, see closest_lane).
+__device__ __noinline__ void bdpt_leading_light(const SceneView& scene, SequentialRng& rng, Ray& ray, float3& weight,
+                                                float3& normal, int32_t& object, float& bits) {
+  int light_index;
+  generate_light_ray(scene, rng, ray.o, ray.d, weight, &light_index);
+  const float4* L = reinterpret_cast<const float4*>(scene.lights + light_index);
+  normal = v3(__ldg(L + 3));
+  object = -3 - light_index;
+  bits = event_bits(__float_as_int(__ldg(L + 4).w), kSurfaceLight);
+}
+__device__ __noinline__ void bdpt_leading_eye(uint32_t pixel, SequentialRng& rng, Ray& ray, float3& weight,
+                                              float3& normal, int32_t& object, float& bits) {
+  const uint32_t width = c_camera.sensor.width;
+  float w;
+  generate_eye_ray(pixel % width, pixel / width, rng, ray.o, ray.d, w, &normal);
+  weight = v3(w, w, w);
+  object = kObjectLens;
+  bits = event_bits(-1, kSurfaceEye);
+}
+
 // GenerateLightSubpath (kImportance = true, :726-801) / GenerateEyeSubpath (false, :821-899).
 // Returns the number of events; `specular` gets one bit per event whose surface is not Diffuse,
 // `eye_surface` one bit per (non-leading) event on an aperture triangle.
-template <class Accel, bool kImportance>
-__device__ __forceinline__ int generate_subpath(const RenderArgs& args, uint32_t pixel, SequentialRng& rng, int cap,
-                                                BdptEvent* out, uint32_t& specular, uint32_t& eye_surface,
-                                                BdptCounters& count) {
+template <class Accel>
+__device__ __noinline__ int generate_subpath(const RenderArgs& args, const bool kImportance, uint32_t pixel,
+                                             SequentialRng& rng, int cap, BdptEvent* out, uint32_t& specular,
+                                             uint32_t& eye_surface, BdptCounters& count) {
   const SceneView& scene = args.scene;
   Ray ray;
   float3 weight, normal;
   int32_t object;
   float bits;
   if (kImportance) {
-    int light_index;
-    generate_light_ray(scene, rng, ray.o, ray.d, weight, &light_index);
-    const float4* L = reinterpret_cast<const float4*>(scene.lights + light_index);
-    normal = v3(__ldg(L + 3));
-    object = -3 - light_index;
-    bits = event_bits(__float_as_int(__ldg(L + 4).w), kSurfaceLight);
+    bdpt_leading_light(scene, rng, ray, weight, normal, object, bits);
   } else {
-    const uint32_t width = c_camera.sensor.width;
-    float w;
-    generate_eye_ray(pixel % width, pixel / width, rng, ray.o, ray.d, w, &normal);
-    weight = v3(w, w, w);
-    object = kObjectLens;
-    bits = event_bits(-1, kSurfaceEye);
+    bdpt_leading_eye(pixel, rng, ray, weight, normal, object, bits);
   }
   // SubpathEvent(object, leading), :281-294: direction_out = normal, NaN geometry factor and pdfs
   out[0].mis = make_float4(CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F, bits);
@@ -287,29 +311,39 @@ struct BdptContribution {
   float edge_gf, edge_p_light, edge_p_importance;
 };
 
-// Connect, :901-1017.  le / ee are register copies of the two endpoints (null = that subpath is empty).
-template <class Accel>
-__device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene, const BdptEvent* le, const BdptEvent* ee,
-                                                         BdptCounters& count) {
+__device__ __forceinline__ BdptContribution empty_contribution() {
   BdptContribution c;
   c.value = v3(0.0f, 0.0f, 0.0f);
   c.has_pixel = false;
   c.pixel = 0;
   c.edge_gf = c.edge_p_light = c.edge_p_importance = 0.0f;
-  if (!le && !ee) return c;
-  if (!le) {  // s = 0: the eye subpath found a light
-    if (ee->surface() != kSurfaceLight) return c;
-    c.value = ee->weight() * emitted_radiance(load_material(scene, ee->material()), ee->normal(), ee->direction_out());
-    return c;
-  }
-  if (!ee) {  // t = 0: the light subpath found the aperture
-    float response;
-    if (le->surface() != kSurfaceEye || le->leading()) return c;
-    if (!lens_response(le->position(), le->direction_out(), c.pixel, response)) return c;
-    c.has_pixel = true;
-    c.value = response * le->weight();
-    return c;
-  }
+  return c;
+}
+
+// Connect, :901-1017, s = 0 (:910-921): the eye subpath found a light.
+__device__ __forceinline__ BdptContribution bdpt_connect_s0(const SceneView& scene, const BdptEvent* ee) {
+  BdptContribution c = empty_contribution();
+  if (ee->surface() != kSurfaceLight) return c;
+  c.value = ee->weight() * emitted_radiance(load_material(scene, ee->material()), ee->normal(), ee->direction_out());
+  return c;
+}
+
+// Connect, t = 0 (:923-936): the light subpath found the aperture.
+__device__ __forceinline__ BdptContribution bdpt_connect_t0(const BdptEvent* le) {
+  BdptContribution c = empty_contribution();
+  float response;
+  if (le->surface() != kSurfaceEye || le->leading()) return c;
+  if (!lens_response(le->position(), le->direction_out(), c.pixel, response)) return c;
+  c.has_pixel = true;
+  c.value = response * le->weight();
+  return c;
+}
+
+// Connect, s >= 1 and t >= 1 (:938-1016).  le / ee are register copies of the two endpoints.
+template <class Accel>
+__device__ __noinline__ BdptContribution bdpt_connect(const SceneView& scene, const BdptEvent* le, const BdptEvent* ee,
+                                                      BdptCounters& count) {
+  BdptContribution c = empty_contribution();
   if (!le->leading() && le->surface() != kSurfaceDiffuse) return c;
   if (!ee->leading() && ee->surface() != kSurfaceDiffuse) return c;
   const float3 lp = le->position(), ep = ee->position();
@@ -373,7 +407,7 @@ __device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene,
 // with p_light[last] = the lens's directional pdf and p_importance[0] = the light's (1/pi).  The
 // technique ratios are accumulated outward from technique s as running products; a technique is
 // disabled when it would connect at a specular interior event (:661-697).
-__device__ __forceinline__ float bdpt_mis_weight(const SceneView& scene, const BdptEvent* L, int s, uint32_t spec_l,
+__device__ __noinline__ float bdpt_mis_weight(const SceneView& scene, const BdptEvent* L, int s, uint32_t spec_l,
                                                  const BdptEvent* E, int t, uint32_t spec_e, const BdptContribution& c) {
   const int n = s + t + 1, last = s + t - 2;  // last edge index
   const float eye_pdf_area = c_camera.lens.p_area;
@@ -469,9 +503,9 @@ __global__ void __launch_bounds__(128) bdpt_kernel(const RenderArgs args, unsign
     int s_max = 0, t_max = 0;
     if (valid) {
       rng.init(args.seed, pixel, sample, 0x40000000u);
-      s_max = generate_subpath<Accel, true>(args, pixel, rng, cap, L, spec_l, eye_l, count);
+      s_max = generate_subpath<Accel>(args, true, pixel, rng, cap, L, spec_l, eye_l, count);
       rng.init(args.seed, pixel, sample, 0x40000001u);
-      t_max = generate_subpath<Accel, false>(args, pixel, rng, cap, E, spec_e, eye_e, count);
+      t_max = generate_subpath<Accel>(args, false, pixel, rng, cap, E, spec_e, eye_e, count);
       pairs++;
     }
     float3 measurement = v3(0.0f, 0.0f, 0.0f);
@@ -495,12 +529,12 @@ __global__ void __launch_bounds__(128) bdpt_kernel(const RenderArgs args, unsign
     // cell of the widest lane's (s, t) grid.
     if (t_max >= 2 && E[t_max - 1].surface() == kSurfaceLight) {
       const BdptEvent ee = E[t_max - 1];
-      accumulate(bdpt_connect<Accel>(args.scene, nullptr, &ee, count), 0, t_max);
+      accumulate(bdpt_connect_s0(args.scene, &ee), 0, t_max);
     }
     for (uint32_t m = eye_l; m; m &= m - 1u) {
       const int s = __ffs(m);  // event index + 1
       const BdptEvent le = L[s - 1];
-      accumulate(bdpt_connect<Accel>(args.scene, &le, nullptr, count), s, 0);
+      accumulate(bdpt_connect_t0(&le), s, 0);
     }
     const uint32_t s_set = (~spec_l | 1u) & ((s_max >= 32 ? 0u : (1u << s_max)) - 1u);       // bit k: s = k + 1
     const uint32_t t_set = (~spec_e & ~1u) & ((t_max >= 32 ? 0u : (1u << t_max)) - 1u);      // bit k: t = k + 1 >= 2

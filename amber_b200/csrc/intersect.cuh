@@ -212,6 +212,7 @@ struct ConstList {
     scan_triangles<false>(ray, hit.t, hit.prim);
     const int n_tris = c_scene.n_tris;
     const int n_spheres = c_scene.n_spheres;
+#pragma unroll 1
     for (int i = 0; i < n_spheres; i++) {
       if (intersect_sphere(c_scene.sphere[i], ray, hit.t, hit.t)) hit.prim = n_tris + i;
     }
@@ -226,6 +227,7 @@ struct ConstList {
     int prim = -1;
     if (scan_triangles<true>(ray, t, prim)) return true;
     const int n_spheres = c_scene.n_spheres;
+#pragma unroll 1
     for (int i = 0; i < n_spheres; i++) {
       if (intersect_sphere(c_scene.sphere[i], ray, t_max, t)) return true;
     }
