@@ -1,5 +1,6 @@
 // bdpt.cuh -- bidirectional path tracing (row N3): include/amber/rendering/bidirectional_path_sampling.h
-// and src/amber/rendering/algorithm_bdpt.cc:116-148 as ONE kernel, one thread per (pixel, sample).
+// and src/amber/rendering/algorithm_bdpt.cc:116-148 as ONE kernel of persistent warps whose lanes each
+// carry one (pixel, sample) through a small state machine (see bdpt_kernel).
 //
 // Why not the wavefront: a BDPT sample is two short subpaths (2.8 events each on the Cornell box)
 // followed by (s + 1)(t + 1) connections whose MIS weights need every event of both subpaths; the
@@ -240,66 +241,80 @@ __device__ __noinline__ void bdpt_leading_eye(uint32_t pixel, SequentialRng& rng
   bits = event_bits(-1, kSurfaceEye);
 }
 
-// GenerateLightSubpath (kImportance = true, :726-801) / GenerateEyeSubpath (false, :821-899).
-// Returns the number of events; `specular` gets one bit per event whose surface is not Diffuse,
-// `eye_surface` one bit per (non-leading) event on an aperture triangle.
-template <class Accel>
-__device__ __noinline__ int generate_subpath(const RenderArgs& args, const bool kImportance, uint32_t pixel,
-                                             SequentialRng& rng, int cap, BdptEvent* out, uint32_t& specular,
-                                             uint32_t& eye_surface, BdptCounters& count) {
-  const SceneView& scene = args.scene;
+// The state one lane carries while it grows a subpath (GenerateLightSubpath, :726-801, kImportance = true;
+// GenerateEyeSubpath, :821-899, false): the ray about to be cast, the weight and normal of the event it
+// leaves, and what Combine needs to know about the events so far.
+struct BdptSubpath {
   Ray ray;
   float3 weight, normal;
+  int n;                 // events so far
+  uint32_t specular;     // bit k: event k's surface is not Diffuse (bit 0 set: a leading event never is)
+  uint32_t eye_surface;  // bit k: (non-leading) event k lies on an aperture triangle
+  bool ends_on_light;    // the last event is an emitter (only the last one can be: a light absorbs)
+};
+
+// The leading event: SubpathEvent(object, leading), :281-294 -- direction_out = normal, NaN geometry
+// factor and pdfs.
+__device__ __forceinline__ void bdpt_begin_subpath(const RenderArgs& args, bool importance, uint32_t pixel,
+                                                   SequentialRng& rng, BdptEvent* out, BdptSubpath& sp) {
   int32_t object;
   float bits;
-  if (kImportance) {
-    bdpt_leading_light(scene, rng, ray, weight, normal, object, bits);
+  if (importance) {
+    bdpt_leading_light(args.scene, rng, sp.ray, sp.weight, sp.normal, object, bits);
   } else {
-    bdpt_leading_eye(pixel, rng, ray, weight, normal, object, bits);
+    bdpt_leading_eye(pixel, rng, sp.ray, sp.weight, sp.normal, object, bits);
   }
-  // SubpathEvent(object, leading), :281-294: direction_out = normal, NaN geometry factor and pdfs
   out[0].mis = make_float4(CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F, bits);
-  out[0].pos_obj = make_float4(ray.o.x, ray.o.y, ray.o.z, __int_as_float(object));
-  out[0].normal4 = make_float4(normal.x, normal.y, normal.z, 0.0f);
+  out[0].pos_obj = make_float4(sp.ray.o.x, sp.ray.o.y, sp.ray.o.z, __int_as_float(object));
+  out[0].normal4 = make_float4(sp.normal.x, sp.normal.y, sp.normal.z, 0.0f);
   out[0].dout4 = out[0].normal4;
-  out[0].weight4 = make_float4(weight.x, weight.y, weight.z, 0.0f);
-  specular = 1u;  // a leading event is never "Diffuse"; bit 0 is not looked at
-  eye_surface = 0u;
-  int n = 1;
-  for (int i = 1; i < cap; i++) {
-    const HitRecord hit = closest_lane<Accel>(scene, ray);
-    count.casts++;
-    if (hit.prim < 0) break;
-    float3 x, hn;
-    int material_index;
-    surface_point(scene, ray, hit, x, hn, material_index);
-    const MaterialDev m = load_material(scene, material_index);
-    const float3 wo = -ray.d;
-    const Scatter scatter = sample_light(m, hn, wo, rng, kImportance);
-    const float3 wi = scatter.dir;
-    // forward = the transport being traced, backward = the other one
-    const float p_forward = event_pdf(m, hn, wo, wi, kImportance);
-    const float p_rr_forward = min_rr(max3(scatter.weight));
-    const float p_backward = event_pdf(m, hn, wi, wo, !kImportance);
-    const float3 bsdf_backward = event_bsdf(m, hn, wi, wo, !kImportance);
-    const float p_rr_backward = min_rr(max3((1.0f / p_backward) * bsdf_backward));
-    const int surface = surface_of_kind(m.kind);
-    if (surface != kSurfaceDiffuse) specular |= 1u << n;
-    if (surface == kSurfaceEye) eye_surface |= 1u << n;
-    BdptEvent& e = out[n++];
-    e.mis = make_float4(fabsf(dot(wo, normal) * dot(wo, hn) / (hit.t * hit.t)), p_backward * p_rr_backward,
-                        p_forward * p_rr_forward, event_bits(material_index, surface));
-    e.pos_obj = make_float4(x.x, x.y, x.z, __int_as_float(hit.prim));
-    e.normal4 = make_float4(hn.x, hn.y, hn.z, 0.0f);
-    e.dout4 = make_float4(wo.x, wo.y, wo.z, 0.0f);
-    e.weight4 = make_float4(weight.x, weight.y, weight.z, 0.0f);
-    if (!(rng.next() < p_rr_forward)) break;
-    ray.o = x;
-    ray.d = wi;
-    normal = hn;
-    weight = weight * ((1.0f / p_rr_forward) * scatter.weight);
-  }
-  return n;
+  out[0].weight4 = make_float4(sp.weight.x, sp.weight.y, sp.weight.z, 0.0f);
+  sp.specular = 1u;
+  sp.eye_surface = 0u;
+  sp.ends_on_light = false;
+  sp.n = 1;
+}
+
+// One iteration of the generators' loop: cast, append the event, Russian roulette.  Returns false when
+// the subpath is complete (miss, roulette, or `cap` events).
+template <class Accel>
+__device__ __noinline__ bool bdpt_grow_subpath(const SceneView& scene, const bool kImportance, SequentialRng& rng,
+                                               int cap, BdptEvent* out, BdptSubpath& sp, BdptCounters& count) {
+  if (sp.n >= cap) return false;
+  const Ray ray = sp.ray;
+  const HitRecord hit = closest_lane<Accel>(scene, ray);
+  count.casts++;
+  if (hit.prim < 0) return false;
+  float3 x, hn;
+  int material_index;
+  surface_point(scene, ray, hit, x, hn, material_index);
+  const MaterialDev m = load_material(scene, material_index);
+  const float3 wo = -ray.d;
+  const Scatter scatter = sample_light(m, hn, wo, rng, kImportance);
+  const float3 wi = scatter.dir;
+  // forward = the transport being traced, backward = the other one
+  const float p_forward = event_pdf(m, hn, wo, wi, kImportance);
+  const float p_rr_forward = min_rr(max3(scatter.weight));
+  const float p_backward = event_pdf(m, hn, wi, wo, !kImportance);
+  const float3 bsdf_backward = event_bsdf(m, hn, wi, wo, !kImportance);
+  const float p_rr_backward = min_rr(max3((1.0f / p_backward) * bsdf_backward));
+  const int surface = surface_of_kind(m.kind);
+  if (surface != kSurfaceDiffuse) sp.specular |= 1u << sp.n;
+  if (surface == kSurfaceEye) sp.eye_surface |= 1u << sp.n;
+  sp.ends_on_light = surface == kSurfaceLight;
+  BdptEvent& e = out[sp.n++];
+  e.mis = make_float4(fabsf(dot(wo, sp.normal) * dot(wo, hn) / (hit.t * hit.t)), p_backward * p_rr_backward,
+                      p_forward * p_rr_forward, event_bits(material_index, surface));
+  e.pos_obj = make_float4(x.x, x.y, x.z, __int_as_float(hit.prim));
+  e.normal4 = make_float4(hn.x, hn.y, hn.z, 0.0f);
+  e.dout4 = make_float4(wo.x, wo.y, wo.z, 0.0f);
+  e.weight4 = make_float4(sp.weight.x, sp.weight.y, sp.weight.z, 0.0f);
+  if (!(rng.next() < p_rr_forward)) return false;
+  sp.ray.o = x;
+  sp.ray.d = wi;
+  sp.normal = hn;
+  sp.weight = sp.weight * ((1.0f / p_rr_forward) * scatter.weight);
+  return sp.n < cap;
 }
 
 struct BdptContribution {
@@ -480,83 +495,165 @@ __device__ __noinline__ float bdpt_mis_weight(const SceneView& scene, const Bdpt
   return 1.0f / sum;
 }
 
-// Thread::operator() / Thread::Render / Combine: one (pixel, sample) per thread, grid-stride.
+// index of the k-th set bit of mask (k < popc(mask)); __fns is a 160-instruction library loop
+__device__ __forceinline__ int nth_set_bit(uint32_t mask, int k) {
+  for (; k > 0; k--) mask &= mask - 1u;
+  return __ffs(mask) - 1;
+}
+
+// Thread::operator() / Thread::Render / Combine (algorithm_bdpt.cc:116-148, :1019-1068): one
+// (pixel, sample) per LANE at a time, persistent warps.
+//
+// A pixel sample goes through four kinds of step -- start a light subpath, grow a subpath by one event
+// (either side: the same code), start the eye subpath, evaluate one connection candidate -- and the
+// number of steps differs from sample to sample (2.8 events per subpath on average, up to 16; 0 to
+// 200 candidates).  Run sample by sample in lockstep, a warp spends most of its instructions with a few
+// lanes active (ncu: 7 of 32).  Here every lane is a small state machine; per iteration the warp votes
+// for the step most lanes are waiting for and runs that step for those lanes; a lane whose sample is
+// finished takes the next pair index from a global counter.  No lane ever waits for another lane's longer
+// subpath or longer candidate list, only for its kind of step to come up.
+//
+// Which (s, t) can contribute follows from the surface types alone (Connect, :910-950): s = 0 needs the
+// eye subpath to END on a light; t = 0 needs a light-subpath event on the aperture; t = 1 never passes
+// the visibility test (see bdpt_connect); every other pair needs a Diffuse (or leading light) endpoint
+// on each side -- the PRODUCT of two event sets.  A lane enumerates its candidates by index in
+// Combine's order: s = 0, the t = 0 ones by increasing s, then the product.
+enum : int { kBdptStartLight = 0, kBdptGrow = 1, kBdptStartEye = 2, kBdptConnect = 3, kBdptDone = 4 };
+
 template <class Accel>
 __global__ void __launch_bounds__(128) bdpt_kernel(const RenderArgs args, unsigned long long total_pairs, int cap) {
-  BdptEvent L[kBdptMaxEvents], E[kBdptMaxEvents];
+  BdptEvent events[2 * kBdptMaxEvents];
+  BdptEvent* const L = events;
+  BdptEvent* const E = events + kBdptMaxEvents;
   BdptCounters count;
   count.casts = 0;
   count.splats = 0;
   uint32_t pairs = 0;
-  const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * blockDim.x;
   const uint32_t lane = threadIdx.x & 31u;
-  // the loop is warp-uniform (the connection rounds below vote across the warp): a warp's lanes
-  // hold 32 consecutive pairs, lanes past the end carry empty subpaths
-  for (unsigned long long first = static_cast<unsigned long long>(blockIdx.x) * blockDim.x + threadIdx.x - lane;
-       first < total_pairs; first += stride) {
-    const unsigned long long pair = first + lane;
-    const bool valid = pair < total_pairs;
-    const uint32_t pixel = static_cast<uint32_t>(pair % args.n_pixels);
-    const uint32_t sample = static_cast<uint32_t>(args.sample_begin + pair / args.n_pixels);
-    SequentialRng rng;
-    uint32_t spec_l = 0, spec_e = 0, eye_l = 0, eye_e = 0;
-    int s_max = 0, t_max = 0;
-    if (valid) {
-      rng.init(args.seed, pixel, sample, 0x40000000u);
-      s_max = generate_subpath<Accel>(args, true, pixel, rng, cap, L, spec_l, eye_l, count);
-      rng.init(args.seed, pixel, sample, 0x40000001u);
-      t_max = generate_subpath<Accel>(args, false, pixel, rng, cap, E, spec_e, eye_e, count);
-      pairs++;
-    }
-    float3 measurement = v3(0.0f, 0.0f, 0.0f);
-    auto accumulate = [&](const BdptContribution& c, int s, int t) {
-      if (!(max3(c.value) > 0.0f)) return;
-      const float weight = bdpt_mis_weight(args.scene, L, s, spec_l, E, t, spec_e, c);
-      if (c.has_pixel) {  // light image: / sensor.Size(), :1054-1056
-        film_add(args.film, c.pixel, (weight * args.inv_n_pixels) * c.value);
-        count.splats++;
-      } else {
-        measurement = measurement + weight * c.value;
+  const uint32_t lane_lt = (1u << lane) - 1u;
+  constexpr uint32_t kFull = 0xffffffffu;
+
+  int phase = kBdptStartLight;
+  bool eye_side = false;  // kBdptGrow: which subpath is growing
+  uint32_t pixel = 0, sample = 0;
+  SequentialRng rng;
+  BdptSubpath sp;
+  int s_max = 0, t_max = 0;
+  uint32_t spec_l = 0, eye_l = 0, s_set = 0, t_set = 0, spec_e = 0;
+  int n_s0 = 0, n_t0 = 0, n_s = 0, candidates = 0, next_candidate = 0;
+  float3 measurement = v3(0.0f, 0.0f, 0.0f);
+
+  for (;;) {
+    const uint32_t want_light = __ballot_sync(kFull, phase == kBdptStartLight);
+    const uint32_t want_grow = __ballot_sync(kFull, phase == kBdptGrow);
+    const uint32_t want_eye = __ballot_sync(kFull, phase == kBdptStartEye);
+    const uint32_t want_connect = __ballot_sync(kFull, phase == kBdptConnect);
+    if (!(want_light | want_grow | want_eye | want_connect)) break;
+    // the step most lanes wait for (ties: grow, connect, start eye, start light -- work in flight first)
+    const int n_light = __popc(want_light), n_grow = __popc(want_grow), n_eye = __popc(want_eye),
+              n_connect = __popc(want_connect);
+    int step = kBdptGrow, best = n_grow;
+    if (n_connect > best) { step = kBdptConnect; best = n_connect; }
+    if (n_eye > best) { step = kBdptStartEye; best = n_eye; }
+    if (n_light > best) { step = kBdptStartLight; best = n_light; }
+
+    if (step == kBdptStartLight) {
+      if (phase == kBdptStartLight) {
+        // next pair index: one atomic per warp
+        const int leader = __ffs(want_light) - 1;
+        unsigned long long base = 0;
+        if (static_cast<int>(lane) == leader)
+          base = atomicAdd(&args.ctl->cursor_bdpt, static_cast<unsigned long long>(n_light));
+        base = __shfl_sync(want_light, base, leader);
+        const unsigned long long pair = base + __popc(want_light & lane_lt);
+        if (pair >= total_pairs) {
+          phase = kBdptDone;
+        } else {
+          pixel = static_cast<uint32_t>(pair % args.n_pixels);
+          sample = static_cast<uint32_t>(args.sample_begin + pair / args.n_pixels);
+          pairs++;
+          measurement = v3(0.0f, 0.0f, 0.0f);
+          rng.init(args.seed, pixel, sample, 0x40000000u);
+          bdpt_begin_subpath(args, true, pixel, rng, L, sp);
+          eye_side = false;
+          phase = kBdptGrow;
+        }
       }
-    };
-    // Combine, :1019-1068.  Which (s, t) can contribute at all follows from the surface types alone
-    // (Connect, :910-950): s = 0 needs the eye subpath to END on a light (a light absorbs: only the
-    // last event can be one); t = 0 needs a light-subpath event on the aperture; t = 1 never passes
-    // the visibility test (see bdpt_connect); every other pair needs a Diffuse (or leading light)
-    // endpoint on each side -- the PRODUCT of two event sets.  A lane therefore walks its
-    // candidate list by index, and the warp runs max-over-lanes rounds in lockstep, so the expensive
-    // part (BSDFs, the shadow cast, the MIS weight) runs with the lanes packed instead of once per
-    // cell of the widest lane's (s, t) grid.
-    if (t_max >= 2 && E[t_max - 1].surface() == kSurfaceLight) {
-      const BdptEvent ee = E[t_max - 1];
-      accumulate(bdpt_connect_s0(args.scene, &ee), 0, t_max);
-    }
-    for (uint32_t m = eye_l; m; m &= m - 1u) {
-      const int s = __ffs(m);  // event index + 1
-      const BdptEvent le = L[s - 1];
-      accumulate(bdpt_connect_t0(&le), s, 0);
-    }
-    const uint32_t s_set = (~spec_l | 1u) & ((s_max >= 32 ? 0u : (1u << s_max)) - 1u);       // bit k: s = k + 1
-    const uint32_t t_set = (~spec_e & ~1u) & ((t_max >= 32 ? 0u : (1u << t_max)) - 1u);      // bit k: t = k + 1 >= 2
-    const int n_s = __popc(s_set), n_t = __popc(t_set);
-    const int mine = n_s * n_t;
-    const int rounds = __reduce_max_sync(0xffffffffu, mine);
-    for (int j = 0; j < rounds; j++) {
-      if (j < mine) {
-        const int s = __fns(s_set, 0, j % n_s + 1) + 1;
-        const int t = __fns(t_set, 0, j / n_s + 1) + 1;
-        const BdptEvent le = L[s - 1];
-        const BdptEvent ee = E[t - 1];
-        accumulate(bdpt_connect<Accel>(args.scene, &le, &ee, count), s, t);
+    } else if (step == kBdptStartEye) {
+      if (phase == kBdptStartEye) {
+        rng.init(args.seed, pixel, sample, 0x40000001u);
+        bdpt_begin_subpath(args, false, pixel, rng, E, sp);
+        eye_side = true;
+        phase = kBdptGrow;
+      }
+    } else if (step == kBdptGrow) {
+      if (phase == kBdptGrow) {
+        const bool more = bdpt_grow_subpath<Accel>(args.scene, !eye_side, rng, cap, eye_side ? E : L, sp, count);
+        if (!more) {
+          if (!eye_side) {
+            s_max = sp.n;
+            spec_l = sp.specular;
+            eye_l = sp.eye_surface;
+            phase = kBdptStartEye;
+          } else {
+            t_max = sp.n;
+            spec_e = sp.specular;
+            // the candidate list of this sample
+            n_s0 = (t_max >= 2 && sp.ends_on_light) ? 1 : 0;
+            n_t0 = __popc(eye_l);
+            s_set = (~spec_l | 1u) & ((s_max >= 32 ? 0u : (1u << s_max)) - 1u);   // bit k: s = k + 1
+            t_set = (~spec_e & ~1u) & ((t_max >= 32 ? 0u : (1u << t_max)) - 1u);  // bit k: t = k + 1 >= 2
+            n_s = __popc(s_set);
+            candidates = n_s0 + n_t0 + n_s * __popc(t_set);
+            next_candidate = 0;
+            phase = candidates > 0 ? kBdptConnect : kBdptStartLight;
+          }
+        }
+      }
+    } else {
+      if (phase == kBdptConnect) {
+        const int j = next_candidate++;
+        BdptContribution c;
+        int s, t;
+        if (j < n_s0) {
+          s = 0;
+          t = t_max;
+          const BdptEvent ee = E[t_max - 1];
+          c = bdpt_connect_s0(args.scene, &ee);
+        } else if (j < n_s0 + n_t0) {
+          s = nth_set_bit(eye_l, j - n_s0) + 1;  // event index + 1
+          t = 0;
+          const BdptEvent le = L[s - 1];
+          c = bdpt_connect_t0(&le);
+        } else {
+          const int k = j - n_s0 - n_t0;
+          s = nth_set_bit(s_set, k % n_s) + 1;
+          t = nth_set_bit(t_set, k / n_s) + 1;
+          const BdptEvent le = L[s - 1];
+          const BdptEvent ee = E[t - 1];
+          c = bdpt_connect<Accel>(args.scene, &le, &ee, count);
+        }
+        if (max3(c.value) > 0.0f) {
+          const float weight = bdpt_mis_weight(args.scene, L, s, spec_l, E, t, spec_e, c);
+          if (c.has_pixel) {  // light image: / sensor.Size(), :1054-1056
+            film_add(args.film, c.pixel, (weight * args.inv_n_pixels) * c.value);
+            count.splats++;
+          } else {
+            measurement = measurement + weight * c.value;
+          }
+        }
+        if (next_candidate >= candidates) {
+          if (max3(measurement) > 0.0f) film_add(args.film, pixel, measurement);
+          phase = kBdptStartLight;
+        }
       }
     }
-    if (max3(measurement) > 0.0f) film_add(args.film, pixel, measurement);
   }
   // counters: one atomic per warp
-  const uint32_t casts = __reduce_add_sync(0xffffffffu, count.casts);
-  const uint32_t splats = __reduce_add_sync(0xffffffffu, count.splats);
-  const uint32_t n_pairs = __reduce_add_sync(0xffffffffu, pairs);
-  if ((threadIdx.x & 31) == 0) {
+  const uint32_t casts = __reduce_add_sync(kFull, count.casts);
+  const uint32_t splats = __reduce_add_sync(kFull, count.splats);
+  const uint32_t n_pairs = __reduce_add_sync(kFull, pairs);
+  if (lane == 0) {
     atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(casts));
     atomicAdd(&args.ctl->splats, static_cast<unsigned long long>(splats));
     atomicAdd(&args.ctl->paths, static_cast<unsigned long long>(n_pairs));

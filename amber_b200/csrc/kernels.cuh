@@ -51,6 +51,7 @@ struct Control {
   unsigned long long base_sample;  // next_path / n_pixels
   unsigned int n_pixels;
   unsigned int pad;
+  unsigned long long cursor_bdpt;  // bdpt_kernel: next (pixel, sample) pair index
 };
 
 struct PathPool {
