@@ -721,6 +721,28 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
     ctx->const_scene.axis_entry[k] = const_list.axis_entries[k];
     ctx->const_scene.axis_tri[k] = const_list.axis_tri[k];
   }
+  {  // pair the unclustered entries of each axis for the packed scan (scene_device.cuh, AxisPair)
+    size_t entry = 0, pair = 0;
+    for (int axis = 0; axis < 3; axis++) {
+      const size_t n = static_cast<size_t>(const_list.n_axis_entries[axis]);
+      for (size_t k = 0; k < n; k += 2, pair++) {
+        const AxisEntry& a = const_list.axis_entries[entry + k];
+        AxisEntry b{};
+        b.limit = -1.0f;
+        if (k + 1 < n) b = const_list.axis_entries[entry + k + 1];
+        AxisPair& P = ctx->const_scene.axis_pair[pair];
+        P.r_k = make_float2(a.r_k, b.r_k);
+        P.neg_r_a = make_float2(-a.r_a, -b.r_a);
+        P.neg_r_b = make_float2(-a.r_b, -b.r_b);
+        P.nu_a = make_float2(a.nu_a, b.nu_a);
+        P.nu_b = make_float2(a.nu_b, b.nu_b);
+        P.nv_a = make_float2(a.nv_a, b.nv_a);
+        P.nv_b = make_float2(a.nv_b, b.nv_b);
+        P.limit = make_float2(a.limit, b.limit);
+      }
+      entry += n;
+    }
+  }
   for (size_t g = 0; g < const_list.groups.size(); g++) ctx->const_scene.group[g] = const_list.groups[g];
   for (size_t k = 0; k < const_list.entries.size(); k++) ctx->const_scene.entry[k] = const_list.entries[k];
   for (size_t k = 0; k < n_spheres; k++) ctx->const_scene.sphere[k] = spheres[k];

@@ -520,8 +520,11 @@ __device__ __forceinline__ int nth_set_bit(uint32_t mask, int k) {
 // Combine's order: s = 0, the t = 0 ones by increasing s, then the product.
 enum : int { kBdptStartLight = 0, kBdptGrow = 1, kBdptStartEye = 2, kBdptConnect = 3, kBdptDone = 4 };
 
+#ifndef AMBER_BDPT_BLOCKS
+#define AMBER_BDPT_BLOCKS 8
+#endif
 template <class Accel>
-__global__ void __launch_bounds__(128) bdpt_kernel(const RenderArgs args, unsigned long long total_pairs, int cap) {
+__global__ void __launch_bounds__(128, AMBER_BDPT_BLOCKS) bdpt_kernel(const RenderArgs args, unsigned long long total_pairs, int cap) {
   BdptEvent events[2 * kBdptMaxEvents];
   BdptEvent* const L = events;
   BdptEvent* const E = events + kBdptMaxEvents;

@@ -149,6 +149,47 @@ struct ConstList {
     return true;
   }
 
+  // scan_axis over the PAIRED unclustered entries of one axis (scene_device.cuh, AxisPair): the arithmetic
+  // of two entries in packed fp32 instructions, the acceptance tests one entry after the other in list
+  // order (so the strict `<` of the closest-hit update sees them as the flat loop does).
+  // `first_entry` is the index of the axis's first entry in axis_tri[].
+  template <bool kAnyHit>
+  static __device__ __forceinline__ bool scan_axis_pairs(int first_pair, int n_pairs, int first_entry, float ok,
+                                                         float oa, float ob, float inv_dk, float da, float db,
+                                                         float& t_best, int& prim) {
+    const float2 nok2 = make_float2(-ok, -ok), oa2 = make_float2(oa, oa), ob2 = make_float2(ob, ob);
+    const float2 inv2 = make_float2(inv_dk, inv_dk), da2 = make_float2(da, da), db2 = make_float2(db, db);
+    int best = -1;
+    float best_sum = 0.0f;
+#pragma unroll 1
+    for (int p = 0; p < n_pairs; p++) {
+      const AxisPair& P = c_scene.axis_pair[first_pair + p];
+      const float2 t = __fmul2_rn(__fadd2_rn(P.r_k, nok2), inv2);
+      const float2 ha = __ffma2_rn(t, da2, __fadd2_rn(oa2, P.neg_r_a));
+      const float2 hb = __ffma2_rn(t, db2, __fadd2_rn(ob2, P.neg_r_b));
+      const float2 s = __ffma2_rn(P.nu_a, ha, __fmul2_rn(P.nu_b, hb));
+      const float2 q = __ffma2_rn(P.nv_a, ha, __fmul2_rn(P.nv_b, hb));
+      const float2 sum = __fadd2_rn(s, q);
+      if ((t.x > kEpsF) & (t.x < t_best) & (s.x >= 0.0f) & (q.x >= 0.0f) & (s.x <= 1.0f) & (q.x <= 1.0f) &
+          (sum.x <= P.limit.x)) {
+        t_best = t.x;
+        best = 2 * p;
+        best_sum = sum.x;
+        if (kAnyHit) return true;
+      }
+      if ((t.y > kEpsF) & (t.y < t_best) & (s.y >= 0.0f) & (q.y >= 0.0f) & (s.y <= 1.0f) & (q.y <= 1.0f) &
+          (sum.y <= P.limit.y)) {
+        t_best = t.y;
+        best = 2 * p + 1;
+        best_sum = sum.y;
+        if (kAnyHit) return true;
+      }
+    }
+    if (best < 0) return false;
+    prim = c_scene.axis_tri[first_entry + best] + (best_sum > 1.0f ? 1 : 0);
+    return true;
+  }
+
   // All constant-memory triangles: axis-perpendicular entries, then the general plane groups.
   template <bool kAnyHit>
   static __device__ __forceinline__ bool scan_triangles(const Ray& ray, float& t_best, int& prim) {
@@ -159,11 +200,12 @@ struct ConstList {
       asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ix) : "f"(ray.d.x));
       asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iy) : "f"(ray.d.y));
       asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iz) : "f"(ray.d.z));
-      any |= scan_axis<kAnyHit>(0, nx, ray.o.x, ray.o.y, ray.o.z, ix, ray.d.y, ray.d.z, t_best, prim);
+      const int px = (nx + 1) >> 1, py = (ny + 1) >> 1, pz = (nz + 1) >> 1;  // pairs per axis
+      any |= scan_axis_pairs<kAnyHit>(0, px, 0, ray.o.x, ray.o.y, ray.o.z, ix, ray.d.y, ray.d.z, t_best, prim);
       if (kAnyHit && any) return true;
-      any |= scan_axis<kAnyHit>(nx, ny, ray.o.y, ray.o.z, ray.o.x, iy, ray.d.z, ray.d.x, t_best, prim);
+      any |= scan_axis_pairs<kAnyHit>(px, py, nx, ray.o.y, ray.o.z, ray.o.x, iy, ray.d.z, ray.d.x, t_best, prim);
       if (kAnyHit && any) return true;
-      any |= scan_axis<kAnyHit>(nx + ny, nz, ray.o.z, ray.o.x, ray.o.y, iz, ray.d.x, ray.d.y, t_best, prim);
+      any |= scan_axis_pairs<kAnyHit>(px + py, pz, nx + ny, ray.o.z, ray.o.x, ray.o.y, iz, ray.d.x, ray.d.y, t_best, prim);
       if (kAnyHit && any) return true;
       // clusters: one bounding-rectangle test per plane, entries only if some lane lands inside.
       // The vote only ever ADDS work (a lane that lands inside always scans), so which lanes take

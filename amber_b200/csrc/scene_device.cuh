@@ -116,6 +116,14 @@ struct AxisEntry {
   float nv_b, limit;
 };
 
+// Two consecutive unclustered entries of one axis, field by field as float2, so that the scan evaluates
+// both with packed FADD2 / FMUL2 / FFMA2 (sm_100: one instruction, two lanes of fp32).  r_a and r_b are
+// stored negated (h = t d + (o + (-r))).  An odd entry count is padded with an entry nothing can hit
+// (nu = nv = 0, limit = -1: s + q = 0 > limit).
+struct AxisPair {
+  float2 r_k, neg_r_a, neg_r_b, nu_a, nu_b, nv_a, nv_b, limit;
+};
+
 // Three or more axis entries in ONE plane (the blades of the aperture, a tessellated wall) form a
 // cluster: the ray/plane point is tested against the cluster's bounding rectangle first and the
 // entries are scanned only if some lane of the warp lands inside it.  The Cornell box's aperture fan
@@ -133,6 +141,7 @@ struct ConstScene {
   int32_t pad;
   AxisCluster cluster[kMaxAxisClusters];
   AxisEntry axis_entry[kMaxConstTris];
+  AxisPair axis_pair[kMaxConstTris / 2 + 3];  // the unclustered entries again, paired per axis (x, y, z in order)
   uint8_t axis_tri[kMaxConstTris];  // first triangle (internal index) of each entry
   PlaneGroup group[kMaxConstTris];
   PlaneEntry entry[kMaxConstTris];  // group by group: quads, then lone triangles
