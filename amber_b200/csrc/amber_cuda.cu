@@ -967,18 +967,19 @@ int render_bdpt(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, uin
   int resident = 0, sm_count = 148;
   CUDA_TRY(ctx, cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device));
   CUDA_TRY(ctx, ctx->use_bvh
-                    ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, bdpt_kernel<WideBvh>, 128, 0)
-                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, bdpt_kernel<ConstList>, 128, 0));
-  const uint64_t blocks_needed = (total_pairs + 127) / 128;
+                    ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, bdpt_kernel<WideBvh>, BdptLaunch<WideBvh>::kThreads, 0)
+                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, bdpt_kernel<ConstList>, BdptLaunch<ConstList>::kThreads, 0));
+  const uint64_t threads = ctx->use_bvh ? BdptLaunch<WideBvh>::kThreads : BdptLaunch<ConstList>::kThreads;
+  const uint64_t blocks_needed = (total_pairs + threads - 1) / threads;
   const unsigned int grid = static_cast<unsigned int>(
       std::min<uint64_t>(blocks_needed, static_cast<uint64_t>(sm_count) * std::max(1, resident)));
   cudaStream_t stream = ctx->stream;
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev_begin, stream));
   CUDA_TRY(ctx, cudaMemsetAsync(&ctx->d_ctl.ptr->cursor_bdpt, 0, sizeof(unsigned long long), stream));
   if (ctx->use_bvh) {
-    bdpt_kernel<WideBvh><<<grid, 128, 0, stream>>>(args, total_pairs, cap);
+    bdpt_kernel<WideBvh><<<grid, BdptLaunch<WideBvh>::kThreads, 0, stream>>>(args, total_pairs, cap);
   } else {
-    bdpt_kernel<ConstList><<<grid, 128, 0, stream>>>(args, total_pairs, cap);
+    bdpt_kernel<ConstList><<<grid, BdptLaunch<ConstList>::kThreads, 0, stream>>>(args, total_pairs, cap);
   }
   ctx->stats.kernel_launches++;
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev_end, stream));

@@ -520,11 +520,20 @@ __device__ __forceinline__ int nth_set_bit(uint32_t mask, int k) {
 // Combine's order: s = 0, the t = 0 ones by increasing s, then the product.
 enum : int { kBdptStartLight = 0, kBdptGrow = 1, kBdptStartEye = 2, kBdptConnect = 3, kBdptDone = 4 };
 
-#ifndef AMBER_BDPT_BLOCKS
-#define AMBER_BDPT_BLOCKS 8
-#endif
+// Who votes.  On the constant-memory list every step takes about the same time, and a BLOCK-wide vote (all
+// warps of a 512-thread block run the same step, two blocks per SM) lets the warps share the instruction
+// cache lines of that step: 231 -> 314 M pixel samples/s (128 / 256 / 512 / 1024 threads: 246 / 285 / 314 /
+// 310).  On the 4-wide BVH a step's duration varies with the walk, a block-wide barrier per step makes every
+// warp wait for the slowest (117 -> 92 M/s at 512 threads), so there each WARP votes for itself.
 template <class Accel>
-__global__ void __launch_bounds__(128, AMBER_BDPT_BLOCKS) bdpt_kernel(const RenderArgs args, unsigned long long total_pairs, int cap) {
+struct BdptLaunch {
+  static constexpr bool kBlockVote = !Accel::kPersistent;
+  static constexpr int kThreads = kBlockVote ? 512 : 128;
+  static constexpr int kBlocks = kBlockVote ? 2 : 8;  // resident blocks per SM: 64 registers either way
+};
+template <class Accel>
+__global__ void __launch_bounds__(BdptLaunch<Accel>::kThreads, BdptLaunch<Accel>::kBlocks)
+    bdpt_kernel(const RenderArgs args, unsigned long long total_pairs, int cap) {
   BdptEvent events[2 * kBdptMaxEvents];
   BdptEvent* const L = events;
   BdptEvent* const E = events + kBdptMaxEvents;
@@ -546,15 +555,44 @@ __global__ void __launch_bounds__(128, AMBER_BDPT_BLOCKS) bdpt_kernel(const Rend
   int n_s0 = 0, n_t0 = 0, n_s = 0, candidates = 0, next_candidate = 0;
   float3 measurement = v3(0.0f, 0.0f, 0.0f);
 
+  constexpr bool kBlockVote = BdptLaunch<Accel>::kBlockVote;
+  __shared__ uint32_t votes[3][4];
+  uint32_t iteration = 0;
+  if (kBlockVote) {
+    if (threadIdx.x < 12) (&votes[0][0])[threadIdx.x] = 0;
+    __syncthreads();
+  }
   for (;;) {
     const uint32_t want_light = __ballot_sync(kFull, phase == kBdptStartLight);
     const uint32_t want_grow = __ballot_sync(kFull, phase == kBdptGrow);
     const uint32_t want_eye = __ballot_sync(kFull, phase == kBdptStartEye);
     const uint32_t want_connect = __ballot_sync(kFull, phase == kBdptConnect);
-    if (!(want_light | want_grow | want_eye | want_connect)) break;
+    int n_light, n_grow, n_eye, n_connect;
+    if (kBlockVote) {
+      // every warp of the block runs the SAME step.  Three vote buffers, one barrier per iteration:
+      // buffer (i+1)%3 was last read in iteration i-2, which every warp finished before it passed
+      // barrier i-1.
+      if (threadIdx.x < 4) votes[(iteration + 1) % 3][threadIdx.x] = 0;
+      if (lane == 0) {
+        if (want_light) atomicAdd(&votes[iteration % 3][0], __popc(want_light));
+        if (want_grow) atomicAdd(&votes[iteration % 3][1], __popc(want_grow));
+        if (want_eye) atomicAdd(&votes[iteration % 3][2], __popc(want_eye));
+        if (want_connect) atomicAdd(&votes[iteration % 3][3], __popc(want_connect));
+      }
+      __syncthreads();
+      n_light = votes[iteration % 3][0];
+      n_grow = votes[iteration % 3][1];
+      n_eye = votes[iteration % 3][2];
+      n_connect = votes[iteration % 3][3];
+      iteration++;
+    } else {
+      n_light = __popc(want_light);
+      n_grow = __popc(want_grow);
+      n_eye = __popc(want_eye);
+      n_connect = __popc(want_connect);
+    }
+    if (!(n_light | n_grow | n_eye | n_connect)) break;
     // the step most lanes wait for (ties: grow, connect, start eye, start light -- work in flight first)
-    const int n_light = __popc(want_light), n_grow = __popc(want_grow), n_eye = __popc(want_eye),
-              n_connect = __popc(want_connect);
     int step = kBdptGrow, best = n_grow;
     if (n_connect > best) { step = kBdptConnect; best = n_connect; }
     if (n_eye > best) { step = kBdptStartEye; best = n_eye; }
@@ -566,7 +604,7 @@ __global__ void __launch_bounds__(128, AMBER_BDPT_BLOCKS) bdpt_kernel(const Rend
         const int leader = __ffs(want_light) - 1;
         unsigned long long base = 0;
         if (static_cast<int>(lane) == leader)
-          base = atomicAdd(&args.ctl->cursor_bdpt, static_cast<unsigned long long>(n_light));
+          base = atomicAdd(&args.ctl->cursor_bdpt, static_cast<unsigned long long>(__popc(want_light)));
         base = __shfl_sync(want_light, base, leader);
         const unsigned long long pair = base + __popc(want_light & lane_lt);
         if (pair >= total_pairs) {
