@@ -36,8 +36,13 @@ struct SequentialRng {
     i = 0;
   }
   // out of line: next() has some 16 call sites in the subpath generator, a Philox block is ~90 instructions
-  __device__ __noinline__ void refill(uint32_t index) { block = philox4x32_10(key0, key1, pixel, sample, id, index); }
-  __device__ __noinline__ float next() {
+  // by value in and out: a member function called out of line would pin the whole generator in local memory
+  static __device__ __noinline__ uint4 philox_block(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t c2,
+                                                    uint32_t c3) {
+    return philox4x32_10(k0, k1, c0, c1, c2, c3);
+  }
+  __device__ __forceinline__ void refill(uint32_t index) { block = philox_block(key0, key1, pixel, sample, id, index); }
+  __device__ __forceinline__ float next() {
     const uint32_t k = i++;
     if ((k & 3u) == 0) refill(k >> 2);
     const uint32_t w = k & 3u;
@@ -153,7 +158,7 @@ __device__ __forceinline__ void refraction_terms(const MaterialDev& m, float3 n,
 // Material::BSDF (adjoint = false) / AdjointBSDF (true) for every material kind:
 // material_{lambertian,phong,specular}.cc (symmetric), material_refraction.cc,
 // material_diffuse_light.h:141-161 (0), material_eye.h:97-117 (kDiracDelta).
-__device__ __noinline__ float3 event_bsdf(const MaterialDev& m, float3 n, float3 wo, float3 wi, bool adjoint) {
+__device__ __noinline__ float3 event_bsdf(const MaterialDev m, float3 n, float3 wo, float3 wi, bool adjoint) {
   const float3 rho = v3(m.r, m.g, m.b);
   switch (m.kind) {
     case 0:
@@ -170,7 +175,7 @@ __device__ __noinline__ float3 event_bsdf(const MaterialDev& m, float3 n, float3
 }
 
 // Material::PDFLight (importance = false) / PDFImportance (true)
-__device__ __noinline__ float event_pdf(const MaterialDev& m, float3 n, float3 wo, float3 wi, bool importance) {
+__device__ __noinline__ float event_pdf(const MaterialDev m, float3 n, float3 wo, float3 wi, bool importance) {
   switch (m.kind) {
     case 0: return 1.0f / kPiF;  // material_lambertian.cc:51-59
     case 1: {                    // material_phong.cc:64-79
@@ -222,7 +227,7 @@ struct BdptCounters {
 
 // The leading event of a light subpath (LightSet::GenerateRay) / an eye subpath (Lens::GenerateRay): run
 // once per subpath, kept out of the generator's loop body (code size, see closest_lane).
-__device__ __noinline__ void bdpt_leading_light(const SceneView& scene, SequentialRng& rng, Ray& ray, float3& weight,
+__device__ __forceinline__ void bdpt_leading_light(const SceneView& scene, SequentialRng& rng, Ray& ray, float3& weight,
                                                 float3& normal, int32_t& object, float& bits) {
   int light_index;
   generate_light_ray(scene, rng, ray.o, ray.d, weight, &light_index);
@@ -231,7 +236,7 @@ __device__ __noinline__ void bdpt_leading_light(const SceneView& scene, Sequenti
   object = -3 - light_index;
   bits = event_bits(__float_as_int(__ldg(L + 4).w), kSurfaceLight);
 }
-__device__ __noinline__ void bdpt_leading_eye(uint32_t pixel, SequentialRng& rng, Ray& ray, float3& weight,
+__device__ __forceinline__ void bdpt_leading_eye(uint32_t pixel, SequentialRng& rng, Ray& ray, float3& weight,
                                               float3& normal, int32_t& object, float& bits) {
   const uint32_t width = c_camera.sensor.width;
   float w;
@@ -278,7 +283,7 @@ __device__ __forceinline__ void bdpt_begin_subpath(const RenderArgs& args, bool 
 // One iteration of the generators' loop: cast, append the event, Russian roulette.  Returns false when
 // the subpath is complete (miss, roulette, or `cap` events).
 template <class Accel>
-__device__ __noinline__ bool bdpt_grow_subpath(const SceneView& scene, const bool kImportance, SequentialRng& rng,
+__device__ __forceinline__ bool bdpt_grow_subpath(const SceneView& scene, const bool kImportance, SequentialRng& rng,
                                                int cap, BdptEvent* out, BdptSubpath& sp, BdptCounters& count) {
   if (sp.n >= cap) return false;
   const Ray ray = sp.ray;
@@ -356,7 +361,7 @@ __device__ __forceinline__ BdptContribution bdpt_connect_t0(const BdptEvent* le)
 
 // Connect, s >= 1 and t >= 1 (:938-1016).  le / ee are register copies of the two endpoints.
 template <class Accel>
-__device__ __noinline__ BdptContribution bdpt_connect(const SceneView& scene, const BdptEvent* le, const BdptEvent* ee,
+__device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene, const BdptEvent* le, const BdptEvent* ee,
                                                       BdptCounters& count) {
   BdptContribution c = empty_contribution();
   if (!le->leading() && le->surface() != kSurfaceDiffuse) return c;
@@ -422,7 +427,7 @@ __device__ __noinline__ BdptContribution bdpt_connect(const SceneView& scene, co
 // with p_light[last] = the lens's directional pdf and p_importance[0] = the light's (1/pi).  The
 // technique ratios are accumulated outward from technique s as running products; a technique is
 // disabled when it would connect at a specular interior event (:661-697).
-__device__ __noinline__ float bdpt_mis_weight(const SceneView& scene, const BdptEvent* L, int s, uint32_t spec_l,
+__device__ __forceinline__ float bdpt_mis_weight(const SceneView& scene, const BdptEvent* L, int s, uint32_t spec_l,
                                                  const BdptEvent* E, int t, uint32_t spec_e, const BdptContribution& c) {
   const int n = s + t + 1, last = s + t - 2;  // last edge index
   const float eye_pdf_area = c_camera.lens.p_area;
@@ -659,20 +664,18 @@ __global__ void __launch_bounds__(BdptLaunch<Accel>::kThreads, BdptLaunch<Accel>
         if (j < n_s0) {
           s = 0;
           t = t_max;
-          const BdptEvent ee = E[t_max - 1];
-          c = bdpt_connect_s0(args.scene, &ee);
+          c = bdpt_connect_s0(args.scene, &E[t_max - 1]);
         } else if (j < n_s0 + n_t0) {
           s = nth_set_bit(eye_l, j - n_s0) + 1;  // event index + 1
           t = 0;
-          const BdptEvent le = L[s - 1];
-          c = bdpt_connect_t0(&le);
+          c = bdpt_connect_t0(&L[s - 1]);
         } else {
           const int k = j - n_s0 - n_t0;
           s = nth_set_bit(s_set, k % n_s) + 1;
           t = nth_set_bit(t_set, k / n_s) + 1;
-          const BdptEvent le = L[s - 1];
-          const BdptEvent ee = E[t - 1];
-          c = bdpt_connect<Accel>(args.scene, &le, &ee, count);
+          // the endpoints are read in place: a copy would be made in local memory (the callee is out of
+          // line), 160 B loaded and stored again per candidate
+          c = bdpt_connect<Accel>(args.scene, &L[s - 1], &E[t - 1], count);
         }
         if (max3(c.value) > 0.0f) {
           const float weight = bdpt_mis_weight(args.scene, L, s, spec_l, E, t, spec_e, c);
