@@ -533,8 +533,10 @@ enum : int { kBdptStartLight = 0, kBdptGrow = 1, kBdptStartEye = 2, kBdptConnect
 template <class Accel>
 struct BdptLaunch {
   static constexpr bool kBlockVote = !Accel::kPersistent;
+  // list: one 512-thread block per SM at 123 registers (fewer spills and a smaller local-memory working
+  // set than two blocks at 64 registers: 436 -> 460 M/s); BVH: 8 blocks of 128 threads at 64 registers
   static constexpr int kThreads = kBlockVote ? 512 : 128;
-  static constexpr int kBlocks = kBlockVote ? 2 : 8;  // resident blocks per SM: 64 registers either way
+  static constexpr int kBlocks = kBlockVote ? 1 : 8;  // BVH at 4 / 5 / 6 blocks: 110 / 113 / 116 M/s against 122
 };
 template <class Accel>
 __global__ void __launch_bounds__(BdptLaunch<Accel>::kThreads, BdptLaunch<Accel>::kBlocks)
