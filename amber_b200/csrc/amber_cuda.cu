@@ -532,7 +532,6 @@ int amber_cuda_create(amber_cuda_ctx** out, int device) {
   ctx->id = g_next_ctx_id.fetch_add(1);
   ctx->device = device;
   cudaError_t err = cudaSetDevice(device);
-  if (const char* g = std::getenv("AMBER_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, std::atoi(g));
   if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (err == cudaSuccess) err = cudaEventCreate(&ctx->ev_begin);
   if (err == cudaSuccess) err = cudaEventCreate(&ctx->ev_end);
