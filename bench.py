@@ -314,8 +314,9 @@ def run_gpu(args) -> None:
             "kernel_share_of_step": {k: v / max(1e-9, sum(kernel_ms.values())) for k, v in kernel_ms.items()},
             "whole_wavefront": {"achieved": whole, "frac": whole / peak,
                                 "bytes_model": "160 B/closest ray + 108 B/shadow ray (SURVEY 8d)"},
-            "note": "the kernels are instruction-issue bound (scene in constant memory, exact-arithmetic "
-                    "shading); issue-slot utilisation per kernel is in profiles/",
+            "note": "shade is limited by DRAM bytes and instruction issue together (ncu, profiles/r01_r01h_summary.txt: "
+                    "593 MB of DRAM traffic per launch, 60 % of the issue slots; adding 93 MB of writes cost 29 us, "
+                    "DESIGN.md section 6); extend is issue bound (83 %), connect DRAM bound (65 % busy)",
         }
         traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(traffic_file):
