@@ -181,7 +181,7 @@ __device__ __noinline__ float event_pdf(const MaterialDev m, float3 n, float3 wo
     case 1: {                    // material_phong.cc:64-79
       const float3 refl = perfect_reflection(wo, n, dot(wo, n));
       const float cos_alpha = fmaxf(0.0f, dot(wi, refl));
-      return (m.param + 1.0f) / (2.0f * kPiF) * powf(cos_alpha, m.param) / fabsf(dot(wi, n));
+      return (m.param + 1.0f) / (2.0f * kPiF) * pow_scale_only(cos_alpha, m.param) / fabsf(dot(wi, n));
     }
     case 3: {
       float term, pdf;

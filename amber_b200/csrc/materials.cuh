@@ -157,6 +157,13 @@ __device__ __forceinline__ Scatter sample_light(const MaterialDev& m, float3 n, 
   return s;
 }
 
+// x^y for a value that only scales a contribution (the Phong lobe in BSDF / pdf evaluation): exp2(y log2 x)
+// on the MUFU unit, ~6 instructions against ~150 for powf; relative error ~4e-5 at y = 256.  Sampled
+// DIRECTIONS keep powf (sample_light): they decide where the path goes.
+__device__ __forceinline__ float pow_scale_only(float x, float y) {
+  return x > 0.0f ? exp2f(y * __log2f(x)) : (y == 0.0f ? 1.0f : 0.0f);
+}
+
 // Material::BSDF for the connectable (SurfaceType::Diffuse) materials, w.r.t.
 // projected solid angle.  Lambertian: material_lambertian.cc:34-49;
 // Phong: material_phong.cc:39-61.  Others return 0 (never connected,
@@ -170,7 +177,7 @@ __device__ __forceinline__ float3 bsdf_eval(const MaterialDev& m, float3 n, floa
   if (m.kind == 1) {
     const float3 refl = perfect_reflection(wi, n, cos_i);
     const float cos_alpha = fmaxf(0.0f, dot(refl, wo));
-    return ((m.param + 2.0f) / (2.0f * kPiF) * powf(cos_alpha, m.param)) * rho;
+    return ((m.param + 2.0f) / (2.0f * kPiF) * pow_scale_only(cos_alpha, m.param)) * rho;
   }
   return v3(0.0f, 0.0f, 0.0f);
 }
