@@ -219,6 +219,33 @@ def test_accumulation_is_independent_of_batching_and_pool_size(cornell_device):
         assert np.allclose(other, whole, rtol=1e-4, atol=1e-7 * whole.mean())
 
 
+@pytest.mark.parametrize("size", [(1, 1), (37, 19), (5, 131)])
+def test_ragged_frames_and_pools(cornell_device, size):
+    """Frame sizes and pools that are no multiple of anything (a 1 x 1 frame, pools below one shade tile
+    and off its boundary), every estimator: exactly W * H * spp paths, a finite image, and -- for the
+    wavefront estimators -- the image of the default pool.  A render of zero samples is a no-op."""
+    from amber_b200 import Sensor, capi
+    w, h = size
+    cornell_device.set_sensor(Sensor(w, h))
+    spp = 6
+    for estimator, depth in ((capi.ESTIMATOR_REFERENCE, 12), (capi.ESTIMATOR_NEE, 12),
+                             (capi.ESTIMATOR_LIGHT_TRACING, 12), (capi.ESTIMATOR_BDPT, 0)):
+        images = []
+        for pool in (0, 300, 777):
+            cornell_device.film_clear()
+            before = cornell_device.stats()["paths"]
+            cornell_device.render(0, 0, seed=5, max_depth=depth, estimator=estimator, pool_paths=pool)
+            cornell_device.render(2, spp, seed=5, max_depth=depth, estimator=estimator, pool_paths=pool)
+            image, done = cornell_device.resolve()
+            assert done == spp
+            assert cornell_device.stats()["paths"] - before == w * h * spp
+            assert image.shape == (h, w, 3) and np.isfinite(image).all() and (image >= 0).all()
+            images.append(image)
+        if estimator != capi.ESTIMATOR_LIGHT_TRACING:  # its splats land in float atomics in any order
+            for other in images[1:]:
+                assert np.allclose(other, images[0], rtol=1e-4, atol=1e-6 * max(images[0].mean(), 1e-6))
+
+
 def test_algorithm_interface_mirrors_the_reference(cornell, oracle):
     """Render(scene, sensor, context): one Iterate() = one sample per pixel; expiry ends early."""
     from amber_b200 import Context, CudaPathTracing, Sensor
