@@ -13,7 +13,8 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libamber_cuda.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
+SAMPLES_IN_FILM = 0xFFFFFFFFFFFFFFFF
 
 PRIM_TRIANGLE, PRIM_SPHERE = 0, 1
 MAT_LAMBERTIAN, MAT_PHONG, MAT_SPECULAR, MAT_REFRACTION, MAT_DIFFUSE_LIGHT, MAT_EYE = range(6)
@@ -30,6 +31,11 @@ SYMBOLS = (
     "amber_cuda_set_sensor",
     "amber_cuda_film_clear",
     "amber_cuda_render",
+    "amber_cuda_render_async",
+    "amber_cuda_wait",
+    "amber_cuda_pending",
+    "amber_cuda_wait_pending",
+    "amber_cuda_film_reduce",
     "amber_cuda_resolve",
     "amber_cuda_resolve_ldr",
     "amber_cuda_film_device",
@@ -85,6 +91,10 @@ class RenderParams(C.Structure):
         ("seed", C.c_uint64),
         ("estimator", C.c_int32),
         ("pool_paths", C.c_uint32),
+        ("pixel_begin", C.c_uint32),
+        ("pixel_count", C.c_uint32),
+        ("sample_stride", C.c_uint32),
+        ("reserved", C.c_uint32),
     ]
 
 
@@ -105,6 +115,15 @@ class Stats(C.Structure):
         ("accel", C.c_uint32),
         ("bvh_nodes", C.c_uint32),
         ("light_splats", C.c_uint64),
+        ("bvh_node_visits", C.c_uint64),
+        ("bvh_triangle_tests", C.c_uint64),
+        ("bvh_node_visits_connect", C.c_uint64),
+        ("bvh_triangle_tests_connect", C.c_uint64),
+        ("bvh_node_bytes", C.c_uint32),
+        ("bvh_triangle_bytes", C.c_uint32),
+        ("chained_renders", C.c_uint64),
+        ("scene_build_ms", C.c_double),
+        ("scene_upload_ms", C.c_double),
     ]
 
 
@@ -139,6 +158,11 @@ def load(path: str | None = None) -> C.CDLL:
         "amber_cuda_set_sensor": [vp, u32, u32, C.c_float, C.c_float],
         "amber_cuda_film_clear": [vp],
         "amber_cuda_render": [vp, C.POINTER(RenderParams)],
+        "amber_cuda_render_async": [vp, C.POINTER(RenderParams)],
+        "amber_cuda_wait": [vp],
+        "amber_cuda_pending": [vp],
+        "amber_cuda_wait_pending": [vp, C.c_int],
+        "amber_cuda_film_reduce": [C.POINTER(vp), C.c_int],
         "amber_cuda_resolve": [vp, vp, C.POINTER(u64)],
         "amber_cuda_resolve_ldr": [vp, vp, C.c_int, C.POINTER(u64)],
         "amber_cuda_film_device": [vp, C.POINTER(vp), C.POINTER(u64), C.POINTER(u64)],

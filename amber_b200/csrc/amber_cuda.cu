@@ -5,12 +5,17 @@
 // it replaces; everything per-ray runs in the kernels of kernels.cuh.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
+#include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -27,8 +32,13 @@ namespace detail {
 
 thread_local std::string g_create_error;
 std::atomic<uint64_t> g_next_ctx_id{1};
+constexpr int kMaxDevices = 64;
 // which context's data currently sits in this device's __constant__ banks
-std::atomic<uint64_t> g_const_owner[64];
+std::atomic<uint64_t> g_const_owner[kMaxDevices];
+// The scene and the camera of a context live in process-wide __constant__ symbols while its kernels
+// run, so contexts that share a device take turns: this lock is held from bind_constants to the last
+// synchronisation of a render job or parity call (DeviceTurn below).
+std::mutex g_device_turn[kMaxDevices];
 
 template <class T>
 struct DeviceBuffer {
@@ -91,11 +101,14 @@ struct amber_cuda_ctx {
   unsigned int bvh_grid = 0;       // persistent grid: SMs * resident blocks
   size_t bvh_smem = 0;
 
-  // film
+  // film: W*H float4 sums + one trailing float4 that carries the sample count across an external
+  // all-reduce (amber_cuda_film_device)
   DeviceBuffer<float4> d_film;
   DeviceBuffer<float> d_resolved;
   DeviceBuffer<uint8_t> d_resolved8;
   uint64_t samples_done = 0;
+  bool samples_in_film = false;  // the trailing element is authoritative (after an external reduce)
+  float4* h_tail = nullptr;      // pinned staging for that element
 
   // path pool
   PathPool pool{};
@@ -113,6 +126,19 @@ struct amber_cuda_ctx {
   // statistics
   amber_cuda_stats stats{};
   bool profiling = false;
+
+  // render queue: amber_cuda_render_async hands jobs to this context's worker thread
+  std::thread worker;
+  std::mutex queue_mutex;
+  std::condition_variable queue_cv, idle_cv;
+  std::deque<amber_cuda_render_params> jobs;
+  int running = 0;    // calls taken by the worker whose paths have not all been started yet
+  bool busy = false;  // the worker is inside a render (its wavefront may still be draining)
+  bool jobs_may_follow = false;
+  std::deque<uint64_t> absorbed_ends;  // end ordinal (samples per pixel) of each call in the running wavefront
+  bool quit = false;
+  int job_rc = AMBER_CUDA_OK;  // first failure of the queue, reported by the next wait
+  std::string job_error;
 };
 
 namespace amber_host {
@@ -134,6 +160,17 @@ int fail(amber_cuda_ctx* ctx, int code, const char* fmt, ...) {
       return fail(ctx, AMBER_CUDA_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(err__), \
                   __FILE__, __LINE__);                                                        \
   } while (0)
+
+// Holds a device's turn (see g_device_turn) for the length of a scope.
+struct DeviceTurn {
+  std::unique_lock<std::mutex> lock;
+  explicit DeviceTurn(const amber_cuda_ctx* ctx) {
+    if (ctx->device >= 0 && ctx->device < kMaxDevices) lock = std::unique_lock<std::mutex>(g_device_turn[ctx->device]);
+  }
+};
+
+void worker_main(amber_cuda_ctx* ctx);
+int wait_idle(amber_cuda_ctx* ctx, int max_pending = 0);
 
 inline unsigned int blocks_for(uint64_t n, int block = kBlock) {
   return static_cast<unsigned int>((n + block - 1) / block);
@@ -491,10 +528,15 @@ int configure_bvh_launch(amber_cuda_ctx* ctx, const bvh_build::WideBvhHost& bvh)
   CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, ctx->device));
   const void* kernels[] = {reinterpret_cast<const void*>(&extend_kernel<WideBvh>),
                            reinterpret_cast<const void*>(&connect_kernel<WideBvh>),
-                           reinterpret_cast<const void*>(&cast_bvh_kernel)};
+                           reinterpret_cast<const void*>(&cast_bvh_kernel),
+                           reinterpret_cast<const void*>(&extend_bvh_counting_kernel),
+                           reinterpret_cast<const void*>(&connect_bvh_counting_kernel)};
   int resident = 1 << 30;
   for (const void* k : kernels) {
-    CUDA_TRY(ctx, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ctx->bvh_smem)));
+    // the limit is per function and process-wide: always the maximum, so that a later upload of a shallower
+    // tree in another context cannot lower it under a launch of this one
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       static_cast<int>(kBvhStackMax * kBlock * sizeof(int32_t))));
     int blocks = 0;
     CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, k, kBlock, ctx->bvh_smem));
     resident = std::min(resident, blocks);
@@ -536,19 +578,30 @@ int amber_cuda_create(amber_cuda_ctx** out, int device) {
   if (err == cudaSuccess) err = cudaEventCreate(&ctx->ev_begin);
   if (err == cudaSuccess) err = cudaEventCreate(&ctx->ev_end);
   if (err == cudaSuccess) err = cudaMallocHost(&ctx->h_ctl, 2 * sizeof(Control));  // two poll slots
+  if (err == cudaSuccess) err = cudaMallocHost(&ctx->h_tail, sizeof(float4));
   if (err == cudaSuccess) err = ctx->d_ctl.resize(1);
   if (err == cudaSuccess) err = cudaMemsetAsync(ctx->d_ctl.ptr, 0, sizeof(Control), ctx->stream);
   if (err != cudaSuccess) {
     fail(nullptr, AMBER_CUDA_ECUDA, "context creation failed: %s", cudaGetErrorString(err));
+    if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
+    if (ctx->h_tail) cudaFreeHost(ctx->h_tail);
     delete ctx;
     return AMBER_CUDA_ECUDA;
   }
+  ctx->worker = std::thread(worker_main, ctx);
   *out = ctx;
   return AMBER_CUDA_OK;
 }
 
 int amber_cuda_destroy(amber_cuda_ctx* ctx) {
   if (!ctx) return AMBER_CUDA_OK;
+  wait_idle(ctx);
+  {
+    std::lock_guard<std::mutex> guard(ctx->queue_mutex);
+    ctx->quit = true;
+  }
+  ctx->queue_cv.notify_all();
+  if (ctx->worker.joinable()) ctx->worker.join();
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   invalidate_constants(ctx);
@@ -562,6 +615,7 @@ int amber_cuda_destroy(amber_cuda_ctx* ctx) {
   for (auto& b : ctx->d_scratch_i) b.release();
   for (auto& b : ctx->d_scratch_4) b.release();
   if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
+  if (ctx->h_tail) cudaFreeHost(ctx->h_tail);
   if (ctx->ev_begin) cudaEventDestroy(ctx->ev_begin);
   if (ctx->ev_end) cudaEventDestroy(ctx->ev_end);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -573,7 +627,9 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   if (!ctx) return AMBER_CUDA_EINVAL;
   if (!scene || (scene->n_primitives && !scene->primitives) || !scene->materials || scene->n_materials == 0)
     return fail(ctx, AMBER_CUDA_EINVAL, "scene description is incomplete");
+  wait_idle(ctx);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const auto build_t0 = std::chrono::steady_clock::now();
 
   // ---- materials ---------------------------------------------------------------
   std::vector<MaterialDev> materials(scene->n_materials);
@@ -705,6 +761,11 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   if (lens_rc != AMBER_CUDA_OK) return lens_rc;
 
   // ---- commit ------------------------------------------------------------------
+  // from here on the context's scene is in flux: it counts as "no scene" until the last fallible call
+  // has succeeded, so a failed upload can never leave new constants next to old device pointers
+  const auto upload_t0 = std::chrono::steady_clock::now();
+  ctx->has_scene = false;
+  ctx->view = SceneView{};
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   invalidate_constants(ctx);
   ctx->use_bvh = use_bvh;
@@ -783,6 +844,9 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
     const int rc = configure_bvh_launch(ctx, bvh);
     if (rc != AMBER_CUDA_OK) return rc;
   }
+  const auto upload_t1 = std::chrono::steady_clock::now();
+  ctx->stats.scene_build_ms = std::chrono::duration<double, std::milli>(upload_t0 - build_t0).count();
+  ctx->stats.scene_upload_ms = std::chrono::duration<double, std::milli>(upload_t1 - upload_t0).count();
   ctx->has_scene = true;
   return AMBER_CUDA_OK;
 }
@@ -794,6 +858,7 @@ int amber_cuda_set_sensor(amber_cuda_ctx* ctx, uint32_t width, uint32_t height, 
     return fail(ctx, AMBER_CUDA_EINVAL, "bad sensor %ux%u, film %g x %g", width, height, film_width, film_height);
   if (static_cast<uint64_t>(width) * height >= (1ull << 31))
     return fail(ctx, AMBER_CUDA_EINVAL, "sensor too large");
+  wait_idle(ctx);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   invalidate_constants(ctx);
@@ -806,15 +871,17 @@ int amber_cuda_set_sensor(amber_cuda_ctx* ctx, uint32_t width, uint32_t height, 
   s.size_over_area = static_cast<float>(static_cast<uint64_t>(width) * height) / (film_width * film_height);
   s.inv_area = 1 / (film_width * film_height);
   ctx->has_sensor = true;
-  CUDA_TRY(ctx, ctx->d_film.resize(static_cast<size_t>(width) * height));
+  CUDA_TRY(ctx, ctx->d_film.resize(static_cast<size_t>(width) * height + 1));  // + the sample-count element
   return amber_cuda_film_clear(ctx);
 }
 
 int amber_cuda_film_clear(amber_cuda_ctx* ctx) {
   if (!ctx) return AMBER_CUDA_EINVAL;
   if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
+  wait_idle(ctx);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  const size_t n = static_cast<size_t>(ctx->camera.sensor.width) * ctx->camera.sensor.height;
+  const size_t n = static_cast<size_t>(ctx->camera.sensor.width) * ctx->camera.sensor.height + 1;
+  ctx->samples_in_film = false;
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_film.ptr, 0, n * sizeof(float4), ctx->stream));
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_ctl.ptr, 0, sizeof(Control), ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
@@ -837,10 +904,18 @@ __global__ void control_begin_kernel(Control* ctl, unsigned long long total_path
   ctl->n_shadow = 0;
   ctl->n_alive = 0;
   ctl->done = 0;
+  for (int k = 0; k < 4; k++) ctl->bvh_work[k] = 0;
+}
+
+// A queued render call that continues the running one is absorbed into its wavefront: more paths to
+// start, nothing else changes.  `done` is cleared, so a poll copy taken after this kernel is current.
+__global__ void control_extend_kernel(Control* ctl, unsigned long long more_paths) {
+  ctl->total_paths += more_paths;
+  ctl->done = 0;
 }
 
 constexpr int kStepsPerPoll = 8;
-// 8 waves of 1024-slot windows at 4 per SM on 148 SMs
+// sixteen waves of shade's 512-slot tiles at 8 resident blocks per SM on 148 SMs
 constexpr uint32_t kDefaultPoolPaths = 148u * 4u * 1024u * 8u;
 
 struct KernelTimer {
@@ -861,8 +936,26 @@ struct KernelTimer {
   }
 };
 
+void launch_extend_counting(const RenderArgs& args, unsigned int grid, size_t smem, cudaStream_t stream) {
+  extend_bvh_counting_kernel<<<grid, kBlock, smem, stream>>>(args);
+}
+void launch_connect_counting(const RenderArgs& args, unsigned int grid, size_t smem, cudaStream_t stream) {
+  connect_bvh_counting_kernel<<<grid, kBlock, smem, stream>>>(args);
+}
+
+uint32_t effective_stride(const amber_cuda_render_params& p) { return p.sample_stride ? p.sample_stride : 1u; }
+
+// Does `next` continue `current` (the call whose wavefront is running, which ends at ordinal `ordinals_done`)?
+bool continues(const amber_cuda_render_params& current, uint64_t ordinals_done, const amber_cuda_render_params& next) {
+  return next.estimator == current.estimator && next.seed == current.seed && next.max_depth == current.max_depth &&
+         next.pool_paths == current.pool_paths && next.pixel_begin == current.pixel_begin &&
+         next.pixel_count == current.pixel_count && effective_stride(next) == effective_stride(current) &&
+         next.sample_begin == current.sample_begin + ordinals_done * effective_stride(current) && next.sample_count > 0;
+}
+
 template <class Accel>
-int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dynamic_smem) {
+int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, const amber_cuda_render_params& first, bool nee,
+                size_t dynamic_smem, uint64_t* ordinals_rendered) {
   const unsigned int grid = blocks_for(args.pool.n_slots);
   const unsigned int shade_grid = blocks_for(args.pool.n_slots, kShadeTile);
   const unsigned int trace_grid = Accel::kPersistent ? ctx->bvh_grid : grid;
@@ -889,12 +982,34 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
     }
   };
   cudaEvent_t poll_event[2];
-  Control* poll_copy = ctx->h_ctl;  // pinned, two slots are overkill: reads happen after the event
+  Control* poll_copy = ctx->h_ctl;  // pinned, one slot per poll in flight
   CUDA_TRY(ctx, cudaEventCreateWithFlags(&poll_event[0], cudaEventDisableTiming));
   CUDA_TRY(ctx, cudaEventCreateWithFlags(&poll_event[1], cudaEventDisableTiming));
   int rc = AMBER_CUDA_OK;
   bool done = false;
+  uint64_t ordinals = first.sample_count;  // samples per pixel this wavefront has been asked for so far
+  int polls_valid_from = 0;                // poll copies of earlier batches predate the last extension
   for (int batch = 0; !done; batch++) {
+    // absorb queued calls that continue this one: the pool keeps running instead of draining
+    for (;;) {
+      uint64_t more = 0;
+      {
+        std::lock_guard<std::mutex> guard(ctx->queue_mutex);
+        if (!ctx->jobs.empty() && continues(first, ordinals, ctx->jobs.front()) &&
+            first.sample_begin + (ordinals + ctx->jobs.front().sample_count) * effective_stride(first) < (1ull << 32)) {
+          more = ctx->jobs.front().sample_count;
+          ctx->jobs.pop_front();
+          ctx->running++;
+          ctx->absorbed_ends.push_back(ordinals + more);
+        }
+      }
+      if (more == 0) break;
+      control_extend_kernel<<<1, 1, 0, stream>>>(args.ctl, more * args.n_pixels);
+      ctx->stats.kernel_launches++;
+      ctx->stats.chained_renders++;
+      ordinals += more;
+      polls_valid_from = batch;
+    }
     for (int step = 0; step < kStepsPerPoll; step++) {
       timed(0, [&] {
         const unsigned int raygen_grid = AMBER_RAYGEN_LOOP ? std::min<unsigned int>(grid, static_cast<unsigned int>(sm_count) * AMBER_RAYGEN_BLOCKS) : grid;
@@ -902,23 +1017,44 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
         else raygen_kernel<false><<<raygen_grid, kBlock, 0, stream>>>(args);
       });
       bookkeep_kernel<<<1, 1, 0, stream>>>(args.ctl);
-      timed(1, [&] { extend_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args); });
+      timed(1, [&] {
+        if (profile && Accel::kPersistent) launch_extend_counting(args, trace_grid, dynamic_smem, stream);
+        else extend_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args);
+      });
       timed(2, [&] {
         if (light_tracing) shade_kernel<true><<<shade_grid, kShadeBlock, 0, stream>>>(args);
         else shade_kernel<false><<<shade_grid, kShadeBlock, 0, stream>>>(args);
       });
-      if (nee) timed(3, [&] { connect_kernel<Accel><<<connect_grid, kBlock, dynamic_smem, stream>>>(args); });
+      if (nee) timed(3, [&] {
+        if (profile && Accel::kPersistent) launch_connect_counting(args, connect_grid, dynamic_smem, stream);
+        else connect_kernel<Accel><<<connect_grid, kBlock, dynamic_smem, stream>>>(args);
+      });
       ctx->stats.kernel_launches += nee ? 5 : 4;
       extend_launches++;
     }
     // poll: the copy of batch b is read while batch b+1 is already queued
     if (batch > 0) {
-      const cudaError_t err = cudaEventSynchronize(poll_event[(batch - 1) & 1]);
+      cudaError_t err = cudaEventSynchronize(poll_event[(batch - 1) & 1]);
+      if (err == cudaSuccess) err = cudaGetLastError();  // launch failures surface here, once per poll
       if (err != cudaSuccess) {
         rc = fail(ctx, AMBER_CUDA_ECUDA, "render failed: %s", cudaGetErrorString(err));
         break;
       }
-      if (poll_copy[(batch - 1) & 1].done) done = true;
+      const Control& seen = poll_copy[(batch - 1) & 1];
+      if (seen.done && batch - 1 >= polls_valid_from) done = true;
+      // calls whose paths have all been started no longer count as pending (amber_cuda_wait_pending):
+      // the caller may queue the next one while this wavefront is still full
+      bool released = false;
+      {
+        std::lock_guard<std::mutex> guard(ctx->queue_mutex);
+        const uint64_t started = seen.next_path / args.n_pixels;
+        while (!ctx->absorbed_ends.empty() && ctx->absorbed_ends.front() <= started) {
+          ctx->absorbed_ends.pop_front();
+          ctx->running--;
+          released = true;
+        }
+      }
+      if (released) ctx->idle_cv.notify_all();
     }
     if (!done) {
       cudaMemcpyAsync(&poll_copy[batch & 1], args.ctl, sizeof(Control), cudaMemcpyDeviceToHost, stream);
@@ -927,6 +1063,7 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
   }
   cudaEventDestroy(poll_event[0]);
   cudaEventDestroy(poll_event[1]);
+  *ordinals_rendered = ordinals;
   if (rc != AMBER_CUDA_OK) return rc;
   CUDA_TRY(ctx, cudaStreamSynchronize(stream));
   if (profile) {
@@ -944,10 +1081,6 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, bool nee, size_t dy
   return AMBER_CUDA_OK;
 }
 
-
-}  // namespace amber_host
-namespace amber_host {
-
 // Bidirectional path tracing (bdpt.cuh): one kernel, one thread per (pixel, sample).
 int render_bdpt(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, uint32_t n_pixels, uint64_t total_pairs) {
   int rc = bind_constants(ctx);
@@ -958,6 +1091,7 @@ int render_bdpt(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, uin
   args.film = ctx->d_film.ptr;
   args.seed = params->seed;
   args.sample_begin = params->sample_begin;
+  args.sample_stride = effective_stride(*params);
   args.n_pixels = n_pixels;
   args.estimator = params->estimator;
   args.inv_n_pixels = 1.0f / static_cast<float>(n_pixels);
@@ -991,14 +1125,8 @@ int render_bdpt(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, uin
   return AMBER_CUDA_OK;
 }
 
-}  // namespace amber_host
-
-using namespace amber_host;
-
-extern "C" {
-
-int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* params) {
-  if (!ctx) return AMBER_CUDA_EINVAL;
+// Argument checks of a render call: done on the caller's thread, so that a bad call fails at once.
+int validate_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* params) {
   if (!params) return fail(ctx, AMBER_CUDA_EINVAL, "params is NULL");
   if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
   if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
@@ -1008,24 +1136,48 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
   if (params->estimator == AMBER_CUDA_ESTIMATOR_BDPT && params->max_depth > static_cast<uint32_t>(kBdptMaxEvents))
     return fail(ctx, AMBER_CUDA_EINVAL, "bidirectional path tracing: max_depth (events per subpath) must be <= %d",
                 kBdptMaxEvents);
-  if (params->estimator == AMBER_CUDA_ESTIMATOR_LIGHT_TRACING || params->estimator == AMBER_CUDA_ESTIMATOR_BDPT) {
+  const bool from_lights = params->estimator == AMBER_CUDA_ESTIMATOR_LIGHT_TRACING || params->estimator == AMBER_CUDA_ESTIMATOR_BDPT;
+  if (from_lights) {
     // LightSet::GenerateRay on an empty set is undefined in the reference (light_set.h:87-92)
     if (ctx->view.n_lights == 0)
-      return fail(ctx, AMBER_CUDA_EINVAL, "light / bidirectional path tracing needs at least one emitting triangle");
-    if (ctx->has_sphere_light)
-      return fail(ctx, AMBER_CUDA_EINVAL,
-                  "light / bidirectional path tracing: emitting spheres are not supported (triangle emitters only)");
+      return fail(ctx, AMBER_CUDA_EINVAL, "light / bidirectional path tracing needs at least one emitter");
   }
-  if (params->sample_begin + params->sample_count >= (1ull << 32))
+  const uint64_t n_frame = static_cast<uint64_t>(ctx->camera.sensor.width) * ctx->camera.sensor.height;
+  if (params->pixel_count != 0) {
+    if (from_lights) return fail(ctx, AMBER_CUDA_EINVAL, "a pixel window needs a path tracing estimator");
+    if (static_cast<uint64_t>(params->pixel_begin) + params->pixel_count > n_frame)
+      return fail(ctx, AMBER_CUDA_EINVAL, "pixel window [%u, +%u) leaves the %llu-pixel frame", params->pixel_begin,
+                  params->pixel_count, static_cast<unsigned long long>(n_frame));
+  } else if (params->pixel_begin != 0) {
+    return fail(ctx, AMBER_CUDA_EINVAL, "pixel_begin without pixel_count");
+  }
+  if (params->sample_begin + static_cast<uint64_t>(params->sample_count) * effective_stride(*params) >= (1ull << 32))
     return fail(ctx, AMBER_CUDA_EINVAL, "sample indices must stay below 2^32");
+  return AMBER_CUDA_OK;
+}
+
+// One render call (and every queued call it absorbs) on the context's device; runs on the worker thread.
+int run_render(amber_cuda_ctx* ctx, const amber_cuda_render_params& job) {
+  const amber_cuda_render_params* params = &job;
   if (params->sample_count == 0) return AMBER_CUDA_OK;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  DeviceTurn turn(ctx);
+  if (ctx->samples_in_film) {  // an external reduce left the count in the film: take it back first
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_tail, ctx->d_film.ptr + ctx->camera.sensor.width * ctx->camera.sensor.height,
+                                  sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->samples_done = static_cast<uint64_t>(ctx->h_tail->x) + (static_cast<uint64_t>(ctx->h_tail->y) << 16) +
+                        (static_cast<uint64_t>(ctx->h_tail->z) << 32);
+    ctx->samples_in_film = false;
+  }
 
-  const uint32_t n_pixels = ctx->camera.sensor.width * ctx->camera.sensor.height;
+  const uint32_t n_frame = ctx->camera.sensor.width * ctx->camera.sensor.height;
+  const uint32_t n_pixels = params->pixel_count ? params->pixel_count : n_frame;
   const uint64_t total_paths = static_cast<uint64_t>(n_pixels) * params->sample_count;
   if (params->estimator == AMBER_CUDA_ESTIMATOR_BDPT) return render_bdpt(ctx, params, n_pixels, total_paths);
   uint64_t slots = params->pool_paths ? params->pool_paths : kDefaultPoolPaths;
-  slots = std::min<uint64_t>(slots, total_paths);
+  // a queue of small calls renders as ONE wavefront: then the pool is sized for it, not for the first call
+  if (!ctx->jobs_may_follow) slots = std::min<uint64_t>(slots, total_paths);
   slots = std::max<uint64_t>(kBlock, (slots + kBlock - 1) / kBlock * kBlock);
   int rc = ensure_pool(ctx, static_cast<uint32_t>(slots));
   if (rc != AMBER_CUDA_OK) return rc;
@@ -1039,10 +1191,12 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
   args.film = ctx->d_film.ptr;
   args.seed = params->seed;
   args.sample_begin = params->sample_begin;
+  args.sample_stride = effective_stride(*params);
   args.n_pixels = n_pixels;
+  args.pixel_begin = params->pixel_begin;
   args.max_depth = params->max_depth ? std::min<uint32_t>(params->max_depth, 1u << 16) : (1u << 16);
   args.estimator = params->estimator;
-  args.inv_n_pixels = 1.0f / static_cast<float>(n_pixels);
+  args.inv_n_pixels = 1.0f / static_cast<float>(n_frame);
 
   cudaStream_t stream = ctx->stream;
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev_begin, stream));
@@ -1050,10 +1204,11 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
   pool_reset_kernel<<<blocks_for(args.pool.n_slots), kBlock, 0, stream>>>(args);
   ctx->stats.kernel_launches += 2;
   const bool nee = params->estimator == AMBER_CUDA_ESTIMATOR_NEE && ctx->view.n_lights > 0;
+  uint64_t ordinals = 0;
   if (ctx->use_bvh) {
-    rc = render_loop<WideBvh>(ctx, args, nee, ctx->bvh_smem);
+    rc = render_loop<WideBvh>(ctx, args, *params, nee, ctx->bvh_smem, &ordinals);
   } else {
-    rc = render_loop<ConstList>(ctx, args, nee, 0);
+    rc = render_loop<ConstList>(ctx, args, *params, nee, 0, &ordinals);
   }
   if (rc != AMBER_CUDA_OK) return rc;
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev_end, stream));
@@ -1062,25 +1217,145 @@ int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* param
   float ms = 0;
   CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
   ctx->stats.last_render_ms = ms;
-  ctx->samples_done += params->sample_count;
+  ctx->samples_done += ordinals;
   return AMBER_CUDA_OK;
+}
+
+void worker_main(amber_cuda_ctx* ctx) {
+  for (;;) {
+    amber_cuda_render_params job;
+    {
+      std::unique_lock<std::mutex> lock(ctx->queue_mutex);
+      ctx->queue_cv.wait(lock, [&] { return ctx->quit || !ctx->jobs.empty(); });
+      if (ctx->jobs.empty()) return;  // quit
+      job = ctx->jobs.front();
+      ctx->jobs.pop_front();
+      ctx->running = 1;
+      ctx->busy = true;
+      ctx->absorbed_ends.assign(1, job.sample_count);
+      ctx->jobs_may_follow = !ctx->jobs.empty();
+    }
+    int rc = AMBER_CUDA_OK;
+    {
+      std::lock_guard<std::mutex> guard(ctx->queue_mutex);
+      rc = ctx->job_rc;
+    }
+    if (rc == AMBER_CUDA_OK) rc = run_render(ctx, job);  // after a failure the rest of the queue is dropped
+    {
+      std::lock_guard<std::mutex> guard(ctx->queue_mutex);
+      if (rc != AMBER_CUDA_OK && ctx->job_rc == AMBER_CUDA_OK) {
+        ctx->job_rc = rc;
+        ctx->job_error = ctx->error;
+      }
+      ctx->running = 0;
+      ctx->busy = false;
+      ctx->absorbed_ends.clear();
+    }
+    ctx->idle_cv.notify_all();
+  }
+}
+
+// Every entry point but render_async / pending starts here: the queue is drained first.
+int wait_idle(amber_cuda_ctx* ctx, int max_pending) {
+  std::unique_lock<std::mutex> lock(ctx->queue_mutex);
+  if (max_pending > 0) {
+    ctx->idle_cv.wait(lock, [&] { return static_cast<int>(ctx->jobs.size()) + ctx->running <= max_pending; });
+  } else {
+    ctx->idle_cv.wait(lock, [&] { return ctx->jobs.empty() && !ctx->busy; });
+  }
+  return AMBER_CUDA_OK;
+}
+
+// The film's sample count after the work queued on the stream: the host's, or (after an external
+// reduce) the one carried by the film's trailing element.  Synchronises the stream.
+int film_sample_count(amber_cuda_ctx* ctx, uint64_t* samples_done) {
+  if (ctx->samples_in_film) {
+    const size_t n_pixels = static_cast<size_t>(ctx->camera.sensor.width) * ctx->camera.sensor.height;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_tail, ctx->d_film.ptr + n_pixels, sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (ctx->samples_in_film)
+    ctx->samples_done = static_cast<uint64_t>(ctx->h_tail->x) + (static_cast<uint64_t>(ctx->h_tail->y) << 16) +
+                        (static_cast<uint64_t>(ctx->h_tail->z) << 32);
+  if (samples_done) *samples_done = ctx->samples_done;
+  return AMBER_CUDA_OK;
+}
+
+}  // namespace amber_host
+
+using namespace amber_host;
+
+extern "C" {
+
+int amber_cuda_render_async(amber_cuda_ctx* ctx, const amber_cuda_render_params* params) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  {
+    // scene and sensor only change while the queue is idle (upload_scene / set_sensor wait), so the
+    // checks below see the state the job will run with
+    std::lock_guard<std::mutex> guard(ctx->queue_mutex);
+    if (ctx->job_rc != AMBER_CUDA_OK) {
+      ctx->error = ctx->job_error;
+      return ctx->job_rc;  // sticky until amber_cuda_wait reports it
+    }
+  }
+  const int rc = validate_render(ctx, params);
+  if (rc != AMBER_CUDA_OK) return rc;
+  if (params->sample_count == 0) return AMBER_CUDA_OK;
+  {
+    std::lock_guard<std::mutex> guard(ctx->queue_mutex);
+    ctx->jobs.push_back(*params);
+  }
+  ctx->queue_cv.notify_one();
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_wait(amber_cuda_ctx* ctx) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  wait_idle(ctx);
+  std::lock_guard<std::mutex> guard(ctx->queue_mutex);
+  const int rc = ctx->job_rc;
+  if (rc != AMBER_CUDA_OK) ctx->error = ctx->job_error;
+  ctx->job_rc = AMBER_CUDA_OK;
+  return rc;
+}
+
+int amber_cuda_pending(amber_cuda_ctx* ctx) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  std::lock_guard<std::mutex> guard(ctx->queue_mutex);
+  return static_cast<int>(ctx->jobs.size()) + ctx->running;
+}
+
+int amber_cuda_wait_pending(amber_cuda_ctx* ctx, int max_pending) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (max_pending <= 0) return amber_cuda_wait(ctx);
+  wait_idle(ctx, max_pending);
+  return AMBER_CUDA_OK;
+}
+
+int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* params) {
+  const int rc = amber_cuda_render_async(ctx, params);
+  if (rc != AMBER_CUDA_OK) return rc;
+  return amber_cuda_wait(ctx);
 }
 
 int amber_cuda_resolve(amber_cuda_ctx* ctx, float* host_rgb, uint64_t* samples_done) {
   if (!ctx) return AMBER_CUDA_EINVAL;
   if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
   if (!host_rgb) return fail(ctx, AMBER_CUDA_EINVAL, "host_rgb is NULL");
+  const int wait_rc = amber_cuda_wait(ctx);
+  if (wait_rc != AMBER_CUDA_OK) return wait_rc;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   const uint32_t n_pixels = ctx->camera.sensor.width * ctx->camera.sensor.height;
   CUDA_TRY(ctx, ctx->d_resolved.resize(static_cast<size_t>(n_pixels) * 3));
   const float inv = ctx->samples_done ? 1.0f / static_cast<float>(ctx->samples_done) : 0.0f;
   resolve_kernel<<<blocks_for(n_pixels), kBlock, 0, ctx->stream>>>(ctx->d_film.ptr, n_pixels, inv,
-                                                                  ctx->d_resolved.ptr);
+                                                                  ctx->samples_in_film ? 1 : 0, ctx->d_resolved.ptr);
   ctx->stats.kernel_launches++;
   CUDA_TRY(ctx, cudaMemcpyAsync(host_rgb, ctx->d_resolved.ptr, static_cast<size_t>(n_pixels) * 3 * sizeof(float),
                                 cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  if (samples_done) *samples_done = ctx->samples_done;
+  const int count_rc = film_sample_count(ctx, samples_done);  // synchronises the stream
+  if (count_rc != AMBER_CUDA_OK) return count_rc;
+  CUDA_TRY(ctx, cudaGetLastError());
   return AMBER_CUDA_OK;
 }
 
@@ -1088,43 +1363,125 @@ int amber_cuda_resolve_ldr(amber_cuda_ctx* ctx, uint8_t* host_rgb8, int flip_x, 
   if (!ctx) return AMBER_CUDA_EINVAL;
   if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
   if (!host_rgb8) return fail(ctx, AMBER_CUDA_EINVAL, "host_rgb8 is NULL");
+  const int wait_rc = amber_cuda_wait(ctx);
+  if (wait_rc != AMBER_CUDA_OK) return wait_rc;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   const uint32_t width = ctx->camera.sensor.width, height = ctx->camera.sensor.height;
   const size_t n_pixels = static_cast<size_t>(width) * height;
   CUDA_TRY(ctx, ctx->d_resolved8.resize(n_pixels * 3));
   const float inv = ctx->samples_done ? 1.0f / static_cast<float>(ctx->samples_done) : 0.0f;
   resolve_tonemap_kernel<<<blocks_for(n_pixels), kBlock, 0, ctx->stream>>>(ctx->d_film.ptr, width, height, inv,
-                                                                          flip_x ? 1 : 0, ctx->d_resolved8.ptr);
+                                                                          ctx->samples_in_film ? 1 : 0, flip_x ? 1 : 0,
+                                                                          ctx->d_resolved8.ptr);
   ctx->stats.kernel_launches++;
   CUDA_TRY(ctx, cudaMemcpyAsync(host_rgb8, ctx->d_resolved8.ptr, n_pixels * 3, cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  const int count_rc = film_sample_count(ctx, samples_done);  // synchronises the stream
+  if (count_rc != AMBER_CUDA_OK) return count_rc;
   CUDA_TRY(ctx, cudaGetLastError());
-  if (samples_done) *samples_done = ctx->samples_done;
   return AMBER_CUDA_OK;
 }
 
 int amber_cuda_film_device(amber_cuda_ctx* ctx, void** device_ptr, uint64_t* n_floats, uint64_t* samples_done) {
   if (!ctx) return AMBER_CUDA_EINVAL;
   if (!ctx->has_sensor) return fail(ctx, AMBER_CUDA_ESTATE, "set_sensor has not been called");
+  const int wait_rc = amber_cuda_wait(ctx);
+  if (wait_rc != AMBER_CUDA_OK) return wait_rc;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const size_t n_pixels = static_cast<size_t>(ctx->camera.sensor.width) * ctx->camera.sensor.height;
+  if (!ctx->samples_in_film) {  // publish the host's count in the trailing element: it travels with the film
+    *ctx->h_tail = make_float4(static_cast<float>(ctx->samples_done & 0xffffu), static_cast<float>((ctx->samples_done >> 16) & 0xffffu),
+                               static_cast<float>(ctx->samples_done >> 32), 0.0f);
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->d_film.ptr + n_pixels, ctx->h_tail, sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  }
   if (device_ptr) *device_ptr = ctx->d_film.ptr;
-  if (n_floats) *n_floats = static_cast<uint64_t>(ctx->camera.sensor.width) * ctx->camera.sensor.height * 4;
+  if (n_floats) *n_floats = static_cast<uint64_t>(n_pixels + 1) * 4;
   if (samples_done) *samples_done = ctx->samples_done;
   return AMBER_CUDA_OK;
 }
 
 int amber_cuda_film_set_samples(amber_cuda_ctx* ctx, uint64_t samples_done) {
   if (!ctx) return AMBER_CUDA_EINVAL;
-  ctx->samples_done = samples_done;
+  wait_idle(ctx);
+  if (samples_done == AMBER_CUDA_SAMPLES_IN_FILM) {
+    ctx->samples_in_film = true;
+  } else {
+    ctx->samples_in_film = false;
+    ctx->samples_done = samples_done;
+  }
   return AMBER_CUDA_OK;
 }
 
-int amber_cuda_cast_device(amber_cuda_ctx* ctx, const void* ray_origin4, const void* ray_direction4, uint64_t n,
-                           void* hit4, float* elapsed_ms) {
-  if (!ctx) return AMBER_CUDA_EINVAL;
-  if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
-  if (n == 0) return AMBER_CUDA_OK;
-  if (!ray_origin4 || !ray_direction4 || !hit4) return fail(ctx, AMBER_CUDA_EINVAL, "NULL buffer");
-  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+int amber_cuda_film_reduce(amber_cuda_ctx* const* ctxs, int n) {
+  if (!ctxs || n < 1 || !ctxs[0]) return AMBER_CUDA_EINVAL;
+  amber_cuda_ctx* dst = ctxs[0];
+  if (n - 1 > kMaxReduceSources) return fail(dst, AMBER_CUDA_EINVAL, "at most %d films can be summed into one", kMaxReduceSources);
+  if (!dst->has_sensor) return fail(dst, AMBER_CUDA_ESTATE, "set_sensor has not been called");
+  const SensorDev& sensor = dst->camera.sensor;
+  const uint32_t n_pixels = sensor.width * sensor.height;
+  for (int k = 0; k < n; k++) {
+    if (!ctxs[k]) return fail(dst, AMBER_CUDA_EINVAL, "context %d is NULL", k);
+    const int rc = amber_cuda_wait(ctxs[k]);
+    if (rc != AMBER_CUDA_OK) {
+      if (k > 0) dst->error = ctxs[k]->error;
+      return rc;
+    }
+    if (!ctxs[k]->has_sensor || ctxs[k]->camera.sensor.width != sensor.width || ctxs[k]->camera.sensor.height != sensor.height)
+      return fail(dst, AMBER_CUDA_EINVAL, "context %d has a different sensor", k);
+    if (ctxs[k]->samples_in_film) return fail(dst, AMBER_CUDA_ESTATE, "context %d holds an externally reduced film", k);
+    for (int j = 0; j < k; j++)
+      if (ctxs[j] == ctxs[k]) return fail(dst, AMBER_CUDA_EINVAL, "context %d is listed twice", k);
+  }
+  if (n == 1) return AMBER_CUDA_OK;
+  CUDA_TRY(dst, cudaSetDevice(dst->device));
+  FilmSources sources{};
+  std::vector<float4*> staged;  // films of devices without peer access, copied next to dst
+  auto release = [&] { for (float4* p : staged) cudaFree(p); };
+  for (int k = 1; k < n; k++) {
+    const amber_cuda_ctx* src = ctxs[k];
+    const float4* film = src->d_film.ptr;
+    if (src->device != dst->device) {
+      int can = 0;
+      CUDA_TRY(dst, cudaDeviceCanAccessPeer(&can, dst->device, src->device));
+      if (can) {
+        const cudaError_t err = cudaDeviceEnablePeerAccess(src->device, 0);
+        if (err == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError(); else if (err != cudaSuccess) can = 0;
+      }
+      if (!can) {
+        cudaGetLastError();
+        float4* copy = nullptr;
+        if (cudaMalloc(&copy, static_cast<size_t>(n_pixels) * sizeof(float4)) != cudaSuccess) {
+          release();
+          return fail(dst, AMBER_CUDA_ECUDA, "film_reduce: no memory to stage the film of device %d", src->device);
+        }
+        staged.push_back(copy);
+        const cudaError_t err = cudaMemcpyPeerAsync(copy, dst->device, film, src->device,
+                                                    static_cast<size_t>(n_pixels) * sizeof(float4), dst->stream);
+        if (err != cudaSuccess) {
+          release();
+          return fail(dst, AMBER_CUDA_ECUDA, "film_reduce: peer copy from device %d failed: %s", src->device, cudaGetErrorString(err));
+        }
+        film = copy;
+      }
+    }
+    sources.film[sources.n++] = film;
+  }
+  int sm_count = 148;
+  cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dst->device);
+  const unsigned int grid = std::min<unsigned int>(blocks_for(n_pixels), static_cast<unsigned int>(sm_count) * 8u);
+  film_sum_kernel<<<grid, kBlock, 0, dst->stream>>>(dst->d_film.ptr, sources, n_pixels);
+  dst->stats.kernel_launches++;
+  const cudaError_t err = cudaStreamSynchronize(dst->stream);
+  release();
+  if (err != cudaSuccess) return fail(dst, AMBER_CUDA_ECUDA, "film_reduce failed: %s", cudaGetErrorString(err));
+  CUDA_TRY(dst, cudaGetLastError());
+  for (int k = 1; k < n; k++) dst->samples_done += ctxs[k]->samples_done;
+  return AMBER_CUDA_OK;
+}
+
+// the caller holds the device's turn
+static int cast_device_locked(amber_cuda_ctx* ctx, const void* ray_origin4, const void* ray_direction4, uint64_t n,
+                              void* hit4, float* elapsed_ms) {
   int rc = bind_constants(ctx);
   if (rc != AMBER_CUDA_OK) return rc;
   const float4* o = static_cast<const float4*>(ray_origin4);
@@ -1147,13 +1504,27 @@ int amber_cuda_cast_device(amber_cuda_ctx* ctx, const void* ray_origin4, const v
   return AMBER_CUDA_OK;
 }
 
+int amber_cuda_cast_device(amber_cuda_ctx* ctx, const void* ray_origin4, const void* ray_direction4, uint64_t n,
+                           void* hit4, float* elapsed_ms) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
+  if (n == 0) return AMBER_CUDA_OK;
+  if (!ray_origin4 || !ray_direction4 || !hit4) return fail(ctx, AMBER_CUDA_EINVAL, "NULL buffer");
+  wait_idle(ctx);
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  DeviceTurn turn(ctx);
+  return cast_device_locked(ctx, ray_origin4, ray_direction4, n, hit4, elapsed_ms);
+}
+
 int amber_cuda_cast(amber_cuda_ctx* ctx, const float* origins, const float* directions, uint64_t n,
                     int32_t* prim, float* t) {
   if (!ctx) return AMBER_CUDA_EINVAL;
   if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
   if (n == 0) return AMBER_CUDA_OK;
   if (!origins || !directions || !prim || !t) return fail(ctx, AMBER_CUDA_EINVAL, "NULL buffer");
+  wait_idle(ctx);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  DeviceTurn turn(ctx);
   cudaStream_t stream = ctx->stream;
   CUDA_TRY(ctx, ctx->d_scratch_f[0].resize(3 * n));
   CUDA_TRY(ctx, ctx->d_scratch_f[1].resize(3 * n));
@@ -1164,8 +1535,8 @@ int amber_cuda_cast(amber_cuda_ctx* ctx, const float* origins, const float* dire
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->d_scratch_f[1].ptr, directions, 3 * n * sizeof(float), cudaMemcpyHostToDevice, stream));
   pack_rays_kernel<<<blocks_for(n), kBlock, 0, stream>>>(ctx->d_scratch_f[0].ptr, ctx->d_scratch_f[1].ptr, n,
                                                         ctx->d_scratch_4[0].ptr, ctx->d_scratch_4[1].ptr);
-  const int rc = amber_cuda_cast_device(ctx, ctx->d_scratch_4[0].ptr, ctx->d_scratch_4[1].ptr, n,
-                                        ctx->d_scratch_4[2].ptr, nullptr);
+  const int rc = cast_device_locked(ctx, ctx->d_scratch_4[0].ptr, ctx->d_scratch_4[1].ptr, n,
+                                    ctx->d_scratch_4[2].ptr, nullptr);
   if (rc != AMBER_CUDA_OK) return rc;
   unpack_hits_kernel<<<blocks_for(n), kBlock, 0, stream>>>(ctx->d_scratch_4[2].ptr, n, ctx->d_internal_to_prim.ptr,
                                                           ctx->d_scratch_i[0].ptr, ctx->d_scratch_f[2].ptr);
@@ -1185,6 +1556,7 @@ static int sample_scatter(amber_cuda_ctx* ctx, bool importance, int32_t material
   if (material < 0 || static_cast<size_t>(material) >= ctx->d_materials.count)
     return fail(ctx, AMBER_CUDA_EINVAL, "material %d out of range", material);
   if (n == 0) return AMBER_CUDA_OK;
+  wait_idle(ctx);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   cudaStream_t stream = ctx->stream;
   auto& f = ctx->d_scratch_f;
@@ -1223,6 +1595,7 @@ int amber_cuda_light_rays(amber_cuda_ctx* ctx, uint64_t n, const float* xi5, flo
   if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
   if (ctx->view.n_lights == 0) return fail(ctx, AMBER_CUDA_EINVAL, "the scene has no emitting triangle");
   if (n == 0) return AMBER_CUDA_OK;
+  wait_idle(ctx);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   cudaStream_t stream = ctx->stream;
   auto& f = ctx->d_scratch_f;
@@ -1245,7 +1618,9 @@ int amber_cuda_lens_response(amber_cuda_ctx* ctx, uint64_t n, const float* posit
   if (!ctx->has_scene || !ctx->has_sensor)
     return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene and set_sensor must be called first");
   if (n == 0) return AMBER_CUDA_OK;
+  wait_idle(ctx);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  DeviceTurn turn(ctx);
   int rc = bind_constants(ctx);
   if (rc != AMBER_CUDA_OK) return rc;
   cudaStream_t stream = ctx->stream;
@@ -1268,6 +1643,7 @@ int amber_cuda_normalize(amber_cuda_ctx* ctx, uint64_t n, const float* vector3, 
   if (!ctx) return AMBER_CUDA_EINVAL;
   if (!vector3 || !unit3) return fail(ctx, AMBER_CUDA_EINVAL, "vector3 / unit3 is NULL");
   if (n == 0) return AMBER_CUDA_OK;
+  wait_idle(ctx);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   cudaStream_t stream = ctx->stream;
   auto& f = ctx->d_scratch_f;
@@ -1291,7 +1667,9 @@ int amber_cuda_eye_rays(amber_cuda_ctx* ctx, uint64_t n, const uint32_t* px, con
   if (!ctx->has_scene || !ctx->has_sensor)
     return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene and set_sensor must be called first");
   if (n == 0) return AMBER_CUDA_OK;
+  wait_idle(ctx);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  DeviceTurn turn(ctx);
   int rc = bind_constants(ctx);
   if (rc != AMBER_CUDA_OK) return rc;
   cudaStream_t stream = ctx->stream;
@@ -1316,6 +1694,7 @@ int amber_cuda_eye_rays(amber_cuda_ctx* ctx, uint64_t n, const uint32_t* px, con
 
 int amber_cuda_get_stats(amber_cuda_ctx* ctx, amber_cuda_stats* out) {
   if (!ctx || !out) return AMBER_CUDA_EINVAL;
+  wait_idle(ctx);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   Control ctl;
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl.ptr, sizeof(Control), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1327,7 +1706,13 @@ int amber_cuda_get_stats(amber_cuda_ctx* ctx, amber_cuda_stats* out) {
   ctx->stats.truncated_paths = ctl.truncated;
   ctx->stats.phong_capped = ctl.phong_capped;
   ctx->stats.light_splats = ctl.splats;
+  ctx->stats.bvh_node_visits = ctl.bvh_work[0];
+  ctx->stats.bvh_triangle_tests = ctl.bvh_work[1];
+  ctx->stats.bvh_node_visits_connect = ctl.bvh_work[2];
+  ctx->stats.bvh_triangle_tests_connect = ctl.bvh_work[3];
   ctx->stats.accel = ctx->use_bvh ? 1u : 0u;
+  ctx->stats.bvh_node_bytes = static_cast<uint32_t>(bvh_build::kNodeFloats * sizeof(float));
+  ctx->stats.bvh_triangle_bytes = static_cast<uint32_t>(sizeof(TriIsect));
   ctx->stats.bvh_nodes = ctx->bvh_nodes;
   *out = ctx->stats;
   return AMBER_CUDA_OK;
@@ -1335,6 +1720,7 @@ int amber_cuda_get_stats(amber_cuda_ctx* ctx, amber_cuda_stats* out) {
 
 int amber_cuda_set_profiling(amber_cuda_ctx* ctx, int profile) {
   if (!ctx) return AMBER_CUDA_EINVAL;
+  wait_idle(ctx);
   ctx->profiling = profile != 0;
   return AMBER_CUDA_OK;
 }

@@ -618,7 +618,7 @@ __global__ void __launch_bounds__(BdptLaunch<Accel>::kThreads, BdptLaunch<Accel>
           phase = kBdptDone;
         } else {
           pixel = static_cast<uint32_t>(pair % args.n_pixels);
-          sample = static_cast<uint32_t>(args.sample_begin + pair / args.n_pixels);
+          sample = static_cast<uint32_t>(args.sample_begin + (pair / args.n_pixels) * args.sample_stride);
           pairs++;
           measurement = v3(0.0f, 0.0f, 0.0f);
           rng.init(args.seed, pixel, sample, 0x40000000u);

@@ -162,9 +162,12 @@ struct WideBvh {
   // lanes keeps the SIMT width used.
   //   Source: uint32_t count(); bool load(i, Ray&, float& t_best) (false: nothing to trace,
   //   the source has written that item's result itself); void store(i, hit, found).
-  template <bool kAnyHit, class Source>
+  // kCount (profiling mode): node steps and triangle tests are counted per lane and added to
+  // counters[0] / counters[1] once per warp at the end -- the traffic floor of the roofline.
+  template <bool kAnyHit, bool kCount = false, class Source>
   static __device__ __forceinline__ void trace_persistent(const SceneView& scene, Source& source,
-                                                          unsigned int* cursor) {
+                                                          unsigned int* cursor,
+                                                          unsigned long long* counters = nullptr) {
     extern __shared__ int32_t bvh_stack_smem[];
     int32_t* stack = bvh_stack_smem + threadIdx.x;
     const int stride = blockDim.x;
@@ -186,6 +189,7 @@ struct WideBvh {
     HitRecord hit;
     hit.t = 0.0f;
     hit.prim = -1;
+    uint32_t node_steps = 0, triangle_tests = 0;
 
     while (true) {
       // ---- fetch ----------------------------------------------------------------------
@@ -224,13 +228,17 @@ struct WideBvh {
         const uint32_t inner_lanes = __ballot_sync(kFull, inner);
         if (inner_lanes == 0) break;
         if (__popc(inner_lanes) < kMinDescendLanes && __any_sync(kFull, current < 0)) break;
-        if (inner) current = node_step(scene, current, idir, oidir, hit.t, stack, stride, sp);
+        if (inner) {
+          current = node_step(scene, current, idir, oidir, hit.t, stack, stride, sp);
+          if (kCount) node_steps++;
+        }
       }
       // ---- leaves ---------------------------------------------------------------------
       // (Dealing the (lane, triangle) pairs of a leaf phase out over the whole warp by shuffle --
       // one pass of ~20 busy lanes for four passes of ~5 -- was measured slower: 570 vs 544 us.)
       if (current < 0) {
         const int first = bvh_leaf_first(current), count = bvh_leaf_count(current);
+        if (kCount) triangle_tests += count;
 #pragma unroll
         for (int k = 0; k < kBvhLeafMax; k++) {
           if (k < count) {
@@ -253,6 +261,14 @@ struct WideBvh {
       }
     }
     if (have_item) source.store(item, hit, found);
+    if (kCount) {
+      node_steps = __reduce_add_sync(kFull, node_steps);
+      triangle_tests = __reduce_add_sync(kFull, triangle_tests);
+      if (lane == 0) {
+        atomicAdd(&counters[0], static_cast<unsigned long long>(node_steps));
+        atomicAdd(&counters[1], static_cast<unsigned long long>(triangle_tests));
+      }
+    }
   }
 
   static constexpr bool kPersistent = true;

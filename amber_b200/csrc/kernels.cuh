@@ -8,7 +8,7 @@
 //   shade    : emission, [light sampling -> shadow queue], BSDF sample, Russian
 //              roulette, next ray in place      (algorithm_pt.cc:137-157)
 //   connect  : any-hit for the shadow queue + film add
-// `shade` sorts each 1024-slot tile by hit class in shared memory so that a warp shades one
+// `shade` sorts each 512-slot tile by hit class in shared memory so that a warp shades one
 // material; freed slots are compacted into `q_new` and slots with a pending shadow ray into
 // `q_shadow`: per-thread bit masks, warp shuffles, one smem scan and ONE global atomic per
 // queue per tile.
@@ -52,6 +52,9 @@ struct Control {
   unsigned int n_pixels;
   unsigned int pad;
   unsigned long long cursor_bdpt;  // bdpt_kernel: next (pixel, sample) pair index
+  // profiling mode: traversal work of the BVH kernels: extend node steps, extend triangle tests, connect
+  // node steps, connect triangle tests
+  unsigned long long bvh_work[4];
 };
 
 struct PathPool {
@@ -71,10 +74,12 @@ struct RenderArgs {
   float4* film;
   uint64_t seed;
   uint64_t sample_begin;
-  uint32_t n_pixels;
+  uint32_t n_pixels;      // pixels sampled by this render: the window, or the whole frame
   uint32_t max_depth;
   int32_t estimator;
   float inv_n_pixels;  // light tracing: each splat is divided by image.Size(), algorithm_lt.cc:146
+  uint32_t pixel_begin;   // first pixel of the window (index in the full frame)
+  uint32_t sample_stride; // global sample index = sample_begin + ordinal * sample_stride
 };
 
 __constant__ CameraDev c_camera;  // single translation unit: defined here
@@ -258,7 +263,7 @@ __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(con
   const Control* ctl = args.ctl;
   const uint32_t n_new = AMBER_RAYGEN_LOOP ? ctl->n_new : min(ctl->n_new, (blockIdx.x + 1) * kBlock);
   const unsigned long long next_path = ctl->next_path, total_paths = ctl->total_paths;
-  const unsigned long long base_pixel = ctl->base_pixel, base_sample = args.sample_begin + ctl->base_sample;
+  const unsigned long long base_pixel = ctl->base_pixel, base_ordinal = ctl->base_sample;
   const uint32_t width = c_camera.sensor.width;
   for (uint32_t j = blockIdx.x * kBlock + threadIdx.x; j < n_new; j += gridDim.x * kBlock) {
     const uint32_t slot = args.pool.q_new[j];
@@ -278,7 +283,8 @@ __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(con
       wrapped = static_cast<uint32_t>(offset) / args.n_pixels;
       pixel = static_cast<uint32_t>(offset) - wrapped * args.n_pixels;
     }
-    const uint32_t sample = static_cast<uint32_t>(base_sample + wrapped);
+    const uint32_t sample = static_cast<uint32_t>(args.sample_begin + (base_ordinal + wrapped) * args.sample_stride);
+    pixel += args.pixel_begin;  // the stream is keyed by the pixel's index in the full frame
     CameraRng rng;
     rng.init(args.seed, pixel, sample);
     float3 o, d, w3;
@@ -409,6 +415,12 @@ template <>
 __global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) extend_kernel<WideBvh>(const RenderArgs args) {
   ExtendSource source{args, {-1}};
   WideBvh::trace_persistent<false>(args.scene, source, &args.ctl->cursor_extend);
+}
+
+// profiling mode: the same kernel with the traversal work counted (amber_cuda_stats.bvh_*)
+__global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) extend_bvh_counting_kernel(const RenderArgs args) {
+  ExtendSource source{args, {-1}};
+  WideBvh::trace_persistent<false, true>(args.scene, source, &args.ctl->cursor_extend, &args.ctl->bvh_work[0]);
 }
 
 struct CastSource {
@@ -871,16 +883,54 @@ __global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) connect_kernel<W
   WideBvh::trace_persistent<true>(args.scene, source, &args.ctl->cursor_connect);
 }
 
+__global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) connect_bvh_counting_kernel(const RenderArgs args) {
+  ConnectSource source{args, 0u};
+  WideBvh::trace_persistent<true, true>(args.scene, source, &args.ctl->cursor_connect, &args.ctl->bvh_work[2]);
+}
+
 // Accumulator::Mean (include/amber/prelude/accumulator.h:88-95): film / samples,
 // packed to the reference's Image<RGB> layout (x + y*W, 3 floats).
+// The sample count either comes from the host (inv_samples) or, after an external all-reduce of the
+// film, from the film's trailing element (count_in_film != 0: three 16-bit digits as floats).
+__device__ __forceinline__ float film_inv_samples(const float4* film, uint32_t n_pixels, float inv_samples,
+                                                  int count_in_film) {
+  if (!count_in_film) return inv_samples;
+  const float4 tail = film[n_pixels];
+  const double count = static_cast<double>(tail.x) + 65536.0 * static_cast<double>(tail.y) +
+                       4294967296.0 * static_cast<double>(tail.z);
+  return count > 0.0 ? 1.0f / static_cast<float>(static_cast<unsigned long long>(count)) : 0.0f;
+}
+
 __global__ void __launch_bounds__(kBlock) resolve_kernel(const float4* __restrict__ film, uint32_t n_pixels,
-                                                         float inv_samples, float* __restrict__ rgb) {
+                                                         float inv_samples, int count_in_film,
+                                                         float* __restrict__ rgb) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= n_pixels) return;
+  inv_samples = film_inv_samples(film, n_pixels, inv_samples, count_in_film);
   const float4 v = film[i];
   rgb[3 * i + 0] = v.x * inv_samples;
   rgb[3 * i + 1] = v.y * inv_samples;
   rgb[3 * i + 2] = v.z * inv_samples;
+}
+
+// Film reduction across the contexts of one process (amber_cuda_film_reduce): dst += sum of the source
+// films, which live on OTHER devices and are read through peer memory over NVLink -- the in-process
+// counterpart of the NCCL all-reduce, Accumulator::operator+= (include/amber/prelude/accumulator.h:136-166).
+constexpr int kMaxReduceSources = 15;
+struct FilmSources {
+  const float4* film[kMaxReduceSources];
+  int n;
+};
+__global__ void __launch_bounds__(kBlock) film_sum_kernel(float4* __restrict__ dst, const FilmSources sources,
+                                                          uint32_t n_pixels) {
+  for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n_pixels; i += gridDim.x * kBlock) {
+    float4 v = dst[i];
+    for (int k = 0; k < sources.n; k++) {
+      const float4 a = sources.film[k][i];
+      v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+    }
+    dst[i] = v;
+  }
 }
 
 // Resolve fused with the reference's post-process (src/amber/cli/application.cc:98-106):
@@ -904,10 +954,11 @@ __device__ __forceinline__ uint8_t tonemap_channel(float value, float white) {
 }
 
 __global__ void __launch_bounds__(kBlock) resolve_tonemap_kernel(const float4* __restrict__ film, uint32_t width,
-                                                                 uint32_t height, float inv_samples, int flip_x,
-                                                                 uint8_t* __restrict__ rgb8) {
+                                                                 uint32_t height, float inv_samples, int count_in_film,
+                                                                 int flip_x, uint8_t* __restrict__ rgb8) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= width * height) return;
+  inv_samples = film_inv_samples(film, width * height, inv_samples, count_in_film);
   const uint32_t x = i % width, y = i / width;
   const float4 v = film[i];
   const float white = filmic_map(0.70f);

@@ -5,7 +5,9 @@ and adds them into a shared accumulator (``include/amber/rendering/parallel.h:50
 ``include/amber/prelude/accumulator.h:136-166``).  Here a rank plays the thread: rank r
 of G renders global sample indices [r*S/G, (r+1)*S/G) for every pixel into its own film;
 the only exchange is ONE sum all-reduce of the film (NCCL over NVLink on GPUs, gloo in
-the CPU tests), after which every rank holds the full sum and divides by S.  Because
+the CPU tests), after which every rank holds the full sum and divides by S.  The sample
+count travels IN the film (its trailing element, see ``amber_cuda_film_device``), so a step
+costs exactly one collective and no device-to-host read.  Because
 the random stream is keyed by (pixel, global sample index), the image does not depend
 on G (up to float summation order).
 """
@@ -23,14 +25,25 @@ def partition_samples(total_samples: int, rank: int, world_size: int) -> tuple[i
     return begin, count
 
 
+def count_digits(samples: int) -> list[float]:
+    """The film's trailing element: the sample count as three 16-bit digits, each exact in
+    float32 under summation over up to 256 ranks (``include/amber_cuda.h``)."""
+    return [float(samples & 0xFFFF), float((samples >> 16) & 0xFFFF), float(samples >> 32), 0.0]
+
+
+def digits_count(tail) -> int:
+    return int(round(float(tail[0]))) + (int(round(float(tail[1]))) << 16) + (int(round(float(tail[2]))) << 32)
+
+
 def all_reduce_film(film: torch.Tensor, samples: int, group=None) -> int:
-    """Sum ``film`` in place across ranks; returns the total sample count."""
+    """Sum ``film`` (any shape) across ranks together with the sample count: ONE collective
+    over the film with the count appended.  In place; returns the total sample count."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return samples
-    dist.all_reduce(film, op=dist.ReduceOp.SUM, group=group)
-    count = torch.tensor([samples], dtype=torch.int64, device=film.device)
-    dist.all_reduce(count, op=dist.ReduceOp.SUM, group=group)
-    return int(count.item())
+    flat = torch.cat([film.reshape(-1), torch.tensor(count_digits(samples), dtype=film.dtype, device=film.device)])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    film.copy_(flat[:-4].reshape(film.shape))
+    return digits_count(flat[-4:].tolist())
 
 
 class _DevicePointer:
@@ -47,12 +60,14 @@ def film_tensor(device) -> torch.Tensor:
     return torch.as_tensor(_DevicePointer(ptr, n), device=torch.device("cuda", device.device))
 
 
-def reduce_device_film(device, group=None) -> int:
-    """All-reduce the film of an ``amber_b200.render.Device`` and fix its sample count."""
-    _, _, samples = device.film_device()
-    film = film_tensor(device)
-    total = all_reduce_film(film, samples, group)
+def reduce_device_film(device, group=None) -> None:
+    """All-reduce the film of an ``amber_b200.render.Device`` in place: one collective, the sample
+    count rides in the film's trailing element and ``resolve`` reads it there on the device."""
+    from . import capi
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    film = film_tensor(device)                      # publishes the count into the trailing element
+    dist.all_reduce(film, op=dist.ReduceOp.SUM, group=group)
     if film.is_cuda:
-        torch.cuda.synchronize(film.device)  # the context resolves on its own stream
-    device.film_set_samples(total)
-    return total
+        torch.cuda.current_stream(film.device).synchronize()  # the context resolves on its own stream
+    device.film_set_samples(capi.SAMPLES_IN_FILM)

@@ -123,9 +123,25 @@ class Device:
 
     # -- rendering ----------------------------------------------------------------
     def render(self, sample_begin: int, sample_count: int, seed: int = 1, max_depth: int = 0,
-               estimator: int = capi.ESTIMATOR_NEE, pool_paths: int = 0) -> None:
-        params = capi.RenderParams(sample_begin, sample_count, max_depth, seed, estimator, pool_paths)
-        self._check(self.lib.amber_cuda_render(self.ctx, C.byref(params)))
+               estimator: int = capi.ESTIMATOR_NEE, pool_paths: int = 0, window: tuple[int, int] = (0, 0),
+               sample_stride: int = 1, wait: bool = True) -> None:
+        """Add ``sample_count`` samples per pixel.  ``window`` = (first pixel, pixel count) restricts the
+        render to a range of pixel indices; ``wait=False`` only queues the call on the context's worker
+        thread (``amber_cuda_render_async``): consecutive queued calls run as one wavefront."""
+        params = capi.RenderParams(sample_begin, sample_count, max_depth, seed, estimator, pool_paths,
+                                   int(window[0]), int(window[1]), int(sample_stride), 0)
+        call = self.lib.amber_cuda_render if wait else self.lib.amber_cuda_render_async
+        self._check(call(self.ctx, C.byref(params)))
+
+    def wait(self) -> None:
+        """Block until every queued render is done; raises the queue's first failure."""
+        self._check(self.lib.amber_cuda_wait(self.ctx))
+
+    def pending(self) -> int:
+        return int(self.lib.amber_cuda_pending(self.ctx))
+
+    def wait_pending(self, max_pending: int) -> None:
+        self._check(self.lib.amber_cuda_wait_pending(self.ctx, int(max_pending)))
 
     def resolve(self, out: np.ndarray | None = None) -> tuple[np.ndarray, int]:
         assert self.sensor is not None
@@ -152,6 +168,12 @@ class Device:
 
     def film_set_samples(self, samples: int) -> None:
         self._check(self.lib.amber_cuda_film_set_samples(self.ctx, samples))
+
+    def film_reduce_from(self, others: "list[Device]") -> None:
+        """Sum the films of ``others`` (contexts of this process, any devices) into this one:
+        ``amber_cuda_film_reduce`` (peer reads over NVLink)."""
+        ctxs = (C.c_void_p * (1 + len(others)))(self.ctx, *[o.ctx for o in others])
+        self._check(self.lib.amber_cuda_film_reduce(ctxs, len(ctxs)))
 
     # -- parity entry points ----------------------------------------------------------
     def cast(self, origins, directions) -> tuple[np.ndarray, np.ndarray]:
@@ -254,38 +276,80 @@ class CudaPathTracing:
     ``batch_spp`` samples (so ``--spp``, expiry and the iteration counter keep their
     reference meaning) and returns the mean image, shape (H, W, 3), float32, row-major
     ``x + y*W`` like ``Image<RGB>`` (``include/amber/prelude/image.h:117-124``).
+
+    Batches are queued (``amber_cuda_render_async``), at most ``depth`` ahead of the device, so
+    consecutive batches run as ONE wavefront and the path pool is never drained in between; with
+    several ``devices`` batch b goes to device b mod G, which renders the interleaved sample
+    indices {d, d + G, ...}, all devices work concurrently -- as the reference's threads do
+    (``include/amber/rendering/parallel.h:55-68``) -- and the films are summed over peer memory
+    (``amber_cuda_film_reduce``).  Contexts, scene and pool stay alive between ``render`` calls.
     """
 
     def __init__(self, estimator: str = "nee", max_depth: int = 0, seed: int = 1, device: int = 0,
-                 batch_spp: int = 64, pool_paths: int = 0):
+                 batch_spp: int = 64, pool_paths: int = 0, devices: "list[int] | None" = None, depth: int = 3):
         self.estimator = {"reference": capi.ESTIMATOR_REFERENCE, "nee": capi.ESTIMATOR_NEE,
                           "lt": capi.ESTIMATOR_LIGHT_TRACING, "bdpt": capi.ESTIMATOR_BDPT}[estimator]
         self.max_depth = max_depth
         self.seed = seed
-        self.device_index = device
-        self.batch_spp = batch_spp
+        self.device_indices = list(devices) if devices else [device]
+        self.batch_spp = max(1, batch_spp)
         self.pool_paths = pool_paths
+        self.depth = max(1, depth)
         self.last_stats: dict | None = None
+        self._devices: list[Device] = []
+        self._scene = None
+
+    def close(self) -> None:
+        for dev in self._devices:
+            dev.close()
+        self._devices = []
+        self._scene = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _bind(self, scene: FlatScene, sensor: Sensor) -> "list[Device]":
+        if not self._devices:
+            self._devices = [Device(i) for i in self.device_indices]
+        for dev in self._devices:
+            if self._scene is not scene:
+                dev.upload_scene(scene)
+            dev.set_sensor(sensor)  # clears the film
+        self._scene = scene
+        return self._devices
 
     def render(self, scene: FlatScene, sensor: Sensor, context: Context) -> np.ndarray:
         if not isinstance(scene, FlatScene):
             # the reference adapter throws std::invalid_argument for a scene it cannot flatten
             raise TypeError("CudaPathTracing needs a FlatScene (no CPU fallback)")
-        with Device(self.device_index) as dev:
-            dev.upload_scene(scene)
-            dev.set_sensor(sensor)
-            begin = 0
-            while True:
-                count = 0
-                while count < self.batch_spp and context.iterate():
-                    count += 1
-                if count == 0:
-                    break
-                dev.render(begin, count, seed=self.seed, max_depth=self.max_depth,
-                           estimator=self.estimator, pool_paths=self.pool_paths)
-                begin += count
-            image, _ = dev.resolve()
-            self.last_stats = dev.stats()
+        devices = self._bind(scene, sensor)
+        n = len(devices)
+        done = [0] * n  # samples per pixel handed to each device
+        batch = 0
+        while True:
+            count = 0
+            while count < self.batch_spp and context.iterate():
+                count += 1
+            if count == 0:
+                break
+            d = batch % n
+            devices[d].wait_pending(self.depth - 1)
+            devices[d].render(d + n * done[d], count, seed=self.seed, max_depth=self.max_depth,
+                              estimator=self.estimator, pool_paths=self.pool_paths, sample_stride=n, wait=False)
+            done[d] += count
+            batch += 1
+        for dev in devices:
+            dev.wait()
+        if n > 1:
+            devices[0].film_reduce_from(devices[1:])
+        image, _ = devices[0].resolve()
+        self.last_stats = devices[0].stats()
+        if n > 1:
+            for key in ("paths", "closest_rays", "shadow_rays", "truncated_paths"):
+                self.last_stats[key] = sum(dev.stats()[key] for dev in devices)
         return image
 
 
@@ -295,8 +359,8 @@ class CudaLightTracing(CudaPathTracing):
     ``context.iterate()`` is W*H light paths, as ``Thread::operator()`` traces them."""
 
     def __init__(self, max_depth: int = 0, seed: int = 1, device: int = 0, batch_spp: int = 64,
-                 pool_paths: int = 0):
-        super().__init__("lt", max_depth, seed, device, batch_spp, pool_paths)
+                 pool_paths: int = 0, devices: "list[int] | None" = None):
+        super().__init__("lt", max_depth, seed, device, batch_spp, pool_paths, devices)
 
 
 class CudaBidirectionalPathTracing(CudaPathTracing):
@@ -305,5 +369,6 @@ class CudaBidirectionalPathTracing(CudaPathTracing):
     ``include/amber/rendering/bidirectional_path_sampling.h``.  ``max_vertices`` caps the events
     per subpath (<= 16; the reference has no cap)."""
 
-    def __init__(self, max_vertices: int = 0, seed: int = 1, device: int = 0, batch_spp: int = 64):
-        super().__init__("bdpt", max_vertices, seed, device, batch_spp, 0)
+    def __init__(self, max_vertices: int = 0, seed: int = 1, device: int = 0, batch_spp: int = 64,
+                 devices: "list[int] | None" = None):
+        super().__init__("bdpt", max_vertices, seed, device, batch_spp, 0, devices)

@@ -19,7 +19,14 @@
  *  - the caller owns every host buffer; the context owns all device memory.
  *  - a context is bound to ONE device and is used by one host thread at a time
  *    (the reference's Render() is likewise called from one thread,
- *    src/amber/cli/application.cc:149-152).
+ *    src/amber/cli/application.cc:149-152).  Different contexts may be driven from different
+ *    threads, also on the same device: the scene and camera of a context live in the device's
+ *    __constant__ banks while it renders, so contexts that share a device take turns (a per-device
+ *    lock held for the length of one render job or parity call).
+ *  - amber_cuda_render_async queues a render on the context's own worker thread and returns;
+ *    every other call on that context first waits for the queue to drain.  G contexts on G devices
+ *    therefore render concurrently, as the reference's worker threads do
+ *    (src/amber/prelude/parallel.cc:29-40, include/amber/rendering/parallel.h:55-68).
  *  - there is no CPU fallback: without a CUDA device amber_cuda_create() fails.
  */
 #ifndef AMBER_CUDA_H_
@@ -32,7 +39,7 @@
 extern "C" {
 #endif
 
-#define AMBER_CUDA_ABI_VERSION 1
+#define AMBER_CUDA_ABI_VERSION 2
 
 /* error codes */
 #define AMBER_CUDA_OK 0
@@ -135,6 +142,17 @@ typedef struct amber_cuda_render_params {
   uint64_t seed;
   int32_t estimator;     /* AMBER_CUDA_ESTIMATOR_* */
   uint32_t pool_paths;   /* resident path slots (0 = default) */
+  /* Pixel window: only pixels [pixel_begin, pixel_begin + pixel_count) of the frame (index x + y*W,
+   * i.e. whole rows when both are multiples of W) are sampled; pixel_count = 0 is the whole frame.
+   * The random stream is keyed by the pixel's index in the FULL frame, so a window holds exactly the
+   * values the full render has there.  Path tracing estimators only. */
+  uint32_t pixel_begin;
+  uint32_t pixel_count;
+  /* The k-th sample of this call has global index sample_begin + k * sample_stride (0 = 1): device d
+   * of G renders {d, d + G, d + 2G, ...}, so that consecutive calls on one device continue one
+   * sequence (see amber_cuda_render_async) and the union over the devices is {0, 1, 2, ...}. */
+  uint32_t sample_stride;
+  uint32_t reserved;
 } amber_cuda_render_params;
 
 typedef struct amber_cuda_stats {
@@ -153,6 +171,14 @@ typedef struct amber_cuda_stats {
   uint32_t accel;           /* 0 = constant-memory list, 1 = wide BVH */
   uint32_t bvh_nodes;
   uint64_t light_splats;    /* light tracing: film contributions through the lens */
+  /* wide-BVH traversal work of the last render (counted in profiling mode only): node steps (one
+   * 128-byte node read each), triangles tested (one 48-byte record each), by `extend` and `connect` */
+  uint64_t bvh_node_visits, bvh_triangle_tests;
+  uint64_t bvh_node_visits_connect, bvh_triangle_tests_connect;
+  uint32_t bvh_node_bytes, bvh_triangle_bytes; /* size of one node / one leaf triangle record in HBM */
+  uint64_t chained_renders; /* render calls absorbed into a running wavefront (no pool drain between them) */
+  double scene_build_ms;    /* host time of the last upload_scene: flattening + acceleration build */
+  double scene_upload_ms;   /* ... and its host->device copies */
 } amber_cuda_stats;
 
 /* ABI version of the loaded library. */
@@ -186,6 +212,27 @@ int amber_cuda_film_clear(amber_cuda_ctx* ctx);
  * connect.  Asynchronous work is complete when the call returns. */
 int amber_cuda_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* params);
 
+/* The same, asynchronously: the render is queued on the context's worker thread and the call returns.
+ * A queued call whose parameters continue the running one (same estimator, seed, depth cap, pool,
+ * window and stride; sample_begin = where the previous call ends) is ABSORBED into the running
+ * wavefront: the path pool is not drained and refilled between the two, which is what makes small
+ * batches of Context::Iterate() (include/amber/rendering/context.h:26-32) as cheap as one big call.
+ * amber_cuda_wait blocks until everything queued is done and returns the first error of the queue
+ * (then forgets it); amber_cuda_pending returns the number of queued + running calls;
+ * amber_cuda_wait_pending blocks until at most max_pending are left.  Every other entry point
+ * implies amber_cuda_wait. */
+int amber_cuda_render_async(amber_cuda_ctx* ctx, const amber_cuda_render_params* params);
+int amber_cuda_wait(amber_cuda_ctx* ctx);
+int amber_cuda_pending(amber_cuda_ctx* ctx);
+int amber_cuda_wait_pending(amber_cuda_ctx* ctx, int max_pending);
+
+/* Sum the films (and sample counts) of contexts 1 .. n-1 into context 0: the reduction of the
+ * per-worker images, Accumulator::operator+= (include/amber/prelude/accumulator.h:136-166), for
+ * contexts of ONE process on different devices.  One kernel on context 0's device reads the other
+ * films through peer memory (NVLink); without peer access they are staged through a copy.  All
+ * contexts must have the same sensor; the other films are left as they are. */
+int amber_cuda_film_reduce(amber_cuda_ctx* const* ctxs, int n);
+
 /* Mean image to the host: host_rgb[(x + y*W)*3 + c] = film / samples.  Replaces
  * Accumulator::Mean (include/amber/prelude/accumulator.h:88-95) and the Image
  * returned by Render (layout include/amber/prelude/image.h:117-124).
@@ -200,9 +247,13 @@ int amber_cuda_resolve(amber_cuda_ctx* ctx, float* host_rgb, uint64_t* samples_d
  * flip_x != 0 mirrors the columns as ExportPNG does (src/amber/cli/image.cc:59-71). */
 int amber_cuda_resolve_ldr(amber_cuda_ctx* ctx, uint8_t* host_rgb8, int flip_x, uint64_t* samples_done);
 
-/* The raw (un-normalised) device film: W*H float4 (r,g,b,unused) sums and the sample
- * count, for the multi-GPU film reduction done by the host (NCCL all-reduce over
- * this buffer, then amber_cuda_film_set_samples). */
+/* The raw (un-normalised) device film for the multi-process film reduction done by the host (ONE
+ * NCCL all-reduce over this buffer): W*H float4 (r,g,b,unused) sums followed by one float4 that
+ * carries the sample count as (count & 0xffff, (count >> 16) & 0xffff, count >> 32, 0) -- exact in
+ * float under summation over up to 256 ranks.  n_floats = 4 * (W*H + 1).  After the all-reduce,
+ * amber_cuda_film_set_samples(ctx, AMBER_CUDA_SAMPLES_IN_FILM) makes resolve take the count from
+ * that element on the device (no host round trip); any other value sets the count directly. */
+#define AMBER_CUDA_SAMPLES_IN_FILM UINT64_MAX
 int amber_cuda_film_device(amber_cuda_ctx* ctx, void** device_ptr, uint64_t* n_floats,
                            uint64_t* samples_done);
 int amber_cuda_film_set_samples(amber_cuda_ctx* ctx, uint64_t samples_done);

@@ -334,9 +334,10 @@ struct CudaPathTracingOptions
   int estimator = AMBER_CUDA_ESTIMATOR_NEE;  // AMBER_CUDA_ESTIMATOR_REFERENCE: algorithm_pt.cc sample for sample
   uint32_t max_depth = 0;                    // 0 = 2^16; the reference has no cap (algorithm_pt.cc:137)
   uint64_t seed = 1;
-  std::vector<int> devices = {0};            // samples are split evenly over these GPUs
-  uint32_t batch_spp = 64;                   // Context::Iterate() calls consumed per device launch
+  std::vector<int> devices = {0};            // samples are dealt to these GPUs, which render concurrently
+  uint32_t batch_spp = 64;                   // Context::Iterate() calls consumed per queued render call
   uint32_t pool_paths = 0;
+  uint32_t queue_depth = 3;                  // render calls queued ahead per device (they run as one wavefront)
 };
 
 namespace detail {
@@ -376,10 +377,20 @@ private:
  *  src/amber/rendering/algorithm_pt.cc:82-95): one successful context.Iterate() is one sample per
  *  pixel over the whole frame, so --spp, --time expiry and SIGINT (src/amber/cli/application.cc:131-147)
  *  keep working and a partial mean is returned on expiry; the result is the mean image, row-major
- *  x + y * W.  Iterations are consumed in batches and dealt to the devices round-robin by global
- *  sample index; each device accumulates into its own film and the films are averaged weighted by
- *  their sample counts (the in-process counterpart of the NCCL film all-reduce of the multi-process
- *  host, amber_b200/dist.py). */
+ *  x + y * W.
+ *
+ *  Iterations are consumed in batches of batch_spp; batch b is QUEUED on device b mod G
+ *  (amber_cuda_render_async) at most queue_depth calls ahead of that device, so the G devices
+ *  render concurrently -- as the reference's worker threads do (src/amber/prelude/parallel.cc:29-40,
+ *  include/amber/rendering/parallel.h:55-68) -- and the batches of one device run as ONE wavefront
+ *  (the path pool is not drained between them).  Device d renders the interleaved global sample
+ *  indices {d, d + G, d + 2G, ...}.  At the end the films are summed into the first device's over
+ *  peer memory (amber_cuda_film_reduce, the counterpart of Accumulator::operator+=,
+ *  include/amber/prelude/accumulator.h:136-166) and resolved once.
+ *
+ *  Unlike the reference's algorithm objects this one keeps state between calls: contexts, the
+ *  uploaded scene and the path pool stay on the devices, and a scene is uploaded again only when
+ *  Render() is handed a different one. */
 class CudaPathTracing
 : public rendering::Algorithm<RGB>
 {
@@ -391,6 +402,9 @@ public:
     }
     if (options_.batch_spp == 0) {
       options_.batch_spp = 1;
+    }
+    if (options_.queue_depth == 0) {
+      options_.queue_depth = 1;
     }
   }
 
@@ -422,16 +436,25 @@ public:
       film_height = sensor.SceneArea() / film_width;
     }
 
-    std::vector<std::unique_ptr<detail::Device>> devices;
-    for (const auto index : options_.devices) {
-      devices.emplace_back(std::make_unique<detail::Device>(index));
-      const auto& device = *devices.back();
-      device.Check(amber_cuda_upload_scene(device.Get(), &provider->FlatDescription()));
-      device.Check(amber_cuda_set_sensor(device.Get(), width, height, film_width, film_height));
+    // contexts live as long as the algorithm object; the scene is uploaded when it changes
+    if (devices_.empty()) {
+      for (const auto index : options_.devices) {
+        devices_.emplace_back(std::make_unique<detail::Device>(index));
+      }
+      scene_key_ = SceneKey();
     }
+    const auto key = MakeSceneKey(provider->FlatDescription());
+    for (const auto& device : devices_) {
+      if (!(key == scene_key_)) {
+        device->Check(amber_cuda_upload_scene(device->Get(), &provider->FlatDescription()));
+      }
+      device->Check(amber_cuda_set_sensor(device->Get(), width, height, film_width, film_height));  // clears the film
+    }
+    scene_key_ = key;
 
-    // consume Iterate() in batches; batch b goes to device b mod G
-    uint64_t next_sample = 0;
+    // consume Iterate() in batches; batch b is queued on device b mod G
+    const std::size_t n_devices = devices_.size();
+    std::vector<uint64_t> handed(n_devices, 0);  // samples per pixel handed to each device
     for (std::size_t batch = 0;; batch++) {
       uint32_t count = 0;
       while (count < options_.batch_spp && context.Iterate()) {
@@ -440,52 +463,100 @@ public:
       if (count == 0) {
         break;
       }
-      const auto& device = *devices[batch % devices.size()];
-      amber_cuda_render_params params;
-      params.sample_begin = next_sample;
+      const std::size_t d = batch % n_devices;
+      const auto& device = *devices_[d];
+      device.Check(amber_cuda_wait_pending(device.Get(), static_cast<int>(options_.queue_depth) - 1));
+      amber_cuda_render_params params = amber_cuda_render_params();
+      params.sample_begin = d + n_devices * handed[d];
+      params.sample_stride = static_cast<uint32_t>(n_devices);
       params.sample_count = count;
       params.max_depth = options_.max_depth;
       params.seed = options_.seed;
       params.estimator = options_.estimator;
       params.pool_paths = options_.pool_paths;
-      device.Check(amber_cuda_render(device.Get(), &params));
-      next_sample += count;
+      device.Check(amber_cuda_render_async(device.Get(), &params));
+      handed[d] += count;
+    }
+    for (const auto& device : devices_) {
+      device->Check(amber_cuda_wait(device->Get()));
     }
 
-    // mean over all samples = sum_d (mean_d * n_d) / sum_d n_d
-    std::vector<float> part(static_cast<std::size_t>(width) * height * 3);
-    std::vector<double> sum(part.size(), 0.0);
-    uint64_t total = 0;
-    for (const auto& device : devices) {
-      uint64_t done = 0;
-      device->Check(amber_cuda_resolve(device->Get(), part.data(), &done));
-      if (done == 0) {
-        continue;
-      }
-      for (std::size_t i = 0; i < part.size(); i++) {
-        sum[i] += static_cast<double>(part[i]) * static_cast<double>(done);
-      }
-      total += done;
+    // sum of the films over peer memory, one resolve: mean = sum / total samples
+    std::vector<amber_cuda_ctx*> contexts;
+    for (const auto& device : devices_) {
+      contexts.push_back(device->Get());
     }
+    devices_.front()->Check(amber_cuda_film_reduce(contexts.data(), static_cast<int>(contexts.size())));
+    std::vector<float> mean(static_cast<std::size_t>(width) * height * 3);
+    uint64_t total = 0;
+    devices_.front()->Check(amber_cuda_resolve(devices_.front()->Get(), mean.data(), &total));
     if (total > 0) {
       for (uint32_t y = 0; y < height; y++) {
         for (uint32_t x = 0; x < width; x++) {
           const std::size_t i = (static_cast<std::size_t>(x) + static_cast<std::size_t>(y) * width) * 3;
-          image[rendering::Pixel(x, y)] = RGB(
-            static_cast<float>(sum[i] / total),
-            static_cast<float>(sum[i + 1] / total),
-            static_cast<float>(sum[i + 2] / total));
+          image[rendering::Pixel(x, y)] = RGB(mean[i], mean[i + 1], mean[i + 2]);
         }
       }
     }
-    amber_cuda_get_stats(devices.front()->Get(), &last_stats_);
+    // counters of the whole job: summed over the devices
+    amber_cuda_get_stats(devices_.front()->Get(), &last_stats_);
+    for (std::size_t d = 1; d < n_devices; d++) {
+      amber_cuda_stats other;
+      amber_cuda_get_stats(devices_[d]->Get(), &other);
+      last_stats_.paths += other.paths;
+      last_stats_.closest_rays += other.closest_rays;
+      last_stats_.shadow_rays += other.shadow_rays;
+      last_stats_.truncated_paths += other.truncated_paths;
+      last_stats_.chained_renders += other.chained_renders;
+    }
     return image;
   }
 
   const amber_cuda_stats& LastStats() const noexcept { return last_stats_; }
 
 private:
+  /** Identity of an uploaded scene: where its arrays live, how long they are, and a sparse
+   *  checksum of their bytes (every 257th word), so a rebuilt scene at a recycled address is
+   *  noticed without hashing 60 MB per Render(). */
+  struct SceneKey
+  {
+    const void* primitives = nullptr;
+    const void* materials = nullptr;
+    uint32_t n_primitives = 0, n_materials = 0;
+    uint64_t checksum = 0;
+    bool operator==(const SceneKey& o) const noexcept
+    {
+      return primitives == o.primitives && materials == o.materials && n_primitives == o.n_primitives &&
+             n_materials == o.n_materials && checksum == o.checksum;
+    }
+  };
+
+  static SceneKey MakeSceneKey(const amber_cuda_scene_desc& d)
+  {
+    SceneKey key;
+    key.primitives = d.primitives;
+    key.materials = d.materials;
+    key.n_primitives = d.n_primitives;
+    key.n_materials = d.n_materials;
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&](const void* data, std::size_t bytes, std::size_t step) {
+      const auto words = static_cast<const unsigned char*>(data);
+      for (std::size_t i = 0; i + 4 <= bytes; i += 4 * step) {
+        uint32_t w;
+        std::memcpy(&w, words + i, 4);
+        h = (h ^ w) * 1099511628211ull;
+      }
+    };
+    mix(d.primitives, static_cast<std::size_t>(d.n_primitives) * sizeof(amber_cuda_primitive), 257);
+    mix(d.materials, static_cast<std::size_t>(d.n_materials) * sizeof(amber_cuda_material), 1);
+    mix(&d.lens, sizeof d.lens, 1);
+    key.checksum = h;
+    return key;
+  }
+
   CudaPathTracingOptions options_;
+  std::vector<std::unique_ptr<detail::Device>> devices_;
+  SceneKey scene_key_;
   amber_cuda_stats last_stats_ = {};
 };
 

@@ -21,6 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 from amber_b200 import capi, scene  # noqa: E402
+from amber_b200.metrics import box_downsample, luminance  # noqa: E402
 from oracle import pyoracle  # noqa: E402
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
@@ -164,8 +165,38 @@ def bdpt_fixture():
     np.savez_compressed(os.path.join(GOLDEN, "bdpt.npz"), **out)
 
 
+def converged_fixture():
+    """8. the reference's own path tracer (MakeRGBPathTracing()->Render, its own non-reproducible
+    mt19937_64 engines), many independent runs on the built-in Cornell box: the converged 64 x 64 image
+    the GPU estimators are compared with block by block, and run means at TWO frame sizes (pixel values
+    scale with 1 / (W * H), src/amber/scene/lens_thin.cc:139-148).  Heavy-tailed: the 2 cm light is found
+    by BSDF sampling only, so a run mean is dominated by a few paths."""
+    builtin = pyoracle.Reference(builtin_cornel_box=True)
+    out = {}
+    for (w, spp, runs) in ((64, 1024, 32), (128, 256, 16)):
+        total = np.zeros((w, w, 3), dtype=np.float64)
+        means, blocks = [], []
+        seconds = 0.0
+        for _ in range(runs):
+            image, _, s = builtin.render(w, w, *FILM, spp, 8, algo=0)
+            total += image
+            means.append(float(image.mean()))
+            blocks.append(box_downsample(luminance(image), w // 4))  # luminance of a 4 x 4 grid of big blocks
+            seconds += s
+        out[f"{w}x{w}.image"] = (total / runs).astype(np.float32)
+        out[f"{w}x{w}.run_means"] = np.array(means, dtype=np.float64)
+        out[f"{w}x{w}.run_block_luminance"] = np.array(blocks, dtype=np.float64)
+        out[f"{w}x{w}.spp_per_run"] = np.array([spp], dtype=np.int64)
+        print(f"converged {w}x{w}: {runs} runs x {spp} spp in {seconds:.0f} s; mean {np.mean(means):.4f} +- "
+              f"{np.std(means, ddof=1) / np.sqrt(runs):.4f} (std of a run {np.std(means, ddof=1):.4f})")
+    np.savez_compressed(os.path.join(GOLDEN, "cornell_converged.npz"), **out)
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "converged":
+        converged_fixture()
+        return
     if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "bdpt":
         bdpt_fixture()
         return

@@ -10,10 +10,16 @@
 // Built by `make -C oracle adapter_demo` into oracle/_ref/ (it links the compiled reference).
 // usage: adapter_demo [size=128] [spp=64] [threads=8] [devices=1]
 //        adapter_demo --dump <file>     (flat scene description only; needs no GPU)
+//        adapter_demo --throughput <size> <spp> <devices> [batch_spp=64] [repeats=3]
+//            the GPU path tracer alone through Algorithm<RGB>::Render on `devices` GPUs, timed per call
+//            (the first call uploads the scene and allocates the pools; later ones reuse them), and --
+//            with more than one device -- compared with the image of ONE device, which holds the same
+//            samples (device d renders the indices d, d + G, ...)
 #include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <mutex>
 #include <string>
 
@@ -133,6 +139,60 @@ int main(int argc, char** argv)
     }
     std::fwrite(&d.lens, sizeof d.lens, 1, f);
     std::fclose(f);
+    return 0;
+  }
+  if (argc > 4 && std::string(argv[1]) == "--throughput") {
+    const unsigned t_size = std::atoi(argv[2]), t_spp = std::atoi(argv[3]), t_devices = std::atoi(argv[4]);
+    const unsigned batch_spp = argc > 5 ? std::atoi(argv[5]) : 64, repeats = argc > 6 ? std::atoi(argv[6]) : 3;
+    const cuda::Sensor t_sensor(t_size, t_size, 0.036f, 0.036f);
+    auto run = [&](unsigned n_dev, unsigned n_repeats, bool print) {
+      cuda::CudaPathTracingOptions options;
+      options.devices.clear();
+      for (unsigned d = 0; d < n_dev; d++) options.devices.push_back(int(d));
+      options.max_depth = 32;
+      options.batch_spp = batch_spp;
+      cuda::CudaPathTracing algorithm(options);
+      rendering::Image<RGB> image(t_size, t_size);
+      for (unsigned r = 0; r < n_repeats; r++) {
+        DemoContext context(1, t_spp);
+        const auto t0 = std::chrono::steady_clock::now();
+        image = algorithm.Render(*scene, t_sensor, context);
+        const double seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        const auto& s = algorithm.LastStats();
+        if (print)
+          std::printf("{\"through\": \"Algorithm<RGB>::Render\", \"devices\": %u, \"size\": %u, \"spp\": %u, \"batch_spp\": %u, "
+                      "\"call\": %u, \"seconds\": %.4f, \"Mrays_per_s\": %.1f, \"Mpaths_per_s\": %.1f, \"chained_renders\": %llu}\n",
+                      n_dev, t_size, t_spp, batch_spp, r, seconds, double(s.closest_rays + s.shadow_rays) / seconds / 1e6,
+                      double(s.paths) / seconds / 1e6, static_cast<unsigned long long>(s.chained_renders));
+      }
+      return image;
+    };
+    try {
+      const auto image = run(t_devices, repeats, true);
+      if (t_devices > 1) {
+        const auto single = run(1, 1, false);
+        double worst = 0, sum = 0;
+        for (unsigned y = 0; y < t_size; y++) {
+          for (unsigned x = 0; x < t_size; x++) {
+            const auto& a = image[rendering::Pixel(x, y)];
+            const auto& b = single[rendering::Pixel(x, y)];
+            const double la = a.X() + a.Y() + a.Z(), lb = b.X() + b.Y() + b.Z();
+            worst = std::max(worst, std::fabs(la - lb) / std::max(1e-30, std::max(la, lb)));
+            sum += lb;
+          }
+        }
+        std::printf("%u devices vs 1 device, same samples: worst relative pixel difference %.3g (mean %.6g)\n", t_devices,
+                    worst, sum / (double(t_size) * t_size));
+        if (!(worst < 1e-3)) {
+          std::printf("adapter_demo: MISMATCH\n");
+          return 1;
+        }
+      }
+    } catch (const std::runtime_error& error) {
+      std::printf("pt-cuda failed loudly (no CPU fallback): %s\n", error.what());
+      return 3;
+    }
+    std::printf("adapter_demo: OK\n");
     return 0;
   }
   const cuda::Sensor sensor(size, size, 0.036f, 0.036f * size / size);

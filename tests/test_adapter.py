@@ -70,3 +70,19 @@ def test_cpp_adapter_renders_through_the_reference_interface():
     print(rc.stdout)
     assert rc.returncode == 0, rc.stdout + rc.stderr
     assert "adapter_demo: OK" in rc.stdout and "refused as expected" in rc.stdout
+
+
+@pytest.mark.gpu
+@needs_demo
+def test_cpp_adapter_queues_batches_as_one_wavefront_and_uses_every_device():
+    """Algorithm<RGB>::Render on the GPU path tracer alone: batches of Iterate() are queued and chained (no
+    pool drain between them), contexts persist across Render() calls, and with more than one device the
+    image holds the same samples as one device's (checked inside the demo)."""
+    import torch
+    devices = min(2, torch.cuda.device_count())
+    rc = subprocess.run([DEMO, "--throughput", "512", "256", str(devices), "16", "2"], capture_output=True, text=True, timeout=600)
+    print(rc.stdout)
+    assert rc.returncode == 0, rc.stdout + rc.stderr
+    assert "adapter_demo: OK" in rc.stdout
+    chained = [int(line.split('"chained_renders": ')[1].rstrip("}\n")) for line in rc.stdout.splitlines() if "chained_renders" in line]
+    assert chained and max(chained) >= 1

@@ -5,6 +5,7 @@ import json
 import os
 
 import numpy as np
+import pytest
 
 from conftest import FILM, GOLDEN, golden
 
@@ -92,9 +93,44 @@ def test_estimators_agree_in_expectation(oracle_lib):
     assert np.all(ref_means.mean(0) > 0)
 
 
-def test_reference_luminance_statistics_are_recorded():
+def test_oracle_estimators_match_the_reference_renderer_on_the_cornell_box(oracle):
+    """The Cornell box (mirror, glass, water: emission after non-connectable vertices) -- mean luminance of
+    both oracle estimators against the reference's OWN renderer (MakeRGBPathTracing()->Render, independent
+    runs recorded by scripts/make_golden.py) at two frame sizes (pixel values scale with 1 / (W * H)).  The
+    2 cm light is found by BSDF sampling only, so a mean over 3e7 paths is still heavy-tailed and its sample
+    standard error is an underestimate: the CPU check uses a 99 % interval (2.58 standard errors); the GPU
+    repeats it with 4e9 paths per estimator and the 95 % interval (tests/test_image_parity.py)."""
     stats = json.load(open(os.path.join(GOLDEN, "cornell_luminance.json")))
     assert stats["runs"] == 16 and len(stats["pt_means"]) == 16
+    conv = golden("cornell_converged.npz")
+    for size, spp in ((64, 1024), (128, 384)):
+        runs = conv[f"{size}x{size}.run_means"]
+        cpu_mean, cpu_sem = runs.mean(), runs.std(ddof=1) / np.sqrt(len(runs))
+        for estimator in (0, 1):
+            means = np.array([oracle.render(size, size, *FILM, 0, spp, 500 + 10 * estimator + seed, 0, estimator=estimator)[0].mean()
+                              for seed in range(8)])
+            sem = means.std(ddof=1) / np.sqrt(len(means))
+            assert abs(means.mean() - cpu_mean) <= 2.58 * np.hypot(cpu_sem, sem), (size, estimator, means.mean(), sem, cpu_mean, cpu_sem)
+    # the two sizes of the golden agree with each other once scaled by the pixel count
+    a, b = conv["64x64.run_means"], 4.0 * conv["128x128.run_means"]
+    assert abs(a.mean() - b.mean()) <= 1.96 * np.hypot(a.std(ddof=1) / np.sqrt(len(a)), b.std(ddof=1) / np.sqrt(len(b)))
+    assert abs(a.mean() - stats["pt_mean"]) <= 1.96 * np.hypot(a.std(ddof=1) / np.sqrt(len(a)), stats["pt_std_of_run"] / 4.0)
+
+
+def test_image_metrics():
+    from amber_b200.metrics import box_downsample, luminance, rrmse, water_line_rows
+    rng = np.random.default_rng(3)
+    image = rng.random((32, 48, 3))
+    assert box_downsample(luminance(image), 4).shape == (8, 12)
+    assert rrmse(image, image) == 0.0
+    assert rrmse(1.1 * image, image) == pytest.approx(0.1 * np.sqrt(np.mean(box_downsample(luminance(image)) ** 2)) /
+                                                      box_downsample(luminance(image)).mean())
+    above, below = water_line_rows(1024)
+    assert (above.start, above.stop) == (0, 158) and (below.start, below.stop) == (195, 256)
+    above, below = water_line_rows(1024, 320, 32)
+    assert (above.start, above.stop) == (0, 8) and below.stop - below.start <= 0 or below.start >= 8
+    above, below = water_line_rows(1024, 800, 32)
+    assert above.stop == 0 and (below.start, below.stop) == (0, 8)
 
 
 def test_tonemap_matches_reference(oracle_lib):
