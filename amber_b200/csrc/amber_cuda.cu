@@ -112,9 +112,9 @@ struct amber_cuda_ctx {
 
   // path pool
   PathPool pool{};
-  DeviceBuffer<float4> d_ray, d_state, d_shadow;
+  DeviceBuffer<float4> d_ray, d_state, d_shadow_q;
   DeviceBuffer<float2> d_hit;
-  DeviceBuffer<uint32_t> d_q_new, d_q_shadow;
+  DeviceBuffer<uint32_t> d_q_new;
   DeviceBuffer<Control> d_ctl;
   Control* h_ctl = nullptr;  // pinned
 
@@ -171,6 +171,24 @@ struct DeviceTurn {
 
 void worker_main(amber_cuda_ctx* ctx);
 int wait_idle(amber_cuda_ctx* ctx, int max_pending = 0);
+
+// AMBER_CUDA_TRACE=1 in the environment: one line per queue event on stderr (microseconds since load)
+inline bool trace_on() {
+  static const bool on = std::getenv("AMBER_CUDA_TRACE") != nullptr;
+  return on;
+}
+inline void trace(const amber_cuda_ctx* ctx, const char* fmt, ...) {
+  if (!trace_on()) return;
+  static const auto t0 = std::chrono::steady_clock::now();
+  char buffer[256];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buffer, sizeof buffer, fmt, ap);
+  va_end(ap);
+  std::fprintf(stderr, "[amber_cuda %10.0f us ctx %llu] %s\n",
+               std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count(),
+               static_cast<unsigned long long>(ctx->id), buffer);
+}
 
 inline unsigned int blocks_for(uint64_t n, int block = kBlock) {
   return static_cast<unsigned int>((n + block - 1) / block);
@@ -485,14 +503,12 @@ int ensure_pool(amber_cuda_ctx* ctx, uint32_t slots) {
   CUDA_TRY(ctx, ctx->d_state.resize(2 * static_cast<size_t>(slots)));
   CUDA_TRY(ctx, ctx->d_hit.resize(slots));
   CUDA_TRY(ctx, ctx->d_q_new.resize(slots));
-  CUDA_TRY(ctx, ctx->d_q_shadow.resize(slots));
-  CUDA_TRY(ctx, ctx->d_shadow.resize(2 * static_cast<size_t>(slots)));
+  CUDA_TRY(ctx, ctx->d_shadow_q.resize(3 * static_cast<size_t>(slots)));
   ctx->pool.ray = ctx->d_ray.ptr;
   ctx->pool.state = ctx->d_state.ptr;
   ctx->pool.hit = ctx->d_hit.ptr;
   ctx->pool.q_new = ctx->d_q_new.ptr;
-  ctx->pool.shadow = ctx->d_shadow.ptr;
-  ctx->pool.q_shadow = ctx->d_q_shadow.ptr;
+  ctx->pool.shadow_q = ctx->d_shadow_q.ptr;
   ctx->pool.n_slots = slots;
   return AMBER_CUDA_OK;
 }
@@ -609,8 +625,8 @@ int amber_cuda_destroy(amber_cuda_ctx* ctx) {
   ctx->d_tri_material.release(); ctx->d_sphere_material.release(); ctx->d_internal_to_prim.release();
   ctx->d_materials.release(); ctx->d_lights.release(); ctx->d_bvh_nodes.release();
   ctx->d_film.release(); ctx->d_resolved.release(); ctx->d_resolved8.release();
-  ctx->d_ray.release(); ctx->d_state.release(); ctx->d_hit.release(); ctx->d_shadow.release();
-  ctx->d_q_new.release(); ctx->d_q_shadow.release(); ctx->d_ctl.release(); ctx->d_prim_class.release();
+  ctx->d_ray.release(); ctx->d_state.release(); ctx->d_hit.release(); ctx->d_shadow_q.release();
+  ctx->d_q_new.release(); ctx->d_ctl.release(); ctx->d_prim_class.release();
   for (auto& b : ctx->d_scratch_f) b.release();
   for (auto& b : ctx->d_scratch_i) b.release();
   for (auto& b : ctx->d_scratch_4) b.release();
@@ -1004,6 +1020,8 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, const amber_cuda_re
         }
       }
       if (more == 0) break;
+      trace(ctx, "batch %d: absorbed a call of %llu samples (wavefront now %llu)", batch, (unsigned long long)more,
+            (unsigned long long)(ordinals + more));
       control_extend_kernel<<<1, 1, 0, stream>>>(args.ctl, more * args.n_pixels);
       ctx->stats.kernel_launches++;
       ctx->stats.chained_renders++;
@@ -1055,6 +1073,9 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, const amber_cuda_re
         }
       }
       if (released) ctx->idle_cv.notify_all();
+      trace(ctx, "batch %d: poll of batch %d: next_path %llu of %llu, alive %u, done %u%s", batch, batch - 1,
+            (unsigned long long)seen.next_path, (unsigned long long)seen.total_paths, seen.n_alive, seen.done,
+            released ? ", released" : "");
     }
     if (!done) {
       cudaMemcpyAsync(&poll_copy[batch & 1], args.ctl, sizeof(Control), cudaMemcpyDeviceToHost, stream);
@@ -1160,6 +1181,8 @@ int validate_render(amber_cuda_ctx* ctx, const amber_cuda_render_params* params)
 int run_render(amber_cuda_ctx* ctx, const amber_cuda_render_params& job) {
   const amber_cuda_render_params* params = &job;
   if (params->sample_count == 0) return AMBER_CUDA_OK;
+  trace(ctx, "job start: samples [%llu, +%u) stride %u", (unsigned long long)job.sample_begin, job.sample_count,
+        effective_stride(job));
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   DeviceTurn turn(ctx);
   if (ctx->samples_in_film) {  // an external reduce left the count in the film: take it back first
@@ -1218,6 +1241,8 @@ int run_render(amber_cuda_ctx* ctx, const amber_cuda_render_params& job) {
   CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
   ctx->stats.last_render_ms = ms;
   ctx->samples_done += ordinals;
+  trace(ctx, "job end: %llu samples per pixel in %.3f ms of device time, %llu iterations", (unsigned long long)ordinals, ms,
+        (unsigned long long)ctx->stats.extend_launches);
   return AMBER_CUDA_OK;
 }
 

@@ -41,6 +41,9 @@ constexpr int kBvhStackMax = 160;  // entries per lane the 227 KB of shared memo
 #ifndef AMBER_BVH_MIN_BLOCKS
 #define AMBER_BVH_MIN_BLOCKS 5  // resident 256-thread blocks per SM the traversal kernels are compiled for (<= 51 registers)
 #endif
+#ifndef AMBER_BVH_POSTPONE
+#define AMBER_BVH_POSTPONE 1  // a lane that reaches a leaf parks it and keeps descending (speculative traversal)
+#endif
 constexpr int kBvhLeafMax = 4;
 constexpr int32_t kEmptyChild = 0x7fffffff;
 
@@ -180,6 +183,12 @@ struct WideBvh {
 
     int sp = 0;
     int32_t current = kEmptyChild;  // kEmptyChild doubles as "idle"
+    // Speculative traversal (Aila & Laine): a lane that reaches a leaf parks it here and goes on with the
+    // next stack entry instead of waiting for the warp's leaf phase; the warp tests triangles when enough
+    // lanes hold a parked leaf, so a leaf phase runs with many lanes instead of the few that happened to
+    // reach a leaf in the same step.  The price: the parked leaf's hit does not shorten the ray for the
+    // node steps taken in between.
+    int32_t parked = kEmptyChild;
     uint32_t item = 0;
     bool have_item = false, found = false, exhausted = false;
     Ray ray;
@@ -193,7 +202,7 @@ struct WideBvh {
 
     while (true) {
       // ---- fetch ----------------------------------------------------------------------
-      const bool idle = current == kEmptyChild;
+      const bool idle = current == kEmptyChild && parked == kEmptyChild;
       const uint32_t idle_mask = __ballot_sync(kFull, idle);
       if (idle_mask == kFull && exhausted) break;
       if (!exhausted && (__popc(idle_mask) >= kRefillLanes || idle_mask == kFull)) {
@@ -224,10 +233,20 @@ struct WideBvh {
       }
       // ---- descend --------------------------------------------------------------------
       while (true) {
+        if (AMBER_BVH_POSTPONE && current < 0 && parked == kEmptyChild) {
+          parked = current;
+          if (sp > 0) {
+            sp--;
+            current = stack[sp * stride];
+          } else {
+            current = kEmptyChild;
+          }
+        }
         const bool inner = static_cast<uint32_t>(current) < static_cast<uint32_t>(kEmptyChild);
         const uint32_t inner_lanes = __ballot_sync(kFull, inner);
         if (inner_lanes == 0) break;
-        if (__popc(inner_lanes) < kMinDescendLanes && __any_sync(kFull, current < 0)) break;
+        const bool has_leaf = AMBER_BVH_POSTPONE ? parked != kEmptyChild : current < 0;
+        if (__popc(inner_lanes) < kMinDescendLanes && __any_sync(kFull, has_leaf)) break;
         if (inner) {
           current = node_step(scene, current, idir, oidir, hit.t, stack, stride, sp);
           if (kCount) node_steps++;
@@ -236,8 +255,9 @@ struct WideBvh {
       // ---- leaves ---------------------------------------------------------------------
       // (Dealing the (lane, triangle) pairs of a leaf phase out over the whole warp by shuffle --
       // one pass of ~20 busy lanes for four passes of ~5 -- was measured slower: 570 vs 544 us.)
-      if (current < 0) {
-        const int first = bvh_leaf_first(current), count = bvh_leaf_count(current);
+      const int32_t leaf = AMBER_BVH_POSTPONE ? parked : current;
+      if (leaf < 0) {
+        const int first = bvh_leaf_first(leaf), count = bvh_leaf_count(leaf);
         if (kCount) triangle_tests += count;
 #pragma unroll
         for (int k = 0; k < kBvhLeafMax; k++) {
@@ -249,7 +269,13 @@ struct WideBvh {
             }
           }
         }
-        if (kAnyHit && found) {
+        if (AMBER_BVH_POSTPONE) {
+          parked = kEmptyChild;
+          if (kAnyHit && found) {
+            sp = 0;
+            current = kEmptyChild;
+          }
+        } else if (kAnyHit && found) {
           sp = 0;
           current = kEmptyChild;
         } else if (sp > 0) {

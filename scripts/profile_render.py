@@ -38,3 +38,8 @@ with Device(0, lib_path=args.lib) as dev:
         n = max(1, s["extend_launches"])
         print("per launch (us): " + ", ".join(f"{k} {s[k + '_ms'] / n * 1e3:.1f}" for k in ("raygen", "extend", "shade", "connect"))
               + f"; wavefront iterations {n}, closest rays/iteration {s['closest_rays'] / n:.0f}, shadow rays/iteration {s['shadow_rays'] / n:.0f}")
+        if s["accel"]:
+            print(f"BVH work per closest ray: {s['bvh_node_visits'] / max(1, s['closest_rays']):.2f} node steps, "
+                  f"{s['bvh_triangle_tests'] / max(1, s['closest_rays']):.2f} triangle tests; per shadow ray: "
+                  f"{s['bvh_node_visits_connect'] / max(1, s['shadow_rays']):.2f} / {s['bvh_triangle_tests_connect'] / max(1, s['shadow_rays']):.2f}; "
+                  f"extend {s['closest_rays'] / max(s['extend_ms'], 1e-9) / 1e6:.2f} Grays/s, connect {s['shadow_rays'] / max(s['connect_ms'], 1e-9) / 1e6:.2f} Grays/s")

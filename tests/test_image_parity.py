@@ -19,14 +19,23 @@ tracer (``cornell_luminance.json``: bdpt_mean 0.314 vs pt_mean 0.861) -- its t =
 and its visibility test is "rough" (``bidirectional_path_sampling.h:1006-1010``); the GPU BDPT reproduces that
 (``test_gpu_parity.py::test_bidirectional_path_tracing_matches_reference_golden``).
 
-Tolerances (stated here, measured values in profiles/r02_parity_stats.json):
-  mean luminance : inside the 95 % confidence interval of the CPU reference's runs (1.96 standard errors), and
-                   |NEE - reference estimator| <= 3 combined standard errors from 8 independent seeds each;
-  rRMSE          : 4x4-block luminance, sqrt(mean((I - R)^2)) / mean(R) <= 0.05 above the water line for NEE
-                   at 1024 spp once the converged reference's own residual noise (measured from its two
-                   independent halves) is removed in quadrature, and <= 0.08 raw.  Below the water line every
-                   light path is a caustic found by BSDF sampling in BOTH estimators; the figure is printed and
-                   only bounded by the noise the two estimators show against themselves.
+Tolerances (stated here; measured values in profiles/r02_parity_stats.json).  The built-in scene's light is a
+2 cm square of radiance 1e11: the relative standard deviation of ONE path sample is 100-250 for the reference
+estimator, and for NEE too wherever a caustic (mirror sphere, glass sphere, water) carries the light, so at the
+benchmark's 1024 spp NO unbiased estimator is within 0.05 of the converged image (NEE at 1024 spp differs from
+another NEE run at 1024 spp by 0.65-1.65 rRMSE).  Equality of EXPECTATION is what can be, and is, pinned:
+  mean luminance : both GPU estimators inside the 95 % confidence interval of the CPU reference's runs
+                   (1.96 standard errors), and |NEE - reference estimator| <= 3 combined standard errors
+                   (8 independent seeds each, 4e9 + 9e9 paths);
+  block z-scores : 4x4-pixel blocks at 64 x 64, NEE vs reference estimator, standard errors from the 8 seeds:
+                   mean z within 4 / sqrt(blocks) of zero, mean z^2 < 2;
+  rRMSE          : 4x4-block luminance, sqrt(mean((I - R)^2)) / mean(R), CONVERGED NEE (1e9-1e10 paths) against
+                   the CONVERGED reference estimator (3e10-7e10 paths): <= 0.05 above the water line once the
+                   two images' own residual noise (each measured from its two independent halves) is removed in
+                   quadrature, and <= 0.10 raw.  Below the water line every light path is a caustic found by
+                   BSDF sampling in BOTH estimators: the figure is printed and bounded by 0.5 net.
+  at 1024 spp    : the rRMSE of NEE at the benchmark's sample count is printed next to NEE's own run-to-run
+                   figure and must not exceed 3x it.
 """
 import json
 import os
@@ -64,25 +73,37 @@ def cornell_device(device, cornell):
 @pytest.mark.parametrize("size", [64, 128])
 def test_mean_luminance_is_inside_the_reference_confidence_interval(cornell_device, size):
     """Both GPU estimators against the reference's own renderer at two frame sizes (pixel values scale with
-    1 / (W * H), src/amber/scene/lens_thin.cc:139-148), and against each other."""
+    1 / (W * H), src/amber/scene/lens_thin.cc:139-148), and against each other -- image means and, at 64 x 64,
+    block by block."""
     from amber_b200 import Sensor
+    from amber_b200.metrics import box_downsample, luminance, water_line_rows
     conv = golden("cornell_converged.npz")
     runs = conv[f"{size}x{size}.run_means"]
     cpu_mean, cpu_sem = runs.mean(), runs.std(ddof=1) / np.sqrt(len(runs))
     cornell_device.set_sensor(Sensor(size, size))
-    spp_ref = (1 << 17) * (64 * 64) // (size * size)   # 8 seeds x 5.4e8 paths
-    ref = np.array([render(cornell_device, REFERENCE, spp_ref, 100 + s).mean() for s in range(8)])
-    nee = np.array([render(cornell_device, NEE, spp_ref // 8, 200 + s).mean() for s in range(8)])
+    spp_ref = (1 << 18) * (64 * 64) // (size * size)   # 8 seeds x 1.07e9 paths
+    ref_images = [render(cornell_device, REFERENCE, spp_ref, 100 + s) for s in range(8)]
+    nee_images = [render(cornell_device, NEE, spp_ref // 2, 200 + s) for s in range(8)]
+    ref, nee = np.array([im.mean() for im in ref_images]), np.array([im.mean() for im in nee_images])
     ref_sem, nee_sem = ref.std(ddof=1) / np.sqrt(8), nee.std(ddof=1) / np.sqrt(8)
     print(f"{size}x{size}: CPU reference {cpu_mean:.4f} +- {cpu_sem:.4f} | GPU reference estimator {ref.mean():.4f} +- "
           f"{ref_sem:.4f} | GPU NEE {nee.mean():.4f} +- {nee_sem:.4f}")
     for name, mean, sem in (("reference estimator", ref.mean(), ref_sem), ("NEE", nee.mean(), nee_sem)):
         assert abs(mean - cpu_mean) <= 1.96 * np.hypot(cpu_sem, sem), f"{name}: {mean} vs CPU reference {cpu_mean} +- {cpu_sem}"
     assert abs(nee.mean() - ref.mean()) <= 3.0 * np.hypot(ref_sem, nee_sem), (nee.mean(), ref.mean(), ref_sem, nee_sem)
-    if size == 64:  # the round-1 golden: 16 runs x 256 spp
-        g = json.load(open(os.path.join(GOLDEN, "cornell_luminance.json")))
+    if size == 64:
+        g = json.load(open(os.path.join(GOLDEN, "cornell_luminance.json")))  # the round-1 golden: 16 runs x 256 spp
         half_width = 1.96 * g["pt_std_of_run"] / np.sqrt(g["runs"])
         assert abs(nee.mean() - g["pt_mean"]) <= half_width and abs(ref.mean() - g["pt_mean"]) <= half_width
+        # block by block: z-scores of the 4x4-pixel blocks above the water line
+        above, _ = water_line_rows(size)
+        rb = np.array([box_downsample(luminance(im))[above] for im in ref_images])
+        nb = np.array([box_downsample(luminance(im))[above] for im in nee_images])
+        sigma = np.sqrt(rb.var(0, ddof=1) / 8 + nb.var(0, ddof=1) / 8)
+        lit = rb.mean(0) > 0.01 * rb.mean()
+        z = ((nb.mean(0) - rb.mean(0)) / np.where(sigma > 0, sigma, 1.0))[lit]
+        print(f"block z-scores ({z.size} blocks): mean {z.mean():+.3f}, mean z^2 {np.mean(z * z):.3f}, max |z| {np.abs(z).max():.2f}")
+        assert abs(z.mean()) < 4.0 / np.sqrt(z.size) and np.mean(z * z) < 2.0
 
 
 def test_coarse_blocks_match_the_cpu_reference_image(cornell_device):
@@ -104,27 +125,30 @@ def test_coarse_blocks_match_the_cpu_reference_image(cornell_device):
     assert np.all(np.abs(z[lit]) < 5.0) and np.abs(z[lit]).mean() < 2.0
 
 
-CASES = [  # tag, frame size, reference spp, window rows (first, count) or None
-    ("64x64", 64, 1 << 22, None),
-    ("256x256", 256, 1 << 18, None),
-    ("1024x1024 rows 320-352", 1024, 1 << 19, (320, 32)),
-    ("1024x1024 rows 800-832", 1024, 1 << 19, (800, 32)),
+CASES = [  # tag, frame size, reference spp, converged-NEE spp, window rows (first, count) or None
+    ("64x64", 64, 1 << 23, 1 << 20, None),
+    ("256x256", 256, 1 << 20, 1 << 17, None),
+    ("1024x1024 rows 320-352", 1024, 1 << 21, 1 << 18, (320, 32)),
+    ("1024x1024 rows 800-832", 1024, 1 << 19, 1 << 16, (800, 32)),
 ]
 
 
-@pytest.mark.parametrize("tag,size,spp_ref,window_rows", CASES, ids=[c[0] for c in CASES])
-def test_rrmse_against_the_converged_reference_estimator(cornell_device, tag, size, spp_ref, window_rows):
-    """rRMSE of NEE at 1024 spp (the benchmark's sample count) against the converged
-    reference estimator, 4x4-block luminance; 1.7e10 reference paths per case.  At 1024 x 1024 a window of 32
-    rows is rendered (the pixel window keeps the full frame's random streams, so it equals a crop)."""
+@pytest.mark.parametrize("tag,size,spp_ref,spp_nee,window_rows", CASES, ids=[c[0] for c in CASES])
+def test_rrmse_against_the_converged_reference_estimator(cornell_device, tag, size, spp_ref, spp_nee, window_rows):
+    """4x4-block luminance rRMSE of NEE against the converged reference estimator.  At
+    1024 x 1024 a window of 32 rows is rendered (the pixel window keeps the full frame's random streams, so it
+    equals a crop of the full render)."""
     from amber_b200 import Sensor
     from amber_b200.metrics import rrmse, water_line_rows
     cornell_device.set_sensor(Sensor(size, size))
     window = (0, 0) if window_rows is None else (window_rows[0] * size, window_rows[1] * size)
-    half_a = render(cornell_device, REFERENCE, spp_ref // 2, 300, window)
-    half_b = render(cornell_device, REFERENCE, spp_ref // 2, 301, window)
-    reference = 0.5 * (half_a + half_b)
-    nee = render(cornell_device, NEE, 1024, 1, window)
+    ref_a = render(cornell_device, REFERENCE, spp_ref // 2, 300, window)
+    ref_b = render(cornell_device, REFERENCE, spp_ref // 2, 301, window)
+    nee_a = render(cornell_device, NEE, spp_nee // 2, 302, window)
+    nee_b = render(cornell_device, NEE, spp_nee // 2, 303, window)
+    reference, converged = 0.5 * (ref_a + ref_b), 0.5 * (nee_a + nee_b)
+    bench_a = render(cornell_device, NEE, 1024, 1, window)     # the benchmark's sample count, two runs
+    bench_b = render(cornell_device, NEE, 1024, 2, window)
     if window_rows is None:
         above, below = water_line_rows(size)
         crop = lambda image: image  # noqa: E731
@@ -133,18 +157,24 @@ def test_rrmse_against_the_converged_reference_estimator(cornell_device, tag, si
         crop = lambda image: image[window_rows[0]: window_rows[0] + window_rows[1]]  # noqa: E731
         outside = np.ones(size, dtype=bool)
         outside[window_rows[0]: window_rows[0] + window_rows[1]] = False
-        assert not nee[outside].any() and not reference[outside].any()  # nothing lands outside the window
+        assert not converged[outside].any() and not reference[outside].any()  # nothing lands outside the window
     for name, rows in (("above the water line", above), ("below the water line", below)):
         if rows.stop <= rows.start:
             continue
-        raw = rrmse(crop(nee), crop(reference), rows)
-        noise = 0.5 * rrmse(crop(half_a), crop(half_b), rows)   # of the mean of the two halves
-        net = float(np.sqrt(max(0.0, raw * raw - noise * noise)))
-        print(f"{tag}, {name}: rRMSE {raw:.4f} (reference's own residual noise {noise:.4f}, net {net:.4f})")
+        raw = rrmse(crop(converged), crop(reference), rows)
+        noise_ref = 0.5 * rrmse(crop(ref_a), crop(ref_b), rows)    # of the mean of two halves
+        noise_nee = 0.5 * rrmse(crop(nee_a), crop(nee_b), rows)
+        net = float(np.sqrt(max(0.0, raw * raw - noise_ref * noise_ref - noise_nee * noise_nee)))
+        at_bench = rrmse(crop(bench_a), crop(reference), rows)
+        bench_own = rrmse(crop(bench_a), crop(bench_b), rows) / np.sqrt(2.0)
+        print(f"{tag}, {name}: converged NEE vs converged reference estimator rRMSE {raw:.4f} (own residual noise: "
+              f"reference {noise_ref:.4f}, NEE {noise_nee:.4f}; net {net:.4f}) | NEE at 1024 spp {at_bench:.3f} "
+              f"(run to run {bench_own:.3f})")
         if name.startswith("above"):
-            assert net <= 0.05 and raw <= 0.08, (tag, raw, noise)
+            assert net <= 0.05 and raw <= 0.10, (tag, raw, noise_ref, noise_nee)
         else:
-            assert np.isfinite(raw) and net <= 0.5, (tag, raw, noise)
+            assert np.isfinite(raw) and net <= 0.5, (tag, raw, noise_ref, noise_nee)
+        assert at_bench <= 3.0 * max(bench_own, noise_ref, 0.05), (tag, at_bench, bench_own)
 
 
 def test_estimators_agree_with_glass_and_mirror_on_the_path(device):
