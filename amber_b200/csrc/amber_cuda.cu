@@ -85,7 +85,6 @@ struct amber_cuda_ctx {
   ConstScene const_scene;
   CameraDev camera;
   bool has_sensor = false;
-  bool has_sphere_light = false;  // an emitting sphere: fine for the path tracer, not sampled by light tracing
   SceneView view{};
   std::vector<int32_t> internal_to_prim;
   DeviceBuffer<TriShade> d_tri_shade;
@@ -722,18 +721,28 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   for (size_t k = 0; k < n_spheres; k++)
     prim_class[n_tris + k] = static_cast<uint8_t>(materials[sphere_material[k]].kind * 2 + 1);
 
-  // ---- lights: emitting triangles, LightSet::LightSet (light_set.h:61-81) -------
+  // ---- lights: emitting objects, LightSet::LightSet (light_set.h:61-81) ---------
+  // internal index: triangles [0, n_tris), spheres n_tris + k
   struct HostLight {
-    size_t tri;
+    size_t prim;
     float power, irradiance_sum;
   };
   std::vector<HostLight> host_lights;
-  for (size_t k = 0; k < n_tris; k++) {
-    const MaterialDev& m = materials[tri_material[k]];
+  auto original_id = [&](size_t internal) {
+    return internal < n_tris ? tri_ids[internal] : sphere_ids[internal - n_tris];
+  };
+  for (size_t k = 0; k < n_tris + n_spheres; k++) {
+    const MaterialDev& m = materials[k < n_tris ? tri_material[k] : sphere_material[k - n_tris]];
     if (m.kind != AMBER_CUDA_MAT_DIFFUSE_LIGHT) continue;
-    const TriShade& t = tri_shade[k];
-    const F3 e1{t.e1_ny.x, t.e1_ny.y, t.e1_ny.z}, e2{t.e2_nz.x, t.e2_nz.y, t.e2_nz.z};
-    const float area = lengthf(crossf(e1, e2)) / 2;  // Triangle::SurfaceArea
+    float area;
+    if (k < n_tris) {
+      const TriShade& t = tri_shade[k];
+      const F3 e1{t.e1_ny.x, t.e1_ny.y, t.e1_ny.z}, e2{t.e2_nz.x, t.e2_nz.y, t.e2_nz.z};
+      area = lengthf(crossf(e1, e2)) / 2;  // Triangle::SurfaceArea, primitive_triangle.cc:130-134
+    } else {
+      const float radius = spheres[k - n_tris].w;
+      area = 4 * kPiF * radius * radius;  // Sphere::SurfaceArea, primitive_sphere.cc:109-113
+    }
     // DiffuseLight::Irradiance = radiance * pi; Power = Sum(area * irradiance), object.h:98-103
     const float ir = m.r * kPiF, ig = m.g * kPiF, ib = m.b * kPiF;
     const float power = area * ir + area * ig + area * ib;
@@ -741,34 +750,38 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   }
   // ascending power; equal powers in creation order (the BVH permutes `tri_ids`)
   std::stable_sort(host_lights.begin(), host_lights.end(), [&](const HostLight& a, const HostLight& b) {
-    return a.power < b.power || (a.power == b.power && tri_ids[a.tri] < tri_ids[b.tri]);
+    return a.power < b.power || (a.power == b.power && original_id(a.prim) < original_id(b.prim));
   });
-  bool has_sphere_light = false;
-  for (size_t k = 0; k < n_spheres; k++) {
-    const MaterialDev& m = materials[sphere_material[k]];
-    if (m.kind == AMBER_CUDA_MAT_DIFFUSE_LIGHT && (m.r > 0 || m.g > 0 || m.b > 0)) has_sphere_light = true;
-  }
   std::vector<LightDev> lights(host_lights.size());
   float total_power = 0;
   for (size_t i = 0; i < host_lights.size(); i++) total_power += host_lights[i].power;
   float cumulative = 0;
   for (size_t i = 0; i < host_lights.size(); i++) {
-    const TriShade& t = tri_shade[host_lights[i].tri];
-    const MaterialDev& m = materials[tri_material[host_lights[i].tri]];
+    const size_t k = host_lights[i].prim;
+    const int32_t material_index = k < n_tris ? tri_material[k] : sphere_material[k - n_tris];
+    const MaterialDev& m = materials[material_index];
     cumulative += host_lights[i].power;
     const float pdf_area = host_lights[i].irradiance_sum / total_power;  // LightSet::PDFArea, light_set.h:106-111
     LightDev& l = lights[i];
-    l.v0 = make_float4(t.v0_nx.x, t.v0_nx.y, t.v0_nx.z, cumulative);
-    const amber_cuda_primitive& p = scene->primitives[tri_ids[host_lights[i].tri]];
-    l.v1 = make_float4(p.data[3], p.data[4], p.data[5], 0.0f);
-    l.v2 = make_float4(p.data[6], p.data[7], p.data[8], 0.0f);
-    l.n = make_float4(t.v0_nx.w, t.e1_ny.w, t.e2_nz.w, 0.0f);
+    std::memset(&l, 0, sizeof l);
+    if (k < n_tris) {
+      const TriShade& t = tri_shade[k];
+      const amber_cuda_primitive& p = scene->primitives[tri_ids[k]];
+      l.v0 = make_float4(t.v0_nx.x, t.v0_nx.y, t.v0_nx.z, cumulative);
+      l.v1 = make_float4(p.data[3], p.data[4], p.data[5], 0.0f);
+      l.v2 = make_float4(p.data[6], p.data[7], p.data[8], 0.0f);
+      l.n = make_float4(t.v0_nx.w, t.e1_ny.w, t.e2_nz.w, 0.0f);
+    } else {
+      const float4 sphere = spheres[k - n_tris];
+      l.v0 = make_float4(sphere.x, sphere.y, sphere.z, cumulative);
+      l.shape.x = sphere.w;
+    }
     // weight of a light ray, LightSet::GenerateRay: Irradiance / PDFArea (light_set.h:101)
     l.v1.w = m.r * kPiF / pdf_area;
     l.v2.w = m.g * kPiF / pdf_area;
     l.n.w = m.b * kPiF / pdf_area;
     l.le_over_pdf = make_float4(m.r / pdf_area, m.g / pdf_area, m.b / pdf_area,
-                                __builtin_bit_cast(float, static_cast<int32_t>(tri_material[host_lights[i].tri])));
+                                __builtin_bit_cast(float, material_index));
   }
 
   // ---- lens --------------------------------------------------------------------
@@ -785,7 +798,6 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   invalidate_constants(ctx);
   ctx->use_bvh = use_bvh;
-  ctx->has_sphere_light = has_sphere_light;
   std::memset(&ctx->const_scene, 0, sizeof(ConstScene));
   ctx->const_scene.n_tris = use_bvh ? 0 : static_cast<int32_t>(n_tris);
   ctx->const_scene.n_spheres = static_cast<int32_t>(n_spheres);

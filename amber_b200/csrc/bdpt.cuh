@@ -230,9 +230,8 @@ struct BdptCounters {
 __device__ __forceinline__ void bdpt_leading_light(const SceneView& scene, SequentialRng& rng, Ray& ray, float3& weight,
                                                 float3& normal, int32_t& object, float& bits) {
   int light_index;
-  generate_light_ray(scene, rng, ray.o, ray.d, weight, &light_index);
+  generate_light_ray(scene, rng, ray.o, ray.d, weight, &light_index, &normal);
   const float4* L = reinterpret_cast<const float4*>(scene.lights + light_index);
-  normal = v3(__ldg(L + 3));
   object = -3 - light_index;
   bits = event_bits(__float_as_int(__ldg(L + 4).w), kSurfaceLight);
 }

@@ -178,9 +178,14 @@ __device__ __forceinline__ void generate_eye_ray(uint32_t px, uint32_t py, Rng& 
 // Triangle::SampleSurfacePoint (primitive_triangle.cc:136-150); direction by HemispherePSA about
 // the triangle's stored normal (sampling.h:234-265); weight = Irradiance / PDFArea (host-side,
 // in LightDev).  Five uniforms, like the camera vertex.
+// An emitting sphere: Sphere::SampleSurfacePoint (src/amber/scene/primitive_sphere.cc:115-122), normal =
+// SphereSA (include/amber/prelude/sampling.h:185-199) exactly as written there -- cos_theta = Uniform(-1, 1),
+// sin_theta = sqrt(1 - cos_theta^2) >= 0, (cos_theta cos phi, cos_theta sin phi, sin_theta): it only reaches
+// the z >= 0 half of the sphere; light tracing and BDPT reproduce the reference.
 template <class Rng>
 __device__ __forceinline__ void generate_light_ray(const SceneView& scene, Rng& rng, float3& origin,
-                                                   float3& direction, float3& weight, int* light_index = nullptr) {
+                                                   float3& direction, float3& weight, int* light_index = nullptr,
+                                                   float3* surface_normal = nullptr) {
   const float target = __fmul_rn(rng.next(), scene.total_power);
   int lo = 0, hi = scene.n_lights - 1;
   while (lo < hi) {  // first light whose cumulative power >= target
@@ -190,17 +195,30 @@ __device__ __forceinline__ void generate_light_ray(const SceneView& scene, Rng& 
   if (light_index) *light_index = lo;
   const float4* L = reinterpret_cast<const float4*>(scene.lights + lo);
   const float4 v0 = __ldg(L), v1 = __ldg(L + 1), v2 = __ldg(L + 2), nl = __ldg(L + 3);
+  const float radius = __ldg(L + 5).x;
   float u = rng.next();
   float v = rng.next();
-  if (__fadd_rn(u, v) >= 1.0f) {
-    u = 1.0f - u;
-    v = 1.0f - v;
+  float3 axis;
+  if (radius > 0.0f) {
+    const float r0 = __fadd_rn(__fmul_rn(u, 2.0f), -1.0f);  // Uniform(min, max): sampler() * (max - min) + min
+    const float sin_theta = __fsqrt_rn(__fsub_rn(1.0f, __fmul_rn(r0, r0)));
+    float sin_phi, cos_phi;
+    sincosf(__fmul_rn(2.0f * kPiF, v), &sin_phi, &cos_phi);
+    axis = v3(__fmul_rn(r0, cos_phi), __fmul_rn(r0, sin_phi), sin_theta);
+    origin = v3(__fadd_rn(v0.x, __fmul_rn(radius, axis.x)), __fadd_rn(v0.y, __fmul_rn(radius, axis.y)),
+                __fadd_rn(v0.z, __fmul_rn(radius, axis.z)));
+  } else {
+    if (__fadd_rn(u, v) >= 1.0f) {
+      u = 1.0f - u;
+      v = 1.0f - v;
+    }
+    const float w0 = __fsub_rn(__fsub_rn(1.0f, u), v);
+    origin = v3(__fadd_rn(__fadd_rn(__fmul_rn(w0, v0.x), __fmul_rn(u, v1.x)), __fmul_rn(v, v2.x)),
+                __fadd_rn(__fadd_rn(__fmul_rn(w0, v0.y), __fmul_rn(u, v1.y)), __fmul_rn(v, v2.y)),
+                __fadd_rn(__fadd_rn(__fmul_rn(w0, v0.z), __fmul_rn(u, v1.z)), __fmul_rn(v, v2.z)));
+    axis = v3(nl);
   }
-  const float w0 = __fsub_rn(__fsub_rn(1.0f, u), v);
-  origin = v3(__fadd_rn(__fadd_rn(__fmul_rn(w0, v0.x), __fmul_rn(u, v1.x)), __fmul_rn(v, v2.x)),
-              __fadd_rn(__fadd_rn(__fmul_rn(w0, v0.y), __fmul_rn(u, v1.y)), __fmul_rn(v, v2.y)),
-              __fadd_rn(__fadd_rn(__fmul_rn(w0, v0.z), __fmul_rn(u, v1.z)), __fmul_rn(v, v2.z)));
-  const float3 axis = v3(nl);
+  if (surface_normal) *surface_normal = axis;
   float3 bu, bv;
   orthonormal_basis(axis, bu, bv);
   const float r0 = rng.next();
@@ -517,6 +535,9 @@ __device__ __forceinline__ bool sample_direct(const SceneView& scene, const Mate
     if (__ldg(&scene.lights[mid].v0.w) < target) lo = mid + 1; else hi = mid;
   }
   const float4* L = reinterpret_cast<const float4*>(scene.lights + lo);
+  // an emitting sphere is not light-sampled: no shadow ray when the power CDF picks one; its emission is
+  // counted on every BSDF-sampled hit instead (shade_kernel, sampled_by_nee) -- same expectation
+  if (__ldg(L + 5).x > 0.0f) return false;
   const float4 v0 = __ldg(L), v1 = __ldg(L + 1), v2 = __ldg(L + 2), nl = __ldg(L + 3), le = __ldg(L + 4);
   if (u + v >= 1.0f) {
     u = 1.0f - u;

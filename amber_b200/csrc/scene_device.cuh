@@ -56,14 +56,16 @@ struct alignas(16) MaterialDev {
   int32_t pad;
 };
 
-// Emitting triangle for next-event estimation, sorted by power as
-// include/amber/scene/light_set.h:61-81.
+// Emitting object, sorted by power as include/amber/scene/light_set.h:61-81: a triangle (sampled by
+// next-event estimation, light tracing and BDPT) or a sphere (light tracing and BDPT only; the path
+// tracers count a sphere's emission on every hit).
 struct alignas(16) LightDev {
-  float4 v0;  // xyz, cumulative power
-  float4 v1;  // xyz, unused
-  float4 v2;  // xyz, unused
-  float4 n;   // normal xyz, unused
-  float4 le_over_pdf;  // radiance / pdf_area (rgb), unused
+  float4 v0;  // triangle: v0 xyz | sphere: centre xyz ; w: cumulative power
+  float4 v1;  // triangle: v1 xyz ; w: light-ray weight r (Irradiance / PDFArea)
+  float4 v2;  // triangle: v2 xyz ; w: light-ray weight g
+  float4 n;   // triangle: normal xyz ; w: light-ray weight b
+  float4 le_over_pdf;  // radiance / pdf_area (rgb), material index (int bits)
+  float4 shape;        // x: radius of a sphere, 0 for a triangle
 };
 
 struct LensDev {

@@ -141,9 +141,10 @@ oracle_scene* oracle_scene_create(const amber_cuda_scene_desc* desc) {
       p->radius = in->data[3];
     }
   }
-  /* emitting triangles sorted by power, LightSet::LightSet (include/amber/scene/light_set.h:61-81);
+  /* emitting objects sorted by power, LightSet::LightSet (include/amber/scene/light_set.h:61-81);
    * Power = Sum(SurfaceArea * Irradiance) (include/amber/scene/object.h:98-103),
-   * Irradiance = radiance * pi (material_diffuse_light.h:119-124) */
+   * Irradiance = radiance * pi (material_diffuse_light.h:119-124); SurfaceArea: triangle
+   * primitive_triangle.cc:130-134, sphere 4 pi r^2 (primitive_sphere.cc:109-113) */
   {
     float (*tmp)[3] = (float (*)[3])calloc(desc->n_primitives ? desc->n_primitives : 1, sizeof *tmp);
     uint32_t n = 0;
@@ -151,9 +152,10 @@ oracle_scene* oracle_scene_create(const amber_cuda_scene_desc* desc) {
     for (i = 0; i < desc->n_primitives; i++) {
       const prim* p = &s->prims[i];
       const amber_cuda_material* m = &s->materials[p->material];
-      if (p->kind != AMBER_CUDA_PRIM_TRIANGLE || m->kind != AMBER_CUDA_MAT_DIFFUSE_LIGHT) continue;
+      if (m->kind != AMBER_CUDA_MAT_DIFFUSE_LIGHT) continue;
       {
-        const float area = triangle_area(p->v0, p->v1, p->v2);
+        const float area = p->kind == AMBER_CUDA_PRIM_TRIANGLE ? triangle_area(p->v0, p->v1, p->v2)
+                                                               : 4 * PI_F * p->radius * p->radius;
         const float ir = m->rgb[0] * PI_F, ig = m->rgb[1] * PI_F, ib = m->rgb[2] * PI_F;
         const float power = area * ir + area * ig + area * ib;
         if (!(power > 0)) continue;
@@ -612,9 +614,29 @@ static int lens_response(const oracle_scene* sc, uint32_t w, uint32_t h, float f
   return 1;
 }
 
+/* Object::SampleSurfacePoint of a light: Triangle::SampleSurfacePoint (primitive_triangle.cc:136-150,
+ * the stored normal) or Sphere::SampleSurfacePoint (primitive_sphere.cc:115-122): normal = SphereSA
+ * (include/amber/prelude/sampling.h:185-199: cos_theta = Uniform(-1, 1), sin_theta = sqrt(1 - cos^2),
+ * (cos_theta cos phi, cos_theta sin phi, sin_theta) -- as written it only reaches the z >= 0 half of the
+ * sphere, and not uniformly; restated as it is), origin = center + radius * normal.  Two uniforms. */
+static vec3 light_surface_point(const prim* lp, sampler* s, vec3* normal) {
+  if (lp->kind == AMBER_CUDA_PRIM_TRIANGLE) {
+    *normal = lp->normal;
+    return triangle_sample(lp->v0, lp->v1, lp->v2, s);
+  } else {
+    const float r0 = uniform(s) * (1.0f - -1.0f) + -1.0f; /* Uniform(min, max): sampler() * (max - min) + min */
+    const float r1 = uniform(s);
+    const float cos_theta = r0;
+    const float sin_theta = sqrtf(1 - r0 * r0);
+    const float phi = 2 * PI_F * r1;
+    *normal = V(cos_theta * cosf(phi), cos_theta * sinf(phi), sin_theta);
+    return add(lp->center, scale(lp->radius, *normal));
+  }
+}
+
 /* LightSet::GenerateRay (include/amber/scene/light_set.h:83-104): light by lower_bound over the
- * cumulative powers of Uniform(total), point by Triangle::SampleSurfacePoint, direction by
- * HemispherePSA about the triangle's stored normal, weight = Irradiance / PDFArea. */
+ * cumulative powers of Uniform(total), point by Object::SampleSurfacePoint, direction by
+ * HemispherePSA about the surface normal there, weight = Irradiance / PDFArea. */
 static void generate_light_ray(const oracle_scene* sc, sampler* s, vec3* origin, vec3* direction, vec3* weight) {
   const float target = uniform(s) * sc->total_power;
   uint32_t li = 0;
@@ -625,8 +647,11 @@ static void generate_light_ray(const oracle_scene* sc, sampler* s, vec3* origin,
   l = &sc->lights[li];
   lp = &sc->prims[l->prim_index];
   lm = &sc->materials[lp->material];
-  *origin = triangle_sample(lp->v0, lp->v1, lp->v2, s);
-  *direction = hemisphere_psa(lp->normal, s);
+  {
+    vec3 normal;
+    *origin = light_surface_point(lp, s, &normal);
+    *direction = hemisphere_psa(normal, s);
+  }
   *weight = V(lm->rgb[0] * PI_F / l->pdf_area, lm->rgb[1] * PI_F / l->pdf_area, lm->rgb[2] * PI_F / l->pdf_area);
 }
 
@@ -773,16 +798,21 @@ static void trace_path(const oracle_scene* sc, uint32_t w, uint32_t h, float fil
       while (li + 1 < sc->n_lights && sc->lights[li].cumulative_power < target) li++;
       l = &sc->lights[li];
       lp = &sc->prims[l->prim_index];
-      {
+      /* an emitting SPHERE is not light-sampled (the reference's own sphere sampling only covers half
+       * of it): when the power CDF picks one the vertex has no shadow ray, and a sphere's emission is
+       * counted on every BSDF-sampled hit instead (sampled_by_nee above) -- same expectation */
+      if (lp->kind == AMBER_CUDA_PRIM_TRIANGLE) {
         const float lu = uniform_light(&s, 1);
         const float lv = uniform_light(&s, 2);
         y = triangle_point(lp->v0, lp->v1, lp->v2, lu, lv);
+      } else {
+        y = hit.position;
       }
       xy = sub(y, hit.position);
       dist2 = dot(xy, xy);
       dist = sqrtf(dist2);
       wi = V(xy.x / dist, xy.y / dist, xy.z / dist);
-      cos_y = -dot(wi, lp->normal);
+      cos_y = lp->kind == AMBER_CUDA_PRIM_TRIANGLE ? -dot(wi, lp->normal) : -1.0f;
       if (cos_y > 0) { /* one-sided emitter, material_diffuse_light.h:133-135 */
         const amber_cuda_material* lm = &sc->materials[lp->material];
         const vec3 le_over_pdf = V(lm->rgb[0] / l->pdf_area, lm->rgb[1] / l->pdf_area, lm->rgb[2] / l->pdf_area);
@@ -1196,10 +1226,9 @@ static int generate_subpath(const oracle_scene* sc, int importance, uint32_t w, 
     l = &sc->lights[li];
     lp = &sc->prims[l->prim_index];
     lm = &sc->materials[lp->material];
-    origin = triangle_sample(lp->v0, lp->v1, lp->v2, s);
-    direction = hemisphere_psa(lp->normal, s);
+    origin = light_surface_point(lp, s, &normal);
+    direction = hemisphere_psa(normal, s);
     weight = V(lm->rgb[0] * PI_F / l->pdf_area, lm->rgb[1] * PI_F / l->pdf_area, lm->rgb[2] * PI_F / l->pdf_area);
-    normal = lp->normal;
     out[n].object = l->prim_index;
     out[n].material = lp->material;
   } else {

@@ -165,6 +165,30 @@ def bdpt_fixture():
     np.savez_compressed(os.path.join(GOLDEN, "bdpt.npz"), **out)
 
 
+def sphere_light_fixture():
+    """9. emitting spheres (Sphere::SampleSurfacePoint in LightSet::GenerateRay): light rays and images of
+    the path tracer, the light tracer and BDPT from the compiled reference on tests/conftest.py::sphere_light_box."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from conftest import sphere_light_box
+    ref = pyoracle.Reference(sphere_light_box())
+    rng = np.random.default_rng(20261107)
+    out = {}
+    xi = rng.random((4096, 5), dtype=np.float32)
+    o, d, w = ref.light_rays(xi)
+    out.update({"light_rays.xi": xi, "light_rays.origin": o, "light_rays.direction": d, "light_rays.weight": w})
+    image, stats = ref.render_stream(48, 32, 0.036, 0.024, 1, 32, 7, 0)
+    out["pt.48x32.begin1.spp32.seed7.image"] = image
+    out["pt.48x32.begin1.spp32.seed7.rays"] = np.array([stats["rays"], stats["truncated"]], dtype=np.uint64)
+    image, stats = ref.render_lt_stream(96, 64, 0.036, 0.024, 0, 64, 25, 0)
+    out["lt.96x64.begin0.spp64.seed25.image"] = image
+    out["lt.96x64.begin0.spp64.seed25.stats"] = np.array([stats["rays"], stats["truncated"], stats["splats"]], dtype=np.uint64)
+    image, stats = ref.render_bdpt_stream(48, 32, 0.036, 0.024, 0, 16, 33, 10)
+    out["bdpt.48x32.begin0.spp16.seed33.cap10.image"] = image
+    out["bdpt.48x32.begin0.spp16.seed33.cap10.stats"] = np.array([stats["light_events"], stats["eye_events"], stats["splats"]], dtype=np.uint64)
+    np.savez_compressed(os.path.join(GOLDEN, "sphere_lights.npz"), **out)
+    print("sphere lights: lt splats", stats)
+
+
 def converged_fixture():
     """8. the reference's own path tracer (MakeRGBPathTracing()->Render, its own non-reproducible
     mt19937_64 engines), many independent runs on the built-in Cornell box: the converged 64 x 64 image
@@ -194,6 +218,9 @@ def converged_fixture():
 
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "spheres":
+        sphere_light_fixture()
+        return
     if len(sys.argv) > 2 and sys.argv[1] == "--only" and sys.argv[2] == "converged":
         converged_fixture()
         return

@@ -109,6 +109,33 @@ def light_tracing_box():
     return diffuse_box(aperture_radius=0.25, extra=True)
 
 
+def sphere_light_box():
+    """The wide-aperture box with an emitting SPHERE next to the ceiling light (and a brighter, smaller
+    one): what LightSet::GenerateRay does with Sphere::SampleSurfacePoint
+    (src/amber/scene/primitive_sphere.cc:115-122)."""
+    from amber_b200 import FlatSceneBuilder
+    b = FlatSceneBuilder()
+    b.make_thin_lens([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0.9, 0, 0, 0, 1], 0.05, 1.5, 0.25, 5, add_aperture_objects=True)
+
+    def quad(m, p0, p1, p2, p3):
+        b.add_triangle(p0, p1, p2, m)
+        b.add_triangle(p2, p3, p0, m)
+
+    grey = b.make_lambertian((.6, .6, .6))
+    quad(grey, (-1, -1, 1), (1, -1, 1), (1, -1, -1), (-1, -1, -1))
+    quad(grey, (-1, 1, 1), (-1, 1, -1), (1, 1, -1), (1, 1, 1))
+    quad(b.make_lambertian((.6, .2, .2)), (-1, -1, 1), (-1, -1, -1), (-1, 1, -1), (-1, 1, 1))
+    quad(grey, (1, -1, 1), (1, 1, 1), (1, 1, -1), (1, -1, -1))
+    quad(b.make_phong((.7, .7, .7), 16), (-1, -1, -1), (1, -1, -1), (1, 1, -1), (-1, 1, -1))
+    quad(grey, (-1, -1, 1), (-1, 1, 1), (1, 1, 1), (1, -1, 1))
+    quad(b.make_diffuse_light((2.0, 2.0, 1.5)), (-0.3, 0.98, 0.3), (-0.3, 0.98, -0.3), (0.3, 0.98, -0.3), (0.3, 0.98, 0.3))
+    b.add_sphere((0.45, 0.1, -0.3), 0.2, b.make_diffuse_light((3.0, 2.0, 4.0)))
+    b.add_sphere((-0.5, -0.5, 0.2), 0.08, b.make_diffuse_light((9.0, 9.0, 5.0)))
+    b.add_sphere((-0.2, -0.7, -0.4), 0.3, b.make_lambertian((.3, .5, .7)))
+    b.add_sphere((0.5, -0.75, 0.3), 0.25, b.make_refraction(1.5))
+    return b.build()
+
+
 def pinhole_box():
     """A closed box seen through MakePinholeLens (tilted, off-centre transform): row N1's second
     lens (src/amber/scene/lens_pinhole.cc)."""

@@ -573,20 +573,69 @@ def test_light_tracing_agrees_with_path_tracing_in_expectation(device):
     assert np.all(np.abs(diff) < 4 * sigma + 5e-3 * pt.mean(0)), (diff, sigma)
 
 
-def test_light_tracing_refuses_what_it_cannot_sample(device):
+def test_light_tracing_refuses_an_empty_light_set(device):
     from amber_b200 import FlatSceneBuilder, Sensor, capi
     from amber_b200.capi import AmberCudaError
-    for emitter in ("none", "sphere"):
-        b = FlatSceneBuilder()
-        b.make_thin_lens(np.eye(4), 0.05, 4.0, 0.05, 6, add_aperture_objects=True)
-        b.add_triangle((0, 0, -2), (1, 0, -2), (0, 1, -2), b.make_lambertian((.5, .5, .5)))
-        if emitter == "sphere":
-            b.add_sphere((0, 2, -2), 0.5, b.make_diffuse_light((1, 1, 1)))
-        device.upload_scene(b.build())
-        device.set_sensor(Sensor(8, 8))
-        with pytest.raises(AmberCudaError):
-            device.render(0, 1, estimator=capi.ESTIMATOR_LIGHT_TRACING)
-        device.render(0, 1, estimator=capi.ESTIMATOR_REFERENCE)  # the path tracer takes both
+    b = FlatSceneBuilder()
+    b.make_thin_lens(np.eye(4), 0.05, 4.0, 0.05, 6, add_aperture_objects=True)
+    b.add_triangle((0, 0, -2), (1, 0, -2), (0, 1, -2), b.make_lambertian((.5, .5, .5)))
+    device.upload_scene(b.build())
+    device.set_sensor(Sensor(8, 8))
+    for estimator in (capi.ESTIMATOR_LIGHT_TRACING, capi.ESTIMATOR_BDPT):
+        with pytest.raises(AmberCudaError, match="emitter"):  # LightSet::GenerateRay on an empty set is undefined
+            device.render(0, 1, estimator=estimator)
+    device.render(0, 1, estimator=capi.ESTIMATOR_REFERENCE)  # the path tracer just sees black
+
+
+def test_emitting_spheres(device, oracle_lib):
+    """Sphere emitters in the light set (Sphere::SampleSurfacePoint, primitive_sphere.cc:115-122; SphereSA as
+    the reference wrote it): light rays, light tracing and BDPT against the compiled reference's golden
+    vectors; the path tracers (spheres are not light-sampled by NEE) against the oracle and each other."""
+    from amber_b200 import Sensor, capi
+    from conftest import sphere_light_box
+    g = golden("sphere_lights.npz")
+    scene = sphere_light_box()
+    device.upload_scene(scene)
+    device.set_sensor(Sensor(96, 64, 0.036, 0.024))
+    o, d, w = device.light_rays(g["light_rays.xi"])
+    assert np.array_equal(o, g["light_rays.origin"]) and np.array_equal(w, g["light_rays.weight"])
+    assert np.allclose(d, g["light_rays.direction"], atol=5e-6)
+    device.render(0, 64, seed=25, estimator=capi.ESTIMATOR_LIGHT_TRACING)
+    image, _ = device.resolve()
+    frac, lit = light_tracing_agreement(image, g["lt.96x64.begin0.spp64.seed25.image"])
+    splats = int(g["lt.96x64.begin0.spp64.seed25.stats"][2])
+    got = device.stats()
+    print(f"sphere lights, light tracing: {frac:.4f} of {lit} lit pixels agree; splats {got['light_splats']} vs {splats}")
+    assert frac >= 0.98 and abs(got["light_splats"] - splats) <= max(3, 0.01 * splats)
+    device.set_sensor(Sensor(48, 32, 0.036, 0.024))
+    device.render(0, 16, seed=33, max_depth=10, estimator=capi.ESTIMATOR_BDPT)
+    image, _ = device.resolve()
+    frac = image_agreement(image, g["bdpt.48x32.begin0.spp16.seed33.cap10.image"], rtol=5e-3)
+    print(f"sphere lights, bdpt: {frac:.4f} of pixels agree")
+    assert frac >= 0.98
+    device.film_clear()
+    device.render(1, 32, seed=7, estimator=capi.ESTIMATOR_REFERENCE)
+    image, _ = device.resolve()
+    assert image_agreement(image, g["pt.48x32.begin1.spp32.seed7.image"]) >= 0.99
+    oracle = oracle_lib.Oracle(scene)
+    device.film_clear()
+    device.render(0, 16, seed=9, max_depth=12, estimator=capi.ESTIMATOR_NEE)
+    image, _ = device.resolve()
+    want, _ = oracle.render(48, 32, 0.036, 0.024, 0, 16, 9, 12, estimator=1)
+    assert image_agreement(image, want) >= 0.99
+    # NEE vs the reference estimator in expectation, with sphere and triangle emitters together
+    device.set_sensor(Sensor(32, 32))
+    means = {}
+    for estimator, spp in ((0, 8192), (1, 2048)):
+        runs = []
+        for seed in range(4):
+            device.film_clear()
+            device.render(0, spp, seed=80 + seed, estimator=estimator)
+            runs.append(device.resolve()[0].mean(axis=(0, 1)))
+        means[estimator] = np.array(runs)
+    diff = means[0].mean(0) - means[1].mean(0)
+    sigma = np.sqrt(means[0].var(0, ddof=1) / 4 + means[1].var(0, ddof=1) / 4)
+    assert np.all(np.abs(diff) < 4 * sigma + 2e-3 * means[0].mean(0)), (diff, sigma)
 
 
 # ---- pinhole lens (row N1): src/amber/scene/lens_pinhole.cc --------------------------------

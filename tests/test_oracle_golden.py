@@ -218,3 +218,32 @@ def test_bidirectional_path_tracing_matches_reference(oracle_lib):
         assert (got["light_events"], got["eye_events"], got["splats"]) == stats, tag
         n += 1
     assert n == 4
+
+
+def test_sphere_lights_match_reference(oracle_lib):
+    """Emitting spheres: light rays (Sphere::SampleSurfacePoint -> SphereSA as written) and the images of
+    the three algorithms on tests/golden/sphere_lights.npz, bit for bit."""
+    from conftest import sphere_light_box
+    g = golden("sphere_lights.npz")
+    orc = oracle_lib.Oracle(sphere_light_box())
+    o, d, w = orc.light_rays(g["light_rays.xi"])
+    assert np.array_equal(o, g["light_rays.origin"]) and np.array_equal(d, g["light_rays.direction"])
+    assert np.array_equal(w, g["light_rays.weight"])
+    image, stats = orc.render(48, 32, 0.036, 0.024, 1, 32, 7, 0, estimator=0)
+    assert np.array_equal(image, g["pt.48x32.begin1.spp32.seed7.image"])
+    assert stats["closest_rays"] == int(g["pt.48x32.begin1.spp32.seed7.rays"][0])
+    image, stats = orc.render_lt(96, 64, 0.036, 0.024, 0, 64, 25, 0)
+    assert np.array_equal(image, g["lt.96x64.begin0.spp64.seed25.image"])
+    assert stats["splats"] == int(g["lt.96x64.begin0.spp64.seed25.stats"][2]) > 100
+    image, stats = orc.render_bdpt(48, 32, 0.036, 0.024, 0, 16, 33, 10)
+    assert np.array_equal(image, g["bdpt.48x32.begin0.spp16.seed33.cap10.image"])
+    assert [stats["light_events"], stats["eye_events"], stats["splats"]] == [int(v) for v in g["bdpt.48x32.begin0.spp16.seed33.cap10.stats"]]
+    # NEE (not in the reference: spheres are not light-sampled, their emission counts on every hit) has the
+    # reference estimator's expectation
+    means = {}
+    for estimator, spp in ((0, 1024), (1, 256)):
+        means[estimator] = np.array([orc.render(24, 16, 0.036, 0.024, 0, spp, 60 + 7 * estimator + seed, 0, estimator=estimator)[0].mean(axis=(0, 1))
+                                     for seed in range(6)])
+    diff = means[0].mean(0) - means[1].mean(0)
+    sigma = np.sqrt(means[0].var(0, ddof=1) / 6 + means[1].var(0, ddof=1) / 6)
+    assert np.all(np.abs(diff) < 4 * sigma + 1e-3 * means[0].mean(0)), (diff, sigma)

@@ -185,3 +185,30 @@ def test_bidirectional_path_tracing_bit_exact(reference, oracle, oracle_lib):
         a, sa = ref_box.render_bdpt_stream(48, 32, *film, 0, 16, 32, 10)
         b, sb = orc_box.render_bdpt(48, 32, *film, 0, 16, 32, 10)
         assert sa == sb and np.array_equal(a, b) and a.mean() > 0
+
+
+# ---- emitting spheres: Sphere::SampleSurfacePoint in LightSet::GenerateRay ------------------
+def test_sphere_lights_bit_exact(oracle_lib):
+    """A scene whose light set holds a triangle pair and two emitting spheres: light rays, the path tracer,
+    the light tracer and BDPT of the C restatement against the compiled reference, bit for bit."""
+    if not oracle_lib.reference_available():
+        import pytest
+        pytest.skip("oracle/_ref/libamber_ref.so not built (needs /root/reference)")
+    from conftest import sphere_light_box
+    flat = sphere_light_box()
+    ref, orc = oracle_lib.Reference(flat), oracle_lib.Oracle(flat)
+    xi = np.random.default_rng(51).random((20000, 5), dtype=np.float32)
+    got, want = orc.light_rays(xi), ref.light_rays(xi)
+    for x, y in zip(got, want):
+        assert np.array_equal(x, y)
+    on_sphere = np.abs(np.linalg.norm(want[0] - np.array([0.45, 0.1, -0.3], np.float32), axis=1) - 0.2) < 1e-5
+    assert 0.2 < on_sphere.mean() < 0.9 and (want[0][on_sphere][:, 2] >= -0.3 - 1e-6).all()  # SphereSA: z >= 0 only
+    a, sa = ref.render_stream(48, 32, 0.036, 0.024, 1, 16, 7, 0)
+    b, sb = orc.render(48, 32, 0.036, 0.024, 1, 16, 7, 0, estimator=0)
+    assert np.array_equal(a, b) and sa["rays"] == sb["closest_rays"]
+    a, sa = ref.render_lt_stream(96, 64, 0.036, 0.024, 0, 64, 25, 0)
+    b, sb = orc.render_lt(96, 64, 0.036, 0.024, 0, 64, 25, 0)
+    assert sa["splats"] == sb["splats"] and sa["splats"] > 100 and np.array_equal(a, b)
+    a, sa = ref.render_bdpt_stream(48, 32, 0.036, 0.024, 0, 16, 33, 10)
+    b, sb = orc.render_bdpt(48, 32, 0.036, 0.024, 0, 16, 33, 10)
+    assert sa == sb and np.array_equal(a, b) and a.mean() > 0
