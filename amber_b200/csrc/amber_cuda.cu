@@ -111,9 +111,9 @@ struct amber_cuda_ctx {
 
   // path pool
   PathPool pool{};
-  DeviceBuffer<float4> d_ray, d_state, d_shadow_q;
+  DeviceBuffer<float4> d_ray, d_state, d_shadow;
   DeviceBuffer<float2> d_hit;
-  DeviceBuffer<uint32_t> d_q_new;
+  DeviceBuffer<uint32_t> d_q_new, d_q_shadow;
   DeviceBuffer<Control> d_ctl;
   Control* h_ctl = nullptr;  // pinned
 
@@ -502,12 +502,14 @@ int ensure_pool(amber_cuda_ctx* ctx, uint32_t slots) {
   CUDA_TRY(ctx, ctx->d_state.resize(2 * static_cast<size_t>(slots)));
   CUDA_TRY(ctx, ctx->d_hit.resize(slots));
   CUDA_TRY(ctx, ctx->d_q_new.resize(slots));
-  CUDA_TRY(ctx, ctx->d_shadow_q.resize(3 * static_cast<size_t>(slots)));
+  CUDA_TRY(ctx, ctx->d_q_shadow.resize(slots));
+  CUDA_TRY(ctx, ctx->d_shadow.resize(2 * static_cast<size_t>(slots)));
   ctx->pool.ray = ctx->d_ray.ptr;
   ctx->pool.state = ctx->d_state.ptr;
   ctx->pool.hit = ctx->d_hit.ptr;
   ctx->pool.q_new = ctx->d_q_new.ptr;
-  ctx->pool.shadow_q = ctx->d_shadow_q.ptr;
+  ctx->pool.shadow = ctx->d_shadow.ptr;
+  ctx->pool.q_shadow = ctx->d_q_shadow.ptr;
   ctx->pool.n_slots = slots;
   return AMBER_CUDA_OK;
 }
@@ -624,8 +626,8 @@ int amber_cuda_destroy(amber_cuda_ctx* ctx) {
   ctx->d_tri_material.release(); ctx->d_sphere_material.release(); ctx->d_internal_to_prim.release();
   ctx->d_materials.release(); ctx->d_lights.release(); ctx->d_bvh_nodes.release();
   ctx->d_film.release(); ctx->d_resolved.release(); ctx->d_resolved8.release();
-  ctx->d_ray.release(); ctx->d_state.release(); ctx->d_hit.release(); ctx->d_shadow_q.release();
-  ctx->d_q_new.release(); ctx->d_ctl.release(); ctx->d_prim_class.release();
+  ctx->d_ray.release(); ctx->d_state.release(); ctx->d_hit.release(); ctx->d_shadow.release();
+  ctx->d_q_new.release(); ctx->d_q_shadow.release(); ctx->d_ctl.release(); ctx->d_prim_class.release();
   for (auto& b : ctx->d_scratch_f) b.release();
   for (auto& b : ctx->d_scratch_i) b.release();
   for (auto& b : ctx->d_scratch_4) b.release();

@@ -42,7 +42,13 @@ constexpr int kBvhStackMax = 160;  // entries per lane the 227 KB of shared memo
 #define AMBER_BVH_MIN_BLOCKS 5  // resident 256-thread blocks per SM the traversal kernels are compiled for (<= 51 registers)
 #endif
 #ifndef AMBER_BVH_POSTPONE
-#define AMBER_BVH_POSTPONE 1  // a lane that reaches a leaf parks it and keeps descending (speculative traversal)
+#define AMBER_BVH_POSTPONE 0  // 1: a lane that reaches a leaf parks it and keeps descending (measured: no gain)
+#endif
+#ifndef AMBER_BVH_PREFETCH_L2
+#define AMBER_BVH_PREFETCH_L2 0  // 1: when a node step finds a leaf child in range, its triangles are prefetched into L2
+#endif
+#ifndef AMBER_BVH_TRI_NO_ALLOCATE
+#define AMBER_BVH_TRI_NO_ALLOCATE 0  // 1: triangle records bypass L1 allocation (they are rarely re-read; nodes are)
 #endif
 constexpr int kBvhLeafMax = 4;
 constexpr int32_t kEmptyChild = 0x7fffffff;
@@ -59,6 +65,17 @@ __device__ __forceinline__ Wide8 ldg256(const void* p) {
       : "l"(p));
   return r;
 }
+
+// 128-bit read-only load that does not allocate in L1 (streaming data next to the re-used nodes).
+__device__ __forceinline__ float4 ldg_no_allocate(const float4* p) {
+  float4 r;
+  asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float4 load_triangle_word(const float4* p) {
+  return AMBER_BVH_TRI_NO_ALLOCATE ? ldg_no_allocate(p) : __ldg(p);
+}
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 __device__ __forceinline__ int32_t bvh_leaf_first(int32_t ref) { return (~ref) >> 3; }
 __device__ __forceinline__ int32_t bvh_leaf_count(int32_t ref) { return (~ref) & 7; }
@@ -128,6 +145,20 @@ struct WideBvh {
     float d1 = child_entry<1>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c1);
     float d2 = child_entry<2>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c2);
     float d3 = child_entry<3>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c3);
+    if (AMBER_BVH_PREFETCH_L2) {
+      // a leaf child in range will be visited unless a nearer hit cuts the ray short first: start moving its
+      // triangles from DRAM to L2 now (the leaf phase's loads are the traversal's longest stalls)
+      const int32_t refs[4] = {c0, c1, c2, c3};
+      const float dist[4] = {d0, d1, d2, d3};
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        if (refs[k] < 0 && dist[k] < CUDART_INF_F) {
+          const TriIsect* tri = scene.tri_isect + bvh_leaf_first(refs[k]);
+          prefetch_l2(tri);
+          if (bvh_leaf_count(refs[k]) > 2) prefetch_l2(tri + 2);
+        }
+      }
+    }
     // sort the four (distance, child) pairs ascending: 5-comparator network, branch-free
 #define AMBER_CSWAP(da, ca, db, cb)            \
   {                                            \
@@ -263,7 +294,7 @@ struct WideBvh {
         for (int k = 0; k < kBvhLeafMax; k++) {
           if (k < count) {
             const float4* tri = reinterpret_cast<const float4*>(scene.tri_isect + first + k);
-            if (intersect_triangle(__ldg(tri), __ldg(tri + 1), __ldg(tri + 2), ray, hit.t, hit.t)) {
+            if (intersect_triangle(load_triangle_word(tri), load_triangle_word(tri + 1), load_triangle_word(tri + 2), ray, hit.t, hit.t)) {
               hit.prim = first + k;
               found = true;
             }

@@ -9,9 +9,9 @@
 //              roulette, next ray in place      (algorithm_pt.cc:137-157)
 //   connect  : any-hit for the shadow queue + film add
 // `shade` sorts each 512-slot tile by hit class in shared memory so that a warp shades one
-// material; freed slots are compacted into `q_new` (per-thread bit masks, warp shuffles, one smem
-// scan) and shadow rays are written as dense 48-byte records into a range of the shadow queue that the
-// tile reserves up front from its class counts: ONE global atomic per queue per tile.
+// material; freed slots are compacted into `q_new` and slots with a pending shadow ray into
+// `q_shadow`: per-thread bit masks, warp shuffles, one smem scan and ONE global atomic per
+// queue per tile.
 // The same wavefront runs amber's light tracer (algorithm_lt.cc:112-163): raygen<true> starts paths
 // on the lights, shade<true> scatters importance and splats paths that land on the aperture.
 // Bidirectional path tracing is one kernel of its own (bdpt.cuh, included at the end).
@@ -20,11 +20,10 @@
 //   ray[2i], ray[2i+1]       origin xyz + live flag, direction xyz             32 B per slot
 //   state[2i], state[2i+1]   throughput rgb ; (pixel, sample, depth|flags, -)  32 B per slot
 //   hit[i]                   (t, primitive | -1 miss | -2 empty slot)           8 B per slot
-//   shadow_q[3j .. 3j+2]     the j-th shadow ray of this iteration, DENSE: origin + pixel ;
-//                            direction + t_max ; contribution rgb                 48 B per shadow ray
-//   q_new[j]                 slot ids                                             4 B per entry
-// A slot's ray and state each fill exactly one 32-byte sector, so the permuted accesses of raygen and
-// shade never touch a partial sector; connect streams its queue.
+//   shadow[2i], shadow[2i+1] direction + t_max ; contribution rgb + pixel      32 B per slot
+//   q_new[j], q_shadow[j]    slot ids                                           4 B per entry
+// A slot's ray, state and shadow record each fill exactly one 32-byte sector, so the
+// permuted accesses of raygen / shade / connect never touch a partial sector.
 #pragma once
 
 #include "bvh.cuh"
@@ -42,7 +41,7 @@ struct Control {
   unsigned long long next_path;    // next path index of this render call
   unsigned long long total_paths;  // W * H * sample_count
   unsigned int n_new;              // entries in q_new
-  unsigned int n_shadow;           // entries RESERVED in the shadow queue (some are marked unused: t_max < 0)
+  unsigned int n_shadow;           // entries in the shadow queue
   unsigned int n_alive;            // survivors of the last shade
   unsigned int done;
   unsigned int cursor_extend, cursor_connect, cursor_cast;  // persistent BVH kernels: next item to fetch
@@ -63,7 +62,8 @@ struct PathPool {
   float4* state;    // [2 * n_slots]
   float2* hit;      // [n_slots]
   uint32_t* q_new;  // [n_slots] slots freed by the last shade
-  float4* shadow_q;  // [3 * n_slots] dense shadow-ray queue: origin + pixel ; direction + t_max ; contribution
+  float4* shadow;   // [2 * n_slots] per-slot shadow ray: direction + t_max ; contribution + pixel
+  uint32_t* q_shadow;  // [n_slots] slots whose shadow ray is pending
   uint32_t n_slots;
 };
 
@@ -278,18 +278,22 @@ constexpr int kQueueBlocks = AMBER_QUEUE_BLOCKS;  // resident blocks per SM of t
 #endif
 template <bool kLightTracing>
 __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(const RenderArgs args) {
+  // q_new is the pool's FREE LIST: entries [0, n_new) are slots without a path.  This launch starts
+  // `generated` = min(n_new, paths left) paths in the LAST `generated` entries; what is left at the front
+  // stays on the list for a later launch (bookkeep shortens n_new by `generated`, shade appends the slots it
+  // frees) -- so a render call absorbed into a wavefront that has partly drained finds the free slots.
   const Control* ctl = args.ctl;
-  const uint32_t n_new = AMBER_RAYGEN_LOOP ? ctl->n_new : min(ctl->n_new, (blockIdx.x + 1) * kBlock);
   const unsigned long long next_path = ctl->next_path, total_paths = ctl->total_paths;
+  const uint32_t n_free = ctl->n_new;
+  const unsigned long long left = next_path < total_paths ? total_paths - next_path : 0ull;
+  const uint32_t generated = left < n_free ? static_cast<uint32_t>(left) : n_free;
+  const uint32_t first_entry = n_free - generated;
+  const uint32_t n_new = AMBER_RAYGEN_LOOP ? generated : min(generated, (blockIdx.x + 1) * kBlock);
   const unsigned long long base_pixel = ctl->base_pixel, base_ordinal = ctl->base_sample;
   const uint32_t width = c_camera.sensor.width;
   for (uint32_t j = blockIdx.x * kBlock + threadIdx.x; j < n_new; j += gridDim.x * kBlock) {
-    const uint32_t slot = args.pool.q_new[j];
+    const uint32_t slot = args.pool.q_new[first_entry + j];
     float4* ray = args.pool.ray + 2 * static_cast<size_t>(slot);
-    if (next_path + j >= total_paths) {
-      ray[0] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-      continue;
-    }
     // path = next_path + j = (base_sample * n_pixels + base_pixel) + j: the 64-bit division is done once
     // per launch by `bookkeep`, a thread divides the 32-bit (base_pixel + j)
     const unsigned long long offset = base_pixel + j;
@@ -340,8 +344,10 @@ __global__ void bookkeep_kernel(Control* ctl) {
   ctl->base_pixel = static_cast<unsigned int>(ctl->next_path % ctl->n_pixels);
   ctl->base_sample = ctl->next_path / ctl->n_pixels;
   ctl->paths += generated;
-  ctl->done = (generated == 0 && ctl->n_alive == 0) ? 1u : 0u;
-  ctl->n_new = 0;
+  ctl->shadow_rays += ctl->n_shadow;
+  // finished: every path of the render has been started and none is alive (n_alive: survivors of the last shade)
+  ctl->done = (generated == 0 && ctl->next_path >= ctl->total_paths && ctl->n_alive == 0) ? 1u : 0u;
+  ctl->n_new -= static_cast<unsigned int>(generated);  // the free list keeps what raygen did not use
   ctl->n_shadow = 0;
   ctl->n_alive = 0;
   ctl->cursor_extend = 0;
@@ -576,15 +582,11 @@ __device__ __forceinline__ void film_add(float4* film, uint32_t pixel, float3 va
 //      code on a few lanes each, and no warp idles while another works through an
 //      expensive class.  Ray / state records are 32-byte sectors, so the permuted accesses
 //      inside the tile's window still move whole sectors.
-//   3. queues: each thread has one bit per chunk for "slot freed"; one block scan and ONE
-//      global atomic per tile hand out the q_new range.
-// Shadow rays go to a DENSE queue of 48-byte records (origin + pixel, direction + t_max,
-// contribution) that `connect` streams: after phase 1 the tile knows how many of its vertices are
-// connectable (the Lambertian and Phong classes sort first), reserves that many queue entries with one
-// global atomic, and phase 2 writes each record at base + a shared-memory counter.  Entries reserved
-// for vertices whose light sample turned out empty (light facing away, zero BSDF) are marked unused
-// (t_max < 0) in phase 3.  Before: a 32-byte record in the slot + a slot id in a queue, gathered by
-// connect as two 32-byte sectors of two different DRAM atoms (198 B of DRAM traffic per shadow ray).
+//   3. queues: each thread has one bit per chunk for "slot freed" and "shadow ray
+//      emitted"; one block scan and ONE global atomic per queue per tile hand out the
+//      q_new / q_shadow ranges.
+// The shadow ray itself stays in the slot (pool.shadow[2 slot..]); its origin is the
+// vertex position, which phase 2 has just written to ray[2 slot].
 #ifndef AMBER_SHADE_MIN_BLOCKS
 #define AMBER_SHADE_MIN_BLOCKS 8
 #endif
@@ -631,16 +633,13 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
   __shared__ uint32_t class_count[16], class_offset[16];
   __shared__ uint32_t warp_scan[kShadeBlock / 32];
   __shared__ uint32_t queue_base[2];
-  __shared__ uint32_t next_chunk, shadow_count;
+  __shared__ uint32_t next_chunk;
   const PathPool& pool = args.pool;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t tile_base = blockIdx.x * kShadeTile;
   const uint32_t lane_lt = (1u << lane) - 1u;
   if (tid < 16) class_count[tid] = 0;
-  if (tid == 0) {
-    next_chunk = 0;
-    shadow_count = 0;
-  }
+  if (tid == 0) next_chunk = 0;
   __syncthreads();
 
   // ---- phase 1: classify + counting sort ------------------------------------------
@@ -673,13 +672,6 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
       if (lane >= delta) scan += up;
     }
     if (lane < 16) class_offset[lane] = scan - count;
-    // connectable vertices = the classes of the Lambertian and Phong materials (kinds 0, 1: classes 0-3);
-    // their number bounds the tile's shadow rays: reserve that many queue entries now
-    const uint32_t n_connectable = __shfl_sync(0xffffffffu, scan, 3);
-    if (lane == 0) {
-      const bool connects = !kLightTracing && args.estimator == kEstimatorNee && args.scene.n_lights > 0;
-      queue_base[1] = connects && n_connectable ? atomicAdd(&args.ctl->n_shadow, n_connectable) : 0u;
-    }
   }
   __syncthreads();
 #pragma unroll
@@ -717,7 +709,7 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     }
     cp_async_commit();
   };
-  uint32_t freed_mask = 0;  // bit c: my entry of chunk c (sorted[32 c + lane])
+  uint32_t freed_mask = 0, shadow_mask = 0;  // bit c: my entry of chunk c (sorted[32 c + lane])
   uint32_t chunk = take_chunk();
   int buf = 0;
   stage_records(chunk, buf);
@@ -730,8 +722,9 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     stage_records(chunk, buf ^ 1);
     cp_async_wait_all_but_one();
     if (j >= n_live) continue;
-    if (j >= n_hit) {  // miss: the slot is free again
+    if (j >= n_hit) {  // miss: the slot is free again (w = 0: a slot on the free list holds no ray)
       freed_mask |= 1u << r;
+      pool.ray[2 * static_cast<size_t>(tile_base + sorted[j])] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
       continue;
     }
     const uint32_t slot = tile_base + sorted[j];
@@ -786,16 +779,11 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
       rng.light_point(lu, lv);
       ShadowRay shadow;
       if (sample_direct(args.scene, m, x, n, wo, throughput, rng.light_choice(), lu, lv, shadow)) {
-        // position in the tile's reserved range: one shared-memory atomic for the lanes that got here together
-        const uint32_t together = __activemask();
-        const int leader = __ffs(together) - 1;
-        uint32_t rank = 0;
-        if (lane == leader) rank = atom_shared_add(&shadow_count, __popc(together));
-        rank = __shfl_sync(together, rank, leader) + __popc(together & lane_lt);
-        float4* out = pool.shadow_q + 3 * static_cast<size_t>(queue_base[1] + rank);
-        out[0] = make_float4(x.x, x.y, x.z, __uint_as_float(pixel));
-        out[1] = make_float4(shadow.d.x, shadow.d.y, shadow.d.z, shadow.t_max);
-        out[2] = make_float4(shadow.contribution.x, shadow.contribution.y, shadow.contribution.z, 0.0f);
+        shadow_mask |= 1u << r;
+        float4* out = pool.shadow + 2 * static_cast<size_t>(slot);
+        out[0] = make_float4(shadow.d.x, shadow.d.y, shadow.d.z, shadow.t_max);
+        out[1] = make_float4(shadow.contribution.x, shadow.contribution.y, shadow.contribution.z,
+                             __uint_as_float(pixel));
       }
     }
 
@@ -812,7 +800,8 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     }
     if (terminated) {
       freed_mask |= 1u << r;
-      ray_slot[0] = make_float4(x.x, x.y, x.z, 0.0f);  // w = 0 marks the slot free
+      // the vertex stays readable for `connect` (shadow origin); w = 0 marks the slot free
+      ray_slot[0] = make_float4(x.x, x.y, x.z, 0.0f);
     } else {
       const float inv_p = __fdividef(1.0f, p);  // scales the throughput only
       throughput = throughput * (inv_p * scatter.weight);
@@ -824,8 +813,8 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
   }
 
   // ---- phase 3: queue ranges, one atomic per queue per tile --------------------------
-  const uint32_t mine = static_cast<uint32_t>(__popc(freed_mask));
-  uint32_t scan = mine;
+  const uint32_t mine = static_cast<uint32_t>(__popc(freed_mask)) | (static_cast<uint32_t>(__popc(shadow_mask)) << 16);
+  uint32_t scan = mine;  // two 16-bit inclusive scans side by side (tile size < 65536)
 #pragma unroll
   for (int delta = 1; delta < 32; delta <<= 1) {
     const uint32_t up = __shfl_up_sync(0xffffffffu, scan, delta);
@@ -843,9 +832,9 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     }
     if (lane < kShadeBlock / 32) warp_scan[lane] = wscan - total;
     if (lane == kShadeBlock / 32 - 1) {
-      const uint32_t n_freed = wscan;
+      const uint32_t n_freed = wscan & 0xffffu, n_shadow = wscan >> 16;
       queue_base[0] = n_freed ? atomicAdd(&args.ctl->n_new, n_freed) : 0u;
-      if (shadow_count) atomicAdd(&args.ctl->shadow_rays, static_cast<unsigned long long>(shadow_count));
+      queue_base[1] = n_shadow ? atomicAdd(&args.ctl->n_shadow, n_shadow) : 0u;
       const uint32_t live = n_live;
       if (live) atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(live));
       if (live > n_freed) atomicAdd(&args.ctl->n_alive, live - n_freed);
@@ -853,17 +842,17 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
   }
   __syncthreads();
   const uint32_t before = warp_scan[warp] + scan - mine;
-  uint32_t freed_at = queue_base[0] + before;
+  uint32_t freed_at = queue_base[0] + (before & 0xffffu);
+  uint32_t shadow_at = queue_base[1] + (before >> 16);
   while (freed_mask) {
     const int r = __ffs(freed_mask) - 1;
     freed_mask &= freed_mask - 1u;
     pool.q_new[freed_at++] = tile_base + sorted[r * 32 + lane];
   }
-  // reserved shadow-queue entries that no vertex filled: marked unused for `connect`
-  if (!kLightTracing && args.estimator == kEstimatorNee && args.scene.n_lights > 0) {
-    const uint32_t reserved = class_offset[4];
-    for (uint32_t k = shadow_count + tid; k < reserved; k += kShadeBlock)
-      pool.shadow_q[3 * static_cast<size_t>(queue_base[1] + k) + 1] = make_float4(0.0f, 0.0f, 1.0f, -1.0f);
+  while (shadow_mask) {
+    const int r = __ffs(shadow_mask) - 1;
+    shadow_mask &= shadow_mask - 1u;
+    pool.q_shadow[shadow_at++] = tile_base + sorted[r * 32 + lane];
   }
 }
 
@@ -873,39 +862,36 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
 template <class Accel>
 __global__ void __launch_bounds__(kBlock, kQueueBlocks) connect_kernel(const RenderArgs args) {
   // grid-stride over the shadow queue (the grid is sized for the device, see raygen_kernel); the loop
-  // bound is warp-uniform so that Accel::occluded may vote.  The queue is dense: consecutive lanes read
-  // consecutive 48-byte records.
+  // bound is warp-uniform so that Accel::occluded may vote
   const uint32_t n_shadow = args.ctl->n_shadow;
   for (uint32_t base = blockIdx.x * kBlock; base < n_shadow; base += gridDim.x * kBlock) {
     const uint32_t j = base + threadIdx.x;
-    bool active = j < n_shadow;
-    float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = make_float4(0.0f, 0.0f, 1.0f, -1.0f);
+    const bool active = j < n_shadow;
+    float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
     float4 c = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     if (active) {
-      const float4* in = args.pool.shadow_q + 3 * static_cast<size_t>(j);
-      o = in[0];
-      d = in[1];
-      c = in[2];
+      const uint32_t slot = args.pool.q_shadow[j];
+      o = args.pool.ray[2 * static_cast<size_t>(slot)];
+      const float4* in = args.pool.shadow + 2 * static_cast<size_t>(slot);
+      d = in[0];
+      c = in[1];  // same 32-byte sector as in[0]: requested now, not after the visibility test
     }
-    active = active && d.w >= 0.0f;  // t_max < 0: an entry reserved by `shade` and not used
     Ray ray;
     ray.o = v3(o);
     ray.d = v3(d);
     if (Accel::occluded(args.scene, ray, d.w, active) || !active) continue;
-    film_add(args.film, __float_as_uint(o.w), v3(c));
+    film_add(args.film, __float_as_uint(c.w), v3(c));
   }
 }
 
 struct ConnectSource {
   const RenderArgs& args;
-  uint32_t entry;
+  uint32_t slot;
   __device__ __forceinline__ uint32_t count() const { return args.ctl->n_shadow; }
   __device__ __forceinline__ bool load(uint32_t j, Ray& ray, float& t_best) {
-    entry = j;
-    const float4* in = args.pool.shadow_q + 3 * static_cast<size_t>(j);
-    const float4 d = in[1];
-    if (d.w < 0.0f) return false;  // reserved, not used
-    const float4 o = in[0];
+    slot = args.pool.q_shadow[j];
+    const float4 o = args.pool.ray[2 * static_cast<size_t>(slot)];
+    const float4 d = args.pool.shadow[2 * static_cast<size_t>(slot)];
     ray.o = v3(o);
     ray.d = v3(d);
     t_best = d.w;
@@ -913,9 +899,8 @@ struct ConnectSource {
   }
   __device__ __forceinline__ void store(uint32_t, const HitRecord&, bool found) const {
     if (found) return;
-    const float4* in = args.pool.shadow_q + 3 * static_cast<size_t>(entry);
-    const float4 o = in[0], c = in[2];
-    film_add(args.film, __float_as_uint(o.w), v3(c));
+    const float4 c = args.pool.shadow[2 * static_cast<size_t>(slot) + 1];
+    film_add(args.film, __float_as_uint(c.w), v3(c));
   }
 };
 

@@ -264,16 +264,27 @@ def run_gpu(args) -> None:
             ms += e0.elapsed_time(e1)
         return ms
 
+    e2e_phases = {"upload_scene": 0.0, "set_sensor": 0.0, "render_and_reduce": 0.0, "resolve": 0.0}
+
     def step(e2e: bool) -> float:
         """Returns device milliseconds of this rank's step."""
+        t0 = time.perf_counter()
         if e2e:
             dev.upload_scene(scene)      # host scene description -> device (H2D)
+            t1 = time.perf_counter()
             dev.set_sensor(sensor)       # (clears the film)
         else:
+            t1 = t0
             dev.film_clear()
+        t2 = time.perf_counter()
         ms = render_and_reduce(begin, count)
+        t3 = time.perf_counter()
         if e2e and rank == 0:
             dev.resolve(image)           # mean image -> host (D2H)
+        if e2e:
+            t4 = time.perf_counter()
+            for key, dt in zip(e2e_phases, (t1 - t0, t2 - t1, t3 - t2, t4 - t3)):
+                e2e_phases[key] += dt * 1e3
         return ms
 
     def over_ranks(values, how):
@@ -492,7 +503,8 @@ def run_gpu(args) -> None:
                                           + ctypes.sizeof(scene.lens)),
                 "d2h_bytes_per_step": int(image.nbytes), "ms_per_step": e2e_wall_ms / args.steps,
                 "mrays_per_s": (e2e_closest + e2e_shadow) / (e2e_wall_ms * 1e-3) / 1e6,
-                "timing": "wall clock around upload_scene + set_sensor + render + resolve through the C ABI"},
+                "timing": "wall clock around upload_scene + set_sensor + render + resolve through the C ABI",
+                "host_ms_per_step": {k: v / args.steps for k, v in e2e_phases.items()}},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": roofline,
