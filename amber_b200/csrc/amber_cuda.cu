@@ -931,6 +931,7 @@ __global__ void control_begin_kernel(Control* ctl, unsigned long long total_path
   ctl->n_pixels = n_pixels;
   ctl->total_paths = total_paths;
   ctl->n_new = slots;
+  ctl->n_marked = slots;  // pool_reset_kernel empties every slot
   ctl->n_shadow = 0;
   ctl->n_alive = 0;
   ctl->done = 0;

@@ -50,7 +50,7 @@ struct Control {
   unsigned long long splats;  // light tracing: film contributions through the lens
   unsigned long long base_sample;  // next_path / n_pixels
   unsigned int n_pixels;
-  unsigned int pad;
+  unsigned int n_marked;  // free-list entries [0, n_marked) are known to hold no ray (ray.w == 0)
   unsigned long long cursor_bdpt;  // bdpt_kernel: next (pixel, sample) pair index
   // profiling mode: traversal work of the BVH kernels: extend node steps, extend triangle tests, connect
   // node steps, connect triangle tests
@@ -282,6 +282,9 @@ __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(con
   // `generated` = min(n_new, paths left) paths in the LAST `generated` entries; what is left at the front
   // stays on the list for a later launch (bookkeep shortens n_new by `generated`, shade appends the slots it
   // frees) -- so a render call absorbed into a wavefront that has partly drained finds the free slots.
+  // A slot whose path left the scene still holds that path's ray (w = 1): when such a slot stays on the list
+  // unused it is marked empty here (entries [n_marked, first_entry): only the ones appended since the last
+  // launch; nothing to do while every free slot is reused at once, the steady state).
   const Control* ctl = args.ctl;
   const unsigned long long next_path = ctl->next_path, total_paths = ctl->total_paths;
   const uint32_t n_free = ctl->n_new;
@@ -289,10 +292,13 @@ __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(con
   const uint32_t generated = left < n_free ? static_cast<uint32_t>(left) : n_free;
   const uint32_t first_entry = n_free - generated;
   const uint32_t n_new = AMBER_RAYGEN_LOOP ? generated : min(generated, (blockIdx.x + 1) * kBlock);
+  for (uint32_t j = ctl->n_marked + blockIdx.x * kBlock + threadIdx.x; j < first_entry; j += gridDim.x * kBlock)
+    args.pool.ray[2 * static_cast<size_t>(args.pool.q_new[j])] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
   const unsigned long long base_pixel = ctl->base_pixel, base_ordinal = ctl->base_sample;
   const uint32_t width = c_camera.sensor.width;
+  const uint32_t* __restrict__ entries = args.pool.q_new + first_entry;
   for (uint32_t j = blockIdx.x * kBlock + threadIdx.x; j < n_new; j += gridDim.x * kBlock) {
-    const uint32_t slot = args.pool.q_new[first_entry + j];
+    const uint32_t slot = entries[j];
     float4* ray = args.pool.ray + 2 * static_cast<size_t>(slot);
     // path = next_path + j = (base_sample * n_pixels + base_pixel) + j: the 64-bit division is done once
     // per launch by `bookkeep`, a thread divides the 32-bit (base_pixel + j)
@@ -347,7 +353,8 @@ __global__ void bookkeep_kernel(Control* ctl) {
   ctl->shadow_rays += ctl->n_shadow;
   // finished: every path of the render has been started and none is alive (n_alive: survivors of the last shade)
   ctl->done = (generated == 0 && ctl->next_path >= ctl->total_paths && ctl->n_alive == 0) ? 1u : 0u;
-  ctl->n_new -= static_cast<unsigned int>(generated);  // the free list keeps what raygen did not use
+  ctl->n_new -= static_cast<unsigned int>(generated);  // the free list keeps what raygen did not use ...
+  ctl->n_marked = ctl->n_new;                           // ... and raygen has marked all of that empty
   ctl->n_shadow = 0;
   ctl->n_alive = 0;
   ctl->cursor_extend = 0;
@@ -722,9 +729,8 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     stage_records(chunk, buf ^ 1);
     cp_async_wait_all_but_one();
     if (j >= n_live) continue;
-    if (j >= n_hit) {  // miss: the slot is free again (w = 0: a slot on the free list holds no ray)
+    if (j >= n_hit) {  // miss: the slot is free again
       freed_mask |= 1u << r;
-      pool.ray[2 * static_cast<size_t>(tile_base + sorted[j])] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
       continue;
     }
     const uint32_t slot = tile_base + sorted[j];

@@ -286,7 +286,8 @@ class CudaPathTracing:
     """
 
     def __init__(self, estimator: str = "nee", max_depth: int = 0, seed: int = 1, device: int = 0,
-                 batch_spp: int = 64, pool_paths: int = 0, devices: "list[int] | None" = None, depth: int = 3):
+                 batch_spp: int = 64, pool_paths: int = 0, devices: "list[int] | None" = None, depth: int = 3,
+                 min_batch_paths: int = 1 << 24):
         self.estimator = {"reference": capi.ESTIMATOR_REFERENCE, "nee": capi.ESTIMATOR_NEE,
                           "lt": capi.ESTIMATOR_LIGHT_TRACING, "bdpt": capi.ESTIMATOR_BDPT}[estimator]
         self.max_depth = max_depth
@@ -295,6 +296,7 @@ class CudaPathTracing:
         self.batch_spp = max(1, batch_spp)
         self.pool_paths = pool_paths
         self.depth = max(1, depth)
+        self.min_batch_paths = min_batch_paths  # small frames: a queued call holds at least this many camera paths
         self.last_stats: dict | None = None
         self._devices: list[Device] = []
         self._scene = None
@@ -329,9 +331,10 @@ class CudaPathTracing:
         n = len(devices)
         done = [0] * n  # samples per pixel handed to each device
         batch = 0
+        batch_spp = min(1 << 20, max(self.batch_spp, -(-self.min_batch_paths // sensor.size())))
         while True:
             count = 0
-            while count < self.batch_spp and context.iterate():
+            while count < batch_spp and context.iterate():
                 count += 1
             if count == 0:
                 break

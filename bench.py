@@ -239,7 +239,9 @@ def run_gpu(args) -> None:
     dev.upload_scene(scene)
     dev.set_sensor(sensor)
     begin, count = partition_samples(SPP * world, rank, world)  # weak scaling: 1024 spp per rank
-    image = np.empty((HEIGHT, WIDTH, 3), dtype=np.float32)
+    # the e2e leg's result buffer: PINNED host memory (a pageable destination is staged by the driver through
+    # bounce buffers at a speed that varies several-fold from box to box: 2 ms to 29 ms for these 12.6 MB)
+    image = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float32, pin_memory=True).numpy()
 
     def barrier():
         if distributed:

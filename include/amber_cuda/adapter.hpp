@@ -335,7 +335,9 @@ struct CudaPathTracingOptions
   uint32_t max_depth = 0;                    // 0 = 2^16; the reference has no cap (algorithm_pt.cc:137)
   uint64_t seed = 1;
   std::vector<int> devices = {0};            // samples are dealt to these GPUs, which render concurrently
-  uint32_t batch_spp = 64;                   // Context::Iterate() calls consumed per queued render call
+  uint32_t batch_spp = 64;                   // Context::Iterate() calls consumed per queued render call (raised for small
+                                             // frames so that a call holds at least min_batch_paths camera paths)
+  uint64_t min_batch_paths = 1ull << 24;     // ~3 ms of work: keeps expiry responsive and the pool full
   uint32_t pool_paths = 0;
   uint32_t queue_depth = 3;                  // render calls queued ahead per device (they run as one wavefront)
 };
@@ -455,9 +457,12 @@ public:
     // consume Iterate() in batches; batch b is queued on device b mod G
     const std::size_t n_devices = devices_.size();
     std::vector<uint64_t> handed(n_devices, 0);  // samples per pixel handed to each device
+    const uint64_t n_pixels = static_cast<uint64_t>(width) * height;
+    const uint32_t batch_spp = static_cast<uint32_t>(std::min<uint64_t>(
+      1u << 20, std::max<uint64_t>(options_.batch_spp, (options_.min_batch_paths + n_pixels - 1) / n_pixels)));
     for (std::size_t batch = 0;; batch++) {
       uint32_t count = 0;
-      while (count < options_.batch_spp && context.Iterate()) {
+      while (count < batch_spp && context.Iterate()) {
         count++;
       }
       if (count == 0) {

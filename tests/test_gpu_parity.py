@@ -598,7 +598,12 @@ def test_emitting_spheres(device, oracle_lib):
     device.upload_scene(scene)
     device.set_sensor(Sensor(96, 64, 0.036, 0.024))
     o, d, w = device.light_rays(g["light_rays.xi"])
-    assert np.array_equal(o, g["light_rays.origin"]) and np.array_equal(w, g["light_rays.weight"])
+    # points on the triangle emitter use the host's operations one by one (bit-identical); points on a
+    # sphere go through sincosf, which may differ from glibc's by an ulp
+    on_triangle = np.abs(g["light_rays.origin"][:, 1] - np.float32(0.98)) < 1e-6
+    assert on_triangle.any() and not on_triangle.all()
+    assert np.array_equal(o[on_triangle], g["light_rays.origin"][on_triangle])
+    assert np.allclose(o, g["light_rays.origin"], atol=2e-7) and np.array_equal(w, g["light_rays.weight"])
     assert np.allclose(d, g["light_rays.direction"], atol=5e-6)
     device.render(0, 64, seed=25, estimator=capi.ESTIMATOR_LIGHT_TRACING)
     image, _ = device.resolve()

@@ -186,7 +186,7 @@ def test_host_algorithm_on_several_devices(cornell):
     import torch
     from amber_b200 import Context, CudaPathTracing, Sensor
     sensor = Sensor(512, 512)
-    single = CudaPathTracing(max_depth=16, seed=5, batch_spp=8)
+    single = CudaPathTracing(max_depth=16, seed=5, batch_spp=8, min_batch_paths=1)
     image1 = single.render(cornell, sensor, Context(1, 64))
     assert single.last_stats["paths"] == 64 * 512 * 512 and single.last_stats["chained_renders"] >= 1
     t0 = time.perf_counter()
@@ -196,7 +196,7 @@ def test_host_algorithm_on_several_devices(cornell):
     if torch.cuda.device_count() < 2:
         pytest.skip("one GPU: multi-device dealing not exercised")
     n = min(4, torch.cuda.device_count())
-    multi = CudaPathTracing(max_depth=16, seed=5, batch_spp=8, devices=list(range(n)))
+    multi = CudaPathTracing(max_depth=16, seed=5, batch_spp=8, devices=list(range(n)), min_batch_paths=1)
     image_n = multi.render(cornell, sensor, Context(1, 64))
     assert multi.last_stats["paths"] == 64 * 512 * 512
     assert close(image_n, image1)
