@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libamber_cuda.so")
 
 ABI_VERSION = 2
 SAMPLES_IN_FILM = 0xFFFFFFFFFFFFFFFF
+CAST_STATIC_MAX = 65536
 
 PRIM_TRIANGLE, PRIM_SPHERE = 0, 1
 MAT_LAMBERTIAN, MAT_PHONG, MAT_SPECULAR, MAT_REFRACTION, MAT_DIFFUSE_LIGHT, MAT_EYE = range(6)
@@ -42,6 +43,7 @@ SYMBOLS = (
     "amber_cuda_film_set_samples",
     "amber_cuda_cast",
     "amber_cuda_cast_device",
+    "amber_cuda_cast_static",
     "amber_cuda_sample_light",
     "amber_cuda_eye_rays",
     "amber_cuda_sample_importance",
@@ -169,6 +171,7 @@ def load(path: str | None = None) -> C.CDLL:
         "amber_cuda_film_set_samples": [vp, u64],
         "amber_cuda_cast": [vp, vp, vp, u64, vp, vp],
         "amber_cuda_cast_device": [vp, vp, vp, u64, vp, f32p],
+        "amber_cuda_cast_static": [vp, vp, vp, u64, vp, vp],
         "amber_cuda_sample_light": [vp, i32, u64, vp, vp, vp, vp, vp, vp],
         "amber_cuda_eye_rays": [vp, u64, vp, vp, vp, vp, vp, vp],
         "amber_cuda_sample_importance": [vp, i32, u64, vp, vp, vp, vp, vp, vp],

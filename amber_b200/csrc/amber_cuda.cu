@@ -1588,6 +1588,80 @@ int amber_cuda_cast(amber_cuda_ctx* ctx, const float* origins, const float* dire
   return AMBER_CUDA_OK;
 }
 
+}  // extern "C"
+
+// ---- amber_cuda_cast_static: closest hit without any allocation ---------------------------------------
+// Scratch of the entry point below: the packed rays (origin, direction as float4) and the float4 hit records
+// of up to AMBER_CUDA_CAST_STATIC_MAX rays, in a file-scope device array instead of cudaMalloc'ed buffers:
+// 3 x 16 B x 65 536 = 3 MiB, held by every GPU that loads the library until the process exits.  In host code
+// the array's NAME is a host-side stand-in, not a device address; the address the kernels get comes from
+// cudaGetSymbolAddress, asked once per device with that device current (static_scratch_for).
+static __device__ __align__(256) float4 g_cast_static_scratch[3 * AMBER_CUDA_CAST_STATIC_MAX];
+
+namespace amber_host {
+
+std::mutex g_static_scratch_mutex;
+float4* g_static_scratch_ptr[kMaxDevices] = {};
+
+// The device address of g_cast_static_scratch on the context's device (which must be current).
+int static_scratch_for(amber_cuda_ctx* ctx, float4** out) {
+  if (ctx->device < 0 || ctx->device >= kMaxDevices) return fail(ctx, AMBER_CUDA_EINVAL, "device %d out of range", ctx->device);
+  std::lock_guard<std::mutex> guard(g_static_scratch_mutex);
+  if (!g_static_scratch_ptr[ctx->device]) {
+    void* address = nullptr;
+    const cudaError_t err = cudaGetSymbolAddress(&address, g_cast_static_scratch);
+    if (err != cudaSuccess || !address)
+      return fail(ctx, AMBER_CUDA_ECUDA, "cudaGetSymbolAddress(g_cast_static_scratch) failed on device %d: %s", ctx->device,
+                  cudaGetErrorString(err));
+    g_static_scratch_ptr[ctx->device] = static_cast<float4*>(address);
+  }
+  *out = g_static_scratch_ptr[ctx->device];
+  return AMBER_CUDA_OK;
+}
+
+}  // namespace amber_host
+
+extern "C" {
+
+int amber_cuda_cast_static(amber_cuda_ctx* ctx, const float* device_origins3, const float* device_directions3, uint64_t n,
+                           int32_t* device_prim, float* device_t) {
+  if (!ctx) return AMBER_CUDA_EINVAL;
+  if (!ctx->has_scene) return fail(ctx, AMBER_CUDA_ESTATE, "upload_scene has not been called");
+  if (n > static_cast<uint64_t>(AMBER_CUDA_CAST_STATIC_MAX))
+    return fail(ctx, AMBER_CUDA_EINVAL, "amber_cuda_cast_static: %llu rays exceed the static scratch of %d rays "
+                "(AMBER_CUDA_CAST_STATIC_MAX); split the call or use amber_cuda_cast",
+                static_cast<unsigned long long>(n), AMBER_CUDA_CAST_STATIC_MAX);
+  if (n == 0) return AMBER_CUDA_OK;
+  if (!device_origins3 || !device_directions3 || !device_prim || !device_t) return fail(ctx, AMBER_CUDA_EINVAL, "NULL buffer");
+  wait_idle(ctx);
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  float4* scratch = nullptr;
+  int rc = static_scratch_for(ctx, &scratch);
+  if (rc != AMBER_CUDA_OK) return rc;
+  DeviceTurn turn(ctx);
+  rc = bind_constants(ctx);
+  if (rc != AMBER_CUDA_OK) return rc;
+  // every element the kernels read is written first by this call (rays by pack, hits by the cast), so the
+  // previous call's contents need no clearing; the BVH walk's ray cursor is the one thing that starts at zero
+  float4* o4 = scratch;
+  float4* d4 = scratch + AMBER_CUDA_CAST_STATIC_MAX;
+  float4* h4 = scratch + 2 * AMBER_CUDA_CAST_STATIC_MAX;
+  cudaStream_t stream = ctx->stream;
+  pack_rays_kernel<<<blocks_for(n), kBlock, 0, stream>>>(device_origins3, device_directions3, n, o4, d4);
+  if (ctx->use_bvh) {
+    CUDA_TRY(ctx, cudaMemsetAsync(&ctx->d_ctl.ptr->cursor_cast, 0, sizeof(unsigned int), stream));
+    cast_bvh_kernel<<<ctx->bvh_grid, kBlock, ctx->bvh_smem, stream>>>(ctx->view, o4, d4, static_cast<uint32_t>(n), h4,
+                                                                    &ctx->d_ctl.ptr->cursor_cast);
+  } else {
+    cast_kernel<ConstList><<<blocks_for(n), kBlock, 0, stream>>>(ctx->view, o4, d4, n, h4);
+  }
+  unpack_hits_kernel<<<blocks_for(n), kBlock, 0, stream>>>(h4, n, ctx->d_internal_to_prim.ptr, device_prim, device_t);
+  ctx->stats.kernel_launches += 3;
+  CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+  CUDA_TRY(ctx, cudaGetLastError());
+  return AMBER_CUDA_OK;
+}
+
 static int sample_scatter(amber_cuda_ctx* ctx, bool importance, int32_t material, uint64_t n, const float* normal3,
                           const float* dir_out3, const float* xi8, float* dir_in3, float* weight3,
                           int32_t* draws) {

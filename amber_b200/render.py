@@ -186,6 +186,11 @@ class Device:
                                              n, prim.ctypes.data_as(C.c_void_p), t.ctypes.data_as(C.c_void_p)))
         return prim, t
 
+    def cast_static(self, origins3_ptr: int, directions3_ptr: int, n: int, prim_ptr: int, t_ptr: int) -> None:
+        """``amber_cuda_cast_static``: closest hits with device-resident inputs / outputs and no allocation
+        inside the library (static scratch, at most ``capi.CAST_STATIC_MAX`` rays per call)."""
+        self._check(self.lib.amber_cuda_cast_static(self.ctx, origins3_ptr, directions3_ptr, n, prim_ptr, t_ptr))
+
     def cast_device(self, origin4_ptr: int, direction4_ptr: int, n: int, hit4_ptr: int) -> float:
         ms = C.c_float()
         self._check(self.lib.amber_cuda_cast_device(self.ctx, origin4_ptr, direction4_ptr, n, hit4_ptr, C.byref(ms)))

@@ -274,6 +274,22 @@ int amber_cuda_cast_device(amber_cuda_ctx* ctx, const void* ray_origin4,
                            const void* ray_direction4, uint64_t n, void* hit4,
                            float* elapsed_ms);
 
+/* Closest hit for n rays WITHOUT ANY ALLOCATION.  This entry point has no counterpart in the reference; it was
+ * added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same result as amber_cuda_cast, but inputs and outputs
+ * are caller-owned DEVICE buffers on the context's device (origins / directions: n*3 floats, unit directions;
+ * prim: n int32, -1 on a miss; t: n floats, NaN on a miss) and the packed rays and hit records in between live in a
+ * static device array of the library sized for AMBER_CUDA_CAST_STATIC_MAX rays (3 MiB, held by every GPU that loads
+ * the library until the process exits).  n beyond that is refused with AMBER_CUDA_EINVAL.  The call makes no
+ * cudaMalloc / cudaFree or other allocating call; it runs on the context's stream and returns when the results
+ * are in device_prim / device_t (the caller synchronises its own producer of the inputs first).  Every call on
+ * a device shares the one array, which keeps the last call's contents (each call overwrites what it reads);
+ * calls that overlap on the same GPU -- from different contexts or processes' threads -- race on it, and
+ * contexts that share a device already take turns (see the conventions above). */
+#define AMBER_CUDA_CAST_STATIC_MAX 65536
+int amber_cuda_cast_static(amber_cuda_ctx* ctx, const float* device_origins3, const float* device_directions3,
+                           uint64_t n, int32_t* device_prim, float* device_t);
+
 /* Per-vertex unit checks (parity entry points; each runs one tiny kernel).
  * sample_light: n BSDF samples for material `material` at normal/dir_out with the
  * scripted uniforms xi[n][8]; outputs direction, rgb weight and draws consumed.
