@@ -1384,6 +1384,7 @@ int amber_cuda_resolve(amber_cuda_ctx* ctx, float* host_rgb, uint64_t* samples_d
   if (!host_rgb) return fail(ctx, AMBER_CUDA_EINVAL, "host_rgb is NULL");
   const int wait_rc = amber_cuda_wait(ctx);
   if (wait_rc != AMBER_CUDA_OK) return wait_rc;
+  trace(ctx, "resolve: queue drained");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   const uint32_t n_pixels = ctx->camera.sensor.width * ctx->camera.sensor.height;
   CUDA_TRY(ctx, ctx->d_resolved.resize(static_cast<size_t>(n_pixels) * 3));
@@ -1393,8 +1394,10 @@ int amber_cuda_resolve(amber_cuda_ctx* ctx, float* host_rgb, uint64_t* samples_d
   ctx->stats.kernel_launches++;
   CUDA_TRY(ctx, cudaMemcpyAsync(host_rgb, ctx->d_resolved.ptr, static_cast<size_t>(n_pixels) * 3 * sizeof(float),
                                 cudaMemcpyDeviceToHost, ctx->stream));
+  trace(ctx, "resolve: kernel and copy of %zu bytes queued", static_cast<size_t>(n_pixels) * 3 * sizeof(float));
   const int count_rc = film_sample_count(ctx, samples_done);  // synchronises the stream
   if (count_rc != AMBER_CUDA_OK) return count_rc;
+  trace(ctx, "resolve: done");
   CUDA_TRY(ctx, cudaGetLastError());
   return AMBER_CUDA_OK;
 }

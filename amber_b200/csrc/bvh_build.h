@@ -174,13 +174,15 @@ struct WideBvhHost {
 inline int32_t leaf_ref(int32_t first, int32_t count) { return ~((first << 3) | count); }
 
 // pad so that float rounding in the slab test can never cull a true hit: the device evaluates
-// t = q * (s * idir) + (o * idir - O * idir) (bvh.cuh node_step), four roundings of relative size
-// 2^-24 on terms no larger than the scene, where the exact slab test has none
-inline void padded(const Box& b, float* lo, float* hi) {
+// t = q * (s * idir) + (o * idir - O * idir) (bvh.cuh node_step), four roundings of relative size 2^-24 on
+// terms as large as the ray origin, the node origin and the node extent -- so the slack scales with the
+// largest coordinate of the WHOLE scene (`scene_scale`: max |coordinate| of the root box, at least 1), not with
+// the child's own coordinates: a child near the coordinate origin of a scene that reaches out to 1000 units
+// is decoded with the rounding error of 1000-unit operands.
+inline void padded(const Box& b, float scene_scale, float* lo, float* hi) {
   for (int a = 0; a < 3; a++) {
-    const float m = std::max(std::max(std::fabs(b.lo[a]), std::fabs(b.hi[a])), 1.0f);
-    lo[a] = b.lo[a] - 2e-6f * m;
-    hi[a] = b.hi[a] + 2e-6f * m;
+    lo[a] = b.lo[a] - 2e-6f * scene_scale;
+    hi[a] = b.hi[a] + 2e-6f * scene_scale;
   }
 }
 
@@ -266,6 +268,9 @@ inline WideBvhHost build(const float* verts9, uint32_t n) {
   }
   // collapse 2 -> 4: breadth-first, each wide node adopts up to four descendants,
   // always opening the inner child with the largest surface area
+  float scene_scale = 1.0f;
+  for (int a = 0; a < 3; a++)
+    scene_scale = std::max(scene_scale, std::max(std::fabs(n2[root].box.lo[a]), std::fabs(n2[root].box.hi[a])));
   struct Pending {
     int32_t node2;
     int32_t wide;
@@ -300,7 +305,7 @@ inline WideBvhHost build(const float* verts9, uint32_t n) {
     int32_t refs[4];
     for (int k = 0; k < n_kids; k++) {
       const Node2& child = n2[kids[k]];
-      padded(child.box, lo[k], hi[k]);
+      padded(child.box, scene_scale, lo[k], hi[k]);
       if (child.count > 0) {
         refs[k] = leaf_ref(child.first, child.count);
       } else {

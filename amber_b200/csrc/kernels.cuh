@@ -292,13 +292,17 @@ __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(con
   const uint32_t generated = left < n_free ? static_cast<uint32_t>(left) : n_free;
   const uint32_t first_entry = n_free - generated;
   const uint32_t n_new = AMBER_RAYGEN_LOOP ? generated : min(generated, (blockIdx.x + 1) * kBlock);
-  for (uint32_t j = ctl->n_marked + blockIdx.x * kBlock + threadIdx.x; j < first_entry; j += gridDim.x * kBlock)
-    args.pool.ray[2 * static_cast<size_t>(args.pool.q_new[j])] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  const uint32_t n_marked = ctl->n_marked;
   const unsigned long long base_pixel = ctl->base_pixel, base_ordinal = ctl->base_sample;
   const uint32_t width = c_camera.sensor.width;
   const uint32_t* __restrict__ entries = args.pool.q_new + first_entry;
   for (uint32_t j = blockIdx.x * kBlock + threadIdx.x; j < n_new; j += gridDim.x * kBlock) {
     const uint32_t slot = entries[j];
+    // Never taken; it makes the slot id a dependency at the TOP of the iteration.  Without it the compiler
+    // keeps the load in flight until the stores at the bottom and reuses its address registers for them, and
+    // the next iteration's load then waits on stores still queued in the LSU (ncu: lg_throttle 0.19 -> 1.04
+    // stalls per issue): 52.0 us per launch against 45.9 us with this line (1.68 M new paths).
+    if (slot >= args.pool.n_slots) continue;
     float4* ray = args.pool.ray + 2 * static_cast<size_t>(slot);
     // path = next_path + j = (base_sample * n_pixels + base_pixel) + j: the 64-bit division is done once
     // per launch by `bookkeep`, a thread divides the 32-bit (base_pixel + j)
@@ -330,6 +334,9 @@ __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(con
     state[0] = make_float4(w3.x, w3.y, w3.z, 0.0f);
     state[1] = make_float4(__uint_as_float(pixel), __uint_as_float(sample), __uint_as_float(kFlagCountEmission), 0.0f);
   }
+  // (after the main loop: in front of it the main loop's loads of the control block are ordered behind these stores)
+  for (uint32_t j = n_marked + blockIdx.x * kBlock + threadIdx.x; j < first_entry; j += gridDim.x * kBlock)
+    args.pool.ray[2 * static_cast<size_t>(args.pool.q_new[j])] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 }
 
 // Fills q_new with every slot (start of a render call: all slots are free).
@@ -548,9 +555,9 @@ __device__ __forceinline__ bool sample_direct(const SceneView& scene, const Mate
     if (__ldg(&scene.lights[mid].v0.w) < target) lo = mid + 1; else hi = mid;
   }
   const float4* L = reinterpret_cast<const float4*>(scene.lights + lo);
-  // an emitting sphere is not light-sampled: no shadow ray when the power CDF picks one; its emission is
-  // counted on every BSDF-sampled hit instead (shade_kernel, sampled_by_nee) -- same expectation
-  if (__ldg(L + 5).x > 0.0f) return false;
+  // an emitting sphere is not light-sampled: its record carries a zero normal, so cos_y below is 0 and no shadow
+  // ray is queued when the power CDF picks one; its emission is counted on every BSDF-sampled hit instead
+  // (shade_kernel, sampled_by_nee) -- same expectation
   const float4 v0 = __ldg(L), v1 = __ldg(L + 1), v2 = __ldg(L + 2), nl = __ldg(L + 3), le = __ldg(L + 4);
   if (u + v >= 1.0f) {
     u = 1.0f - u;

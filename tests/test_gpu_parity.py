@@ -302,6 +302,42 @@ def test_bvh_path_matches_oracle(device, oracle_lib):
         assert image_agreement(image, want) >= 0.985
 
 
+def test_bvh_far_from_the_coordinate_origin(device, oracle_lib):
+    """The quantised child boxes are padded for the rounding of the device's slab arithmetic, which scales with
+    the scene's largest coordinate: a mesh pushed 1000 units away (and one corner of it left near the origin)
+    must not lose hits -- a culled box shows up as a miss where the brute-force oracle hits."""
+    from amber_b200 import FlatSceneBuilder
+    from amber_b200.scene import icosphere
+    rng = np.random.default_rng(5)
+    offset = np.array([1000.0, -700.0, 850.0])
+    b = FlatSceneBuilder()
+    b.make_thin_lens([1, 0, 0, 1000, 0, 1, 0, -700, 0, 0, 1, 854, 0, 0, 0, 1], 0.05, 4.0, 0.05, 6, add_aperture_objects=False)
+    grey = b.make_lambertian((.5, .5, .5))
+    b.add_triangles(icosphere(4, center=tuple(offset), radius=2.0, displacement=0.1), grey)       # 5120 triangles far out
+    b.add_triangles(icosphere(2, center=(0.0, 0.0, 0.0), radius=1.0, displacement=0.05), grey)   # 320 near the origin
+    b.add_triangle((0, 0, 0), (1000, -700, 850), (1000, -700, 852), b.make_diffuse_light((1, 1, 1)))  # spans both
+    scene = b.build()
+    oracle = oracle_lib.Oracle(scene)
+    device.upload_scene(scene)
+    assert device.stats()["accel"] == 1
+    n = 40000
+    # rays from around either cluster towards it, and rays from one cluster to the other
+    centres = np.where(rng.random((n, 1)) < 0.5, offset[None, :], np.zeros((1, 3)))
+    o = (centres + unit_vectors(rng, n) * rng.uniform(3.0, 6.0, (n, 1))).astype(np.float32)
+    target = centres + rng.normal(0, 0.8, (n, 3))
+    target[: n // 8] = (offset[None, :] - centres[: n // 8]) + rng.normal(0, 0.8, (n // 8, 3))   # across the scene
+    d = (target - o).astype(np.float64)
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    want_prim, want_t = oracle.cast(o, d, threads=32)
+    prim, t = device.cast(o, d)
+    lost = (want_prim >= 0) & (prim < 0)
+    print(f"far scene: oracle hits {(want_prim >= 0).mean():.3f}, ids agree {(prim == want_prim).mean():.5f}, lost hits {lost.sum()}")
+    assert (want_prim >= 0).mean() > 0.3
+    # at 1000 units one float ulp is 6e-5: grazing hits may go to a neighbouring triangle or across a silhouette on
+    # either side; a conservative traversal loses (almost) none of the oracle's hits
+    assert lost.mean() <= 2e-4 and (prim == want_prim).mean() >= 0.995
+
+
 def test_bvh_full_size_mesh_against_brute_force(device, oracle_lib):
     """Config 4's geometry at full size (1 310 720-triangle displaced icosphere + room): the
     persistent BVH traversal against the oracle's brute-force scan on a ray set small enough
