@@ -446,10 +446,19 @@ def run_gpu(args) -> None:
             traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
             if os.path.exists(traffic_file):
                 measured = json.load(open(traffic_file)).get("extend_bvh", {})
-                c4_profile["roofline"]["traffic"] = measured.get("dram_bytes_per_launch")
-                for key in ("l2_bytes_per_launch", "dram_gbs", "l2_gbs", "captured_with"):
-                    if key in measured:
-                        c4_profile["roofline"][key] = measured[key]
+                roof = c4_profile["roofline"]
+                roof["traffic"] = measured.get("dram_bytes_per_launch")
+                if roof["traffic"]:
+                    # ncu's bytes of one steady-state launch (profiles/traffic.json) over the LIVE launch time
+                    roof["dram_gbs"] = roof["traffic"] / (ext_us * 1e-6) / 1e9
+                    roof["dram_frac"] = roof["dram_gbs"] / peak
+                if measured.get("l2_read_bytes_per_launch"):
+                    roof["l2_read_bytes_per_launch"] = measured["l2_read_bytes_per_launch"]
+                    roof["l2_read_gbs"] = measured["l2_read_bytes_per_launch"] / (ext_us * 1e-6) / 1e9
+                roof["reading"] = ("achieved = the traversal's byte demand (nodes visited x node bytes + triangles tested x record "
+                                   "bytes + 40 B per ray) over the launch time: what L1 must deliver; l2_read_gbs / dram_gbs = what "
+                                   "L2 / DRAM actually moved (ncu).  The kernel is bound by dependent-load latency at ~14 of 32 "
+                                   "lanes per instruction, not by any of these bandwidths (profiles/r02_mesh_summary.txt)")
         c4.update({"job": f"Cornell room + 1 310 720-triangle displaced icosphere, 2048x2048, 64 spp split over {world} rank(s) "
                           "(BASELINE configs[3])", "spp_per_rank": m_count, "primitives": int(mesh.desc.n_primitives),
                    "scene_generation_s": scene_s, "upload_and_bvh_build_s": upload_s})
