@@ -235,6 +235,9 @@ struct WideBvh {
       // ---- fetch ----------------------------------------------------------------------
       const bool idle = current == kEmptyChild && parked == kEmptyChild;
       const uint32_t idle_mask = __ballot_sync(kFull, idle);
+      // (Measured and dropped: a per-warp reserved range that grows after refills that found no ray, so that sweeping a
+      // draining pool costs fewer atomics -- the extra bookkeeping cost the steady state 4 %: 51.6 -> 53.9 ms per 16 spp,
+      // and a short job gained nothing: 29.7 -> 30.9 ms per 8 spp.)
       if (idle_mask == kFull && exhausted) break;
       if (!exhausted && (__popc(idle_mask) >= kRefillLanes || idle_mask == kFull)) {
         if (idle && have_item) {

@@ -286,6 +286,7 @@ __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(con
   // unused it is marked empty here (entries [n_marked, first_entry): only the ones appended since the last
   // launch; nothing to do while every free slot is reused at once, the steady state).
   const Control* ctl = args.ctl;
+  if (ctl->done) return;  // the render has finished: the iterations queued behind the last useful one cost a launch each
   const unsigned long long next_path = ctl->next_path, total_paths = ctl->total_paths;
   const uint32_t n_free = ctl->n_new;
   const unsigned long long left = next_path < total_paths ? total_paths - next_path : 0ull;
@@ -373,6 +374,7 @@ __global__ void bookkeep_kernel(Control* ctl) {
 // ray pass active = false.
 template <class Accel>
 __global__ void __launch_bounds__(kBlock) extend_kernel(const RenderArgs args) {
+  if (args.ctl->done) return;
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   const bool in_range = i < args.pool.n_slots;
   float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
@@ -450,12 +452,14 @@ struct ExtendSource {
 
 template <>
 __global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) extend_kernel<WideBvh>(const RenderArgs args) {
+  if (args.ctl->done) return;
   ExtendSource source{args, {-1}};
   WideBvh::trace_persistent<false>(args.scene, source, &args.ctl->cursor_extend);
 }
 
 // profiling mode: the same kernel with the traversal work counted (amber_cuda_stats.bvh_*)
 __global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) extend_bvh_counting_kernel(const RenderArgs args) {
+  if (args.ctl->done) return;
   ExtendSource source{args, {-1}};
   WideBvh::trace_persistent<false, true>(args.scene, source, &args.ctl->cursor_extend, &args.ctl->bvh_work[0]);
 }
@@ -648,6 +652,7 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
   __shared__ uint32_t warp_scan[kShadeBlock / 32];
   __shared__ uint32_t queue_base[2];
   __shared__ uint32_t next_chunk;
+  if (args.ctl->done) return;  // (block-uniform: before any barrier)
   const PathPool& pool = args.pool;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t tile_base = blockIdx.x * kShadeTile;
