@@ -1051,6 +1051,7 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, const amber_cuda_re
       });
       bookkeep_kernel<<<1, 1, 0, stream>>>(args.ctl);
       timed(1, [&] {
+        if (AMBER_FUSE_EXTEND && !Accel::kPersistent) return;  // experiment: raygen and shade found the hits
         if (profile && Accel::kPersistent) launch_extend_counting(args, trace_grid, dynamic_smem, stream);
         else extend_kernel<Accel><<<trace_grid, kBlock, dynamic_smem, stream>>>(args);
       });

@@ -276,6 +276,11 @@ constexpr int kQueueBlocks = AMBER_QUEUE_BLOCKS;  // resident blocks per SM of t
 #ifndef AMBER_RAYGEN_LOOP
 #define AMBER_RAYGEN_LOOP 1
 #endif
+// Experiment: with the constant-memory list the closest hit of a path's NEXT ray is found by the
+// kernel that makes the ray (raygen, shade) and `extend` is not launched.  Off: see DESIGN.md section 4.4.
+#ifndef AMBER_FUSE_EXTEND
+#define AMBER_FUSE_EXTEND 0
+#endif
 template <bool kLightTracing>
 __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(const RenderArgs args) {
   // q_new is the pool's FREE LIST: entries [0, n_new) are slots without a path.  This launch starts
@@ -334,6 +339,15 @@ __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(con
     float4* state = args.pool.state + 2 * static_cast<size_t>(slot);
     state[0] = make_float4(w3.x, w3.y, w3.z, 0.0f);
     state[1] = make_float4(__uint_as_float(pixel), __uint_as_float(sample), __uint_as_float(kFlagCountEmission), 0.0f);
+#if AMBER_FUSE_EXTEND
+    if (!args.scene.bvh_nodes) {
+      Ray first;
+      first.o = o;
+      first.d = d;
+      const HitRecord h = ConstList::closest(args.scene, first, true);
+      args.pool.hit[slot] = make_float2(h.t, __int_as_float(h.prim));
+    }
+#endif
   }
   // (after the main loop: in front of it the main loop's loads of the control block are ordered behind these stores)
   for (uint32_t j = n_marked + blockIdx.x * kBlock + threadIdx.x; j < first_entry; j += gridDim.x * kBlock)
@@ -346,6 +360,9 @@ __global__ void __launch_bounds__(kBlock) pool_reset_kernel(const RenderArgs arg
   if (i >= args.pool.n_slots) return;
   args.pool.q_new[i] = i;
   args.pool.ray[2 * static_cast<size_t>(i)] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#if AMBER_FUSE_EXTEND
+  args.pool.hit[i] = make_float2(CUDART_NAN_F, __int_as_float(-2));
+#endif
 }
 
 __global__ void bookkeep_kernel(Control* ctl) {
@@ -743,6 +760,9 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
     if (j >= n_live) continue;
     if (j >= n_hit) {  // miss: the slot is free again
       freed_mask |= 1u << r;
+#if AMBER_FUSE_EXTEND
+      if (!args.scene.bvh_nodes) pool.hit[tile_base + sorted[j]] = make_float2(CUDART_NAN_F, __int_as_float(kPrimDead));
+#endif
       continue;
     }
     const uint32_t slot = tile_base + sorted[j];
@@ -820,6 +840,9 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
       freed_mask |= 1u << r;
       // the vertex stays readable for `connect` (shadow origin); w = 0 marks the slot free
       ray_slot[0] = make_float4(x.x, x.y, x.z, 0.0f);
+#if AMBER_FUSE_EXTEND
+      if (!args.scene.bvh_nodes) pool.hit[slot] = make_float2(CUDART_NAN_F, __int_as_float(kPrimDead));
+#endif
     } else {
       const float inv_p = __fdividef(1.0f, p);  // scales the throughput only
       throughput = throughput * (inv_p * scatter.weight);
@@ -827,6 +850,15 @@ __global__ void __launch_bounds__(kShadeBlock, AMBER_SHADE_MIN_BLOCKS) shade_ker
       ray_slot[1] = make_float4(scatter.dir.x, scatter.dir.y, scatter.dir.z, 0.0f);
       state_slot[0] = make_float4(throughput.x, throughput.y, throughput.z, 0.0f);
       state_slot[1] = make_float4(m4.x, m4.y, __uint_as_float(depth | (connect ? 0u : kFlagCountEmission)), 0.0f);
+#if AMBER_FUSE_EXTEND
+      if (!args.scene.bvh_nodes) {
+        Ray next;
+        next.o = x;
+        next.d = scatter.dir;
+        const HitRecord h = ConstList::closest(args.scene, next, true);
+        pool.hit[slot] = make_float2(h.t, __int_as_float(h.prim));
+      }
+#endif
     }
   }
 
