@@ -524,7 +524,7 @@ int wide_bvh_depth(const bvh_build::WideBvhHost& bvh) {
     const auto [node, d] = todo.back();
     todo.pop_back();
     depth = std::max(depth, d);
-    for (int c = 0; c < 4; c++) {
+    for (int c = 0; c < 4 && bvh_build::kWidth == 4; c++) {
       int32_t ref;
       std::memcpy(&ref, &bvh.nodes[static_cast<size_t>(node) * bvh_build::kNodeFloats + 12 + c], sizeof ref);
       if (ref >= 0 && ref != bvh_build::kEmpty) todo.push_back({ref, d + 1});
@@ -535,12 +535,15 @@ int wide_bvh_depth(const bvh_build::WideBvhHost& bvh) {
 
 // Persistent BVH kernels: stack size from the tree depth, grid = SMs x resident blocks.
 int configure_bvh_launch(amber_cuda_ctx* ctx, const bvh_build::WideBvhHost& bvh) {
-  const int depth = wide_bvh_depth(bvh);
-  ctx->bvh_stack_entries = static_cast<uint32_t>(3 * depth + 1);
-  if (ctx->bvh_stack_entries > static_cast<uint32_t>(kBvhStackMax))
-    return fail(ctx, AMBER_CUDA_EINVAL, "BVH depth %d needs %u stack entries per lane (limit %d)", depth,
-                ctx->bvh_stack_entries, kBvhStackMax);
-  ctx->bvh_smem = static_cast<size_t>(ctx->bvh_stack_entries) * kBlock * sizeof(int32_t);
+  // 4-wide: a node step pushes up to three 4-byte child references; 8-wide: at most one 8-byte node group
+  const int depth = bvh_build::kWidth == 8 ? bvh.depth : wide_bvh_depth(bvh);
+  const size_t entry_bytes = bvh_build::kWidth == 8 ? sizeof(uint2) : sizeof(int32_t);
+  const uint32_t entry_limit = bvh_build::kWidth == 8 ? 64u : static_cast<uint32_t>(kBvhStackMax);  // 8-wide: bdpt.cuh kLaneStackMax
+  ctx->bvh_stack_entries = static_cast<uint32_t>(bvh_build::kWidth == 8 ? depth + 1 : 3 * depth + 1);
+  if (ctx->bvh_stack_entries > entry_limit)
+    return fail(ctx, AMBER_CUDA_EINVAL, "BVH depth %d needs %u stack entries per lane (limit %u)", depth,
+                ctx->bvh_stack_entries, entry_limit);
+  ctx->bvh_smem = static_cast<size_t>(ctx->bvh_stack_entries) * kBlock * entry_bytes;
   cudaDeviceProp prop;
   CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, ctx->device));
   const void* kernels[] = {reinterpret_cast<const void*>(&extend_kernel<WideBvh>),
@@ -559,6 +562,11 @@ int configure_bvh_launch(amber_cuda_ctx* ctx, const bvh_build::WideBvhHost& bvh)
     resident = std::min(resident, blocks);
   }
   if (resident < 1) return fail(ctx, AMBER_CUDA_ECUDA, "BVH kernels do not fit on an SM (%zu B of shared memory)", ctx->bvh_smem);
+#ifdef AMBER_BVH_CARVEOUT
+  // what the stacks do not need of the SM's 228 KB is L1 for nodes and triangles: ask for exactly that split
+  const int carveout = static_cast<int>(std::min<size_t>(100, (ctx->bvh_smem + 1024) * static_cast<size_t>(resident) * 100 / (228 * 1024) + 1));
+  for (const void* k : kernels) CUDA_TRY(ctx, cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, carveout));
+#endif
   ctx->bvh_grid = static_cast<unsigned int>(prop.multiProcessorCount * resident);
   return AMBER_CUDA_OK;
 }
@@ -803,6 +811,7 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   std::memset(&ctx->const_scene, 0, sizeof(ConstScene));
   ctx->const_scene.n_tris = use_bvh ? 0 : static_cast<int32_t>(n_tris);
   ctx->const_scene.n_spheres = static_cast<int32_t>(n_spheres);
+  ctx->const_scene.bvh_plane_magic = bvh_build::kPlaneMagic;
   ctx->const_scene.n_groups = static_cast<int32_t>(const_list.groups.size());
   for (int axis = 0; axis < 3; axis++) ctx->const_scene.n_axis_entries[axis] = const_list.n_axis_entries[axis];
   ctx->const_scene.n_clusters = static_cast<int32_t>(const_list.clusters.size());

@@ -99,6 +99,19 @@ template <>
 __device__ __forceinline__ HitRecord closest_lane_inline<ConstList>(const SceneView& scene, const Ray& ray) {
   return ConstList::closest(scene, ray, true);
 }
+#if AMBER_BVH_WIDTH == 8
+constexpr int kLaneStackMax = 64;  // node groups: one entry per level (configure_bvh_launch refuses deeper trees)
+template <>
+__device__ __forceinline__ HitRecord closest_lane_inline<WideBvh>(const SceneView& scene, const Ray& ray) {
+  SphereBound spheres;
+  HitRecord hit;
+  hit.t = spheres.bound(scene, ray);
+  hit.prim = -1;
+  uint2 stack[kLaneStackMax];
+  const bool found = WideBvh::walk_lane<false>(scene, ray, hit, stack);
+  return spheres.resolve(scene, hit, found);
+}
+#else
 template <>
 __device__ __forceinline__ HitRecord closest_lane_inline<WideBvh>(const SceneView& scene, const Ray& ray) {
   SphereBound spheres;
@@ -128,6 +141,8 @@ __device__ __forceinline__ HitRecord closest_lane_inline<WideBvh>(const SceneVie
   }
   return spheres.resolve(scene, hit, found);
 }
+
+#endif
 
 template <class Accel>
 __device__ __noinline__ HitRecord closest_lane(const SceneView& scene, const Ray& ray) {

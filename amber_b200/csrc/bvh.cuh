@@ -11,7 +11,7 @@
 // bound by the L1 gather path (every lane reads its own line; measured: lane-gathers cost in
 // proportion to the SECTORS they touch, scripts/micro/gather.cu), so the node is as small as four
 // children allow: child boxes are 8-bit grid indices on the node's own box,
-//   plane = origin + q * scale   (lo rounded down, hi rounded up: conservative; bvh_build.h)
+//   plane = origin + g(code) * scale   (g: bvh_build.h plane_coordinate; lo rounded down, hi rounded up: conservative)
 //   [0] origin.xyz, scale.x      [1] scale.yz, x-lo word, x-hi word (byte k = child k)
 //   [2] y-lo, y-hi, z-lo, z-hi   [3] child references (int bits): >= 0 inner node index; < 0
 //       leaf, ~ref = (first_triangle << 3) | triangle_count; kEmptyChild for an unused lane
@@ -22,6 +22,9 @@
 
 namespace amber_cuda {
 
+#ifndef AMBER_BVH_WIDTH
+#define AMBER_BVH_WIDTH 4
+#endif
 constexpr int kBvhStackMax = 160;  // entries per lane the 227 KB of shared memory allow at 256 threads + margin
 // Vote thresholds of trace_persistent, measured on the 1.3 M-triangle scene (closest hit: 8/16
 // 544 us, 20/12 592 us per launch; any hit: 20/12 286 us, 8/16 339 us -- shadow rays end early, so
@@ -47,8 +50,26 @@ constexpr int kBvhStackMax = 160;  // entries per lane the 227 KB of shared memo
 #ifndef AMBER_BVH_PREFETCH_L2
 #define AMBER_BVH_PREFETCH_L2 0  // 1: when a node step finds a leaf child in range, its triangles are prefetched into L2
 #endif
+#ifndef AMBER_BVH_LEAF_PREFETCH
+#define AMBER_BVH_LEAF_PREFETCH 0  // 8-wide: 1 = L1 prefetch of a triangle group's later triangles at the start of the leaf phase
+#endif
+#ifndef AMBER_BVH_LEAF_PAIRS
+#define AMBER_BVH_LEAF_PAIRS 0  // 8-wide: 1 = the leaf phase loads two triangles per round
+#endif
 #ifndef AMBER_BVH_TRI_NO_ALLOCATE
 #define AMBER_BVH_TRI_NO_ALLOCATE 0  // 1: triangle records bypass L1 allocation (they are rarely re-read; nodes are)
+#endif
+// Phase policy of trace_persistent.  0: descend while >= kMinDescendLanes lanes hold an inner node, test leaves as soon as fewer
+// do and ANY lane holds a leaf, refill only between the two.  1: one vote per step picks the phase -- refill as soon as
+// kRefillLanes lanes are idle, test leaves only once kLeafLanes lanes hold one (or nothing else is left to do), else descend.
+#ifndef AMBER_BVH_POLICY
+#define AMBER_BVH_POLICY 0
+#endif
+#ifndef AMBER_BVH_LEAF_LANES
+#define AMBER_BVH_LEAF_LANES 12
+#endif
+#ifndef AMBER_BVH_LEAF_LANES_ANYHIT
+#define AMBER_BVH_LEAF_LANES_ANYHIT 12
 #endif
 constexpr int kBvhLeafMax = 4;
 constexpr int32_t kEmptyChild = 0x7fffffff;
@@ -80,19 +101,22 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 __device__ __forceinline__ int32_t bvh_leaf_first(int32_t ref) { return (~ref) >> 3; }
 __device__ __forceinline__ int32_t bvh_leaf_count(int32_t ref) { return (~ref) & 7; }
 
-struct WideBvh {
-  // Byte k of a packed plane word as a float: PRMT builds 2^23 + q, the subtraction is exact.
-  template <int k>
-  static __device__ __forceinline__ float plane_magic(uint32_t word) {  // 2^23 + byte k
-    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440 | k));
-  }
-  template <int k>
-  static __device__ __forceinline__ float plane_byte(uint32_t word) {
-    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440 | k)) - 8388608.0f;
-  }
+// Plane code -> grid coordinate (bvh_build.h, plane_coordinate): byte k of a packed plane word becomes bits 16-23 of
+// the float 0x3F000000 | code << 16.  `magic` = 0x3F000000 must arrive in a REGISTER the compiler cannot see through (a
+// word of the node, a constant-bank load): PRMT takes one immediate, and with the selector as the immediate the
+// instruction stands alone -- with a known magic the compiler makes THAT the immediate and spends a move on the
+// selector in front of every permute (48 moves per 8-wide node step).
+template <int k>
+__device__ __forceinline__ float plane_float(uint32_t word, uint32_t magic) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(word), "r"(magic), "n"(0x7044 | (k << 8)));
+  return __uint_as_float(r);
+}
 
-  // Slab test of child k against [0, t_best] in the node's quantised frame: the plane at grid
-  // index q lies at ray parameter q * s + o with s = scale * idir, o = (origin - O) * idir per
+#if AMBER_BVH_WIDTH == 4
+struct WideBvh {
+  // Slab test of child k against [0, t_best] in the node's quantised frame: the plane with grid
+  // coordinate g lies at ray parameter g * s + o with s = scale * idir, o = (origin - O) * idir per
   // axis; `near`/`far` are the plane words already chosen by the sign of the direction, so no
   // min/max per axis is left.  Returns the entry distance or +inf.  fminf/fmaxf drop NaNs
   // (0 * inf on an axis-parallel ray), which only ever makes the test more permissive; boxes
@@ -100,24 +124,16 @@ struct WideBvh {
   template <int k>
   static __device__ __forceinline__ float child_entry(uint32_t near_x, uint32_t far_x, uint32_t near_y, uint32_t far_y,
                                                       uint32_t near_z, uint32_t far_z, const float3& s,
-                                                      const float3& o, float t_best, int32_t ref) {
-#ifdef AMBER_BVH_SCALAR_DECODE
-    const float nx = fmaf(plane_byte<k>(near_x), s.x, o.x), fx = fmaf(plane_byte<k>(far_x), s.x, o.x);
-    const float ny = fmaf(plane_byte<k>(near_y), s.y, o.y), fy = fmaf(plane_byte<k>(far_y), s.y, o.y);
-    const float nz = fmaf(plane_byte<k>(near_z), s.z, o.z), fz = fmaf(plane_byte<k>(far_z), s.z, o.z);
-#else
-    // the near and far plane of an axis go through one packed FADD2 + FFMA2 (sm_100)
-    const float2 magic = make_float2(-8388608.0f, -8388608.0f);
-    const float2 x = __ffma2_rn(__fadd2_rn(make_float2(plane_magic<k>(near_x), plane_magic<k>(far_x)), magic),
+                                                      const float3& o, float t_best, int32_t ref, uint32_t magic) {
+    // the near and far plane of an axis go through one packed FFMA2 (sm_100)
+    const float2 x = __ffma2_rn(make_float2(plane_float<k>(near_x, magic), plane_float<k>(far_x, magic)),
                                 make_float2(s.x, s.x), make_float2(o.x, o.x));
-    const float2 y = __ffma2_rn(__fadd2_rn(make_float2(plane_magic<k>(near_y), plane_magic<k>(far_y)), magic),
+    const float2 y = __ffma2_rn(make_float2(plane_float<k>(near_y, magic), plane_float<k>(far_y, magic)),
                                 make_float2(s.y, s.y), make_float2(o.y, o.y));
-    const float2 z = __ffma2_rn(__fadd2_rn(make_float2(plane_magic<k>(near_z), plane_magic<k>(far_z)), magic),
+    const float2 z = __ffma2_rn(make_float2(plane_float<k>(near_z, magic), plane_float<k>(far_z, magic)),
                                 make_float2(s.z, s.z), make_float2(o.z, o.z));
-    const float nx = x.x, fx = x.y, ny = y.x, fy = y.y, nz = z.x, fz = z.y;
-#endif
-    const float t_near = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
-    const float t_far = fminf(fminf(fx, fy), fminf(fz, t_best));
+    const float t_near = fmaxf(fmaxf(x.x, y.x), fmaxf(z.x, 0.0f));
+    const float t_far = fminf(fminf(x.y, y.y), fminf(z.y, t_best));
     return (t_near <= t_far) & (ref != kEmptyChild) ? t_near : CUDART_INF_F;
   }
 
@@ -141,10 +157,11 @@ struct WideBvh {
     const float4 ref4 = tail.b;
     int32_t c0 = __float_as_int(ref4.x), c1 = __float_as_int(ref4.y), c2 = __float_as_int(ref4.z),
             c3 = __float_as_int(ref4.w);
-    float d0 = child_entry<0>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c0);
-    float d1 = child_entry<1>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c1);
-    float d2 = child_entry<2>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c2);
-    float d3 = child_entry<3>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c3);
+    const uint32_t magic = c_scene.bvh_plane_magic;  // (an opaque register: see plane_float)
+    float d0 = child_entry<0>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c0, magic);
+    float d1 = child_entry<1>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c1, magic);
+    float d2 = child_entry<2>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c2, magic);
+    float d3 = child_entry<3>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, c3, magic);
     if (AMBER_BVH_PREFETCH_L2) {
       // a leaf child in range will be visited unless a nearer hit cuts the ray short first: start moving its
       // triangles from DRAM to L2 now (the leaf phase's loads are the traversal's longest stalls)
@@ -231,6 +248,77 @@ struct WideBvh {
     hit.prim = -1;
     uint32_t node_steps = 0, triangle_tests = 0;
 
+#if AMBER_BVH_POLICY
+    constexpr int kLeafLanes = kAnyHit ? AMBER_BVH_LEAF_LANES_ANYHIT : AMBER_BVH_LEAF_LANES;
+    while (true) {
+      const bool inner = static_cast<uint32_t>(current) < static_cast<uint32_t>(kEmptyChild);
+      const uint32_t inner_mask = __ballot_sync(kFull, inner);
+      const uint32_t leaf_mask = __ballot_sync(kFull, current < 0);
+      const uint32_t idle_mask = ~(inner_mask | leaf_mask);
+      if (idle_mask == kFull && exhausted) break;
+      if (!exhausted && (__popc(idle_mask) >= kRefillLanes)) {
+        // ---- fetch --------------------------------------------------------------------
+        const bool idle = current == kEmptyChild;
+        if (idle && have_item) {
+          source.store(item, hit, found);
+          have_item = false;
+        }
+        const uint32_t wanted = __popc(idle_mask);
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(cursor, wanted);
+        base = __shfl_sync(kFull, base, 0);
+        exhausted = base + wanted >= n;
+        if (idle) {
+          const uint32_t mine = base + __popc(idle_mask & lane_lt);
+          float t_best = CUDART_MAX_NORMAL_F;
+          if (mine < n && source.load(mine, ray, t_best)) {
+            item = mine;
+            have_item = true;
+            found = false;
+            hit.t = t_best;
+            hit.prim = -1;
+            sp = 0;
+            idir = v3(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
+            oidir = v3(ray.o.x * idir.x, ray.o.y * idir.y, ray.o.z * idir.z);
+            current = scene.bvh_root;
+          }
+        }
+        continue;
+      }
+      if (__popc(leaf_mask) >= kLeafLanes || inner_mask == 0) {
+        // ---- leaves -------------------------------------------------------------------
+        if (current < 0) {
+          const int first = bvh_leaf_first(current), count = bvh_leaf_count(current);
+          if (kCount) triangle_tests += count;
+#pragma unroll
+          for (int k = 0; k < kBvhLeafMax; k++) {
+            if (k < count) {
+              const float4* tri = reinterpret_cast<const float4*>(scene.tri_isect + first + k);
+              if (intersect_triangle(load_triangle_word(tri), load_triangle_word(tri + 1), load_triangle_word(tri + 2), ray, hit.t, hit.t)) {
+                hit.prim = first + k;
+                found = true;
+              }
+            }
+          }
+          if (kAnyHit && found) {
+            sp = 0;
+            current = kEmptyChild;
+          } else if (sp > 0) {
+            sp--;
+            current = stack[sp * stride];
+          } else {
+            current = kEmptyChild;
+          }
+        }
+        continue;
+      }
+      // ---- descend --------------------------------------------------------------------
+      if (inner) {
+        current = node_step(scene, current, idir, oidir, hit.t, stack, stride, sp);
+        if (kCount) node_steps++;
+      }
+    }
+#else
     while (true) {
       // ---- fetch ----------------------------------------------------------------------
       const bool idle = current == kEmptyChild && parked == kEmptyChild;
@@ -320,6 +408,7 @@ struct WideBvh {
         }
       }
     }
+#endif
     if (have_item) source.store(item, hit, found);
     if (kCount) {
       node_steps = __reduce_add_sync(kFull, node_steps);
@@ -333,5 +422,297 @@ struct WideBvh {
 
   static constexpr bool kPersistent = true;
 };
+
+#else
+// ---- 8-wide ------------------------------------------------------------------------------------------------
+// Node = 6 float4 = 96 B = three sectors, read with three 256-bit loads (host side: bvh_build.h, build8):
+//   words 0-2 origin, 3-5 scale                  (child planes = origin + g(code) * scale, 8 bits per plane, as above)
+//   word  6   child_base: node index of the first INNER child; inner children are consecutive in slot order
+//   word  7   tri_base: index of the first triangle of the first LEAF child; leaf triangles are consecutive
+//   words 8-9 meta, byte k = child slot k: inner (1 << 5) | (24 + k); leaf (count one-bits << 5) | offset from
+//             tri_base (count <= 3, offset + count <= 24); empty 0
+//   word  10  imask: bit k set = slot k holds an inner child          word 11 0x3F000000 (plane_float)
+//   words 12-23 planes: x lo [slots 0-3][4-7], x hi, y lo, y hi, z lo, z hi
+// One node step yields a 32-bit HIT MASK: bits 0-23 the triangles of the leaf children the ray enters (bit =
+// offset from tri_base), bits 24-31 the inner children it enters at bit 24 + (slot ^ octinv), octinv = 7 ^ the
+// ray's direction octant -- the builder puts children into the slot that matches their position in the node, so the
+// HIGHEST set bit is the nearest child for this ray: no distances are compared, nothing is sorted (Ylitie, Karras,
+// Laine, "Efficient incoherent ray traversal on GPUs through compressed wide BVHs", 2017; restated for our node).
+// The traversal state of a ray is a NODE GROUP (child_base, imask << 8 | pending inner children) and a TRIANGLE
+// GROUP (tri_base, pending triangles); a node step pushes at most ONE stack entry -- the rest of the group it took
+// its node from -- so the per-lane stack is `depth` 8-byte entries instead of 3 * depth 4-byte ones.
+__device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {  // each byte: 0xff if its top bit is set, else 0
+  uint32_t r;
+  asm("prmt.b32 %0, %1, 0, 0x0000ba98;" : "=r"(r) : "r"(x));
+  return r;
+}
+
+struct WideBvh {
+  // Slab test of the child in byte k of the plane words (see the 4-wide child_entry): does the ray enter it
+  // within [0, t_best]?  An empty slot has lo = 255 > hi = 0 on every axis and fails.
+  template <int k>
+  static __device__ __forceinline__ bool child_hit(uint32_t near_x, uint32_t far_x, uint32_t near_y, uint32_t far_y,
+                                                   uint32_t near_z, uint32_t far_z, const float3& s, const float3& o,
+                                                   float t_best, uint32_t magic) {
+    const float2 x = __ffma2_rn(make_float2(plane_float<k>(near_x, magic), plane_float<k>(far_x, magic)),
+                                make_float2(s.x, s.x), make_float2(o.x, o.x));
+    const float2 y = __ffma2_rn(make_float2(plane_float<k>(near_y, magic), plane_float<k>(far_y, magic)),
+                                make_float2(s.y, s.y), make_float2(o.y, o.y));
+    const float2 z = __ffma2_rn(make_float2(plane_float<k>(near_z, magic), plane_float<k>(far_z, magic)),
+                                make_float2(s.z, s.z), make_float2(o.z, o.z));
+    const float t_near = fmaxf(fmaxf(x.x, y.x), fmaxf(z.x, 0.0f));
+    const float t_far = fminf(fminf(x.y, y.y), fminf(z.y, t_best));
+    return t_near <= t_far;
+  }
+
+  // Four children (one word of each plane kind): OR their bits into the hit mask.
+  static __device__ __forceinline__ uint32_t four_children(uint32_t lo_x, uint32_t hi_x, uint32_t lo_y, uint32_t hi_y,
+                                                           uint32_t lo_z, uint32_t hi_z, bool rx, bool ry, bool rz,
+                                                           const float3& s, const float3& o, float t_best, uint32_t meta4,
+                                                           uint32_t octinv4, uint32_t magic) {
+    const uint32_t near_x = rx ? hi_x : lo_x, far_x = rx ? lo_x : hi_x;
+    const uint32_t near_y = ry ? hi_y : lo_y, far_y = ry ? lo_y : hi_y;
+    const uint32_t near_z = rz ? hi_z : lo_z, far_z = rz ? lo_z : hi_z;
+    // byte-parallel: which children are inner (index >= 24: bits 3 and 4 set), where their bits go, which bits
+    const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+    const uint32_t index4 = (meta4 ^ (octinv4 & sign_extend_s8x4(is_inner4 << 3))) & 0x1f1f1f1fu;
+    const uint32_t bits4 = (meta4 >> 5) & 0x07070707u;
+    uint32_t mask = 0;
+    if (child_hit<0>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, magic)) mask |= (bits4 & 0xffu) << (index4 & 0xffu);
+    if (child_hit<1>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, magic)) mask |= __byte_perm(bits4, 0, 0x4441) << __byte_perm(index4, 0, 0x4441);
+    if (child_hit<2>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, magic)) mask |= __byte_perm(bits4, 0, 0x4442) << __byte_perm(index4, 0, 0x4442);
+    if (child_hit<3>(near_x, far_x, near_y, far_y, near_z, far_z, s, o, t_best, magic)) mask |= (bits4 >> 24) << (index4 >> 24);
+    return mask;
+  }
+
+  // One node step of one lane: the node's hit mask for this ray, split into the two groups.
+  static __device__ __forceinline__ void node_step(const SceneView& scene, uint32_t node_index, const float3& idir,
+                                                   const float3& oidir, float t_best, uint32_t octinv,
+                                                   uint32_t& group_base, uint32_t& group_hits, uint32_t& tri_base,
+                                                   uint32_t& tri_mask) {
+    const float4* node = scene.bvh_nodes + static_cast<size_t>(node_index) * 6;
+    const Wide8 a = ldg256(node), b = ldg256(node + 2), c = ldg256(node + 4);
+    const float3 s = v3(a.a.w * idir.x, a.b.x * idir.y, a.b.y * idir.z);
+    const float3 o = v3(fmaf(a.a.x, idir.x, -oidir.x), fmaf(a.a.y, idir.y, -oidir.y), fmaf(a.a.z, idir.z, -oidir.z));
+    const bool rx = idir.x < 0.0f, ry = idir.y < 0.0f, rz = idir.z < 0.0f;
+    const uint32_t octinv4 = octinv * 0x01010101u;
+    uint32_t mask = four_children(__float_as_uint(b.b.x), __float_as_uint(b.b.z), __float_as_uint(c.a.x), __float_as_uint(c.a.z),
+                                  __float_as_uint(c.b.x), __float_as_uint(c.b.z), rx, ry, rz, s, o, t_best,
+                                  __float_as_uint(b.a.x), octinv4, __float_as_uint(b.a.w));
+    mask |= four_children(__float_as_uint(b.b.y), __float_as_uint(b.b.w), __float_as_uint(c.a.y), __float_as_uint(c.a.w),
+                          __float_as_uint(c.b.y), __float_as_uint(c.b.w), rx, ry, rz, s, o, t_best,
+                          __float_as_uint(b.a.y), octinv4, __float_as_uint(b.a.w));
+    group_base = __float_as_uint(a.b.z);
+    group_hits = (mask >> 24) | (__float_as_uint(b.a.z) << 8);
+    tri_base = __float_as_uint(a.b.w);
+    tri_mask = mask & 0x00ffffffu;
+  }
+
+  static __device__ __forceinline__ uint32_t octant_inverse(const float3& d) {
+    return 7u ^ ((d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u));
+  }
+  // The group that holds only the root (node 0 = "inner child in slot 0 of a parent whose child_base is 0").
+  static __device__ __forceinline__ uint32_t root_hits(uint32_t octinv) { return (1u << 8) | (1u << octinv); }
+  // Takes the nearest pending child out of a node group; returns its node index.
+  static __device__ __forceinline__ uint32_t take_child(uint32_t group_base, uint32_t& group_hits, uint32_t octinv) {
+    const uint32_t p = 31u - static_cast<uint32_t>(__clz(static_cast<int>(group_hits & 0xffu)));
+    group_hits ^= 1u << p;
+    const uint32_t slot = p ^ octinv;
+    return group_base + __popc((group_hits >> 8) & ((1u << slot) - 1u));
+  }
+
+  // One thread walks one ray on its own (no votes): the BDPT kernel's casts, where lanes of a warp are at
+  // different stages of different paths.  `stack`: `depth` entries.
+  template <bool kAnyHit>
+  static __device__ __forceinline__ bool walk_lane(const SceneView& scene, const Ray& ray, HitRecord& hit, uint2* stack) {
+    const float3 idir = v3(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
+    const float3 oidir = v3(ray.o.x * idir.x, ray.o.y * idir.y, ray.o.z * idir.z);
+    const uint32_t octinv = octant_inverse(ray.d);
+    uint32_t group_base = 0, group_hits = root_hits(octinv), tri_base = 0, tri_mask = 0;
+    int sp = 0;
+    bool found = false;
+    while (true) {
+      if (group_hits & 0xffu) {
+        const uint32_t node = take_child(group_base, group_hits, octinv);
+        if (group_hits & 0xffu) stack[sp++] = make_uint2(group_base, group_hits);
+        node_step(scene, node, idir, oidir, hit.t, octinv, group_base, group_hits, tri_base, tri_mask);
+      }
+      while (tri_mask) {
+        const uint32_t k = tri_base + (__ffs(tri_mask) - 1);
+        tri_mask &= tri_mask - 1u;
+        const float4* tri = reinterpret_cast<const float4*>(scene.tri_isect + k);
+        if (intersect_triangle(__ldg(tri), __ldg(tri + 1), __ldg(tri + 2), ray, hit.t, hit.t)) {
+          hit.prim = static_cast<int32_t>(k);
+          found = true;
+          if (kAnyHit) return true;
+        }
+      }
+      if ((group_hits & 0xffu) == 0) {
+        if (sp == 0) break;
+        const uint2 top = stack[--sp];
+        group_base = top.x;
+        group_hits = top.y;
+      }
+    }
+    return found;
+  }
+
+  // Persistent warp-converged traversal with dynamic ray fetch: same three voted phases as the 4-wide version above
+  // (fetch / descend / leaves; Source, kCount: see there).  A lane is "inner" while its node group has a pending
+  // child and it holds no triangles, "at a leaf" while its triangle group is not empty, idle when both are empty
+  // (the stack is popped as soon as a group runs out, so idle implies an empty stack).
+  template <bool kAnyHit, bool kCount = false, class Source>
+  static __device__ __forceinline__ void trace_persistent(const SceneView& scene, Source& source,
+                                                          unsigned int* cursor,
+                                                          unsigned long long* counters = nullptr) {
+    extern __shared__ uint2 bvh_stack_smem8[];
+    uint2* stack = bvh_stack_smem8 + threadIdx.x;
+    const int stride = blockDim.x;
+    constexpr uint32_t kFull = 0xffffffffu;
+    constexpr int kRefillLanes = kAnyHit ? AMBER_BVH_REFILL_LANES_ANYHIT : AMBER_BVH_REFILL_LANES;
+    constexpr int kMinDescendLanes = kAnyHit ? AMBER_BVH_MIN_DESCEND_LANES_ANYHIT : AMBER_BVH_MIN_DESCEND_LANES;
+    const int lane = threadIdx.x & 31;
+    const uint32_t lane_lt = (1u << lane) - 1u;
+    const uint32_t n = source.count();
+
+    int sp = 0;
+    uint32_t group_base = 0, group_hits = 0, tri_base = 0, tri_mask = 0, octinv = 0;
+    uint32_t item = 0;
+    bool have_item = false, found = false, exhausted = false;
+    Ray ray;
+    ray.o = v3(0.0f, 0.0f, 0.0f);
+    ray.d = v3(0.0f, 0.0f, 1.0f);
+    float3 idir = v3(0.0f, 0.0f, 0.0f), oidir = idir;
+    HitRecord hit;
+    hit.t = 0.0f;
+    hit.prim = -1;
+    uint32_t node_steps = 0, triangle_tests = 0;
+
+    while (true) {
+      // ---- fetch ----------------------------------------------------------------------
+      const bool idle = (group_hits & 0xffu) == 0 && tri_mask == 0;
+      const uint32_t idle_mask = __ballot_sync(kFull, idle);
+      if (idle_mask == kFull && exhausted) break;
+      if (!exhausted && (__popc(idle_mask) >= kRefillLanes || idle_mask == kFull)) {
+        if (idle && have_item) {
+          source.store(item, hit, found);
+          have_item = false;
+        }
+        const uint32_t wanted = __popc(idle_mask);
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(cursor, wanted);
+        base = __shfl_sync(kFull, base, 0);
+        exhausted = base + wanted >= n;
+        if (idle) {
+          const uint32_t mine = base + __popc(idle_mask & lane_lt);
+          float t_best = CUDART_MAX_NORMAL_F;
+          if (mine < n && source.load(mine, ray, t_best)) {
+            item = mine;
+            have_item = true;
+            found = false;
+            hit.t = t_best;
+            hit.prim = -1;
+            sp = 0;
+            idir = v3(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
+            oidir = v3(ray.o.x * idir.x, ray.o.y * idir.y, ray.o.z * idir.z);
+            octinv = octant_inverse(ray.d);
+            group_base = 0;
+            group_hits = root_hits(octinv);
+          }
+        }
+      }
+      // ---- descend --------------------------------------------------------------------
+      while (true) {
+        const bool inner = tri_mask == 0 && (group_hits & 0xffu) != 0;
+        const uint32_t inner_lanes = __ballot_sync(kFull, inner);
+        if (inner_lanes == 0) break;
+        if (__popc(inner_lanes) < kMinDescendLanes && __any_sync(kFull, tri_mask != 0)) break;
+        if (inner) {
+          const uint32_t node = take_child(group_base, group_hits, octinv);
+          if (group_hits & 0xffu) {
+            stack[sp * stride] = make_uint2(group_base, group_hits);
+            sp++;
+          }
+          node_step(scene, node, idir, oidir, hit.t, octinv, group_base, group_hits, tri_base, tri_mask);
+          if (kCount) node_steps++;
+          if ((group_hits & 0xffu) == 0 && tri_mask == 0 && sp > 0) {
+            sp--;
+            const uint2 top = stack[sp * stride];
+            group_base = top.x;
+            group_hits = top.y;
+          }
+        }
+      }
+      // ---- leaves ---------------------------------------------------------------------
+      if (tri_mask != 0) {
+        if (kCount) triangle_tests += __popc(tri_mask);
+#if AMBER_BVH_LEAF_PREFETCH
+        // the triangles of the group are tested one after the other, each behind its own L2 / DRAM round trip (the
+        // kernel's largest stall): ask for all but the first now, so that the round trips overlap
+        for (uint32_t rest = tri_mask & (tri_mask - 1u); rest; rest &= rest - 1u) {
+          const char* next = reinterpret_cast<const char*>(scene.tri_isect + tri_base + (__ffs(rest) - 1));
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(next));
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(next + 32));
+        }
+#endif
+#if AMBER_BVH_LEAF_PAIRS
+        while (tri_mask) {  // two triangles per round: their six loads are in flight together
+          const uint32_t k0 = tri_base + (__ffs(tri_mask) - 1);
+          tri_mask &= tri_mask - 1u;
+          const bool second = tri_mask != 0;
+          const uint32_t k1 = second ? tri_base + (__ffs(tri_mask) - 1) : k0;
+          tri_mask &= tri_mask - 1u;
+          const float4* t0 = reinterpret_cast<const float4*>(scene.tri_isect + k0);
+          const float4* t1 = reinterpret_cast<const float4*>(scene.tri_isect + k1);
+          const float4 a0 = __ldg(t0), a1 = __ldg(t0 + 1), a2 = __ldg(t0 + 2);
+          const float4 b0 = __ldg(t1), b1 = __ldg(t1 + 1), b2 = __ldg(t1 + 2);
+          if (intersect_triangle(a0, a1, a2, ray, hit.t, hit.t)) {
+            hit.prim = static_cast<int32_t>(k0);
+            found = true;
+          }
+          if (second && intersect_triangle(b0, b1, b2, ray, hit.t, hit.t)) {
+            hit.prim = static_cast<int32_t>(k1);
+            found = true;
+          }
+          if (kAnyHit && found) tri_mask = 0;
+        }
+#else
+        while (tri_mask) {
+          const uint32_t k = tri_base + (__ffs(tri_mask) - 1);
+          tri_mask &= tri_mask - 1u;
+          const float4* tri = reinterpret_cast<const float4*>(scene.tri_isect + k);
+          if (intersect_triangle(load_triangle_word(tri), load_triangle_word(tri + 1), load_triangle_word(tri + 2), ray, hit.t, hit.t)) {
+            hit.prim = static_cast<int32_t>(k);
+            found = true;
+            if (kAnyHit) tri_mask = 0;
+          }
+        }
+#endif
+        if (kAnyHit && found) {
+          sp = 0;
+          group_hits = 0;
+        } else if ((group_hits & 0xffu) == 0 && sp > 0) {
+          sp--;
+          const uint2 top = stack[sp * stride];
+          group_base = top.x;
+          group_hits = top.y;
+        }
+      }
+    }
+    if (have_item) source.store(item, hit, found);
+    if (kCount) {
+      node_steps = __reduce_add_sync(kFull, node_steps);
+      triangle_tests = __reduce_add_sync(kFull, triangle_tests);
+      if (lane == 0) {
+        atomicAdd(&counters[0], static_cast<unsigned long long>(node_steps));
+        atomicAdd(&counters[1], static_cast<unsigned long long>(triangle_tests));
+      }
+    }
+  }
+
+  static constexpr bool kPersistent = true;
+};
+
+#endif  // AMBER_BVH_WIDTH
 
 }  // namespace amber_cuda

@@ -22,8 +22,17 @@
 namespace amber_cuda {
 namespace bvh_build {
 
+#ifndef AMBER_BVH_WIDTH
+#define AMBER_BVH_WIDTH 4
+#endif
+constexpr int kWidth = AMBER_BVH_WIDTH;
+static_assert(kWidth == 4 || kWidth == 8, "4-wide 64-byte nodes or 8-wide 96-byte nodes");
 constexpr int kBins = 16;
-constexpr int kLeafMax = 4;
+#ifndef AMBER_BVH_LEAF_MAX
+#define AMBER_BVH_LEAF_MAX (AMBER_BVH_WIDTH == 8 ? 3 : 4)
+#endif
+constexpr int kLeafMax = AMBER_BVH_LEAF_MAX;  // 8-wide: a node's leaf triangles are 24 bits of its hit mask
+static_assert(kLeafMax >= 1 && kLeafMax <= (kWidth == 8 ? 3 : 4), "leaf size the node format can address");
 constexpr int32_t kEmpty = 0x7fffffff;
 
 struct Box {
@@ -80,7 +89,7 @@ struct Builder {
       cbounds.grow(&centroid[3 * order[i]]);
     }
     node.box = bounds;
-    if (count <= 2) {
+    if (count <= static_cast<uint32_t>(std::min(2, kLeafMax))) {
       node.first = first;
       node.count = count;
       return;
@@ -165,10 +174,11 @@ struct Builder {
 };
 
 struct WideBvhHost {
-  std::vector<float> nodes;     // n_nodes * kNodeFloats (4 float4 per node, bvh.cuh)
+  std::vector<float> nodes;     // n_nodes * kNodeFloats (bvh.cuh)
   std::vector<uint32_t> order;  // leaf order -> input triangle index
-  int32_t root = 0;             // 0, or a leaf reference when the whole scene is one leaf
+  int32_t root = 0;             // 4-wide: 0, or a leaf reference when the whole scene is one leaf; 8-wide: always node 0
   uint32_t n_nodes = 0;
+  int depth = 0;                // wide nodes on the longest root-to-leaf chain (sizes the traversal stack)
 };
 
 inline int32_t leaf_ref(int32_t first, int32_t count) { return ~((first << 3) | count); }
@@ -186,42 +196,75 @@ inline void padded(const Box& b, float scene_scale, float* lo, float* hi) {
   }
 }
 
-// One 64-byte node (bvh.cuh): the children's boxes quantised to 8 bits per plane on the grid
-// origin + q * scale of the node's own box; lo rounds down, hi rounds up, checked with the very
-// expression the device decodes with (fmaf(q, scale, origin)), so a decoded box always contains
-// the true one.  lo/hi: [n_kids][3]; unused lanes get ref = kEmpty (and lo > hi).
+// Plane codes.  Code b (8 bits) stands for the grid coordinate g(b) = the float whose bit pattern is
+// 0x3F000000 | b << 16 -- 0.5 + b/256 for b < 128, b/128 from there on (the code's top bit is the exponent's lowest) --
+// and the plane lies at origin + g(b) * scale.  The device builds g(b) with ONE byte permute and feeds it to the FMA
+// that takes the plane into ray space: no integer-to-float conversion, no subtraction of a magic constant.  The grid is
+// uneven (steps of extent/382 in the lower third of the node, extent/191 above), which a box hierarchy does not mind.
+constexpr uint32_t kPlaneMagic = 0x3F000000u;
+inline float plane_coordinate(int code) {
+  const uint32_t bits = kPlaneMagic | (static_cast<uint32_t>(code) << 16);
+  float g;
+  std::memcpy(&g, &bits, 4);
+  return g;
+}
+
+// One axis of up to `width` child boxes: lo codes round down, hi codes round up, checked with the very expression
+// the device decodes with (fmaf(g, scale, origin)), so a decoded box always contains the true one.  Unused slots get
+// lo = 255 > hi = 0: the slab test fails for every ray.
+inline void quantise_axis(const float* lo, const float* hi, const bool* used, int width, float& origin, float& scale,
+                          uint8_t* q_lo, uint8_t* q_hi) {
+  float bottom = FLT_MAX, top = -FLT_MAX;
+  for (int k = 0; k < width; k++) {
+    if (!used[k]) continue;
+    bottom = std::min(bottom, lo[k]);
+    top = std::max(top, hi[k]);
+  }
+  const float span = plane_coordinate(255) - plane_coordinate(0);
+  float s = std::max((top - bottom) / span, 1e-30f);
+  for (bool ok = false; !ok;) {
+    ok = true;
+    const float o = bottom - plane_coordinate(0) * s;
+    auto plane = [&](int code) { return std::fmaf(plane_coordinate(code), s, o); };
+    for (int k = 0; k < width && ok; k++) {
+      int a = 255, b = 0;
+      if (used[k]) {
+        a = 0;
+        for (int step = 128; step > 0; step >>= 1)  // largest code whose plane is <= lo (the planes are monotone)
+          if (a + step <= 255 && plane(a + step) <= lo[k]) a += step;
+        b = 255;
+        for (int step = 128; step > 0; step >>= 1)  // smallest code whose plane is >= hi
+          if (b - step >= 0 && plane(b - step) >= hi[k]) b -= step;
+        if (plane(a) > lo[k] || plane(b) < hi[k]) ok = false;  // rounding left the grid short at an end: widen it
+      }
+      q_lo[k] = static_cast<uint8_t>(a);
+      q_hi[k] = static_cast<uint8_t>(b);
+    }
+    origin = o;
+    scale = s;
+    if (!ok) {
+      s = std::max(std::nextafter(s, FLT_MAX), s * 1.0001f);
+      bottom -= 1e-6f * std::max(1.0f, std::fabs(bottom));
+    }
+  }
+}
+
+// One 64-byte node (bvh.cuh): four children.  lo/hi: [n_kids][3]; unused lanes get ref = kEmpty.
 inline void encode_node(const float (*lo)[3], const float (*hi)[3], const int32_t* refs, int n_kids, float* out16) {
   uint32_t words[6] = {0, 0, 0, 0, 0, 0};  // x lo, x hi, y lo, y hi, z lo, z hi; byte k = child k
   float origin[3], scale[3];
   for (int a = 0; a < 3; a++) {
-    float o = FLT_MAX, top = -FLT_MAX;
-    for (int k = 0; k < n_kids; k++) {
-      o = std::min(o, lo[k][a]);
-      top = std::max(top, hi[k][a]);
+    float axis_lo[4], axis_hi[4];
+    bool used[4];
+    uint8_t q_lo[4], q_hi[4];
+    for (int k = 0; k < 4; k++) {
+      used[k] = k < n_kids;
+      axis_lo[k] = used[k] ? lo[k][a] : 0.0f;
+      axis_hi[k] = used[k] ? hi[k][a] : 0.0f;
     }
-    float s = std::max((top - o) / 255.0f, 1e-30f);
-    uint32_t w_lo = 0, w_hi = 0;
-    for (bool ok = false; !ok;) {
-      ok = true;
-      w_lo = w_hi = 0;
-      for (int k = 0; k < 4 && ok; k++) {
-        int q_lo = 255, q_hi = 0;  // unused lane: empty interval
-        if (k < n_kids) {
-          q_lo = std::min(255, std::max(0, static_cast<int>(std::floor((lo[k][a] - o) / s))));
-          while (q_lo > 0 && std::fmaf(static_cast<float>(q_lo), s, o) > lo[k][a]) q_lo--;
-          q_hi = std::min(255, std::max(0, static_cast<int>(std::ceil((hi[k][a] - o) / s))));
-          while (q_hi < 255 && std::fmaf(static_cast<float>(q_hi), s, o) < hi[k][a]) q_hi++;
-          if (std::fmaf(static_cast<float>(q_hi), s, o) < hi[k][a]) ok = false;  // grid too short: widen it
-        }
-        w_lo |= static_cast<uint32_t>(q_lo) << (8 * k);
-        w_hi |= static_cast<uint32_t>(q_hi) << (8 * k);
-      }
-      if (!ok) s = std::max(std::nextafter(s, FLT_MAX), s * 1.0001f);
-    }
-    origin[a] = o;
-    scale[a] = s;
-    words[2 * a] = w_lo;
-    words[2 * a + 1] = w_hi;
+    quantise_axis(axis_lo, axis_hi, used, 4, origin[a], scale[a], q_lo, q_hi);
+    std::memcpy(&words[2 * a], q_lo, 4);
+    std::memcpy(&words[2 * a + 1], q_hi, 4);
   }
   out16[0] = origin[0]; out16[1] = origin[1]; out16[2] = origin[2];
   out16[3] = scale[0]; out16[4] = scale[1]; out16[5] = scale[2];
@@ -232,7 +275,133 @@ inline void encode_node(const float (*lo)[3], const float (*hi)[3], const int32_
   }
 }
 
-constexpr int kNodeFloats = 16;  // 64 B
+constexpr int kNodeFloats = kWidth == 8 ? 24 : 16;  // 96 B / 64 B
+
+// ---- 8-wide nodes (layout and traversal: bvh.cuh) ----------------------------------------------------------
+// Collapse 2 -> 8.  Children sit in the slot whose sign pattern (bit a set: towards +axis a) best matches the
+// direction from the node's centre to theirs, so that `slot ^ (7 ^ ray octant)` orders them front to back without
+// any distance sort (Ylitie, Karras, Laine 2017).  A node's inner children are consecutive nodes (child_base + rank
+// among the inner slots) and the triangles of its leaf children are consecutive in the triangle order (tri_base +
+// 5-bit offset), which is what lets one node address eight children in 16 bytes.
+inline WideBvhHost build8(const Builder& b, int32_t root) {
+  WideBvhHost out;
+  const std::vector<Node2>& n2 = b.nodes;
+  float scene_scale = 1.0f;
+  for (int a = 0; a < 3; a++)
+    scene_scale = std::max(scene_scale, std::max(std::fabs(n2[root].box.lo[a]), std::fabs(n2[root].box.hi[a])));
+  struct Pending {
+    int32_t node2;
+    int32_t wide;
+    int depth;
+  };
+  std::vector<Pending> queue;
+  queue.push_back({root, 0, 1});
+  out.n_nodes = 1;
+  out.order.reserve(b.order.size());
+  out.nodes.resize(kNodeFloats);
+  for (size_t head = 0; head < queue.size(); head++) {
+    const Pending item = queue[head];
+    out.depth = std::max(out.depth, item.depth);
+    int32_t kids[8];
+    int n_kids;
+    if (n2[item.node2].count > 0) {  // the whole scene is one leaf: a root with one child
+      kids[0] = item.node2;
+      n_kids = 1;
+    } else {
+      kids[0] = n2[item.node2].left;
+      kids[1] = n2[item.node2].right;
+      n_kids = 2;
+      while (n_kids < 8) {  // always open the inner child with the largest surface area
+        int best = -1;
+        float best_area = -1.0f;
+        for (int k = 0; k < n_kids; k++) {
+          if (n2[kids[k]].count > 0) continue;
+          const float a = n2[kids[k]].box.area();
+          if (a > best_area) {
+            best_area = a;
+            best = k;
+          }
+        }
+        if (best < 0) break;
+        const int32_t open = kids[best];
+        kids[best] = n2[open].left;
+        kids[n_kids++] = n2[open].right;
+      }
+    }
+    // slots: greedy assignment by the largest projection of (child centre - node centre) on the slot's diagonal
+    const Box& parent = n2[item.node2].box;
+    int slot_kid[8];
+    for (int s = 0; s < 8; s++) slot_kid[s] = -1;
+    bool placed[8] = {false};
+    for (int round = 0; round < n_kids; round++) {
+      float best = -FLT_MAX;
+      int best_k = -1, best_s = -1;
+      for (int k = 0; k < n_kids; k++) {
+        if (placed[k]) continue;
+        const Box& cb = n2[kids[k]].box;
+        for (int s = 0; s < 8; s++) {
+          if (slot_kid[s] >= 0) continue;
+          float score = 0.0f;
+          for (int a = 0; a < 3; a++) {
+            const float d = 0.5f * (cb.lo[a] + cb.hi[a]) - 0.5f * (parent.lo[a] + parent.hi[a]);
+            score += ((s >> a) & 1) ? d : -d;
+          }
+          if (score > best) {
+            best = score;
+            best_k = k;
+            best_s = s;
+          }
+        }
+      }
+      placed[best_k] = true;
+      slot_kid[best_s] = kids[best_k];
+    }
+    float lo[3][8], hi[3][8];
+    bool used[8];
+    uint8_t meta[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t imask = 0;
+    const uint32_t child_base = out.n_nodes, tri_base = static_cast<uint32_t>(out.order.size());
+    for (int s = 0; s < 8; s++) {
+      used[s] = slot_kid[s] >= 0;
+      if (!used[s]) continue;
+      const Node2& child = n2[slot_kid[s]];
+      float plo[3], phi[3];
+      padded(child.box, scene_scale, plo, phi);
+      for (int a = 0; a < 3; a++) {
+        lo[a][s] = plo[a];
+        hi[a][s] = phi[a];
+      }
+      if (child.count > 0) {  // leaf: `count` one-bits above the 5-bit offset of its first triangle
+        const uint32_t offset = static_cast<uint32_t>(out.order.size()) - tri_base;
+        meta[s] = static_cast<uint8_t>((((1u << child.count) - 1u) << 5) | offset);
+        for (int32_t t = 0; t < child.count; t++) out.order.push_back(b.order[child.first + t]);
+      } else {                // inner: one bit at index 24 + slot
+        imask |= 1u << s;
+        meta[s] = static_cast<uint8_t>((1u << 5) | (24u + s));
+        queue.push_back({slot_kid[s], static_cast<int32_t>(out.n_nodes++), item.depth + 1});
+      }
+    }
+    if (out.nodes.size() < static_cast<size_t>(out.n_nodes) * kNodeFloats)
+      out.nodes.resize(std::max(out.nodes.size() * 2, static_cast<size_t>(out.n_nodes) * kNodeFloats));
+    float* node = &out.nodes[static_cast<size_t>(item.wide) * 24];
+    uint32_t words[24];
+    uint8_t q[6][8];  // x lo, x hi, y lo, y hi, z lo, z hi
+    float origin[3], scale[3];
+    for (int a = 0; a < 3; a++) quantise_axis(lo[a], hi[a], used, 8, origin[a], scale[a], q[2 * a], q[2 * a + 1]);
+    std::memcpy(&words[0], origin, 12);
+    std::memcpy(&words[3], scale, 12);
+    words[6] = child_base;
+    words[7] = tri_base;
+    std::memcpy(&words[8], meta, 8);
+    words[10] = imask;
+    words[11] = kPlaneMagic;  // read by the device as the second operand of its byte permutes (bvh.cuh, plane_float)
+    for (int plane = 0; plane < 6; plane++) std::memcpy(&words[12 + 2 * plane], q[plane], 8);
+    std::memcpy(node, words, sizeof words);
+  }
+  out.nodes.resize(static_cast<size_t>(out.n_nodes) * kNodeFloats);
+  out.root = 0;
+  return out;
+}
 
 inline WideBvhHost build(const float* verts9, uint32_t n) {
   WideBvhHost out;
@@ -257,6 +426,19 @@ inline WideBvhHost build(const float* verts9, uint32_t n) {
   const int32_t root = b.alloc_node();
   b.build_range(root, 0, n, 0);
 
+  if (kWidth == 8) {
+    if (n == 0) {  // a dummy node whose slots are all empty keeps the device pointer valid
+      out.nodes.assign(kNodeFloats, 0.0f);
+      uint32_t empty_planes[12];
+      for (int plane = 0; plane < 6; plane++) empty_planes[2 * plane] = empty_planes[2 * plane + 1] = (plane & 1) ? 0u : 0xffffffffu;
+      std::memcpy(&out.nodes[12], empty_planes, sizeof empty_planes);
+      std::memcpy(&out.nodes[11], &kPlaneMagic, 4);
+      out.n_nodes = 1;
+      out.depth = 1;
+      return out;
+    }
+    return build8(b, root);
+  }
   out.order = b.order;
   const std::vector<Node2>& n2 = b.nodes;
   if (n2[root].count > 0 || n == 0) {

@@ -140,6 +140,7 @@ struct ConstScene {
   int32_t n_tris, n_spheres, n_groups;
   int32_t n_axis_entries[3];  // unclustered entries perpendicular to x, y, z: axis_entry[] holds them in that order
   int32_t n_clusters;         // clustered entries follow in axis_entry[]
+  uint32_t bvh_plane_magic;   // 0x3F000000, read by the 4-wide BVH decode so that it sits in a register (bvh.cuh, plane_float)
   int32_t pad;
   AxisCluster cluster[kMaxAxisClusters];
   AxisEntry axis_entry[kMaxConstTris];

@@ -86,10 +86,12 @@ def test_render_rejects_a_foreign_scene():
         CudaPathTracing().render(object(), Sensor(8, 8), Context(1, 1))
 
 
-def test_bvh_builder_invariants(tmp_path):
+@pytest.mark.parametrize("width", [4, 8])
+def test_bvh_builder_invariants(tmp_path, width):
+    """Both node formats (bvh.cuh): 4-wide 64-byte nodes and 8-wide 96-byte nodes."""
     exe = tmp_path / "bvh_check"
-    subprocess.check_call(["g++", "-std=c++17", "-O2", "-pthread", os.path.join(ROOT, "tests", "cpp", "bvh_check.cc"),
-                           "-o", str(exe)])
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-pthread", f"-DAMBER_BVH_WIDTH={width}",
+                           os.path.join(ROOT, "tests", "cpp", "bvh_check.cc"), "-o", str(exe)])
     out = subprocess.run([str(exe), "200000"], capture_output=True, text=True)
     assert out.returncode == 0, out.stdout + out.stderr
     assert out.stdout.count("ok") == 3
