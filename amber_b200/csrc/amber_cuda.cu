@@ -1118,6 +1118,22 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, const amber_cuda_re
       cudaEventElapsedTime(&ms, timer.events[2 * k], timer.events[2 * k + 1]);
       ms_by_kind[timer.kinds[k]] += ms;
     }
+    if (trace_on()) {  // AMBER_CUDA_TRACE + profiling: the last iterations kernel by kernel (the drain tail of a render)
+      const size_t per_iteration = nee ? 4 : 3;
+      const size_t iterations = timer.kinds.size() / per_iteration, from = iterations > 48 ? iterations - 48 : 0;
+      for (size_t it = from; it < iterations; it++) {
+        float us[4] = {0, 0, 0, 0};
+        for (size_t k = it * per_iteration; k < (it + 1) * per_iteration; k++) {
+          float ms = 0;
+          cudaEventElapsedTime(&ms, timer.events[2 * k], timer.events[2 * k + 1]);
+          us[timer.kinds[k]] = 1e3f * ms;
+        }
+        float whole = 0;
+        if (it + 1 < iterations) cudaEventElapsedTime(&whole, timer.events[2 * it * per_iteration], timer.events[2 * (it + 1) * per_iteration]);
+        trace(ctx, "iteration %zu: raygen %.1f extend %.1f shade %.1f connect %.1f us, start to next start %.1f us", it, us[0], us[1],
+              us[2], us[3], 1e3f * whole);
+      }
+    }
   }
   ctx->stats.raygen_ms = ms_by_kind[0];
   ctx->stats.extend_ms = ms_by_kind[1];
