@@ -944,6 +944,7 @@ __global__ void control_begin_kernel(Control* ctl, unsigned long long total_path
   ctl->n_shadow = 0;
   ctl->n_alive = 0;
   ctl->done = 0;
+  ctl->raygen_blocks_done = 0;
   for (int k = 0; k < 4; k++) ctl->bvh_work[k] = 0;
 }
 
@@ -1058,7 +1059,9 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, const amber_cuda_re
         if (light_tracing) raygen_kernel<true><<<raygen_grid, kBlock, 0, stream>>>(args);
         else raygen_kernel<false><<<raygen_grid, kBlock, 0, stream>>>(args);
       });
+#if !AMBER_FUSE_BOOKKEEP
       bookkeep_kernel<<<1, 1, 0, stream>>>(args.ctl);
+#endif
       timed(1, [&] {
         if (AMBER_FUSE_EXTEND && !Accel::kPersistent) return;  // experiment: raygen and shade found the hits
         if (profile && Accel::kPersistent) launch_extend_counting(args, trace_grid, dynamic_smem, stream);
@@ -1072,7 +1075,7 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, const amber_cuda_re
         if (profile && Accel::kPersistent) launch_connect_counting(args, connect_grid, dynamic_smem, stream);
         else connect_kernel<Accel><<<connect_grid, kBlock, dynamic_smem, stream>>>(args);
       });
-      ctx->stats.kernel_launches += nee ? 5 : 4;
+      ctx->stats.kernel_launches += (nee ? 4 : 3) + (AMBER_FUSE_BOOKKEEP ? 0 : 1);
       extend_launches++;
     }
     // poll: the copy of batch b is read while batch b+1 is already queued

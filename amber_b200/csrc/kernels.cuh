@@ -51,6 +51,7 @@ struct Control {
   unsigned long long base_sample;  // next_path / n_pixels
   unsigned int n_pixels;
   unsigned int n_marked;  // free-list entries [0, n_marked) are known to hold no ray (ray.w == 0)
+  unsigned int raygen_blocks_done;  // blocks of the running raygen launch that have finished (the last one does the bookkeeping)
   unsigned long long cursor_bdpt;  // bdpt_kernel: next (pixel, sample) pair index
   // profiling mode: traversal work of the BVH kernels: extend node steps, extend triangle tests, connect
   // node steps, connect triangle tests
@@ -276,6 +277,32 @@ constexpr int kQueueBlocks = AMBER_QUEUE_BLOCKS;  // resident blocks per SM of t
 #ifndef AMBER_RAYGEN_LOOP
 #define AMBER_RAYGEN_LOOP 1
 #endif
+#ifndef AMBER_FUSE_BOOKKEEP
+#define AMBER_FUSE_BOOKKEEP 1
+#endif
+// Between raygen and extend: advances the render's counters by what raygen has just started and resets the per-iteration
+// queues.  Run by the LAST block of raygen to finish (AMBER_FUSE_BOOKKEEP, the default) instead of a launch of its own.
+__device__ __forceinline__ void bookkeep(Control* ctl) {
+  unsigned long long generated = 0;
+  if (ctl->next_path < ctl->total_paths) {
+    const unsigned long long left = ctl->total_paths - ctl->next_path;
+    generated = ctl->n_new < left ? ctl->n_new : left;
+  }
+  ctl->next_path += generated;
+  ctl->base_pixel = static_cast<unsigned int>(ctl->next_path % ctl->n_pixels);
+  ctl->base_sample = ctl->next_path / ctl->n_pixels;
+  ctl->paths += generated;
+  ctl->shadow_rays += ctl->n_shadow;
+  // finished: every path of the render has been started and none is alive (n_alive: survivors of the last shade)
+  ctl->done = (generated == 0 && ctl->next_path >= ctl->total_paths && ctl->n_alive == 0) ? 1u : 0u;
+  ctl->n_new -= static_cast<unsigned int>(generated);  // the free list keeps what raygen did not use ...
+  ctl->n_marked = ctl->n_new;                           // ... and raygen has marked all of that empty
+  ctl->n_shadow = 0;
+  ctl->n_alive = 0;
+  ctl->cursor_extend = 0;
+  ctl->cursor_connect = 0;
+}
+
 // Experiment: with the constant-memory list the closest hit of a path's NEXT ray is found by the
 // kernel that makes the ray (raygen, shade) and `extend` is not launched.  Off: see DESIGN.md section 4.4.
 #ifndef AMBER_FUSE_EXTEND
@@ -352,6 +379,18 @@ __global__ void __launch_bounds__(kBlock, AMBER_RAYGEN_BLOCKS) raygen_kernel(con
   // (after the main loop: in front of it the main loop's loads of the control block are ordered behind these stores)
   for (uint32_t j = n_marked + blockIdx.x * kBlock + threadIdx.x; j < first_entry; j += gridDim.x * kBlock)
     args.pool.ray[2 * static_cast<size_t>(args.pool.q_new[j])] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#if AMBER_FUSE_BOOKKEEP
+  // The last block to arrive here advances the counters: by then every block has used the values it read above.
+  // (One launch per iteration less: a one-thread kernel costs its ~2.6 us plus the gaps either side of it.)
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&args.ctl->raygen_blocks_done, 1u) == gridDim.x - 1) {
+      args.ctl->raygen_blocks_done = 0;
+      bookkeep(args.ctl);
+    }
+  }
+#endif
 }
 
 // Fills q_new with every slot (start of a render call: all slots are free).
@@ -365,26 +404,9 @@ __global__ void __launch_bounds__(kBlock) pool_reset_kernel(const RenderArgs arg
 #endif
 }
 
-__global__ void bookkeep_kernel(Control* ctl) {
-  unsigned long long generated = 0;
-  if (ctl->next_path < ctl->total_paths) {
-    const unsigned long long left = ctl->total_paths - ctl->next_path;
-    generated = ctl->n_new < left ? ctl->n_new : left;
-  }
-  ctl->next_path += generated;
-  ctl->base_pixel = static_cast<unsigned int>(ctl->next_path % ctl->n_pixels);
-  ctl->base_sample = ctl->next_path / ctl->n_pixels;
-  ctl->paths += generated;
-  ctl->shadow_rays += ctl->n_shadow;
-  // finished: every path of the render has been started and none is alive (n_alive: survivors of the last shade)
-  ctl->done = (generated == 0 && ctl->next_path >= ctl->total_paths && ctl->n_alive == 0) ? 1u : 0u;
-  ctl->n_new -= static_cast<unsigned int>(generated);  // the free list keeps what raygen did not use ...
-  ctl->n_marked = ctl->n_new;                           // ... and raygen has marked all of that empty
-  ctl->n_shadow = 0;
-  ctl->n_alive = 0;
-  ctl->cursor_extend = 0;
-  ctl->cursor_connect = 0;
-}
+#if !AMBER_FUSE_BOOKKEEP
+__global__ void bookkeep_kernel(Control* ctl) { bookkeep(ctl); }
+#endif
 
 // ---------------------------------------------------------------------------------
 // Every thread reaches Accel::closest (the BVH walk votes across the warp); threads without a
