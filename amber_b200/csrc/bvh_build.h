@@ -79,14 +79,66 @@ struct Builder {
 
   int32_t alloc_node() { return node_count.fetch_add(1); }
 
+  // Ranges of at least kParallelRange triangles are scanned by several threads (bounds, bins); subtrees are built on
+  // their own threads down to kSpawnDepth.  Boxes and counts merge exactly, so the tree does not depend on the
+  // number of threads.
+  static constexpr uint32_t kParallelRange = 1u << 17;
+  static constexpr int kSpawnDepth = 5, kMaxChunks = 32;
+  int workers = 1;  // hardware threads to use (build() sets it), at most kMaxChunks
+
+  struct Bins {
+    Box box[3][kBins];
+    uint32_t count[3][kBins];
+    void reset() {
+      for (int a = 0; a < 3; a++)
+        for (int b = 0; b < kBins; b++) {
+          box[a][b].reset();
+          count[a][b] = 0;
+        }
+    }
+  };
+
+  // f(chunk, begin, end) over [first, first + count) cut into chunks; returns the number of chunks
+  template <class F>
+  int for_chunks(uint32_t first, uint32_t count, int depth, F&& f) {
+    const int chunks = count >= kParallelRange ? std::max(1, std::min(kMaxChunks, workers >> std::min(depth, 30))) : 1;
+    if (chunks == 1) {
+      f(0, first, first + count);
+      return 1;
+    }
+    const uint32_t per = (count + chunks - 1) / chunks;
+    std::vector<std::thread> pool;
+    for (int c = 1; c < chunks; c++)
+      pool.emplace_back([&f, c, first, count, per]() {
+        f(c, std::min(first + count, first + c * per), std::min(first + count, first + (c + 1) * per));
+      });
+    f(0, first, std::min(first + count, first + per));
+    for (auto& t : pool) t.join();
+    return chunks;
+  }
+
   void build_range(int32_t node_index, uint32_t first, uint32_t count, int depth) {
     Node2& node = nodes[node_index];
     Box bounds, cbounds;
-    bounds.reset();
-    cbounds.reset();
-    for (uint32_t i = first; i < first + count; i++) {
-      bounds.grow(tri_box[order[i]]);
-      cbounds.grow(&centroid[3 * order[i]]);
+    {
+      Box part_bounds[kMaxChunks], part_cbounds[kMaxChunks];
+      const int chunks = for_chunks(first, count, depth, [&](int c, uint32_t begin, uint32_t end) {
+        Box b, cb;
+        b.reset();
+        cb.reset();
+        for (uint32_t i = begin; i < end; i++) {
+          b.grow(tri_box[order[i]]);
+          cb.grow(&centroid[3 * static_cast<size_t>(order[i])]);
+        }
+        part_bounds[c] = b;
+        part_cbounds[c] = cb;
+      });
+      bounds = part_bounds[0];
+      cbounds = part_cbounds[0];
+      for (int c = 1; c < chunks; c++) {
+        bounds.grow(part_bounds[c]);
+        cbounds.grow(part_cbounds[c]);
+      }
     }
     node.box = bounds;
     if (count <= static_cast<uint32_t>(std::min(2, kLeafMax))) {
@@ -94,24 +146,45 @@ struct Builder {
       node.count = count;
       return;
     }
-    // binned SAH over the centroid bounds
+    // binned SAH over the centroid bounds: the three axes are binned in one pass over the range
+    float bin_scale[3];
+    for (int axis = 0; axis < 3; axis++) {
+      const float extent = cbounds.hi[axis] - cbounds.lo[axis];
+      bin_scale[axis] = extent > 0 ? kBins / extent : 0.0f;
+    }
+    std::vector<Bins> part(1);
+    {
+      const int want = count >= kParallelRange ? std::max(1, std::min(kMaxChunks, workers >> std::min(depth, 30))) : 1;
+      part.resize(want);
+      for_chunks(first, count, depth, [&](int c, uint32_t begin, uint32_t end) {
+        Bins& bins = part[c];
+        bins.reset();
+        for (uint32_t i = begin; i < end; i++) {
+          const uint32_t t = order[i];
+          const Box& tb = tri_box[t];
+          for (int axis = 0; axis < 3; axis++) {
+            int b = static_cast<int>((centroid[3 * static_cast<size_t>(t) + axis] - cbounds.lo[axis]) * bin_scale[axis]);
+            b = std::min(kBins - 1, std::max(0, b));
+            bins.count[axis][b]++;
+            bins.box[axis][b].grow(tb);
+          }
+        }
+      });
+      for (size_t c = 1; c < part.size(); c++)
+        for (int axis = 0; axis < 3; axis++)
+          for (int b = 0; b < kBins; b++) {
+            part[0].count[axis][b] += part[c].count[axis][b];
+            part[0].box[axis][b].grow(part[c].box[axis][b]);
+          }
+    }
     float best_cost = FLT_MAX;
     int best_axis = -1, best_bin = -1;
     const float parent_area = std::max(bounds.area(), 1e-30f);
     for (int axis = 0; axis < 3; axis++) {
       const float extent = cbounds.hi[axis] - cbounds.lo[axis];
       if (!(extent > 0)) continue;
-      Box bin_box[kBins];
-      uint32_t bin_count[kBins] = {0};
-      for (auto& b : bin_box) b.reset();
-      const float scale = kBins / extent;
-      for (uint32_t i = first; i < first + count; i++) {
-        const uint32_t t = order[i];
-        int b = static_cast<int>((centroid[3 * t + axis] - cbounds.lo[axis]) * scale);
-        b = std::min(kBins - 1, std::max(0, b));
-        bin_count[b]++;
-        bin_box[b].grow(tri_box[t]);
-      }
+      const Box* bin_box = part[0].box[axis];
+      const uint32_t* bin_count = part[0].count[axis];
       float right_area[kBins];
       uint32_t right_count[kBins];
       Box acc;
@@ -147,8 +220,7 @@ struct Builder {
       // no useful SAH split (coincident centroids): split the range in half
       mid = first + count / 2;
     } else {
-      const float extent = cbounds.hi[best_axis] - cbounds.lo[best_axis];
-      const float scale = kBins / extent;
+      const float scale = bin_scale[best_axis];
       const float lo = cbounds.lo[best_axis];
       auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](uint32_t t) {
         int b = static_cast<int>((centroid[3 * t + best_axis] - lo) * scale);
@@ -162,7 +234,7 @@ struct Builder {
     nodes[node_index].left = left;
     nodes[node_index].right = right;
     const uint32_t n_left = mid - first, n_right = first + count - mid;
-    if (depth < 3 && count > (1u << 16)) {
+    if (depth < kSpawnDepth && count > (1u << 15) && workers > 1) {
       std::thread worker([&, left, first, n_left, depth]() { build_range(left, first, n_left, depth + 1); });
       build_range(right, mid, n_right, depth + 1);
       worker.join();
@@ -202,6 +274,18 @@ inline void padded(const Box& b, float scene_scale, float* lo, float* hi) {
 // that takes the plane into ray space: no integer-to-float conversion, no subtraction of a magic constant.  The grid is
 // uneven (steps of extent/382 in the lower third of the node, extent/191 above), which a box hierarchy does not mind.
 constexpr uint32_t kPlaneMagic = 0x3F000000u;
+
+// fmaf as ONE hardware instruction where the CPU has it: without -mfma std::fmaf is a library call that emulates the
+// single rounding in software (~100 ns), and the plane search below makes ~200 of them per node.
+#if defined(__x86_64__) && defined(__GNUC__)
+__attribute__((target("fma"))) inline float fmaf_hardware(float a, float b, float c) { return __builtin_fmaf(a, b, c); }
+inline float fused_multiply_add(float a, float b, float c) {
+  static const bool hardware = __builtin_cpu_supports("fma");
+  return hardware ? fmaf_hardware(a, b, c) : std::fmaf(a, b, c);
+}
+#else
+inline float fused_multiply_add(float a, float b, float c) { return std::fmaf(a, b, c); }
+#endif
 inline float plane_coordinate(int code) {
   const uint32_t bits = kPlaneMagic | (static_cast<uint32_t>(code) << 16);
   float g;
@@ -221,11 +305,14 @@ inline void quantise_axis(const float* lo, const float* hi, const bool* used, in
     top = std::max(top, hi[k]);
   }
   const float span = plane_coordinate(255) - plane_coordinate(0);
-  float s = std::max((top - bottom) / span, 1e-30f);
+  // The grid spans [bottom - margin, top + margin]; rounding in o, s or the decode can leave it short at an end by an
+  // ulp or two of the coordinates, so the margin starts at zero and doubles from one ulp until every box is covered.
+  float margin = 0.0f;
   for (bool ok = false; !ok;) {
     ok = true;
-    const float o = bottom - plane_coordinate(0) * s;
-    auto plane = [&](int code) { return std::fmaf(plane_coordinate(code), s, o); };
+    const float s = std::max(((top + margin) - (bottom - margin)) / span, 1e-30f);
+    const float o = (bottom - margin) - plane_coordinate(0) * s;
+    auto plane = [&](int code) { return fused_multiply_add(plane_coordinate(code), s, o); };
     for (int k = 0; k < width && ok; k++) {
       int a = 255, b = 0;
       if (used[k]) {
@@ -235,17 +322,14 @@ inline void quantise_axis(const float* lo, const float* hi, const bool* used, in
         b = 255;
         for (int step = 128; step > 0; step >>= 1)  // smallest code whose plane is >= hi
           if (b - step >= 0 && plane(b - step) >= hi[k]) b -= step;
-        if (plane(a) > lo[k] || plane(b) < hi[k]) ok = false;  // rounding left the grid short at an end: widen it
+        if (plane(a) > lo[k] || plane(b) < hi[k]) ok = false;
       }
       q_lo[k] = static_cast<uint8_t>(a);
       q_hi[k] = static_cast<uint8_t>(b);
     }
     origin = o;
     scale = s;
-    if (!ok) {
-      s = std::max(std::nextafter(s, FLT_MAX), s * 1.0001f);
-      bottom -= 1e-6f * std::max(1.0f, std::fabs(bottom));
-    }
+    if (!ok) margin = std::max(2.0f * margin, 1.2e-7f * std::max(std::max(std::fabs(bottom), std::fabs(top)), 1e-30f));
   }
 }
 
@@ -423,6 +507,7 @@ inline WideBvhHost build(const float* verts9, uint32_t n) {
     b.order[i] = i;
   }
   b.nodes.resize(std::max<size_t>(1, 2 * static_cast<size_t>(n)));
+  b.workers = static_cast<int>(std::max(1u, std::min<unsigned>(Builder::kMaxChunks, std::thread::hardware_concurrency())));
   const int32_t root = b.alloc_node();
   b.build_range(root, 0, n, 0);
 
@@ -457,10 +542,14 @@ inline WideBvhHost build(const float* verts9, uint32_t n) {
     int32_t node2;
     int32_t wide;
   };
+  struct Wide4 {
+    int32_t kids[4], refs[4];
+    int n_kids;
+  };
   std::vector<Pending> queue;
+  std::vector<Wide4> plan;  // first the shape of the wide tree, serially (node indices are handed out in queue order) ...
   queue.push_back({root, 0});
   out.n_nodes = 1;
-  out.nodes.resize(kNodeFloats);
   for (size_t head = 0; head < queue.size(); head++) {
     const Pending item = queue[head];
     int32_t kids[4];
@@ -483,23 +572,36 @@ inline WideBvhHost build(const float* verts9, uint32_t n) {
       kids[best] = n2[open].left;
       kids[n_kids++] = n2[open].right;
     }
-    float lo[4][3], hi[4][3];
-    int32_t refs[4];
+    Wide4 wide;
+    wide.n_kids = n_kids;
     for (int k = 0; k < n_kids; k++) {
       const Node2& child = n2[kids[k]];
-      padded(child.box, scene_scale, lo[k], hi[k]);
+      wide.kids[k] = kids[k];
       if (child.count > 0) {
-        refs[k] = leaf_ref(child.first, child.count);
+        wide.refs[k] = leaf_ref(child.first, child.count);
       } else {
-        refs[k] = static_cast<int32_t>(out.n_nodes++);
-        queue.push_back({kids[k], refs[k]});
+        wide.refs[k] = static_cast<int32_t>(out.n_nodes++);
+        queue.push_back({kids[k], wide.refs[k]});
       }
     }
-    if (out.nodes.size() < static_cast<size_t>(out.n_nodes) * kNodeFloats)
-      out.nodes.resize(std::max(out.nodes.size() * 2, static_cast<size_t>(out.n_nodes) * kNodeFloats));
-    encode_node(lo, hi, refs, n_kids, &out.nodes[static_cast<size_t>(item.wide) * kNodeFloats]);
+    plan.push_back(wide);  // plan[item.wide]: the queue is in node order
   }
+  // ... then the nodes are encoded (the plane search of quantise_axis is most of this phase), independently of each other
   out.nodes.resize(static_cast<size_t>(out.n_nodes) * kNodeFloats);
+  const unsigned threads = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+  auto encode_range = [&](size_t begin, size_t end) {
+    for (size_t w = begin; w < end; w++) {
+      float lo[4][3], hi[4][3];
+      for (int k = 0; k < plan[w].n_kids; k++) padded(n2[plan[w].kids[k]].box, scene_scale, lo[k], hi[k]);
+      encode_node(lo, hi, plan[w].refs, plan[w].n_kids, &out.nodes[w * kNodeFloats]);
+    }
+  };
+  std::vector<std::thread> pool;
+  const size_t per = (plan.size() + threads - 1) / threads;
+  for (unsigned t = 1; t < threads && plan.size() > 4096; t++)
+    pool.emplace_back(encode_range, std::min(plan.size(), t * per), std::min(plan.size(), (t + 1) * per));
+  encode_range(0, pool.empty() ? plan.size() : std::min(plan.size(), per));
+  for (auto& t : pool) t.join();
   return out;
 }
 
