@@ -114,6 +114,10 @@ struct amber_cuda_ctx {
   DeviceBuffer<float4> d_ray, d_state, d_shadow;
   DeviceBuffer<float2> d_hit;
   DeviceBuffer<uint32_t> d_q_new, d_q_shadow;
+  // wavefront BDPT (bdpt.cuh, BdptPool): allocated by the first such render
+  DeviceBuffer<float4> d_bdpt_state;
+  DeviceBuffer<BdptEvent> d_bdpt_events;
+  DeviceBuffer<uint32_t> d_bdpt_queue;
   DeviceBuffer<Control> d_ctl;
   Control* h_ctl = nullptr;  // pinned
 
@@ -635,6 +639,7 @@ int amber_cuda_destroy(amber_cuda_ctx* ctx) {
   ctx->d_materials.release(); ctx->d_lights.release(); ctx->d_bvh_nodes.release();
   ctx->d_film.release(); ctx->d_resolved.release(); ctx->d_resolved8.release();
   ctx->d_ray.release(); ctx->d_state.release(); ctx->d_hit.release(); ctx->d_shadow.release();
+  ctx->d_bdpt_state.release(); ctx->d_bdpt_events.release(); ctx->d_bdpt_queue.release();
   ctx->d_q_new.release(); ctx->d_q_shadow.release(); ctx->d_ctl.release(); ctx->d_prim_class.release();
   for (auto& b : ctx->d_scratch_f) b.release();
   for (auto& b : ctx->d_scratch_i) b.release();
@@ -1146,6 +1151,71 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, const amber_cuda_re
   return AMBER_CUDA_OK;
 }
 
+// Bidirectional path tracing as a wavefront (bdpt.cuh, second half): a pool of pixel samples in flight, one subpath step
+// per item per iteration, connections from a queue.
+// Pool: 2 M items = 5.4 GB of events + 200 MB of state (512 k / 1 M / 2 M / 4 M items: 601 / 682 / 726 / 739 M pixel samples/s
+// on the Cornell box at 64 spp).  AMBER_CUDA_BDPT_POOL overrides it (experiments).
+constexpr uint32_t kBdptPoolItems = 1u << 21;
+uint32_t bdpt_pool_items() {
+  const char* text = std::getenv("AMBER_CUDA_BDPT_POOL");
+  const long long wanted = text ? std::atoll(text) : 0;
+  return wanted >= 1024 && wanted <= (1ll << 24) ? static_cast<uint32_t>(wanted) : kBdptPoolItems;
+}
+// Which implementation: the wavefront on the constant-memory list (726 against 470 M pixel samples/s), the one-kernel
+// version on the BVH, where a per-thread walk of the tree inside a lock-step launch waits for its slowest lane every
+// iteration (110 against 131 M/s).  AMBER_CUDA_BDPT=wavefront|megakernel forces one (tests compare the two).
+bool bdpt_wavefront_selected(bool use_bvh) {
+  const char* choice = std::getenv("AMBER_CUDA_BDPT");
+  if (choice && std::strcmp(choice, "megakernel") == 0) return false;
+  if (choice && std::strcmp(choice, "wavefront") == 0) return true;
+  return !use_bvh;
+}
+template <class Accel>
+int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, const RenderArgs& args,
+                          uint64_t total_pairs, int cap) {
+  const uint64_t wanted = std::min<uint64_t>(bdpt_pool_items(), total_pairs);
+  const uint32_t n_items = static_cast<uint32_t>((wanted + kBdptGrowBlock - 1) / kBdptGrowBlock * kBdptGrowBlock);
+  CUDA_TRY(ctx, ctx->d_bdpt_state.resize(static_cast<size_t>(kBdptStateWords) * n_items));
+  CUDA_TRY(ctx, ctx->d_bdpt_events.resize(static_cast<size_t>(2 * kBdptMaxEvents) * n_items));
+  CUDA_TRY(ctx, ctx->d_bdpt_queue.resize(n_items));
+  BdptPool pool;
+  // (the arrays may be larger than this render needs: the state words are n_items apart, whatever the allocation)
+  pool.state = ctx->d_bdpt_state.ptr;
+  pool.events = ctx->d_bdpt_events.ptr;
+  pool.q_connect = ctx->d_bdpt_queue.ptr;
+  pool.n_items = n_items;
+  cudaStream_t stream = ctx->stream;
+  int sm_count = 148, resident = 1;
+  CUDA_TRY(ctx, cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device));
+  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, bdpt_connect_kernel<Accel>, kBdptConnectBlock, 0));
+  const unsigned int connect_grid = static_cast<unsigned int>(sm_count * std::max(1, resident));
+  const unsigned int grow_grid = n_items / kBdptGrowBlock;
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_begin, stream));
+  // every item starts in the "take a pair" phase: all-zero ids
+  CUDA_TRY(ctx, cudaMemsetAsync(pool.state + 3 * static_cast<size_t>(n_items), 0, sizeof(float4) * n_items, stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(&ctx->d_ctl.ptr->cursor_bdpt, 0, sizeof(unsigned long long), stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(&ctx->d_ctl.ptr->bdpt_n_connect[0], 0, 4 * sizeof(unsigned int), stream));
+  Control* seen = ctx->h_ctl;
+  for (uint32_t iteration = 0;;) {
+    for (int step = 0; step < kStepsPerPoll; step++, iteration++) {
+      bdpt_grow_kernel<Accel><<<grow_grid, kBdptGrowBlock, 0, stream>>>(args, pool, total_pairs, cap, iteration & 1u);
+      bdpt_connect_kernel<Accel><<<connect_grid, kBdptConnectBlock, 0, stream>>>(args, pool, iteration & 1u);
+      ctx->stats.kernel_launches += 2;
+    }
+    CUDA_TRY(ctx, cudaMemcpyAsync(seen, args.ctl, sizeof(Control), cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+    CUDA_TRY(ctx, cudaGetLastError());
+    if (seen->bdpt_done >= n_items) break;
+  }
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_end, stream));
+  CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_end));
+  float ms = 0;
+  CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end));
+  ctx->stats.last_render_ms = ms;
+  ctx->samples_done += params->sample_count;
+  return AMBER_CUDA_OK;
+}
+
 // Bidirectional path tracing (bdpt.cuh): one kernel, one thread per (pixel, sample).
 int render_bdpt(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, uint32_t n_pixels, uint64_t total_pairs) {
   int rc = bind_constants(ctx);
@@ -1161,6 +1231,9 @@ int render_bdpt(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, uin
   args.estimator = params->estimator;
   args.inv_n_pixels = 1.0f / static_cast<float>(n_pixels);
   const int cap = params->max_depth ? static_cast<int>(params->max_depth) : kBdptMaxEvents;
+  if (bdpt_wavefront_selected(ctx->use_bvh))
+    return ctx->use_bvh ? render_bdpt_wavefront<WideBvh>(ctx, params, args, total_pairs, cap)
+                        : render_bdpt_wavefront<ConstList>(ctx, params, args, total_pairs, cap);
   // persistent warps: one resident wave, lanes fetch pair indices from ctl->cursor_bdpt
   int resident = 0, sm_count = 148;
   CUDA_TRY(ctx, cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device));

@@ -144,7 +144,9 @@ __device__ __forceinline__ HitRecord closest_lane_inline<WideBvh>(const SceneVie
 
 #endif
 
-template <class Accel>
+// kCopy: each kernel that casts gets its own copy of the out-of-line walk (ptxas 12.9 crashes on a module in which two
+// of the wavefront kernels share the BVH instantiation).
+template <class Accel, int kCopy = 0>
 __device__ __noinline__ HitRecord closest_lane(const SceneView& scene, const Ray& ray) {
   return closest_lane_inline<Accel>(scene, ray);
 }
@@ -294,16 +296,12 @@ __device__ __forceinline__ void bdpt_begin_subpath(const RenderArgs& args, bool 
   sp.n = 1;
 }
 
-// One iteration of the generators' loop: cast, append the event, Russian roulette.  Returns false when
-// the subpath is complete (miss, roulette, or `cap` events).
-template <class Accel>
-__device__ __forceinline__ bool bdpt_grow_subpath(const SceneView& scene, const bool kImportance, SequentialRng& rng,
-                                               int cap, BdptEvent* out, BdptSubpath& sp, BdptCounters& count) {
-  if (sp.n >= cap) return false;
-  const Ray ray = sp.ray;
-  const HitRecord hit = closest_lane<Accel>(scene, ray);
-  count.casts++;
+// One iteration of the generators' loop: cast (bdpt_grow_subpath), then append the event and play Russian roulette
+// (bdpt_grow_event).  Both return false when the subpath is complete (miss, roulette, or `cap` events).
+__device__ __forceinline__ bool bdpt_grow_event(const SceneView& scene, const bool kImportance, SequentialRng& rng, int cap,
+                                                BdptEvent* out, BdptSubpath& sp, const HitRecord& hit) {
   if (hit.prim < 0) return false;
+  const Ray ray = sp.ray;
   float3 x, hn;
   int material_index;
   surface_point(scene, ray, hit, x, hn, material_index);
@@ -334,6 +332,14 @@ __device__ __forceinline__ bool bdpt_grow_subpath(const SceneView& scene, const 
   sp.normal = hn;
   sp.weight = sp.weight * ((1.0f / p_rr_forward) * scatter.weight);
   return sp.n < cap;
+}
+template <class Accel, int kCopy = 0>
+__device__ __forceinline__ bool bdpt_grow_subpath(const SceneView& scene, const bool kImportance, SequentialRng& rng,
+                                               int cap, BdptEvent* out, BdptSubpath& sp, BdptCounters& count) {
+  if (sp.n >= cap) return false;
+  const HitRecord hit = closest_lane<Accel, kCopy>(scene, sp.ray);
+  count.casts++;
+  return bdpt_grow_event(scene, kImportance, rng, cap, out, sp, hit);
 }
 
 struct BdptContribution {
@@ -374,7 +380,7 @@ __device__ __forceinline__ BdptContribution bdpt_connect_t0(const BdptEvent* le)
 }
 
 // Connect, s >= 1 and t >= 1 (:938-1016).  le / ee are register copies of the two endpoints.
-template <class Accel>
+template <class Accel, int kCopy = 0>
 __device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene, const BdptEvent* le, const BdptEvent* ee,
                                                       BdptCounters& count) {
   BdptContribution c = empty_contribution();
@@ -411,7 +417,7 @@ __device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene,
   // endpoint's object.  The eye's leading event carries the lens's own aperture object, which
   // no cast ever returns, so t = 1 connections contribute nothing in the reference -- nor here.
   if (ee->leading()) return c;
-  const HitRecord hit = closest_lane<Accel>(scene, shadow);
+  const HitRecord hit = closest_lane<Accel, kCopy>(scene, shadow);
   count.casts++;
   if (hit.prim != ee->object()) return c;
   c.edge_gf = geometry_factor(lp, ep, le->normal(), ee->normal());
@@ -717,6 +723,271 @@ __global__ void __launch_bounds__(BdptLaunch<Accel>::kThreads, BdptLaunch<Accel>
     atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(casts));
     atomicAdd(&args.ctl->splats, static_cast<unsigned long long>(splats));
     atomicAdd(&args.ctl->paths, static_cast<unsigned long long>(n_pairs));
+  }
+}
+
+// =====================================================================================================
+// The same algorithm as a WAVEFRONT: a pool of items, each one (pixel, sample) pair in flight,
+// state in global memory, two kernels per iteration.
+//   bdpt_grow_kernel     one thread per item, every item of the pool: take a new pair / start the eye subpath where
+//                        due, then ONE step of the subpath generator (cast, event, roulette) -- the state machine's
+//                        "start light", "start eye" and "grow" steps, which every item is in at any time except while it
+//                        waits for its connections, so no queue is needed and every lane of the launch has work.
+//                        (Splitting it into a cast kernel and an event kernel whose blocks deal their items out in order
+//                        of the material hit was measured: 134 + 143 us against 190 us for the one kernel -- the split
+//                        pays the state traffic twice and the start steps still diverge.)
+//   bdpt_connect_kernel  the items whose eye subpath ended in this iteration (a queue): the candidates of the 32 items
+//                        of a warp are POOLED and dealt out lane by lane (prefix sums in shared memory), so a sample
+//                        with 200 candidates does not hold up one with 2; measurements go to the film one by one.
+// The subpath state is a structure of arrays (coalesced: thread i <-> item i); the events are an array of structures per
+// item (80-byte events read through pointers by the same connection / MIS code as the one-kernel version).
+struct BdptPool {
+  float4* state;        // [kBdptStateWords][n_items]
+  BdptEvent* events;    // [n_items][2 * kBdptMaxEvents]: light subpath, eye subpath
+  uint32_t* q_connect;  // [n_items]
+  uint32_t n_items;     // a multiple of kBdptGrowBlock
+};
+// state words: 0 ray.o + weight.x | 1 ray.d + weight.y | 2 normal + weight.z | 3 pixel, sample, rng index, packed |
+//              4 specular, eye_surface (growing subpath), spec_l, eye_l (finished light subpath) | 5 the rng's Philox block
+// packed: events so far [0,5) | eye side 5 | ends on light 6 | phase [7,9) | s_max [9,14)
+constexpr int kBdptStateWords = 6;
+constexpr int kBdptGrowBlock = 128;
+enum : uint32_t { kWaveStartLight = 0, kWaveGrow = 1, kWaveStartEye = 2, kWaveDone = 3 };
+
+#ifndef AMBER_BDPT_GROW_BLOCKS
+#define AMBER_BDPT_GROW_BLOCKS 6
+#endif
+#ifndef AMBER_BDPT_CONNECT_BLOCKS
+#define AMBER_BDPT_CONNECT_BLOCKS 5
+#endif
+constexpr uint32_t kPackedCount = 31u, kPackedEyeSide = 32u, kPackedEndsOnLight = 64u;
+
+template <class Accel>
+__global__ void __launch_bounds__(kBdptGrowBlock, AMBER_BDPT_GROW_BLOCKS) bdpt_grow_kernel(const RenderArgs args, const BdptPool pool,
+                                                                                            unsigned long long total_pairs, int cap,
+                                                                                            uint32_t parity) {
+  constexpr uint32_t kFull = 0xffffffffu;
+  const uint32_t i = blockIdx.x * kBdptGrowBlock + threadIdx.x;  // < n_items: the grid is exact
+  const uint32_t lane = threadIdx.x & 31u, lane_lt = (1u << lane) - 1u;
+  const size_t n = pool.n_items;
+  uint4 ids = reinterpret_cast<const uint4*>(pool.state + 3 * n)[i];
+  uint32_t pixel = ids.x, sample = ids.y;
+  uint32_t phase = (ids.w >> 7) & 3u;
+  BdptCounters count;
+  count.casts = 0;
+  count.splats = 0;
+  uint32_t pairs = 0, newly_done = 0;
+  // new pairs: one atomic per warp
+  const uint32_t want = __ballot_sync(kFull, phase == kWaveStartLight);
+  if (want) {
+    const int leader = __ffs(want) - 1;
+    unsigned long long base = 0;
+    if (static_cast<int>(lane) == leader)
+      base = atomicAdd(&args.ctl->cursor_bdpt, static_cast<unsigned long long>(__popc(want)));
+    base = __shfl_sync(kFull, base, leader);
+    if (phase == kWaveStartLight) {
+      const unsigned long long pair = base + __popc(want & lane_lt);
+      if (pair >= total_pairs) {
+        phase = kWaveDone;
+        newly_done = 1;
+      } else {
+        pixel = static_cast<uint32_t>(pair % args.n_pixels);
+        sample = static_cast<uint32_t>(args.sample_begin + (pair / args.n_pixels) * args.sample_stride);
+        pairs = 1;
+      }
+    }
+  }
+  if (i == 0) args.ctl->bdpt_connect_cursor = 0;  // for this iteration's connect kernel
+  const bool active = phase != kWaveDone;
+  BdptEvent* const L = pool.events + static_cast<size_t>(i) * (2 * kBdptMaxEvents);
+  BdptEvent* const E = L + kBdptMaxEvents;
+  SequentialRng rng;
+  BdptSubpath sp;
+  bool eye_side = false, more = false;
+  uint32_t s_max = (ids.w >> 9) & 31u, spec_l = 0, eye_l = 0;
+  if (active) {
+    if (phase == kWaveStartLight) {
+      rng.init(args.seed, pixel, sample, 0x40000000u);
+      bdpt_begin_subpath(args, true, pixel, rng, L, sp);
+    } else if (phase == kWaveStartEye) {
+      const uint4 masks = reinterpret_cast<const uint4*>(pool.state + 4 * n)[i];
+      spec_l = masks.z;
+      eye_l = masks.w;
+      rng.init(args.seed, pixel, sample, 0x40000001u);
+      bdpt_begin_subpath(args, false, pixel, rng, E, sp);
+      eye_side = true;
+    } else {
+      const float4 a = pool.state[i], b = pool.state[n + i], c = pool.state[2 * n + i];
+      const uint4 masks = reinterpret_cast<const uint4*>(pool.state + 4 * n)[i];
+      sp.ray.o = v3(a);
+      sp.ray.d = v3(b);
+      sp.normal = v3(c);
+      sp.weight = v3(a.w, b.w, c.w);
+      sp.n = static_cast<int>(ids.w & kPackedCount);
+      sp.specular = masks.x;
+      sp.eye_surface = masks.y;
+      spec_l = masks.z;
+      eye_l = masks.w;
+      sp.ends_on_light = false;  // (a subpath that goes on did not end on a light)
+      eye_side = (ids.w & kPackedEyeSide) != 0;
+      rng.init(args.seed, pixel, sample, eye_side ? 0x40000001u : 0x40000000u);
+      rng.i = ids.z;
+      rng.block = reinterpret_cast<const uint4*>(pool.state + 5 * n)[i];
+    }
+    more = bdpt_grow_subpath<Accel, 1>(args.scene, !eye_side, rng, cap, eye_side ? E : L, sp, count);
+  }
+  bool to_connect = false;
+  if (active) {
+    if (more) {
+      phase = kWaveGrow;
+    } else if (!eye_side) {
+      s_max = static_cast<uint32_t>(sp.n);
+      spec_l = sp.specular;
+      eye_l = sp.eye_surface;
+      phase = kWaveStartEye;
+    } else {
+      // the candidate list of this sample (see bdpt_kernel): anything to connect?
+      const int t_max = sp.n;
+      const uint32_t s_set = (~spec_l | 1u) & ((s_max >= 32u ? 0u : (1u << s_max)) - 1u);
+      const uint32_t t_set = (~sp.specular & ~1u) & ((t_max >= 32 ? 0u : (1u << t_max)) - 1u);
+      const int candidates = ((t_max >= 2 && sp.ends_on_light) ? 1 : 0) + __popc(eye_l) + __popc(s_set) * __popc(t_set);
+      to_connect = candidates > 0;
+      phase = kWaveStartLight;
+    }
+  }
+  const uint32_t queued = __ballot_sync(kFull, to_connect);
+  if (queued) {
+    const int leader = __ffs(queued) - 1;
+    uint32_t base = 0;
+    if (static_cast<int>(lane) == leader) base = atomicAdd(&args.ctl->bdpt_n_connect[parity], __popc(queued));
+    base = __shfl_sync(kFull, base, leader);
+    if (to_connect) pool.q_connect[base + __popc(queued & lane_lt)] = i;
+  }
+  if (active) {
+    pool.state[i] = make_float4(sp.ray.o.x, sp.ray.o.y, sp.ray.o.z, sp.weight.x);
+    pool.state[n + i] = make_float4(sp.ray.d.x, sp.ray.d.y, sp.ray.d.z, sp.weight.y);
+    pool.state[2 * n + i] = make_float4(sp.normal.x, sp.normal.y, sp.normal.z, sp.weight.z);
+    reinterpret_cast<uint4*>(pool.state + 4 * n)[i] = make_uint4(sp.specular, sp.eye_surface, spec_l, eye_l);
+    reinterpret_cast<uint4*>(pool.state + 5 * n)[i] = rng.block;
+    ids = make_uint4(pixel, sample, rng.i,
+                     static_cast<uint32_t>(sp.n) | (eye_side ? kPackedEyeSide : 0u) | (sp.ends_on_light ? kPackedEndsOnLight : 0u) |
+                         (phase << 7) | (s_max << 9));
+  } else {
+    ids.w = (ids.w & ~(3u << 7)) | (kWaveDone << 7);
+  }
+  reinterpret_cast<uint4*>(pool.state + 3 * n)[i] = ids;
+  const uint32_t casts = __reduce_add_sync(kFull, count.casts);
+  const uint32_t n_pairs = __reduce_add_sync(kFull, pairs);
+  const uint32_t n_done = __reduce_add_sync(kFull, newly_done);
+  if (lane == 0) {
+    if (casts) atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(casts));
+    if (n_pairs) atomicAdd(&args.ctl->paths, static_cast<unsigned long long>(n_pairs));
+    if (n_done) atomicAdd(&args.ctl->bdpt_done, n_done);
+  }
+}
+
+constexpr int kBdptConnectBlock = 128;
+template <class Accel>
+__global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) bdpt_connect_kernel(const RenderArgs args, const BdptPool pool, uint32_t parity) {
+  constexpr uint32_t kFull = 0xffffffffu;
+  constexpr int kWarps = kBdptConnectBlock / 32;
+  __shared__ uint32_t s_first[kWarps][32];   // index of an item's first candidate in the warp's pooled list
+  __shared__ uint32_t s_item[kWarps][32], s_pixel[kWarps][32], s_counts[kWarps][32];
+  __shared__ uint32_t s_spec_l[kWarps][32], s_spec_e[kWarps][32], s_eye_l[kWarps][32];
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const uint32_t n_queued = args.ctl->bdpt_n_connect[parity];
+  // the other counter is the one the next iteration's grow kernel appends to; its last reader was the previous connect
+  if (blockIdx.x == 0 && threadIdx.x == 0) args.ctl->bdpt_n_connect[parity ^ 1u] = 0;
+  const size_t n = pool.n_items;
+  BdptCounters count;
+  count.casts = 0;
+  count.splats = 0;
+  // chunks of 32 queue entries are taken from a counter (the grow kernel of this iteration reset it): an item has 0 to
+  // ~200 candidates, and with a fixed assignment the launch lasts as long as its unluckiest warp
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(&args.ctl->bdpt_connect_cursor, 32u);
+    base = __shfl_sync(kFull, base, 0);
+    if (base >= n_queued) break;
+    const bool have = base + lane < n_queued;
+    const uint32_t item = have ? pool.q_connect[base + lane] : 0u;
+    uint32_t candidates = 0;
+    if (have) {
+      const uint4 ids = reinterpret_cast<const uint4*>(pool.state + 3 * n)[item];
+      const uint4 masks = reinterpret_cast<const uint4*>(pool.state + 4 * n)[item];
+      const uint32_t t_max = ids.w & 31u, s_max = (ids.w >> 9) & 31u;
+      const uint32_t spec_e = masks.x, spec_l = masks.z, eye_l = masks.w;
+      const uint32_t n_s0 = (t_max >= 2u && ((ids.w >> 6) & 1u)) ? 1u : 0u;
+      const uint32_t s_set = (~spec_l | 1u) & ((s_max >= 32u ? 0u : (1u << s_max)) - 1u);
+      const uint32_t t_set = (~spec_e & ~1u) & ((t_max >= 32u ? 0u : (1u << t_max)) - 1u);
+      candidates = n_s0 + __popc(eye_l) + __popc(s_set) * __popc(t_set);
+      s_item[warp][lane] = item;
+      s_pixel[warp][lane] = ids.x;
+      s_counts[warp][lane] = s_max | (t_max << 8) | (n_s0 << 16);
+      s_spec_l[warp][lane] = spec_l;
+      s_spec_e[warp][lane] = spec_e;
+      s_eye_l[warp][lane] = eye_l;
+    }
+    uint32_t scan = candidates;
+#pragma unroll
+    for (int delta = 1; delta < 32; delta <<= 1) {
+      const uint32_t up = __shfl_up_sync(kFull, scan, delta);
+      if (lane >= static_cast<uint32_t>(delta)) scan += up;
+    }
+    s_first[warp][lane] = scan - candidates;
+    const uint32_t total = __shfl_sync(kFull, scan, 31);
+    __syncwarp();
+    for (uint32_t c = lane; c < total; c += 32u) {
+      // owner: the last item whose first candidate is <= c (items without candidates share their index with the next)
+      int owner = 0;
+#pragma unroll
+      for (int step = 16; step > 0; step >>= 1)
+        if (owner + step < 32 && s_first[warp][owner + step] <= c) owner += step;
+      const int j = static_cast<int>(c - s_first[warp][owner]);
+      const BdptEvent* const L = pool.events + static_cast<size_t>(s_item[warp][owner]) * (2 * kBdptMaxEvents);
+      const BdptEvent* const E = L + kBdptMaxEvents;
+      const uint32_t counts = s_counts[warp][owner];
+      const int s_max = counts & 0xff, t_max = (counts >> 8) & 0xff, n_s0 = (counts >> 16) & 1;
+      const uint32_t spec_l = s_spec_l[warp][owner], spec_e = s_spec_e[warp][owner], eye_l = s_eye_l[warp][owner];
+      const int n_t0 = __popc(eye_l);
+      const uint32_t s_set = (~spec_l | 1u) & ((s_max >= 32 ? 0u : (1u << s_max)) - 1u);
+      const uint32_t t_set = (~spec_e & ~1u) & ((t_max >= 32 ? 0u : (1u << t_max)) - 1u);
+      const int n_s = __popc(s_set);
+      BdptContribution contribution;
+      int s, t;
+      if (j < n_s0) {
+        s = 0;
+        t = t_max;
+        contribution = bdpt_connect_s0(args.scene, &E[t_max - 1]);
+      } else if (j < n_s0 + n_t0) {
+        s = nth_set_bit(eye_l, j - n_s0) + 1;
+        t = 0;
+        contribution = bdpt_connect_t0(&L[s - 1]);
+      } else {
+        const int k = j - n_s0 - n_t0;
+        s = nth_set_bit(s_set, k % n_s) + 1;
+        t = nth_set_bit(t_set, k / n_s) + 1;
+        contribution = bdpt_connect<Accel, 2>(args.scene, &L[s - 1], &E[t - 1], count);
+      }
+      if (max3(contribution.value) > 0.0f) {
+        const float weight = bdpt_mis_weight(args.scene, L, s, spec_l, E, t, spec_e, contribution);
+        if (contribution.has_pixel) {  // light image: / sensor.Size(), :1054-1056
+          film_add(args.film, contribution.pixel, (weight * args.inv_n_pixels) * contribution.value);
+          count.splats++;
+        } else if (weight == weight) {
+          // (a NaN weight -- a 0 * inf among the pdf ratios of a degenerate path -- never reaches the film in the
+          // one-kernel version either: there it makes the sample's whole measurement NaN, which fails `> 0`)
+          film_add(args.film, s_pixel[warp][owner], weight * contribution.value);
+        }
+      }
+    }
+    __syncwarp();
+  }
+  const uint32_t casts = __reduce_add_sync(kFull, count.casts);
+  const uint32_t splats = __reduce_add_sync(kFull, count.splats);
+  if (lane == 0) {
+    if (casts) atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(casts));
+    if (splats) atomicAdd(&args.ctl->splats, static_cast<unsigned long long>(splats));
   }
 }
 

@@ -762,6 +762,43 @@ def test_bidirectional_path_tracing_matches_oracle_and_path_tracing(device, orac
         device.render(0, 1, max_depth=17, estimator=capi.ESTIMATOR_BDPT)
 
 
+def test_bdpt_wavefront_equals_the_one_kernel_version(device, cornell, monkeypatch):
+    """Two implementations of the same estimator (bdpt.cuh): the wavefront (pool of pixel samples, grow + connect
+    kernels; the default on the constant-memory list) and the one-kernel state machine (the default on the BVH).  Same
+    random streams, same arithmetic: the images differ only by the order of the film's float additions -- and, on the
+    BVH scene, both run on the other one's home ground."""
+    from amber_b200 import Sensor, capi, cornel_mesh
+    for scene, size, spp in ((cornell, 96, 24), (cornel_mesh(subdivisions=3), 48, 8)):
+        device.upload_scene(scene)
+        device.set_sensor(Sensor(size, size))
+        images, stats = {}, {}
+        for mode in ("megakernel", "wavefront"):
+            monkeypatch.setenv("AMBER_CUDA_BDPT", mode)
+            device.film_clear()
+            before = device.stats()
+            device.render(0, spp, seed=21, estimator=capi.ESTIMATOR_BDPT)
+            images[mode], done = device.resolve()
+            after = device.stats()
+            stats[mode] = tuple(after[k] - before[k] for k in ("paths", "closest_rays", "light_splats"))
+            assert done == spp
+        monkeypatch.delenv("AMBER_CUDA_BDPT")
+        assert stats["wavefront"] == stats["megakernel"], stats           # pixel samples, casts, light-image splats
+        assert stats["wavefront"][0] == spp * size * size
+        a, b = images["megakernel"], images["wavefront"]
+        assert np.isfinite(b).all()
+        frac = image_agreement(b, a, rtol=1e-4)
+        print(f"bdpt wavefront vs one kernel, {size}x{size}x{spp}: {frac:.5f} of pixels agree to 1e-4")
+        assert frac >= 0.999
+        assert abs(float(b.mean()) - float(a.mean())) <= 1e-5 * float(a.mean())
+    # a pool smaller than the job: items take several pairs in turn
+    monkeypatch.setenv("AMBER_CUDA_BDPT_POOL", "2048")
+    monkeypatch.setenv("AMBER_CUDA_BDPT", "wavefront")
+    device.film_clear()
+    device.render(0, spp, seed=21, estimator=capi.ESTIMATOR_BDPT)
+    small_pool, _ = device.resolve()
+    assert image_agreement(small_pool, images["wavefront"], rtol=1e-4) >= 0.999
+
+
 def test_light_and_bidirectional_tracing_through_the_bvh(device, oracle_lib):
     """Rows N2 / N3 on a scene above the constant-memory limit: the light tracer's wavefront and the
     BDPT kernel's per-thread walk of the 4-wide BVH against the brute-force oracle."""
