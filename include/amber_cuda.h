@@ -83,14 +83,18 @@ extern "C" {
  *   paths started on the lights (LightSet::GenerateRay, include/amber/scene/light_set.h:83-104),
  *   scattered with Material::SampleImportance; a path that lands on the aperture is mapped to a
  *   pixel by the lens (BasicThin::Response, src/amber/scene/lens_thin.cc:109-130) and its weight
- *   / (W*H) is added there.  Emitters must be triangles. */
+ *   / (W*H) is added there.  Emitters are triangles or spheres (a sphere is sampled as the reference's
+ *   SphereSA does, src/amber/scene/primitive_sphere.cc:116-122). */
 #define AMBER_CUDA_ESTIMATOR_LIGHT_TRACING 2
 /* BDPT (row N3): sample for sample src/amber/rendering/algorithm_bdpt.cc:116-148 over
  *   include/amber/rendering/bidirectional_path_sampling.h (GenerateLightSubpath,
  *   GenerateEyeSubpath, Connect for every (s, t), balance-heuristic MIS weights, light image) --
  *   one sample = one light subpath + one eye subpath per pixel.  max_depth is the number of
- *   events per subpath (0 = 16, the maximum; the reference has no cap).  Emitters must be
- *   triangles. */
+ *   events per subpath (0 = 16, the maximum; the reference has no cap).  Emitters as for light
+ *   tracing.  Two implementations with the same results up to float summation order: a wavefront over a
+ *   pool of pixel samples (default when the scene is in constant memory; it allocates 5.6 GB of device
+ *   memory on first use) and one persistent kernel (default with the BVH); the environment variable
+ *   AMBER_CUDA_BDPT=wavefront|megakernel forces one. */
 #define AMBER_CUDA_ESTIMATOR_BDPT 3
 
 typedef struct amber_cuda_ctx amber_cuda_ctx;
