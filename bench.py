@@ -20,7 +20,9 @@ all host threads) on a bounded sample of the same workload instead.
 After the timed headline the same process measures, once each, what BASELINE.json's other configs
 ask for (keys `strong`, `config4`, `config5` of the same line): the headline job split over the N
 ranks (strong scaling), config 4 (1.3 M-triangle mesh, 2048^2 x 64 spp split over the ranks, with the
-roofline of the BVH kernels), and at N = 8 config 5 (4096^2 x 16 384 spp split over the ranks).
+roofline of the BVH kernels), and at N = 8 config 5 (4096^2 x 16 384 spp split over the ranks).  At N = 1
+`other_estimators` adds the throughput of light tracing and bidirectional path tracing
+on the headline scene.
 """
 from __future__ import annotations
 
@@ -485,6 +487,29 @@ def run_gpu(args) -> None:
                 c5.update({"mean": float(mean_image.mean()), "samples_in_film": samples,
                            "mean_times_pixels_over_1024x1024": float(mean_image.mean()) * 16.0})
             extras["config5"] = c5
+
+        # ---- rows N2 / N3 of SURVEY 8(f) on the headline scene (one GPU only; not part of the headline) ------
+        if world == 1:
+            dev.upload_scene(scene)
+            dev.set_sensor(Sensor(WIDTH, HEIGHT))
+            rows = {}
+            for name, other, spp, depth in (("light_tracing", capi.ESTIMATOR_LIGHT_TRACING, 64, MAX_DEPTH),
+                                                ("bidirectional_path_tracing", capi.ESTIMATOR_BDPT, 32, 0)):
+                best_ms, best_stats = None, None
+                for _ in range(2):
+                    dev.film_clear()
+                    dev.render(0, spp, seed=SEED, max_depth=depth, estimator=other)
+                    st = dev.stats()
+                    if best_ms is None or st["last_render_ms"] < best_ms:
+                        best_ms, best_stats = st["last_render_ms"], st
+                samples = float(spp) * WIDTH * HEIGHT
+                rows[name] = {"msamples_per_s": samples / best_ms / 1e3, "ms": best_ms, "spp": spp,
+                              "closest_rays_per_sample": best_stats["closest_rays"] / samples,
+                              "film_splats_per_sample": best_stats["light_splats"] / samples}
+            rows["light_tracing"]["note"] = "one sample = one light path per pixel (algorithm_lt.cc:112-122)"
+            rows["bidirectional_path_tracing"]["note"] = ("one sample = one light + one eye subpath per pixel, every (s, t) connected "
+                                                          "(bidirectional_path_sampling.h); wavefront implementation (DESIGN 4.10)")
+            extras["other_estimators"] = rows
 
     if rank != 0:
         if distributed:
