@@ -1156,6 +1156,7 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, const amber_cuda_re
 // Pool: 2 M items = 5.4 GB of events + 200 MB of state (512 k / 1 M / 2 M / 4 M items: 601 / 682 / 726 / 739 M pixel samples/s
 // on the Cornell box at 64 spp).  AMBER_CUDA_BDPT_POOL overrides it (experiments).
 constexpr uint32_t kBdptPoolItems = 1u << 21;
+constexpr int AMBER_CUDA_ENOMEM_POOL = -1000;  // internal: the wavefront's pool could not be allocated
 uint32_t bdpt_pool_items() {
   const char* text = std::getenv("AMBER_CUDA_BDPT_POOL");
   const long long wanted = text ? std::atoll(text) : 0;
@@ -1175,9 +1176,16 @@ int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* p
                           uint64_t total_pairs, int cap) {
   const uint64_t wanted = std::min<uint64_t>(bdpt_pool_items(), total_pairs);
   const uint32_t n_items = static_cast<uint32_t>((wanted + kBdptGrowBlock - 1) / kBdptGrowBlock * kBdptGrowBlock);
-  CUDA_TRY(ctx, ctx->d_bdpt_state.resize(static_cast<size_t>(kBdptStateWords) * n_items));
-  CUDA_TRY(ctx, ctx->d_bdpt_events.resize(static_cast<size_t>(2 * kBdptMaxEvents) * n_items));
-  CUDA_TRY(ctx, ctx->d_bdpt_queue.resize(n_items));
+  if (ctx->d_bdpt_state.resize(static_cast<size_t>(kBdptStateWords) * n_items) != cudaSuccess ||
+      ctx->d_bdpt_events.resize(static_cast<size_t>(2 * kBdptMaxEvents) * n_items) != cudaSuccess ||
+      ctx->d_bdpt_queue.resize(n_items) != cudaSuccess) {
+    // no room for the pool (2.7 KB per item): the caller runs the one-kernel version, which needs none
+    cudaGetLastError();
+    ctx->d_bdpt_state.release();
+    ctx->d_bdpt_events.release();
+    ctx->d_bdpt_queue.release();
+    return AMBER_CUDA_ENOMEM_POOL;
+  }
   BdptPool pool;
   // (the arrays may be larger than this render needs: the state words are n_items apart, whatever the allocation)
   pool.state = ctx->d_bdpt_state.ptr;
@@ -1231,9 +1239,11 @@ int render_bdpt(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, uin
   args.estimator = params->estimator;
   args.inv_n_pixels = 1.0f / static_cast<float>(n_pixels);
   const int cap = params->max_depth ? static_cast<int>(params->max_depth) : kBdptMaxEvents;
-  if (bdpt_wavefront_selected(ctx->use_bvh))
-    return ctx->use_bvh ? render_bdpt_wavefront<WideBvh>(ctx, params, args, total_pairs, cap)
-                        : render_bdpt_wavefront<ConstList>(ctx, params, args, total_pairs, cap);
+  if (bdpt_wavefront_selected(ctx->use_bvh)) {
+    rc = ctx->use_bvh ? render_bdpt_wavefront<WideBvh>(ctx, params, args, total_pairs, cap)
+                      : render_bdpt_wavefront<ConstList>(ctx, params, args, total_pairs, cap);
+    if (rc != AMBER_CUDA_ENOMEM_POOL) return rc;
+  }
   // persistent warps: one resident wave, lanes fetch pair indices from ctl->cursor_bdpt
   int resident = 0, sm_count = 148;
   CUDA_TRY(ctx, cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device));
