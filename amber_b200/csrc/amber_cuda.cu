@@ -24,6 +24,7 @@
 #include "bvh.cuh"
 #include "bvh_build.h"
 #include "kernels.cuh"
+#include "bvh_build_gpu.cuh"
 
 namespace amber_cuda {
 
@@ -518,6 +519,21 @@ int ensure_pool(amber_cuda_ctx* ctx, uint32_t slots) {
   return AMBER_CUDA_OK;
 }
 
+// f(begin, end) over [0, n) on the host's threads (large scenes: the per-triangle loops of upload_scene)
+template <class F>
+void parallel_ranges(size_t n, F&& f) {
+  const size_t threads = n < (1u << 16) ? 1 : std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+  if (threads == 1) {
+    f(static_cast<size_t>(0), n);
+    return;
+  }
+  const size_t per = (n + threads - 1) / threads;
+  std::vector<std::thread> pool;
+  for (size_t t = 1; t < threads; t++) pool.emplace_back([&f, t, per, n]() { f(std::min(n, t * per), std::min(n, (t + 1) * per)); });
+  f(static_cast<size_t>(0), std::min(n, per));
+  for (auto& t : pool) t.join();
+}
+
 // Depth of the flattened 4-wide tree (root = depth 1); a node step pushes at most 3 children,
 // so 3 * depth + 1 stack entries per lane can never overflow.
 int wide_bvh_depth(const bvh_build::WideBvhHost& bvh) {
@@ -699,9 +715,25 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   bvh_build::WideBvhHost bvh;
   if (use_bvh) {
     std::vector<float> verts(tri_ids.size() * 9);
-    for (size_t k = 0; k < tri_ids.size(); k++)
-      std::memcpy(&verts[9 * k], scene->primitives[tri_ids[k]].data, 9 * sizeof(float));
-    bvh = bvh_build::build(verts.data(), static_cast<uint32_t>(tri_ids.size()));
+    parallel_ranges(tri_ids.size(), [&](size_t begin, size_t end) {
+      for (size_t k = begin; k < end; k++) std::memcpy(&verts[9 * k], scene->primitives[tri_ids[k]].data, 9 * sizeof(float));
+    });
+    // AMBER_CUDA_BVH_BUILDER=lbvh: the tree is built on the device (bvh_build_gpu.cuh): tens of milliseconds instead
+    // of half a second, for a tree that traces slower -- worth it when the render is shorter than the host build.
+    const char* builder = std::getenv("AMBER_CUDA_BVH_BUILDER");
+    const auto bvh_t0 = std::chrono::steady_clock::now();
+    bool built = false;
+    if (bvh_build::kWidth == 4 && builder && std::strcmp(builder, "lbvh") == 0 && tri_ids.size() > 64) {
+      built = bvh_gpu::build(verts.data(), static_cast<uint32_t>(tri_ids.size()), ctx->stream, bvh) == cudaSuccess;
+      if (!built) {
+        cudaGetLastError();
+        bvh = bvh_build::WideBvhHost();
+      }
+    }
+    if (!built) bvh = bvh_build::build(verts.data(), static_cast<uint32_t>(tri_ids.size()));
+    trace(ctx, "upload_scene: %zu triangles, BVH of %u nodes by the %s builder in %.1f ms", tri_ids.size(), bvh.n_nodes,
+          built ? "device (lbvh)" : "host (binned SAH)",
+          std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - bvh_t0).count());
     std::vector<uint32_t> reordered(tri_ids.size());
     for (size_t k = 0; k < tri_ids.size(); k++) reordered[k] = tri_ids[bvh.order[k]];
     tri_ids.swap(reordered);
@@ -717,12 +749,14 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
   std::vector<int32_t> tri_material(n_tris), sphere_material(n_spheres);
   std::vector<float4> spheres(n_spheres);
   ctx->internal_to_prim.assign(n_tris + n_spheres, 0);
-  for (size_t k = 0; k < n_tris; k++) {
-    const amber_cuda_primitive& p = scene->primitives[tri_ids[k]];
-    make_triangle(p.data, tri_isect[k], tri_shade[k]);
-    tri_material[k] = p.material;
-    ctx->internal_to_prim[k] = static_cast<int32_t>(tri_ids[k]);
-  }
+  parallel_ranges(n_tris, [&](size_t begin, size_t end) {
+    for (size_t k = begin; k < end; k++) {
+      const amber_cuda_primitive& p = scene->primitives[tri_ids[k]];
+      make_triangle(p.data, tri_isect[k], tri_shade[k]);
+      tri_material[k] = p.material;
+      ctx->internal_to_prim[k] = static_cast<int32_t>(tri_ids[k]);
+    }
+  });
   for (size_t k = 0; k < n_spheres; k++) {
     const amber_cuda_primitive& p = scene->primitives[sphere_ids[k]];
     spheres[k] = make_float4(p.data[0], p.data[1], p.data[2], p.data[3]);
@@ -732,7 +766,9 @@ int amber_cuda_upload_scene(amber_cuda_ctx* ctx, const amber_cuda_scene_desc* sc
 
   // hit class of every primitive (internal order): what `shade` sorts a tile by
   std::vector<uint8_t> prim_class(n_tris + n_spheres);
-  for (size_t k = 0; k < n_tris; k++) prim_class[k] = static_cast<uint8_t>(materials[tri_material[k]].kind * 2);
+  parallel_ranges(n_tris, [&](size_t begin, size_t end) {
+    for (size_t k = begin; k < end; k++) prim_class[k] = static_cast<uint8_t>(materials[tri_material[k]].kind * 2);
+  });
   for (size_t k = 0; k < n_spheres; k++)
     prim_class[n_tris + k] = static_cast<uint8_t>(materials[sphere_material[k]].kind * 2 + 1);
 

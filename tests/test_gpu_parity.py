@@ -338,6 +338,38 @@ def test_bvh_far_from_the_coordinate_origin(device, oracle_lib):
     assert lost.mean() <= 2e-4 and (prim == want_prim).mean() >= 0.995
 
 
+def test_bvh_built_on_the_device(device, oracle_lib, monkeypatch):
+    """AMBER_CUDA_BVH_BUILDER=lbvh: the tree comes from the device builder (bvh_build_gpu.cuh: Morton order, binary
+    radix tree, collapsed to the same 4-wide quantised nodes).  Another tree over the same triangles: closest hits
+    against the brute-force oracle, hit for hit against the host-built tree, and images against the oracle."""
+    from amber_b200 import Sensor, cornel_mesh
+    scene = cornel_mesh(subdivisions=5)  # 20 480 + 18 triangles
+    oracle = oracle_lib.Oracle(scene)
+    o, d = oracle.ray_set(256, 256, *FILM, 78, 60000)
+    want_prim, want_t = oracle.cast(o, d, threads=32)
+    results = {}
+    for builder in ("host", "lbvh"):
+        monkeypatch.setenv("AMBER_CUDA_BVH_BUILDER", builder)
+        device.upload_scene(scene)
+        device.set_sensor(Sensor(32, 32))
+        stats = device.stats()
+        assert stats["accel"] == 1 and stats["bvh_nodes"] > 1000
+        results[builder] = (stats["bvh_nodes"],) + tuple(device.cast(o, d))
+        check_cast(results[builder][1], results[builder][2], want_prim, want_t)
+    monkeypatch.delenv("AMBER_CUDA_BVH_BUILDER")
+    assert results["host"][0] != results["lbvh"][0], "the two builders gave the same node count: was the device builder used?"
+    # the primitive ids reported are the caller's (creation order), whatever order a builder put the triangles in
+    same = results["host"][1] == results["lbvh"][1]
+    assert same.mean() >= ID_AGREEMENT
+    assert np.allclose(results["host"][2][same], results["lbvh"][2][same], rtol=T_RTOL, atol=2e-6, equal_nan=True)
+    for estimator in (0, 1):  # (the scene of the last upload is the device-built one)
+        device.film_clear()
+        device.render(0, 8, seed=6, max_depth=16, estimator=estimator)
+        image, _ = device.resolve()
+        want, _ = oracle.render(32, 32, *FILM, 0, 8, 6, 16, estimator=estimator, threads=32)
+        assert image_agreement(image, want) >= 0.985
+
+
 def test_bvh_full_size_mesh_against_brute_force(device, oracle_lib):
     """Config 4's geometry at full size (1 310 720-triangle displaced icosphere + room): the
     persistent BVH traversal against the oracle's brute-force scan on a ray set small enough
