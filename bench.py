@@ -468,6 +468,21 @@ def run_gpu(args) -> None:
             st = dev.stats()
             c4.update({"bvh_nodes": st["bvh_nodes"], "host_build_ms": st["scene_build_ms"], "host_to_device_ms": st["scene_upload_ms"]})
             c4["profile"] = c4_profile
+            if world == 1:
+                # the same job with the tree built on the device (AMBER_CUDA_BVH_BUILDER=lbvh, bvh_build_gpu.cuh)
+                os.environ["AMBER_CUDA_BVH_BUILDER"] = "lbvh"
+                t0 = time.perf_counter()
+                dev.upload_scene(mesh)
+                lbvh_upload_s = time.perf_counter() - t0
+                os.environ.pop("AMBER_CUDA_BVH_BUILDER")
+                dev.set_sensor(Sensor(2048, 2048))
+                st = dev.stats()
+                lbvh = summary(*best_of(2, m_begin, m_count))
+                c4["device_built_tree"] = {"upload_and_bvh_build_s": lbvh_upload_s, "scene_build_ms": st["scene_build_ms"],
+                                           "host_to_device_ms": st["scene_upload_ms"], "bvh_nodes": st["bvh_nodes"],
+                                           "ms": lbvh["ms"], "mrays_per_s": lbvh["mrays_per_s"],
+                                           "note": "Morton-order radix tree built on the GPU: the tree is ready sooner and traces "
+                                                   "slower than the host's binned-SAH tree above (the default)"}
         extras["config4"] = c4
 
         # ---- config 5 (N = 8 only): 4096^2 x 16 384 spp split over the ranks ------------------------------
