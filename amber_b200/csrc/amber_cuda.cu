@@ -119,6 +119,7 @@ struct amber_cuda_ctx {
   DeviceBuffer<float4> d_bdpt_state;
   DeviceBuffer<BdptEvent> d_bdpt_events;
   DeviceBuffer<uint32_t> d_bdpt_queue;
+  DeviceBuffer<uint2> d_bdpt_evaluate;
   DeviceBuffer<Control> d_ctl;
   Control* h_ctl = nullptr;  // pinned
 
@@ -655,7 +656,7 @@ int amber_cuda_destroy(amber_cuda_ctx* ctx) {
   ctx->d_materials.release(); ctx->d_lights.release(); ctx->d_bvh_nodes.release();
   ctx->d_film.release(); ctx->d_resolved.release(); ctx->d_resolved8.release();
   ctx->d_ray.release(); ctx->d_state.release(); ctx->d_hit.release(); ctx->d_shadow.release();
-  ctx->d_bdpt_state.release(); ctx->d_bdpt_events.release(); ctx->d_bdpt_queue.release();
+  ctx->d_bdpt_state.release(); ctx->d_bdpt_events.release(); ctx->d_bdpt_queue.release(); ctx->d_bdpt_evaluate.release();
   ctx->d_q_new.release(); ctx->d_q_shadow.release(); ctx->d_ctl.release(); ctx->d_prim_class.release();
   for (auto& b : ctx->d_scratch_f) b.release();
   for (auto& b : ctx->d_scratch_i) b.release();
@@ -1192,20 +1193,20 @@ int render_loop(amber_cuda_ctx* ctx, const RenderArgs& args, const amber_cuda_re
 // Pool: 2 M items = 5.4 GB of events + 200 MB of state (512 k / 1 M / 2 M / 4 M items: 601 / 682 / 726 / 739 M pixel samples/s
 // on the Cornell box at 64 spp).  AMBER_CUDA_BDPT_POOL overrides it (experiments).
 constexpr uint32_t kBdptPoolItems = 1u << 21;
+// candidates that pass the probe, per pool item and iteration: ~0.25 on the Cornell box; beyond the capacity they are
+// evaluated in place
+constexpr uint32_t kBdptEvaluatePerItem = 2;
 constexpr int AMBER_CUDA_ENOMEM_POOL = -1000;  // internal: the wavefront's pool could not be allocated
 uint32_t bdpt_pool_items() {
   const char* text = std::getenv("AMBER_CUDA_BDPT_POOL");
   const long long wanted = text ? std::atoll(text) : 0;
   return wanted >= 1024 && wanted <= (1ll << 24) ? static_cast<uint32_t>(wanted) : kBdptPoolItems;
 }
-// Which implementation: the wavefront on the constant-memory list (726 against 470 M pixel samples/s), the one-kernel
-// version on the BVH, where a per-thread walk of the tree inside a lock-step launch waits for its slowest lane every
-// iteration (110 against 131 M/s).  AMBER_CUDA_BDPT=wavefront|megakernel forces one (tests compare the two).
-bool bdpt_wavefront_selected(bool use_bvh) {
+// Which implementation: the wavefront (825 against 470 M pixel samples/s on the Cornell box, 165 against 131 on the
+// 1.3 M-triangle scene) unless AMBER_CUDA_BDPT=megakernel asks for round 1's one-kernel version (tests compare the two).
+bool bdpt_wavefront_selected() {
   const char* choice = std::getenv("AMBER_CUDA_BDPT");
-  if (choice && std::strcmp(choice, "megakernel") == 0) return false;
-  if (choice && std::strcmp(choice, "wavefront") == 0) return true;
-  return !use_bvh;
+  return !(choice && std::strcmp(choice, "megakernel") == 0);
 }
 template <class Accel>
 int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, const RenderArgs& args,
@@ -1214,12 +1215,14 @@ int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* p
   const uint32_t n_items = static_cast<uint32_t>((wanted + kBdptGrowBlock - 1) / kBdptGrowBlock * kBdptGrowBlock);
   if (ctx->d_bdpt_state.resize(static_cast<size_t>(kBdptStateWords) * n_items) != cudaSuccess ||
       ctx->d_bdpt_events.resize(static_cast<size_t>(2 * kBdptMaxEvents) * n_items) != cudaSuccess ||
-      ctx->d_bdpt_queue.resize(n_items) != cudaSuccess) {
+      ctx->d_bdpt_queue.resize(n_items) != cudaSuccess ||
+      ctx->d_bdpt_evaluate.resize(static_cast<size_t>(kBdptEvaluatePerItem) * n_items) != cudaSuccess) {
     // no room for the pool (2.7 KB per item): the caller runs the one-kernel version, which needs none
     cudaGetLastError();
     ctx->d_bdpt_state.release();
     ctx->d_bdpt_events.release();
     ctx->d_bdpt_queue.release();
+    ctx->d_bdpt_evaluate.release();
     return AMBER_CUDA_ENOMEM_POOL;
   }
   BdptPool pool;
@@ -1227,6 +1230,8 @@ int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* p
   pool.state = ctx->d_bdpt_state.ptr;
   pool.events = ctx->d_bdpt_events.ptr;
   pool.q_connect = ctx->d_bdpt_queue.ptr;
+  pool.q_evaluate = ctx->d_bdpt_evaluate.ptr;
+  pool.evaluate_capacity = kBdptEvaluatePerItem * n_items;
   pool.n_items = n_items;
   cudaStream_t stream = ctx->stream;
   int sm_count = 148, resident = 1;
@@ -1238,13 +1243,14 @@ int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* p
   // every item starts in the "take a pair" phase: all-zero ids
   CUDA_TRY(ctx, cudaMemsetAsync(pool.state + 3 * static_cast<size_t>(n_items), 0, sizeof(float4) * n_items, stream));
   CUDA_TRY(ctx, cudaMemsetAsync(&ctx->d_ctl.ptr->cursor_bdpt, 0, sizeof(unsigned long long), stream));
-  CUDA_TRY(ctx, cudaMemsetAsync(&ctx->d_ctl.ptr->bdpt_n_connect[0], 0, 4 * sizeof(unsigned int), stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(&ctx->d_ctl.ptr->bdpt_n_connect[0], 0, 6 * sizeof(unsigned int), stream));
   Control* seen = ctx->h_ctl;
   for (uint32_t iteration = 0;;) {
     for (int step = 0; step < kStepsPerPoll; step++, iteration++) {
       bdpt_grow_kernel<Accel><<<grow_grid, kBdptGrowBlock, 0, stream>>>(args, pool, total_pairs, cap, iteration & 1u);
       bdpt_connect_kernel<Accel><<<connect_grid, kBdptConnectBlock, 0, stream>>>(args, pool, iteration & 1u);
-      ctx->stats.kernel_launches += 2;
+      bdpt_evaluate_kernel<Accel><<<connect_grid, kBdptConnectBlock, 0, stream>>>(args, pool);
+      ctx->stats.kernel_launches += 3;
     }
     CUDA_TRY(ctx, cudaMemcpyAsync(seen, args.ctl, sizeof(Control), cudaMemcpyDeviceToHost, stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(stream));
@@ -1275,7 +1281,7 @@ int render_bdpt(amber_cuda_ctx* ctx, const amber_cuda_render_params* params, uin
   args.estimator = params->estimator;
   args.inv_n_pixels = 1.0f / static_cast<float>(n_pixels);
   const int cap = params->max_depth ? static_cast<int>(params->max_depth) : kBdptMaxEvents;
-  if (bdpt_wavefront_selected(ctx->use_bvh)) {
+  if (bdpt_wavefront_selected()) {
     rc = ctx->use_bvh ? render_bdpt_wavefront<WideBvh>(ctx, params, args, total_pairs, cap)
                       : render_bdpt_wavefront<ConstList>(ctx, params, args, total_pairs, cap);
     if (rc != AMBER_CUDA_ENOMEM_POOL) return rc;

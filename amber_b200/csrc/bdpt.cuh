@@ -380,7 +380,8 @@ __device__ __forceinline__ BdptContribution bdpt_connect_t0(const BdptEvent* le)
 }
 
 // Connect, s >= 1 and t >= 1 (:938-1016).  le / ee are register copies of the two endpoints.
-template <class Accel, int kCopy = 0>
+// kProbe: stop in front of the visibility cast and return the unoccluded value -- "is this candidate worth a cast?"
+template <class Accel, int kCopy = 0, bool kProbe = false>
 __device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene, const BdptEvent* le, const BdptEvent* ee,
                                                       BdptCounters& count) {
   BdptContribution c = empty_contribution();
@@ -417,6 +418,10 @@ __device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene,
   // endpoint's object.  The eye's leading event carries the lens's own aperture object, which
   // no cast ever returns, so t = 1 connections contribute nothing in the reference -- nor here.
   if (ee->leading()) return c;
+  if (kProbe) {
+    c.value = value;
+    return c;
+  }
   const HitRecord hit = closest_lane<Accel, kCopy>(scene, shadow);
   count.casts++;
   if (hit.prim != ee->object()) return c;
@@ -745,6 +750,8 @@ struct BdptPool {
   float4* state;        // [kBdptStateWords][n_items]
   BdptEvent* events;    // [n_items][2 * kBdptMaxEvents]: light subpath, eye subpath
   uint32_t* q_connect;  // [n_items]
+  uint2* q_evaluate;    // [evaluate_capacity] candidates that passed the probe: item, s | t << 8
+  uint32_t evaluate_capacity;
   uint32_t n_items;     // a multiple of kBdptGrowBlock
 };
 // state words: 0 ray.o + weight.x | 1 ray.d + weight.y | 2 normal + weight.z | 3 pixel, sample, rng index, packed |
@@ -758,12 +765,21 @@ enum : uint32_t { kWaveStartLight = 0, kWaveGrow = 1, kWaveStartEye = 2, kWaveDo
 #define AMBER_BDPT_GROW_BLOCKS 6
 #endif
 #ifndef AMBER_BDPT_CONNECT_BLOCKS
-#define AMBER_BDPT_CONNECT_BLOCKS 5
+#define AMBER_BDPT_CONNECT_BLOCKS 6
+#endif
+#ifndef AMBER_BDPT_COPY_ENDPOINTS
+#define AMBER_BDPT_COPY_ENDPOINTS 1
 #endif
 constexpr uint32_t kPackedCount = 31u, kPackedEyeSide = 32u, kPackedEndsOnLight = 64u;
 
+// resident blocks per SM of the grow kernel: 6 at 80 registers on the list, 8 at 64 on the BVH, whose per-thread walk wants
+// warps more than registers (Cornell: 6 / 8 blocks 825 / 739 M pixel samples/s; 1.3 M-triangle scene: 162 / 170)
 template <class Accel>
-__global__ void __launch_bounds__(kBdptGrowBlock, AMBER_BDPT_GROW_BLOCKS) bdpt_grow_kernel(const RenderArgs args, const BdptPool pool,
+struct BdptWave {
+  static constexpr int kGrowBlocks = Accel::kPersistent ? 8 : AMBER_BDPT_GROW_BLOCKS;
+};
+template <class Accel>
+__global__ void __launch_bounds__(kBdptGrowBlock, BdptWave<Accel>::kGrowBlocks) bdpt_grow_kernel(const RenderArgs args, const BdptPool pool,
                                                                                             unsigned long long total_pairs, int cap,
                                                                                             uint32_t parity) {
   constexpr uint32_t kFull = 0xffffffffu;
@@ -797,7 +813,10 @@ __global__ void __launch_bounds__(kBdptGrowBlock, AMBER_BDPT_GROW_BLOCKS) bdpt_g
       }
     }
   }
-  if (i == 0) args.ctl->bdpt_connect_cursor = 0;  // for this iteration's connect kernel
+  if (i == 0) {  // for this iteration's connect kernels
+    args.ctl->bdpt_connect_cursor = 0;
+    args.ctl->bdpt_n_evaluate = 0;
+  }
   const bool active = phase != kWaveDone;
   BdptEvent* const L = pool.events + static_cast<size_t>(i) * (2 * kBdptMaxEvents);
   BdptEvent* const E = L + kBdptMaxEvents;
@@ -887,14 +906,53 @@ __global__ void __launch_bounds__(kBdptGrowBlock, AMBER_BDPT_GROW_BLOCKS) bdpt_g
 }
 
 constexpr int kBdptConnectBlock = 128;
+
+// One connection candidate of an item, start to finish: Connect for (s, t), the MIS weight, the film.
+template <class Accel, int kCopy>
+__device__ __forceinline__ void bdpt_evaluate_candidate(const RenderArgs& args, const BdptPool& pool, uint32_t item, int s, int t,
+                                                        BdptCounters& count) {
+  const size_t n = pool.n_items;
+  const BdptEvent* const L = pool.events + static_cast<size_t>(item) * (2 * kBdptMaxEvents);
+  const BdptEvent* const E = L + kBdptMaxEvents;
+  BdptContribution contribution;
+  if (s == 0) contribution = bdpt_connect_s0(args.scene, &E[t - 1]);
+  else if (t == 0) contribution = bdpt_connect_t0(&L[s - 1]);
+  else {
+#if AMBER_BDPT_COPY_ENDPOINTS
+    const BdptEvent le = L[s - 1], ee = E[t - 1];  // ten 16-byte loads in flight at once instead of one per early-out test
+    contribution = bdpt_connect<Accel, kCopy>(args.scene, &le, &ee, count);
+#else
+    contribution = bdpt_connect<Accel, kCopy>(args.scene, &L[s - 1], &E[t - 1], count);
+#endif
+  }
+  if (!(max3(contribution.value) > 0.0f)) return;
+  const uint4 masks = reinterpret_cast<const uint4*>(pool.state + 4 * n)[item];  // spec_e, -, spec_l, eye_l
+  const float weight = bdpt_mis_weight(args.scene, L, s, masks.z, E, t, masks.x, contribution);
+  if (contribution.has_pixel) {  // light image: / sensor.Size(), :1054-1056
+    film_add(args.film, contribution.pixel, (weight * args.inv_n_pixels) * contribution.value);
+    count.splats++;
+  } else if (weight == weight) {
+    // (a NaN weight -- a 0 * inf among the pdf ratios of a degenerate path -- never reaches the film in the
+    // one-kernel version either: there it makes the sample's whole measurement NaN, which fails `> 0`)
+    const uint32_t pixel = reinterpret_cast<const uint4*>(pool.state + 3 * n)[item].x;
+    film_add(args.film, pixel, weight * contribution.value);
+  }
+}
+
+// Connections, step 1: the candidates of the items whose eye subpath ended in this iteration.  A warp takes 32 queued
+// items, pools their candidates behind a prefix sum and deals them out lane by lane; a lane PROBES its candidate --
+// everything Connect does in front of the visibility cast -- and the one in five that is worth a cast goes onto the
+// evaluation queue.  (Evaluating in place ran the cast and the MIS weight with a fifth of the lanes: 152 us per
+// iteration of a 1 M-item pool against 50 + 50 for probe + evaluate.)
 template <class Accel>
-__global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) bdpt_connect_kernel(const RenderArgs args, const BdptPool pool, uint32_t parity) {
+__global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) bdpt_connect_kernel(const RenderArgs args, const BdptPool pool,
+                                                                                                    uint32_t parity) {
   constexpr uint32_t kFull = 0xffffffffu;
   constexpr int kWarps = kBdptConnectBlock / 32;
   __shared__ uint32_t s_first[kWarps][32];   // index of an item's first candidate in the warp's pooled list
-  __shared__ uint32_t s_item[kWarps][32], s_pixel[kWarps][32], s_counts[kWarps][32];
+  __shared__ uint32_t s_item[kWarps][32], s_counts[kWarps][32];
   __shared__ uint32_t s_spec_l[kWarps][32], s_spec_e[kWarps][32], s_eye_l[kWarps][32];
-  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, lane_lt = (1u << lane) - 1u;
   const uint32_t n_queued = args.ctl->bdpt_n_connect[parity];
   // the other counter is the one the next iteration's grow kernel appends to; its last reader was the previous connect
   if (blockIdx.x == 0 && threadIdx.x == 0) args.ctl->bdpt_n_connect[parity ^ 1u] = 0;
@@ -902,8 +960,7 @@ __global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) 
   BdptCounters count;
   count.casts = 0;
   count.splats = 0;
-  // chunks of 32 queue entries are taken from a counter (the grow kernel of this iteration reset it): an item has 0 to
-  // ~200 candidates, and with a fixed assignment the launch lasts as long as its unluckiest warp
+  // chunks of 32 queue entries are taken from a counter (the grow kernel of this iteration reset it)
   for (;;) {
     uint32_t base = 0;
     if (lane == 0) base = atomicAdd(&args.ctl->bdpt_connect_cursor, 32u);
@@ -922,7 +979,6 @@ __global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) 
       const uint32_t t_set = (~spec_e & ~1u) & ((t_max >= 32u ? 0u : (1u << t_max)) - 1u);
       candidates = n_s0 + __popc(eye_l) + __popc(s_set) * __popc(t_set);
       s_item[warp][lane] = item;
-      s_pixel[warp][lane] = ids.x;
       s_counts[warp][lane] = s_max | (t_max << 8) | (n_s0 << 16);
       s_spec_l[warp][lane] = spec_l;
       s_spec_e[warp][lane] = spec_e;
@@ -937,47 +993,55 @@ __global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) 
     s_first[warp][lane] = scan - candidates;
     const uint32_t total = __shfl_sync(kFull, scan, 31);
     __syncwarp();
-    for (uint32_t c = lane; c < total; c += 32u) {
-      // owner: the last item whose first candidate is <= c (items without candidates share their index with the next)
-      int owner = 0;
+    for (uint32_t c0 = 0; c0 < total; c0 += 32u) {
+      const uint32_t c = c0 + lane;
+      bool worth = false;
+      uint32_t owner_item = 0;
+      int s = 0, t = 0;
+      if (c < total) {
+        // owner: the last item whose first candidate is <= c (items without candidates share their index with the next)
+        int owner = 0;
 #pragma unroll
-      for (int step = 16; step > 0; step >>= 1)
-        if (owner + step < 32 && s_first[warp][owner + step] <= c) owner += step;
-      const int j = static_cast<int>(c - s_first[warp][owner]);
-      const BdptEvent* const L = pool.events + static_cast<size_t>(s_item[warp][owner]) * (2 * kBdptMaxEvents);
-      const BdptEvent* const E = L + kBdptMaxEvents;
-      const uint32_t counts = s_counts[warp][owner];
-      const int s_max = counts & 0xff, t_max = (counts >> 8) & 0xff, n_s0 = (counts >> 16) & 1;
-      const uint32_t spec_l = s_spec_l[warp][owner], spec_e = s_spec_e[warp][owner], eye_l = s_eye_l[warp][owner];
-      const int n_t0 = __popc(eye_l);
-      const uint32_t s_set = (~spec_l | 1u) & ((s_max >= 32 ? 0u : (1u << s_max)) - 1u);
-      const uint32_t t_set = (~spec_e & ~1u) & ((t_max >= 32 ? 0u : (1u << t_max)) - 1u);
-      const int n_s = __popc(s_set);
-      BdptContribution contribution;
-      int s, t;
-      if (j < n_s0) {
-        s = 0;
-        t = t_max;
-        contribution = bdpt_connect_s0(args.scene, &E[t_max - 1]);
-      } else if (j < n_s0 + n_t0) {
-        s = nth_set_bit(eye_l, j - n_s0) + 1;
-        t = 0;
-        contribution = bdpt_connect_t0(&L[s - 1]);
-      } else {
-        const int k = j - n_s0 - n_t0;
-        s = nth_set_bit(s_set, k % n_s) + 1;
-        t = nth_set_bit(t_set, k / n_s) + 1;
-        contribution = bdpt_connect<Accel, 2>(args.scene, &L[s - 1], &E[t - 1], count);
+        for (int step = 16; step > 0; step >>= 1)
+          if (owner + step < 32 && s_first[warp][owner + step] <= c) owner += step;
+        const int j = static_cast<int>(c - s_first[warp][owner]);
+        owner_item = s_item[warp][owner];
+        const BdptEvent* const L = pool.events + static_cast<size_t>(owner_item) * (2 * kBdptMaxEvents);
+        const BdptEvent* const E = L + kBdptMaxEvents;
+        const uint32_t counts = s_counts[warp][owner];
+        const int s_max = counts & 0xff, t_max = (counts >> 8) & 0xff, n_s0 = (counts >> 16) & 1;
+        const uint32_t spec_l = s_spec_l[warp][owner], spec_e = s_spec_e[warp][owner], eye_l = s_eye_l[warp][owner];
+        const int n_t0 = __popc(eye_l);
+        if (j < n_s0) {  // the eye subpath ended on a light (that is what n_s0 says)
+          s = 0;
+          t = t_max;
+          worth = true;
+        } else if (j < n_s0 + n_t0) {  // a light-subpath event on the aperture
+          s = nth_set_bit(eye_l, j - n_s0) + 1;
+          t = 0;
+          worth = true;
+        } else {
+          const uint32_t s_set = (~spec_l | 1u) & ((s_max >= 32 ? 0u : (1u << s_max)) - 1u);
+          const uint32_t t_set = (~spec_e & ~1u) & ((t_max >= 32 ? 0u : (1u << t_max)) - 1u);
+          const int n_s = __popc(s_set), k = j - n_s0 - n_t0;
+          s = nth_set_bit(s_set, k % n_s) + 1;
+          t = nth_set_bit(t_set, k / n_s) + 1;
+#if AMBER_BDPT_COPY_ENDPOINTS
+          const BdptEvent le = L[s - 1], ee = E[t - 1];
+          worth = max3(bdpt_connect<Accel, 3, true>(args.scene, &le, &ee, count).value) > 0.0f;
+#else
+          worth = max3(bdpt_connect<Accel, 3, true>(args.scene, &L[s - 1], &E[t - 1], count).value) > 0.0f;
+#endif
+        }
       }
-      if (max3(contribution.value) > 0.0f) {
-        const float weight = bdpt_mis_weight(args.scene, L, s, spec_l, E, t, spec_e, contribution);
-        if (contribution.has_pixel) {  // light image: / sensor.Size(), :1054-1056
-          film_add(args.film, contribution.pixel, (weight * args.inv_n_pixels) * contribution.value);
-          count.splats++;
-        } else if (weight == weight) {
-          // (a NaN weight -- a 0 * inf among the pdf ratios of a degenerate path -- never reaches the film in the
-          // one-kernel version either: there it makes the sample's whole measurement NaN, which fails `> 0`)
-          film_add(args.film, s_pixel[warp][owner], weight * contribution.value);
+      const uint32_t keep = __ballot_sync(kFull, worth);
+      if (keep) {
+        uint32_t at = 0;
+        if (lane == 0) at = atomicAdd(&args.ctl->bdpt_n_evaluate, __popc(keep));
+        at = __shfl_sync(kFull, at, 0) + __popc(keep & lane_lt);
+        if (worth) {
+          if (at < pool.evaluate_capacity) pool.q_evaluate[at] = make_uint2(owner_item, static_cast<uint32_t>(s) | (static_cast<uint32_t>(t) << 8));
+          else bdpt_evaluate_candidate<Accel, 3>(args, pool, owner_item, s, t, count);  // queue full: in place
         }
       }
     }
@@ -986,6 +1050,29 @@ __global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) 
   const uint32_t casts = __reduce_add_sync(kFull, count.casts);
   const uint32_t splats = __reduce_add_sync(kFull, count.splats);
   if (lane == 0) {
+    if (casts) atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(casts));
+    if (splats) atomicAdd(&args.ctl->splats, static_cast<unsigned long long>(splats));
+  }
+}
+
+// Connections, step 2: one thread per candidate that passed the probe -- the visibility cast, the MIS weight, the film.
+template <class Accel>
+__global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) bdpt_evaluate_kernel(const RenderArgs args, const BdptPool pool) {
+  constexpr uint32_t kFull = 0xffffffffu;
+  const uint32_t n_queued = min(args.ctl->bdpt_n_evaluate, pool.evaluate_capacity);
+  BdptCounters count;
+  count.casts = 0;
+  count.splats = 0;
+  for (uint32_t base = blockIdx.x * kBdptConnectBlock; base < n_queued; base += gridDim.x * kBdptConnectBlock) {
+    const uint32_t j = base + threadIdx.x;
+    if (j < n_queued) {
+      const uint2 candidate = pool.q_evaluate[j];
+      bdpt_evaluate_candidate<Accel, 2>(args, pool, candidate.x, static_cast<int>(candidate.y & 0xffu), static_cast<int>(candidate.y >> 8), count);
+    }
+  }
+  const uint32_t casts = __reduce_add_sync(kFull, count.casts);
+  const uint32_t splats = __reduce_add_sync(kFull, count.splats);
+  if ((threadIdx.x & 31u) == 0) {
     if (casts) atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(casts));
     if (splats) atomicAdd(&args.ctl->splats, static_cast<unsigned long long>(splats));
   }

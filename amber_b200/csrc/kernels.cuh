@@ -54,7 +54,7 @@ struct Control {
   unsigned int raygen_blocks_done;  // blocks of the running raygen launch that have finished (the last one does the bookkeeping)
   unsigned long long cursor_bdpt;  // bdpt_kernel: next (pixel, sample) pair index
   // wavefront BDPT (bdpt.cuh): items waiting for their connections, by iteration parity; items that found no pair left
-  unsigned int bdpt_n_connect[2], bdpt_done, bdpt_connect_cursor;
+  unsigned int bdpt_n_connect[2], bdpt_done, bdpt_connect_cursor, bdpt_n_evaluate, bdpt_pad;
   // profiling mode: traversal work of the BVH kernels: extend node steps, extend triangle tests, connect
   // node steps, connect triangle tests
   unsigned long long bvh_work[4];

@@ -92,9 +92,8 @@ extern "C" {
  *   one sample = one light subpath + one eye subpath per pixel.  max_depth is the number of
  *   events per subpath (0 = 16, the maximum; the reference has no cap).  Emitters as for light
  *   tracing.  Two implementations with the same results up to float summation order: a wavefront over a
- *   pool of pixel samples (default when the scene is in constant memory; it allocates 5.6 GB of device
- *   memory on first use) and one persistent kernel (default with the BVH); the environment variable
- *   AMBER_CUDA_BDPT=wavefront|megakernel forces one. */
+ *   pool of pixel samples (the default; it allocates 5.7 GB of device memory on first use and falls back to
+ *   the other one if that fails) and one persistent kernel (environment variable AMBER_CUDA_BDPT=megakernel). */
 #define AMBER_CUDA_ESTIMATOR_BDPT 3
 
 typedef struct amber_cuda_ctx amber_cuda_ctx;

@@ -795,10 +795,9 @@ def test_bidirectional_path_tracing_matches_oracle_and_path_tracing(device, orac
 
 
 def test_bdpt_wavefront_equals_the_one_kernel_version(device, cornell, monkeypatch):
-    """Two implementations of the same estimator (bdpt.cuh): the wavefront (pool of pixel samples, grow + connect
-    kernels; the default on the constant-memory list) and the one-kernel state machine (the default on the BVH).  Same
-    random streams, same arithmetic: the images differ only by the order of the film's float additions -- and, on the
-    BVH scene, both run on the other one's home ground."""
+    """Two implementations of the same estimator (bdpt.cuh): the wavefront (pool of pixel samples; grow, connect and
+    evaluate kernels; the default) and round 1's one-kernel state machine.  Same random streams, same arithmetic: the
+    images differ only by the order of the film's float additions; on the constant-memory list and on the BVH."""
     from amber_b200 import Sensor, capi, cornel_mesh
     for scene, size, spp in ((cornell, 96, 24), (cornel_mesh(subdivisions=3), 48, 8)):
         device.upload_scene(scene)
