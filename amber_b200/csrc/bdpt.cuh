@@ -786,31 +786,46 @@ __global__ void __launch_bounds__(kBdptGrowBlock, BdptWave<Accel>::kGrowBlocks) 
   const uint32_t i = blockIdx.x * kBdptGrowBlock + threadIdx.x;  // < n_items: the grid is exact
   const uint32_t lane = threadIdx.x & 31u, lane_lt = (1u << lane) - 1u;
   const size_t n = pool.n_items;
+  // the whole state is requested at once, before the phase (in `ids`) says which words this step needs: one round trip
+  // to memory instead of two
   uint4 ids = reinterpret_cast<const uint4*>(pool.state + 3 * n)[i];
+  const float4 state_a = pool.state[i], state_b = pool.state[n + i], state_c = pool.state[2 * n + i];
+  const uint4 state_masks = reinterpret_cast<const uint4*>(pool.state + 4 * n)[i];
+  const uint4 state_block = reinterpret_cast<const uint4*>(pool.state + 5 * n)[i];
   uint32_t pixel = ids.x, sample = ids.y;
   uint32_t phase = (ids.w >> 7) & 3u;
   BdptCounters count;
   count.casts = 0;
   count.splats = 0;
   uint32_t pairs = 0, newly_done = 0;
-  // new pairs: one atomic per warp
+  // new pairs: one atomic per BLOCK (60 k atomics on one address per launch of a 2 M-item pool when every warp asks)
+  constexpr int kWarps = kBdptGrowBlock / 32;
+  __shared__ uint32_t warp_count[kWarps];
+  __shared__ unsigned long long block_pair_base;
+  const uint32_t warp = threadIdx.x >> 5;
   const uint32_t want = __ballot_sync(kFull, phase == kWaveStartLight);
-  if (want) {
-    const int leader = __ffs(want) - 1;
-    unsigned long long base = 0;
-    if (static_cast<int>(lane) == leader)
-      base = atomicAdd(&args.ctl->cursor_bdpt, static_cast<unsigned long long>(__popc(want)));
-    base = __shfl_sync(kFull, base, leader);
-    if (phase == kWaveStartLight) {
-      const unsigned long long pair = base + __popc(want & lane_lt);
-      if (pair >= total_pairs) {
-        phase = kWaveDone;
-        newly_done = 1;
-      } else {
-        pixel = static_cast<uint32_t>(pair % args.n_pixels);
-        sample = static_cast<uint32_t>(args.sample_begin + (pair / args.n_pixels) * args.sample_stride);
-        pairs = 1;
-      }
+  if (lane == 0) warp_count[warp] = __popc(want);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t total = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; w++) total += warp_count[w];
+    block_pair_base = total ? atomicAdd(&args.ctl->cursor_bdpt, static_cast<unsigned long long>(total)) : 0ull;
+  }
+  __syncthreads();
+  if (phase == kWaveStartLight) {
+    uint32_t before = __popc(want & lane_lt);
+#pragma unroll
+    for (int w = 0; w < kWarps; w++)
+      if (static_cast<uint32_t>(w) < warp) before += warp_count[w];
+    const unsigned long long pair = block_pair_base + before;
+    if (pair >= total_pairs) {
+      phase = kWaveDone;
+      newly_done = 1;
+    } else {
+      pixel = static_cast<uint32_t>(pair % args.n_pixels);
+      sample = static_cast<uint32_t>(args.sample_begin + (pair / args.n_pixels) * args.sample_stride);
+      pairs = 1;
     }
   }
   if (i == 0) {  // for this iteration's connect kernels
@@ -829,15 +844,15 @@ __global__ void __launch_bounds__(kBdptGrowBlock, BdptWave<Accel>::kGrowBlocks) 
       rng.init(args.seed, pixel, sample, 0x40000000u);
       bdpt_begin_subpath(args, true, pixel, rng, L, sp);
     } else if (phase == kWaveStartEye) {
-      const uint4 masks = reinterpret_cast<const uint4*>(pool.state + 4 * n)[i];
+      const uint4 masks = state_masks;
       spec_l = masks.z;
       eye_l = masks.w;
       rng.init(args.seed, pixel, sample, 0x40000001u);
       bdpt_begin_subpath(args, false, pixel, rng, E, sp);
       eye_side = true;
     } else {
-      const float4 a = pool.state[i], b = pool.state[n + i], c = pool.state[2 * n + i];
-      const uint4 masks = reinterpret_cast<const uint4*>(pool.state + 4 * n)[i];
+      const float4 a = state_a, b = state_b, c = state_c;
+      const uint4 masks = state_masks;
       sp.ray.o = v3(a);
       sp.ray.d = v3(b);
       sp.normal = v3(c);
@@ -851,7 +866,7 @@ __global__ void __launch_bounds__(kBdptGrowBlock, BdptWave<Accel>::kGrowBlocks) 
       eye_side = (ids.w & kPackedEyeSide) != 0;
       rng.init(args.seed, pixel, sample, eye_side ? 0x40000001u : 0x40000000u);
       rng.i = ids.z;
-      rng.block = reinterpret_cast<const uint4*>(pool.state + 5 * n)[i];
+      rng.block = state_block;
     }
     more = bdpt_grow_subpath<Accel, 1>(args.scene, !eye_side, rng, cap, eye_side ? E : L, sp, count);
   }
@@ -875,7 +890,7 @@ __global__ void __launch_bounds__(kBdptGrowBlock, BdptWave<Accel>::kGrowBlocks) 
     }
   }
   const uint32_t queued = __ballot_sync(kFull, to_connect);
-  if (queued) {
+  if (queued) {  // (per warp: a block-wide count would make every warp wait here for the block's longest cast)
     const int leader = __ffs(queued) - 1;
     uint32_t base = 0;
     if (static_cast<int>(lane) == leader) base = atomicAdd(&args.ctl->bdpt_n_connect[parity], __popc(queued));
