@@ -354,6 +354,8 @@ def test_bvh_built_on_the_device(device, oracle_lib, monkeypatch):
         device.set_sensor(Sensor(32, 32))
         stats = device.stats()
         assert stats["accel"] == 1 and stats["bvh_nodes"] > 1000
+        if stats["bvh_node_bytes"] != 64:
+            pytest.skip("library built with the 8-wide node option: the device builder writes 4-wide nodes only")
         results[builder] = (stats["bvh_nodes"],) + tuple(device.cast(o, d))
         check_cast(results[builder][1], results[builder][2], want_prim, want_t)
     monkeypatch.delenv("AMBER_CUDA_BVH_BUILDER")
