@@ -31,6 +31,9 @@ namespace bvh_gpu {
 inline cudaError_t build(const float*, uint32_t, cudaStream_t, bvh_build::WideBvhHost&) { return cudaErrorNotSupported; }
 #else
 constexpr int kBuildBlock = 256;
+#ifndef AMBER_LBVH_LEAF_MAX
+#define AMBER_LBVH_LEAF_MAX 4  // triangles per leaf of the device-built tree (<= bvh_build::kLeafMax)
+#endif
 
 struct Box3 {
   float3 lo, hi;
@@ -233,7 +236,7 @@ __global__ void __launch_bounds__(kBuildBlock) collapse_kernel(RadixTree tree, i
   if (t >= n_tasks) return;
   const CollapseTask task = tasks[t];
   auto triangles_under = [&](int node) -> uint32_t { return node >= n - 1 ? 1u : tree.last[node] - tree.first[node] + 1u; };
-  auto is_leaf = [&](int node) { return triangles_under(node) <= static_cast<uint32_t>(bvh_build::kLeafMax); };
+  auto is_leaf = [&](int node) { return triangles_under(node) <= static_cast<uint32_t>(AMBER_LBVH_LEAF_MAX); };
   int kids[4];
   int n_kids = 2;
   kids[0] = tree.left[task.node2];
