@@ -1245,10 +1245,12 @@ int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* p
   CUDA_TRY(ctx, cudaMemsetAsync(&ctx->d_ctl.ptr->cursor_bdpt, 0, sizeof(unsigned long long), stream));
   CUDA_TRY(ctx, cudaMemsetAsync(&ctx->d_ctl.ptr->bdpt_n_connect[0], 0, 6 * sizeof(unsigned int), stream));
   Control* seen = ctx->h_ctl;
-  for (uint32_t iteration = 0;;) {
+  const uint64_t max_iterations = 8 * ((total_pairs + n_items - 1) / n_items + 1) * (2ull * kBdptMaxEvents + 2) + 64;
+  for (uint64_t iteration = 0;;) {
     for (int step = 0; step < kStepsPerPoll; step++, iteration++) {
-      bdpt_grow_kernel<Accel><<<grow_grid, kBdptGrowBlock, 0, stream>>>(args, pool, total_pairs, cap, iteration & 1u);
-      bdpt_connect_kernel<Accel><<<connect_grid, kBdptConnectBlock, 0, stream>>>(args, pool, iteration & 1u);
+      const uint32_t parity = static_cast<uint32_t>(iteration & 1u);
+      bdpt_grow_kernel<Accel><<<grow_grid, kBdptGrowBlock, 0, stream>>>(args, pool, total_pairs, cap, parity);
+      bdpt_connect_kernel<Accel><<<connect_grid, kBdptConnectBlock, 0, stream>>>(args, pool, parity);
       bdpt_evaluate_kernel<Accel><<<connect_grid, kBdptConnectBlock, 0, stream>>>(args, pool);
       ctx->stats.kernel_launches += 3;
     }
@@ -1256,6 +1258,11 @@ int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* p
     CUDA_TRY(ctx, cudaStreamSynchronize(stream));
     CUDA_TRY(ctx, cudaGetLastError());
     if (seen->bdpt_done >= n_items) break;
+    // every iteration advances every unfinished item by one step, and a pair takes at most 2 * 16 of them: a render
+    // that is still going far beyond that has a broken invariant -- fail instead of spinning
+    if (iteration > max_iterations)
+      return fail(ctx, AMBER_CUDA_ECUDA, "bidirectional wavefront did not finish within %llu iterations (%u of %u items done)",
+                  static_cast<unsigned long long>(max_iterations), seen->bdpt_done, n_items);
   }
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev_end, stream));
   CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_end));
