@@ -37,6 +37,12 @@ with Device(0) as dev:
     d2 /= np.linalg.norm(d2, axis=1, keepdims=True)
     o2 = o2 + 1e-3 * d2
     octant = (d2[:, 0] < 0).astype(np.uint64) | ((d2[:, 1] < 0).astype(np.uint64) << np.uint64(1)) | ((d2[:, 2] < 0).astype(np.uint64) << np.uint64(2))
+    # shadow-like rays: from the same surface points towards the (tiny) light -- one direction field, scattered origins
+    d_light = np.array([0.0, 0.99, 0.0], dtype=np.float32) - o2
+    d_light /= np.linalg.norm(d_light, axis=1, keepdims=True)
+    shadow_orders = {"shadow-like, random": rng.permutation(len(o2)),
+                     "shadow-like, sorted by origin (morton 30 bit)": np.argsort(morton(o2), kind="stable"),
+                     "shadow-like, sorted by origin (morton 15 bit)": np.argsort(morton(o2, 5), kind="stable")}
     orders = {
         "pixel order": np.arange(len(o2)),
         "random": rng.permutation(len(o2)),
@@ -44,12 +50,12 @@ with Device(0) as dev:
         "sorted by octant, origin": np.argsort((octant << np.uint64(30)) | morton(o2), kind="stable"),
         "sorted by origin (morton 12 bit)": np.argsort(morton(o2, 4), kind="stable"),
     }
-    for name, perm in orders.items():
+    for name, perm in list(orders.items()) + list(shadow_orders.items()):
         m = len(perm)
         o4 = torch.zeros((m, 4), dtype=torch.float32, device="cuda")
         d4 = torch.zeros((m, 4), dtype=torch.float32, device="cuda")
         o4[:, :3] = torch.from_numpy(o2[perm]).cuda()
-        d4[:, :3] = torch.from_numpy(d2[perm]).cuda()
+        d4[:, :3] = torch.from_numpy((d_light if name.startswith("shadow") else d2)[perm]).cuda()
         h4 = torch.empty((m, 4), dtype=torch.float32, device="cuda")
         torch.cuda.synchronize()
         times = [dev.cast_device(o4.data_ptr(), d4.data_ptr(), m, h4.data_ptr()) for _ in range(8)]
