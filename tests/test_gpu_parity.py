@@ -437,6 +437,29 @@ def test_bvh_full_size_mesh_against_the_reference_bvh(device):
     print(f"mesh8 golden: id agreement {agree.mean():.6f} on {len(prim)} rays")
 
 
+def test_device_built_bvh_at_full_size_against_the_reference_bvh(device, monkeypatch):
+    """The same golden hits (the reference's own BVH over the 1.3 M triangles) through the tree built on the device."""
+    from amber_b200 import cornel_mesh
+    g = golden("mesh8_cast.npz")
+    monkeypatch.setenv("AMBER_CUDA_BVH_BUILDER", "lbvh")
+    device.upload_scene(cornel_mesh(subdivisions=8))
+    monkeypatch.delenv("AMBER_CUDA_BVH_BUILDER")
+    stats = device.stats()
+    if stats["bvh_node_bytes"] != 64:
+        pytest.skip("library built with the 8-wide node option: the device builder writes 4-wide nodes only")
+    assert stats["bvh_nodes"] != 281134, "the host builder's node count: was the device builder used?"
+    prim, t = device.cast(g["origins"], g["directions"])
+    agree = prim == g["prim"]
+    assert agree.mean() >= ID_AGREEMENT, f"hit ids agree on {agree.mean():.6f}"
+    both = agree & (g["prim"] >= 0)
+    err = np.abs(t[both] - g["t"][both])
+    assert np.all(err <= T_RTOL * g["t"][both] + 2e-6), f"max abs t error {err.max():.3e}"
+    assert np.isnan(t[agree & (g["prim"] < 0)]).all()
+    print(f"mesh8 golden, device-built tree ({stats['bvh_nodes']} nodes, scene prepared in {stats['scene_build_ms']:.0f} ms): "
+          f"id agreement {agree.mean():.6f}")
+    device.scene = None  # the next test that wants this mesh uploads it again with the default builder
+
+
 def test_full_size_properties(cornell_device):
     """Config 2 geometry (Cornell 1024x1024) at a few spp: properties that do not need an
     oracle run of that size."""
