@@ -120,6 +120,8 @@ struct amber_cuda_ctx {
   DeviceBuffer<BdptEvent> d_bdpt_events;
   DeviceBuffer<uint32_t> d_bdpt_queue;
   DeviceBuffer<uint2> d_bdpt_evaluate;
+  DeviceBuffer<float4> d_bdpt_evaluate_ray;
+  DeviceBuffer<float2> d_bdpt_evaluate_hit;
   DeviceBuffer<Control> d_ctl;
   Control* h_ctl = nullptr;  // pinned
 
@@ -571,7 +573,9 @@ int configure_bvh_launch(amber_cuda_ctx* ctx, const bvh_build::WideBvhHost& bvh)
                            reinterpret_cast<const void*>(&connect_kernel<WideBvh>),
                            reinterpret_cast<const void*>(&cast_bvh_kernel),
                            reinterpret_cast<const void*>(&extend_bvh_counting_kernel),
-                           reinterpret_cast<const void*>(&connect_bvh_counting_kernel)};
+                           reinterpret_cast<const void*>(&connect_bvh_counting_kernel),
+                           reinterpret_cast<const void*>(&bdpt_trace_kernel),
+                           reinterpret_cast<const void*>(&bdpt_trace_evaluate_kernel)};
   int resident = 1 << 30;
   for (const void* k : kernels) {
     // the limit is per function and process-wide: always the maximum, so that a later upload of a shallower
@@ -657,6 +661,7 @@ int amber_cuda_destroy(amber_cuda_ctx* ctx) {
   ctx->d_film.release(); ctx->d_resolved.release(); ctx->d_resolved8.release();
   ctx->d_ray.release(); ctx->d_state.release(); ctx->d_hit.release(); ctx->d_shadow.release();
   ctx->d_bdpt_state.release(); ctx->d_bdpt_events.release(); ctx->d_bdpt_queue.release(); ctx->d_bdpt_evaluate.release();
+  ctx->d_bdpt_evaluate_ray.release(); ctx->d_bdpt_evaluate_hit.release();
   ctx->d_q_new.release(); ctx->d_q_shadow.release(); ctx->d_ctl.release(); ctx->d_prim_class.release();
   for (auto& b : ctx->d_scratch_f) b.release();
   for (auto& b : ctx->d_scratch_i) b.release();
@@ -1216,13 +1221,17 @@ int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* p
   if (ctx->d_bdpt_state.resize(static_cast<size_t>(kBdptStateWords) * n_items) != cudaSuccess ||
       ctx->d_bdpt_events.resize(static_cast<size_t>(2 * kBdptMaxEvents) * n_items) != cudaSuccess ||
       ctx->d_bdpt_queue.resize(n_items) != cudaSuccess ||
-      ctx->d_bdpt_evaluate.resize(static_cast<size_t>(kBdptEvaluatePerItem) * n_items) != cudaSuccess) {
+      ctx->d_bdpt_evaluate.resize(static_cast<size_t>(kBdptEvaluatePerItem) * n_items) != cudaSuccess ||
+      (Accel::kPersistent && (ctx->d_bdpt_evaluate_ray.resize(2 * static_cast<size_t>(kBdptEvaluatePerItem) * n_items) != cudaSuccess ||
+                              ctx->d_bdpt_evaluate_hit.resize(static_cast<size_t>(kBdptEvaluatePerItem) * n_items) != cudaSuccess))) {
     // no room for the pool (2.7 KB per item): the caller runs the one-kernel version, which needs none
     cudaGetLastError();
     ctx->d_bdpt_state.release();
     ctx->d_bdpt_events.release();
     ctx->d_bdpt_queue.release();
     ctx->d_bdpt_evaluate.release();
+    ctx->d_bdpt_evaluate_ray.release();
+    ctx->d_bdpt_evaluate_hit.release();
     return AMBER_CUDA_ENOMEM_POOL;
   }
   BdptPool pool;
@@ -1231,6 +1240,8 @@ int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* p
   pool.events = ctx->d_bdpt_events.ptr;
   pool.q_connect = ctx->d_bdpt_queue.ptr;
   pool.q_evaluate = ctx->d_bdpt_evaluate.ptr;
+  pool.evaluate_ray = ctx->d_bdpt_evaluate_ray.ptr;
+  pool.evaluate_hit = ctx->d_bdpt_evaluate_hit.ptr;
   pool.evaluate_capacity = kBdptEvaluatePerItem * n_items;
   pool.n_items = n_items;
   cudaStream_t stream = ctx->stream;
@@ -1249,8 +1260,19 @@ int render_bdpt_wavefront(amber_cuda_ctx* ctx, const amber_cuda_render_params* p
   for (uint64_t iteration = 0;;) {
     for (int step = 0; step < kStepsPerPoll; step++, iteration++) {
       const uint32_t parity = static_cast<uint32_t>(iteration & 1u);
-      bdpt_grow_kernel<Accel><<<grow_grid, kBdptGrowBlock, 0, stream>>>(args, pool, total_pairs, cap, parity);
+      if constexpr (Accel::kPersistent) {
+        bdpt_begin_kernel<<<grow_grid, kBdptGrowBlock, 0, stream>>>(args, pool, total_pairs);
+        bdpt_trace_kernel<<<ctx->bvh_grid, kBlock, ctx->bvh_smem, stream>>>(args, pool, cap);
+        bdpt_event_kernel<<<grow_grid, kBdptGrowBlock, 0, stream>>>(args, pool, cap, parity);
+        ctx->stats.kernel_launches += 2;
+      } else {
+        bdpt_grow_kernel<Accel><<<grow_grid, kBdptGrowBlock, 0, stream>>>(args, pool, total_pairs, cap, parity);
+      }
       bdpt_connect_kernel<Accel><<<connect_grid, kBdptConnectBlock, 0, stream>>>(args, pool, parity);
+      if constexpr (Accel::kPersistent) {
+        bdpt_trace_evaluate_kernel<<<ctx->bvh_grid, kBlock, ctx->bvh_smem, stream>>>(args, pool);
+        ctx->stats.kernel_launches++;
+      }
       bdpt_evaluate_kernel<Accel><<<connect_grid, kBdptConnectBlock, 0, stream>>>(args, pool);
       ctx->stats.kernel_launches += 3;
     }

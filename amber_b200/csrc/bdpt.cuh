@@ -381,9 +381,10 @@ __device__ __forceinline__ BdptContribution bdpt_connect_t0(const BdptEvent* le)
 
 // Connect, s >= 1 and t >= 1 (:938-1016).  le / ee are register copies of the two endpoints.
 // kProbe: stop in front of the visibility cast and return the unoccluded value -- "is this candidate worth a cast?"
+// given: the hit of the visibility ray when a traversal kernel has already found it (wavefront on the BVH)
 template <class Accel, int kCopy = 0, bool kProbe = false>
 __device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene, const BdptEvent* le, const BdptEvent* ee,
-                                                      BdptCounters& count) {
+                                                      BdptCounters& count, const HitRecord* given = nullptr) {
   BdptContribution c = empty_contribution();
   if (!le->leading() && le->surface() != kSurfaceDiffuse) return c;
   if (!ee->leading() && ee->surface() != kSurfaceDiffuse) return c;
@@ -422,8 +423,13 @@ __device__ __forceinline__ BdptContribution bdpt_connect(const SceneView& scene,
     c.value = value;
     return c;
   }
-  const HitRecord hit = closest_lane<Accel, kCopy>(scene, shadow);
-  count.casts++;
+  HitRecord hit;
+  if (given) {
+    hit = *given;
+  } else {
+    hit = closest_lane<Accel, kCopy>(scene, shadow);
+    count.casts++;
+  }
   if (hit.prim != ee->object()) return c;
   c.edge_gf = geometry_factor(lp, ep, le->normal(), ee->normal());
   c.value = c.edge_gf * value;
@@ -751,13 +757,16 @@ struct BdptPool {
   BdptEvent* events;    // [n_items][2 * kBdptMaxEvents]: light subpath, eye subpath
   uint32_t* q_connect;  // [n_items]
   uint2* q_evaluate;    // [evaluate_capacity] candidates that passed the probe: item, s | t << 8
+  float4* evaluate_ray; // [2 * evaluate_capacity] BVH only: the candidate's visibility ray (direction.w = 1) or no ray (0)
+  float2* evaluate_hit; // [evaluate_capacity] BVH only: what bdpt_trace_evaluate_kernel found along it
   uint32_t evaluate_capacity;
   uint32_t n_items;     // a multiple of kBdptGrowBlock
 };
 // state words: 0 ray.o + weight.x | 1 ray.d + weight.y | 2 normal + weight.z | 3 pixel, sample, rng index, packed |
-//              4 specular, eye_surface (growing subpath), spec_l, eye_l (finished light subpath) | 5 the rng's Philox block
+//              4 specular, eye_surface (growing subpath), spec_l, eye_l (finished light subpath) | 5 the rng's Philox block |
+//              6 (BVH only) the hit of this iteration's cast: t, primitive
 // packed: events so far [0,5) | eye side 5 | ends on light 6 | phase [7,9) | s_max [9,14)
-constexpr int kBdptStateWords = 6;
+constexpr int kBdptStateWords = 7;
 constexpr int kBdptGrowBlock = 128;
 enum : uint32_t { kWaveStartLight = 0, kWaveGrow = 1, kWaveStartEye = 2, kWaveDone = 3 };
 
@@ -766,6 +775,9 @@ enum : uint32_t { kWaveStartLight = 0, kWaveGrow = 1, kWaveStartEye = 2, kWaveDo
 #endif
 #ifndef AMBER_BDPT_CONNECT_BLOCKS
 #define AMBER_BDPT_CONNECT_BLOCKS 6
+#endif
+#ifndef AMBER_BDPT_EVENT_BLOCKS
+#define AMBER_BDPT_EVENT_BLOCKS 6  // 80 registers, no spills (8 / 10 blocks at 64 / 48 registers: no faster)
 #endif
 #ifndef AMBER_BDPT_SORT_PHASES
 #define AMBER_BDPT_SORT_PHASES 1
@@ -955,12 +967,198 @@ __global__ void __launch_bounds__(kBdptGrowBlock, BdptWave<Accel>::kGrowBlocks) 
   }
 }
 
+// ---- the grow step in three launches, for the BVH -------------------------------------------------------------
+// On the BVH the cast is most of a grow step, and a per-thread walk of the tree inside a lock-step launch runs at a quarter
+// of the rate of the path tracer's warp-cooperative traversal (bvh.cuh, trace_persistent: lanes of a warp kept together
+// by votes, finished lanes refilled).  So there the step is: begin (new pairs, leading events) -> trace (the persistent
+// traversal over the items' rays, hits to state word 6) -> event (the rest of the generator's loop body).
+constexpr int32_t kPrimCapped = -3;  // state word 6 of an item whose subpath already holds `cap` events: no cast was made
+
+__global__ void __launch_bounds__(kBdptGrowBlock) bdpt_begin_kernel(const RenderArgs args, const BdptPool pool, unsigned long long total_pairs) {
+  constexpr uint32_t kFull = 0xffffffffu;
+  constexpr int kWarps = kBdptGrowBlock / 32;
+  __shared__ uint32_t warp_count[kWarps];
+  __shared__ unsigned long long block_pair_base;
+  const uint32_t lane = threadIdx.x & 31u, lane_lt = (1u << lane) - 1u, warp = threadIdx.x >> 5;
+  const size_t n = pool.n_items;
+  // (dealing the block's items to its threads by what they start -- light, eye, nothing -- was measured: 196 us per
+  // launch against 171)
+  const uint32_t i = blockIdx.x * kBdptGrowBlock + threadIdx.x;
+  uint4 ids = reinterpret_cast<const uint4*>(pool.state + 3 * n)[i];
+  uint32_t phase = (ids.w >> 7) & 3u;
+  uint32_t pairs = 0, newly_done = 0;
+  const uint32_t want = __ballot_sync(kFull, phase == kWaveStartLight);
+  if (lane == 0) warp_count[warp] = __popc(want);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t total = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; w++) total += warp_count[w];
+    block_pair_base = total ? atomicAdd(&args.ctl->cursor_bdpt, static_cast<unsigned long long>(total)) : 0ull;
+  }
+  __syncthreads();
+  if (i == 0) {  // for this iteration's trace and connect kernels
+    args.ctl->cursor_cast = 0;
+    args.ctl->cursor_connect = 0;
+    args.ctl->bdpt_connect_cursor = 0;
+    args.ctl->bdpt_n_evaluate = 0;
+  }
+  bool begin = phase == kWaveStartEye;
+  if (phase == kWaveStartLight) {
+    uint32_t before = __popc(want & lane_lt);
+#pragma unroll
+    for (int w = 0; w < kWarps; w++)
+      if (static_cast<uint32_t>(w) < warp) before += warp_count[w];
+    const unsigned long long pair = block_pair_base + before;
+    if (pair >= total_pairs) {
+      newly_done = 1;
+      ids.w = (ids.w & ~(3u << 7)) | (kWaveDone << 7);
+      reinterpret_cast<uint4*>(pool.state + 3 * n)[i] = ids;
+    } else {
+      ids.x = static_cast<uint32_t>(pair % args.n_pixels);
+      ids.y = static_cast<uint32_t>(args.sample_begin + (pair / args.n_pixels) * args.sample_stride);
+      pairs = 1;
+      begin = true;
+    }
+  }
+  if (begin) {
+    const bool eye_side = phase == kWaveStartEye;
+    BdptEvent* const L = pool.events + static_cast<size_t>(i) * (2 * kBdptMaxEvents);
+    SequentialRng rng;
+    BdptSubpath sp;
+    rng.init(args.seed, ids.x, ids.y, eye_side ? 0x40000001u : 0x40000000u);
+    bdpt_begin_subpath(args, !eye_side, ids.x, rng, eye_side ? L + kBdptMaxEvents : L, sp);
+    uint4 masks = make_uint4(sp.specular, sp.eye_surface, 0u, 0u);
+    if (eye_side) {  // the finished light subpath's masks stay
+      const uint4 old = reinterpret_cast<const uint4*>(pool.state + 4 * n)[i];
+      masks.z = old.z;
+      masks.w = old.w;
+    }
+    pool.state[i] = make_float4(sp.ray.o.x, sp.ray.o.y, sp.ray.o.z, sp.weight.x);
+    pool.state[n + i] = make_float4(sp.ray.d.x, sp.ray.d.y, sp.ray.d.z, sp.weight.y);
+    pool.state[2 * n + i] = make_float4(sp.normal.x, sp.normal.y, sp.normal.z, sp.weight.z);
+    reinterpret_cast<uint4*>(pool.state + 4 * n)[i] = masks;
+    reinterpret_cast<uint4*>(pool.state + 5 * n)[i] = rng.block;
+    ids.z = rng.i;
+    ids.w = static_cast<uint32_t>(sp.n) | (eye_side ? kPackedEyeSide : 0u) | (kWaveGrow << 7) | (ids.w & (31u << 9));
+    reinterpret_cast<uint4*>(pool.state + 3 * n)[i] = ids;
+  }
+  const uint32_t n_pairs = __reduce_add_sync(kFull, pairs);
+  const uint32_t n_done = __reduce_add_sync(kFull, newly_done);
+  if (lane == 0) {
+    if (n_pairs) atomicAdd(&args.ctl->paths, static_cast<unsigned long long>(n_pairs));
+    if (n_done) atomicAdd(&args.ctl->bdpt_done, n_done);
+  }
+}
+
+struct BdptCastSource {
+  const RenderArgs& args;
+  const BdptPool& pool;
+  int cap;
+  SphereBound spheres;
+  uint32_t casts;
+  __device__ __forceinline__ uint32_t count() const { return pool.n_items; }
+  __device__ __forceinline__ bool load(uint32_t item, Ray& ray, float& t_best) {
+    const size_t n = pool.n_items;
+    const uint32_t packed = reinterpret_cast<const uint4*>(pool.state + 3 * n)[item].w;
+    if (((packed >> 7) & 3u) != kWaveGrow) return false;
+    if (static_cast<int>(packed & kPackedCount) >= cap) {
+      pool.state[6 * n + item] = make_float4(0.0f, __int_as_float(kPrimCapped), 0.0f, 0.0f);
+      return false;
+    }
+    ray.o = v3(pool.state[item]);
+    ray.d = v3(pool.state[n + item]);
+    t_best = spheres.bound(args.scene, ray);
+    casts++;
+    return true;
+  }
+  __device__ __forceinline__ void store(uint32_t item, const HitRecord& hit, bool found) const {
+    const HitRecord out = spheres.resolve(args.scene, hit, found);
+    pool.state[6 * static_cast<size_t>(pool.n_items) + item] = make_float4(out.t, __int_as_float(out.prim), 0.0f, 0.0f);
+  }
+};
+
+__global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) bdpt_trace_kernel(const RenderArgs args, const BdptPool pool, int cap) {
+  BdptCastSource source{args, pool, cap, {-1}, 0u};
+  WideBvh::trace_persistent<false>(args.scene, source, &args.ctl->cursor_cast);
+  const uint32_t casts = __reduce_add_sync(0xffffffffu, source.casts);
+  if ((threadIdx.x & 31) == 0 && casts) atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(casts));
+}
+
+__global__ void __launch_bounds__(kBdptGrowBlock, AMBER_BDPT_EVENT_BLOCKS) bdpt_event_kernel(const RenderArgs args, const BdptPool pool, int cap, uint32_t parity) {
+  constexpr uint32_t kFull = 0xffffffffu;
+  const uint32_t i = blockIdx.x * kBdptGrowBlock + threadIdx.x;
+  const uint32_t lane = threadIdx.x & 31u, lane_lt = (1u << lane) - 1u;
+  const size_t n = pool.n_items;
+  uint4 ids = reinterpret_cast<const uint4*>(pool.state + 3 * n)[i];
+  const float4 a = pool.state[i], b = pool.state[n + i], c = pool.state[2 * n + i], h = pool.state[6 * n + i];
+  uint4 masks = reinterpret_cast<const uint4*>(pool.state + 4 * n)[i];
+  const uint4 block = reinterpret_cast<const uint4*>(pool.state + 5 * n)[i];
+  bool to_connect = false;
+  if (((ids.w >> 7) & 3u) == kWaveGrow) {
+    BdptEvent* const L = pool.events + static_cast<size_t>(i) * (2 * kBdptMaxEvents);
+    const bool eye_side = (ids.w & kPackedEyeSide) != 0;
+    uint32_t s_max = (ids.w >> 9) & 31u;
+    BdptSubpath sp;
+    sp.ray.o = v3(a);
+    sp.ray.d = v3(b);
+    sp.normal = v3(c);
+    sp.weight = v3(a.w, b.w, c.w);
+    sp.n = static_cast<int>(ids.w & kPackedCount);
+    sp.specular = masks.x;
+    sp.eye_surface = masks.y;
+    sp.ends_on_light = (ids.w & kPackedEndsOnLight) != 0;
+    SequentialRng rng;
+    rng.init(args.seed, ids.x, ids.y, eye_side ? 0x40000001u : 0x40000000u);
+    rng.i = ids.z;
+    rng.block = block;
+    HitRecord hit;
+    hit.t = h.x;
+    hit.prim = __float_as_int(h.y);
+    const bool more = hit.prim != kPrimCapped &&
+                      bdpt_grow_event(args.scene, !eye_side, rng, cap, eye_side ? L + kBdptMaxEvents : L, sp, hit);
+    uint32_t phase = kWaveGrow;
+    if (!more) {
+      if (!eye_side) {
+        s_max = static_cast<uint32_t>(sp.n);
+        masks.z = sp.specular;
+        masks.w = sp.eye_surface;
+        phase = kWaveStartEye;
+      } else {
+        const int t_max = sp.n;
+        const uint32_t s_set = (~masks.z | 1u) & ((s_max >= 32u ? 0u : (1u << s_max)) - 1u);
+        const uint32_t t_set = (~sp.specular & ~1u) & ((t_max >= 32 ? 0u : (1u << t_max)) - 1u);
+        const int candidates = ((t_max >= 2 && sp.ends_on_light) ? 1 : 0) + __popc(masks.w) + __popc(s_set) * __popc(t_set);
+        to_connect = candidates > 0;
+        phase = kWaveStartLight;
+      }
+    }
+    pool.state[i] = make_float4(sp.ray.o.x, sp.ray.o.y, sp.ray.o.z, sp.weight.x);
+    pool.state[n + i] = make_float4(sp.ray.d.x, sp.ray.d.y, sp.ray.d.z, sp.weight.y);
+    pool.state[2 * n + i] = make_float4(sp.normal.x, sp.normal.y, sp.normal.z, sp.weight.z);
+    reinterpret_cast<uint4*>(pool.state + 4 * n)[i] = make_uint4(sp.specular, sp.eye_surface, masks.z, masks.w);
+    reinterpret_cast<uint4*>(pool.state + 5 * n)[i] = rng.block;
+    ids.z = rng.i;
+    ids.w = static_cast<uint32_t>(sp.n) | (eye_side ? kPackedEyeSide : 0u) | (sp.ends_on_light ? kPackedEndsOnLight : 0u) |
+            (phase << 7) | (s_max << 9);
+    reinterpret_cast<uint4*>(pool.state + 3 * n)[i] = ids;
+  }
+  const uint32_t queued = __ballot_sync(kFull, to_connect);
+  if (queued) {
+    const int leader = __ffs(queued) - 1;
+    uint32_t base = 0;
+    if (static_cast<int>(lane) == leader) base = atomicAdd(&args.ctl->bdpt_n_connect[parity], __popc(queued));
+    base = __shfl_sync(kFull, base, leader);
+    if (to_connect) pool.q_connect[base + __popc(queued & lane_lt)] = i;
+  }
+}
+
 constexpr int kBdptConnectBlock = 128;
 
 // One connection candidate of an item, start to finish: Connect for (s, t), the MIS weight, the film.
 template <class Accel, int kCopy>
 __device__ __forceinline__ void bdpt_evaluate_candidate(const RenderArgs& args, const BdptPool& pool, uint32_t item, int s, int t,
-                                                        BdptCounters& count) {
+                                                        BdptCounters& count, const HitRecord* given = nullptr) {
   const size_t n = pool.n_items;
   const BdptEvent* const L = pool.events + static_cast<size_t>(item) * (2 * kBdptMaxEvents);
   const BdptEvent* const E = L + kBdptMaxEvents;
@@ -970,9 +1168,9 @@ __device__ __forceinline__ void bdpt_evaluate_candidate(const RenderArgs& args, 
   else {
 #if AMBER_BDPT_COPY_ENDPOINTS
     const BdptEvent le = L[s - 1], ee = E[t - 1];  // ten 16-byte loads in flight at once instead of one per early-out test
-    contribution = bdpt_connect<Accel, kCopy>(args.scene, &le, &ee, count);
+    contribution = bdpt_connect<Accel, kCopy>(args.scene, &le, &ee, count, given);
 #else
-    contribution = bdpt_connect<Accel, kCopy>(args.scene, &L[s - 1], &E[t - 1], count);
+    contribution = bdpt_connect<Accel, kCopy>(args.scene, &L[s - 1], &E[t - 1], count, given);
 #endif
   }
   if (!(max3(contribution.value) > 0.0f)) return;
@@ -1048,6 +1246,8 @@ __global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) 
       bool worth = false;
       uint32_t owner_item = 0;
       int s = 0, t = 0;
+      float3 ray_o = v3(0.0f, 0.0f, 0.0f), ray_d = v3(0.0f, 0.0f, 0.0f);  // BVH: the visibility ray of a product candidate
+      float ray_reach = 0.0f;                                              // ... and the distance to its eye endpoint
       if (c < total) {
         // owner: the last item whose first candidate is <= c (items without candidates share their index with the next)
         int owner = 0;
@@ -1079,6 +1279,12 @@ __global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) 
 #if AMBER_BDPT_COPY_ENDPOINTS
           const BdptEvent le = L[s - 1], ee = E[t - 1];
           worth = max3(bdpt_connect<Accel, 3, true>(args.scene, &le, &ee, count).value) > 0.0f;
+          if (Accel::kPersistent && worth) {  // as bdpt_connect builds it
+            const float3 lp = le.position(), ep = ee.position();
+            ray_o = lp;
+            ray_d = normalize_exact(v3(ep.x - lp.x, ep.y - lp.y, ep.z - lp.z));
+            ray_reach = sqrtf(dot(ep - lp, ep - lp));
+          }
 #else
           worth = max3(bdpt_connect<Accel, 3, true>(args.scene, &L[s - 1], &E[t - 1], count).value) > 0.0f;
 #endif
@@ -1090,8 +1296,15 @@ __global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) 
         if (lane == 0) at = atomicAdd(&args.ctl->bdpt_n_evaluate, __popc(keep));
         at = __shfl_sync(kFull, at, 0) + __popc(keep & lane_lt);
         if (worth) {
-          if (at < pool.evaluate_capacity) pool.q_evaluate[at] = make_uint2(owner_item, static_cast<uint32_t>(s) | (static_cast<uint32_t>(t) << 8));
-          else bdpt_evaluate_candidate<Accel, 3>(args, pool, owner_item, s, t, count);  // queue full: in place
+          if (at < pool.evaluate_capacity) {
+            pool.q_evaluate[at] = make_uint2(owner_item, static_cast<uint32_t>(s) | (static_cast<uint32_t>(t) << 8));
+            if (Accel::kPersistent) {
+              pool.evaluate_ray[2 * static_cast<size_t>(at)] = make_float4(ray_o.x, ray_o.y, ray_o.z, ray_reach);
+              pool.evaluate_ray[2 * static_cast<size_t>(at) + 1] = make_float4(ray_d.x, ray_d.y, ray_d.z, (s > 0 && t > 0) ? 1.0f : 0.0f);
+            }
+          } else {
+            bdpt_evaluate_candidate<Accel, 3>(args, pool, owner_item, s, t, count);  // queue full: in place
+          }
         }
       }
     }
@@ -1103,6 +1316,38 @@ __global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) 
     if (casts) atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(casts));
     if (splats) atomicAdd(&args.ctl->splats, static_cast<unsigned long long>(splats));
   }
+}
+
+// BVH: the visibility rays of the candidates that passed the probe, through the warp-cooperative traversal.
+struct BdptShadowSource {
+  const RenderArgs& args;
+  const BdptPool& pool;
+  uint32_t n_queued;
+  SphereBound spheres;
+  uint32_t casts;
+  __device__ __forceinline__ uint32_t count() const { return n_queued; }
+  __device__ __forceinline__ bool load(uint32_t j, Ray& ray, float& t_best) {
+    const float4 d = pool.evaluate_ray[2 * static_cast<size_t>(j) + 1];
+    if (d.w == 0.0f) return false;  // s = 0 or t = 0: nothing to cast
+    const float4 o = pool.evaluate_ray[2 * static_cast<size_t>(j)];
+    ray.o = v3(o);
+    ray.d = v3(d);
+    // Connect only asks whether the FIRST object along the ray is the eye endpoint's: nothing beyond the endpoint
+    // (o.w away, plus slack for its own rounding) can be that first object, so the walk need not go there
+    t_best = fminf(spheres.bound(args.scene, ray), o.w * 1.001f + 1e-4f);
+    casts++;
+    return true;
+  }
+  __device__ __forceinline__ void store(uint32_t j, const HitRecord& hit, bool found) const {
+    const HitRecord out = spheres.resolve(args.scene, hit, found);
+    pool.evaluate_hit[j] = make_float2(out.t, __int_as_float(out.prim));
+  }
+};
+__global__ void __launch_bounds__(kBlock, AMBER_BVH_MIN_BLOCKS) bdpt_trace_evaluate_kernel(const RenderArgs args, const BdptPool pool) {
+  BdptShadowSource source{args, pool, min(args.ctl->bdpt_n_evaluate, pool.evaluate_capacity), {-1}, 0u};
+  WideBvh::trace_persistent<false>(args.scene, source, &args.ctl->cursor_connect);
+  const uint32_t casts = __reduce_add_sync(0xffffffffu, source.casts);
+  if ((threadIdx.x & 31) == 0 && casts) atomicAdd(&args.ctl->closest_rays, static_cast<unsigned long long>(casts));
 }
 
 // Connections, step 2: one thread per candidate that passed the probe -- the visibility cast, the MIS weight, the film.
@@ -1117,7 +1362,16 @@ __global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) 
     const uint32_t j = base + threadIdx.x;
     if (j < n_queued) {
       const uint2 candidate = pool.q_evaluate[j];
-      bdpt_evaluate_candidate<Accel, 2>(args, pool, candidate.x, static_cast<int>(candidate.y & 0xffu), static_cast<int>(candidate.y >> 8), count);
+      const int s = static_cast<int>(candidate.y & 0xffu), t = static_cast<int>(candidate.y >> 8);
+      if (Accel::kPersistent && s > 0 && t > 0) {  // bdpt_trace_evaluate_kernel has cast the visibility ray
+        const float2 found = pool.evaluate_hit[j];
+        HitRecord hit;
+        hit.t = found.x;
+        hit.prim = __float_as_int(found.y);
+        bdpt_evaluate_candidate<Accel, 2>(args, pool, candidate.x, s, t, count, &hit);
+      } else {
+        bdpt_evaluate_candidate<Accel, 2>(args, pool, candidate.x, s, t, count);
+      }
     }
   }
   const uint32_t casts = __reduce_add_sync(kFull, count.casts);
