@@ -806,14 +806,13 @@ __global__ void __launch_bounds__(kBdptGrowBlock, BdptWave<Accel>::kGrowBlocks) 
   const size_t n = pool.n_items;
   uint32_t i = blockIdx.x * kBdptGrowBlock + threadIdx.x;  // < n_items: the grid is exact
   if constexpr (BdptWave<Accel>::kSortPhases) {
-  // The block's items are dealt to its threads in order of what they are about to do -- take a pair and start a light
-  // subpath, start the eye subpath, grow a light subpath, grow an eye subpath, nothing -- so that the start code, which a
-  // quarter of the items run in a given iteration, occupies whole warps instead of a few lanes of every warp.
-  __shared__ uint32_t kind_count[5], kind_first[5];
-  __shared__ uint16_t order[kBdptGrowBlock];
-  if (threadIdx.x < 5) kind_count[threadIdx.x] = 0;
-  __syncthreads();
-  {
+    // The block's items are dealt to its threads in order of what they are about to do -- take a pair and start a light
+    // subpath, start the eye subpath, grow a light subpath, grow an eye subpath, nothing -- so that the start code, which
+    // a quarter of the items run in a given iteration, occupies whole warps instead of a few lanes of every warp.
+    __shared__ uint32_t kind_count[5], kind_first[5];
+    __shared__ uint16_t order[kBdptGrowBlock];
+    if (threadIdx.x < 5) kind_count[threadIdx.x] = 0;
+    __syncthreads();
     const uint32_t packed = reinterpret_cast<const uint4*>(pool.state + 3 * n)[i].w;
     const uint32_t item_phase = (packed >> 7) & 3u;
     const uint32_t kind = item_phase == kWaveStartLight ? 0u : item_phase == kWaveStartEye ? 1u
@@ -831,7 +830,6 @@ __global__ void __launch_bounds__(kBdptGrowBlock, BdptWave<Accel>::kGrowBlocks) 
     order[kind_first[kind] + rank] = static_cast<uint16_t>(threadIdx.x);
     __syncthreads();
     i = blockIdx.x * kBdptGrowBlock + order[threadIdx.x];
-  }
   }
   // the whole state is requested at once, before the phase (in `ids`) says which words this step needs: one round trip
   // to memory instead of two
@@ -1287,6 +1285,12 @@ __global__ void __launch_bounds__(kBdptConnectBlock, AMBER_BDPT_CONNECT_BLOCKS) 
           }
 #else
           worth = max3(bdpt_connect<Accel, 3, true>(args.scene, &L[s - 1], &E[t - 1], count).value) > 0.0f;
+          if (Accel::kPersistent && worth) {
+            const float3 lp = L[s - 1].position(), ep = E[t - 1].position();
+            ray_o = lp;
+            ray_d = normalize_exact(v3(ep.x - lp.x, ep.y - lp.y, ep.z - lp.z));
+            ray_reach = sqrtf(dot(ep - lp, ep - lp));
+          }
 #endif
         }
       }
