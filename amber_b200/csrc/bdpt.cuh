@@ -779,58 +779,22 @@ enum : uint32_t { kWaveStartLight = 0, kWaveGrow = 1, kWaveStartEye = 2, kWaveDo
 #ifndef AMBER_BDPT_EVENT_BLOCKS
 #define AMBER_BDPT_EVENT_BLOCKS 6  // 80 registers, no spills (8 / 10 blocks at 64 / 48 registers: no faster)
 #endif
-#ifndef AMBER_BDPT_SORT_PHASES
-#define AMBER_BDPT_SORT_PHASES 1
-#endif
 #ifndef AMBER_BDPT_COPY_ENDPOINTS
 #define AMBER_BDPT_COPY_ENDPOINTS 1
 #endif
 constexpr uint32_t kPackedCount = 31u, kPackedEyeSide = 32u, kPackedEndsOnLight = 64u;
 
-// resident blocks per SM of the grow kernel: 6 at 80 registers on the list, 8 at 64 on the BVH, whose per-thread walk wants
-// warps more than registers (Cornell: 6 / 8 blocks 825 / 739 M pixel samples/s; 1.3 M-triangle scene: 162 / 170)
+// (Constant-memory list only: on the BVH the step is split into begin / trace / event kernels, below.  Dealing a block's
+// items to its threads in order of the step they take -- start light, start eye, grow light, grow eye -- cost the list
+// 3 %: 841 -> 818 M pixel samples/s.)
 template <class Accel>
-struct BdptWave {
-  static constexpr int kGrowBlocks = Accel::kPersistent ? 8 : AMBER_BDPT_GROW_BLOCKS;
-  // deal a block's items to its threads in order of the step they are about to take (see bdpt_grow_kernel): on the BVH
-  // 172 -> 180 M pixel samples/s (a warp of starting items does not hold back a warp of tree walks), on the list
-  // 841 -> 818 (the permuted state accesses and three barriers cost more than the divergence of the start code)
-  static constexpr bool kSortPhases = AMBER_BDPT_SORT_PHASES && Accel::kPersistent;
-};
-template <class Accel>
-__global__ void __launch_bounds__(kBdptGrowBlock, BdptWave<Accel>::kGrowBlocks) bdpt_grow_kernel(const RenderArgs args, const BdptPool pool,
+__global__ void __launch_bounds__(kBdptGrowBlock, AMBER_BDPT_GROW_BLOCKS) bdpt_grow_kernel(const RenderArgs args, const BdptPool pool,
                                                                                             unsigned long long total_pairs, int cap,
                                                                                             uint32_t parity) {
   constexpr uint32_t kFull = 0xffffffffu;
   const uint32_t lane = threadIdx.x & 31u, lane_lt = (1u << lane) - 1u;
   const size_t n = pool.n_items;
-  uint32_t i = blockIdx.x * kBdptGrowBlock + threadIdx.x;  // < n_items: the grid is exact
-  if constexpr (BdptWave<Accel>::kSortPhases) {
-    // The block's items are dealt to its threads in order of what they are about to do -- take a pair and start a light
-    // subpath, start the eye subpath, grow a light subpath, grow an eye subpath, nothing -- so that the start code, which
-    // a quarter of the items run in a given iteration, occupies whole warps instead of a few lanes of every warp.
-    __shared__ uint32_t kind_count[5], kind_first[5];
-    __shared__ uint16_t order[kBdptGrowBlock];
-    if (threadIdx.x < 5) kind_count[threadIdx.x] = 0;
-    __syncthreads();
-    const uint32_t packed = reinterpret_cast<const uint4*>(pool.state + 3 * n)[i].w;
-    const uint32_t item_phase = (packed >> 7) & 3u;
-    const uint32_t kind = item_phase == kWaveStartLight ? 0u : item_phase == kWaveStartEye ? 1u
-                          : item_phase == kWaveDone ? 4u : (packed & kPackedEyeSide) ? 3u : 2u;
-    const uint32_t rank = atomicAdd(&kind_count[kind], 1u);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      uint32_t first = 0;
-      for (int k = 0; k < 5; k++) {
-        kind_first[k] = first;
-        first += kind_count[k];
-      }
-    }
-    __syncthreads();
-    order[kind_first[kind] + rank] = static_cast<uint16_t>(threadIdx.x);
-    __syncthreads();
-    i = blockIdx.x * kBdptGrowBlock + order[threadIdx.x];
-  }
+  const uint32_t i = blockIdx.x * kBdptGrowBlock + threadIdx.x;  // < n_items: the grid is exact
   // the whole state is requested at once, before the phase (in `ids`) says which words this step needs: one round trip
   // to memory instead of two
   uint4 ids = reinterpret_cast<const uint4*>(pool.state + 3 * n)[i];
